@@ -342,3 +342,504 @@ class OraclePort:
         self.last_joint_pos_target[:] = self.joint_pos_target[:]
         self.last_dof_vel[:] = self.dof_vel[:]
         self.last_root_vel[:] = self.robot_root[:, 7:13]
+
+    # ------------------------------------------------------------------ a5: heights
+    def get_heights(self):
+        """LR:1918-1965 (+ stack_heights LR:1967-1970).  Returns [N,2,nx,ny]."""
+        f = self.flat
+        N = self.N
+        if self.plane:
+            top = torch.ones(N, self.nx, self.ny)
+            bottom = torch.zeros(N, self.nx, self.ny)
+            return torch.stack([top, bottom], dim=1)
+        # F3: the yaw-rotated points are discarded; F5: pitch is the previous step's (base_rotation not yet refreshed)
+        self.camera_pitch_angle = self.base_rotation[:, 1].clone()
+        points = self.height_points.clone()
+        points[..., :2] += self.robot_root[:, None, None, :2]
+        if f["camera_zero"]:
+            camera_offset_xy = self.camera_offset[None, :2] * torch.cos(self.camera_pitch_angle[:, None])
+            points[..., :2] += camera_offset_xy[:, None, None]
+        points -= self.env_terrain_origin[:, None, None, :]
+        points = (points / f["horizontal_scale"]).long()
+        px = torch.clip(points[..., 0], 0, f["tile_rows"] - 2)
+        py = torch.clip(points[..., 1], 0, f["tile_cols"] - 2)
+        self.last_px, self.last_py = px, py
+        if self.faithful_gather:
+            samples = self.tile_heights
+            tile = self.env_tile
+            heights = torch.stack([samples[int(tile[e]), :, px[e], py[e]] for e in range(N)], dim=0)
+        else:
+            heights = self.tile_heights[self.env_tile[:, None, None], :, px, py].permute(0, 3, 1, 2)
+        return heights
+
+    # ------------------------------------------------------------------ a6: goal-relative pose
+    def compute_relative_target_pose(self, target_poses):
+        """LR:922-932"""
+        root = self.robot_root
+        relative_linear = target_poses[:, :3] - root[:, :3]
+        relative_linear = quat_apply_yaw_inverse(root[:, 3:7], relative_linear)
+        self.base_rotation = quaternion_to_roll_pitch_yaw(root[:, 3:7])
+        relative_rotation = target_poses[:, 3:] - self.base_rotation
+        relative_rotation = wrap_to_pi(relative_rotation)
+        return relative_linear, relative_rotation
+
+    # ------------------------------------------------------------------ a7: callback
+    def randomize_dof_props(self, env_ids, uniforms, base):
+        """LR:744-764.  `base` = first slot (rng_slots.INTERVAL_STRENGTH or RESET_STRENGTH)."""
+        f = self.flat
+        u = uniforms[env_ids]
+        if f["randomize_motor_strength"]:
+            lo, hi = f["motor_strength_range"]
+            self.motor_strengths[env_ids, :] = u[:, base + 0].unsqueeze(1) * (hi - lo) + lo
+        if f["randomize_motor_offset"]:
+            lo, hi = f["motor_offset_range"]
+            self.motor_offsets[env_ids, :] = u[:, base + 1: base + 13] * (hi - lo) + lo
+        if f["randomize_Kp_factor"]:
+            lo, hi = f["Kp_factor_range"]
+            self.Kp_factors[env_ids, :] = u[:, base + 13].unsqueeze(1) * (hi - lo) + lo
+        if f["randomize_Kd_factor"]:
+            lo, hi = f["Kd_factor_range"]
+            self.Kd_factors[env_ids, :] = u[:, base + 14].unsqueeze(1) * (hi - lo) + lo
+
+    def randomize_gravity(self, external_force=None, gravity_uniform=None):
+        """LR:645-660"""
+        f = self.flat
+        if external_force is not None:
+            self.gravities[:, :] = external_force.unsqueeze(0)
+        elif f["randomize_gravity"]:
+            lo, hi = f["gravity_range"]
+            ext = torch.as_tensor(gravity_uniform, dtype=torch.float32) * (hi - lo) + lo
+            self.gravities[:, :] = ext.unsqueeze(0)
+        gravity = self.gravities[0, :] + torch.Tensor([0, 0, -9.8])
+        self.gravity_vec[:, :] = gravity.unsqueeze(0) / torch.norm(gravity)
+
+    def post_physics_step_callback(self, uniforms, gravity_uniform):
+        """LR:774-848"""
+        f = self.flat
+        if f["observe_heights"]:
+            self.measured_heights = self.get_heights()
+        idx = self.curr_pose_index
+        self.target_poses = self.trajectories[torch.arange(self.N), idx, :]                 # LR:854
+        self.relative_linear, self.relative_rotation = self.compute_relative_target_pose(self.target_poses)
+        self.local_target_poses = self.target_poses                                          # LR:918-920
+        self.local_relative_linear, self.local_relative_rotation = \
+            self.compute_relative_target_pose(self.local_target_poses)
+        # _set_the_target_pose_visual LR:934-947
+        arrow = self.root_states.view(self.N, self.A, 13)[:, self.A - 1, :]
+        arrow[:, :3] = self.local_target_poses[:, :3]
+        arrow[:, 3:7] = quat_from_euler_xyz(self.local_target_poses[:, 3], self.local_target_poses[:, 4],
+                                            self.local_target_poses[:, 5])
+        # interval DR LR:822-824
+        env_ids = (self.episode_length_buf % int(f["rand_interval"]) == 0).nonzero(as_tuple=False).flatten()
+        if len(env_ids) > 0:
+            self.randomize_dof_props(env_ids, uniforms, RS.INTERVAL_STRENGTH)
+        # gravity LR:826-830
+        if self.common_step_counter % int(f["gravity_rand_interval"]) == 0:
+            self.randomize_gravity(gravity_uniform=gravity_uniform)
+        if int(self.common_step_counter - f["gravity_rand_duration"]) % int(f["gravity_rand_interval"]) == 0:
+            self.randomize_gravity(external_force=torch.tensor([0, 0, 0]))
+        # waypoint switching LR:836-848
+        if f["switch_upon_reach"]:
+            self.switched_buf = torch.linalg.norm(self.relative_linear[:, :2], dim=1) < f["switch_dist"]
+        else:
+            self.switched_buf = (self.episode_length_buf % f["switch_interval"] == 0)
+        env_ids = self.switched_buf.nonzero(as_tuple=False).flatten()
+        self.curr_pose_index[env_ids] += 1
+        self.curr_pose_index[env_ids] = torch.clip(self.curr_pose_index[env_ids], max=f["traj_length"] - 1)
+        self.reached_buf = torch.logical_and(self.switched_buf, self.curr_pose_index == f["traj_length"] - 1)
+        plan_buf_linear = torch.linalg.norm(self.local_relative_linear[:, :2], dim=1) < f["switch_dist"]
+        plan_buf_yaw = torch.abs(self.local_relative_rotation[:, 2]) < f["switch_yaw"]
+        self.plan_buf = torch.logical_and(plan_buf_linear, plan_buf_yaw)
+        self.collision_count += torch.sum(
+            (torch.norm(self.contact_forces[:, self.penalised_contact_indices, :], dim=-1) > 0.1).long(), dim=-1)
+
+    # ------------------------------------------------------------------ a8: termination
+    def check_termination(self):
+        """LR:198-216"""
+        f = self.flat
+        self.reset_buf = torch.any(
+            torch.norm(self.contact_forces[:, self.termination_contact_indices, :], dim=-1) > 1., dim=1)
+        self.time_out_buf = self.episode_length_buf > f["max_episode_length"]
+        self.reset_buf |= self.time_out_buf
+        if f["use_terminal_body_height"]:
+            self.body_height_buf = torch.mean(self.robot_root[:, 2].unsqueeze(1), dim=1) < f["terminal_body_height"]
+            self.reset_buf = torch.logical_or(self.body_height_buf, self.reset_buf)
+        if f["terminate_end_of_trajectory"]:
+            reached = torch.logical_and(self.reached_buf, self.episode_length_buf > f["T_reach"])
+            self.reset_buf = torch.logical_or(reached, self.reset_buf)
+        if f["use_terminal_body_rotation"]:
+            self.reset_buf = torch.logical_or(self.reset_buf, self.projected_gravity[:, 2] > 0.0)
+
+    # ------------------------------------------------------------------ a9.1 / a9.2: reward terms
+    # RewardsCrawling: go1_gym/envs/rewards/reward_crawling.py:18-123
+    # TrajectoryTrackingRewards: go1_gym/envs/rewards/trajectory_tracking_reward.py:17-171
+    def _target_lin_vel(self):
+        f = self.flat
+        target_linear_vel = self.relative_linear[:, :2]
+        magnitude = torch.linalg.norm(target_linear_vel, dim=1, keepdim=True)
+        target_linear_vel = target_linear_vel / (magnitude + EPSILON) * f["target_lin_vel"]
+        target_linear_vel = target_linear_vel * (magnitude > f["lin_reaching_criterion"])
+        return target_linear_vel, magnitude
+
+    def _reward_dof_acc(self):
+        return torch.sum(torch.square((self.last_dof_vel - self.dof_vel) / self.flat["dt"]), dim=1)
+
+    def _reward_torques(self):
+        return torch.sum(torch.square(self.torques), dim=1)
+
+    def _reward_dof_pos_limits(self):
+        out_of_limits = -(self.dof_pos - self.dof_pos_limits[:, 0]).clip(max=0.)
+        out_of_limits += (self.dof_pos - self.dof_pos_limits[:, 1]).clip(min=0.)
+        return torch.sum(out_of_limits, dim=1)
+
+    def _reward_collision(self):
+        return torch.sum(1. * (torch.norm(self.contact_forces[:, self.penalised_contact_indices, :], dim=-1) > 0.1), dim=1)
+
+    def _reward_action_rate(self):
+        return torch.sum(torch.square(self.last_actions - self.actions), dim=1)
+
+    def _reward_base_height(self):
+        return torch.square(self.robot_root[:, 2] - self.flat["base_height_target"])
+
+    def _reward_ang_vel_xy(self):
+        return torch.sum(torch.square(self.base_ang_vel[:, :2]), dim=1)
+
+    def _reward_orientation(self):
+        return torch.sum(torch.square(self.projected_gravity[:, :2]), dim=1)
+
+    def _reward_large_vel(self):
+        magnitude = torch.norm(self.base_lin_vel[:, :2], dim=1) > 0.5
+        return torch.sum(torch.square(self.base_lin_vel[:, :2]), dim=1) * magnitude.float()
+
+    def _reward_e2e(self):
+        f = self.flat
+        magnitude = torch.norm(self.relative_linear[:, :2], dim=1)
+        if f["terminate_end_of_trajectory"]:
+            return (magnitude < f["switch_dist"]) * f["max_episode_length"]
+        reached = (magnitude < f["switch_dist"])
+        after_t_reach = self.episode_length_buf > f["T_reach"]
+        linear_vel_error = torch.sum(torch.square(self.base_lin_vel[:, :2]), dim=-1)
+        return torch.exp(-linear_vel_error / f["tracking_sigma_lin"]) * reached.float() * after_t_reach.float()
+
+    def _lin_vel_form(self, allow_prod):
+        f = self.flat
+        target_linear_vel, magnitude = self._target_lin_vel()
+        form = f["lin_vel_form"]
+        if form == "exp":
+            err = torch.sum(torch.square(target_linear_vel - self.base_lin_vel[:, :2]), dim=-1)
+            return torch.exp(-err / f["tracking_sigma_lin"])
+        if form == "l1":
+            return torch.sum(torch.abs(target_linear_vel - self.base_lin_vel[:, :2]), dim=-1)
+        if form == "l2":
+            return torch.sum(torch.square(target_linear_vel - self.base_lin_vel[:, :2]), dim=-1)
+        if form == "prod" and allow_prod:
+            base_vel_magnitude = torch.linalg.norm(self.base_lin_vel[:, :2], dim=1, keepdim=True)
+            rew = target_linear_vel / f["target_lin_vel"] * self.base_lin_vel[:, :2] / (base_vel_magnitude + EPSILON)
+            rew = torch.sum(rew, dim=-1)
+            rew *= (base_vel_magnitude.flatten() > f["small_vel_threshold"])
+            rew += torch.exp(-base_vel_magnitude.flatten() ** 2 / f["tracking_sigma_lin"]) * \
+                (magnitude.flatten() < f["lin_reaching_criterion"])
+            return rew
+        raise NotImplementedError(form)
+
+    def _reward_exploration_lin(self):
+        return self._lin_vel_form(allow_prod=True)
+
+    def _reward_reaching_linear_vel(self):
+        return self._lin_vel_form(allow_prod=False)
+
+    def _reward_exploration_yaw(self):
+        f = self.flat
+        target_angular_vel = self.relative_rotation[:, 2]
+        magnitude = target_angular_vel.abs()
+        target_angular_vel = target_angular_vel / (magnitude + EPSILON) * f["target_ang_vel"]
+        target_angular_vel = target_angular_vel * (magnitude > f["ang_reaching_criterion"])
+        ang_vel_error = torch.square(target_angular_vel - self.base_ang_vel[:, 2])
+        return torch.exp(-ang_vel_error / f["tracking_sigma_ang"])
+
+    _reward_reaching_yaw = _reward_exploration_yaw
+
+    def _reward_reaching_z(self):
+        return torch.square(self.relative_linear[:, 2])
+
+    def _reward_reaching_roll(self):
+        return torch.square(self.relative_rotation[:, 0])
+
+    def _reward_reaching_pitch(self):
+        return torch.square(self.relative_rotation[:, 1])
+
+    def _reward_reaching_yaw_abs(self):
+        return torch.square(self.relative_rotation[:, 2])
+
+    def _reward_dof_vel(self):
+        return torch.sum(torch.square(self.dof_vel), dim=1)
+
+    def _reward_dof_pos(self):
+        return torch.sum(torch.square(self.dof_pos - self.default_dof_pos), dim=1)
+
+    def _reward_task_old(self):
+        f = self.flat
+        target_dist = 0.5
+        r = target_dist / (target_dist + torch.norm(self.relative_linear[:, :2], dim=1)) / f["T_reach"]
+        r = r * (self.episode_length_buf > f["T_reach"])
+        return r
+
+    def _reward_reach_goal(self):
+        return self.reached_buf
+
+    def _reward_reach_goal_t(self):
+        return self.reached_buf * self.episode_length_buf.float()
+
+    def _reward_reach_goal_T(self):
+        return self.reached_buf * (self.episode_length_buf > self.flat["T_reach"]).float()
+
+    def _reward_task(self):
+        f = self.flat
+        target_linear_vel, _ = self._target_lin_vel()
+        err = torch.sum(torch.square(target_linear_vel - self.base_lin_vel[:, :2]), dim=-1)
+        in_dist = torch.norm(self.relative_linear[:, :2], dim=1) < f["large_dist_threshold"]
+        return torch.exp(-err / f["tracking_sigma_lin"]) * in_dist.float()
+
+    def _reward_exploration(self):
+        f = self.flat
+        r = torch.sum(self.base_lin_vel[:, :2] * self.local_relative_linear[:, :2], dim=1)
+        r /= (torch.norm(self.local_relative_linear[:, :2], dim=1) + EPSILON)
+        r /= (torch.norm(self.base_lin_vel[:, :2], dim=1) + EPSILON)
+        r *= (torch.norm(self.base_lin_vel[:, :2], dim=1) > f["small_vel_threshold"]).float()
+        return r
+
+    def _reward_stalling(self):
+        f = self.flat
+        small_vel = torch.norm(self.base_lin_vel[:, :2], dim=1) < f["small_vel_threshold"]
+        large_dist = torch.norm(self.relative_linear[:, :2], dim=1) > f["large_dist_threshold"]
+        return -(small_vel * large_dist).float()
+
+    def _reward_linear_vel(self):
+        return torch.norm(self.base_lin_vel[:, :3], dim=1) > 0.7
+
+    def _reward_lin_vel_z(self):
+        return torch.square(self.base_lin_vel[:, 2])
+
+    def _reward_feet_air_time(self):
+        contact = self.contact_forces[:, self.feet_indices, 2] > 1.
+        contact_filt = torch.logical_or(contact, self.last_contacts)
+        self.last_contacts = contact
+        first_contact = (self.feet_air_time > 0.) * contact_filt
+        self.feet_air_time += self.flat["dt"]
+        rew = torch.sum((self.feet_air_time - 0.5) * first_contact, dim=1)
+        self.feet_air_time *= ~contact_filt
+        return rew
+
+    def _reward_survive(self):
+        return torch.ones(self.N)
+
+    # ------------------------------------------------------------------ a9: reward sum
+    def compute_reward(self, external=None):
+        """LR:320-355"""
+        f = self.flat
+        self.rew_buf[:] = 0.
+        self.rew_buf_pos[:] = 0.
+        self.rew_buf_neg[:] = 0.
+        self.term_values = {}
+        for name in self.reward_names:
+            if name == "external":
+                val = external
+            else:
+                val = getattr(self, "_reward_" + name)()
+            rew = val * self.reward_scales[name]
+            self.term_values[name] = rew.clone() if torch.is_tensor(rew) else rew
+            self.rew_buf += rew
+            if torch.sum(rew) >= 0:
+                self.rew_buf_pos += rew
+            elif torch.sum(rew) <= 0:
+                self.rew_buf_neg += rew
+            self.episode_sums[name] += rew
+            self.command_sums[name] += rew
+        if f["only_positive_rewards"]:
+            self.rew_buf[:] = torch.clip(self.rew_buf[:], min=0.)
+        elif f["only_positive_rewards_ji22_style"]:
+            self.rew_buf[:] = self.rew_buf_pos[:] * torch.exp(self.rew_buf_neg[:] / f["sigma_rew_neg"])
+        self.episode_sums["total"] += self.rew_buf
+        self.episode_sums["total_pos"] += self.rew_buf_pos
+        self.episode_sums["total_neg"] += self.rew_buf_neg
+        if "termination" in self.reward_scales:
+            raise NotImplementedError("termination reward: no container in the reference defines _reward_termination")
+        self.command_sums["ep_timesteps"] += 1
+
+    # ------------------------------------------------------------------ a10: reset
+    def trajectory_function(self, env_ids, uniforms):
+        """go1_gym/envs/trajectories/trajectory_function.py:14-93"""
+        f = self.flat
+        fn = f["traj_function"]
+        root = self.robot_root
+        K = len(env_ids)
+        L = f["traj_length"]
+        if fn == "fixed_target":                                           # :14-26
+            x = torch.arange(1, L + 1).repeat(K, 1) * f["base_x"]
+            x += root[env_ids, 0:1]
+            y = torch.arange(1, L + 1).repeat(K, 1) * f["base_y"]
+            y += root[env_ids, 1:2]
+            z = torch.zeros_like(x) + f["base_z"]
+            yaw = torch.zeros_like(x) * f["base_yaw"]
+            pitch = torch.zeros_like(x) + f["base_pitch"]
+            roll = torch.zeros_like(x) + f["base_roll"]
+            return torch.stack([x, y, z, roll, pitch, yaw], dim=2)
+        u = uniforms[env_ids][:, RS.TRAJ:]
+        if fn == "random_goal":                                            # :28-41
+            x = (u[:, 0:1] - 0.5) * f["x_range"] + f["x_mean"]
+            x += root[env_ids, 0:1]
+            y = (u[:, 1:2] - 0.5) * f["y_range"] + f["y_mean"]
+            y += root[env_ids, 1:2]
+            z = torch.zeros_like(x) + f["base_z"]
+            yaw = u[:, 2:3] * 2 * f["yaw_range"] - f["yaw_range"]
+            pitch = torch.zeros_like(x)
+            roll = torch.zeros_like(x)
+            return torch.stack([x, y, z, roll, pitch, yaw], dim=2)
+        if fn == "random_target":                                          # :70-93
+            ni = f["num_interpolation"]
+            nt = L // ni + 1
+            blk = lambda i: u[:, i * nt:(i + 1) * nt]                      # noqa: E731
+            x = blk(0) * 2 * f["x_range"] - f["x_range"]
+            y = blk(1) * 2 * f["y_range"] - f["y_range"]
+            z = blk(2) * 2 * f["z_range"] - f["z_range"]
+            yaw = blk(3) * 2 * f["yaw_range"] - f["yaw_range"]
+            pitch = blk(4) * 2 * f["pitch_range"] - f["pitch_range"]
+            roll = blk(5) * 2 * f["roll_range"] - f["roll_range"]
+            target_pose = torch.stack([x, y, z, roll, pitch, yaw], dim=2)
+            target_pose[:, 0, :] = 0
+            delta = (target_pose[:, 1:, :] - target_pose[:, :-1, :]) / ni
+            interp = torch.stack([target_pose[:, :-1] + (i + 1) * delta for i in range(ni)], dim=2)
+            interp = interp.reshape(K, -1, 6)
+            interp[:, :, :3] += root[env_ids, :3][:, None, :]
+            return interp
+        raise NotImplementedError(fn)
+
+    def reset_idx(self, env_ids, uniforms):
+        """LR:218-296 with _reset_dofs LR:998-1013, _reset_root_states LR:1015-1052, _resample_trajectory LR:949-953"""
+        f = self.flat
+        if len(env_ids) == 0:
+            return
+        u = uniforms[env_ids]
+        self.randomize_dof_props(env_ids, uniforms, RS.RESET_STRENGTH)
+        # _reset_dofs
+        self.dof_pos[env_ids] = self.default_dof_pos * ((1.5 - 0.5) * u[:, RS.RESET_DOF:RS.RESET_DOF + 12] + 0.5)
+        self.dof_vel[env_ids] = 0.
+        # _reset_root_states
+        root = self.robot_root
+        root[env_ids] = self.base_init_state
+        root[env_ids, :3] += self.env_origins[env_ids]
+        if f["custom_origins"]:
+            xr, yr = f["x_init_range"], f["y_init_range"]
+            root[env_ids, 0:1] += (xr - (-xr)) * u[:, RS.RESET_X:RS.RESET_X + 1] + (-xr)
+            root[env_ids, 1:2] += (yr - (-yr)) * u[:, RS.RESET_Y:RS.RESET_Y + 1] + (-yr)
+            root[env_ids, 0] += f["x_init_offset"]
+            root[env_ids, 1] += f["y_init_offset"]
+        yr = f["yaw_init_range"]
+        init_yaws = (yr - (-yr)) * u[:, RS.RESET_YAW:RS.RESET_YAW + 1] + (-yr)
+        root[env_ids, 3:7] = quat_from_yaw(init_yaws)
+        root[env_ids, 7:13] = (0.5 - (-0.5)) * u[:, RS.RESET_VEL:RS.RESET_VEL + 6] + (-0.5)
+        # _resample_trajectory
+        self.curr_pose_index[env_ids] = 0
+        self.trajectories[env_ids] = self.trajectory_function(env_ids, uniforms)
+        episode_length_buf = self.episode_length_buf.float().clone()
+        self.last_actions[env_ids] = 0.
+        self.last_last_actions[env_ids] = 0.
+        self.last_dof_vel[env_ids] = 0.
+        self.feet_air_time[env_ids] = 0.
+        self.episode_length_buf[env_ids] = 0
+        self.reset_buf[env_ids] = 1
+        self.local_relative_linear[env_ids] = 0.
+        self.local_relative_rotation[env_ids] = 0.
+        self.plan_buf[env_ids] = 1
+        # extras (LR:256-273): what the reference pushes to host deques
+        rec = {"env_ids": env_ids.clone(), "episode_length": episode_length_buf[env_ids].clone(),
+               "reached": self.reached_buf[env_ids].clone(),
+               "goal_distance": torch.norm(self.relative_linear[env_ids], dim=1)}
+        for key in self.episode_sums.keys():
+            rec["rew_" + key] = self.episode_sums[key][env_ids].clone()
+            self.episode_sums[key][env_ids] = 0.
+        self.finished_episodes.append(rec)
+        self.reached_env_buf[env_ids] = self.reached_buf[env_ids]
+        self.collision_env_buf[env_ids] = self.collision_count[env_ids] * self.reached_buf[env_ids]
+        self.collision_count[env_ids] = 0
+        if f["send_timeouts"]:
+            self.time_outs_latched = self.time_out_buf.clone()                # extras["time_outs"], LR:289-291
+        for i in range(len(self.lag_buffer)):
+            self.lag_buffer[i][env_ids, :] = 0
+
+    # ------------------------------------------------------------------ a11: observations
+    def compute_observations(self, noise_uniforms):
+        """LR:357-590"""
+        f = self.flat
+        root = self.robot_root
+        commands = self.local_relative_linear[:, :2]                         # a VIEW in the reference (LR:801-802)
+        parts = [self.projected_gravity]
+        if f["observe_command"]:
+            parts.append(commands * 1.0)                                     # commands_scale = ones (LR:1275)
+        parts += [(self.dof_pos - self.default_dof_pos) * f["obs_scale_dof_pos"],
+                  self.dof_vel * f["obs_scale_dof_vel"], self.actions]
+        obs = torch.cat(parts, dim=-1)
+        if f["observe_command"] and f["timestep_in_obs"]:
+            obs = torch.cat((obs, self.episode_length_buf.unsqueeze(1) / f["max_episode_length"]), dim=-1)
+        if f["observe_heights"]:
+            x_start = int(self.measured_heights.shape[2] // 2 + 1) if f["measure_front_half"] else 0
+            mh = self.measured_heights[:, :, x_start:, :]
+            if f["camera_zero"]:
+                mh -= root[..., 2:3, None, None]                             # POST-reset root z (in place on the view)
+                camera_offset_z = torch.sin(self.camera_pitch_angle) * torch.norm(self.camera_offset[None, :], dim=-1)
+                mh -= camera_offset_z[:, None, None, None]
+                mh = torch.clip(mh, min=-0.3, max=0.3)
+            else:
+                mh = torch.clip(mh, min=0, max=f["ceiling_height"])
+                mh /= f["ceiling_height"]
+                mh -= 0.5
+            mh = mh.reshape(self.N, -1) * f["obs_scale_height"]
+            obs = torch.cat((obs, mh), dim=-1)
+        if f["observe_two_prev_actions"]:
+            obs = torch.cat((obs, self.last_actions), dim=-1)
+        if f["observe_vel"]:
+            if f["global_reference"]:
+                obs = torch.cat((root[:, 7:10] * f["obs_scale_lin_vel"], self.base_ang_vel * f["obs_scale_ang_vel"], obs), dim=-1)
+            else:
+                obs = torch.cat((self.base_lin_vel * f["obs_scale_lin_vel"], self.base_ang_vel * f["obs_scale_ang_vel"], obs), dim=-1)
+        if f["observe_only_ang_vel"]:
+            obs = torch.cat((self.base_ang_vel * f["obs_scale_ang_vel"], obs), dim=-1)
+        if f["observe_only_lin_vel"]:
+            obs = torch.cat((self.base_lin_vel * f["obs_scale_lin_vel"], obs), dim=-1)
+        if f["observe_yaw"]:
+            forward = quat_apply(root[:, 3:7], torch.tensor([1., 0., 0.]).repeat(self.N, 1))
+            heading = torch.atan2(forward[:, 1], forward[:, 0]).unsqueeze(1)
+            obs = torch.cat((obs, heading), dim=-1)
+        if f["observe_contact_states"]:
+            obs = torch.cat((obs, (self.contact_forces[:, self.feet_indices, 2] > 1.).view(self.N, -1) * 1.0), dim=1)
+        if f["add_noise"]:
+            obs += (2 * torch.as_tensor(noise_uniforms, dtype=torch.float32) - 1) * self.noise_scale_vec
+        assert obs.shape[1] == f["num_obs"], (obs.shape, f["num_obs"])
+        self.obs_buf = obs
+        # privileged observations LR:477-590
+        priv = torch.empty(self.N, 0)
+        def add(x, rng, divide=False):
+            nonlocal priv
+            scale, shift = scale_shift(rng)
+            v = (x - shift) / scale if divide else (x - shift) * scale
+            priv = torch.cat((priv, v), dim=1)
+        if f["priv_observe_friction"]:
+            add(self.friction_coeffs[:, 0].unsqueeze(1), f["norm_friction_range"])
+        if f["priv_observe_restitution"]:
+            add(self.restitutions[:, 0].unsqueeze(1), f["norm_restitution_range"])
+        if f["priv_observe_base_mass"]:
+            add(self.payloads[:, 0].unsqueeze(1), f["norm_added_mass_range"])
+        if f["priv_observe_com_displacement"]:
+            add(self.com_displacements, f["norm_com_displacement_range"])
+        if f["priv_observe_motor_strength"]:
+            add(self.motor_strengths, f["norm_motor_strength_range"])
+        if f["priv_observe_motor_offset"]:
+            add(self.motor_offsets, f["norm_motor_offset_range"])
+        if f["priv_observe_body_height"]:
+            add(root[:, 2].view(self.N, -1), f["norm_body_height_range"])
+        if f["priv_observe_body_velocity"]:
+            add(self.base_lin_vel.view(self.N, -1), f["norm_body_velocity_range"])
+        if f["priv_observe_gravity"]:
+            add(self.gravities, f["norm_gravity_range"], divide=True)        # LR:574-579 divides by the scale
+        assert priv.shape[1] == f["num_privileged_obs"], (priv.shape, f["num_privileged_obs"])
+        self.privileged_obs_buf = priv
