@@ -1,0 +1,261 @@
+/* lt_b200.h -- C ABI of liblt_b200.so: the B200-native (sm_100a) per-environment step path of
+ * Daffan/legged_tracking.
+ *
+ * The reference has no FFI layer: its boundary is the Python object protocol of
+ * go1_gym/envs/base/legged_robot_trajectory_tracking.py (LR below), class LeggedRobot.  Every entry point
+ * here cites the reference method(s) it replaces.  A maintainer binds these with ctypes from that class
+ * (see INTEGRATION.md); legged_tracking_b200/_abi.py is exactly such a binding.
+ *
+ * Conventions
+ *   - every call returns LT_OK (0) or a negative lt_status; nothing throws across the boundary;
+ *   - all buffer pointers are DEVICE pointers owned by the caller (torch tensors in the Python host) unless a
+ *     parameter is documented as host memory; the library allocates only private scratch, freed by lt_destroy;
+ *   - every compute call is asynchronous on the cudaStream_t passed as `void* stream` (NULL = legacy default
+ *     stream) and never synchronises the host, so a step (4 x lt_compute_torques + lt_post_physics_step) can be
+ *     captured in a CUDA graph;
+ *   - one handle per GPU / process rank; a handle is not thread-safe;
+ *   - structs hold only 4-byte ints/floats (lt_config) or only pointers (lt_sim_ptrs, lt_state_ptrs, ...):
+ *     no padding, trivially mirrored by ctypes.
+ */
+#ifndef LT_B200_H
+#define LT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LT_ABI_VERSION 3
+
+#define LT_MAX_DOF 12
+#define LT_MAX_FEET 4
+#define LT_MAX_BODIES 32
+#define LT_MAX_POINTS 32
+#define LT_MAX_TERMS 32
+#define LT_ACT_HIDDEN 32
+#define LT_ACT_IN 6
+
+typedef enum {
+    LT_OK = 0,
+    LT_ERR_INVALID = -1,     /* bad argument / unsupported configuration (message in lt_last_error) */
+    LT_ERR_UNBOUND = -2,     /* a required buffer was never bound */
+    LT_ERR_CUDA = -3,        /* CUDA runtime error (message in lt_last_error) */
+    LT_ERR_NO_DEVICE = -4    /* no sm_100 device: there is NO CPU fallback */
+} lt_status;
+
+/* reward term ids: the `_reward_<name>` plugin methods of
+ * go1_gym/envs/rewards/reward_crawling.py:18-123 and trajectory_tracking_reward.py:17-171 */
+enum {
+    LT_TERM_DOF_ACC = 0, LT_TERM_TORQUES, LT_TERM_DOF_POS_LIMITS, LT_TERM_COLLISION, LT_TERM_ACTION_RATE,
+    LT_TERM_BASE_HEIGHT, LT_TERM_ANG_VEL_XY, LT_TERM_ORIENTATION, LT_TERM_LARGE_VEL, LT_TERM_E2E,
+    LT_TERM_EXPLORATION_LIN, LT_TERM_EXPLORATION_YAW, LT_TERM_REACHING_Z, LT_TERM_REACHING_ROLL,
+    LT_TERM_REACHING_PITCH, LT_TERM_DOF_VEL, LT_TERM_DOF_POS, LT_TERM_TASK_OLD, LT_TERM_REACH_GOAL,
+    LT_TERM_REACH_GOAL_T, LT_TERM_REACH_GOAL_TT, LT_TERM_TASK, LT_TERM_EXPLORATION, LT_TERM_STALLING,
+    LT_TERM_LINEAR_VEL, LT_TERM_LIN_VEL_Z, LT_TERM_FEET_AIR_TIME, LT_TERM_SURVIVE, LT_TERM_REACHING_LINEAR_VEL,
+    LT_TERM_REACHING_YAW_ABS, LT_TERM_REACHING_YAW,
+    LT_TERM_EXTERNAL = 31    /* user plugin evaluated by the host in torch on the device: value read from extra_reward */
+};
+enum { LT_FORM_EXP = 0, LT_FORM_L1 = 1, LT_FORM_L2 = 2, LT_FORM_PROD = 3 };
+enum { LT_TRAJ_FIXED_TARGET = 0, LT_TRAJ_RANDOM_GOAL = 1, LT_TRAJ_RANDOM_TARGET = 2 };
+enum { LT_CONTROL_ACTUATOR_NET = 0, LT_CONTROL_P = 1 };
+/* per-term bucket for rew_buf_pos / rew_buf_neg (LR:332-335): decided by the sign of the ALL-ENV sum */
+enum { LT_BUCKET_POS = 1, LT_BUCKET_NEG = -1, LT_BUCKET_BY_SUM = 0 };
+
+/* Everything _parse_cfg (LR:1860-1878), _init_buffers (LR:1169-1327), _process_dof_props (LR:680-708) and
+ * _prepare_reward_function (LR:1368-1418) derive from `Cfg`.  Only int32_t and float members. */
+typedef struct lt_config {
+    int32_t struct_bytes;            /* sizeof(lt_config): ABI check */
+    int32_t abi_version;             /* LT_ABI_VERSION */
+    /* sizes */
+    int32_t num_envs, num_actors, num_bodies, num_dof, num_actions, num_obs, num_privileged_obs, obs_history_length;
+    /* control (LR:957-996) */
+    int32_t decimation, control_type, randomize_lag_timesteps, lag_timesteps;
+    float dt, clip_actions, clip_observations, action_scale, hip_scale_reduction;
+    float default_dof_pos[LT_MAX_DOF], torque_limits[LT_MAX_DOF], p_gains[LT_MAX_DOF], d_gains[LT_MAX_DOF];
+    float dof_pos_lower[LT_MAX_DOF], dof_pos_upper[LT_MAX_DOF];
+    /* body index sets (LR:1647-1664) */
+    int32_t n_feet, feet_indices[LT_MAX_FEET];
+    uint32_t penalised_mask, termination_mask;      /* bit b = rigid body b of the env */
+    /* heights (LR:1902-1965) */
+    int32_t plane, observe_heights, n_points_x, n_points_y, measure_front_half, camera_zero, tile_rows, tile_cols;
+    float points_x[LT_MAX_POINTS], points_y[LT_MAX_POINTS], camera_offset[3], horizontal_scale, ceiling_height;
+    /* goals (trajectory_function.py:14-93, LR:836-848) */
+    int32_t traj_function, traj_length, num_interpolation, switch_upon_reach;
+    float base_x, base_y, base_z, base_roll, base_pitch, base_yaw;
+    float x_mean, x_range, y_mean, y_range, z_range, roll_range, pitch_range, yaw_range;
+    float switch_dist, switch_yaw, switch_interval;
+    /* termination (LR:198-216) */
+    int32_t use_terminal_body_height, terminate_end_of_trajectory, use_terminal_body_rotation;
+    float max_episode_length, terminal_body_height, T_reach;
+    /* rewards (LR:320-355): evaluation order = term_ids[0..n_terms) */
+    int32_t n_terms, term_ids[LT_MAX_TERMS], term_bucket[LT_MAX_TERMS];
+    int32_t only_positive_rewards, only_positive_rewards_ji22_style, lin_vel_form;
+    float term_scales[LT_MAX_TERMS];                /* already multiplied by dt (LR:1385) */
+    float sigma_rew_neg, base_height_target, tracking_sigma_lin, tracking_sigma_ang, target_lin_vel, target_ang_vel;
+    float lin_reaching_criterion, ang_reaching_criterion, small_vel_threshold, large_dist_threshold;
+    /* observations (LR:357-590) */
+    int32_t observe_command, timestep_in_obs, observe_two_prev_actions, observe_vel, observe_only_ang_vel;
+    int32_t observe_only_lin_vel, observe_yaw, observe_contact_states, global_reference, add_noise;
+    float obs_scale_lin_vel, obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel, obs_scale_height;
+    int32_t priv_observe_friction, priv_observe_restitution, priv_observe_base_mass, priv_observe_com_displacement;
+    int32_t priv_observe_motor_strength, priv_observe_motor_offset, priv_observe_body_height;
+    int32_t priv_observe_body_velocity, priv_observe_gravity;
+    float priv_scale[9], priv_shift[9];             /* get_scale_shift (math_utils.py:35-38), in the order above */
+    /* reset (LR:218-296, 998-1052) and domain randomisation (LR:744-764) */
+    int32_t custom_origins, randomize_motor_strength, randomize_motor_offset, randomize_Kp_factor;
+    int32_t randomize_Kd_factor, rand_interval, send_timeouts;
+    float base_init_state[13], x_init_range, y_init_range, x_init_offset, y_init_offset, yaw_init_range;
+    float motor_strength_range[2], motor_offset_range[2], Kp_factor_range[2], Kd_factor_range[2];
+    /* tuning: environments per warp of the fused step kernel (4, 8, 16 or 32; 0 = choose from num_envs) */
+    int32_t envs_per_warp;
+    /* seed of the in-kernel counter-based generator (used when no uniforms are injected) */
+    uint32_t seed_lo, seed_hi;
+} lt_config;
+
+/* HOST arrays copied at lt_create. */
+typedef struct lt_tables {
+    const float* noise_scale_vec;    /* [num_obs]  _get_noise_scale_vec (LR:1086-1166) */
+    const float* act_w0;             /* [32,6]  resources/actuator_nets/unitree_go1.pt, Linear 0 (LR:1307-1322) */
+    const float* act_b0;             /* [32] */
+    const float* act_w1;             /* [32,32] */
+    const float* act_b1;             /* [32] */
+    const float* act_w2;             /* [1,32] */
+    const float* act_b2;             /* [1] */
+} lt_tables;
+
+/* Isaac Gym acquire_*_tensor layouts (LR:1173-1201).  Borrowed, never freed. */
+typedef struct lt_sim_ptrs {
+    float* root_states;              /* [num_envs*num_actors, 13]  pos3 quat(xyzw) linvel3 angvel3; robot = actor 0 */
+    float* dof_state;                /* [num_envs*num_dof, 2]      (pos, vel) */
+    const float* contact_forces;     /* [num_envs, num_bodies, 3] */
+    const float* rigid_body_state;   /* [num_envs*num_bodies, 13]  (only read by host-side extras) */
+} lt_sim_ptrs;
+
+/* Terrain: the per-env copy env_height_samples[N,2,R,C] of LR:1827-1840 is replaced by the tile table it is
+ * copied from plus a per-env tile index (same values, 26 MB instead of 1.7 GB at 65,536 envs). */
+typedef struct lt_terrain_ptrs {
+    const float* tile_heights;       /* [n_tiles, 2, tile_rows, tile_cols] metres; layer 0 ceiling, 1 floor; NULL on plane */
+    const int32_t* env_tile;         /* [num_envs] */
+    const float* env_terrain_origin; /* [num_envs, 3]  LR:1842-1847 */
+    const float* env_origins;        /* [num_envs, 3]  LR:1808-1825 */
+} lt_terrain_ptrs;
+
+/* Struct-of-arrays env state: one row-major [num_envs, d] array per LeggedRobot attribute of the same name. */
+typedef struct lt_state_ptrs {
+    /* fp32 */
+    float *actions, *last_actions, *last_last_actions;                                  /* [N,12] LR:71-72,148-149 */
+    float *joint_pos_target, *last_joint_pos_target, *last_last_joint_pos_target;       /* [N,12] LR:150-151 */
+    float *last_dof_vel, *last_root_vel, *torques;                                      /* [N,12] [N,6] [N,12] */
+    float *joint_pos_err_last, *joint_pos_err_last_last, *joint_vel_last, *joint_vel_last_last;   /* [N,12] LR:985-988 */
+    float *motor_strengths, *motor_offsets, *Kp_factors, *Kd_factors;                   /* [N,12] LR:744-764 */
+    float *friction_coeffs, *restitutions, *payloads, *com_displacements, *gravities;   /* [N] [N] [N] [N,3] [N,3] */
+    float *gravity_vec;                                                                 /* [3] (LR:1221 keeps N equal rows) */
+    float *base_lin_vel, *base_ang_vel, *projected_gravity, *base_rotation;             /* [N,3] */
+    float *relative_linear, *relative_rotation, *local_relative_linear, *local_relative_rotation;   /* [N,3] */
+    float *target_poses, *feet_air_time;                                                /* [N,6] [N,n_feet] */
+    float *rew_buf, *rew_buf_pos, *rew_buf_neg, *camera_pitch_angle;                    /* [N] */
+    float *trajectories;                                                                /* [N, traj_length, 6] */
+    float *lag_buffer;                                                                  /* [lag_timesteps+1, N, 12] ring, see lt_get_counters */
+    float *episode_sums;                                                                /* [n_terms+3, N]  rows: terms, total, total_pos, total_neg */
+    float *command_sums;                                                                /* [n_terms+1, N] or NULL: terms, ep_timesteps */
+    float *obs_buf, *privileged_obs_buf, *obs_history;                                  /* [N,num_obs] [N,num_priv] [N,H*num_obs] */
+    float *finished_sums, *finished_episode_length, *finished_goal_distance;            /* [n_terms+3,N] [N] [N]: episode record of the env's last reset (LR:256-273) */
+    /* int64 (torch.long attributes) */
+    int64_t *episode_length_buf, *curr_pose_index, *collision_count, *collision_env_buf;
+    int64_t *reset_env_ids;                                                             /* [N] out: reset_buf.nonzero() ascending (LR:143) */
+    /* bool (1 byte, torch.bool attributes) */
+    uint8_t *reset_buf, *time_out_buf, *body_height_buf, *switched_buf, *reached_buf, *plan_buf;
+    uint8_t *reached_env_buf, *time_outs_latched, *last_contacts;                       /* last_contacts [N,n_feet] */
+    /* int32 */
+    int32_t *reset_count;                                                               /* [1] out: len(env_ids) */
+    /* optional debug/parity exports (NULL = skip) */
+    int32_t *height_px, *height_py;                                                     /* [N,n_points_x] [N,n_points_y] cell indices (LR:1955-1956) */
+} lt_state_ptrs;
+
+/* Per-step inputs of lt_post_physics_step. */
+typedef struct lt_step_args {
+    const float* extra_reward;       /* [N] or NULL: value of the LT_TERM_EXTERNAL plugin term (unscaled) */
+    const float* uniforms;           /* [N, lt_num_uniform_slots] in [0,1) or NULL -> in-kernel Philox4x32-10 */
+    const float* noise_uniforms;     /* [N, num_obs] or NULL -> in-kernel Philox (only read if add_noise) */
+    const float* new_gravity;        /* HOST float[3] or NULL: _randomize_gravity fired this step (LR:645-660): written
+                                        to `gravities` before the observations are assembled */
+} lt_step_args;
+
+typedef struct lt_handle lt_handle;
+
+/* -------------------------------------------------------------------------------------------------------------
+ * life cycle */
+int lt_abi_version(void);
+int lt_config_bytes(void);                                  /* sizeof(lt_config) as compiled */
+int lt_num_uniform_slots(const lt_config* cfg);             /* row width of lt_step_args.uniforms */
+int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out);      /* LR:25-62 (__init__) */
+void lt_destroy(lt_handle* h);
+const char* lt_last_error(const lt_handle* h);              /* h may be NULL: error of the last failed lt_create */
+
+/* LR:1173-1201 (gym.acquire_*_tensor + gymtorch.wrap_tensor) */
+int lt_bind_sim(lt_handle* h, const lt_sim_ptrs* sim);
+/* LR:1808-1847 (_get_env_origins) */
+int lt_bind_terrain(lt_handle* h, const lt_terrain_ptrs* terrain, int32_t n_tiles);
+/* LR:1203-1305 (_init_buffers: the torch.zeros(...) attributes) */
+int lt_bind_state(lt_handle* h, const lt_state_ptrs* state);
+
+/* -------------------------------------------------------------------------------------------------------------
+ * the step path */
+
+/* LeggedRobot._compute_torques (LR:957-996) incl. eval_actuator_network (LR:1311-1320), called once per physics
+ * sub-step from LeggedRobot.step (LR:82-88).  `actions` is the RAW policy output [N,12]; clipping to
+ * +-clip_actions (LR:71-72) is fused here and, when substep == 0, stored to state.actions.  Reads sim.dof_state,
+ * advances the lag FIFO and the actuator-net history, writes state.joint_pos_target and state.torques. */
+int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void* stream);
+
+/* LeggedRobot.post_physics_step (LR:114-169) with everything it calls: _post_physics_step_callback (LR:774-848),
+ * _get_heights (LR:1918-1970), _plan_target_pose / _compute_relative_target_pose (LR:850-932),
+ * check_termination (LR:198-216), compute_reward (LR:320-355), reset_idx (LR:218-296, 998-1052),
+ * compute_observations (LR:357-590), the history shifts (LR:148-153), the +-clip_observations clamp of
+ * LeggedRobot.step (LR:108-111) and HistoryWrapper.step's obs_history shift (history_wrapper.py:18-24).
+ * Two launches: the fused step kernel and the ordered reset-id compaction (reset_buf.nonzero(), LR:143). */
+int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream);
+
+/* Only when a term has LT_BUCKET_BY_SUM: evaluates those terms without side effects and leaves their all-env
+ * sums in the device array returned by lt_term_sum_buffer (float[LT_MAX_TERMS]); a multi-GPU host all-reduces
+ * that array before lt_post_physics_step.  lt_post_physics_step runs it itself when the host did not. */
+int lt_reward_sign_prepass(lt_handle* h, const lt_step_args* args, void* stream);
+float* lt_term_sum_buffer(lt_handle* h);
+
+/* Device int32[4]: {policy steps done, physics sub-steps done (= pushes into the lag FIFO), lag ring head, 0}.
+ * Logical lag slot j of LR:972-974 lives in physical slot (head + j) % (lag_timesteps + 1). */
+int32_t* lt_counters(lt_handle* h);
+
+/* -------------------------------------------------------------------------------------------------------------
+ * rollout path: go1_gym_learn/ppo_cse/rollout_storage.py */
+
+/* RolloutStorage.add_transitions (rollout_storage.py:57-71): one fused copy of a transition into row `t` of the
+ * [T,N,*] buffers.  Any source may be NULL (skipped). */
+typedef struct lt_rollout_ptrs {
+    float *observations, *privileged_observations, *observation_histories, *actions, *rewards, *values;
+    float *actions_log_prob, *mu, *sigma, *returns, *advantages;
+    uint8_t* dones;
+} lt_rollout_ptrs;
+typedef struct lt_transition_ptrs {
+    const float *observations, *privileged_observations, *observation_histories, *actions, *rewards, *values;
+    const float *actions_log_prob, *action_mean, *action_sigma;
+    const uint8_t *dones, *time_outs;    /* time_outs: extras["time_outs"]; bootstrap rewards += gamma*values*time_outs (ppo.py:85-87) */
+} lt_transition_ptrs;
+int lt_rollout_store(const lt_rollout_ptrs* storage, const lt_transition_ptrs* tr, int32_t t, int32_t num_envs,
+                     int32_t num_obs, int32_t num_privileged_obs, int32_t num_obs_history, int32_t num_actions,
+                     float gamma, void* stream);
+
+/* RolloutStorage.compute_returns (rollout_storage.py:76-90): GAE over T steps for N envs.  Writes returns and
+ * raw advantages, and accumulates {sum A, sum A^2, count} into stats (device double[3], zeroed by the call) so that
+ * a multi-GPU host can all-reduce them; lt_normalize_advantages then applies (A - mean) / (std + 1e-8) with the
+ * unbiased std of torch.Tensor.std(). */
+int lt_gae(const float* rewards, const float* values, const uint8_t* dones, const float* last_values,
+           float* returns, float* advantages, double* stats, int32_t T, int32_t num_envs, float gamma, float lam,
+           void* stream);
+int lt_normalize_advantages(float* advantages, const double* stats, int64_t count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LT_B200_H */

@@ -1,0 +1,248 @@
+"""StepEngine: torch-owned device buffers + the liblt_b200 handle that steps them.
+
+This is the host side of the drop-in boundary: it owns what LeggedRobot._init_buffers owns in the reference
+(go1_gym/envs/base/legged_robot_trajectory_tracking.py:1169-1327, LR below) -- the four simulator tensors in
+Isaac Gym's acquire_*_tensor layout and one tensor per env attribute -- and forwards step()'s two phases to the
+C ABI (include/lt_b200.h).  PyTorch is used for device memory and streams only; all per-env arithmetic happens
+in the CUDA kernels.  No CPU fallback: constructing an engine on a CPU device raises.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _abi, cconfig
+
+_TORCH_DTYPES = {"f32": torch.float32, "i64": torch.int64, "bool": torch.bool, "i32": torch.int32}
+
+
+class GravitySchedule:
+    """Host-side control flow of _randomize_gravity (LR:645-660, 826-830): WHEN gravity changes is decided by the
+    global step counter, identical for every env, so it stays on the host; the per-env rows are written by the
+    step kernel.  Arithmetic on the 3-vector uses torch CPU float32 ops in the reference's order."""
+
+    def __init__(self, flat):
+        self.enabled = bool(flat["randomize_gravity"])
+        self.lo, self.hi = [float(v) for v in flat["gravity_range"]]
+        self.interval = int(flat["gravity_rand_interval"])
+        self.duration = int(flat["gravity_rand_duration"])
+        self.gravities = torch.zeros(3)
+        self.common_step_counter = 0
+
+    @staticmethod
+    def gravity_vec_of(gravities):
+        gravity = gravities + torch.tensor([0.0, 0.0, -9.8])
+        return gravity / torch.norm(gravity)
+
+    def advance(self, draw_uniform3):
+        """Called once per policy step BEFORE the kernel launch.  Returns the new `gravities` row (float32[3]
+        tensor) if _randomize_gravity fires during this step's callback, else None."""
+        self.common_step_counter += 1
+        new = None
+        if self.common_step_counter % self.interval == 0:
+            if self.enabled:
+                u = torch.as_tensor(draw_uniform3(), dtype=torch.float32)
+                new = u * (self.hi - self.lo) + self.lo
+            else:
+                new = self.gravities.clone()              # gravity_vec is recomputed from the unchanged rows
+        if int(self.common_step_counter - self.duration) % self.interval == 0:
+            new = torch.zeros(3)
+        if new is not None:
+            self.gravities = new.clone()
+        return new
+
+
+class StepEngine:
+    def __init__(self, flat, terrain, actuator, device="cuda:0", seed=0, envs_per_warp=0, track_command_sums=True,
+                 export_height_indices=False):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _abi.LtError("StepEngine needs a CUDA device (sm_100a); there is no CPU implementation in this package")
+        self.lib = _abi.load()
+        self.flat = flat
+        self.N = int(flat["num_envs"])
+        self.cfg = cconfig.make_lt_config(flat, seed=seed, envs_per_warp=envs_per_warp)
+        self.n_slots = self.lib.lt_num_uniform_slots(C.byref(self.cfg))
+        tables = cconfig.Tables(flat, actuator)
+        self.handle = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _abi.check(self.lib.lt_create(C.byref(self.cfg), C.byref(tables.c), C.byref(self.handle)), None, "lt_create")
+        dev = self.device
+        N, A, B, D = self.N, int(flat["num_actors"]), int(flat["num_bodies"]), int(flat["num_dof"])
+        # ---- simulator tensors, Isaac Gym layout (LR:1173-1201)
+        self.root_states = torch.zeros(N * A, 13, device=dev)
+        self.root_states[:, 6] = 1.0
+        self.dof_state = torch.zeros(N * D, 2, device=dev)
+        self.contact_forces = torch.zeros(N, B, 3, device=dev)
+        self.rigid_body_state = torch.zeros(N * B, 13, device=dev)
+        sim = _abi.lt_sim_ptrs(self.root_states.data_ptr(), self.dof_state.data_ptr(), self.contact_forces.data_ptr(),
+                               self.rigid_body_state.data_ptr())
+        _abi.check(self.lib.lt_bind_sim(self.handle, C.byref(sim)), self.handle, "lt_bind_sim")
+        # ---- terrain (LR:1808-1847)
+        t = lambda x, dt: torch.as_tensor(np.ascontiguousarray(np.asarray(x)), dtype=dt).to(dev).contiguous()   # noqa: E731
+        self.env_origins = t(terrain["env_origins"], torch.float32).view(N, 3)
+        self.plane = flat["mesh_type"] == "plane"
+        ter = _abi.lt_terrain_ptrs()
+        ter.env_origins = self.env_origins.data_ptr()
+        n_tiles = 0
+        if not self.plane:
+            self.tile_heights = t(terrain["tile_heights"], torch.float32)
+            self.env_tile = t(terrain["env_tile"], torch.int32)
+            self.env_terrain_origin = t(terrain["env_terrain_origin"], torch.float32).view(N, 3)
+            n_tiles = int(self.tile_heights.shape[0])
+            assert tuple(self.tile_heights.shape[1:]) == (2, flat["tile_rows"], flat["tile_cols"])
+            assert int(self.env_tile.max()) < n_tiles
+            ter.tile_heights = self.tile_heights.data_ptr()
+            ter.env_tile = self.env_tile.data_ptr()
+            ter.env_terrain_origin = self.env_terrain_origin.data_ptr()
+        _abi.check(self.lib.lt_bind_terrain(self.handle, C.byref(ter), n_tiles), self.handle, "lt_bind_terrain")
+        # ---- env state, one tensor per LeggedRobot attribute (LR:1203-1305)
+        self.state = {}
+        ptrs = _abi.lt_state_ptrs()
+        skip = set()
+        if not track_command_sums:
+            skip.add("command_sums")
+        if not export_height_indices:
+            skip |= {"height_px", "height_py"}
+        for name, dt, shape in cconfig.state_spec(flat):
+            if name in skip:
+                setattr(ptrs, name, None)
+                continue
+            buf = torch.full(shape, cconfig.STATE_INIT.get(name, 0), dtype=_TORCH_DTYPES[dt], device=dev)
+            self.state[name] = buf
+            setattr(ptrs, name, buf.data_ptr())
+        self.state["gravity_vec"].copy_(torch.tensor([0.0, 0.0, -1.0]))
+        _abi.check(self.lib.lt_bind_state(self.handle, C.byref(ptrs)), self.handle, "lt_bind_state")
+        self._ptrs = ptrs
+        self.counters = self._wrap_i32(self.lib.lt_counters(self.handle), 4)
+        self.gravity = GravitySchedule(flat)
+        self.reward_names = list(flat["reward_names"])
+        self.sum_names = self.reward_names + ["total", "total_pos", "total_neg"]
+        self._keepalive = []
+
+    def _wrap_i32(self, ptr, n):
+        """torch view of a library-owned device int32 array (read-only use)."""
+        class _Holder:
+            pass
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+        return torch.as_tensor(h, device=self.device)
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.lt_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    # ---------------------------------------------------------------- views with the reference's attribute names
+    def __getattr__(self, name):
+        st = self.__dict__.get("state")
+        if st is not None and name in st:
+            return st[name]
+        raise AttributeError(name)
+
+    @property
+    def robot_root(self):
+        return self.root_states.view(self.N, -1, 13)[:, 0, :]
+
+    @property
+    def dof_pos(self):
+        return self.dof_state.view(self.N, -1, 2)[..., 0]
+
+    @property
+    def dof_vel(self):
+        return self.dof_state.view(self.N, -1, 2)[..., 1]
+
+    def lag_buffer_logical(self):
+        """lag_buffer in the reference's list order (slot 0 = oldest, LR:972-974)."""
+        head = int(self.counters[2].item())
+        L = self.state["lag_buffer"].shape[0]
+        idx = [(head + j) % L for j in range(L)]
+        return self.state["lag_buffer"][idx]
+
+    # ---------------------------------------------------------------- stepping
+    @staticmethod
+    def _stream_ptr(stream):
+        s = stream if stream is not None else torch.cuda.current_stream()
+        return C.c_void_p(s.cuda_stream)
+
+    def compute_torques(self, actions, substep, stream=None):
+        """LeggedRobot._compute_torques (LR:957-996).  `actions`: raw policy output [N,12] on the device."""
+        assert actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
+        _abi.check(self.lib.lt_compute_torques(self.handle, C.c_void_p(actions.data_ptr()), int(substep),
+                                               self._stream_ptr(stream)), self.handle, "lt_compute_torques")
+        return self.state["torques"]
+
+    def post_physics_step(self, uniforms=None, noise_uniforms=None, extra_reward=None, gravity_uniform=None, stream=None,
+                          advance_gravity=True):
+        """LeggedRobot.post_physics_step (LR:114-169) on the bound simulator tensors."""
+        args = _abi.lt_step_args()
+        for name, tns, shape in (("uniforms", uniforms, (self.N, self.n_slots)),
+                                 ("noise_uniforms", noise_uniforms, (self.N, self.flat["num_obs"])),
+                                 ("extra_reward", extra_reward, (self.N,))):
+            if tns is not None:
+                assert tns.is_cuda and tns.dtype == torch.float32 and tns.is_contiguous() and tuple(tns.shape) == shape, name
+                setattr(args, name, tns.data_ptr())
+        new_g = None
+        if advance_gravity:
+            draw = (lambda: gravity_uniform) if gravity_uniform is not None else (lambda: torch.rand(3))
+            new_g = self.gravity.advance(draw)
+        if new_g is not None:
+            g_host = (C.c_float * 3)(*[float(v) for v in new_g])
+            args.new_gravity = C.cast(g_host, C.c_void_p)
+        _abi.check(self.lib.lt_post_physics_step(self.handle, C.byref(args), self._stream_ptr(stream)), self.handle,
+                   "lt_post_physics_step")
+        if new_g is not None:
+            # gravity_vec changes AFTER this step's projected_gravity was computed (LR:134 precedes LR:826-830)
+            self.state["gravity_vec"].copy_(GravitySchedule.gravity_vec_of(new_g), non_blocking=False)
+
+    def reset_env_ids(self):
+        """env_ids = reset_buf.nonzero().flatten() (LR:143); synchronises to read the count."""
+        n = int(self.state["reset_count"].item())
+        return self.state["reset_env_ids"][:n]
+
+    # ---------------------------------------------------------------- state import / export (oracle naming)
+    def load_state(self, st):
+        """Accepts the keys of oracle.port.OraclePort.export_state / the `init/*` arrays of the golden fixtures."""
+        def put(dst, src):
+            src = torch.as_tensor(np.asarray(src))
+            dst.copy_(src.to(dst.dtype).reshape(dst.shape).to(dst.device))
+        for name, buf in self.state.items():
+            if name in st and name not in ("lag_buffer", "episode_sums", "command_sums"):
+                put(buf, st[name])
+        if "root_states" in st:
+            put(self.root_states, st["root_states"])
+        if "dof_state" in st:
+            put(self.dof_state, st["dof_state"])
+        if "lag_buffer" in st:
+            put(self.state["lag_buffer"], st["lag_buffer"])          # logical order == physical while head == 0
+            assert int(self.counters[2].item()) == 0, "load_state: lag ring already rotated"
+        for r, name in enumerate(self.sum_names):
+            if "episode_sums/" + name in st:
+                put(self.state["episode_sums"][r], st["episode_sums/" + name])
+        if "command_sums" in self.state:
+            for r, name in enumerate(self.reward_names + ["ep_timesteps"]):
+                if "command_sums/" + name in st:
+                    put(self.state["command_sums"][r], st["command_sums/" + name])
+        if "gravity_vec" in st:
+            put(self.state["gravity_vec"], np.asarray(st["gravity_vec"]).reshape(-1)[:3])
+        if "gravities" in st:
+            self.gravity.gravities = torch.as_tensor(np.asarray(st["gravities"]), dtype=torch.float32).reshape(-1, 3)[0].clone()
+        if "common_step_counter" in st:
+            self.gravity.common_step_counter = int(st["common_step_counter"])
+
+    def export_state(self):
+        out = {k: v.detach().cpu() for k, v in self.state.items()
+               if k not in ("lag_buffer", "episode_sums", "command_sums", "finished_sums")}
+        out["root_states"] = self.root_states.cpu()
+        out["dof_state"] = self.dof_state.cpu()
+        out["lag_buffer"] = self.lag_buffer_logical().cpu()
+        for r, name in enumerate(self.sum_names):
+            out["episode_sums/" + name] = self.state["episode_sums"][r].cpu()
+        if "command_sums" in self.state:
+            for r, name in enumerate(self.reward_names + ["ep_timesteps"]):
+                out["command_sums/" + name] = self.state["command_sums"][r].cpu()
+        out["common_step_counter"] = torch.tensor(self.gravity.common_step_counter)
+        return out
