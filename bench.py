@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py -- env-steps/s of the fused step path (BASELINE.json metric) on N B200s of one node.
+
+A "step" is one pass of LeggedRobot.step's data-parallel work over all envs of the rank:
+4 x lt_compute_torques (actuator net, one per physics sub-step) + lt_post_physics_step (fused step kernel + ordered
+reset compaction), on seeded synthetic simulator state in Isaac Gym's tensor layout (PhysX itself is out of scope).
+Default workload: BASELINE config 5 shape (single_path tunnel, 2x10x11 front-half heights, camera_zero, e2e reward
+set, noise + domain randomisation on), 65,536 envs PER GPU (weak scaling: env shards are independent).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--envs-per-gpu E]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+from legged_tracking_b200 import workload  # noqa: E402
+
+METRIC = "env_steps_per_s"
+UNIT = "env-steps/s"
+N_REPLAY_SETS = 3
+
+
+def measured_peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self.stop_flag = False
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                 getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                 getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                 getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+class ReplaySets:
+    """A few pre-generated 'PhysX outputs' resident in HBM; the step is re-pointed at one of them per step."""
+
+    def __init__(self, eng, synth, flat, n_sets, pinned_host=False):
+        N, A, D = eng.N, flat["num_actors"], flat["num_dof"]
+        dev = eng.device
+        self.sets = []
+        self.host = []
+        for k in range(n_sets):
+            root_all = torch.zeros(N, A, 13)
+            root_all[:, :, 6] = 1.0
+            root_all[:, 0, :] = synth.root(k)
+            h = {"actions": synth.actions(k).contiguous(),
+                 "dof": [synth.dof_state(k, s) for s in range(flat["decimation"])],
+                 "root": root_all.view(N * A, 13).contiguous(), "contact": synth.contact(k)}
+            if pinned_host:
+                h = {"actions": h["actions"].pin_memory(), "dof": [d.pin_memory() for d in h["dof"]],
+                     "root": h["root"].pin_memory(), "contact": h["contact"].pin_memory()}
+                self.host.append(h)
+            self.sets.append({"actions": h["actions"].to(dev), "dof": [d.to(dev) for d in h["dof"]],
+                              "root": h["root"].to(dev), "contact": h["contact"].to(dev)})
+
+
+def launch_step(eng, s, eager_gravity=True):
+    """One full step on replay set s (6 kernel launches)."""
+    for sub, dof in enumerate(s["dof"]):
+        eng.bind_sim(dof_state=dof)
+        eng.compute_torques(s["actions"], sub)
+    eng.bind_sim(root_states=s["root"], contact_forces=s["contact"])
+    eng.post_physics_step(advance_gravity=eager_gravity)
+
+
+def init_engine_state(eng, synth, flat):
+    """Spread episode phases like TrajectoryTrackingEnv.reset (trajectory_tracking/__init__.py:49) and give every env
+    a goal so that the relative-pose math runs on meaningful numbers."""
+    N = eng.N
+    eng.state["episode_length_buf"].copy_(synth.initial_episode_length(flat["max_episode_length"]).to(eng.device))
+    g = torch.Generator().manual_seed(5)
+    eng.state["friction_coeffs"].copy_((0.05 + 4.45 * torch.rand(N, 1, generator=g)).to(eng.device))
+    eng.state["restitutions"].copy_((0.4 * torch.rand(N, 1, generator=g)).to(eng.device))
+    traj = torch.zeros(N, flat["traj_length"], 6)
+    traj[:, :, 0] = eng.env_origins[:, 0:1].cpu() + 2.5
+    traj[:, :, 1] = eng.env_origins[:, 1:2].cpu()
+    traj[:, :, 2] = 0.34
+    eng.state["trajectories"].copy_(traj.to(eng.device))
+
+
+def time_region(fn, steps, stream_sync=True):
+    """CUDA-event time (ms) of `steps` calls of fn(k) on the current stream, synchronised on both sides."""
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        fn(k)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1)
+
+
+def cpu_oracle_rate(steps, n_envs, config):
+    """The reference's torch step path on the host cores (oracle port, faithful per-env height gather): env-steps/s."""
+    from oracle.port import OraclePort
+    from legged_tracking_b200 import cconfig
+    torch.set_num_threads(os.cpu_count() or 1)
+    flat, terrain, act, synth = workload.make(config, num_envs=n_envs)
+    port = OraclePort(flat, terrain, act, faithful_gather=True)
+    n = flat["num_envs"]
+    U = torch.full((n, cconfig.rng_n_slots(flat)), 0.5)
+    inputs = []
+    for k in range(2):
+        root = synth.root(k)
+        inputs.append((synth.actions(k), dict(dof_state=[synth.dof_state(k, s) for s in range(flat["decimation"])], root=root,
+                                              contact=synth.contact(k), rigid=synth.rigid(k, root))))
+    port.episode_length_buf.copy_(synth.initial_episode_length(flat["max_episode_length"]))
+
+    def one(k):
+        a, sim = inputs[k % 2]
+        port.step(a, sim, U, torch.rand(n, flat["num_obs"]) if flat["add_noise"] else None, torch.rand(3))
+    one(0)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        one(k + 1)
+    dt = time.perf_counter() - t0
+    return n * steps / dt, dt / steps, torch.get_num_threads()
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port; /root/reference does not
+    exist on the GPU box), bounded sample per step."""
+    if rank != 0:
+        return
+    n_envs = args.cpu_envs
+    for _ in range(max(args.warmup, 0) and 1):
+        pass
+    rate, s_per_step, cores = cpu_oracle_rate(max(1, min(args.steps, 20)), n_envs, "cfg2")
+    line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": max(1, min(args.steps, 20)), "warmup": 1, "ms_per_step": s_per_step * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"cfg5 shape (single_path, 2x10x11 heights, camera_zero, e2e rewards), bounded sample of {n_envs} envs per step on the host CPU"},
+            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{n_envs} envs x {max(1, min(args.steps, 20))} steps, oracle/port.py with the reference's per-env height gather"},
+            "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, rank, world, local_rank):
+    from legged_tracking_b200.engine import StepEngine
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    torch.cuda.set_device(local_rank)
+    dev = f"cuda:{local_rank}"
+    n_env = args.envs_per_gpu
+    flat, terrain, act, synth = workload.make(args.config, num_envs=n_env, seed=1000 + rank)
+    eng = StepEngine(flat, terrain, act, device=dev, seed=11 + rank, envs_per_warp=args.epw)
+    init_engine_state(eng, synth, flat)
+    rs = ReplaySets(eng, synth, flat, N_REPLAY_SETS, pinned_host=True)
+    alg = workload.algorithmic_bytes(flat)
+    launches_per_step = flat["decimation"] + 2
+
+    # ---- warm-up (eager), then one CUDA graph per replay set
+    for k in range(max(args.warmup, 3)):
+        launch_step(eng, rs.sets[k % N_REPLAY_SETS])
+    torch.cuda.synchronize()
+    graphs = []
+    if not args.no_graph:
+        side = torch.cuda.Stream()
+        for s in rs.sets:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                launch_step(eng, s, eager_gravity=False)
+            graphs.append(g)
+
+    def step_fn(k):
+        s = k % N_REPLAY_SETS
+        if graphs and not eng.gravity.fires_next():
+            graphs[s].replay()
+            eng.gravity.common_step_counter += 1
+        else:
+            launch_step(eng, rs.sets[s])
+    for k in range(3):
+        step_fn(k)
+
+    # ---- timed region: exactly K steps, barrier + synchronize on both sides, device timed, max over ranks
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if dist:
+        dist.barrier()
+    ms = time_region(step_fn, args.steps)
+    if dist:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    # per-kernel shares (same launches, each kernel class alone), for the roofline of the dominant kernel
+    s0 = rs.sets[0]
+
+    def torque_only(k):
+        s = rs.sets[k % N_REPLAY_SETS]
+        for sub, dof in enumerate(s["dof"]):
+            eng.bind_sim(dof_state=dof)
+            eng.compute_torques(s["actions"], sub)
+
+    def post_only(k):
+        s = rs.sets[k % N_REPLAY_SETS]
+        eng.bind_sim(root_states=s["root"], contact_forces=s["contact"], dof_state=s["dof"][-1])
+        eng.post_physics_step(advance_gravity=False)
+    ksub = max(20, min(args.steps, 300))
+    ms_torque = time_region(torque_only, ksub) / (ksub * flat["decimation"])
+    ms_post = time_region(post_only, ksub) / ksub
+    sampler.stop_flag = True
+    sampler.join()
+
+    # ---- e2e: the same step through the public call with HOST buffers (pinned): H2D inputs, kernels, D2H results
+    N, A = eng.N, flat["num_actors"]
+    out_h = {"obs": torch.empty(N, flat["num_obs"]).pin_memory(), "priv": torch.empty(N, flat["num_privileged_obs"]).pin_memory(),
+             "rew": torch.empty(N).pin_memory(), "done": torch.empty(N, dtype=torch.bool).pin_memory()}
+    own = {"actions": torch.empty(N, 12, device=dev), "dof": torch.empty(N * 12, 2, device=dev),
+           "root": torch.empty(N * A, 13, device=dev), "contact": torch.empty(N, flat["num_bodies"], 3, device=dev)}
+    eng.bind_sim(root_states=own["root"], dof_state=own["dof"], contact_forces=own["contact"])
+
+    def e2e_step(k):
+        h = rs.host[k % N_REPLAY_SETS]
+        own["actions"].copy_(h["actions"], non_blocking=True)
+        for sub, dof in enumerate(h["dof"]):
+            own["dof"].copy_(dof, non_blocking=True)                  # what PhysX would hand back after sub-step `sub`
+            eng.compute_torques(own["actions"], sub)
+        own["root"].copy_(h["root"], non_blocking=True)
+        own["contact"].copy_(h["contact"], non_blocking=True)
+        eng.post_physics_step()
+        out_h["obs"].copy_(eng.state["obs_buf"], non_blocking=True)
+        out_h["priv"].copy_(eng.state["privileged_obs_buf"], non_blocking=True)
+        out_h["rew"].copy_(eng.state["rew_buf"], non_blocking=True)
+        out_h["done"].copy_(eng.state["reset_buf"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()                     # the caller needs obs/rew/done before acting again
+    for k in range(3):
+        e2e_step(k)
+    ke = max(10, min(args.steps, 200))
+    if dist:
+        dist.barrier()
+    ms_e2e = time_region(e2e_step, ke)
+    if dist:
+        t = torch.tensor([ms_e2e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    h2d = sum(int(x.numel()) * 4 for x in (own["actions"], own["root"], own["contact"])) + flat["decimation"] * own["dof"].numel() * 4
+    d2h = sum(int(v.numel()) * v.element_size() for v in out_h.values())
+
+    if rank != 0:
+        return
+    peak, peak_src = measured_peaks()
+    ms_step = ms / args.steps
+    value = world * n_env * args.steps / (ms * 1e-3)
+    torque_total = ms_torque * flat["decimation"]
+    dominant = "lt_torque_kernel" if torque_total > ms_post else "lt_step_kernel"
+    k_post = {"kernel": "lt_step_kernel (+ lt_compact_kernel)", "ms_per_launch": ms_post,
+              "achieved": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9}
+    k_tq = {"kernel": "lt_torque_kernel", "ms_per_launch": ms_torque,
+            "achieved": alg["torque_substep"] * n_env / (ms_torque * 1e-3) / 1e9,
+            "fp32_tflops": alg["torque_flops_substep"] * n_env / (ms_torque * 1e-3) / 1e12}
+    for d in (k_post, k_tq):
+        d.update({"bound": "hbm", "peak": peak, "unit": "GB/s", "frac": d["achieved"] / peak})
+    dom = k_tq if dominant == "lt_torque_kernel" else k_post
+    roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": None,
+                "kernel": dom["kernel"], "peak_source": peak_src, "ms_per_launch": dom["ms_per_launch"],
+                "algorithmic_bytes_per_env": alg["torque_substep"] if dom is k_tq else alg["post_physics"],
+                "kernels": {"post_physics": k_post, "torque_substep": k_tq},
+                "share_of_step": {"torque_x%d" % flat["decimation"]: torque_total / (torque_total + ms_post),
+                                  "post_physics": ms_post / (torque_total + ms_post)}}
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        rate, s_per_step, cores = cpu_oracle_rate(args.cpu_steps, args.cpu_envs, "cfg2")
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same workload shape, oracle/port.py (torch CPU, "
+                         f"reference's per-env height gather), {s_per_step * 1e3:.1f} ms/step"}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"{args.config}: single_path tunnel, 2x10x11 front-half heights, camera_zero, e2e reward set, "
+                                   f"noise+DR on; full step = {flat['decimation']} x actuator-net torques + fused post-physics step",
+                       "envs_per_gpu": n_env, "total_envs": n_env * world, "parallelism": f"env-sharded x{world}, no data-path collective",
+                       "cuda_graph": not args.no_graph, "envs_per_warp": args.epw,
+                       "l2": f"inputs larger than L2: {alg['full_step'] * n_env / 1e6:.0f} MB touched per step, "
+                             f"{N_REPLAY_SETS} replay sets cycled"},
+            "clocks": sampler.summary(), "gpu_launches": launches_per_step * args.steps,
+            "e2e": {"value": world * n_env * ke / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / ke, "steps": ke},
+            "post_physics_only": {"value": world * n_env / (ms_post * 1e-3), "unit": UNIT, "ms_per_step": ms_post},
+            "roofline": roofline}
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="cfg5")
+    ap.add_argument("--envs-per-gpu", type=int, default=65536)
+    ap.add_argument("--epw", type=int, default=0, help="envs per warp of the step kernel (0 = auto)")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-envs", type=int, default=4096)
+    ap.add_argument("--cpu-steps", type=int, default=40)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU baseline")
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -34,6 +34,11 @@ class GravitySchedule:
         gravity = gravities + torch.tensor([0.0, 0.0, -9.8])
         return gravity / torch.norm(gravity)
 
+    def fires_next(self):
+        """True if advance() will return a new gravity on the next step (lets a caller keep such steps out of a CUDA graph)."""
+        n = self.common_step_counter + 1
+        return n % self.interval == 0 or int(n - self.duration) % self.interval == 0
+
     def advance(self, draw_uniform3):
         """Called once per policy step BEFORE the kernel launch.  Returns the new `gravities` row (float32[3]
         tensor) if _randomize_gravity fires during this step's callback, else None."""
@@ -161,6 +166,17 @@ class StepEngine:
         L = self.state["lag_buffer"].shape[0]
         idx = [(head + j) % L for j in range(L)]
         return self.state["lag_buffer"][idx]
+
+    def bind_sim(self, root_states=None, dof_state=None, contact_forces=None, rigid_body_state=None):
+        """Re-point the step at other simulator tensors (host-only; e.g. a replay set).  LR:1173-1201."""
+        for name, tns in (("root_states", root_states), ("dof_state", dof_state), ("contact_forces", contact_forces),
+                          ("rigid_body_state", rigid_body_state)):
+            if tns is not None:
+                assert tns.is_cuda and tns.dtype == torch.float32 and tns.is_contiguous() and tns.numel() == getattr(self, name).numel(), name
+                setattr(self, name, tns)
+        sim = _abi.lt_sim_ptrs(self.root_states.data_ptr(), self.dof_state.data_ptr(), self.contact_forces.data_ptr(),
+                               self.rigid_body_state.data_ptr())
+        _abi.check(self.lib.lt_bind_sim(self.handle, C.byref(sim)), self.handle, "lt_bind_sim")
 
     # ---------------------------------------------------------------- stepping
     @staticmethod
