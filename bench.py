@@ -206,7 +206,7 @@ def run_b200(args, rank, world, local_rank):
     init_engine_state(eng, synth, flat)
     rs = ReplaySets(eng, synth, flat, N_REPLAY_SETS, pinned_host=True)
     alg = workload.algorithmic_bytes(flat)
-    launches_per_step = flat["decimation"] + 2
+    launches_per_step = flat["decimation"] + 3
 
     # ---- warm-up (eager), then one CUDA graph per replay set
     for k in range(max(args.warmup, 3)):

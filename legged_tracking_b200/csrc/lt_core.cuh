@@ -36,6 +36,8 @@
 #define LT_FSQRT(a) sqrtf((a))
 #endif
 
+#define LT_ND 12   /* Go1: 12 actuated dofs = 12 actions; lt_create validates num_dof == num_actions == LT_ND */
+
 #define LT_TWO_PI_F 6.28318530717958647692f   /* float(2*np.pi) */
 #define LT_PI_F 3.14159265358979323846f       /* float(np.pi) */
 #define LT_HALF_PI_F 1.57079632679489661923f
@@ -124,6 +126,9 @@ LT_HD void lt_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 LT_HD float lt_u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }   // [0,1), 24 bits like torch.rand
+
+// 16-bit uniform in (0,1) for the observation noise: two per Philox word, 8 per call
+LT_HD float lt_u16(uint32_t x) { return LT_FMUL((float)(x & 0xffffu) + 0.5f, 1.0f / 65536.0f); }
 
 // Per-env source of the step's uniform slots: injected row (parity) or Philox.
 struct lt_uniform_src {
@@ -285,14 +290,14 @@ struct lt_env_rows {
     float* root;                 // [13] robot actor root state (LR:1189); overwritten on reset (LR:1015-1052)
     float* arrow;                // [13] goal-arrow actor or nullptr; pose written every step (LR:934-947)
     float* dof;                  // [num_dof*2] (pos, vel) interleaved; overwritten on reset (LR:998-1013)
-    const float* contact;        // [num_bodies*3]
+    uint32_t cinfo;              // lt_contact_summary of this env's contact_forces rows
     const float* actions;        // [12] clipped actions of this step (state.actions)
     const float* last_actions;   // [12] before this step's shift
     const float* last_dof_vel;   // [12]
     const float* torques;        // [12]
-    float* head;                 // [head_w] out: non-height observation columns, before noise / clipping
-    int32_t* ix;                 // [nxf] out: heightfield row index of each measured x (LR:1955)
-    int32_t* iy;                 // [n_points_y] out: column index (LR:1956)
+    float* obs_row;              // this env's obs_buf row: the non-height columns are written here, before noise / clipping
+    uint8_t* ix;                 // [nxf] out: heightfield row index of each measured x (LR:1955)
+    uint8_t* iy;                 // [n_points_y] out: column index (LR:1956)
 };
 struct lt_env_result {
     int reset;                   // reset_buf
@@ -309,25 +314,25 @@ struct lt_step_scalars {         // per-launch scalars
 
 LT_HD void lt_randomize_dof_props(const lt_config& c, const lt_state_ptrs& st, int i, const lt_uniform_src& U, int base) {
     // LR:744-764: torch.rand(K,1)*(hi-lo)+lo broadcast over the 12 dofs; offsets draw 12
-    const int nd = c.num_dof;
+    constexpr int nd = LT_ND;
     if (c.randomize_motor_strength) {
         const float v = LT_FADD(LT_FMUL(U.get(base + 0), LT_FSUB(c.motor_strength_range[1], c.motor_strength_range[0])),
                                 c.motor_strength_range[0]);
-        for (int d = 0; d < nd; ++d) st.motor_strengths[(size_t)i * nd + d] = v;
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) st.motor_strengths[(size_t)i * nd + d] = v;
     }
     if (c.randomize_motor_offset) {
-        for (int d = 0; d < nd; ++d)
+        _Pragma("unroll") for (int d = 0; d < nd; ++d)
             st.motor_offsets[(size_t)i * nd + d] =
                 LT_FADD(LT_FMUL(U.get(base + 1 + d), LT_FSUB(c.motor_offset_range[1], c.motor_offset_range[0])),
                         c.motor_offset_range[0]);
     }
     if (c.randomize_Kp_factor) {
         const float v = LT_FADD(LT_FMUL(U.get(base + 13), LT_FSUB(c.Kp_factor_range[1], c.Kp_factor_range[0])), c.Kp_factor_range[0]);
-        for (int d = 0; d < nd; ++d) st.Kp_factors[(size_t)i * nd + d] = v;
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) st.Kp_factors[(size_t)i * nd + d] = v;
     }
     if (c.randomize_Kd_factor) {
         const float v = LT_FADD(LT_FMUL(U.get(base + 14), LT_FSUB(c.Kd_factor_range[1], c.Kd_factor_range[0])), c.Kd_factor_range[0]);
-        for (int d = 0; d < nd; ++d) st.Kd_factors[(size_t)i * nd + d] = v;
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) st.Kd_factors[(size_t)i * nd + d] = v;
     }
 }
 
@@ -369,7 +374,7 @@ struct lt_reward_ctx {
     const float* torques;
     const float* actions;
     const float* last_actions;
-    const float* contact;
+    uint32_t cinfo;
     float root_z;
     float blv[3], bav[3], pg[3], rel_lin[3], rel_rot[3], loc_lin[3];
     float ep_f;                  // episode_length_buf as float
@@ -379,21 +384,21 @@ struct lt_reward_ctx {
 // value of reward term `id` (unscaled).  `dry`: evaluate without touching state (sign pre-pass).
 LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, int id, const lt_reward_ctx& r,
                            const float* extra_reward, bool dry) {
-    const int nd = c.num_dof;
+    constexpr int nd = LT_ND;
     switch (id) {
     case LT_TERM_DOF_ACC: {           // reward_crawling.py:18-20
         float s = 0.0f;
-        for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(LT_FDIV(LT_FSUB(r.last_dof_vel[d], r.dof[2 * d + 1]), c.dt)));
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(LT_FDIV(LT_FSUB(r.last_dof_vel[d], r.dof[2 * d + 1]), c.dt)));
         return s;
     }
     case LT_TERM_TORQUES: {           // :22-24
         float s = 0.0f;
-        for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(r.torques[d]));
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(r.torques[d]));
         return s;
     }
     case LT_TERM_DOF_POS_LIMITS: {    // :26-30
         float s = 0.0f;
-        for (int d = 0; d < nd; ++d) {
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) {
             const float q = r.dof[2 * d];
             float o = -fminf(LT_FSUB(q, c.dof_pos_lower[d]), 0.0f);
             o = LT_FADD(o, fmaxf(LT_FSUB(q, c.dof_pos_upper[d]), 0.0f));
@@ -404,7 +409,7 @@ LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, i
     case LT_TERM_COLLISION: return (float)r.n_collisions;                       // :32-35
     case LT_TERM_ACTION_RATE: {       // :37-39
         float s = 0.0f;
-        for (int d = 0; d < c.num_actions; ++d) s = LT_FADD(s, lt_square(LT_FSUB(r.last_actions[d], r.actions[d])));
+        _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) s = LT_FADD(s, lt_square(LT_FSUB(r.last_actions[d], r.actions[d])));
         return s;
     }
     case LT_TERM_BASE_HEIGHT: return lt_square(LT_FSUB(r.root_z, c.base_height_target));          // :41-42
@@ -438,12 +443,12 @@ LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, i
     case LT_TERM_REACHING_YAW_ABS: return lt_square(r.rel_rot[2]);
     case LT_TERM_DOF_VEL: {
         float s = 0.0f;
-        for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(r.dof[2 * d + 1]));
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(r.dof[2 * d + 1]));
         return s;
     }
     case LT_TERM_DOF_POS: {
         float s = 0.0f;
-        for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(LT_FSUB(r.dof[2 * d], c.default_dof_pos[d])));
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) s = LT_FADD(s, lt_square(LT_FSUB(r.dof[2 * d], c.default_dof_pos[d])));
         return s;
     }
     case LT_TERM_TASK_OLD: {          // trajectory_tracking_reward.py:55-62
@@ -477,7 +482,7 @@ LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, i
         float rew = 0.0f;
         for (int f = 0; f < c.n_feet; ++f) {
             const size_t k = (size_t)i * c.n_feet + f;
-            const bool contact = r.contact[c.feet_indices[f] * 3 + 2] > 1.0f;
+            const bool contact = (r.cinfo >> (16 + f)) & 1u;
             const bool filt = contact || (st.last_contacts[k] != 0);
             float air = st.feet_air_time[k];
             const bool first = (air > 0.0f) && filt;
@@ -513,11 +518,21 @@ LT_HD void lt_derive_pose(const lt_state_ptrs& st, const lt_config& c, int i, co
     lt_quat_to_rpy(q, p.base_rot);
     for (int k = 0; k < 3; ++k) p.rel_rot[k] = lt_wrap_to_pi(LT_FSUB(p.target[3 + k], p.base_rot[k]));
 }
-LT_HD int lt_count_contacts(const lt_config& c, const float* contact, uint32_t mask, float thresh) {
-    int n = 0;
-    for (int b = 0; b < c.num_bodies; ++b)
-        if ((mask >> b) & 1u) n += (lt_norm3(contact[3 * b], contact[3 * b + 1], contact[3 * b + 2]) > thresh) ? 1 : 0;
-    return n;
+// Everything the step needs from one env's net contact forces, packed: bits 0-7 number of penalised bodies with
+// |F| > 0.1 (LR:846-848, reward_crawling.py:32-35), bit 8 any termination body with |F| > 1 (LR:201-203),
+// bits 16+f foot f has F_z > 1 (trajectory_tracking_reward.py:116, LR:464-467).
+LT_HD uint32_t lt_contact_summary(const lt_config& c, const float* contact) {
+    uint32_t w = 0;
+    const uint32_t any = c.penalised_mask | c.termination_mask;
+    for (int b = 0; b < c.num_bodies; ++b) {
+        if (!((any >> b) & 1u)) continue;                       // uniform across envs: only listed bodies cost a norm
+        const float f = lt_norm3(contact[3 * b], contact[3 * b + 1], contact[3 * b + 2]);
+        if (((c.penalised_mask >> b) & 1u) && f > 0.1f) w += 1u;
+        if (((c.termination_mask >> b) & 1u) && f > 1.0f) w |= 0x100u;
+    }
+    for (int k = 0; k < c.n_feet; ++k)
+        if (contact[3 * c.feet_indices[k] + 2] > 1.0f) w |= 0x10000u << k;
+    return w;
 }
 
 // trajectory functions (go1_gym/envs/trajectories/trajectory_function.py:14-93) for one reset env
@@ -573,7 +588,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
                                 const lt_terrain_ptrs& ter, const lt_step_args& args, const lt_step_scalars& sc,
                                 int i, const lt_env_rows& R) {
     lt_env_result res;
-    const int nd = c.num_dof;
+    constexpr int nd = LT_ND;
     lt_uniform_src U;
     U.row = args.uniforms ? args.uniforms + (size_t)i * L.n_slots : nullptr;
     U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.step = sc.step; U.env = (uint32_t)i;
@@ -600,7 +615,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
             p = LT_FDIV(LT_FSUB(p, ox), c.horizontal_scale);
             int v = (int)p;                                       // .long(): truncation toward zero
             v = v < 0 ? 0 : (v > c.tile_rows - 2 ? c.tile_rows - 2 : v);
-            R.ix[a] = v;
+            R.ix[a] = (uint8_t)v;
             if (st.height_px) st.height_px[(size_t)i * c.n_points_x + L.x_start + a] = v;
         }
         for (int b = 0; b < c.n_points_y; ++b) {
@@ -609,7 +624,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
             p = LT_FDIV(LT_FSUB(p, oy), c.horizontal_scale);
             int v = (int)p;
             v = v < 0 ? 0 : (v > c.tile_cols - 2 ? c.tile_cols - 2 : v);
-            R.iy[b] = v;
+            R.iy[b] = (uint8_t)v;
             if (st.height_py) st.height_py[(size_t)i * c.n_points_y + b] = v;
         }
     }
@@ -647,10 +662,10 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     if (switched) { cpi += 1; if (cpi > c.traj_length - 1) cpi = c.traj_length - 1; }
     const bool reached = switched && (cpi == c.traj_length - 1);
     bool plan = (lt_norm2(loc_lin[0], loc_lin[1]) < c.switch_dist) && (fabsf(loc_rot[2]) < c.switch_yaw);
-    const int n_coll = lt_count_contacts(c, R.contact, c.penalised_mask, 0.1f);
+    const int n_coll = (int)(R.cinfo & 0xffu);
     int64_t coll_count = st.collision_count[i] + n_coll;
     // ---- check_termination (LR:198-216)
-    bool reset = lt_count_contacts(c, R.contact, c.termination_mask, 1.0f) > 0;
+    bool reset = (R.cinfo & 0x100u) != 0;
     const bool time_out = ep_f > c.max_episode_length;
     reset = reset || time_out;
     bool body_h = st.body_height_buf[i] != 0;
@@ -665,7 +680,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     // ---- compute_reward (LR:320-355), on pre-reset state
     lt_reward_ctx rc;
     rc.dof = R.dof; rc.last_dof_vel = R.last_dof_vel; rc.torques = R.torques; rc.actions = R.actions;
-    rc.last_actions = R.last_actions; rc.contact = R.contact; rc.root_z = root[2];
+    rc.last_actions = R.last_actions; rc.cinfo = R.cinfo; rc.root_z = root[2];
     for (int k = 0; k < 3; ++k) { rc.blv[k] = P.blv[k]; rc.bav[k] = P.bav[k]; rc.pg[k] = P.pg[k];
                                   rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = loc_lin[k]; }
     rc.ep_f = ep_f; rc.reached = reached; rc.n_collisions = n_coll;
@@ -695,12 +710,12 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     if (st.command_sums) st.command_sums[(size_t)c.n_terms * N + i] = LT_FADD(st.command_sums[(size_t)c.n_terms * N + i], 1.0f);
 
     // ---- reset_idx (LR:218-296) for this env
-    float last_actions_post[LT_MAX_DOF];
-    for (int d = 0; d < c.num_actions; ++d) last_actions_post[d] = R.last_actions[d];
+    float last_actions_post[LT_ND];
+    _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) last_actions_post[d] = R.last_actions[d];
     if (reset) {
         lt_randomize_dof_props(c, st, i, U, LT_SLOT_RESET_STRENGTH);
         // _reset_dofs LR:998-1013
-        for (int d = 0; d < nd; ++d) {
+        _Pragma("unroll") for (int d = 0; d < nd; ++d) {
             R.dof[2 * d] = LT_FMUL(c.default_dof_pos[d], LT_FADD(LT_FMUL(1.0f, U.get(LT_SLOT_RESET_DOF + d)), 0.5f));
             R.dof[2 * d + 1] = 0.0f;
         }
@@ -730,7 +745,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         cpi = 0;
         lt_resample_trajectory(c, st, i, root, U);
         // buffers LR:246-254
-        for (int d = 0; d < c.num_actions; ++d) last_actions_post[d] = 0.0f;
+        _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) last_actions_post[d] = 0.0f;
         for (int f = 0; f < c.n_feet; ++f) st.feet_air_time[(size_t)i * c.n_feet + f] = 0.0f;
         for (int k = 0; k < 3; ++k) { loc_lin[k] = 0.0f; loc_rot[k] = 0.0f; }
         plan = true;
@@ -746,7 +761,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         coll_count = 0;
         ep = 0;
         for (int s = 0; s < L.lag_slots; ++s)
-            for (int d = 0; d < nd; ++d) st.lag_buffer[((size_t)s * N + i) * nd + d] = 0.0f;
+            _Pragma("unroll") for (int d = 0; d < nd; ++d) st.lag_buffer[((size_t)s * N + i) * nd + d] = 0.0f;
     }
     st.episode_length_buf[i] = ep;
     st.curr_pose_index[i] = cpi;
@@ -761,25 +776,25 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     res.z_post = root[2];
 
     // ---- compute_observations, non-height columns (LR:357-475); state is post-reset except projected_gravity
-    float* H = R.head;
-    if (L.col_lin_only >= 0) for (int k = 0; k < 3; ++k) H[lt_head_index(L, L.col_lin_only + k)] = LT_FMUL(P.blv[k], c.obs_scale_lin_vel);
-    if (L.col_ang_only >= 0) for (int k = 0; k < 3; ++k) H[lt_head_index(L, L.col_ang_only + k)] = LT_FMUL(P.bav[k], c.obs_scale_ang_vel);
+    float* H = R.obs_row;
+    if (L.col_lin_only >= 0) for (int k = 0; k < 3; ++k) H[L.col_lin_only + k] = LT_FMUL(P.blv[k], c.obs_scale_lin_vel);
+    if (L.col_ang_only >= 0) for (int k = 0; k < 3; ++k) H[L.col_ang_only + k] = LT_FMUL(P.bav[k], c.obs_scale_ang_vel);
     if (L.col_vel >= 0) {
         for (int k = 0; k < 3; ++k) {
             const float lv = c.global_reference ? root[7 + k] : P.blv[k];
-            H[lt_head_index(L, L.col_vel + k)] = LT_FMUL(lv, c.obs_scale_lin_vel);
-            H[lt_head_index(L, L.col_vel + 3 + k)] = LT_FMUL(P.bav[k], c.obs_scale_ang_vel);
+            H[L.col_vel + k] = LT_FMUL(lv, c.obs_scale_lin_vel);
+            H[L.col_vel + 3 + k] = LT_FMUL(P.bav[k], c.obs_scale_ang_vel);
         }
     }
-    for (int k = 0; k < 3; ++k) H[lt_head_index(L, L.col_gravity + k)] = P.pg[k];
-    if (L.col_commands >= 0) for (int k = 0; k < 2; ++k) H[lt_head_index(L, L.col_commands + k)] = LT_FMUL(loc_lin[k], 1.0f);
-    for (int d = 0; d < nd; ++d) {
-        H[lt_head_index(L, L.col_dof_pos + d)] = LT_FMUL(LT_FSUB(R.dof[2 * d], c.default_dof_pos[d]), c.obs_scale_dof_pos);
-        H[lt_head_index(L, L.col_dof_vel + d)] = LT_FMUL(R.dof[2 * d + 1], c.obs_scale_dof_vel);
+    for (int k = 0; k < 3; ++k) H[L.col_gravity + k] = P.pg[k];
+    if (L.col_commands >= 0) for (int k = 0; k < 2; ++k) H[L.col_commands + k] = LT_FMUL(loc_lin[k], 1.0f);
+    _Pragma("unroll") for (int d = 0; d < nd; ++d) {
+        H[L.col_dof_pos + d] = LT_FMUL(LT_FSUB(R.dof[2 * d], c.default_dof_pos[d]), c.obs_scale_dof_pos);
+        H[L.col_dof_vel + d] = LT_FMUL(R.dof[2 * d + 1], c.obs_scale_dof_vel);
     }
-    for (int d = 0; d < c.num_actions; ++d) H[lt_head_index(L, L.col_actions + d)] = R.actions[d];
-    if (L.col_timestep >= 0) H[lt_head_index(L, L.col_timestep)] = LT_FDIV((float)ep, c.max_episode_length);
-    if (L.col_last_actions >= 0) for (int d = 0; d < c.num_actions; ++d) H[lt_head_index(L, L.col_last_actions + d)] = last_actions_post[d];
+    _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) H[L.col_actions + d] = R.actions[d];
+    if (L.col_timestep >= 0) H[L.col_timestep] = LT_FDIV((float)ep, c.max_episode_length);
+    if (L.col_last_actions >= 0) _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) H[L.col_last_actions + d] = last_actions_post[d];
     if (L.col_yaw >= 0) {
         // quat_apply(base_quat, [1,0,0]) then atan2 (LR:459-462; planner.py:17-23)
         const float* q = root + 3;
@@ -790,11 +805,11 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         lt_cross(q, t, u);
         const float fx = LT_FADD(LT_FADD(fwd[0], LT_FMUL(q[3], t[0])), u[0]);
         const float fy = LT_FADD(LT_FADD(fwd[1], LT_FMUL(q[3], t[1])), u[1]);
-        H[lt_head_index(L, L.col_yaw)] = atan2f(fy, fx);
+        H[L.col_yaw] = atan2f(fy, fx);
     }
     if (L.col_contacts >= 0)
         for (int f = 0; f < c.n_feet; ++f)
-            H[lt_head_index(L, L.col_contacts + f)] = (R.contact[c.feet_indices[f] * 3 + 2] > 1.0f) ? 1.0f : 0.0f;
+            H[L.col_contacts + f] = ((R.cinfo >> (16 + f)) & 1u) ? 1.0f : 0.0f;
 
     // ---- privileged observations (LR:477-590), clipped like LR:110-111
     if (c.num_privileged_obs > 0) {
@@ -806,8 +821,8 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         if (c.priv_observe_restitution) LT_PRIV(1, st.restitutions[i]);
         if (c.priv_observe_base_mass) LT_PRIV(2, st.payloads[i]);
         if (c.priv_observe_com_displacement) for (int a = 0; a < 3; ++a) LT_PRIV(3, st.com_displacements[(size_t)i * 3 + a]);
-        if (c.priv_observe_motor_strength) for (int d = 0; d < nd; ++d) LT_PRIV(4, st.motor_strengths[(size_t)i * nd + d]);
-        if (c.priv_observe_motor_offset) for (int d = 0; d < nd; ++d) LT_PRIV(5, st.motor_offsets[(size_t)i * nd + d]);
+        if (c.priv_observe_motor_strength) _Pragma("unroll") for (int d = 0; d < nd; ++d) LT_PRIV(4, st.motor_strengths[(size_t)i * nd + d]);
+        if (c.priv_observe_motor_offset) _Pragma("unroll") for (int d = 0; d < nd; ++d) LT_PRIV(5, st.motor_offsets[(size_t)i * nd + d]);
         if (c.priv_observe_body_height) LT_PRIV(6, root[2]);
         if (c.priv_observe_body_velocity) for (int a = 0; a < 3; ++a) LT_PRIV(7, P.blv[a]);
         if (c.priv_observe_gravity)       // LR:574-579 DIVIDES by the scale
@@ -833,4 +848,27 @@ LT_HD float lt_height_obs(const lt_config& c, float h, float z_post, float cam_z
 LT_HD float lt_obs_finish(const lt_config& c, float v, float u, float noise_scale) {
     if (c.add_noise) v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), noise_scale));
     return fminf(fmaxf(v, -c.clip_observations), c.clip_observations);
+}
+
+// Observation-noise uniform of (env, obs column) when none is injected: the kernel's lane/block assignment restated
+// per column (heights: lane = point & 31, 8 values = 4 points x 2 layers per call; other columns: 8 per call).
+LT_HD float lt_noise_uniform(const lt_config& c, const lt_layout& L, uint32_t env, int col, uint32_t step) {
+    const int per_layer = L.nxf * c.n_points_y;
+    const int hc = col - L.h0;
+    uint32_t lane, block;
+    int word, half;
+    if (hc >= 0 && hc < L.n_heights) {
+        const int layer = hc / per_layer, pt = hc - layer * per_layer, k = pt >> 5;
+        lane = (uint32_t)(pt & 31); block = (uint32_t)(k >> 2);
+        word = (k & 1) ? (layer ? 3 : 2) : (layer ? 1 : 0);
+        half = (k & 2) ? 1 : 0;
+    } else {
+        const int hi = lt_head_index(L, col), m = hi >> 5, s = m & 7;
+        lane = (uint32_t)(hi & 31); block = (uint32_t)(64 + (m >> 3));
+        word = (s & 2) ? ((s & 4) ? 3 : 1) : ((s & 4) ? 2 : 0);
+        half = s & 1;
+    }
+    uint32_t o[4];
+    lt_philox(env, (lane + 32u * block) | LT_STREAM_NOISE, step, 0u, c.seed_lo, c.seed_hi, o);
+    return lt_u16(o[word] >> (half ? 16 : 0));
 }

@@ -2,10 +2,11 @@
 //
 // Kernels (LR = reference go1_gym/envs/base/legged_robot_trajectory_tracking.py):
 //   lt_torque_kernel     _compute_torques + actuator net (LR:957-996, 1311-1320); one thread per (env, dof)
-//   lt_step_kernel<EPW>  post_physics_step (LR:114-169) fused: each warp owns a tile of EPW consecutive envs;
-//                        tile rows are staged in shared memory with 16-byte cp.async copies, one lane per env runs
-//                        the scalar logic (lt_core.cuh), then the whole warp streams the wide rows (observation
-//                        row incl. the heightfield gathers, history shifts) with coalesced accesses
+//   lt_step_kernel<EPW>  post_physics_step (LR:114-169) up to the observation row: each warp owns a tile of EPW
+//                        consecutive envs; root/dof tile rows are staged in shared memory with 16-byte cp.async
+//                        copies, one lane per env runs the scalar logic (lt_core.cuh) and shifts the history rows
+//   lt_obs_kernel<KP,N>  compute_observations (LR:357-475): one warp per env streams the observation row incl. the
+//                        heightfield gathers, noise, clamp, obs_history
 //   lt_compact_kernel    reset_buf.nonzero() (LR:143), extras["time_outs"] latch (LR:289-291), step counters
 //   lt_sign_kernel       all-env sums of the sign-indefinite reward terms (LR:332-335), only when configured
 // There is no CPU fallback: lt_create fails without an sm_100 device.
@@ -18,10 +19,10 @@
 
 #include "lt_core.cuh"
 
-#define LT_ND 12                       // Go1: 12 actuated dofs = 12 actions (validated in lt_create)
-#define LT_STEP_THREADS 128
+#define LT_STEP_THREADS 64
 #define LT_TORQUE_THREADS 128
 #define LT_COMPACT_THREADS 1024
+#define LT_OBS_THREADS 256
 
 // ---------------------------------------------------------------------------------------------------------------
 struct lt_step_params {
@@ -34,7 +35,23 @@ struct lt_step_params {
     lt_step_scalars sc;
     const float* noise_scale_vec;    // device [num_obs]
     const int32_t* counters;         // device int32[4]
-    int32_t smem_floats_per_warp;
+    uint8_t* scratch;                // [num_envs, rec_bytes] private: what lt_obs_kernel needs from lt_step_kernel
+    int32_t rec_bytes;
+};
+
+struct lt_obs_params {
+    int32_t num_envs, num_obs, obs_history_length, per_layer, nxf, h0, n_heights, head_w, plane, camera_zero;
+    int32_t tile_cols, tile_cells, rec_bytes;
+    uint32_t seed_lo, seed_hi;
+    float clip_observations, ceiling_height, obs_scale_height;
+    const uint8_t* scratch;
+    const uint32_t* ptlut;           // [per_layer] x row | y column << 8 of each measured point
+    const float* tile_heights;
+    const int32_t* env_tile;
+    const float* noise_scale_vec;
+    const float* noise_uniforms;
+    const int32_t* counters;
+    float *obs_buf, *obs_history;
 };
 
 struct lt_torque_params {
@@ -59,6 +76,9 @@ struct lt_handle {
     float* d_noise_scale;
     float* d_term_sums;
     int32_t* d_counters;
+    uint8_t* d_scratch;
+    uint32_t* d_ptlut;
+    int32_t rec_bytes;
     int32_t substeps_pending;        // lt_compute_torques calls since the last lt_post_physics_step
     bool sign_prepass_done;
     int epw;
@@ -103,6 +123,7 @@ __device__ __forceinline__ void lt_tile_store(float* g, const float* s, int n, i
         for (int k = lane; k < n; k += 32) g[k] = s[k];
     }
 }
+__device__ __forceinline__ void lt_prefetch(const void* g) { asm volatile("prefetch.global.L1 [%0];" ::"l"(g)); }
 __device__ __forceinline__ bool lt_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -155,30 +176,38 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS) lt_torque_kernel(const __gr
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// post_physics_step, fused.  Shared memory per warp (floats), all regions 16-byte aligned for EPW % 4 == 0:
-//   root[EPW*A*13] dof[EPW*24] contact[EPW*B*3] actions[EPW*12] last_actions[EPW*12] last_dof_vel[EPW*12]
-//   torques[EPW*12] head[EPW*head_w4] ix[EPW*nxf] iy[EPW*ny] meta[EPW*4] (reset, z_post, cam_z, tile)
+// post_physics_step up to the observation row.  One warp owns EPW consecutive envs, one lane per env.
+//   phase 0  cp.async (16 B) stages the tile's root_states and dof_state rows in shared memory (both are written
+//            back: arrow pose every step, robot root / dofs on reset); each lane reads its env's [12]-rows straight
+//            into registers, reduces its env's contact forces to one packed word and prefetches the per-env words
+//            the scalar logic will touch
+//   phase 1  the scalar step logic (lt_core.cuh); non-height observation columns go straight to obs_buf, the
+//            heightfield cell indices + post-reset z + camera z into a packed per-env record for lt_obs_kernel
+//   phase 2  flat coalesced write-back of the root / dof / record tiles
+// Shared memory per warp: root[EPW*A*13] dof[EPW*24] floats + rec[EPW*rec_bytes] bytes.
 struct lt_smem_plan {
-    int root, dof, contact, actions, last_actions, last_dof_vel, torques, head, ix, iy, meta, total, head_w4;
+    int root, dof, rec, total;       // float offsets
 };
 __host__ __device__ inline int lt_align4(int x) { return (x + 3) & ~3; }
-__host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, const lt_layout& L, int epw) {
+__host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, int rec_bytes, int epw) {
     lt_smem_plan P;
     int o = 0;
     P.root = o; o += lt_align4(epw * c.num_actors * 13);
     P.dof = o; o += lt_align4(epw * LT_ND * 2);
-    P.contact = o; o += lt_align4(epw * c.num_bodies * 3);
-    P.actions = o; o += lt_align4(epw * LT_ND);
-    P.last_actions = o; o += lt_align4(epw * LT_ND);
-    P.last_dof_vel = o; o += lt_align4(epw * LT_ND);
-    P.torques = o; o += lt_align4(epw * LT_ND);
-    P.head_w4 = L.head_w | 1;                       // odd stride: conflict-free lane-per-env writes
-    P.head = o; o += lt_align4(epw * P.head_w4);
-    P.ix = o; o += lt_align4(epw * (L.nxf > 0 ? L.nxf : 1));
-    P.iy = o; o += lt_align4(epw * (c.n_points_y > 0 ? c.n_points_y : 1));
-    P.meta = o; o += lt_align4(epw * 4);
+    P.rec = o; o += lt_align4(epw * rec_bytes / 4);
     P.total = o;
     return P;
+}
+
+__device__ __forceinline__ void lt_load_row12(const float* g, float* r) {
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { const float4 v = g4[k]; r[4 * k] = v.x; r[4 * k + 1] = v.y; r[4 * k + 2] = v.z; r[4 * k + 3] = v.w; }
+}
+__device__ __forceinline__ void lt_store_row12(float* g, const float* r) {
+    float4* g4 = reinterpret_cast<float4*>(g);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) g4[k] = make_float4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
 }
 
 template <int EPW>
@@ -192,150 +221,177 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     constexpr int WARPS = LT_STEP_THREADS / 32;
     const int N = c.num_envs;
     const int A13 = c.num_actors * 13, B3 = c.num_bodies * 3;
+    const int rec_bytes = p.rec_bytes;
 
-    // per-CTA lookup: height column -> (layer, x row, y column) packed
-    uint32_t* lut = reinterpret_cast<uint32_t*>(smem);
-    const int lut_words = lt_align4(L.n_heights);
-    for (int k = threadIdx.x; k < L.n_heights; k += LT_STEP_THREADS) {
-        const int per_layer = L.nxf * c.n_points_y;
-        const int layer = k / per_layer, rem = k - layer * per_layer;
-        const int a = rem / c.n_points_y, b = rem - a * c.n_points_y;
-        lut[k] = (uint32_t)a | ((uint32_t)b << 8) | ((uint32_t)layer << 16);
-    }
-    __syncthreads();
-
-    const lt_smem_plan P = lt_plan_smem(c, L, EPW);
-    float* ws = smem + lut_words + (size_t)warp * P.total;
+    const lt_smem_plan P = lt_plan_smem(c, rec_bytes, EPW);
+    float* ws = smem + (size_t)warp * P.total;
     float* s_root = ws + P.root;
     float* s_dof = ws + P.dof;
-    float* s_contact = ws + P.contact;
-    float* s_actions = ws + P.actions;
-    float* s_last_actions = ws + P.last_actions;
-    float* s_last_dof_vel = ws + P.last_dof_vel;
-    float* s_torques = ws + P.torques;
-    float* s_head = ws + P.head;
-    int32_t* s_ix = reinterpret_cast<int32_t*>(ws + P.ix);
-    int32_t* s_iy = reinterpret_cast<int32_t*>(ws + P.iy);
-    float* s_meta = ws + P.meta;
+    uint8_t* s_rec = reinterpret_cast<uint8_t*>(ws + P.rec);
 
     const int tile = blockIdx.x * WARPS + warp;
     const int env0 = tile * EPW;
     if (env0 >= N) return;
     const int nv = min(EPW, N - env0);            // valid envs in this tile
     const bool full = (nv == EPW) && (EPW % 4 == 0);
-    const uint32_t step = (uint32_t)p.counters[0];
+    const bool mine = lane < nv;
+    const int i = env0 + lane;
 
-    // ---- phase 0: stage the tile rows (flat, contiguous in every source tensor)
+    // ---- phase 0
     lt_tile_load(s_root, p.sim.root_states + (size_t)env0 * A13, nv * A13, lane, full);
     lt_tile_load(s_dof, p.sim.dof_state + (size_t)env0 * LT_ND * 2, nv * LT_ND * 2, lane, full);
-    lt_tile_load(s_contact, p.sim.contact_forces + (size_t)env0 * B3, nv * B3, lane, full);
-    lt_tile_load(s_actions, st.actions + (size_t)env0 * LT_ND, nv * LT_ND, lane, full);
-    lt_tile_load(s_last_actions, st.last_actions + (size_t)env0 * LT_ND, nv * LT_ND, lane, full);
-    lt_tile_load(s_last_dof_vel, st.last_dof_vel + (size_t)env0 * LT_ND, nv * LT_ND, lane, full);
-    lt_tile_load(s_torques, st.torques + (size_t)env0 * LT_ND, nv * LT_ND, lane, full);
+    float r_act[LT_ND], r_last_act[LT_ND], r_last_dof_vel[LT_ND], r_torques[LT_ND];
+    uint32_t cinfo = 0u;
+    if (mine) {
+        lt_load_row12(st.actions + (size_t)i * LT_ND, r_act);
+        lt_load_row12(st.last_actions + (size_t)i * LT_ND, r_last_act);
+        lt_load_row12(st.last_dof_vel + (size_t)i * LT_ND, r_last_dof_vel);
+        lt_load_row12(st.torques + (size_t)i * LT_ND, r_torques);
+        // the scalar phase walks these per-env words one dependent round trip at a time: start them all now
+        lt_prefetch(st.episode_length_buf + i);
+        lt_prefetch(st.curr_pose_index + i);
+        lt_prefetch(st.collision_count + i);
+        lt_prefetch(st.base_rotation + (size_t)i * 3);
+        lt_prefetch(st.trajectories + (size_t)i * c.traj_length * 6);
+        lt_prefetch(st.friction_coeffs + i);
+        lt_prefetch(st.restitutions + i);
+        lt_prefetch(st.body_height_buf + i);
+        lt_prefetch(st.joint_pos_target + (size_t)i * LT_ND);
+        lt_prefetch(st.last_joint_pos_target + (size_t)i * LT_ND);
+        if (c.observe_heights && !c.plane) lt_prefetch(p.ter.env_terrain_origin + (size_t)i * 3);
+        for (int t = 0; t < L.n_sums; ++t) lt_prefetch(st.episode_sums + (size_t)t * N + i);
+        if (st.command_sums) for (int t = 0; t <= c.n_terms; ++t) lt_prefetch(st.command_sums + (size_t)t * N + i);
+        cinfo = lt_contact_summary(c, p.sim.contact_forces + (size_t)i * B3);
+    }
     lt_cp_async_wait_all();
     __syncwarp();
 
-    // ---- phase 1: one lane per env, the scalar logic of the step
-    if (lane < nv) {
-        const int i = env0 + lane;
+    // ---- phase 1: the scalar logic of the step
+    int my_reset = 0;
+    if (mine) {
         lt_env_rows R;
         R.root = s_root + lane * A13;
         R.arrow = (c.num_actors > 1) ? s_root + lane * A13 + (c.num_actors - 1) * 13 : nullptr;
         R.dof = s_dof + lane * LT_ND * 2;
-        R.contact = s_contact + lane * B3;
-        R.actions = s_actions + lane * LT_ND;
-        R.last_actions = s_last_actions + lane * LT_ND;
-        R.last_dof_vel = s_last_dof_vel + lane * LT_ND;
-        R.torques = s_torques + lane * LT_ND;
-        R.head = s_head + lane * P.head_w4;
-        R.ix = s_ix + lane * (L.nxf > 0 ? L.nxf : 1);
-        R.iy = s_iy + lane * (c.n_points_y > 0 ? c.n_points_y : 1);
+        R.cinfo = cinfo;
+        R.actions = r_act;
+        R.last_actions = r_last_act;
+        R.last_dof_vel = r_last_dof_vel;
+        R.torques = r_torques;
+        R.obs_row = st.obs_buf + (size_t)i * c.num_obs;
+        uint8_t* rec = s_rec + lane * rec_bytes;
+        R.ix = rec;
+        R.iy = rec + L.nxf;
         lt_step_scalars sc = p.sc;
-        sc.step = step;
+        sc.step = (uint32_t)p.counters[0];
         const lt_env_result r = lt_env_step(c, L, st, p.ter, p.args, sc, i, R);
-        s_meta[lane * 4 + 0] = r.reset ? 1.0f : 0.0f;
-        s_meta[lane * 4 + 1] = r.z_post;
-        s_meta[lane * 4 + 2] = r.cam_z;
-        s_meta[lane * 4 + 3] = __int_as_float((c.observe_heights && !c.plane) ? p.ter.env_tile[i] : 0);
+        my_reset = r.reset;
+        *reinterpret_cast<float2*>(rec + rec_bytes - 8) = make_float2(r.z_post, r.cam_z);
+        // history shifts (LR:148-153) of this env's rows, straight from registers
+        float row[LT_ND];
+#pragma unroll
+        for (int d = 0; d < LT_ND; ++d) row[d] = my_reset ? 0.0f : r_last_act[d];      // last_actions[env_ids] = 0 precedes the shift (LR:246)
+        lt_store_row12(st.last_last_actions + (size_t)i * LT_ND, row);
+        lt_store_row12(st.last_actions + (size_t)i * LT_ND, r_act);
+        lt_load_row12(st.last_joint_pos_target + (size_t)i * LT_ND, row);
+        lt_store_row12(st.last_last_joint_pos_target + (size_t)i * LT_ND, row);
+        lt_load_row12(st.joint_pos_target + (size_t)i * LT_ND, row);
+        lt_store_row12(st.last_joint_pos_target + (size_t)i * LT_ND, row);
+#pragma unroll
+        for (int d = 0; d < LT_ND; ++d) row[d] = R.dof[2 * d + 1];                      // post-reset dof_vel
+        lt_store_row12(st.last_dof_vel + (size_t)i * LT_ND, row);
+        float2* lrv = reinterpret_cast<float2*>(st.last_root_vel + (size_t)i * 6);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) lrv[k] = make_float2(R.root[7 + 2 * k], R.root[8 + 2 * k]);
     }
     __syncwarp();
-    const unsigned reset_mask = __ballot_sync(0xffffffffu, lane < nv && s_meta[lane * 4] != 0.0f);
+    const unsigned reset_mask = __ballot_sync(0xffffffffu, my_reset != 0);
 
-    // ---- phase 2: write back the sim rows the step owns (arrow pose every step; robot root / dofs on reset)
+    // ---- phase 2: write back the sim rows the step owns (arrow pose every step; robot root / dofs on reset) and the
+    // records of the observation pass
     if (c.num_actors > 1 || reset_mask) lt_tile_store(p.sim.root_states + (size_t)env0 * A13, s_root, nv * A13, lane, full);
     if (reset_mask) lt_tile_store(p.sim.dof_state + (size_t)env0 * LT_ND * 2, s_dof, nv * LT_ND * 2, lane, full);
+    lt_tile_store(reinterpret_cast<float*>(p.scratch + (size_t)env0 * rec_bytes), reinterpret_cast<const float*>(s_rec),
+                  nv * rec_bytes / 4, lane, true);
+}
 
-    // ---- phase 3: history shifts (LR:148-153), float4 over the [EPW, 12] tiles
-    {
-        const size_t g0 = (size_t)env0 * LT_ND;
-        for (int k = lane * 4; k < nv * LT_ND; k += 128) {
-            const int e = k / LT_ND, d = k - e * LT_ND;
-            const bool rs = (reset_mask >> e) & 1u;
-            float4 la = *reinterpret_cast<const float4*>(s_last_actions + k);
-            if (rs) la = make_float4(0.f, 0.f, 0.f, 0.f);          // last_actions[env_ids] = 0 before the shift (LR:246)
-            *reinterpret_cast<float4*>(st.last_last_actions + g0 + k) = la;
-            *reinterpret_cast<float4*>(st.last_actions + g0 + k) = *reinterpret_cast<const float4*>(s_actions + k);
-            const float4 jt = *reinterpret_cast<const float4*>(st.joint_pos_target + g0 + k);
-            const float4 ljt = *reinterpret_cast<const float4*>(st.last_joint_pos_target + g0 + k);
-            *reinterpret_cast<float4*>(st.last_last_joint_pos_target + g0 + k) = ljt;
-            *reinterpret_cast<float4*>(st.last_joint_pos_target + g0 + k) = jt;
-            const float* dv = s_dof + e * LT_ND * 2 + 2 * d + 1;   // post-reset dof_vel
-            *reinterpret_cast<float4*>(st.last_dof_vel + g0 + k) = make_float4(dv[0], dv[2], dv[4], dv[6]);
-        }
-        for (int k = lane; k < nv * 6; k += 32) {
-            const int e = k / 6, j = k - e * 6;
-            st.last_root_vel[(size_t)env0 * 6 + k] = s_root[e * A13 + 7 + j];
+// ---------------------------------------------------------------------------------------------------------------
+// Observation pass: one warp per env.  Reads the env's packed record + raw non-height columns, gathers the 2 x nxf x ny
+// heightfield samples from the (L2-resident) tile table, applies camera / clip / scale (LR:395-409), observation
+// noise (LR:473-474; NOISE 0 = off, 1 = injected uniforms, 2 = in-kernel Philox4x32-10, 8 columns per call), the
+// +-clip_observations clamp (LR:108-109) and writes obs_buf and the newest obs_history block (history_wrapper.py:22).
+// Lane <-> measured point pt = lane + 32 k (k < KP); one cell offset serves both layers.
+template <int KP, int NOISE>
+__global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_constant__ lt_obs_params p) {
+    const int lane = threadIdx.x & 31;
+    const int ie = blockIdx.x * (LT_OBS_THREADS / 32) + (threadIdx.x >> 5);
+    if (ie >= p.num_envs) return;
+    const int no = p.num_obs, H = p.obs_history_length, per_layer = p.per_layer;
+    const uint8_t* rec = p.scratch + (size_t)ie * p.rec_bytes;
+    const float2 zc = *reinterpret_cast<const float2*>(rec + p.rec_bytes - 8);        // (z_post, cam_z)
+    float hc[KP], hf[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+        const int pt = lane + 32 * k;
+        hc[k] = 1.0f;                             // plane: ceiling 1, floor 0 (LR:1928-1932)
+        hf[k] = 0.0f;
+        if (!p.plane && pt < per_layer) {
+            const uint32_t w = __ldg(p.ptlut + pt);
+            const int off = (int)rec[w & 0xffu] * p.tile_cols + (int)rec[p.nxf + (w >> 8)];
+            const float* tile_base = p.tile_heights + (size_t)__ldg(p.env_tile + ie) * 2 * p.tile_cells;
+            hc[k] = __ldg(tile_base + off);
+            hf[k] = __ldg(tile_base + p.tile_cells + off);
         }
     }
-
-    // ---- phase 4: observation rows (LR:357-475) + obs_history (history_wrapper.py:18-24); warp per env
-    const int no = c.num_obs;
-    const int H = c.obs_history_length;
-    const bool plane = c.plane != 0;
-    for (int e = 0; e < nv; ++e) {
-        const int i = env0 + e;
-        const float z_post = s_meta[e * 4 + 1], cam_z = s_meta[e * 4 + 2];
-        const int tile_id = __float_as_int(s_meta[e * 4 + 3]);
-        const float* tile_base = plane ? nullptr : p.ter.tile_heights + (size_t)tile_id * 2 * L.tile_cells;
-        const float* head = s_head + e * P.head_w4;
-        const int32_t* ix = s_ix + e * (L.nxf > 0 ? L.nxf : 1);
-        const int32_t* iy = s_iy + e * (c.n_points_y > 0 ? c.n_points_y : 1);
-        float* obs_row = st.obs_buf + (size_t)i * no;
-        float* hist_row = st.obs_history + (size_t)i * no * H;
-        if (H > 1) {
-            const int keep = (H - 1) * no;
-            for (int k = lane; k < keep; k += 32) { const float v = hist_row[k + no]; hist_row[k] = v; }
+    float* obs_row = p.obs_buf + (size_t)ie * no;
+    float* hist_row = p.obs_history + (size_t)ie * no * H;
+    if (H > 1) {
+        const int keep = (H - 1) * no;
+        for (int k = lane; k < keep; k += 32) { const float v = hist_row[k + no]; hist_row[k] = v; }
+    }
+    float* hist_new = hist_row + (size_t)(H - 1) * no;
+    const float* nz = NOISE == 1 ? p.noise_uniforms + (size_t)ie * no : nullptr;
+    const float clip = p.clip_observations;
+    auto finish = [&](int col, float v, float u) {
+        if (NOISE) v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), __ldg(p.noise_scale_vec + col)));
+        v = fminf(fmaxf(v, -clip), clip);
+        obs_row[col] = v;
+        hist_new[col] = v;
+    };
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+        const int pt = lane + 32 * k;
+        uint32_t rnd[4] = {0u, 0u, 0u, 0u};
+        if (NOISE == 2 && (k & 3) == 0 && pt < per_layer)
+            lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (k >> 2)) | LT_STREAM_NOISE, p.counters[0], 0u, p.seed_lo, p.seed_hi, rnd);
+        if (pt < per_layer) {
+#pragma unroll
+            for (int layer = 0; layer < 2; ++layer) {
+                const int col = p.h0 + layer * per_layer + pt;
+                float h = layer ? hf[k] : hc[k];
+                if (p.camera_zero) h = fminf(fmaxf(LT_FSUB(LT_FSUB(h, zc.x), zc.y), -0.3f), 0.3f);
+                else h = LT_FSUB(LT_FDIV(fminf(fmaxf(h, 0.0f), p.ceiling_height), p.ceiling_height), 0.5f);
+                h = LT_FMUL(h, p.obs_scale_height);
+                float u = 0.5f;
+                if (NOISE == 1) u = nz[col];
+                if (NOISE == 2) u = lt_u16(rnd[(k & 1) * 2 + layer] >> ((k & 2) ? 16 : 0));
+                finish(col, h, u);
+            }
         }
-        float* hist_new = hist_row + (size_t)(H - 1) * no;
-        const float* nz = (c.add_noise && p.args.noise_uniforms) ? p.args.noise_uniforms + (size_t)i * no : nullptr;
-        uint32_t rnd[4];
-        int it = 0;
-        for (int col = lane; col < no; col += 32, ++it) {
-            float v;
-            const int hc = col - L.h0;
-            if (hc >= 0 && hc < L.n_heights) {
-                const uint32_t w = lut[hc];
-                const int a = w & 0xff, b = (w >> 8) & 0xff, layer = w >> 16;
-                float h;
-                if (plane) h = (layer == 0) ? 1.0f : 0.0f;          // LR:1928-1932
-                else h = __ldg(tile_base + (size_t)layer * L.tile_cells + ix[a] * c.tile_cols + iy[b]);
-                v = lt_height_obs(c, h, z_post, cam_z);
-            } else {
-                v = head[hc < 0 ? col : col - L.n_heights];
-            }
+    }
+    const int head_iters = (p.head_w + 31) >> 5;
+    uint32_t rnd[4] = {0u, 0u, 0u, 0u};
+    for (int m = 0; m < head_iters; ++m) {
+        const int hi = lane + 32 * m;
+        if (NOISE == 2 && (m & 7) == 0)
+            lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (64 + (m >> 3))) | LT_STREAM_NOISE, p.counters[0], 0u, p.seed_lo, p.seed_hi, rnd);
+        if (hi < p.head_w) {
+            const int col = hi < p.h0 ? hi : hi + p.n_heights;
+            const int s = m & 7;
             float u = 0.5f;
-            if (c.add_noise) {
-                if (nz) u = nz[col];
-                else {
-                    if ((it & 3) == 0) lt_philox((uint32_t)i, (uint32_t)(lane + 32 * (it >> 2)) | LT_STREAM_NOISE, step, 0u,
-                                                 c.seed_lo, c.seed_hi, rnd);
-                    u = lt_u01(rnd[it & 3]);
-                }
-            }
-            v = lt_obs_finish(c, v, u, c.add_noise ? p.noise_scale_vec[col] : 0.0f);
-            obs_row[col] = v;
-            hist_new[col] = v;
+            if (NOISE == 1) u = nz[col];
+            if (NOISE == 2) u = lt_u16(((s & 2) ? ((s & 4) ? rnd[3] : rnd[1]) : ((s & 4) ? rnd[2] : rnd[0])) >> ((s & 1) ? 16 : 0));
+            finish(col, obs_row[col], u);
         }
     }
 }
@@ -411,7 +467,7 @@ __global__ void __launch_bounds__(256) lt_sign_kernel(const __grid_constant__ lt
             rc.torques = p.st.torques + (size_t)i * LT_ND;
             rc.actions = p.st.actions + (size_t)i * LT_ND;
             rc.last_actions = p.st.last_actions + (size_t)i * LT_ND;
-            rc.contact = p.sim.contact_forces + (size_t)i * c.num_bodies * 3;
+            rc.cinfo = lt_contact_summary(c, p.sim.contact_forces + (size_t)i * c.num_bodies * 3);
             rc.root_z = root[2];
             for (int k = 0; k < 3; ++k) { rc.blv[k] = P.blv[k]; rc.bav[k] = P.bav[k]; rc.pg[k] = P.pg[k];
                                           rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = P.rel_lin[k]; }
@@ -438,8 +494,8 @@ __global__ void __launch_bounds__(256) lt_sign_kernel(const __grid_constant__ lt
 template <int EPW>
 static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) {
     constexpr int WARPS = LT_STEP_THREADS / 32;
-    const lt_smem_plan P = lt_plan_smem(p.c, p.L, EPW);
-    const size_t smem = sizeof(float) * ((size_t)lt_align4(p.L.n_heights) + (size_t)WARPS * P.total);
+    const lt_smem_plan P = lt_plan_smem(p.c, p.rec_bytes, EPW);
+    const size_t smem = sizeof(float) * (size_t)WARPS * P.total;
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(lt_step_kernel<EPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -448,6 +504,14 @@ static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) 
     }
     const int tiles = (p.c.num_envs + EPW - 1) / EPW;
     lt_step_kernel<EPW><<<(tiles + WARPS - 1) / WARPS, LT_STEP_THREADS, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+template <int KP>
+static cudaError_t lt_launch_obs(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
+    const unsigned grid = (unsigned)((p.num_envs + LT_OBS_THREADS / 32 - 1) / (LT_OBS_THREADS / 32));
+    if (noise_mode == 0) lt_obs_kernel<KP, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else if (noise_mode == 1) lt_obs_kernel<KP, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else lt_obs_kernel<KP, 2><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -481,6 +545,8 @@ static int lt_validate(const lt_config& c, std::string& why) {
     LT_REQ(c.control_type == LT_CONTROL_ACTUATOR_NET || c.control_type == LT_CONTROL_P);
     LT_REQ(c.rand_interval >= 1);
     LT_REQ(c.plane || !c.observe_heights || (c.tile_rows >= 2 && c.tile_cols >= 2));
+    LT_REQ(c.n_points_x * c.n_points_y <= 256);
+    LT_REQ(c.plane || !c.observe_heights || (c.tile_rows <= 256 && c.tile_cols <= 256));
     LT_REQ(c.envs_per_warp == 0 || c.envs_per_warp == 4 || c.envs_per_warp == 8 || c.envs_per_warp == 16 || c.envs_per_warp == 32);
 #undef LT_REQ
     lt_layout L;
@@ -536,7 +602,7 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
     int epw = cfg->envs_per_warp;
     if (epw == 0) {
         const int per_sm = (cfg->num_envs + prop.multiProcessorCount - 1) / prop.multiProcessorCount;
-        epw = per_sm >= 384 ? 16 : (per_sm >= 96 ? 8 : 4);
+        epw = per_sm >= 32 ? 32 : 8;
     }
     h->epw = epw;
     cudaError_t e = cudaMalloc(&h->d_noise_scale, sizeof(float) * (size_t)cfg->num_obs);
@@ -545,6 +611,18 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
     if (e == cudaSuccess) e = cudaMemset(h->d_term_sums, 0, sizeof(float) * LT_MAX_TERMS);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_counters, sizeof(int32_t) * 4);
     if (e == cudaSuccess) e = cudaMemset(h->d_counters, 0, sizeof(int32_t) * 4);
+    // private scratch between lt_step_kernel and lt_obs_kernel: per env nxf + ny cell indices (bytes) + 2 floats
+    h->rec_bytes = ((h->L.nxf + cfg->n_points_y + 3) / 4 * 4 + 8 + 15) / 16 * 16;
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_scratch, (size_t)h->rec_bytes * (size_t)cfg->num_envs);
+    if (e == cudaSuccess) e = cudaMemset(h->d_scratch, 0, (size_t)h->rec_bytes * (size_t)cfg->num_envs);
+    {
+        const int per_layer = h->L.nxf * cfg->n_points_y;
+        std::string lut((size_t)(per_layer > 0 ? per_layer : 1) * 4, '\0');
+        uint32_t* w = reinterpret_cast<uint32_t*>(&lut[0]);
+        for (int pt = 0; pt < per_layer; ++pt) w[pt] = (uint32_t)(pt / cfg->n_points_y) | ((uint32_t)(pt % cfg->n_points_y) << 8);
+        if (e == cudaSuccess) e = cudaMalloc(&h->d_ptlut, lut.size());
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_ptlut, lut.data(), lut.size(), cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         const std::string msg = std::string("lt_create: ") + cudaGetErrorString(e);
         delete h;
@@ -559,6 +637,8 @@ void lt_destroy(lt_handle* h) {
     cudaFree(h->d_noise_scale);
     cudaFree(h->d_term_sums);
     cudaFree(h->d_counters);
+    cudaFree(h->d_scratch);
+    cudaFree(h->d_ptlut);
     delete h;
 }
 
@@ -659,6 +739,8 @@ static void lt_fill_step_params(lt_handle* h, const lt_step_args* args, lt_step_
     p.sc.term_sums = h->d_term_sums;
     p.noise_scale_vec = h->d_noise_scale;
     p.counters = h->d_counters;
+    p.scratch = h->d_scratch;
+    p.rec_bytes = h->rec_bytes;
 }
 
 int lt_reward_sign_prepass(lt_handle* h, const lt_step_args* args, void* stream) {
@@ -692,6 +774,21 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream) {
     default: e = lt_launch_step<32>(p, (cudaStream_t)stream); break;
     }
     if (e != cudaSuccess) return lt_fail(h, LT_ERR_CUDA, std::string("lt_step_kernel: ") + cudaGetErrorString(e));
+    {
+        const lt_config& c = h->c;
+        lt_obs_params o;
+        o.num_envs = c.num_envs; o.num_obs = c.num_obs; o.obs_history_length = c.obs_history_length;
+        o.per_layer = h->L.nxf * c.n_points_y; o.nxf = h->L.nxf; o.h0 = h->L.h0; o.n_heights = h->L.n_heights; o.head_w = h->L.head_w;
+        o.plane = c.plane; o.camera_zero = c.camera_zero; o.tile_cols = c.tile_cols; o.tile_cells = h->L.tile_cells;
+        o.rec_bytes = h->rec_bytes; o.seed_lo = c.seed_lo; o.seed_hi = c.seed_hi;
+        o.clip_observations = c.clip_observations; o.ceiling_height = c.ceiling_height; o.obs_scale_height = c.obs_scale_height;
+        o.scratch = h->d_scratch; o.ptlut = h->d_ptlut; o.tile_heights = h->ter.tile_heights; o.env_tile = h->ter.env_tile;
+        o.noise_scale_vec = h->d_noise_scale; o.noise_uniforms = p.args.noise_uniforms; o.counters = h->d_counters;
+        o.obs_buf = h->st.obs_buf; o.obs_history = h->st.obs_history;
+        const int mode = !c.add_noise ? 0 : (p.args.noise_uniforms ? 1 : 2);
+        e = o.per_layer <= 128 ? lt_launch_obs<4>(o, mode, (cudaStream_t)stream) : lt_launch_obs<8>(o, mode, (cudaStream_t)stream);
+        if (e != cudaSuccess) return lt_fail(h, LT_ERR_CUDA, std::string("lt_obs_kernel: ") + cudaGetErrorString(e));
+    }
     const int n = h->c.num_envs;
     lt_compact_kernel<<<(n + LT_COMPACT_THREADS - 1) / LT_COMPACT_THREADS, LT_COMPACT_THREADS, 0, (cudaStream_t)stream>>>(
         h->st.reset_buf, h->st.time_out_buf, h->st.time_outs_latched, h->st.reset_env_ids, h->st.reset_count, h->d_counters, n,

@@ -88,7 +88,7 @@ int lths_post_physics(const lt_config* cfg, const lt_tables* tb, const lt_state_
             lt_reward_ctx rc;
             rc.dof = sim.dof_state + (size_t)i * nd * 2; rc.last_dof_vel = st.last_dof_vel + (size_t)i * nd;
             rc.torques = st.torques + (size_t)i * nd; rc.actions = st.actions + (size_t)i * nd;
-            rc.last_actions = st.last_actions + (size_t)i * nd; rc.contact = sim.contact_forces + (size_t)i * B3;
+            rc.last_actions = st.last_actions + (size_t)i * nd; rc.cinfo = lt_contact_summary(c, sim.contact_forces + (size_t)i * B3);
             rc.root_z = root[2];
             for (int k = 0; k < 3; ++k) { rc.blv[k] = P.blv[k]; rc.bav[k] = P.bav[k]; rc.pg[k] = P.pg[k];
                                           rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = P.rel_lin[k]; }
@@ -97,21 +97,20 @@ int lths_post_physics(const lt_config* cfg, const lt_tables* tb, const lt_state_
         }
         term_sums[t] = (float)acc;
     }
-    std::vector<float> head(L.head_w + 1);
-    std::vector<int32_t> ix(L.nxf + 1), iy(c.n_points_y + 1);
+    std::vector<uint8_t> ix(L.nxf + 1), iy(c.n_points_y + 1);
     std::vector<float> la_pre(nd);
     for (int i = 0; i < N; ++i) {
         lt_env_rows R;
         R.root = sim.root_states + (size_t)i * A13;
         R.arrow = c.num_actors > 1 ? R.root + (c.num_actors - 1) * 13 : nullptr;
         R.dof = sim.dof_state + (size_t)i * nd * 2;
-        R.contact = sim.contact_forces + (size_t)i * B3;
+        R.cinfo = lt_contact_summary(c, sim.contact_forces + (size_t)i * B3);
         R.actions = st.actions + (size_t)i * nd;
         for (int d = 0; d < nd; ++d) la_pre[d] = st.last_actions[(size_t)i * nd + d];
         R.last_actions = la_pre.data();
         R.last_dof_vel = st.last_dof_vel + (size_t)i * nd;
         R.torques = st.torques + (size_t)i * nd;
-        R.head = head.data(); R.ix = ix.data(); R.iy = iy.data();
+        R.obs_row = st.obs_buf + (size_t)i * no; R.ix = ix.data(); R.iy = iy.data();
         const lt_env_result r = lt_env_step(c, L, st, ter, args, sc, i, R);
         // history shifts (kernel phase 3)
         for (int d = 0; d < nd; ++d) {
@@ -138,19 +137,15 @@ int lths_post_physics(const lt_config* cfg, const lt_tables* tb, const lt_state_
                 const int layer = hc / per_layer, rem = hc % per_layer, a = rem / c.n_points_y, b = rem % c.n_points_y;
                 float h;
                 if (c.plane) h = layer == 0 ? 1.0f : 0.0f;
-                else h = tile_base[(size_t)layer * L.tile_cells + ix[a] * c.tile_cols + iy[b]];
+                else h = tile_base[(size_t)layer * L.tile_cells + (int)ix[a] * c.tile_cols + (int)iy[b]];
                 v = lt_height_obs(c, h, r.z_post, r.cam_z);
             } else {
-                v = head[lt_head_index(L, col)];
+                v = obs_row[col];
             }
             float u = 0.5f;
             if (c.add_noise) {
                 if (args.noise_uniforms) u = args.noise_uniforms[(size_t)i * no + col];
-                else {
-                    uint32_t o[4];
-                    lt_philox((uint32_t)i, (uint32_t)((col & 31) + 32 * (col >> 7)) | LT_STREAM_NOISE, sc.step, 0u, c.seed_lo, c.seed_hi, o);
-                    u = lt_u01(o[(col >> 5) & 3]);
-                }
+                else u = lt_noise_uniform(c, L, (uint32_t)i, col, sc.step);
             }
             v = lt_obs_finish(c, v, u, c.add_noise ? tb->noise_scale_vec[col] : 0.0f);
             obs_row[col] = v;

@@ -41,3 +41,63 @@ def test_library_was_loaded_from_tree():
     lib = _abi.load()
     assert _abi.LIB_PATH.endswith("legged_tracking_b200/liblt_b200.so")
     assert lib.lt_abi_version() == _abi.DEFINES["LT_ABI_VERSION"]
+
+
+@pytest.mark.parametrize("name", ["cfg2_single_path_64", "opts_random_target_32"])
+def test_in_kernel_philox_matches_host_mirror(name):
+    """No injected uniforms: the kernel's counter-based generator (reset / DR slots and observation noise) must agree
+    draw for draw with the host-compiled mirror of the same arithmetic (tests/hostsim)."""
+    from tests.hostsim_runner import HostSim
+    fx = T.load_fixture(name)
+    eng = _engine(fx, seed=1234)
+    host = HostSim(fx["flat"], T.sub(fx, "terrain/"), T.load_actuator(), seed=1234)
+    host.load_state(T.sub(fx, "init/"))
+    flat = fx["flat"]
+    N = flat["num_envs"]
+    for k in range(T.num_steps(fx)):
+        d = T.sub(fx, f"step{k}/in/")
+        for e, xp in ((eng, _xp), (host, lambda a: a)):
+            a = xp(np.ascontiguousarray(d["actions"], np.float32))
+            for s in range(flat["decimation"]):
+                e.compute_torques(a, s)
+                e.dof_state[...] = xp(np.ascontiguousarray(d["dof_state"][s], np.float32).reshape(N * 12, 2))
+            e.root_states.reshape(N, -1, 13)[:, 0, :] = xp(np.ascontiguousarray(d["root"], np.float32))
+            e.contact_forces[...] = xp(np.ascontiguousarray(d["contact"], np.float32).reshape(N, -1, 3))
+            e.post_physics_step(gravity_uniform=np.array([0.25, 0.5, 0.75], np.float32))
+        torch.cuda.synchronize()
+        for key in ("obs_buf", "rew_buf", "motor_strengths", "motor_offsets", "trajectories", "obs_history"):
+            T.assert_close(f"step{k}/{key}", T.to_np(eng.state[key]), host.state[key])
+        T.assert_close(f"step{k}/root_states", T.to_np(eng.root_states), host.root_states)
+        T.assert_close(f"step{k}/reset_buf", T.to_np(eng.state["reset_buf"]).astype(bool), host.state["reset_buf"].astype(bool))
+    if flat["add_noise"]:      # the noise actually is noise: obs differs from the noise-free value, within the scale
+        assert np.abs(T.to_np(eng.state["obs_buf"]) - T.sub(fx, f"step{T.num_steps(fx) - 1}/out/")["obs"]).max() > 1e-4
+
+
+def test_philox_noise_statistics():
+    """Uniformity of the in-kernel observation noise: mean 0 and variance scale^2/3 per column over 16k envs."""
+    from legged_tracking_b200 import workload
+    from legged_tracking_b200.engine import StepEngine
+    flat, terrain, act, synth = workload.make("cfg2", num_envs=16384)
+    flat_off = dict(flat, add_noise=False)
+    outs = []
+    for f in (flat, flat_off):
+        eng = StepEngine(f, terrain, act, device="cuda:0", seed=7)
+        a = synth.actions(0).cuda()
+        for s in range(4):
+            eng.dof_state.copy_(synth.dof_state(0, s).cuda())
+            eng.compute_torques(a, s)
+        eng.root_states.view(eng.N, -1, 13)[:, 0, :] = synth.root(0).cuda()
+        eng.contact_forces.copy_(synth.contact(0).cuda())
+        eng.post_physics_step()
+        outs.append(eng.state["obs_buf"].double().cpu())
+    noise = outs[0] - outs[1]
+    scale = torch.tensor(flat["noise_scale_vec"], dtype=torch.float64)
+    cols = scale > 0
+    z = noise[:, cols] / scale[cols]                   # should be U(-1, 1)
+    assert z.abs().max() <= 1.0 + 1e-3
+    assert z.mean(0).abs().max() < 0.03                # sigma of the mean = 0.577 / sqrt(16384) = 0.0045
+    assert (z.var(0) - 1.0 / 3.0).abs().max() < 0.02
+    # neighbouring columns / envs are uncorrelated
+    zc = z - z.mean(0)
+    corr = (zc[:, :-1] * zc[:, 1:]).mean(0) * 3.0
+    assert corr.abs().max() < 0.05
