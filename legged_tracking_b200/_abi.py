@@ -15,7 +15,7 @@ import re
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 HEADER = os.path.join(REPO, "include", "lt_b200.h")
-LIB_PATH = os.path.join(PKG_DIR, "liblt_b200.so")
+LIB_PATH = os.environ.get("LT_B200_LIB") or os.path.join(PKG_DIR, "liblt_b200.so")     # override: tuning variants only
 
 _SCALARS = {"int32_t": C.c_int32, "uint32_t": C.c_uint32, "float": C.c_float, "int64_t": C.c_int64,
             "uint8_t": C.c_uint8, "double": C.c_double}

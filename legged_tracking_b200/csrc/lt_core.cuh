@@ -15,8 +15,10 @@
 
 #if defined(__CUDACC__)
 #define LT_HD __host__ __device__ __forceinline__
+#define LT_HD_COLD __host__ __device__ __noinline__      /* rare paths (reset, domain randomisation): keep them out of the hot code */
 #else
 #define LT_HD inline
+#define LT_HD_COLD inline
 #endif
 
 #if defined(__CUDA_ARCH__)
@@ -34,6 +36,19 @@
 #define LT_FFMA(a, b, c) fmaf((a), (b), (c))
 #define LT_FDIV(a, b) ((a) / (b))
 #define LT_FSQRT(a) sqrtf((a))
+#endif
+
+// tuning switches (profiles/variants.py builds and times the alternatives)
+#ifndef LT_OPT_SUMS_LOCAL
+#define LT_OPT_SUMS_LOCAL 1     /* episode/command sums: load all rows up front into a local array, store once at the end */
+#endif
+#ifndef LT_OPT_UNROLL1
+#define LT_OPT_UNROLL1 1        /* keep the small runtime-bounded loops rolled (instruction-cache footprint) */
+#endif
+#if LT_OPT_UNROLL1
+#define LT_ROLLED _Pragma("unroll 1")
+#else
+#define LT_ROLLED
 #endif
 
 #define LT_ND 12   /* Go1: 12 actuated dofs = 12 actions; lt_create validates num_dof == num_actions == LT_ND */
@@ -127,14 +142,22 @@ LT_HD void lt_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_
 }
 LT_HD float lt_u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }   // [0,1), 24 bits like torch.rand
 
-// 16-bit uniform in (0,1) for the observation noise: two per Philox word, 8 per call
-LT_HD float lt_u16(uint32_t x) { return LT_FMUL((float)(x & 0xffffu) + 0.5f, 1.0f / 65536.0f); }
+// Observation noise: ONE Philox4x32-10 call per (env, lane, call) yields ten 12-bit uniforms in (0,1) (120 of its 128
+// bits).  Value v of a lane (heights: v = 2 k + layer for point lane + 32 k; other columns: v = 2 KP + m for staged
+// column lane + 32 m) uses call v / 10, slot v % 10.
+#define LT_NOISE_PER_CALL 10
+LT_HD float lt_u12(const uint32_t rnd[4], int slot) {
+    const int bit = 12 * slot, w = bit >> 5, sh = bit & 31;
+    const uint64_t pair = (uint64_t)rnd[w] | ((uint64_t)rnd[w < 3 ? w + 1 : 3] << 32);
+    const uint32_t x = (uint32_t)(pair >> sh) & 0xfffu;
+    return LT_FMUL((float)x + 0.5f, 1.0f / 4096.0f);
+}
 
 // Per-env source of the step's uniform slots: injected row (parity) or Philox.
 struct lt_uniform_src {
     const float* row;            // [n_slots] or nullptr
     uint32_t seed_lo, seed_hi, step, env;
-    LT_HD float get(int slot) const {
+    LT_HD_COLD float get(int slot) const {          // only reached on reset / interval randomisation
         if (row) return row[slot];
         uint32_t o[4];
         lt_philox(env, (uint32_t)(slot >> 2) | LT_STREAM_SLOTS, step, 0u, seed_lo, seed_hi, o);
@@ -169,8 +192,9 @@ LT_HD void lt_quat_rotate_inverse(const float q[4], const float v[3], float o[3]
     }
 }
 // python-style float remainder (torch.remainder): sign of the divisor
+LT_HD_COLD float lt_fmod_cold(float a, float b) { return fmodf(a, b); }
 LT_HD float lt_remainder(float a, float b) {
-    float m = fmodf(a, b);
+    float m = fabsf(a) < b ? a : lt_fmod_cold(a, b);      // fmod(a, b) == a exactly when |a| < b (b > 0 at every call site)
     if (m != 0.0f && ((b < 0.0f) != (m < 0.0f))) m = LT_FADD(m, b);
     return m;
 }
@@ -206,7 +230,8 @@ LT_HD void lt_quat_apply_yaw_inverse(const float q[4], const float v[3], float o
 // quat_from_euler_xyz (LR:942; go1_gym/utils/planner.py:25-38)
 LT_HD void lt_quat_from_euler(float roll, float pitch, float yaw, float q[4]) {
     const float hy = LT_FMUL(yaw, 0.5f), hr = LT_FMUL(roll, 0.5f), hp = LT_FMUL(pitch, 0.5f);
-    const float cy = cosf(hy), sy = sinf(hy), cr = cosf(hr), sr = sinf(hr), cp = cosf(hp), sp = sinf(hp);
+    float cy, sy, cr, sr, cp, sp;
+    sincosf(hy, &sy, &cy); sincosf(hr, &sr, &cr); sincosf(hp, &sp, &cp);
     q[3] = LT_FADD(LT_FMUL(LT_FMUL(cy, cr), cp), LT_FMUL(LT_FMUL(sy, sr), sp));
     q[0] = LT_FSUB(LT_FMUL(LT_FMUL(cy, sr), cp), LT_FMUL(LT_FMUL(sy, cr), sp));
     q[1] = LT_FADD(LT_FMUL(LT_FMUL(cy, cr), sp), LT_FMUL(LT_FMUL(sy, sr), cp));
@@ -224,7 +249,15 @@ struct lt_act_weights {
     float w1[LT_ACT_HIDDEN * LT_ACT_HIDDEN], b1[LT_ACT_HIDDEN];
     float w2[LT_ACT_HIDDEN], b2[1];
 };
-LT_HD float lt_softsign(float x) { return LT_FDIV(x, LT_FADD(fabsf(x), 1.0f)); }
+// softsign x / (1 + |x|).  Device: MUFU.RCP-based divide (<= 2 ulp; the denominator is >= 1, never denormal) -- an IEEE
+// divide would be a third of the torque kernel's instructions; the parity budget of the torques is 1e-5.
+LT_HD float lt_softsign(float x) {
+#if defined(__CUDA_ARCH__)
+    return __fdividef(x, fabsf(x) + 1.0f);
+#else
+    return x / (fabsf(x) + 1.0f);
+#endif
+}
 LT_HD float lt_actuator_mlp(const lt_act_weights& W, const float x[LT_ACT_IN]) {
     float h1[LT_ACT_HIDDEN];
 #pragma unroll
@@ -312,7 +345,7 @@ struct lt_step_scalars {         // per-launch scalars
     const float* term_sums;      // device float[LT_MAX_TERMS] all-env sums for LT_BUCKET_BY_SUM terms (or nullptr)
 };
 
-LT_HD void lt_randomize_dof_props(const lt_config& c, const lt_state_ptrs& st, int i, const lt_uniform_src& U, int base) {
+LT_HD_COLD void lt_randomize_dof_props(const lt_config& c, const lt_state_ptrs& st, int i, const lt_uniform_src& U, int base) {
     // LR:744-764: torch.rand(K,1)*(hi-lo)+lo broadcast over the 12 dofs; offsets draw 12
     constexpr int nd = LT_ND;
     if (c.randomize_motor_strength) {
@@ -536,7 +569,7 @@ LT_HD uint32_t lt_contact_summary(const lt_config& c, const float* contact) {
 }
 
 // trajectory functions (go1_gym/envs/trajectories/trajectory_function.py:14-93) for one reset env
-LT_HD void lt_resample_trajectory(const lt_config& c, const lt_state_ptrs& st, int i, const float* root, const lt_uniform_src& U) {
+LT_HD_COLD void lt_resample_trajectory(const lt_config& c, const lt_state_ptrs& st, int i, const float* root, const lt_uniform_src& U) {
     const int L = c.traj_length;
     float* T = st.trajectories + (size_t)i * L * 6;
     if (c.traj_function == LT_TRAJ_FIXED_TARGET) {                 // :14-26
@@ -583,6 +616,43 @@ LT_HD void lt_resample_trajectory(const lt_config& c, const lt_state_ptrs& st, i
     }
 }
 
+// The simulator-state part of reset_idx for one env (rare path, kept out of line): _randomize_dof_props (LR:744-764),
+// _reset_dofs (LR:998-1013), _reset_root_states (LR:1015-1052), _resample_trajectory (LR:949-953).
+LT_HD_COLD void lt_reset_sim_state(const lt_config& c, const lt_state_ptrs& st, const lt_terrain_ptrs& ter,
+                                   const lt_uniform_src& U, int i, float* root, float* dof) {
+    constexpr int nd = LT_ND;
+    lt_randomize_dof_props(c, st, i, U, LT_SLOT_RESET_STRENGTH);
+    // _reset_dofs LR:998-1013
+    _Pragma("unroll") for (int d = 0; d < nd; ++d) {
+        dof[2 * d] = LT_FMUL(c.default_dof_pos[d], LT_FADD(LT_FMUL(1.0f, U.get(LT_SLOT_RESET_DOF + d)), 0.5f));
+        dof[2 * d + 1] = 0.0f;
+    }
+    // _reset_root_states LR:1015-1052
+    for (int k = 0; k < 13; ++k) root[k] = c.base_init_state[k];
+    for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], ter.env_origins[(size_t)i * 3 + k]);
+    if (c.custom_origins) {
+        const float xr = c.x_init_range, yr = c.y_init_range;
+        root[0] = LT_FADD(root[0], LT_FADD(LT_FMUL(LT_FSUB(xr, -xr), U.get(LT_SLOT_RESET_X)), -xr));
+        root[1] = LT_FADD(root[1], LT_FADD(LT_FMUL(LT_FSUB(yr, -yr), U.get(LT_SLOT_RESET_Y)), -yr));
+        root[0] = LT_FADD(root[0], c.x_init_offset);
+        root[1] = LT_FADD(root[1], c.y_init_offset);
+    }
+    {
+        const float yr = c.yaw_init_range;
+        const float yaw = LT_FADD(LT_FMUL(LT_FSUB(yr, -yr), U.get(LT_SLOT_RESET_YAW)), -yr);
+        const float th = LT_FDIV(yaw, 2.0f);
+        const float s = sinf(th), w = cosf(th);
+        // quat_from_angle_axis: normalise([axis*sin, cos]) with axis (0,0,1); 4-norm unfused sequential
+        float n = LT_FSQRT(LT_FADD(LT_FADD(LT_FADD(LT_FMUL(0.0f, 0.0f), LT_FMUL(0.0f, 0.0f)), LT_FMUL(s, s)), LT_FMUL(w, w)));
+        n = fmaxf(n, 1e-9f);
+        root[3] = LT_FDIV(LT_FMUL(0.0f, s), n); root[4] = LT_FDIV(LT_FMUL(0.0f, s), n);
+        root[5] = LT_FDIV(LT_FMUL(1.0f, s), n); root[6] = LT_FDIV(w, n);
+    }
+    for (int k = 0; k < 6; ++k) root[7 + k] = LT_FADD(LT_FMUL(1.0f, U.get(LT_SLOT_RESET_VEL + k)), -0.5f);
+    // _resample_trajectory LR:949-953
+    lt_resample_trajectory(c, st, i, root, U);
+}
+
 // The whole scalar part of one env's post_physics_step.  Returns what the vector phases need.
 LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt_state_ptrs& st,
                                 const lt_terrain_ptrs& ter, const lt_step_args& args, const lt_step_scalars& sc,
@@ -593,13 +663,29 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     U.row = args.uniforms ? args.uniforms + (size_t)i * L.n_slots : nullptr;
     U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.step = sc.step; U.env = (uint32_t)i;
 
-    // ---- LR:126-134
-    int64_t ep = st.episode_length_buf[i] + 1;
+    // ---- every per-env word the step reads, loaded before the first store so that the loads overlap (the compiler
+    // cannot move a load above a store that may alias it)
+    const size_t N = (size_t)c.num_envs;
+    int64_t ep = st.episode_length_buf[i] + 1;      // LR:126
     int64_t cpi = st.curr_pose_index[i];
+    const int64_t coll_count0 = st.collision_count[i];
+    const bool body_h0 = st.body_height_buf[i] != 0;
+    const float cam_pitch_prev = st.base_rotation[(size_t)i * 3 + 1];
+    const float cam_pitch_state = st.camera_pitch_angle[i];
+#if LT_OPT_SUMS_LOCAL
+    float es[LT_MAX_TERMS + 3], cs[LT_MAX_TERMS + 1];
+    LT_ROLLED for (int t = 0; t < L.n_sums; ++t) es[t] = st.episode_sums[(size_t)t * N + i];
+    if (st.command_sums) LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) cs[t] = st.command_sums[(size_t)t * N + i];
+#define LT_ES(t) es[t]
+#define LT_CS(t) cs[t]
+#else
+#define LT_ES(t) st.episode_sums[(size_t)(t) * N + i]
+#define LT_CS(t) st.command_sums[(size_t)(t) * N + i]
+#endif
     float* root = R.root;
 
     // ---- _get_heights index part (LR:1918-1956): previous step's pitch (base_rotation not refreshed yet)
-    const float cam_pitch = st.base_rotation[(size_t)i * 3 + 1];
+    const float cam_pitch = cam_pitch_prev;
     if (c.observe_heights && !c.plane) {
         st.camera_pitch_angle[i] = cam_pitch;
         float offx = 0.0f, offy = 0.0f;
@@ -628,7 +714,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
             if (st.height_py) st.height_py[(size_t)i * c.n_points_y + b] = v;
         }
     }
-    const float cam_pitch_obs = (c.observe_heights && !c.plane) ? cam_pitch : st.camera_pitch_angle[i];
+    const float cam_pitch_obs = (c.observe_heights && !c.plane) ? cam_pitch : cam_pitch_state;
     res.cam_z = LT_FMUL(sinf(cam_pitch_obs), L.cam_off_norm);
 
     // ---- base-frame quantities and goal-relative pose (LR:130-134, 850-932)
@@ -663,12 +749,12 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     const bool reached = switched && (cpi == c.traj_length - 1);
     bool plan = (lt_norm2(loc_lin[0], loc_lin[1]) < c.switch_dist) && (fabsf(loc_rot[2]) < c.switch_yaw);
     const int n_coll = (int)(R.cinfo & 0xffu);
-    int64_t coll_count = st.collision_count[i] + n_coll;
+    int64_t coll_count = coll_count0 + n_coll;
     // ---- check_termination (LR:198-216)
     bool reset = (R.cinfo & 0x100u) != 0;
     const bool time_out = ep_f > c.max_episode_length;
     reset = reset || time_out;
-    bool body_h = st.body_height_buf[i] != 0;
+    bool body_h = body_h0;
     if (c.use_terminal_body_height) { body_h = root[2] < c.terminal_body_height; reset = reset || body_h; }
     if (c.terminate_end_of_trajectory) reset = reset || (reached && ep_f > c.T_reach);
     if (c.use_terminal_body_rotation) reset = reset || (P.pg[2] > 0.0f);
@@ -685,7 +771,6 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
                                   rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = loc_lin[k]; }
     rc.ep_f = ep_f; rc.reached = reached; rc.n_collisions = n_coll;
     float rew = 0.0f, rew_pos = 0.0f, rew_neg = 0.0f;
-    const size_t N = (size_t)c.num_envs;
     for (int t = 0; t < c.n_terms; ++t) {
         const float v = lt_reward_term(c, st, i, c.term_ids[t], rc, args.extra_reward, false);
         const float r = LT_FMUL(v, c.term_scales[t]);
@@ -697,53 +782,28 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         }
         if (bucket == LT_BUCKET_POS) rew_pos = LT_FADD(rew_pos, r);
         else if (bucket == LT_BUCKET_NEG) rew_neg = LT_FADD(rew_neg, r);
-        st.episode_sums[(size_t)t * N + i] = LT_FADD(st.episode_sums[(size_t)t * N + i], r);
-        if (st.command_sums) st.command_sums[(size_t)t * N + i] = LT_FADD(st.command_sums[(size_t)t * N + i], r);
+        LT_ES(t) = LT_FADD(LT_ES(t), r);
+        if (st.command_sums) LT_CS(t) = LT_FADD(LT_CS(t), r);
     }
     if (c.only_positive_rewards) rew = fmaxf(rew, 0.0f);
     else if (c.only_positive_rewards_ji22_style) rew = LT_FMUL(rew_pos, expf(LT_FDIV(rew_neg, c.sigma_rew_neg)));
     st.rew_buf[i] = rew; st.rew_buf_pos[i] = rew_pos; st.rew_buf_neg[i] = rew_neg;
-    float* es_total = st.episode_sums + (size_t)c.n_terms * N;
-    es_total[i] = LT_FADD(es_total[i], rew);
-    es_total[N + i] = LT_FADD(es_total[N + i], rew_pos);
-    es_total[2 * N + i] = LT_FADD(es_total[2 * N + i], rew_neg);
-    if (st.command_sums) st.command_sums[(size_t)c.n_terms * N + i] = LT_FADD(st.command_sums[(size_t)c.n_terms * N + i], 1.0f);
+    LT_ES(c.n_terms) = LT_FADD(LT_ES(c.n_terms), rew);
+    LT_ES(c.n_terms + 1) = LT_FADD(LT_ES(c.n_terms + 1), rew_pos);
+    LT_ES(c.n_terms + 2) = LT_FADD(LT_ES(c.n_terms + 2), rew_neg);
+    if (st.command_sums) {
+        LT_CS(c.n_terms) = LT_FADD(LT_CS(c.n_terms), 1.0f);
+#if LT_OPT_SUMS_LOCAL
+        LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) st.command_sums[(size_t)t * N + i] = cs[t];
+#endif
+    }
 
     // ---- reset_idx (LR:218-296) for this env
     float last_actions_post[LT_ND];
     _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) last_actions_post[d] = R.last_actions[d];
     if (reset) {
-        lt_randomize_dof_props(c, st, i, U, LT_SLOT_RESET_STRENGTH);
-        // _reset_dofs LR:998-1013
-        _Pragma("unroll") for (int d = 0; d < nd; ++d) {
-            R.dof[2 * d] = LT_FMUL(c.default_dof_pos[d], LT_FADD(LT_FMUL(1.0f, U.get(LT_SLOT_RESET_DOF + d)), 0.5f));
-            R.dof[2 * d + 1] = 0.0f;
-        }
-        // _reset_root_states LR:1015-1052
-        for (int k = 0; k < 13; ++k) root[k] = c.base_init_state[k];
-        for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], ter.env_origins[(size_t)i * 3 + k]);
-        if (c.custom_origins) {
-            const float xr = c.x_init_range, yr = c.y_init_range;
-            root[0] = LT_FADD(root[0], LT_FADD(LT_FMUL(LT_FSUB(xr, -xr), U.get(LT_SLOT_RESET_X)), -xr));
-            root[1] = LT_FADD(root[1], LT_FADD(LT_FMUL(LT_FSUB(yr, -yr), U.get(LT_SLOT_RESET_Y)), -yr));
-            root[0] = LT_FADD(root[0], c.x_init_offset);
-            root[1] = LT_FADD(root[1], c.y_init_offset);
-        }
-        {
-            const float yr = c.yaw_init_range;
-            const float yaw = LT_FADD(LT_FMUL(LT_FSUB(yr, -yr), U.get(LT_SLOT_RESET_YAW)), -yr);
-            const float th = LT_FDIV(yaw, 2.0f);
-            const float s = sinf(th), w = cosf(th);
-            // quat_from_angle_axis: normalise([axis*sin, cos]) with axis (0,0,1); 4-norm unfused sequential
-            float n = LT_FSQRT(LT_FADD(LT_FADD(LT_FADD(LT_FMUL(0.0f, 0.0f), LT_FMUL(0.0f, 0.0f)), LT_FMUL(s, s)), LT_FMUL(w, w)));
-            n = fmaxf(n, 1e-9f);
-            root[3] = LT_FDIV(LT_FMUL(0.0f, s), n); root[4] = LT_FDIV(LT_FMUL(0.0f, s), n);
-            root[5] = LT_FDIV(LT_FMUL(1.0f, s), n); root[6] = LT_FDIV(w, n);
-        }
-        for (int k = 0; k < 6; ++k) root[7 + k] = LT_FADD(LT_FMUL(1.0f, U.get(LT_SLOT_RESET_VEL + k)), -0.5f);
-        // _resample_trajectory LR:949-953
+        lt_reset_sim_state(c, st, ter, U, i, root, R.dof);       // DR, dofs, root pose / velocity, new trajectory
         cpi = 0;
-        lt_resample_trajectory(c, st, i, root, U);
         // buffers LR:246-254
         _Pragma("unroll") for (int d = 0; d < LT_ND; ++d) last_actions_post[d] = 0.0f;
         for (int f = 0; f < c.n_feet; ++f) st.feet_air_time[(size_t)i * c.n_feet + f] = 0.0f;
@@ -752,17 +812,20 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         // finished-episode record (LR:256-273) then zero the sums
         st.finished_episode_length[i] = ep_f;
         st.finished_goal_distance[i] = lt_norm3(P.rel_lin[0], P.rel_lin[1], P.rel_lin[2]);
-        for (int s = 0; s < L.n_sums; ++s) {
-            st.finished_sums[(size_t)s * N + i] = st.episode_sums[(size_t)s * N + i];
-            st.episode_sums[(size_t)s * N + i] = 0.0f;
+        LT_ROLLED for (int s = 0; s < L.n_sums; ++s) {
+            st.finished_sums[(size_t)s * N + i] = LT_ES(s);
+            LT_ES(s) = 0.0f;
         }
         st.reached_env_buf[i] = reached ? 1 : 0;
         st.collision_env_buf[i] = reached ? coll_count : 0;
         coll_count = 0;
         ep = 0;
-        for (int s = 0; s < L.lag_slots; ++s)
+        LT_ROLLED for (int s = 0; s < L.lag_slots; ++s)
             _Pragma("unroll") for (int d = 0; d < nd; ++d) st.lag_buffer[((size_t)s * N + i) * nd + d] = 0.0f;
     }
+#if LT_OPT_SUMS_LOCAL
+    LT_ROLLED for (int t = 0; t < L.n_sums; ++t) st.episode_sums[(size_t)t * N + i] = es[t];
+#endif
     st.episode_length_buf[i] = ep;
     st.curr_pose_index[i] = cpi;
     st.collision_count[i] = coll_count;
@@ -850,25 +913,24 @@ LT_HD float lt_obs_finish(const lt_config& c, float v, float u, float noise_scal
     return fminf(fmaxf(v, -c.clip_observations), c.clip_observations);
 }
 
-// Observation-noise uniform of (env, obs column) when none is injected: the kernel's lane/block assignment restated
-// per column (heights: lane = point & 31, 8 values = 4 points x 2 layers per call; other columns: 8 per call).
+// Observation-noise uniform of (env, obs column) when none is injected: lt_obs_kernel's lane / call / slot assignment
+// restated per column (used by the host mirror).
 LT_HD float lt_noise_uniform(const lt_config& c, const lt_layout& L, uint32_t env, int col, uint32_t step) {
     const int per_layer = L.nxf * c.n_points_y;
+    const int kp = per_layer <= 128 ? 4 : 8;
     const int hc = col - L.h0;
-    uint32_t lane, block;
-    int word, half;
+    uint32_t lane;
+    int v;
     if (hc >= 0 && hc < L.n_heights) {
-        const int layer = hc / per_layer, pt = hc - layer * per_layer, k = pt >> 5;
-        lane = (uint32_t)(pt & 31); block = (uint32_t)(k >> 2);
-        word = (k & 1) ? (layer ? 3 : 2) : (layer ? 1 : 0);
-        half = (k & 2) ? 1 : 0;
+        const int layer = hc / per_layer, pt = hc - layer * per_layer;
+        lane = (uint32_t)(pt & 31);
+        v = 2 * (pt >> 5) + layer;
     } else {
-        const int hi = lt_head_index(L, col), m = hi >> 5, s = m & 7;
-        lane = (uint32_t)(hi & 31); block = (uint32_t)(64 + (m >> 3));
-        word = (s & 2) ? ((s & 4) ? 3 : 1) : ((s & 4) ? 2 : 0);
-        half = s & 1;
+        const int hi = lt_head_index(L, col);
+        lane = (uint32_t)(hi & 31);
+        v = 2 * kp + (hi >> 5);
     }
     uint32_t o[4];
-    lt_philox(env, (lane + 32u * block) | LT_STREAM_NOISE, step, 0u, c.seed_lo, c.seed_hi, o);
-    return lt_u16(o[word] >> (half ? 16 : 0));
+    lt_philox(env, (lane + 32u * (uint32_t)(v / LT_NOISE_PER_CALL)) | LT_STREAM_NOISE, step, 0u, c.seed_lo, c.seed_hi, o);
+    return lt_u12(o, v % LT_NOISE_PER_CALL);
 }

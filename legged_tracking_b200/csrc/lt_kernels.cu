@@ -19,7 +19,9 @@
 
 #include "lt_core.cuh"
 
+#ifndef LT_STEP_THREADS
 #define LT_STEP_THREADS 64
+#endif
 #define LT_TORQUE_THREADS 128
 #define LT_COMPACT_THREADS 1024
 #define LT_OBS_THREADS 256
@@ -111,19 +113,26 @@ __device__ __forceinline__ void lt_cp_async_wait_all() {
 // stage `n` floats (16-byte aligned source, n % 4 == 0 when `vec`) global -> shared, one warp
 __device__ __forceinline__ void lt_tile_load(float* s, const float* g, int n, int lane, bool vec) {
     if (vec) {
-        for (int k = lane * 4; k < n; k += 128) lt_cp_async16(s + k, g + k);
+        LT_ROLLED for (int k = lane * 4; k < n; k += 128) lt_cp_async16(s + k, g + k);
     } else {
-        for (int k = lane; k < n; k += 32) s[k] = g[k];
+        LT_ROLLED for (int k = lane; k < n; k += 32) s[k] = g[k];
     }
 }
 __device__ __forceinline__ void lt_tile_store(float* g, const float* s, int n, int lane, bool vec) {
     if (vec) {
-        for (int k = lane * 4; k < n; k += 128) *reinterpret_cast<float4*>(g + k) = *reinterpret_cast<const float4*>(s + k);
+        LT_ROLLED for (int k = lane * 4; k < n; k += 128) *reinterpret_cast<float4*>(g + k) = *reinterpret_cast<const float4*>(s + k);
     } else {
-        for (int k = lane; k < n; k += 32) g[k] = s[k];
+        LT_ROLLED for (int k = lane; k < n; k += 32) g[k] = s[k];
     }
 }
-__device__ __forceinline__ void lt_prefetch(const void* g) { asm volatile("prefetch.global.L1 [%0];" ::"l"(g)); }
+#ifndef LT_OPT_PREFETCH
+#define LT_OPT_PREFETCH 1
+#endif
+__device__ __forceinline__ void lt_prefetch(const void* g) {
+#if LT_OPT_PREFETCH
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(g));
+#endif
+}
 __device__ __forceinline__ bool lt_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -179,14 +188,14 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS) lt_torque_kernel(const __gr
 // post_physics_step up to the observation row.  One warp owns EPW consecutive envs, one lane per env.
 //   phase 0  cp.async (16 B) stages the tile's root_states and dof_state rows in shared memory (both are written
 //            back: arrow pose every step, robot root / dofs on reset); each lane reads its env's [12]-rows straight
-//            into registers, reduces its env's contact forces to one packed word and prefetches the per-env words
-//            the scalar logic will touch
+//            into registers and prefetches the per-env words the scalar logic will touch; the contact-force tile is
+//            staged too and reduced to one packed word per env
 //   phase 1  the scalar step logic (lt_core.cuh); non-height observation columns go straight to obs_buf, the
 //            heightfield cell indices + post-reset z + camera z into a packed per-env record for lt_obs_kernel
 //   phase 2  flat coalesced write-back of the root / dof / record tiles
-// Shared memory per warp: root[EPW*A*13] dof[EPW*24] floats + rec[EPW*rec_bytes] bytes.
+// Shared memory per warp: root[EPW*A*13] dof[EPW*24] contact[EPW*B*3] floats + rec[EPW*rec_bytes] bytes.
 struct lt_smem_plan {
-    int root, dof, rec, total;       // float offsets
+    int root, dof, contact, rec, total;       // float offsets
 };
 __host__ __device__ inline int lt_align4(int x) { return (x + 3) & ~3; }
 __host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, int rec_bytes, int epw) {
@@ -194,6 +203,7 @@ __host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, int rec
     int o = 0;
     P.root = o; o += lt_align4(epw * c.num_actors * 13);
     P.dof = o; o += lt_align4(epw * LT_ND * 2);
+    P.contact = o; o += lt_align4(epw * c.num_bodies * 3);
     P.rec = o; o += lt_align4(epw * rec_bytes / 4);
     P.total = o;
     return P;
@@ -227,6 +237,7 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     float* ws = smem + (size_t)warp * P.total;
     float* s_root = ws + P.root;
     float* s_dof = ws + P.dof;
+    float* s_contact = ws + P.contact;
     uint8_t* s_rec = reinterpret_cast<uint8_t*>(ws + P.rec);
 
     const int tile = blockIdx.x * WARPS + warp;
@@ -240,6 +251,7 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     // ---- phase 0
     lt_tile_load(s_root, p.sim.root_states + (size_t)env0 * A13, nv * A13, lane, full);
     lt_tile_load(s_dof, p.sim.dof_state + (size_t)env0 * LT_ND * 2, nv * LT_ND * 2, lane, full);
+    lt_tile_load(s_contact, p.sim.contact_forces + (size_t)env0 * B3, nv * B3, lane, full);
     float r_act[LT_ND], r_last_act[LT_ND], r_last_dof_vel[LT_ND], r_torques[LT_ND];
     uint32_t cinfo = 0u;
     if (mine) {
@@ -259,12 +271,12 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         lt_prefetch(st.joint_pos_target + (size_t)i * LT_ND);
         lt_prefetch(st.last_joint_pos_target + (size_t)i * LT_ND);
         if (c.observe_heights && !c.plane) lt_prefetch(p.ter.env_terrain_origin + (size_t)i * 3);
-        for (int t = 0; t < L.n_sums; ++t) lt_prefetch(st.episode_sums + (size_t)t * N + i);
-        if (st.command_sums) for (int t = 0; t <= c.n_terms; ++t) lt_prefetch(st.command_sums + (size_t)t * N + i);
-        cinfo = lt_contact_summary(c, p.sim.contact_forces + (size_t)i * B3);
+        LT_ROLLED for (int t = 0; t < L.n_sums; ++t) lt_prefetch(st.episode_sums + (size_t)t * N + i);
+        if (st.command_sums) LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) lt_prefetch(st.command_sums + (size_t)t * N + i);
     }
     lt_cp_async_wait_all();
     __syncwarp();
+    if (mine) cinfo = lt_contact_summary(c, s_contact + lane * B3);
 
     // ---- phase 1: the scalar logic of the step
     int my_reset = 0;
@@ -318,80 +330,105 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
 // ---------------------------------------------------------------------------------------------------------------
 // Observation pass: one warp per env.  Reads the env's packed record + raw non-height columns, gathers the 2 x nxf x ny
 // heightfield samples from the (L2-resident) tile table, applies camera / clip / scale (LR:395-409), observation
-// noise (LR:473-474; NOISE 0 = off, 1 = injected uniforms, 2 = in-kernel Philox4x32-10, 8 columns per call), the
+// noise (LR:473-474; NOISE 0 = off, 1 = injected uniforms, 2 = in-kernel Philox4x32-10, ten 12-bit values per call), the
 // +-clip_observations clamp (LR:108-109) and writes obs_buf and the newest obs_history block (history_wrapper.py:22).
-// Lane <-> measured point pt = lane + 32 k (k < KP); one cell offset serves both layers.
-template <int KP, int NOISE>
+// Lane <-> measured point pt = lane + 32 k (k < KP); one cell offset serves both layers.  CAM = env.camera_zero.
+template <int NOISE>
+__device__ __forceinline__ float lt_obs_finish_dev(float v, float u, float scale, float clip) {
+    if (NOISE) v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), scale));
+    return fminf(fmaxf(v, -clip), clip);
+}
+template <int SLOT>
+__device__ __forceinline__ float lt_u12_static(const uint32_t (&rnd)[4]) {      // == lt_u12(rnd, SLOT)
+    constexpr int bit = 12 * SLOT, w = bit >> 5, sh = bit & 31;
+    uint32_t x = rnd[w] >> sh;
+    if (sh > 20) x |= rnd[w < 3 ? w + 1 : 3] << (32 - sh);
+    return LT_FMUL((float)(x & 0xfffu) + 0.5f, 1.0f / 4096.0f);
+}
+template <int KP, int NOISE, int CAM>
 __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_constant__ lt_obs_params p) {
     const int lane = threadIdx.x & 31;
     const int ie = blockIdx.x * (LT_OBS_THREADS / 32) + (threadIdx.x >> 5);
     if (ie >= p.num_envs) return;
     const int no = p.num_obs, H = p.obs_history_length, per_layer = p.per_layer;
+    const float clip = p.clip_observations, hscale = p.obs_scale_height, ceil_h = p.ceiling_height;
+    const uint32_t step = NOISE == 2 ? (uint32_t)p.counters[0] : 0u;
     const uint8_t* rec = p.scratch + (size_t)ie * p.rec_bytes;
     const float2 zc = *reinterpret_cast<const float2*>(rec + p.rec_bytes - 8);        // (z_post, cam_z)
     float hc[KP], hf[KP];
+    {
+        const float* tile_base = p.plane ? nullptr : p.tile_heights + (size_t)__ldg(p.env_tile + ie) * 2 * p.tile_cells;
 #pragma unroll
-    for (int k = 0; k < KP; ++k) {
-        const int pt = lane + 32 * k;
-        hc[k] = 1.0f;                             // plane: ceiling 1, floor 0 (LR:1928-1932)
-        hf[k] = 0.0f;
-        if (!p.plane && pt < per_layer) {
-            const uint32_t w = __ldg(p.ptlut + pt);
-            const int off = (int)rec[w & 0xffu] * p.tile_cols + (int)rec[p.nxf + (w >> 8)];
-            const float* tile_base = p.tile_heights + (size_t)__ldg(p.env_tile + ie) * 2 * p.tile_cells;
-            hc[k] = __ldg(tile_base + off);
-            hf[k] = __ldg(tile_base + p.tile_cells + off);
+        for (int k = 0; k < KP; ++k) {
+            const int pt = lane + 32 * k;
+            hc[k] = 1.0f;                         // plane: ceiling 1, floor 0 (LR:1928-1932)
+            hf[k] = 0.0f;
+            if (tile_base && pt < per_layer) {
+                const uint32_t w = __ldg(p.ptlut + pt);
+                const int off = (int)rec[w & 0xffu] * p.tile_cols + (int)rec[p.nxf + (w >> 8)];
+                hc[k] = __ldg(tile_base + off);
+                hf[k] = __ldg(tile_base + p.tile_cells + off);
+            }
         }
     }
-    float* obs_row = p.obs_buf + (size_t)ie * no;
+    uint32_t rnd[4] = {0u, 0u, 0u, 0u};
+    if (NOISE == 2) lt_philox((uint32_t)ie, (uint32_t)lane | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
     float* hist_row = p.obs_history + (size_t)ie * no * H;
     if (H > 1) {
         const int keep = (H - 1) * no;
         for (int k = lane; k < keep; k += 32) { const float v = hist_row[k + no]; hist_row[k] = v; }
     }
+    // per-lane base pointers: column h0 + lane (ceiling layer) and h0 + per_layer + lane (floor layer)
+    float* obs_row = p.obs_buf + (size_t)ie * no;
     float* hist_new = hist_row + (size_t)(H - 1) * no;
+    const int c0 = p.h0 + lane, c1 = c0 + per_layer;
     const float* nz = NOISE == 1 ? p.noise_uniforms + (size_t)ie * no : nullptr;
-    const float clip = p.clip_observations;
-    auto finish = [&](int col, float v, float u) {
-        if (NOISE) v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), __ldg(p.noise_scale_vec + col)));
-        v = fminf(fmaxf(v, -clip), clip);
-        obs_row[col] = v;
-        hist_new[col] = v;
-    };
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-        const int pt = lane + 32 * k;
-        uint32_t rnd[4] = {0u, 0u, 0u, 0u};
-        if (NOISE == 2 && (k & 3) == 0 && pt < per_layer)
-            lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (k >> 2)) | LT_STREAM_NOISE, p.counters[0], 0u, p.seed_lo, p.seed_hi, rnd);
-        if (pt < per_layer) {
+        if (lane + 32 * k < per_layer) {
 #pragma unroll
             for (int layer = 0; layer < 2; ++layer) {
-                const int col = p.h0 + layer * per_layer + pt;
+                constexpr int dummy = 0; (void)dummy;
+                const int col = (layer ? c1 : c0) + 32 * k;
                 float h = layer ? hf[k] : hc[k];
-                if (p.camera_zero) h = fminf(fmaxf(LT_FSUB(LT_FSUB(h, zc.x), zc.y), -0.3f), 0.3f);
-                else h = LT_FSUB(LT_FDIV(fminf(fmaxf(h, 0.0f), p.ceiling_height), p.ceiling_height), 0.5f);
-                h = LT_FMUL(h, p.obs_scale_height);
+                if (CAM) h = fminf(fmaxf(LT_FSUB(LT_FSUB(h, zc.x), zc.y), -0.3f), 0.3f);
+                else h = LT_FSUB(LT_FDIV(fminf(fmaxf(h, 0.0f), ceil_h), ceil_h), 0.5f);
+                h = LT_FMUL(h, hscale);
                 float u = 0.5f;
                 if (NOISE == 1) u = nz[col];
-                if (NOISE == 2) u = lt_u16(rnd[(k & 1) * 2 + layer] >> ((k & 2) ? 16 : 0));
-                finish(col, h, u);
+                if (NOISE == 2) {
+                    const int v = 2 * k + layer;                 // compile-time after unrolling
+                    if (v == LT_NOISE_PER_CALL)                  // KP = 8 only: values 10.. come from the second call
+                        lt_philox((uint32_t)ie, (uint32_t)(lane + 32) | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
+                    switch (v % LT_NOISE_PER_CALL) {
+                    case 0: u = lt_u12_static<0>(rnd); break; case 1: u = lt_u12_static<1>(rnd); break;
+                    case 2: u = lt_u12_static<2>(rnd); break; case 3: u = lt_u12_static<3>(rnd); break;
+                    case 4: u = lt_u12_static<4>(rnd); break; case 5: u = lt_u12_static<5>(rnd); break;
+                    case 6: u = lt_u12_static<6>(rnd); break; case 7: u = lt_u12_static<7>(rnd); break;
+                    case 8: u = lt_u12_static<8>(rnd); break; default: u = lt_u12_static<9>(rnd); break;
+                    }
+                }
+                const float o = lt_obs_finish_dev<NOISE>(h, u, NOISE ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
+                obs_row[col] = o;
+                hist_new[col] = o;
             }
         }
     }
     const int head_iters = (p.head_w + 31) >> 5;
-    uint32_t rnd[4] = {0u, 0u, 0u, 0u};
+#pragma unroll 1
     for (int m = 0; m < head_iters; ++m) {
         const int hi = lane + 32 * m;
-        if (NOISE == 2 && (m & 7) == 0)
-            lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (64 + (m >> 3))) | LT_STREAM_NOISE, p.counters[0], 0u, p.seed_lo, p.seed_hi, rnd);
+        const int v = 2 * KP + m;
+        if (NOISE == 2 && v % LT_NOISE_PER_CALL == 0)
+            lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (v / LT_NOISE_PER_CALL)) | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
         if (hi < p.head_w) {
             const int col = hi < p.h0 ? hi : hi + p.n_heights;
-            const int s = m & 7;
             float u = 0.5f;
             if (NOISE == 1) u = nz[col];
-            if (NOISE == 2) u = lt_u16(((s & 2) ? ((s & 4) ? rnd[3] : rnd[1]) : ((s & 4) ? rnd[2] : rnd[0])) >> ((s & 1) ? 16 : 0));
-            finish(col, obs_row[col], u);
+            if (NOISE == 2) u = lt_u12(rnd, v % LT_NOISE_PER_CALL);
+            const float o = lt_obs_finish_dev<NOISE>(obs_row[col], u, NOISE ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
+            obs_row[col] = o;
+            hist_new[col] = o;
         }
     }
 }
@@ -506,13 +543,17 @@ static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) 
     lt_step_kernel<EPW><<<(tiles + WARPS - 1) / WARPS, LT_STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
 }
+template <int KP, int CAM>
+static cudaError_t lt_launch_obs_cam(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
+    const unsigned grid = (unsigned)((p.num_envs + LT_OBS_THREADS / 32 - 1) / (LT_OBS_THREADS / 32));
+    if (noise_mode == 0) lt_obs_kernel<KP, 0, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else if (noise_mode == 1) lt_obs_kernel<KP, 1, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else lt_obs_kernel<KP, 2, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    return cudaGetLastError();
+}
 template <int KP>
 static cudaError_t lt_launch_obs(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
-    const unsigned grid = (unsigned)((p.num_envs + LT_OBS_THREADS / 32 - 1) / (LT_OBS_THREADS / 32));
-    if (noise_mode == 0) lt_obs_kernel<KP, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else if (noise_mode == 1) lt_obs_kernel<KP, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else lt_obs_kernel<KP, 2><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    return cudaGetLastError();
+    return p.camera_zero ? lt_launch_obs_cam<KP, 1>(p, noise_mode, stream) : lt_launch_obs_cam<KP, 0>(p, noise_mode, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

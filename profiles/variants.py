@@ -1,0 +1,74 @@
+"""Tuning harness: build liblt_b200 variants (-D switches) here, time them on the GPU box.
+
+  python profiles/variants.py build            # in the build container: writes build/variants/<name>.so
+  python profiles/variants.py run [N ...]      # on the GPU box (gpurun): post-physics + torque time per variant
+"""
+import json
+import os
+import subprocess
+import sys
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+VDIR = os.path.join(REPO, "build", "variants")
+VARIANTS = {
+    "base": [],
+    "sums_direct": ["LT_OPT_SUMS_LOCAL=0"],
+    "no_prefetch": ["LT_OPT_PREFETCH=0"],
+    "unrolled": ["LT_OPT_UNROLL1=0"],
+    "cta128": ["LT_STEP_THREADS=128"],
+    "cta32": ["LT_STEP_THREADS=32"],
+}
+
+
+def build():
+    from legged_tracking_b200 import build as b
+    os.makedirs(VDIR, exist_ok=True)
+    for name, defs in VARIANTS.items():
+        b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"))
+        print("built", name)
+
+
+def run_one(n_envs):
+    import torch
+    from legged_tracking_b200 import workload
+    from legged_tracking_b200.engine import StepEngine
+    import bench
+    flat, terrain, act, synth = workload.make("cfg5", num_envs=n_envs)
+    eng = StepEngine(flat, terrain, act, device="cuda:0", seed=3)
+    bench.init_engine_state(eng, synth, flat)
+    rs = bench.ReplaySets(eng, synth, flat, 3)
+
+    def post(k):
+        s = rs.sets[k % 3]
+        eng.bind_sim(root_states=s["root"], contact_forces=s["contact"], dof_state=s["dof"][-1])
+        eng.post_physics_step(advance_gravity=False)
+
+    def torque(k):
+        s = rs.sets[k % 3]
+        eng.bind_sim(dof_state=s["dof"][k % 4])
+        eng.compute_torques(s["actions"], k % 4)
+    for k in range(10):
+        torque(k)
+        post(k)
+    return {"n": n_envs, "post_us": bench.time_region(post, 200) / 200 * 1e3, "torque_us": bench.time_region(torque, 200) / 200 * 1e3}
+
+
+def run(ns):
+    for name in VARIANTS:
+        lib = os.path.join(VDIR, name + ".so")
+        if not os.path.exists(lib):
+            continue
+        for n in ns:
+            env = dict(os.environ, LT_B200_LIB=lib)
+            r = subprocess.run([sys.executable, __file__, "one", str(n)], env=env, capture_output=True, text=True)
+            print(name, r.stdout.strip().splitlines()[-1] if r.returncode == 0 else r.stderr[-400:], flush=True)
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "build":
+        build()
+    elif sys.argv[1] == "one":
+        print(json.dumps(run_one(int(sys.argv[2]))))
+    else:
+        run([int(a) for a in sys.argv[2:]] or [65536, 8192])
