@@ -7,8 +7,8 @@
 // ---------------------------------------------------------------------------------------------------------------
 // RolloutStorage.add_transitions (rollout_storage.py:57-71): every field of one transition copied into row t of
 // its [T, N, w] buffer by ONE launch (the reference issues 11 copy_ kernels).  Work is laid out as a flat list of
-// float4 chunks over the concatenated fields so every access is a coalesced 16-byte load/store.
-struct lt_copy_seg { const float* src; float* dst; long long n4; long long tail0, tail; };   // n4 float4 chunks, then scalar tail
+// chunks over the concatenated fields: 16-byte float4 copies for aligned segments, scalar otherwise.
+struct lt_copy_seg { const float* src; float* dst; long long n4; int vec; };   // n4 chunks: float4 when vec (16 B aligned), else float
 struct lt_store_params {
     lt_copy_seg seg[9];
     int n_seg;
@@ -29,7 +29,8 @@ __global__ void __launch_bounds__(256) lt_rollout_store_kernel(const __grid_cons
         long long r = k;
         int s = 0;
         while (r >= p.seg[s].n4) { r -= p.seg[s].n4; ++s; }
-        reinterpret_cast<float4*>(p.seg[s].dst)[r] = reinterpret_cast<const float4*>(p.seg[s].src)[r];
+        if (p.seg[s].vec) reinterpret_cast<float4*>(p.seg[s].dst)[r] = reinterpret_cast<const float4*>(p.seg[s].src)[r];
+        else p.seg[s].dst[r] = p.seg[s].src[r];
     }
     if (tid < p.n) {
         if (p.rewards_dst) {
@@ -39,9 +40,6 @@ __global__ void __launch_bounds__(256) lt_rollout_store_kernel(const __grid_cons
         }
         if (p.dones_dst) p.dones_dst[tid] = p.dones[tid];
     }
-    if (tid == 0)
-        for (int s = 0; s < p.n_seg; ++s)
-            for (long long j = p.seg[s].tail0; j < p.seg[s].tail0 + p.seg[s].tail; ++j) p.seg[s].dst[j] = p.seg[s].src[j];
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -116,10 +114,8 @@ int lt_rollout_store(const lt_rollout_ptrs* st, const lt_transition_ptrs* tr, in
         lt_copy_seg& s = p.seg[p.n_seg++];
         s.src = src;
         s.dst = d;
-        const bool al = (((uintptr_t)src | (uintptr_t)d) & 15u) == 0;
-        s.n4 = al ? cnt / 4 : 0;
-        s.tail0 = s.n4 * 4;
-        s.tail = cnt - s.tail0;
+        s.vec = ((((uintptr_t)src | (uintptr_t)d) & 15u) == 0 && cnt % 4 == 0) ? 1 : 0;
+        s.n4 = s.vec ? cnt / 4 : cnt;
         p.total4 += s.n4;
     };
     add(tr->observations, st->observations, num_obs);
