@@ -115,7 +115,8 @@ def test_gae_full_size_properties():
     assert abs(float(adv.double().mean())) < 1e-6
     assert abs(float(adv.double().std()) - 1.0) < 1e-5
     done = D.bool()
-    assert torch.equal(ret[done], R[done])          # terminal step: return == reward (no bootstrap, no carry)
+    # terminal step: return == (reward - value) + value (no bootstrap, no carry from later steps)
+    assert torch.equal(ret[done], (R[done] - V[done]) + V[done])
 
 
 @pytest.mark.parametrize("N,no,npv,H,na", [(64, 42, 6, 5, 12), (33, 7, 3, 3, 5), (1, 1, 1, 1, 1)])
