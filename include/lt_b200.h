@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LT_ABI_VERSION 3
+#define LT_ABI_VERSION 4
 
 #define LT_MAX_DOF 12
 #define LT_MAX_FEET 4
@@ -175,7 +175,7 @@ typedef struct lt_state_ptrs {
 
 /* Per-step inputs of lt_post_physics_step. */
 typedef struct lt_step_args {
-    const float* extra_reward;       /* [N] or NULL: value of the LT_TERM_EXTERNAL plugin term (unscaled) */
+    const float* extra_reward;       /* [n_external, N] or NULL: unscaled values of the LT_TERM_EXTERNAL plugin terms, row k = k-th such term slot */
     const float* uniforms;           /* [N, lt_num_uniform_slots] in [0,1) or NULL -> in-kernel Philox4x32-10 */
     const float* noise_uniforms;     /* [N, num_obs] or NULL -> in-kernel Philox (only read if add_noise) */
     const float* new_gravity;        /* HOST float[3] or NULL: _randomize_gravity fired this step (LR:645-660): written
@@ -214,7 +214,8 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
  * check_termination (LR:198-216), compute_reward (LR:320-355), reset_idx (LR:218-296, 998-1052),
  * compute_observations (LR:357-590), the history shifts (LR:148-153), the +-clip_observations clamp of
  * LeggedRobot.step (LR:108-111) and HistoryWrapper.step's obs_history shift (history_wrapper.py:18-24).
- * Two launches: the fused step kernel and the ordered reset-id compaction (reset_buf.nonzero(), LR:143). */
+ * Three launches (+ the sign pre-pass when a term needs it): lt_step_kernel (per-env scalar logic), lt_obs_kernel
+ * (heightfield gathers, noise, observation rows) and the ordered reset-id compaction (reset_buf.nonzero(), LR:143). */
 int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream);
 
 /* Only when a term has LT_BUCKET_BY_SUM: evaluates those terms without side effects and leaves their all-env
@@ -222,6 +223,12 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream);
  * that array before lt_post_physics_step.  lt_post_physics_step runs it itself when the host did not. */
 int lt_reward_sign_prepass(lt_handle* h, const lt_step_args* args, void* stream);
 float* lt_term_sum_buffer(lt_handle* h);
+
+/* LeggedRobot.update_curriculum (LR:171-183) decays the exploration_lin / exploration_yaw scales on the host once
+ * common_step_counter exceeds rewards.exploration_steps: `scales` (HOST float[n_terms], same order as
+ * lt_config.term_scales, already multiplied by dt) replaces the term scales from the next launch on.  A CUDA graph
+ * captured earlier keeps the scales it was captured with. */
+int lt_set_term_scales(lt_handle* h, const float* scales, int32_t n);
 
 /* Device int32[4]: {policy steps done, physics sub-steps done (= pushes into the lag FIFO), lag ring head, 0}.
  * Logical lag slot j of LR:972-974 lives in physical slot (head + j) % (lag_timesteps + 1). */

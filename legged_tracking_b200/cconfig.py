@@ -14,7 +14,7 @@ from . import _abi, flatcfg, rng_slots
 
 def _bucket(name, scale, flat):
     """Which of rew_buf_pos / rew_buf_neg a term lands in (LR:332-335 tests the sign of the all-env sum)."""
-    indefinite = name in flatcfg.SIGN_INDEFINITE_TERMS or (
+    indefinite = name in flatcfg.SIGN_INDEFINITE_TERMS or name in flat.get("external_reward_names", ()) or (
         name == "exploration_lin" and flat["lin_vel_form"] == "prod")       # a normalised dot product (reward_crawling.py:95-101)
     if indefinite:
         return _abi.ENUMS["LT_BUCKET_BY_SUM"]
@@ -84,7 +84,7 @@ def make_lt_config(flat, seed=0, envs_per_warp=0):
     c.n_terms = len(names)
     for i, n in enumerate(names):
         scale = float(f["reward_scales"][n])
-        c.term_ids[i] = flatcfg.REWARD_TERM_IDS[n]
+        c.term_ids[i] = flatcfg.REWARD_TERM_IDS["external" if n in f.get("external_reward_names", ()) else n]
         c.term_scales[i] = scale
         c.term_bucket[i] = _bucket(n, scale, f)
     for i, n in enumerate(PRIV_ORDER):

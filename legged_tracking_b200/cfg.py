@@ -295,4 +295,6 @@ def flat_from_cfg(cfg, model=Go1Model, sim_dt=None, num_envs=None, extra_reward_
         push_robots=bool(c.domain_rand.push_robots), randomize_rigids_after_start=bool(c.domain_rand.randomize_rigids_after_start),
         send_timeouts=bool(c.env.send_timeouts),
     )
+    if extra_reward_names:
+        flat["external_reward_names"] = [n for n in names if n in extra_reward_names]
     return flat

@@ -414,6 +414,14 @@ struct lt_reward_ctx {
     int reached, n_collisions;
 };
 
+// Row of lt_step_args.extra_reward ([n_external, N]) that belongs to term slot t: the k-th LT_TERM_EXTERNAL slot reads row k.
+LT_HD const float* lt_ext_row(const lt_config& c, const float* ext, int t) {
+    if (!ext || c.term_ids[t] != LT_TERM_EXTERNAL) return ext;
+    int k = 0;
+    for (int q = 0; q < t; ++q) k += (c.term_ids[q] == LT_TERM_EXTERNAL) ? 1 : 0;
+    return ext + (size_t)k * (size_t)c.num_envs;
+}
+
 // value of reward term `id` (unscaled).  `dry`: evaluate without touching state (sign pre-pass).
 LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, int id, const lt_reward_ctx& r,
                            const float* extra_reward, bool dry) {
@@ -772,7 +780,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     rc.ep_f = ep_f; rc.reached = reached; rc.n_collisions = n_coll;
     float rew = 0.0f, rew_pos = 0.0f, rew_neg = 0.0f;
     for (int t = 0; t < c.n_terms; ++t) {
-        const float v = lt_reward_term(c, st, i, c.term_ids[t], rc, args.extra_reward, false);
+        const float v = lt_reward_term(c, st, i, c.term_ids[t], rc, lt_ext_row(c, args.extra_reward, t), false);
         const float r = LT_FMUL(v, c.term_scales[t]);
         rew = LT_FADD(rew, r);
         int bucket = c.term_bucket[t];

@@ -511,7 +511,7 @@ __global__ void __launch_bounds__(256) lt_sign_kernel(const __grid_constant__ lt
             rc.ep_f = (float)(p.st.episode_length_buf[i] + 1);
             rc.reached = 0;
             rc.n_collisions = 0;
-            v = lt_reward_term(c, p.st, i, c.term_ids[t], rc, p.args.extra_reward, true) * c.term_scales[t];
+            v = lt_reward_term(c, p.st, i, c.term_ids[t], rc, lt_ext_row(c, p.args.extra_reward, t), true) * c.term_scales[t];
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -732,6 +732,13 @@ int lt_bind_state(lt_handle* h, const lt_state_ptrs* s) {
 
 int32_t* lt_counters(lt_handle* h) { return h ? h->d_counters : nullptr; }
 float* lt_term_sum_buffer(lt_handle* h) { return h ? h->d_term_sums : nullptr; }
+
+int lt_set_term_scales(lt_handle* h, const float* scales, int32_t n) {
+    if (!h) return LT_ERR_INVALID;
+    if (!scales || n != h->c.n_terms) return lt_fail(h, LT_ERR_INVALID, "lt_set_term_scales: expected " + std::to_string(h->c.n_terms) + " scales");
+    for (int t = 0; t < n; ++t) h->c.term_scales[t] = scales[t];      // the config travels as a kernel parameter: effective from the next launch
+    return LT_OK;
+}
 
 static int lt_ready(lt_handle* h) {
     if (!h) return LT_ERR_INVALID;

@@ -57,6 +57,35 @@ class GravitySchedule:
         return new
 
 
+class ExplorationCurriculum:
+    """Host side of LeggedRobot.update_curriculum (LR:171-183): once the global step counter exceeds
+    rewards.exploration_steps the exploration_lin / exploration_yaw scales decay linearly to zero, in Python double
+    arithmetic exactly as the reference mutates its reward_scales dict; the kernels pick the new scales up from the
+    next step (the update runs after compute_observations, LR:146)."""
+
+    KEYS = ("exploration_lin", "exploration_yaw")
+
+    def __init__(self, flat):
+        self.scales = {k: float(v) for k, v in flat["reward_scales"].items()}
+        self.cfg_scales = flat["reward_scales_cfg"]
+        self.dt = float(flat["dt"])
+        self.steps = float(flat["exploration_steps"])
+        self.names = list(flat["reward_names"])
+
+    def advance(self, common_step_counter):
+        """-> True if a scale changed."""
+        changed = False
+        for key in self.KEYS:
+            if key in self.scales and common_step_counter > self.steps:
+                self.scales[key] -= self.cfg_scales[key] * self.dt / self.steps
+                self.scales[key] = max(self.scales[key], 0)
+                changed = True
+        return changed
+
+    def term_scales(self):
+        return [self.scales[n] for n in self.names]
+
+
 class StepEngine:
     def __init__(self, flat, terrain, actuator, device="cuda:0", seed=0, envs_per_warp=0, track_command_sums=True,
                  export_height_indices=False):
@@ -121,7 +150,9 @@ class StepEngine:
         self._ptrs = ptrs
         self.counters = self._wrap_i32(self.lib.lt_counters(self.handle), 4)
         self.gravity = GravitySchedule(flat)
+        self.curriculum = ExplorationCurriculum(flat)
         self.reward_names = list(flat["reward_names"])
+        self.n_external = sum(1 for n in self.reward_names if n == "external" or n in flat.get("external_reward_names", ()))
         self.sum_names = self.reward_names + ["total", "total_pos", "total_neg"]
         self._keepalive = []
 
@@ -197,8 +228,10 @@ class StepEngine:
         args = _abi.lt_step_args()
         for name, tns, shape in (("uniforms", uniforms, (self.N, self.n_slots)),
                                  ("noise_uniforms", noise_uniforms, (self.N, self.flat["num_obs"])),
-                                 ("extra_reward", extra_reward, (self.N,))):
+                                 ("extra_reward", extra_reward, (self.n_external, self.N))):
             if tns is not None:
+                if name == "extra_reward" and tns.dim() == 1:
+                    tns = tns.view(1, -1)
                 assert tns.is_cuda and tns.dtype == torch.float32 and tns.is_contiguous() and tuple(tns.shape) == shape, name
                 setattr(args, name, tns.data_ptr())
         new_g = None
@@ -213,6 +246,13 @@ class StepEngine:
         if new_g is not None:
             # gravity_vec changes AFTER this step's projected_gravity was computed (LR:134 precedes LR:826-830)
             self.state["gravity_vec"].copy_(GravitySchedule.gravity_vec_of(new_g), non_blocking=False)
+        if advance_gravity and self.curriculum.advance(self.gravity.common_step_counter):
+            self.set_reward_scales(self.curriculum.term_scales())
+
+    def set_reward_scales(self, scales):
+        """New per-term scales (already multiplied by dt, order of reward_names) for the following steps (LR:171-183)."""
+        arr = (C.c_float * len(scales))(*[float(v) for v in scales])
+        _abi.check(self.lib.lt_set_term_scales(self.handle, arr, len(scales)), self.handle, "lt_set_term_scales")
 
     def reset_env_ids(self):
         """env_ids = reset_buf.nonzero().flatten() (LR:143); synchronises to read the count."""

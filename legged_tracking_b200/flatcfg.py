@@ -149,7 +149,7 @@ def check_supported(flat):
     if flat["traj_function"] not in ("fixed_target", "random_goal", "random_target"):
         problems.append(f"commands.traj_function={flat['traj_function']!r}")
     for name in flat["reward_names"]:
-        if name not in REWARD_TERM_IDS:
+        if name not in REWARD_TERM_IDS and name not in flat.get("external_reward_names", ()):
             problems.append(f"reward term {name!r} has no fused implementation")
     if obs_width(flat) != flat["num_obs"]:
         problems.append(f"observation layout is {obs_width(flat)} wide but num_obs={flat['num_obs']} (LR:475)")

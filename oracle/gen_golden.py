@@ -315,6 +315,9 @@ FIXTURES = {
     # BASELINE config 3 shape (vel strategy, terminal body height 0.25 -> many resets)
     "cfg3_vel_64": dict(argv=COMMON + ["--camera_zero", "--strategy", "vel", "--terrain", "single_path",
                                        "--terminal_body_height", "0.25"], num_envs=64, num_rows=4, num_cols=4, steps=8),
+    # update_curriculum (LR:171-183): exploration scales start decaying after 3 global steps
+    "cfg2_curriculum_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path",
+                                              "--exploration_steps", "3"], num_envs=32, num_rows=4, num_cols=4, steps=7),
     # option coverage: random_target trajectories, timestep in obs, positive-only reward, 3-step history,
     # prod-form exploration reward, terminate at end of trajectory, full (non front-half) grid
     "opts_random_target_32": dict(argv=["--old_ppo", "--camera_zero", "--strategy", "e2e", "--terrain", "single_path",

@@ -336,6 +336,7 @@ class OraclePort:
         self.reset_env_ids = env_ids
         self.reset_idx(env_ids, uniforms)
         self.compute_observations(noise_uniforms)
+        self.update_curriculum()
         self.last_last_actions[:] = self.last_actions[:]
         self.last_actions[:] = self.actions[:]
         self.last_last_joint_pos_target[:] = self.last_joint_pos_target[:]
@@ -412,6 +413,15 @@ class OraclePort:
             self.gravities[:, :] = ext.unsqueeze(0)
         gravity = self.gravities[0, :] + torch.Tensor([0, 0, -9.8])
         self.gravity_vec[:, :] = gravity.unsqueeze(0) / torch.norm(gravity)
+
+    def update_curriculum(self):
+        """LR:171-183 (the cl_fix_target branch, LR:186-196, only rewrites logging deques and commands.x_mean)."""
+        f = self.flat
+        for key in ("exploration_lin", "exploration_yaw"):
+            if key in self.reward_scales:
+                if self.common_step_counter > f["exploration_steps"]:
+                    self.reward_scales[key] -= f["reward_scales_cfg"][key] * f["dt"] / f["exploration_steps"]
+                    self.reward_scales[key] = max(self.reward_scales[key], 0)
 
     def post_physics_step_callback(self, uniforms, gravity_uniform):
         """LR:774-848"""

@@ -93,7 +93,7 @@ int lths_post_physics(const lt_config* cfg, const lt_tables* tb, const lt_state_
             for (int k = 0; k < 3; ++k) { rc.blv[k] = P.blv[k]; rc.bav[k] = P.bav[k]; rc.pg[k] = P.pg[k];
                                           rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = P.rel_lin[k]; }
             rc.ep_f = (float)(st.episode_length_buf[i] + 1); rc.reached = 0; rc.n_collisions = 0;
-            acc += lt_reward_term(c, st, i, c.term_ids[t], rc, args.extra_reward, true) * c.term_scales[t];
+            acc += lt_reward_term(c, st, i, c.term_ids[t], rc, lt_ext_row(c, args.extra_reward, t), true) * c.term_scales[t];
         }
         term_sums[t] = (float)acc;
     }

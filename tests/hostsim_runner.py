@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from legged_tracking_b200 import _abi, cconfig
-from legged_tracking_b200.engine import GravitySchedule
+from legged_tracking_b200.engine import GravitySchedule, ExplorationCurriculum
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "hostsim", "hostsim.cpp")
@@ -64,6 +64,7 @@ class HostSim:
         self.state["gravity_vec"][:] = [0.0, 0.0, -1.0]
         self.counters = np.zeros(4, np.int32)
         self.gravity = GravitySchedule(flat)
+        self.curriculum = ExplorationCurriculum(flat)
         self.reward_names = list(flat["reward_names"])
         self.sum_names = self.reward_names + ["total", "total_pos", "total_neg"]
         self.n_slots = cconfig.rng_n_slots(flat)
@@ -98,6 +99,9 @@ class HostSim:
         self.pending = 0
         if new_g is not None:
             self.state["gravity_vec"][:] = GravitySchedule.gravity_vec_of(new_g).numpy()
+        if self.curriculum.advance(self.gravity.common_step_counter):
+            for t, v in enumerate(self.curriculum.term_scales()):
+                self.cfg.term_scales[t] = float(v)
 
     def reset_env_ids(self):
         return self.state["reset_env_ids"][: int(self.state["reset_count"][0])]
