@@ -218,6 +218,14 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
  * (heightfield gathers, noise, observation rows) and the ordered reset-id compaction (reset_buf.nonzero(), LR:143). */
 int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream);
 
+/* LeggedRobot.reset_idx(env_ids) (LR:218-296) called from OUTSIDE a step, e.g. by reset() (trajectory_tracking/__init__.py:46-56):
+ * re-spawns the listed envs exactly as the step kernel does for envs whose reset_buf fired -- DR resample, dof / root state
+ * written into the bound simulator tensors, new trajectory, histories / lag ring / episode sums zeroed, finished-episode
+ * record filled.  env_ids: DEVICE int64[count]; count_dev: optional DEVICE int32 holding the live count (<= count) so that
+ * a compacted id list can be used without a host read; uniforms: [N, lt_num_uniform_slots] or NULL (Philox). */
+int lt_reset_idx(lt_handle* h, const int64_t* env_ids, int32_t count, const int32_t* count_dev, const float* uniforms,
+                 void* stream);
+
 /* Only when a term has LT_BUCKET_BY_SUM: evaluates those terms without side effects and leaves their all-env
  * sums in the device array returned by lt_term_sum_buffer (float[LT_MAX_TERMS]); a multi-GPU host all-reduces
  * that array before lt_post_physics_step.  lt_post_physics_step runs it itself when the host did not. */

@@ -93,7 +93,7 @@ lt_rollout_ptrs = _mk("lt_rollout_ptrs")
 lt_transition_ptrs = _mk("lt_transition_ptrs")
 
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
-           "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step",
+           "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
            "lt_reward_sign_prepass", "lt_term_sum_buffer", "lt_set_term_scales", "lt_counters", "lt_rollout_store", "lt_gae",
            "lt_normalize_advantages"]
 
@@ -138,6 +138,7 @@ def load(path=LIB_PATH):
     lib.lt_reward_sign_prepass.argtypes = [vp, C.POINTER(lt_step_args), vp]
     lib.lt_term_sum_buffer.argtypes = [vp]
     lib.lt_term_sum_buffer.restype = vp
+    lib.lt_reset_idx.argtypes = [vp, vp, i32, vp, vp, vp]
     lib.lt_set_term_scales.argtypes = [vp, C.POINTER(C.c_float), i32]
     lib.lt_counters.argtypes = [vp]
     lib.lt_counters.restype = vp

@@ -528,6 +528,57 @@ __global__ void __launch_bounds__(256) lt_sign_kernel(const __grid_constant__ lt
 
 // ---------------------------------------------------------------------------------------------------------------
 // launch helper (C++ linkage)
+
+// ---------------------------------------------------------------------------------------------------------------
+// LeggedRobot.reset_idx(env_ids) called from OUTSIDE a step (env.reset(), LR:218-296): the same per-env reset the step
+// kernel performs in line, for an explicit id list.  Rare path: thread per listed env, straight to global memory.
+__global__ void __launch_bounds__(128) lt_reset_idx_kernel(const __grid_constant__ lt_step_params p, const int64_t* __restrict__ ids,
+                                                           int count, const int32_t* __restrict__ count_dev) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_ids = count_dev ? *count_dev : count;
+    if (k >= n_ids) return;
+    const lt_config& c = p.c;
+    const lt_state_ptrs& st = p.st;
+    const int i = (int)ids[k];
+    if (i < 0 || i >= c.num_envs) return;
+    const size_t N = (size_t)c.num_envs;
+    constexpr int nd = LT_ND;
+    lt_uniform_src U;
+    U.row = p.args.uniforms ? p.args.uniforms + (size_t)i * p.L.n_slots : nullptr;
+    U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.step = (uint32_t)p.counters[0] | 0x80000000u; U.env = (uint32_t)i;
+    float* root = p.sim.root_states + (size_t)i * c.num_actors * 13;
+    float* dof = p.sim.dof_state + (size_t)i * nd * 2;
+    // finished-episode record (LR:256-273) before anything is zeroed
+    st.finished_episode_length[i] = (float)st.episode_length_buf[i];
+    const float* rl = st.relative_linear + (size_t)i * 3;
+    st.finished_goal_distance[i] = lt_norm3(rl[0], rl[1], rl[2]);
+    for (int s = 0; s < p.L.n_sums; ++s) {
+        st.finished_sums[(size_t)s * N + i] = st.episode_sums[(size_t)s * N + i];
+        st.episode_sums[(size_t)s * N + i] = 0.0f;
+    }
+    const bool reached = st.reached_buf[i] != 0;
+    st.reached_env_buf[i] = reached ? 1 : 0;
+    st.collision_env_buf[i] = reached ? st.collision_count[i] : 0;
+    st.collision_count[i] = 0;
+    lt_reset_sim_state(c, st, p.ter, U, i, root, dof);
+    st.curr_pose_index[i] = 0;
+    for (int d = 0; d < nd; ++d) {
+        st.last_actions[(size_t)i * nd + d] = 0.0f;
+        st.last_last_actions[(size_t)i * nd + d] = 0.0f;
+        st.last_dof_vel[(size_t)i * nd + d] = 0.0f;
+    }
+    for (int f = 0; f < c.n_feet; ++f) st.feet_air_time[(size_t)i * c.n_feet + f] = 0.0f;
+    st.episode_length_buf[i] = 0;
+    st.reset_buf[i] = 1;
+    st.plan_buf[i] = 1;
+    for (int q = 0; q < 3; ++q) {
+        st.local_relative_linear[(size_t)i * 3 + q] = 0.0f;
+        st.local_relative_rotation[(size_t)i * 3 + q] = 0.0f;
+    }
+    for (int s = 0; s < p.L.lag_slots; ++s)
+        for (int d = 0; d < nd; ++d) st.lag_buffer[((size_t)s * N + i) * nd + d] = 0.0f;
+}
+
 template <int EPW>
 static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) {
     constexpr int WARPS = LT_STEP_THREADS / 32;
@@ -731,6 +782,21 @@ int lt_bind_state(lt_handle* h, const lt_state_ptrs* s) {
 }
 
 int32_t* lt_counters(lt_handle* h) { return h ? h->d_counters : nullptr; }
+int lt_reset_idx(lt_handle* h, const int64_t* env_ids, int32_t count, const int32_t* count_dev, const float* uniforms, void* stream) {
+    if (!h) return LT_ERR_INVALID;
+    if (!h->have_sim || !h->have_terrain || !h->have_state) return lt_fail(h, LT_ERR_UNBOUND, "lt_reset_idx: bind sim, terrain and state first");
+    if (!env_ids || count < 0) return lt_fail(h, LT_ERR_INVALID, "lt_reset_idx: bad id list");
+    if (count == 0) return LT_OK;
+    lt_step_params p;
+    memset(&p, 0, sizeof p);
+    p.c = h->c; p.L = h->L; p.st = h->st; p.sim = h->sim; p.ter = h->ter;
+    p.args.uniforms = uniforms;
+    p.counters = h->d_counters;
+    lt_reset_idx_kernel<<<(count + 127) / 128, 128, 0, (cudaStream_t)stream>>>(p, env_ids, count, count_dev);
+    LT_CUDA(h, cudaGetLastError());
+    return LT_OK;
+}
+
 float* lt_term_sum_buffer(lt_handle* h) { return h ? h->d_term_sums : nullptr; }
 
 int lt_set_term_scales(lt_handle* h, const float* scales, int32_t n) {

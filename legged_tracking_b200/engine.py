@@ -254,6 +254,19 @@ class StepEngine:
         arr = (C.c_float * len(scales))(*[float(v) for v in scales])
         _abi.check(self.lib.lt_set_term_scales(self.handle, arr, len(scales)), self.handle, "lt_set_term_scales")
 
+    def reset_idx(self, env_ids, uniforms=None, stream=None):
+        """LeggedRobot.reset_idx (LR:218-296) for an explicit id list, outside a step."""
+        env_ids = torch.as_tensor(env_ids, dtype=torch.int64, device=self.device).contiguous()
+        if env_ids.numel() == 0:
+            return
+        u = None
+        if uniforms is not None:
+            assert uniforms.is_cuda and uniforms.dtype == torch.float32 and tuple(uniforms.shape) == (self.N, self.n_slots)
+            u = C.c_void_p(uniforms.data_ptr())
+        _abi.check(self.lib.lt_reset_idx(self.handle, C.c_void_p(env_ids.data_ptr()), int(env_ids.numel()), None, u,
+                                         self._stream_ptr(stream)), self.handle, "lt_reset_idx")
+        self._keepalive = [env_ids, uniforms]
+
     def reset_env_ids(self):
         """env_ids = reset_buf.nonzero().flatten() (LR:143); synchronises to read the count."""
         n = int(self.state["reset_count"].item())

@@ -248,26 +248,45 @@ class RolloutStorage:
             raise ValueError(f"transition mask has {t.numel()} elements, expected {n}")
         return t.contiguous()
 
-    def add_transitions(self, transition):
-        if self.step >= self.num_transitions_per_env:
-            raise AssertionError("Rollout buffer overflow")
+    def _launch_store(self, transition, fields):
         n = self.num_envs
         no, npv, nh, na = (int(s[0]) for s in (self.obs_shape, self.privileged_obs_shape, self.obs_history_shape, self.actions_shape))
+        widths = dict(observations=no, privileged_observations=npv, observation_histories=nh, actions=na, rewards=1, values=1,
+                      actions_log_prob=1, action_mean=na, action_sigma=na)
         tr = _abi.lt_transition_ptrs()
-        keep = dict(observations=self._f32(transition.observations, n, no),
-                    privileged_observations=self._f32(transition.privileged_observations, n, npv),
-                    observation_histories=self._f32(transition.observation_histories, n, nh),
-                    actions=self._f32(transition.actions, n, na), rewards=self._f32(transition.rewards, n, 1),
-                    values=self._f32(transition.values, n, 1), actions_log_prob=self._f32(transition.actions_log_prob, n, 1),
-                    action_mean=self._f32(transition.action_mean, n, na), action_sigma=self._f32(transition.action_sigma, n, na),
-                    dones=self._u8(transition.dones, n), time_outs=self._u8(getattr(transition, "time_outs", None), n))
-        for k, v in keep.items():
+        keep = {}
+        for k in fields:
+            src = getattr(transition, k, None)
+            v = self._u8(src, n) if k in ("dones", "time_outs") else self._f32(src, n, widths[k])
             if v is not None and v.device != self.device:
                 raise ValueError(f"transition.{k} is on {v.device}, storage on {self.device}")
+            keep[k] = v
             setattr(tr, k, v.data_ptr() if v is not None else None)
         self._keep = keep            # sources stay referenced until the next call (the launch is asynchronous)
         _abi.check(self.lib.lt_rollout_store(C.byref(self._ptrs), C.byref(tr), self.step, n, no, npv, nh, na,
                                              C.c_float(PPO_Args.gamma), _stream(self.device)), None, "lt_rollout_store")
+
+    _POLICY_FIELDS = ("observations", "privileged_observations", "observation_histories", "actions", "values", "actions_log_prob",
+                      "action_mean", "action_sigma")
+    _ENV_FIELDS = ("rewards", "values", "dones", "time_outs")
+
+    def add_transitions(self, transition):
+        """rollout_storage.py:57-71 (+ the time-out bootstrap of ppo.py:85-87 when transition.time_outs is set)."""
+        if self.step >= self.num_transitions_per_env:
+            raise AssertionError("Rollout buffer overflow")
+        self._launch_store(transition, self._POLICY_FIELDS + ("rewards", "dones", "time_outs"))
+        self.step += 1
+
+    def store_policy_step(self, transition):
+        """First half of a transition, at act() time: everything known before env.step().  The env's observation buffers
+        are rewritten in place by the step kernels, so they must be captured now, not at process_env_step() time."""
+        if self.step >= self.num_transitions_per_env:
+            raise AssertionError("Rollout buffer overflow")
+        self._launch_store(transition, self._POLICY_FIELDS)
+
+    def store_env_step(self, transition):
+        """Second half, after env.step(): rewards (+ time-out bootstrap from the stored values) and dones."""
+        self._launch_store(transition, self._ENV_FIELDS)
         self.step += 1
 
     def clear(self):
@@ -426,6 +445,7 @@ class PPO:
         self.transition.critic_observations = obs
         self.transition.privileged_observations = privileged_obs
         self.transition.observation_histories = obs_history
+        self.storage.store_policy_step(self.transition)       # captured now: env.step() rewrites its buffers in place
         return self.transition.actions
 
     def process_env_step(self, rewards, dones, infos):
@@ -433,7 +453,7 @@ class PPO:
         self.transition.rewards = rewards
         self.transition.dones = dones
         self.transition.time_outs = infos['time_outs'].to(self.device) if 'time_outs' in infos else None
-        self.storage.add_transitions(self.transition)
+        self.storage.store_env_step(self.transition)
         self.transition.clear()
         self.actor_critic.reset(dones)
 
