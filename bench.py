@@ -111,7 +111,7 @@ class ReplaySets:
 
 
 def launch_step(eng, s, eager_gravity=True):
-    """One full step on replay set s (6 kernel launches)."""
+    """One full step on replay set s (decimation torque launches + step, obs and compaction kernels)."""
     for sub, dof in enumerate(s["dof"]):
         eng.bind_sim(dof_state=dof)
         eng.compute_torques(s["actions"], sub)
@@ -192,6 +192,59 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def ppo_iteration(eng, rs, graphs, flat, dev, dist, iters):
+    """BASELINE metric part 2: ms of one PPO iteration = T=24-step rollout (policy forward, transition store, full env step)
+    + GAE + 5 epochs x 4 minibatches of the actor-critic update (+ gradient / KL / advantage-moment all-reduces for N>1)."""
+    from legged_tracking_b200 import ppo
+    N, T = eng.N, ppo.RunnerArgs.num_steps_per_env
+    no, npv, H = flat["num_obs"], flat["num_privileged_obs"], flat["obs_history_length"]
+    torch.manual_seed(0)
+    ac = ppo.ActorCritic(no, npv, no * H, flat["num_actions"]).to(dev)
+    alg = ppo.PPO(ac, device=dev)
+    alg.init_storage(N, T, [no], [npv], [no * H], [flat["num_actions"]])
+    st = eng.state
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+    def iteration(k0):
+        ev[0].record()
+        with torch.inference_mode():
+            for t in range(T):
+                actions = alg.act(st["obs_buf"], st["privileged_obs_buf"], st["obs_history"])
+                s = (k0 + t) % N_REPLAY_SETS
+                rs.sets[s]["actions"].copy_(actions)
+                if graphs and not eng.gravity.fires_next():
+                    graphs[s].replay()
+                    eng.gravity.common_step_counter += 1
+                else:
+                    launch_step(eng, rs.sets[s])
+                alg.process_env_step(st["rew_buf"], st["reset_buf"], {"time_outs": st["time_outs_latched"]})
+            ev[1].record()
+            alg.compute_returns(st["obs_history"], st["privileged_obs_buf"])
+        ev[2].record()
+        losses = alg.update()
+        ev[3].record()
+        torch.cuda.synchronize()
+        return [ev[i].elapsed_time(ev[i + 1]) for i in range(3)], losses
+    iteration(0)                                             # warm-up (cuBLAS heuristics, allocator)
+    if dist:
+        dist.barrier()
+    parts, losses = [], None
+    for it in range(iters):
+        p_, losses = iteration(1 + it * T)
+        parts.append(p_)
+    parts = np.asarray(parts).mean(axis=0)
+    tot = torch.tensor([float(parts.sum())] + [float(x) for x in parts], device=dev)
+    if dist:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    tot = tot.tolist()
+    del alg, ac
+    torch.cuda.empty_cache()
+    return {"iter_ms": tot[0], "rollout_ms": tot[1], "gae_ms": tot[2], "update_ms": tot[3], "iters_timed": iters,
+            "num_steps_per_env": T, "epochs": ppo.PPO_Args.num_learning_epochs, "mini_batches": ppo.PPO_Args.num_mini_batches,
+            "samples_per_iter_per_gpu": N * T, "gemm": "fp32 cuBLAS via torch autograd (TF32 off, as the reference)",
+            "finite": bool(all(np.isfinite(x) for x in losses))}
+
+
 def run_b200(args, rank, world, local_rank):
     from legged_tracking_b200.engine import StepEngine
     dist = None
@@ -260,6 +313,10 @@ def run_b200(args, rank, world, local_rank):
     ms_post = time_region(post_only, ksub) / ksub
     sampler.stop_flag = True
     sampler.join()
+
+    ppo_res = None
+    if not args.no_ppo:
+        ppo_res = ppo_iteration(eng, rs, graphs, flat, dev, dist, args.ppo_iters)
 
     # ---- e2e: the same step through the public call with HOST buffers (pinned): H2D inputs, kernels, D2H results
     N, A = eng.N, flat["num_actors"]
@@ -337,6 +394,8 @@ def run_b200(args, rank, world, local_rank):
                     "ms_per_step": ms_e2e / ke, "steps": ke},
             "post_physics_only": {"value": world * n_env / (ms_post * 1e-3), "unit": UNIT, "ms_per_step": ms_post},
             "roofline": roofline}
+    if ppo_res:
+        line["ppo_iteration"] = ppo_res
     if cpu:
         line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)
@@ -353,6 +412,8 @@ def main():
     ap.add_argument("--epw", type=int, default=0, help="envs per warp of the step kernel (0 = auto)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ppo", action="store_true", help="skip the PPO-iteration timing (rollout + GAE + update)")
+    ap.add_argument("--ppo-iters", type=int, default=2)
     ap.add_argument("--cpu-envs", type=int, default=4096)
     ap.add_argument("--cpu-steps", type=int, default=40)
     args = ap.parse_args()
