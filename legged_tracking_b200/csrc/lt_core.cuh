@@ -244,11 +244,28 @@ LT_HD float lt_square(float x) { return LT_FMUL(x, x); }
 
 // ---------------------------------------------------------------------------------------------------------------
 // actuator network: Sequential(Linear(6,32), softsign, Linear(32,32), softsign, Linear(32,1))  (LR:1307-1322)
-struct lt_act_weights {
+struct alignas(16) lt_act_weights {
     float w0[LT_ACT_HIDDEN * LT_ACT_IN], b0[LT_ACT_HIDDEN];
     float w1[LT_ACT_HIDDEN * LT_ACT_HIDDEN], b1[LT_ACT_HIDDEN];
-    float w2[LT_ACT_HIDDEN], b2[1];
+    float w2[LT_ACT_HIDDEN], b2[1], pad_[3];      // 16-byte multiple: the next kernel parameter stays aligned
 };
+#if defined(__CUDACC__)
+// Blackwell packed fp32: one FFMA2 issues two independent IEEE fp32 FMAs (d.lo = a.lo*b.lo + c.lo, d.hi likewise), so the
+// result of every output unit is bit-identical to the scalar chain while the FMA issue count halves.
+__device__ __forceinline__ unsigned long long lt_pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void lt_unpack2(unsigned long long v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long lt_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+#endif
 // softsign x / (1 + |x|).  Device: MUFU.RCP-based divide (<= 2 ulp; the denominator is >= 1, never denormal) -- an IEEE
 // divide would be a third of the torque kernel's instructions; the parity budget of the torques is 1e-5.
 LT_HD float lt_softsign(float x) {
@@ -293,27 +310,89 @@ LT_HD float lt_scaled_action(const lt_config& c, float action_raw, int dof, floa
     if (dof % 3 == 0) a = LT_FMUL(a, c.hip_scale_reduction);       // columns 0,3,6,9 (LR:962)
     return a;
 }
-LT_HD void lt_torque_sample(const lt_config& c, const lt_act_weights& W, int dof, lt_torque_io& s) {
+// _compute_torques for one (env, dof) sample, split around the network so that the device kernel can run the network for
+// several samples of one thread at once.  pre: joint target, network input x (returns false for the PD controller, whose
+// torque is then already in tq); post: history shift, motor strength, clip.
+LT_HD bool lt_torque_pre(const lt_config& c, int dof, lt_torque_io& s, float x[LT_ACT_IN], float& tq) {
     const float tgt_in = c.randomize_lag_timesteps ? s.lag_out : s.action_scaled;
     s.joint_pos_target = LT_FADD(tgt_in, c.default_dof_pos[dof]);
-    float tq;
     if (c.control_type == LT_CONTROL_ACTUATOR_NET) {
         const float err = LT_FADD(LT_FSUB(s.dof_pos, s.joint_pos_target), s.motor_offset);
-        const float x[LT_ACT_IN] = {err, s.err_last, s.err_last_last, s.dof_vel, s.vel_last, s.vel_last_last};
-        tq = lt_actuator_mlp(W, x);
+        x[0] = err; x[1] = s.err_last; x[2] = s.err_last_last; x[3] = s.dof_vel; x[4] = s.vel_last; x[5] = s.vel_last_last;
+        return true;
+    }
+    const float p = LT_FMUL(LT_FMUL(c.p_gains[dof], s.kp_factor), LT_FADD(LT_FSUB(s.joint_pos_target, s.dof_pos), s.motor_offset));
+    const float d = LT_FMUL(LT_FMUL(c.d_gains[dof], s.kd_factor), s.dof_vel);
+    tq = LT_FSUB(p, d);
+    return false;
+}
+LT_HD void lt_torque_post(const lt_config& c, int dof, lt_torque_io& s, bool net, const float x[LT_ACT_IN], float tq) {
+    if (net) {
         s.err_last_last = s.err_last;
-        s.err_last = err;
+        s.err_last = x[0];
         s.vel_last_last = s.vel_last;
         s.vel_last = s.dof_vel;
-    } else {
-        const float p = LT_FMUL(LT_FMUL(c.p_gains[dof], s.kp_factor),
-                                LT_FADD(LT_FSUB(s.joint_pos_target, s.dof_pos), s.motor_offset));
-        const float d = LT_FMUL(LT_FMUL(c.d_gains[dof], s.kd_factor), s.dof_vel);
-        tq = LT_FSUB(p, d);
     }
     tq = LT_FMUL(tq, s.motor_strength);
     s.torque = fminf(fmaxf(tq, -c.torque_limits[dof]), c.torque_limits[dof]);
 }
+LT_HD void lt_torque_sample(const lt_config& c, const lt_act_weights& W, int dof, lt_torque_io& s) {
+    float x[LT_ACT_IN] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    float tq = 0.0f;
+    const bool net = lt_torque_pre(c, dof, s, x, tq);
+    if (net) tq = lt_actuator_mlp(W, x);
+    lt_torque_post(c, dof, s, net, x, tq);
+}
+
+#if defined(__CUDACC__)
+// The network for 2*P samples of one thread: sample pairs ride in the two halves of FFMA2 operands and every weight is a
+// broadcast uniform-register operand, so one 128-bit constant load feeds 8*P FMAs (the one-sample chain needs one constant
+// load per 4 FMAs and is bound by the uniform datapath, not by the FMA pipe).  Per-sample op order = the scalar chain.
+template <int P>
+__device__ __forceinline__ void lt_actuator_mlp_pairs(const lt_act_weights& W, const unsigned long long (&x)[P][LT_ACT_IN],
+                                                      unsigned long long (&out)[P]) {
+    unsigned long long h1[P][LT_ACT_HIDDEN];
+#pragma unroll
+    for (int j = 0; j < LT_ACT_HIDDEN; ++j) {
+        unsigned long long a[P];
+#pragma unroll
+        for (int q = 0; q < P; ++q) a[q] = lt_pack2(W.b0[j], W.b0[j]);
+#pragma unroll
+        for (int k = 0; k < LT_ACT_IN; ++k) {
+            const unsigned long long w = lt_pack2(W.w0[j * LT_ACT_IN + k], W.w0[j * LT_ACT_IN + k]);
+#pragma unroll
+            for (int q = 0; q < P; ++q) a[q] = lt_fma2(w, x[q][k], a[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+            float lo, hi;
+            lt_unpack2(a[q], lo, hi);
+            h1[q][j] = lt_pack2(lt_softsign(lo), lt_softsign(hi));
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < P; ++q) out[q] = lt_pack2(W.b2[0], W.b2[0]);
+#pragma unroll
+    for (int j = 0; j < LT_ACT_HIDDEN; ++j) {
+        unsigned long long a[P];
+#pragma unroll
+        for (int q = 0; q < P; ++q) a[q] = lt_pack2(W.b1[j], W.b1[j]);
+#pragma unroll
+        for (int k = 0; k < LT_ACT_HIDDEN; ++k) {
+            const unsigned long long w = lt_pack2(W.w1[j * LT_ACT_HIDDEN + k], W.w1[j * LT_ACT_HIDDEN + k]);
+#pragma unroll
+            for (int q = 0; q < P; ++q) a[q] = lt_fma2(w, h1[q][k], a[q]);
+        }
+        const unsigned long long w2 = lt_pack2(W.w2[j], W.w2[j]);
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+            float lo, hi;
+            lt_unpack2(a[q], lo, hi);
+            out[q] = lt_fma2(w2, lt_pack2(lt_softsign(lo), lt_softsign(hi)), out[q]);
+        }
+    }
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------------------------
 // One env of post_physics_step up to and including reset_idx and the non-height observation columns.

@@ -22,7 +22,15 @@
 #ifndef LT_STEP_THREADS
 #define LT_STEP_THREADS 64
 #endif
+#ifndef LT_TORQUE_THREADS
 #define LT_TORQUE_THREADS 128
+#endif
+#ifndef LT_TORQUE_MINB
+#define LT_TORQUE_MINB 1           // min resident CTAs per SM asked of ptxas for the multi-sample torque kernel
+#endif
+#ifndef LT_TORQUE_SPT
+#define LT_TORQUE_SPT 2            // (env, dof) samples per thread of the torque kernel: 1, 2 or 4 (tuning: profiles/variants.py)
+#endif
 #define LT_COMPACT_THREADS 1024
 #define LT_OBS_THREADS 256
 
@@ -182,6 +190,118 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS) lt_torque_kernel(const __gr
     if (p.substep == 0) p.st.actions[s] = io.action_clipped;
     p.st.joint_pos_target[s] = io.joint_pos_target;
     p.st.torques[s] = io.torque;
+}
+
+// Multi-sample variant: S (2 or 4) consecutive (env, dof) samples per thread.  The [N,12] rows are contiguous, so the S
+// samples of a thread are S adjacent floats of every buffer: vector loads/stores, and the network runs on sample PAIRS in
+// the two halves of FFMA2 (lt_actuator_mlp_pairs).  12 % S == 0, so a thread never straddles the end of the arrays.
+template <int S> struct lt_vec;
+template <> struct lt_vec<2> { typedef float2 T; };
+template <> struct lt_vec<4> { typedef float4 T; };
+template <int S> __device__ __forceinline__ void lt_ldv(const float* g, float (&r)[S]) {
+    const typename lt_vec<S>::T v = *reinterpret_cast<const typename lt_vec<S>::T*>(g);
+    const float* f = reinterpret_cast<const float*>(&v);
+#pragma unroll
+    for (int i = 0; i < S; ++i) r[i] = f[i];
+}
+template <int S> __device__ __forceinline__ void lt_stv(float* g, const float (&r)[S]) {
+    typename lt_vec<S>::T v;
+    float* f = reinterpret_cast<float*>(&v);
+#pragma unroll
+    for (int i = 0; i < S; ++i) f[i] = r[i];
+    *reinterpret_cast<typename lt_vec<S>::T*>(g) = v;
+}
+
+template <int S>
+__global__ void __launch_bounds__(LT_TORQUE_THREADS, LT_TORQUE_MINB) lt_torque_kernel_v(const __grid_constant__ lt_torque_params p) {
+    const lt_config& c = p.c;
+    const size_t n = (size_t)c.num_envs * LT_ND;
+    const size_t s0 = ((size_t)blockIdx.x * LT_TORQUE_THREADS + threadIdx.x) * S;
+    if (s0 >= n) return;
+    const int dof0 = (int)(s0 % LT_ND);
+    const bool net = c.control_type == LT_CONTROL_ACTUATOR_NET;
+    float act[S], pos[S], vel[S], lag[S], moff[S], mstr[S], el[S], ell[S], vl[S], vll[S], kp[S], kd[S];
+    lt_ldv<S>(p.actions_raw + s0, act);
+    {
+        float ds[2][S];
+        lt_ldv<S>(p.dof_state + 2 * s0, ds[0]);
+        lt_ldv<S>(p.dof_state + 2 * s0 + S, ds[1]);
+#pragma unroll
+        for (int i = 0; i < S; ++i) { pos[i] = ds[(2 * i) / S][(2 * i) % S]; vel[i] = ds[(2 * i + 1) / S][(2 * i + 1) % S]; }
+    }
+    lt_ldv<S>(p.st.motor_offsets + s0, moff);
+    lt_ldv<S>(p.st.motor_strengths + s0, mstr);
+    if (net) {
+        lt_ldv<S>(p.st.joint_pos_err_last + s0, el);
+        lt_ldv<S>(p.st.joint_pos_err_last_last + s0, ell);
+        lt_ldv<S>(p.st.joint_vel_last + s0, vl);
+        lt_ldv<S>(p.st.joint_vel_last_last + s0, vll);
+    } else {
+        lt_ldv<S>(p.st.Kp_factors + s0, kp);
+        lt_ldv<S>(p.st.Kd_factors + s0, kd);
+    }
+    lt_torque_io io[S];
+    float clipped[S], scaled[S];
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        io[i].action_raw = act[i];
+        scaled[i] = lt_scaled_action(c, act[i], dof0 + i, clipped[i]);
+        lag[i] = 0.0f;
+    }
+    if (c.randomize_lag_timesteps) {
+        const int Lg = c.lag_timesteps + 1;
+        const int head = (p.counters[2] + p.substep) % Lg;
+        const int rd = (head + 1) % Lg;
+        lt_stv<S>(p.st.lag_buffer + (size_t)head * n + s0, scaled);
+        if (rd == head) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) lag[i] = scaled[i];
+        } else {
+            lt_ldv<S>(p.st.lag_buffer + (size_t)rd * n + s0, lag);
+        }
+    }
+    float x[S][LT_ACT_IN], tq[S];
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        lt_torque_io& o = io[i];
+        o.dof_pos = pos[i]; o.dof_vel = vel[i]; o.lag_out = lag[i];
+        o.action_clipped = clipped[i]; o.action_scaled = scaled[i];
+        o.motor_offset = moff[i]; o.motor_strength = mstr[i];
+        o.kp_factor = net ? 1.0f : kp[i]; o.kd_factor = net ? 1.0f : kd[i];
+        o.err_last = net ? el[i] : 0.0f; o.err_last_last = net ? ell[i] : 0.0f;
+        o.vel_last = net ? vl[i] : 0.0f; o.vel_last_last = net ? vll[i] : 0.0f;
+        tq[i] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < LT_ACT_IN; ++k) x[i][k] = 0.0f;
+        lt_torque_pre(c, dof0 + i, o, x[i], tq[i]);
+    }
+    if (net) {
+        constexpr int P = S / 2;
+        unsigned long long xp[P][LT_ACT_IN], op[P];
+#pragma unroll
+        for (int q = 0; q < P; ++q)
+#pragma unroll
+            for (int k = 0; k < LT_ACT_IN; ++k) xp[q][k] = lt_pack2(x[2 * q][k], x[2 * q + 1][k]);
+        lt_actuator_mlp_pairs<P>(p.W, xp, op);
+#pragma unroll
+        for (int q = 0; q < P; ++q) lt_unpack2(op[q], tq[2 * q], tq[2 * q + 1]);
+    }
+    float tgt[S], out[S];
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        lt_torque_post(c, dof0 + i, io[i], net, x[i], tq[i]);
+        el[i] = io[i].err_last; ell[i] = io[i].err_last_last; vl[i] = io[i].vel_last; vll[i] = io[i].vel_last_last;
+        tgt[i] = io[i].joint_pos_target; out[i] = io[i].torque;
+    }
+    if (net) {
+        lt_stv<S>(p.st.joint_pos_err_last + s0, el);
+        lt_stv<S>(p.st.joint_pos_err_last_last + s0, ell);
+        lt_stv<S>(p.st.joint_vel_last + s0, vl);
+        lt_stv<S>(p.st.joint_vel_last_last + s0, vll);
+    }
+    if (p.substep == 0) lt_stv<S>(p.st.actions + s0, clipped);
+    lt_stv<S>(p.st.joint_pos_target + s0, tgt);
+    lt_stv<S>(p.st.torques + s0, out);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -826,8 +946,19 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
     p.counters = h->d_counters;
     p.substep = substep;
     const size_t n = (size_t)h->c.num_envs * LT_ND;
-    const unsigned grid = (unsigned)((n + LT_TORQUE_THREADS - 1) / LT_TORQUE_THREADS);
-    lt_torque_kernel<<<grid, LT_TORQUE_THREADS, 0, (cudaStream_t)stream>>>(p);
+    // samples per thread: the vector kernel needs 16-byte aligned rows (torch allocations are); else one sample per thread
+    uintptr_t al = (uintptr_t)actions | (uintptr_t)p.dof_state | (uintptr_t)p.st.torques | (uintptr_t)p.st.joint_pos_target |
+                   (uintptr_t)p.st.actions | (uintptr_t)p.st.motor_offsets | (uintptr_t)p.st.motor_strengths |
+                   (uintptr_t)p.st.joint_pos_err_last | (uintptr_t)p.st.joint_pos_err_last_last | (uintptr_t)p.st.joint_vel_last |
+                   (uintptr_t)p.st.joint_vel_last_last | (uintptr_t)p.st.Kp_factors | (uintptr_t)p.st.Kd_factors |
+                   (uintptr_t)p.st.lag_buffer;
+    const int spt = (al & 15u) ? 1 : LT_TORQUE_SPT;
+    const unsigned grid = (unsigned)((n / spt + LT_TORQUE_THREADS - 1) / LT_TORQUE_THREADS);
+#if LT_TORQUE_SPT > 1
+    if (spt > 1) lt_torque_kernel_v<LT_TORQUE_SPT><<<grid, LT_TORQUE_THREADS, 0, (cudaStream_t)stream>>>(p);
+    else
+#endif
+        lt_torque_kernel<<<grid, LT_TORQUE_THREADS, 0, (cudaStream_t)stream>>>(p);
     LT_CUDA(h, cudaGetLastError());
     h->substeps_pending += 1;
     return LT_OK;

@@ -34,7 +34,9 @@ def load_fixture_flat(fixture):
 
 
 def load_actuator():
-    z = np.load(os.path.join(GOLDEN, "actuator_net_go1.npz"))
+    """Weights of the reference's actuator network (resources/actuator_nets/unitree_go1.pt, LR:1307-1309) as plain arrays:
+    w0 [32,6] b0 [32] w1 [32,32] b1 [32] w2 [1,32] b2 [1] (extracted by oracle/gen_golden.actuator_from_reference)."""
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "actuator_net_go1.npz"))
     return {k: z[k] for k in z.files}
 
 

@@ -12,21 +12,27 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
 VDIR = os.path.join(REPO, "build", "variants")
 VARIANTS = {
-    "base": [],
-    "sums_direct": ["LT_OPT_SUMS_LOCAL=0"],
-    "no_prefetch": ["LT_OPT_PREFETCH=0"],
-    "unrolled": ["LT_OPT_UNROLL1=0"],
-    "cta128": ["LT_STEP_THREADS=128"],
-    "cta32": ["LT_STEP_THREADS=32"],
+    "spt2_b4": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=4"],
+    "spt2_b5": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=5"],
+    "spt2_b6": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=6"],
+    "spt2_t64_b8": ["LT_TORQUE_SPT=2", "LT_TORQUE_THREADS=64", "LT_TORQUE_MINB=8"],
+    "spt2_t64_b10": ["LT_TORQUE_SPT=2", "LT_TORQUE_THREADS=64", "LT_TORQUE_MINB=10"],
+    "spt4_b2": ["LT_TORQUE_SPT=4", "LT_TORQUE_MINB=2"],
+    "spt4_b3": ["LT_TORQUE_SPT=4", "LT_TORQUE_MINB=3"],
 }
 
 
 def build():
+    from concurrent.futures import ThreadPoolExecutor
     from legged_tracking_b200 import build as b
     os.makedirs(VDIR, exist_ok=True)
-    for name, defs in VARIANTS.items():
+
+    def one(item):
+        name, defs = item
         b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"))
-        print("built", name)
+        print("built", name, flush=True)
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        list(ex.map(one, VARIANTS.items()))
 
 
 def run_one(n_envs):
