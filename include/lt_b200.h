@@ -206,7 +206,9 @@ int lt_bind_state(lt_handle* h, const lt_state_ptrs* state);
 /* LeggedRobot._compute_torques (LR:957-996) incl. eval_actuator_network (LR:1311-1320), called once per physics
  * sub-step from LeggedRobot.step (LR:82-88).  `actions` is the RAW policy output [N,12]; clipping to
  * +-clip_actions (LR:71-72) is fused here and, when substep == 0, stored to state.actions.  Reads sim.dof_state,
- * advances the lag FIFO and the actuator-net history, writes state.joint_pos_target and state.torques. */
+ * advances the lag FIFO and the actuator-net history, writes state.joint_pos_target and state.torques.  The call with
+ * substep == decimation - 1 also performs the joint-target history shift of post_physics_step (LR:151-152:
+ * last_last_joint_pos_target <- last_joint_pos_target <- joint_pos_target), so a step must issue sub-steps 0..decimation-1. */
 int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void* stream);
 
 /* LeggedRobot.post_physics_step (LR:114-169) with everything it calls: _post_physics_step_callback (LR:774-848),

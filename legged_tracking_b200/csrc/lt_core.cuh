@@ -39,9 +39,6 @@
 #endif
 
 // tuning switches (profiles/variants.py builds and times the alternatives)
-#ifndef LT_OPT_SUMS_LOCAL
-#define LT_OPT_SUMS_LOCAL 1     /* episode/command sums: load all rows up front into a local array, store once at the end */
-#endif
 #ifndef LT_OPT_UNROLL1
 #define LT_OPT_UNROLL1 1        /* keep the small runtime-bounded loops rolled (instruction-cache footprint) */
 #endif
@@ -408,6 +405,9 @@ struct lt_env_rows {
     const float* last_dof_vel;   // [12]
     const float* torques;        // [12]
     float* obs_row;              // this env's obs_buf row: the non-height columns are written here, before noise / clipping
+    float* es;                   // this env's episode_sums column: es[t * sum_stride], t < n_terms + 3
+    float* cs;                   // this env's command_sums column or nullptr
+    size_t sum_stride;
     uint8_t* ix;                 // [nxf] out: heightfield row index of each measured x (LR:1955)
     uint8_t* iy;                 // [n_points_y] out: column index (LR:1956)
 };
@@ -759,16 +759,10 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     const bool body_h0 = st.body_height_buf[i] != 0;
     const float cam_pitch_prev = st.base_rotation[(size_t)i * 3 + 1];
     const float cam_pitch_state = st.camera_pitch_angle[i];
-#if LT_OPT_SUMS_LOCAL
-    float es[LT_MAX_TERMS + 3], cs[LT_MAX_TERMS + 1];
-    LT_ROLLED for (int t = 0; t < L.n_sums; ++t) es[t] = st.episode_sums[(size_t)t * N + i];
-    if (st.command_sums) LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) cs[t] = st.command_sums[(size_t)t * N + i];
-#define LT_ES(t) es[t]
-#define LT_CS(t) cs[t]
-#else
-#define LT_ES(t) st.episode_sums[(size_t)(t) * N + i]
-#define LT_CS(t) st.command_sums[(size_t)(t) * N + i]
-#endif
+    // this env's episode_sums / command_sums rows: staged in shared memory by the kernel (stride = envs per warp), the
+    // global arrays themselves on the host mirror (stride = num_envs)
+#define LT_ES(t) R.es[(size_t)(t) * R.sum_stride]
+#define LT_CS(t) R.cs[(size_t)(t) * R.sum_stride]
     float* root = R.root;
 
     // ---- _get_heights index part (LR:1918-1956): previous step's pitch (base_rotation not refreshed yet)
@@ -880,9 +874,6 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     LT_ES(c.n_terms + 2) = LT_FADD(LT_ES(c.n_terms + 2), rew_neg);
     if (st.command_sums) {
         LT_CS(c.n_terms) = LT_FADD(LT_CS(c.n_terms), 1.0f);
-#if LT_OPT_SUMS_LOCAL
-        LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) st.command_sums[(size_t)t * N + i] = cs[t];
-#endif
     }
 
     // ---- reset_idx (LR:218-296) for this env
@@ -910,9 +901,6 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         LT_ROLLED for (int s = 0; s < L.lag_slots; ++s)
             _Pragma("unroll") for (int d = 0; d < nd; ++d) st.lag_buffer[((size_t)s * N + i) * nd + d] = 0.0f;
     }
-#if LT_OPT_SUMS_LOCAL
-    LT_ROLLED for (int t = 0; t < L.n_sums; ++t) st.episode_sums[(size_t)t * N + i] = es[t];
-#endif
     st.episode_length_buf[i] = ep;
     st.curr_pose_index[i] = cpi;
     st.collision_count[i] = coll_count;

@@ -51,7 +51,7 @@ struct lt_step_params {
 
 struct lt_obs_params {
     int32_t num_envs, num_obs, obs_history_length, per_layer, nxf, h0, n_heights, head_w, plane, camera_zero;
-    int32_t tile_cols, tile_cells, rec_bytes;
+    int32_t tile_cols, tile_cells, rec_bytes, height_noise;
     uint32_t seed_lo, seed_hi;
     float clip_observations, ceiling_height, obs_scale_height;
     const uint8_t* scratch;
@@ -84,6 +84,7 @@ struct lt_handle {
     int32_t n_tiles;
     bool have_state, have_sim, have_terrain;
     float* d_noise_scale;
+    int height_noise;                // 1 if any height column has a nonzero noise scale
     float* d_term_sums;
     int32_t* d_counters;
     uint8_t* d_scratch;
@@ -114,6 +115,10 @@ static int lt_fail(lt_handle* h, int code, const std::string& msg) {
 __device__ __forceinline__ void lt_cp_async16(void* smem, const void* gmem) {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void lt_cp_async4(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void lt_cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
@@ -189,6 +194,10 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS) lt_torque_kernel(const __gr
     }
     if (p.substep == 0) p.st.actions[s] = io.action_clipped;
     p.st.joint_pos_target[s] = io.joint_pos_target;
+    if (p.substep == c.decimation - 1) {         // LR:151-152, done here where the rows are walked coalesced anyway
+        p.st.last_last_joint_pos_target[s] = p.st.last_joint_pos_target[s];
+        p.st.last_joint_pos_target[s] = io.joint_pos_target;
+    }
     p.st.torques[s] = io.torque;
 }
 
@@ -301,6 +310,12 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS, LT_TORQUE_MINB) lt_torque_k
     }
     if (p.substep == 0) lt_stv<S>(p.st.actions + s0, clipped);
     lt_stv<S>(p.st.joint_pos_target + s0, tgt);
+    if (p.substep == c.decimation - 1) {         // LR:151-152, done here where the rows are walked coalesced anyway
+        float prev[S];
+        lt_ldv<S>(p.st.last_joint_pos_target + s0, prev);
+        lt_stv<S>(p.st.last_last_joint_pos_target + s0, prev);
+        lt_stv<S>(p.st.last_joint_pos_target + s0, tgt);
+    }
     lt_stv<S>(p.st.torques + s0, out);
 }
 
@@ -313,9 +328,9 @@ __global__ void __launch_bounds__(LT_TORQUE_THREADS, LT_TORQUE_MINB) lt_torque_k
 //   phase 1  the scalar step logic (lt_core.cuh); non-height observation columns go straight to obs_buf, the
 //            heightfield cell indices + post-reset z + camera z into a packed per-env record for lt_obs_kernel
 //   phase 2  flat coalesced write-back of the root / dof / record tiles
-// Shared memory per warp: root[EPW*A*13] dof[EPW*24] contact[EPW*B*3] floats + rec[EPW*rec_bytes] bytes.
+// Shared memory per warp: root[EPW*A*13] dof[EPW*24] cinfo[EPW] es[EPW*(terms+3)] cs[EPW*(terms+1)] floats + rec[EPW*rec_bytes] bytes.
 struct lt_smem_plan {
-    int root, dof, contact, rec, total;       // float offsets
+    int root, dof, contact, rec, es, cs, total;       // float offsets
 };
 __host__ __device__ inline int lt_align4(int x) { return (x + 3) & ~3; }
 __host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, int rec_bytes, int epw) {
@@ -323,9 +338,11 @@ __host__ __device__ inline lt_smem_plan lt_plan_smem(const lt_config& c, int rec
     int o = 0;
     P.root = o; o += lt_align4(epw * c.num_actors * 13);
     P.dof = o; o += lt_align4(epw * LT_ND * 2);
-    P.contact = o; o += lt_align4(epw * c.num_bodies * 3);
+    P.contact = o; o += lt_align4(epw);              // one packed contact word per env (lt_contact_summary)
     P.rec = o; o += lt_align4(epw * rec_bytes / 4);
-    P.total = o;
+    P.es = o; o += epw * (c.n_terms + 3);            // episode_sums rows [t][lane]
+    P.cs = o; o += epw * (c.n_terms + 1);            // command_sums rows [t][lane]
+    P.total = lt_align4(o);
     return P;
 }
 
@@ -357,8 +374,10 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     float* ws = smem + (size_t)warp * P.total;
     float* s_root = ws + P.root;
     float* s_dof = ws + P.dof;
-    float* s_contact = ws + P.contact;
+    uint32_t* s_cinfo = reinterpret_cast<uint32_t*>(ws + P.contact);
     uint8_t* s_rec = reinterpret_cast<uint8_t*>(ws + P.rec);
+    float* s_es = ws + P.es;
+    float* s_cs = ws + P.cs;
 
     const int tile = blockIdx.x * WARPS + warp;
     const int env0 = tile * EPW;
@@ -371,7 +390,32 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     // ---- phase 0
     lt_tile_load(s_root, p.sim.root_states + (size_t)env0 * A13, nv * A13, lane, full);
     lt_tile_load(s_dof, p.sim.dof_state + (size_t)env0 * LT_ND * 2, nv * LT_ND * 2, lane, full);
-    lt_tile_load(s_contact, p.sim.contact_forces + (size_t)env0 * B3, nv * B3, lane, full);
+    // net contact forces: never staged.  Lane <-> (env, body) pair, so that the tile is read as one coalesced stream, and
+    // each pair's flags are merged into its env's packed word (same bits as lt_contact_summary; integer, order-free)
+    if (lane < EPW) s_cinfo[lane] = 0u;
+    __syncwarp();
+    {
+        const float* cg = p.sim.contact_forces + (size_t)env0 * B3;
+        const int nb = c.num_bodies, pairs = nv * nb;
+        const int step_e = 32 / nb, step_b = 32 % nb;
+        int e = lane / nb, b = lane % nb;
+#pragma unroll 2
+        for (int q = lane; q < pairs; q += 32) {
+            const float fx = cg[3 * q], fy = cg[3 * q + 1], fz = cg[3 * q + 2];
+            uint32_t cnt = 0u, flags = 0u;
+            if (((c.penalised_mask | c.termination_mask) >> b) & 1u) {
+                const float f = lt_norm3(fx, fy, fz);
+                if (((c.penalised_mask >> b) & 1u) && f > 0.1f) cnt = 1u;
+                if (((c.termination_mask >> b) & 1u) && f > 1.0f) flags |= 0x100u;
+            }
+            for (int k = 0; k < c.n_feet; ++k)
+                if (c.feet_indices[k] == b && fz > 1.0f) flags |= 0x10000u << k;
+            if (cnt) atomicAdd(s_cinfo + e, cnt);
+            if (flags) atomicOr(s_cinfo + e, flags);
+            e += step_e; b += step_b;
+            if (b >= nb) { b -= nb; e += 1; }
+        }
+    }
     float r_act[LT_ND], r_last_act[LT_ND], r_last_dof_vel[LT_ND], r_torques[LT_ND];
     uint32_t cinfo = 0u;
     if (mine) {
@@ -388,15 +432,15 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         lt_prefetch(st.friction_coeffs + i);
         lt_prefetch(st.restitutions + i);
         lt_prefetch(st.body_height_buf + i);
-        lt_prefetch(st.joint_pos_target + (size_t)i * LT_ND);
-        lt_prefetch(st.last_joint_pos_target + (size_t)i * LT_ND);
         if (c.observe_heights && !c.plane) lt_prefetch(p.ter.env_terrain_origin + (size_t)i * 3);
-        LT_ROLLED for (int t = 0; t < L.n_sums; ++t) lt_prefetch(st.episode_sums + (size_t)t * N + i);
-        if (st.command_sums) LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) lt_prefetch(st.command_sums + (size_t)t * N + i);
+        // episode / command sums: asynchronous 4-byte copies into [t][lane] shared rows (no register, no stall until the wait)
+        LT_ROLLED for (int t = 0; t < L.n_sums; ++t) lt_cp_async4(s_es + t * EPW + lane, st.episode_sums + (size_t)t * N + i);
+        if (st.command_sums)
+            LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) lt_cp_async4(s_cs + t * EPW + lane, st.command_sums + (size_t)t * N + i);
     }
     lt_cp_async_wait_all();
     __syncwarp();
-    if (mine) cinfo = lt_contact_summary(c, s_contact + lane * B3);
+    if (mine) cinfo = s_cinfo[lane];
 
     // ---- phase 1: the scalar logic of the step
     int my_reset = 0;
@@ -411,6 +455,9 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         R.last_dof_vel = r_last_dof_vel;
         R.torques = r_torques;
         R.obs_row = st.obs_buf + (size_t)i * c.num_obs;
+        R.es = s_es + lane;
+        R.cs = st.command_sums ? s_cs + lane : nullptr;
+        R.sum_stride = EPW;
         uint8_t* rec = s_rec + lane * rec_bytes;
         R.ix = rec;
         R.iy = rec + L.nxf;
@@ -425,16 +472,17 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         for (int d = 0; d < LT_ND; ++d) row[d] = my_reset ? 0.0f : r_last_act[d];      // last_actions[env_ids] = 0 precedes the shift (LR:246)
         lt_store_row12(st.last_last_actions + (size_t)i * LT_ND, row);
         lt_store_row12(st.last_actions + (size_t)i * LT_ND, r_act);
-        lt_load_row12(st.last_joint_pos_target + (size_t)i * LT_ND, row);
-        lt_store_row12(st.last_last_joint_pos_target + (size_t)i * LT_ND, row);
-        lt_load_row12(st.joint_pos_target + (size_t)i * LT_ND, row);
-        lt_store_row12(st.last_joint_pos_target + (size_t)i * LT_ND, row);
+        // (the joint_pos_target history shift of LR:151-152 is done by the torque kernel's last sub-step)
 #pragma unroll
         for (int d = 0; d < LT_ND; ++d) row[d] = R.dof[2 * d + 1];                      // post-reset dof_vel
         lt_store_row12(st.last_dof_vel + (size_t)i * LT_ND, row);
         float2* lrv = reinterpret_cast<float2*>(st.last_root_vel + (size_t)i * 6);
 #pragma unroll
         for (int k = 0; k < 3; ++k) lrv[k] = make_float2(R.root[7 + 2 * k], R.root[8 + 2 * k]);
+        // sums back to their term-major rows (coalesced across the warp)
+        LT_ROLLED for (int t = 0; t < L.n_sums; ++t) st.episode_sums[(size_t)t * N + i] = s_es[t * EPW + lane];
+        if (st.command_sums)
+            LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) st.command_sums[(size_t)t * N + i] = s_cs[t * EPW + lane];
     }
     __syncwarp();
     const unsigned reset_mask = __ballot_sync(0xffffffffu, my_reset != 0);
@@ -465,7 +513,9 @@ __device__ __forceinline__ float lt_u12_static(const uint32_t (&rnd)[4]) {      
     if (sh > 20) x |= rnd[w < 3 ? w + 1 : 3] << (32 - sh);
     return LT_FMUL((float)(x & 0xfffu) + 0.5f, 1.0f / 4096.0f);
 }
-template <int KP, int NOISE, int CAM>
+// HN = 1 only when a height column has a nonzero noise scale; the reference's _get_noise_scale_vec hard-codes zeros there
+// (LR:1125-1131), and v + (2u-1)*0 == v, so the usual instantiation skips noise for the 220 height columns altogether.
+template <int KP, int NOISE, int CAM, int HN>
 __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_constant__ lt_obs_params p) {
     const int lane = threadIdx.x & 31;
     const int ie = blockIdx.x * (LT_OBS_THREADS / 32) + (threadIdx.x >> 5);
@@ -492,7 +542,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
         }
     }
     uint32_t rnd[4] = {0u, 0u, 0u, 0u};
-    if (NOISE == 2) lt_philox((uint32_t)ie, (uint32_t)lane | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
+    if (HN && NOISE == 2) lt_philox((uint32_t)ie, (uint32_t)lane | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
     float* hist_row = p.obs_history + (size_t)ie * no * H;
     if (H > 1) {
         const int keep = (H - 1) * no;
@@ -515,8 +565,8 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
                 else h = LT_FSUB(LT_FDIV(fminf(fmaxf(h, 0.0f), ceil_h), ceil_h), 0.5f);
                 h = LT_FMUL(h, hscale);
                 float u = 0.5f;
-                if (NOISE == 1) u = nz[col];
-                if (NOISE == 2) {
+                if (HN && NOISE == 1) u = nz[col];
+                if (HN && NOISE == 2) {
                     const int v = 2 * k + layer;                 // compile-time after unrolling
                     if (v == LT_NOISE_PER_CALL)                  // KP = 8 only: values 10.. come from the second call
                         lt_philox((uint32_t)ie, (uint32_t)(lane + 32) | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
@@ -528,7 +578,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
                     case 8: u = lt_u12_static<8>(rnd); break; default: u = lt_u12_static<9>(rnd); break;
                     }
                 }
-                const float o = lt_obs_finish_dev<NOISE>(h, u, NOISE ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
+                const float o = lt_obs_finish_dev<(HN ? NOISE : 0)>(h, u, (HN && NOISE) ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
                 obs_row[col] = o;
                 hist_new[col] = o;
             }
@@ -539,7 +589,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
     for (int m = 0; m < head_iters; ++m) {
         const int hi = lane + 32 * m;
         const int v = 2 * KP + m;
-        if (NOISE == 2 && v % LT_NOISE_PER_CALL == 0)
+        if (NOISE == 2 && (v % LT_NOISE_PER_CALL == 0 || (!HN && m == 0)))      // !HN: the height loop made no call yet
             lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (v / LT_NOISE_PER_CALL)) | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
         if (hi < p.head_w) {
             const int col = hi < p.h0 ? hi : hi + p.n_heights;
@@ -717,9 +767,12 @@ static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) 
 template <int KP, int CAM>
 static cudaError_t lt_launch_obs_cam(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
     const unsigned grid = (unsigned)((p.num_envs + LT_OBS_THREADS / 32 - 1) / (LT_OBS_THREADS / 32));
-    if (noise_mode == 0) lt_obs_kernel<KP, 0, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else if (noise_mode == 1) lt_obs_kernel<KP, 1, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else lt_obs_kernel<KP, 2, CAM><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    const bool hn = p.height_noise != 0;
+    if (noise_mode == 0) lt_obs_kernel<KP, 0, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else if (noise_mode == 1 && hn) lt_obs_kernel<KP, 1, CAM, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else if (noise_mode == 1) lt_obs_kernel<KP, 1, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else if (hn) lt_obs_kernel<KP, 2, CAM, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
+    else lt_obs_kernel<KP, 2, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
 template <int KP>
@@ -817,6 +870,9 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
         epw = per_sm >= 32 ? 32 : 8;
     }
     h->epw = epw;
+    h->height_noise = 0;
+    for (int q = 0; q < h->L.n_heights; ++q)
+        if (tables->noise_scale_vec[h->L.h0 + q] != 0.0f) h->height_noise = 1;
     cudaError_t e = cudaMalloc(&h->d_noise_scale, sizeof(float) * (size_t)cfg->num_obs);
     if (e == cudaSuccess) e = cudaMemcpy(h->d_noise_scale, tables->noise_scale_vec, sizeof(float) * (size_t)cfg->num_obs, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_term_sums, sizeof(float) * LT_MAX_TERMS);
@@ -951,7 +1007,7 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
                    (uintptr_t)p.st.actions | (uintptr_t)p.st.motor_offsets | (uintptr_t)p.st.motor_strengths |
                    (uintptr_t)p.st.joint_pos_err_last | (uintptr_t)p.st.joint_pos_err_last_last | (uintptr_t)p.st.joint_vel_last |
                    (uintptr_t)p.st.joint_vel_last_last | (uintptr_t)p.st.Kp_factors | (uintptr_t)p.st.Kd_factors |
-                   (uintptr_t)p.st.lag_buffer;
+                   (uintptr_t)p.st.lag_buffer | (uintptr_t)p.st.last_joint_pos_target | (uintptr_t)p.st.last_last_joint_pos_target;
     const int spt = (al & 15u) ? 1 : LT_TORQUE_SPT;
     const unsigned grid = (unsigned)((n / spt + LT_TORQUE_THREADS - 1) / LT_TORQUE_THREADS);
 #if LT_TORQUE_SPT > 1
@@ -1028,6 +1084,7 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream) {
         o.rec_bytes = h->rec_bytes; o.seed_lo = c.seed_lo; o.seed_hi = c.seed_hi;
         o.clip_observations = c.clip_observations; o.ceiling_height = c.ceiling_height; o.obs_scale_height = c.obs_scale_height;
         o.scratch = h->d_scratch; o.ptlut = h->d_ptlut; o.tile_heights = h->ter.tile_heights; o.env_tile = h->ter.env_tile;
+        o.height_noise = h->height_noise;
         o.noise_scale_vec = h->d_noise_scale; o.noise_uniforms = p.args.noise_uniforms; o.counters = h->d_counters;
         o.obs_buf = h->st.obs_buf; o.obs_history = h->st.obs_history;
         const int mode = !c.add_noise ? 0 : (p.args.noise_uniforms ? 1 : 2);

@@ -111,6 +111,7 @@ int lths_post_physics(const lt_config* cfg, const lt_tables* tb, const lt_state_
         R.last_dof_vel = st.last_dof_vel + (size_t)i * nd;
         R.torques = st.torques + (size_t)i * nd;
         R.obs_row = st.obs_buf + (size_t)i * no; R.ix = ix.data(); R.iy = iy.data();
+        R.es = st.episode_sums + i; R.cs = st.command_sums ? st.command_sums + i : nullptr; R.sum_stride = (size_t)N;
         const lt_env_result r = lt_env_step(c, L, st, ter, args, sc, i, R);
         // history shifts (kernel phase 3)
         for (int d = 0; d < nd; ++d) {
