@@ -154,10 +154,14 @@ LT_HD float lt_u12(const uint32_t rnd[4], int slot) {
 struct lt_uniform_src {
     const float* row;            // [n_slots] or nullptr
     uint32_t seed_lo, seed_hi, step, env;
+    mutable uint32_t blk = 0xffffffffu, o[4] = {0u, 0u, 0u, 0u};      // last Philox block: consecutive slots share one call
     LT_HD_COLD float get(int slot) const {          // only reached on reset / interval randomisation
         if (row) return row[slot];
-        uint32_t o[4];
-        lt_philox(env, (uint32_t)(slot >> 2) | LT_STREAM_SLOTS, step, 0u, seed_lo, seed_hi, o);
+        const uint32_t b = (uint32_t)(slot >> 2);
+        if (b != blk) {
+            lt_philox(env, b | LT_STREAM_SLOTS, step, 0u, seed_lo, seed_hi, o);
+            blk = b;
+        }
         return lt_u01(o[slot & 3]);
     }
 };
@@ -759,6 +763,8 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     const bool body_h0 = st.body_height_buf[i] != 0;
     const float cam_pitch_prev = st.base_rotation[(size_t)i * 3 + 1];
     const float cam_pitch_state = st.camera_pitch_angle[i];
+    const float friction0 = c.priv_observe_friction ? st.friction_coeffs[i] : 0.0f;          // read early: used last
+    const float restitution0 = c.priv_observe_restitution ? st.restitutions[i] : 0.0f;
     // this env's episode_sums / command_sums rows: staged in shared memory by the kernel (stride = envs per warp), the
     // global arrays themselves on the host mirror (stride = num_envs)
 #define LT_ES(t) R.es[(size_t)(t) * R.sum_stride]
@@ -955,8 +961,8 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
         int k = 0;
         const float co = c.clip_observations;
 #define LT_PRIV(idx, x) po[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB((x), c.priv_shift[idx]), c.priv_scale[idx]), -co), co)
-        if (c.priv_observe_friction) LT_PRIV(0, st.friction_coeffs[i]);
-        if (c.priv_observe_restitution) LT_PRIV(1, st.restitutions[i]);
+        if (c.priv_observe_friction) LT_PRIV(0, friction0);
+        if (c.priv_observe_restitution) LT_PRIV(1, restitution0);
         if (c.priv_observe_base_mass) LT_PRIV(2, st.payloads[i]);
         if (c.priv_observe_com_displacement) for (int a = 0; a < 3; ++a) LT_PRIV(3, st.com_displacements[(size_t)i * 3 + a]);
         if (c.priv_observe_motor_strength) _Pragma("unroll") for (int d = 0; d < nd; ++d) LT_PRIV(4, st.motor_strengths[(size_t)i * nd + d]);

@@ -399,17 +399,34 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         const int nb = c.num_bodies, pairs = nv * nb;
         const int step_e = 32 / nb, step_b = 32 % nb;
         int e = lane / nb, b = lane % nb;
-#pragma unroll 2
+        const uint32_t listed = c.penalised_mask | c.termination_mask;
+        uint32_t foot_bit[2] = {0u, 0u};          // body -> foot slot + 1, 4 bits per body (LT_MAX_BODIES = 32 -> 2 x 64 bits as 4 x 32)
+        unsigned long long foot_lut0 = 0ull, foot_lut1 = 0ull;
+        for (int k = 0; k < c.n_feet; ++k) {
+            const int fb = c.feet_indices[k];
+            if (fb < 16) foot_lut0 |= (unsigned long long)(k + 1) << (4 * fb);
+            else foot_lut1 |= (unsigned long long)(k + 1) << (4 * (fb - 16));
+        }
+        (void)foot_bit;
+#pragma unroll 6
         for (int q = lane; q < pairs; q += 32) {
             const float fx = cg[3 * q], fy = cg[3 * q + 1], fz = cg[3 * q + 2];
             uint32_t cnt = 0u, flags = 0u;
-            if (((c.penalised_mask | c.termination_mask) >> b) & 1u) {
-                const float f = lt_norm3(fx, fy, fz);
-                if (((c.penalised_mask >> b) & 1u) && f > 0.1f) cnt = 1u;
-                if (((c.termination_mask >> b) & 1u) && f > 1.0f) flags |= 0x100u;
+            if ((listed >> b) & 1u) {
+                // |F| > 0.1 and |F| > 1 are decided on |F|^2 away from the thresholds (sqrt is monotonic; the 2 % bands are far wider
+                // than its rounding); inside a band the exact lt_norm3 comparison runs
+                const float ss = LT_FFMA(fz, fz, LT_FFMA(fy, fy, LT_FMUL(fx, fx)));
+                bool g01 = ss > 0.0102f, g1 = ss > 1.02f;
+                if ((ss > 0.0098f && ss <= 0.0102f) || (ss > 0.98f && ss <= 1.02f)) {
+                    const float f = LT_FSQRT(ss);
+                    g01 = f > 0.1f;
+                    g1 = f > 1.0f;
+                }
+                if (((c.penalised_mask >> b) & 1u) && g01) cnt = 1u;
+                if (((c.termination_mask >> b) & 1u) && g1) flags |= 0x100u;
             }
-            for (int k = 0; k < c.n_feet; ++k)
-                if (c.feet_indices[k] == b && fz > 1.0f) flags |= 0x10000u << k;
+            const uint32_t slot = (uint32_t)((b < 16 ? foot_lut0 >> (4 * b) : foot_lut1 >> (4 * (b - 16))) & 0xfull);
+            if (slot && fz > 1.0f) flags |= 0x8000u << slot;          // 0x10000 << (slot - 1)
             if (cnt) atomicAdd(s_cinfo + e, cnt);
             if (flags) atomicOr(s_cinfo + e, flags);
             e += step_e; b += step_b;
@@ -480,9 +497,9 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
 #pragma unroll
         for (int k = 0; k < 3; ++k) lrv[k] = make_float2(R.root[7 + 2 * k], R.root[8 + 2 * k]);
         // sums back to their term-major rows (coalesced across the warp)
-        LT_ROLLED for (int t = 0; t < L.n_sums; ++t) st.episode_sums[(size_t)t * N + i] = s_es[t * EPW + lane];
+        _Pragma("unroll 4") for (int t = 0; t < L.n_sums; ++t) st.episode_sums[(size_t)t * N + i] = s_es[t * EPW + lane];
         if (st.command_sums)
-            LT_ROLLED for (int t = 0; t <= c.n_terms; ++t) st.command_sums[(size_t)t * N + i] = s_cs[t * EPW + lane];
+            _Pragma("unroll 4") for (int t = 0; t <= c.n_terms; ++t) st.command_sums[(size_t)t * N + i] = s_cs[t * EPW + lane];
     }
     __syncwarp();
     const unsigned reset_mask = __ballot_sync(0xffffffffu, my_reset != 0);
@@ -524,7 +541,20 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
     const float clip = p.clip_observations, hscale = p.obs_scale_height, ceil_h = p.ceiling_height;
     const uint32_t step = NOISE == 2 ? (uint32_t)p.counters[0] : 0u;
     const uint8_t* rec = p.scratch + (size_t)ie * p.rec_bytes;
-    const float2 zc = *reinterpret_cast<const float2*>(rec + p.rec_bytes - 8);        // (z_post, cam_z)
+    // the env's packed record (cell-index bytes, then (z_post, cam_z)) in ONE coalesced load: lane l holds word l; a
+    // point's row / column byte is fetched from the owning lane by shuffle instead of a dependent byte load
+    const int rec_words = p.rec_bytes >> 2;
+    const uint32_t rec_w = lane < rec_words ? __ldg(reinterpret_cast<const uint32_t*>(rec) + lane) : 0u;
+    float* obs_row = p.obs_buf + (size_t)ie * no;
+    // raw non-height columns (written by lt_step_kernel) and their noise scales: issued now, used after the height loop
+    const int hcol0 = lane < p.h0 ? lane : lane + p.n_heights;
+    const int hcol1 = (lane + 32) < p.h0 ? lane + 32 : lane + 32 + p.n_heights;
+    const float raw0 = lane < p.head_w ? obs_row[hcol0] : 0.0f;
+    const float raw1 = lane + 32 < p.head_w ? obs_row[hcol1] : 0.0f;
+    const float ns0 = (NOISE && lane < p.head_w) ? __ldg(p.noise_scale_vec + hcol0) : 0.0f;
+    const float ns1 = (NOISE && lane + 32 < p.head_w) ? __ldg(p.noise_scale_vec + hcol1) : 0.0f;
+    const float2 zc = make_float2(__uint_as_float(__shfl_sync(0xffffffffu, rec_w, rec_words - 2)),
+                                  __uint_as_float(__shfl_sync(0xffffffffu, rec_w, rec_words - 1)));        // (z_post, cam_z)
     float hc[KP], hf[KP];
     {
         const float* tile_base = p.plane ? nullptr : p.tile_heights + (size_t)__ldg(p.env_tile + ie) * 2 * p.tile_cells;
@@ -533,9 +563,12 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
             const int pt = lane + 32 * k;
             hc[k] = 1.0f;                         // plane: ceiling 1, floor 0 (LR:1928-1932)
             hf[k] = 0.0f;
-            if (tile_base && pt < per_layer) {
-                const uint32_t w = __ldg(p.ptlut + pt);
-                const int off = (int)rec[w & 0xffu] * p.tile_cols + (int)rec[p.nxf + (w >> 8)];
+            const bool on = pt < per_layer;
+            const uint32_t w = on ? __ldg(p.ptlut + pt) : 0u;
+            const int bx = (int)(w & 0xffu), by = p.nxf + (int)(w >> 8);           // byte positions in the record
+            const uint32_t wx = __shfl_sync(0xffffffffu, rec_w, bx >> 2), wy = __shfl_sync(0xffffffffu, rec_w, by >> 2);
+            if (tile_base && on) {
+                const int off = (int)((wx >> (8 * (bx & 3))) & 0xffu) * p.tile_cols + (int)((wy >> (8 * (by & 3))) & 0xffu);
                 hc[k] = __ldg(tile_base + off);
                 hf[k] = __ldg(tile_base + p.tile_cells + off);
             }
@@ -549,7 +582,6 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
         for (int k = lane; k < keep; k += 32) { const float v = hist_row[k + no]; hist_row[k] = v; }
     }
     // per-lane base pointers: column h0 + lane (ceiling layer) and h0 + per_layer + lane (floor layer)
-    float* obs_row = p.obs_buf + (size_t)ie * no;
     float* hist_new = hist_row + (size_t)(H - 1) * no;
     const int c0 = p.h0 + lane, c1 = c0 + per_layer;
     const float* nz = NOISE == 1 ? p.noise_uniforms + (size_t)ie * no : nullptr;
@@ -596,7 +628,9 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
             float u = 0.5f;
             if (NOISE == 1) u = nz[col];
             if (NOISE == 2) u = lt_u12(rnd, v % LT_NOISE_PER_CALL);
-            const float o = lt_obs_finish_dev<NOISE>(obs_row[col], u, NOISE ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
+            const float raw = m == 0 ? raw0 : (m == 1 ? raw1 : obs_row[col]);
+            const float ns = !NOISE ? 0.0f : (m == 0 ? ns0 : (m == 1 ? ns1 : __ldg(p.noise_scale_vec + col)));
+            const float o = lt_obs_finish_dev<NOISE>(raw, u, ns, clip);
             obs_row[col] = o;
             hist_new[col] = o;
         }
