@@ -10,9 +10,11 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 OUT = os.path.join(PKG_DIR, "liblt_b200.so")
-SOURCES = ["lt_kernels.cu", "lt_rollout.cu"]
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--shared",
+SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_rollout.cu"]
+HEADERS = ["lt_core.cuh", "lt_torque_mma.h"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-I", os.path.join(REPO, "include")]
+OBJ_DIR = os.path.join(REPO, "build", "obj")
 
 
 def _stale(out, deps):
@@ -22,19 +24,42 @@ def _stale(out, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False, defines=(), out=OUT):
-    """defines / out: tuning variants (profiles/variants.py); the product build uses neither."""
+def build(force=False, verbose=False, defines=(), out=OUT, only=None):
+    """Each .cu is compiled to its own object (in parallel; only stale ones) and the objects are linked into `out`.
+    defines / out / only: tuning variants (profiles/variants.py); the product build uses none of them.  `only` names the
+    sources the defines apply to -- the other objects are taken from the default build."""
+    from concurrent.futures import ThreadPoolExecutor
     srcs = [os.path.join(CSRC, s) for s in SOURCES]
-    deps = srcs + [os.path.join(CSRC, "lt_core.cuh"), os.path.join(REPO, "include", "lt_b200.h")]
-    if not force and not _stale(out, deps):
-        return out
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.join(REPO, "include", "lt_b200.h")]
+    tag = "default" if not defines else "v_" + "_".join(d.replace("=", "-") for d in defines)
+    odir = os.path.join(OBJ_DIR, tag)
+    os.makedirs(odir, exist_ok=True)
+    objs = [os.path.join(odir if (only is None or os.path.basename(s) in only) else os.path.join(OBJ_DIR, "default"),
+                         os.path.splitext(os.path.basename(s))[0] + ".o") for s in srcs]
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", out] + srcs
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    log = []
+
+    def compile_one(so):
+        src, obj = so
+        mine = only is None or os.path.basename(src) in only
+        if not mine and os.path.exists(obj):
+            return
+        if not force and not _stale(obj, [src] + hdrs):
+            return
+        cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in (defines if mine else ())] + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+        log.append(r.stdout + r.stderr)
+    with ThreadPoolExecutor(max_workers=len(srcs)) as ex:
+        list(ex.map(compile_one, zip(srcs, objs)))
+    if force or _stale(out, objs):
+        cmd = [nvcc, "--shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("link failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     if verbose:
-        print(r.stdout + r.stderr)
+        print("".join(log))
     return out
 
 

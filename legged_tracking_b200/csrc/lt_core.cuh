@@ -15,7 +15,7 @@
 
 #if defined(__CUDACC__)
 #define LT_HD __host__ __device__ __forceinline__
-#define LT_HD_COLD __host__ __device__ __noinline__      /* rare paths (reset, domain randomisation): keep them out of the hot code */
+#define LT_HD_COLD inline __host__ __device__ __noinline__      /* rare paths (reset, domain randomisation): keep them out of the hot code */
 #else
 #define LT_HD inline
 #define LT_HD_COLD inline

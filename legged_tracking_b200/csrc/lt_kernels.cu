@@ -18,6 +18,7 @@
 #include <string>
 
 #include "lt_core.cuh"
+#include "lt_torque_mma.h"
 
 #ifndef LT_STEP_THREADS
 #define LT_STEP_THREADS 64
@@ -30,6 +31,9 @@
 #endif
 #ifndef LT_TORQUE_SPT
 #define LT_TORQUE_SPT 2            // (env, dof) samples per thread of the torque kernel: 1, 2 or 4 (tuning: profiles/variants.py)
+#endif
+#ifndef LT_TORQUE_MMA
+#define LT_TORQUE_MMA 1            // actuator net on the tensor pipe (lt_torque_mma.cu); 0 = FP32-pipe kernels below
 #endif
 #define LT_COMPACT_THREADS 1024
 #define LT_OBS_THREADS 256
@@ -89,6 +93,8 @@ struct lt_handle {
     int32_t* d_counters;
     uint8_t* d_scratch;
     uint32_t* d_ptlut;
+    float* d_act_frag;               // [LT_MMA_FRAG_REGS, 32] pre-split TF32 weight fragments of the actuator net
+    int sm_count;
     int32_t rec_bytes;
     int32_t substeps_pending;        // lt_compute_torques calls since the last lt_post_physics_step
     bool sign_prepass_done;
@@ -925,6 +931,13 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
         if (e == cudaSuccess) e = cudaMalloc(&h->d_ptlut, lut.size());
         if (e == cudaSuccess) e = cudaMemcpy(h->d_ptlut, lut.data(), lut.size(), cudaMemcpyHostToDevice);
     }
+    {
+        std::string fr((size_t)LT_MMA_FRAG_REGS * 32 * sizeof(float), '\0');
+        lt_torque_mma_build_frags(h->W, reinterpret_cast<float*>(&fr[0]));
+        if (e == cudaSuccess) e = cudaMalloc(&h->d_act_frag, fr.size());
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_act_frag, fr.data(), fr.size(), cudaMemcpyHostToDevice);
+    }
+    h->sm_count = prop.multiProcessorCount;
     if (e != cudaSuccess) {
         const std::string msg = std::string("lt_create: ") + cudaGetErrorString(e);
         delete h;
@@ -941,6 +954,7 @@ void lt_destroy(lt_handle* h) {
     cudaFree(h->d_counters);
     cudaFree(h->d_scratch);
     cudaFree(h->d_ptlut);
+    cudaFree(h->d_act_frag);
     delete h;
 }
 
@@ -1036,6 +1050,14 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
     p.counters = h->d_counters;
     p.substep = substep;
     const size_t n = (size_t)h->c.num_envs * LT_ND;
+#if LT_TORQUE_MMA
+    if (h->c.control_type == LT_CONTROL_ACTUATOR_NET) {
+        LT_CUDA(h, lt_torque_mma_launch(h->c, h->d_act_frag, actions, h->sim.dof_state, h->st, h->d_counters, substep, h->sm_count,
+                                        (cudaStream_t)stream));
+        h->substeps_pending += 1;
+        return LT_OK;
+    }
+#endif
     // samples per thread: the vector kernel needs 16-byte aligned rows (torch allocations are); else one sample per thread
     uintptr_t al = (uintptr_t)actions | (uintptr_t)p.dof_state | (uintptr_t)p.st.torques | (uintptr_t)p.st.joint_pos_target |
                    (uintptr_t)p.st.actions | (uintptr_t)p.st.motor_offsets | (uintptr_t)p.st.motor_strengths |

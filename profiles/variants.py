@@ -11,7 +11,15 @@ import sys
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
 VDIR = os.path.join(REPO, "build", "variants")
+MMA_ONLY = ("lt_torque_mma.cu",)          # variants whose defines touch only the tensor-pipe torque kernel
 VARIANTS = {
+    "mma_mb1_b3": ["LT_MMA_MB=1", "LT_MMA_MINB=3"],
+    "mma_mb2_b3": ["LT_MMA_MB=2", "LT_MMA_MINB=3"],
+    "mma_mb2_b2": ["LT_MMA_MB=2", "LT_MMA_MINB=2"],
+    "mma_mb2_b4": ["LT_MMA_MB=2", "LT_MMA_MINB=4"],
+    "mma_mb1_b4": ["LT_MMA_MB=1", "LT_MMA_MINB=4"],
+}
+OLD_VARIANTS = {
     "spt2_b4": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=4"],
     "spt2_b5": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=5"],
     "spt2_b6": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=6"],
@@ -29,7 +37,7 @@ def build():
 
     def one(item):
         name, defs = item
-        b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"))
+        b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"), only=MMA_ONLY if name.startswith("mma_") else None)
         print("built", name, flush=True)
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         list(ex.map(one, VARIANTS.items()))

@@ -101,3 +101,50 @@ def test_philox_noise_statistics():
     zc = z - z.mean(0)
     corr = (zc[:, :-1] * zc[:, 1:]).mean(0) * 3.0
     assert corr.abs().max() < 0.05
+
+
+@pytest.mark.parametrize("n_envs", [3, 67, 1024])
+def test_torque_kernel_ragged_tiles_and_float64_reference(n_envs):
+    """lt_compute_torques (tensor-pipe actuator net, 32-sample warp tiles) on env counts whose 12*N samples do not fill
+    the last tile, over enough sub-steps for the error/velocity histories and the 7-slot lag ring to wrap: torques,
+    joint targets and the shifted histories against the oracle port; the network itself against a float64 evaluation
+    of the same weights on the same fp32 inputs (what the 3xTF32 split has to reproduce to 1e-5 of the contraction)."""
+    from legged_tracking_b200 import workload
+    from legged_tracking_b200.engine import StepEngine
+    from oracle.port import OraclePort
+    flat, terrain, act, synth = workload.make("cfg2", num_envs=n_envs, tile_grid=(1, 1))
+    eng = StepEngine(flat, terrain, act, device="cuda:0")
+    port = OraclePort(flat, terrain, act)
+    W = {k: torch.as_tensor(v, dtype=torch.float64) for k, v in act.items()}
+    worst = 0.0
+    for k in range(3):
+        a = synth.actions(k)
+        a_dev = a.cuda().contiguous()
+        port.actions = torch.clip(a, -flat["clip_actions"], flat["clip_actions"])
+        for s in range(flat["decimation"]):
+            ds = synth.dof_state(k, s)
+            eng.dof_state.copy_(ds.cuda())
+            port.dof_state.copy_(ds)
+            x64 = None
+            if flat["control_type"] == "actuator_net":
+                hist = [T.to_np(eng.state[q]).copy() for q in ("joint_pos_err_last", "joint_pos_err_last_last", "joint_vel_last",
+                                                               "joint_vel_last_last")]
+            want = port.compute_torques(port.actions)
+            got = eng.compute_torques(a_dev, flat["decimation"] * k + s)    # no post-physics step in between: the ring head advances with the sub-step index
+            torch.cuda.synchronize()
+            T.assert_close(f"step{k}.{s}/torques", T.to_np(got), want.numpy(), atol=T.TORQUE_ATOL)
+            T.assert_close(f"step{k}.{s}/joint_pos_target", T.to_np(eng.state["joint_pos_target"]), port.joint_pos_target.numpy())
+            for q in ("joint_pos_err_last", "joint_pos_err_last_last", "joint_vel_last", "joint_vel_last_last"):
+                T.assert_close(f"step{k}.{s}/{q}", T.to_np(eng.state[q]), getattr(port, q).numpy())
+            # float64 network on the exact fp32 inputs the kernel saw
+            x = np.stack([T.to_np(eng.state["joint_pos_err_last"]), hist[0], hist[1], T.to_np(eng.state["joint_vel_last"]), hist[2],
+                          hist[3]], -1).reshape(-1, 6)
+            x64 = torch.as_tensor(x, dtype=torch.float64)
+            ss = torch.nn.functional.softsign
+            y = ss(ss(x64 @ W["w0"].T + W["b0"]) @ W["w1"].T + W["b1"]) @ W["w2"].reshape(1, -1).T + W["b2"]
+            y = y.view(n_envs, 12) * eng.state["motor_strengths"].double().cpu()
+            lim = torch.as_tensor(flat["torque_limits"], dtype=torch.float64)
+            y = torch.minimum(torch.maximum(y, -lim), lim)
+            worst = max(worst, float((y - got.double().cpu()).abs().max()))
+    print(f"torque kernel vs float64 network, N={n_envs}: max abs err {worst:.3e}")
+    assert worst < 1e-5
