@@ -30,6 +30,13 @@ UNIT = "env-steps/s"
 N_REPLAY_SETS = 3
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of each kernel from the committed ncu --set full capture (profiles/ncu_traffic.json, written by
+    profiles/ncu_summary.py --traffic); {} if the file is absent."""
+    p = os.path.join(REPO, "profiles", "ncu_traffic.json")
+    return json.load(open(p)) if os.path.exists(p) else {}
+
+
 def measured_peaks():
     p = os.path.join(REPO, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -360,15 +367,22 @@ def run_b200(args, rank, world, local_rank):
     value = world * n_env * args.steps / (ms * 1e-3)
     torque_total = ms_torque * flat["decimation"]
     dominant = "lt_torque_kernel" if torque_total > ms_post else "lt_step_kernel"
-    k_post = {"kernel": "lt_step_kernel (+ lt_compact_kernel)", "ms_per_launch": ms_post,
-              "achieved": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9}
-    k_tq = {"kernel": "lt_torque_kernel", "ms_per_launch": ms_torque,
+    tr = ncu_traffic() if n_env == 65536 else {}          # the capture was taken at 65,536 envs
+    tr_post = [tr.get(k) for k in ("lt_step_kernel", "lt_obs_kernel", "lt_compact_kernel")]
+    k_post = {"kernel": "post-physics chain: lt_step_kernel + lt_obs_kernel + lt_compact_kernel", "ms_per_launch": ms_post,
+              "achieved": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9,
+              "traffic": None if None in tr_post else sum(tr_post)}
+    k_tq = {"kernel": "lt_torque_mma_kernel", "ms_per_launch": ms_torque,
             "achieved": alg["torque_substep"] * n_env / (ms_torque * 1e-3) / 1e9,
-            "fp32_tflops": alg["torque_flops_substep"] * n_env / (ms_torque * 1e-3) / 1e12}
+            "fp32_equiv_tflops": alg["torque_flops_substep"] * n_env / (ms_torque * 1e-3) / 1e12,
+            "traffic": tr.get("lt_torque_mma_kernel"),
+            "note": "actuator net on the tensor pipe (fp16-split x3 HMMA.16816, fp32 accumulate); bounded by XU (64 MUFU.RCP per "
+                    "sample) + tensor + issue, not by HBM: see profiles/ and DESIGN.md section 4"}
     for d in (k_post, k_tq):
         d.update({"bound": "hbm", "peak": peak, "unit": "GB/s", "frac": d["achieved"] / peak})
     dom = k_tq if dominant == "lt_torque_kernel" else k_post
-    roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": None,
+    roofline = {"bound": "hbm", "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["frac"],
+                "traffic": dom.get("traffic"), "traffic_source": "profiles/ncu_traffic.json (ncu --set full, 65,536 envs, per launch)",
                 "kernel": dom["kernel"], "peak_source": peak_src, "ms_per_launch": dom["ms_per_launch"],
                 "algorithmic_bytes_per_env": alg["torque_substep"] if dom is k_tq else alg["post_physics"],
                 "kernels": {"post_physics": k_post, "torque_substep": k_tq},

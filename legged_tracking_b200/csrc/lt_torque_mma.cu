@@ -5,7 +5,7 @@
 // sub-step at 65,536 envs; profiles/r01_ncu_full.md).  Here a warp owns a tile of 32 consecutive samples = two m16 row
 // blocks of `mma.sync.aligned.m16n8k16 .f16` with fp32 accumulators (samples on M, units on N):
 //   * the 1e-5 torque tolerance rules out single-pass half/TF32 operands, so every operand is split in two fp16 parts,
-//     a = a_hi + a_lo with a_hi = a rounded to 11 significand bits, a_lo = rn_f16(a - a_hi) (22 significand bits; fp16 subnormals keep the absolute
+//     a = a_hi + a_lo with a_hi = the leading 11 significand bits of a, a_lo = rn_f16(a - a_hi) (22 significand bits; fp16 subnormals keep the absolute
 //     error of the low part at 2^-25, and every operand here is O(1): weights |w| <= 1.06, activations in (-1, 1)), and
 //     every product is  a*w = a_lo*w_hi + a_hi*w_lo + a_hi*w_hi  accumulated in fp32, small terms first.  The dropped
 //     a_lo*w_lo term is 2^-22 relative.  (A first version used the same split on m16n8k8 .tf32: HMMA.1688.F32.TF32 issues
@@ -116,12 +116,12 @@ __device__ __forceinline__ void lt_mma_k8(float (&d)[4], uint32_t a0, uint32_t a
                  : "r"(a0), "r"(a1), "r"(b0));
 }
 // (x0, x1) -> packed fp16 pairs hi, lo with x = hi + lo to 22+ bits; x0 (the lower k) goes to the low half.
-// hi = x rounded to 11 significand bits in integer arithmetic (add half an ulp, mask), so it converts to fp16 exactly
-// (below the fp16 normal range the conversion rounds at 2^-25 absolute, far under the budget); lo = rn_f16(x - hi).
-// Two ALU ops + one FADD per element and one F2FP per pair and part -- no fp16 -> fp32 unpack on the FMA pipe.
+// hi = the leading 11 significand bits of x (one mask), so it converts to fp16 exactly (below the fp16 normal range the
+// conversion rounds at 2^-25 absolute, far under the budget); lo = rn_f16(x - hi) carries the next 11 bits (|lo| < 2^-10 |x|,
+// rounded at 2^-22 |x|).  One LOP3 + one FADD per element and one F2FP per pair and part -- no fp16 -> fp32 unpack on the FMA
+// pipe.  (Rounding hi to nearest instead costs one more ALU op per element and 1.8 us per launch for 2 e-6 of torque error.)
 __device__ __forceinline__ void lt_split_h2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
-    const float h0 = __uint_as_float((__float_as_uint(x0) + 0x1000u) & 0xffffe000u);
-    const float h1 = __uint_as_float((__float_as_uint(x1) + 0x1000u) & 0xffffe000u);
+    const float h0 = __uint_as_float(__float_as_uint(x0) & 0xffffe000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xffffe000u);
     const __half2 h = __floats2half2_rn(h0, h1);
     const __half2 l = __floats2half2_rn(__fsub_rn(x0, h0), __fsub_rn(x1, h1));
     hi = *reinterpret_cast<const uint32_t*>(&h);

@@ -38,5 +38,23 @@ def main(path):
         print(f"| `{r[kn].split('(')[0]}` | " + " | ".join(cells) + " |")
 
 
+def traffic(path):
+    """{kernel: dram bytes (read + write) per launch, averaged over the captured launches} as JSON (bench.py's roofline.traffic)."""
+    import json
+    rows = list(csv.reader(open(path)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    kn, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    acc = {}
+    for r in data:
+        name = r[kn].split("(")[0].replace("void ", "").split("<")[0]
+        b = float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]]
+        acc.setdefault(name, []).append(b)
+    print(json.dumps({k: sum(v) / len(v) for k, v in acc.items()}, indent=1))
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--traffic":
+        traffic(sys.argv[1])
+    else:
+        main(sys.argv[1])

@@ -147,4 +147,4 @@ def test_torque_kernel_ragged_tiles_and_float64_reference(n_envs):
             y = torch.minimum(torch.maximum(y, -lim), lim)
             worst = max(worst, float((y - got.double().cpu()).abs().max()))
     print(f"torque kernel vs float64 network, N={n_envs}: max abs err {worst:.3e}")
-    assert worst < 1e-5
+    assert worst < T.TORQUE_ATOL          # measured: 9e-6 on torques of up to 33.5 N m
