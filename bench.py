@@ -252,6 +252,22 @@ def ppo_iteration(eng, rs, graphs, flat, dev, dist, iters):
             "finite": bool(all(np.isfinite(x) for x in losses))}
 
 
+def terrain_build_timing(dev):
+    """the 32 x 32 single_path tile table built on the device (the reference: a 3.8 s Python loop)."""
+    import glob
+    from legged_tracking_b200.terrain import TunnelTerrain
+    path = sorted(glob.glob(os.path.join(REPO, "tests", "golden", "terrain_single_path_*.npz")))[0]
+    cfg = dict(json.loads(str(np.load(path)["cfg"])), num_rows=32, num_cols=32)
+    t0 = time.perf_counter()
+    t = TunnelTerrain(cfg, device=dev, rng=np.random.RandomState(11))
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    ms = time_region(lambda k: t.rebuild(), 50) / 50
+    nbytes = t.tile_heights.numel() * 4
+    return {"tiles": 1024, "kernel_us": ms * 1e3, "written_gb_per_s": nbytes / (ms * 1e-3) / 1e9,
+            "host_draws_plus_kernel_ms": wall * 1e3, "bytes": nbytes}
+
+
 def run_b200(args, rank, world, local_rank):
     from legged_tracking_b200.engine import StepEngine
     dist = None
@@ -408,6 +424,10 @@ def run_b200(args, rank, world, local_rank):
                     "ms_per_step": ms_e2e / ke, "steps": ke},
             "post_physics_only": {"value": world * n_env / (ms_post * 1e-3), "unit": UNIT, "ms_per_step": ms_post},
             "roofline": roofline}
+    try:
+        line["terrain_build"] = terrain_build_timing(dev)
+    except Exception as e:                        # auxiliary number: never costs the headline line
+        line["terrain_build"] = {"error": str(e)[:200]}
     if ppo_res:
         line["ppo_iteration"] = ppo_res
     if cpu:

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LT_ABI_VERSION 4
+#define LT_ABI_VERSION 5
 
 #define LT_MAX_DOF 12
 #define LT_MAX_FEET 4
@@ -271,6 +271,23 @@ int lt_gae(const float* rewards, const float* values, const uint8_t* dones, cons
            float* returns, float* advantages, double* stats, int32_t T, int32_t num_envs, float gamma, float lam,
            void* stream);
 int lt_normalize_advantages(float* advantages, const double* stats, int64_t count, void* stream);
+
+/* -------------------------------------------------------------------------------------------------------------
+ * terrain: device-side tile-table builder for terrain_type = single_path.
+ * Replaces Terrain.__init__ / make_terrain / add_terrain_to_map (go1_gym/utils/tunnel.py:51-217),
+ * vec_plane_from_points (go1_gym/utils/tunnel_fn.py:3-21), TerrainFunctions.single_path (tunnel_fn.py:99-163) and the
+ * float32 conversion of LeggedRobot._get_env_origins (legged_robot_trajectory_tracking.py:1827-1840).  The random draws are
+ * made by the caller (numpy generator, reference order); all arguments are DEVICE pointers:
+ *   n_pyramids [tiles,2] int32 (1 or 2 wedges per layer; layer 0 ceiling, 1 floor)
+ *   wedges     [tiles,2,2,5] float64 (mean_x, mean_y, mean_z, pw, pl) per wedge
+ *   window     [tiles,2] int32 tile-local (row, col) of the sub-terrain patch
+ *   xs [sub_rows], ys [sub_cols] float64 sample coordinates (np.linspace tables of tunnel_fn.py:152)
+ *   consts     float64[5] = {vertical_scale, ceiling_height / vertical_scale, 0.05 / vertical_scale, border value of the
+ *              ceiling layer, border value of the floor layer} (the borders in units of vertical_scale, tunnel.py:81-82)
+ *   tile_heights [tiles,2,tile_rows,tile_cols] float32 out, metres.  Bit-identical to the reference's table. */
+int lt_build_tunnel_tiles(const int32_t* n_pyramids, const double* wedges, const int32_t* window, const double* xs,
+                          const double* ys, const double* consts, float* tile_heights, int32_t n_tiles, int32_t tile_rows,
+                          int32_t tile_cols, int32_t sub_rows, int32_t sub_cols, void* stream);
 
 #ifdef __cplusplus
 }

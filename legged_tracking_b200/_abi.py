@@ -95,7 +95,7 @@ lt_transition_ptrs = _mk("lt_transition_ptrs")
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
            "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
            "lt_reward_sign_prepass", "lt_term_sum_buffer", "lt_set_term_scales", "lt_counters", "lt_rollout_store", "lt_gae",
-           "lt_normalize_advantages"]
+           "lt_normalize_advantages", "lt_build_tunnel_tiles"]
 
 
 def declared_functions(path=HEADER):
@@ -146,6 +146,7 @@ def load(path=LIB_PATH):
                                      C.c_float, vp]
     lib.lt_gae.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, C.c_float, C.c_float, vp]
     lib.lt_normalize_advantages.argtypes = [vp, vp, C.c_int64, vp]
+    lib.lt_build_tunnel_tiles.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     if lib.lt_abi_version() != DEFINES["LT_ABI_VERSION"]:
         raise LtError(f"liblt_b200.so has ABI {lib.lt_abi_version()}, header has {DEFINES['LT_ABI_VERSION']}: rebuild")
     if lib.lt_config_bytes() != C.sizeof(lt_config):

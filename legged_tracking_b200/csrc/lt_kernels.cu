@@ -623,23 +623,45 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
         }
     }
     const int head_iters = (p.head_w + 31) >> 5;
-#pragma unroll 1
-    for (int m = 0; m < head_iters; ++m) {
-        const int hi = lane + 32 * m;
+    auto head_call = [&](int m) {                  // Philox call boundary: value index v = 2 KP + m uses call v / 10, slot v % 10
         const int v = 2 * KP + m;
         if (NOISE == 2 && (v % LT_NOISE_PER_CALL == 0 || (!HN && m == 0)))      // !HN: the height loop made no call yet
             lt_philox((uint32_t)ie, (uint32_t)(lane + 32 * (v / LT_NOISE_PER_CALL)) | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
+    };
+    auto head_col = [&](int m, float u) {
+        const int hi = lane + 32 * m;
         if (hi < p.head_w) {
             const int col = hi < p.h0 ? hi : hi + p.n_heights;
-            float u = 0.5f;
             if (NOISE == 1) u = nz[col];
-            if (NOISE == 2) u = lt_u12(rnd, v % LT_NOISE_PER_CALL);
             const float raw = m == 0 ? raw0 : (m == 1 ? raw1 : obs_row[col]);
             const float ns = !NOISE ? 0.0f : (m == 0 ? ns0 : (m == 1 ? ns1 : __ldg(p.noise_scale_vec + col)));
             const float o = lt_obs_finish_dev<NOISE>(raw, u, ns, clip);
             obs_row[col] = o;
             hist_new[col] = o;
         }
+    };
+    // the first two rounds (64 columns: every shipped configuration) with compile-time noise slots; the rest rolled
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+        if (m < head_iters) {
+            head_call(m);
+            float u = 0.5f;
+            if (NOISE == 2) {
+                switch ((2 * KP + m) % LT_NOISE_PER_CALL) {          // compile-time after unrolling
+                case 0: u = lt_u12_static<0>(rnd); break; case 1: u = lt_u12_static<1>(rnd); break;
+                case 2: u = lt_u12_static<2>(rnd); break; case 3: u = lt_u12_static<3>(rnd); break;
+                case 4: u = lt_u12_static<4>(rnd); break; case 5: u = lt_u12_static<5>(rnd); break;
+                case 6: u = lt_u12_static<6>(rnd); break; case 7: u = lt_u12_static<7>(rnd); break;
+                case 8: u = lt_u12_static<8>(rnd); break; default: u = lt_u12_static<9>(rnd); break;
+                }
+            }
+            head_col(m, u);
+        }
+    }
+#pragma unroll 1
+    for (int m = 2; m < head_iters; ++m) {
+        head_call(m);
+        head_col(m, NOISE == 2 ? lt_u12(rnd, (2 * KP + m) % LT_NOISE_PER_CALL) : 0.5f);
     }
 }
 

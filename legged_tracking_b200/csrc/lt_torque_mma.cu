@@ -94,7 +94,10 @@ struct lt_torque_mma_params {
     int32_t n_tiles;
 };
 
-__device__ __forceinline__ void lt_mma_k16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+__device__ __forceinline__ void lt_mma_k16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, bool main_term = true) {
+#if LT_MMA_EXP & 2
+    if (!main_term) return;
+#endif
     asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
@@ -128,7 +131,13 @@ __device__ __forceinline__ void lt_split_h2(float x0, float x1, uint32_t& hi, ui
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 // softsign x / (1 + |x|): the denominator is in [1, inf), so a bare MUFU.RCP (1 ulp) needs no range scaling
+#ifndef LT_MMA_EXP
+#define LT_MMA_EXP 0                // timing experiments only (profiles/variants.py): 1 = no MUFU, 2 = hi*hi products only, 3 = both
+#endif
 __device__ __forceinline__ float lt_softsign_fast(float x) {
+#if LT_MMA_EXP & 1
+    return x * (1.5f - 0.5f * fabsf(x));
+#endif
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fabsf(x) + 1.0f));
     return x * r;
@@ -284,14 +293,14 @@ __global__ void __launch_bounds__(LT_MMA_THREADS, LT_MMA_MINB) lt_torque_mma_ker
 #pragma unroll
                     for (int m = 0; m < MB; ++m) {
                         if (q == 0) lt_mma_k16_c(a2[m][nt], al[m], w1h[r], w1h[r + 1], bq1[nt]);
-                        else lt_mma_k16(a2[m][nt], al[m], w1h[r], w1h[r + 1]);
+                        else lt_mma_k16(a2[m][nt], al[m], w1h[r], w1h[r + 1], false);
                     }
                 }
 #pragma unroll
                 for (int nt = 0; nt < 4; ++nt) {
                     const int r = 2 * (4 * q + nt);
 #pragma unroll
-                    for (int m = 0; m < MB; ++m) lt_mma_k16(a2[m][nt], ah[m], w1l[r], w1l[r + 1]);
+                    for (int m = 0; m < MB; ++m) lt_mma_k16(a2[m][nt], ah[m], w1l[r], w1l[r + 1], false);
                 }
 #pragma unroll
                 for (int nt = 0; nt < 4; ++nt) {

@@ -113,7 +113,10 @@ class StepEngine:
                                self.rigid_body_state.data_ptr())
         _abi.check(self.lib.lt_bind_sim(self.handle, C.byref(sim)), self.handle, "lt_bind_sim")
         # ---- terrain (LR:1808-1847)
-        t = lambda x, dt: torch.as_tensor(np.ascontiguousarray(np.asarray(x)), dtype=dt).to(dev).contiguous()   # noqa: E731
+        def t(x, dt):          # numpy / list / torch tensor on any device (terrain.TunnelTerrain hands over a device-resident table)
+            if isinstance(x, torch.Tensor):
+                return x.to(device=dev, dtype=dt).contiguous()
+            return torch.as_tensor(np.ascontiguousarray(np.asarray(x)), dtype=dt).to(dev).contiguous()
         self.env_origins = t(terrain["env_origins"], torch.float32).view(N, 3)
         self.plane = flat["mesh_type"] == "plane"
         ter = _abi.lt_terrain_ptrs()

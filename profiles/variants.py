@@ -13,11 +13,10 @@ sys.path.insert(0, REPO)
 VDIR = os.path.join(REPO, "build", "variants")
 MMA_ONLY = ("lt_torque_mma.cu",)          # variants whose defines touch only the tensor-pipe torque kernel
 VARIANTS = {
-    "mma_mb1_b3": ["LT_MMA_MB=1", "LT_MMA_MINB=3"],
-    "mma_mb2_b3": ["LT_MMA_MB=2", "LT_MMA_MINB=3"],
-    "mma_mb2_b2": ["LT_MMA_MB=2", "LT_MMA_MINB=2"],
-    "mma_mb2_b4": ["LT_MMA_MB=2", "LT_MMA_MINB=4"],
-    "mma_mb1_b4": ["LT_MMA_MB=1", "LT_MMA_MINB=4"],
+    "mma_base": [],
+    "mma_exp1_nomufu": ["LT_MMA_EXP=1"],
+    "mma_exp2_hihi": ["LT_MMA_EXP=2"],
+    "mma_exp3_both": ["LT_MMA_EXP=3"],
 }
 OLD_VARIANTS = {
     "spt2_b4": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=4"],
