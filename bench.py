@@ -17,6 +17,9 @@ import sys
 import threading
 import time
 
+# rank 0 prints exactly ONE line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION in this image) off it
+os.environ["NCCL_DEBUG"] = os.environ.get("LT_NCCL_DEBUG", "WARN")
+
 import numpy as np
 import torch
 
@@ -28,6 +31,26 @@ from legged_tracking_b200 import workload  # noqa: E402
 METRIC = "env_steps_per_s"
 UNIT = "env-steps/s"
 N_REPLAY_SETS = 3
+
+
+_STDOUT_FD = None
+
+
+def _quiet_stdout():
+    """Libraries (NCCL's version banner, torch's C++ logging) write to fd 1; the contract is ONE JSON line on stdout.  Point fd 1
+    at stderr for the duration of the run and keep the real stdout for _emit."""
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(text):
+    sys.stdout.flush()
+    if _STDOUT_FD is None:
+        print(text, flush=True)
+    else:
+        os.write(_STDOUT_FD, (text + "\n").encode())
 
 
 def ncu_traffic():
@@ -196,7 +219,7 @@ def run_reference(args, rank):
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{n_envs} envs x {max(1, min(args.steps, 20))} steps, oracle/port.py with the reference's per-env height gather"},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(json.dumps(line))
 
 
 def ppo_iteration(eng, rs, graphs, flat, dev, dist, iters):
@@ -432,7 +455,7 @@ def run_b200(args, rank, world, local_rank):
         line["ppo_iteration"] = ppo_res
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    _emit(json.dumps(line))
 
 
 def main():
@@ -454,12 +477,15 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    _quiet_stdout()
     if args.impl == "reference":
         run_reference(args, rank)
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU baseline")
     run_b200(args, rank, world, local_rank)
+    if world > 1 and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":
