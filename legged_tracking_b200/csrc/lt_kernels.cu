@@ -366,6 +366,8 @@ __device__ __forceinline__ void lt_store_row12(float* g, const float* r) {
 template <int EPW>
 __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_constant__ lt_step_params p) {
     extern __shared__ __align__(16) float smem[];
+    lt_pdl_launch_dependents();
+    lt_pdl_wait();                                 // everything below reads what the torque kernels / PhysX wrote
     const lt_config& c = p.c;
     const lt_layout& L = p.L;
     const lt_state_ptrs& st = p.st;
@@ -540,6 +542,8 @@ __device__ __forceinline__ float lt_u12_static(const uint32_t (&rnd)[4]) {      
 // (LR:1125-1131), and v + (2u-1)*0 == v, so the usual instantiation skips noise for the 220 height columns altogether.
 template <int KP, int NOISE, int CAM, int HN>
 __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_constant__ lt_obs_params p) {
+    lt_pdl_launch_dependents();
+    lt_pdl_wait();                                 // the record and the head columns come from lt_step_kernel
     const int lane = threadIdx.x & 31;
     const int ie = blockIdx.x * (LT_OBS_THREADS / 32) + (threadIdx.x >> 5);
     if (ie >= p.num_envs) return;
@@ -674,6 +678,8 @@ __global__ void __launch_bounds__(LT_COMPACT_THREADS) lt_compact_kernel(const ui
                                                                         int32_t* __restrict__ counters, int n, int send_timeouts,
                                                                         int n_substeps, int lag_slots) {
     __shared__ int s_base[32], s_total[32], s_warp[32];
+    lt_pdl_launch_dependents();
+    lt_pdl_wait();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int start = blockIdx.x * LT_COMPACT_THREADS;
     int base = 0, total = 0;
@@ -823,19 +829,17 @@ static cudaError_t lt_launch_step(const lt_step_params& p, cudaStream_t stream) 
         configured = smem;
     }
     const int tiles = (p.c.num_envs + EPW - 1) / EPW;
-    lt_step_kernel<EPW><<<(tiles + WARPS - 1) / WARPS, LT_STEP_THREADS, smem, stream>>>(p);
-    return cudaGetLastError();
+    return lt_launch_chain(lt_step_kernel<EPW>, (unsigned)((tiles + WARPS - 1) / WARPS), LT_STEP_THREADS, smem, stream, p);
 }
 template <int KP, int CAM>
 static cudaError_t lt_launch_obs_cam(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
     const unsigned grid = (unsigned)((p.num_envs + LT_OBS_THREADS / 32 - 1) / (LT_OBS_THREADS / 32));
     const bool hn = p.height_noise != 0;
-    if (noise_mode == 0) lt_obs_kernel<KP, 0, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else if (noise_mode == 1 && hn) lt_obs_kernel<KP, 1, CAM, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else if (noise_mode == 1) lt_obs_kernel<KP, 1, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else if (hn) lt_obs_kernel<KP, 2, CAM, 1><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    else lt_obs_kernel<KP, 2, CAM, 0><<<grid, LT_OBS_THREADS, 0, stream>>>(p);
-    return cudaGetLastError();
+    if (noise_mode == 0) return lt_launch_chain(lt_obs_kernel<KP, 0, CAM, 0>, grid, LT_OBS_THREADS, 0, stream, p);
+    else if (noise_mode == 1 && hn) return lt_launch_chain(lt_obs_kernel<KP, 1, CAM, 1>, grid, LT_OBS_THREADS, 0, stream, p);
+    else if (noise_mode == 1) return lt_launch_chain(lt_obs_kernel<KP, 1, CAM, 0>, grid, LT_OBS_THREADS, 0, stream, p);
+    else if (hn) return lt_launch_chain(lt_obs_kernel<KP, 2, CAM, 1>, grid, LT_OBS_THREADS, 0, stream, p);
+    else return lt_launch_chain(lt_obs_kernel<KP, 2, CAM, 0>, grid, LT_OBS_THREADS, 0, stream, p);
 }
 template <int KP>
 static cudaError_t lt_launch_obs(const lt_obs_params& p, int noise_mode, cudaStream_t stream) {
@@ -929,7 +933,7 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
     int epw = cfg->envs_per_warp;
     if (epw == 0) {
         const int per_sm = (cfg->num_envs + prop.multiProcessorCount - 1) / prop.multiProcessorCount;
-        epw = per_sm >= 32 ? 32 : 8;
+        epw = per_sm >= 256 ? 32 : 8;      // measured (B200): 8 wins at 8,192 and 16,384 envs, 32 at 65,536
     }
     h->epw = epw;
     h->height_noise = 0;
@@ -1170,10 +1174,9 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream) {
         if (e != cudaSuccess) return lt_fail(h, LT_ERR_CUDA, std::string("lt_obs_kernel: ") + cudaGetErrorString(e));
     }
     const int n = h->c.num_envs;
-    lt_compact_kernel<<<(n + LT_COMPACT_THREADS - 1) / LT_COMPACT_THREADS, LT_COMPACT_THREADS, 0, (cudaStream_t)stream>>>(
-        h->st.reset_buf, h->st.time_out_buf, h->st.time_outs_latched, h->st.reset_env_ids, h->st.reset_count, h->d_counters, n,
-        h->c.send_timeouts, h->substeps_pending, h->L.lag_slots);
-    LT_CUDA(h, cudaGetLastError());
+    LT_CUDA(h, lt_launch_chain(lt_compact_kernel, (unsigned)((n + LT_COMPACT_THREADS - 1) / LT_COMPACT_THREADS), LT_COMPACT_THREADS, 0,
+                               (cudaStream_t)stream, h->st.reset_buf, h->st.time_out_buf, h->st.time_outs_latched, h->st.reset_env_ids,
+                               h->st.reset_count, h->d_counters, n, h->c.send_timeouts, h->substeps_pending, h->L.lag_slots));
     h->substeps_pending = 0;
     return LT_OK;
 }

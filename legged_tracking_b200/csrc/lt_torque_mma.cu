@@ -189,7 +189,8 @@ __global__ void __launch_bounds__(LT_MMA_THREADS, LT_MMA_MINB) lt_torque_mma_ker
         const size_t s = (size_t)tile * 32 + lane;
         lt_torque_fetch(p, s < n ? s : n - 1, n, rd_fetch, cur);
     }
-    // weight fragments: one coalesced pass over the [regs][32] table (L2-resident, 7 KB)
+    // weight fragments: one coalesced pass over the [regs][32] table (L2-resident, 7 KB).  (Programmatic dependent launch was
+    // tried here -- fragments before griddepcontrol.wait -- and cost 0.6 us per launch; the post-physics kernels keep it.)
     uint32_t w0h[4], w0l[4], w1h[16], w1l[16];
     float bq1[4][4], w2[8];
 #pragma unroll
@@ -207,6 +208,7 @@ __global__ void __launch_bounds__(LT_MMA_THREADS, LT_MMA_MINB) lt_torque_mma_ker
         w1l[r] = __ldg(p.frag + (FR_W1_LO + r) * 32 + lane);
     }
     const float b2 = __uint_as_float(__ldg(p.frag + FR_B2 * 32 + lane));
+
 
     for (; tile < p.n_tiles; tile += n_warps) {
         const size_t s_raw = (size_t)tile * 32 + lane;

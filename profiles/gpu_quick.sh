@@ -1,4 +1,9 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_terrain.py -m gpu -x -q > gpurun_out/t_terrain.log 2>&1; echo "rc=$?" >> gpurun_out/t_terrain.log
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
-timeout 600 python bench.py --no-ppo --no-cpu --steps 500 > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err
+: > gpurun_out/pdl.log
+for pdl in 1 0; do for n in 8192 65536; do
+  LT_PDL=$pdl timeout 300 python bench.py --no-ppo --no-cpu --steps 1000 --envs-per-gpu $n 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('pdl',$pdl,$n,round(d['value']/1e6,1),'M/s step_us',round(d['ms_per_step']*1e3,1),'post_us',round(d['post_physics_only']['ms_per_step']*1e3,1),'e2e',round(d['e2e']['value']/1e6,2))" >> gpurun_out/pdl.log
+done; done
+LT_PDL=1 timeout 300 python bench.py --no-ppo --no-cpu --steps 1000 --envs-per-gpu 32768 --epw 32 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('pdl 1 epw32 32768',round(d['value']/1e6,1),'M/s step_us',round(d['ms_per_step']*1e3,1))" >> gpurun_out/pdl.log
