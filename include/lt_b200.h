@@ -240,7 +240,8 @@ float* lt_term_sum_buffer(lt_handle* h);
  * captured earlier keeps the scales it was captured with. */
 int lt_set_term_scales(lt_handle* h, const float* scales, int32_t n);
 
-/* Device int32[4]: {policy steps done, physics sub-steps done (= pushes into the lag FIFO), lag ring head, 0}.
+/* Device int32[4]: {policy steps done, physics sub-steps done (= pushes into the lag FIFO), lag ring head, value of [0] the
+ * last lt_post_physics_step started with}.
  * Logical lag slot j of LR:972-974 lives in physical slot (head + j) % (lag_timesteps + 1). */
 int32_t* lt_counters(lt_handle* h);
 

@@ -93,7 +93,10 @@ struct lt_handle {
     int32_t* d_counters;
     uint8_t* d_scratch;
     uint32_t* d_ptlut;
-    float* d_act_frag;               // [LT_MMA_FRAG_REGS, 32] pre-split TF32 weight fragments of the actuator net
+    float* d_act_frag;               // [LT_MMA_FRAG_REGS, 32] pre-split fp16 weight fragments of the actuator net
+    cudaStream_t side;               // lt_compact_kernel runs here, beside lt_obs_kernel (both depend only on lt_step_kernel)
+    cudaEvent_t ev_fork, ev_join;
+    bool fork_compact;
     int sm_count;
     int32_t rec_bytes;
     int32_t substeps_pending;        // lt_compute_torques calls since the last lt_post_physics_step
@@ -488,6 +491,8 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
         R.iy = rec + L.nxf;
         lt_step_scalars sc = p.sc;
         sc.step = (uint32_t)p.counters[0];
+        // lt_obs_kernel runs beside lt_compact_kernel, which advances counters[0]: leave it this step's value in counters[3]
+        if (tile == 0 && lane == 0) const_cast<int32_t*>(p.counters)[3] = (int32_t)sc.step;
         const lt_env_result r = lt_env_step(c, L, st, p.ter, p.args, sc, i, R);
         my_reset = r.reset;
         *reinterpret_cast<float2*>(rec + rec_bytes - 8) = make_float2(r.z_post, r.cam_z);
@@ -549,7 +554,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
     if (ie >= p.num_envs) return;
     const int no = p.num_obs, H = p.obs_history_length, per_layer = p.per_layer;
     const float clip = p.clip_observations, hscale = p.obs_scale_height, ceil_h = p.ceiling_height;
-    const uint32_t step = NOISE == 2 ? (uint32_t)p.counters[0] : 0u;
+    const uint32_t step = NOISE == 2 ? (uint32_t)p.counters[3] : 0u;        // = counters[0] as lt_step_kernel saw it
     const uint8_t* rec = p.scratch + (size_t)ie * p.rec_bytes;
     // the env's packed record (cell-index bytes, then (z_post, cam_z)) in ONE coalesced load: lane l holds word l; a
     // point's row / column byte is fetched from the owning lane by shuffle instead of a dependent byte load
@@ -964,6 +969,13 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
         if (e == cudaSuccess) e = cudaMemcpy(h->d_act_frag, fr.data(), fr.size(), cudaMemcpyHostToDevice);
     }
     h->sm_count = prop.multiProcessorCount;
+    {
+        const char* f = getenv("LT_FORK_COMPACT");
+        h->fork_compact = !(f && f[0] == '0');
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+    }
     if (e != cudaSuccess) {
         const std::string msg = std::string("lt_create: ") + cudaGetErrorString(e);
         delete h;
@@ -981,6 +993,9 @@ void lt_destroy(lt_handle* h) {
     cudaFree(h->d_scratch);
     cudaFree(h->d_ptlut);
     cudaFree(h->d_act_frag);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->side) cudaStreamDestroy(h->side);
     delete h;
 }
 
@@ -1157,6 +1172,19 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream) {
     default: e = lt_launch_step<32>(p, (cudaStream_t)stream); break;
     }
     if (e != cudaSuccess) return lt_fail(h, LT_ERR_CUDA, std::string("lt_step_kernel: ") + cudaGetErrorString(e));
+    // ordered reset compaction + counters: needs only lt_step_kernel's masks, so it is forked onto the handle's side stream and
+    // joins after lt_obs_kernel (under stream capture the side stream becomes a parallel branch of the graph)
+    const int n = h->c.num_envs;
+    cudaStream_t cs = (cudaStream_t)stream;
+    if (h->fork_compact) {
+        LT_CUDA(h, cudaEventRecord(h->ev_fork, (cudaStream_t)stream));
+        LT_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+        cs = h->side;
+    }
+    LT_CUDA(h, lt_launch_chain(lt_compact_kernel, (unsigned)((n + LT_COMPACT_THREADS - 1) / LT_COMPACT_THREADS), LT_COMPACT_THREADS, 0,
+                               cs, h->st.reset_buf, h->st.time_out_buf, h->st.time_outs_latched, h->st.reset_env_ids,
+                               h->st.reset_count, h->d_counters, n, h->c.send_timeouts, h->substeps_pending, h->L.lag_slots));
+    if (h->fork_compact) LT_CUDA(h, cudaEventRecord(h->ev_join, h->side));
     {
         const lt_config& c = h->c;
         lt_obs_params o;
@@ -1173,10 +1201,7 @@ int lt_post_physics_step(lt_handle* h, const lt_step_args* args, void* stream) {
         e = o.per_layer <= 128 ? lt_launch_obs<4>(o, mode, (cudaStream_t)stream) : lt_launch_obs<8>(o, mode, (cudaStream_t)stream);
         if (e != cudaSuccess) return lt_fail(h, LT_ERR_CUDA, std::string("lt_obs_kernel: ") + cudaGetErrorString(e));
     }
-    const int n = h->c.num_envs;
-    LT_CUDA(h, lt_launch_chain(lt_compact_kernel, (unsigned)((n + LT_COMPACT_THREADS - 1) / LT_COMPACT_THREADS), LT_COMPACT_THREADS, 0,
-                               (cudaStream_t)stream, h->st.reset_buf, h->st.time_out_buf, h->st.time_outs_latched, h->st.reset_env_ids,
-                               h->st.reset_count, h->d_counters, n, h->c.send_timeouts, h->substeps_pending, h->L.lag_slots));
+    if (h->fork_compact) LT_CUDA(h, cudaStreamWaitEvent((cudaStream_t)stream, h->ev_join, 0));
     h->substeps_pending = 0;
     return LT_OK;
 }
