@@ -583,7 +583,9 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
             const int bx = (int)(w & 0xffu), by = p.nxf + (int)(w >> 8);           // byte positions in the record
             const uint32_t wx = __shfl_sync(0xffffffffu, rec_w, bx >> 2), wy = __shfl_sync(0xffffffffu, rec_w, by >> 2);
             if (tile_base && on) {
-                const int off = (int)((wx >> (8 * (bx & 3))) & 0xffu) * p.tile_cols + (int)((wy >> (8 * (by & 3))) & 0xffu);
+                // one PRMT per byte: selector 0x444s puts byte s of the word in the low byte and zeros (byte 4 of {word, 0}) above it
+                const int off = (int)__byte_perm(wx, 0u, 0x4440u | (uint32_t)(bx & 3)) * p.tile_cols +
+                                (int)__byte_perm(wy, 0u, 0x4440u | (uint32_t)(by & 3));
                 hc[k] = __ldg(tile_base + off);
                 hf[k] = __ldg(tile_base + p.tile_cells + off);
             }
@@ -599,6 +601,9 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
     // per-lane base pointers: column h0 + lane (ceiling layer) and h0 + per_layer + lane (floor layer)
     float* hist_new = hist_row + (size_t)(H - 1) * no;
     const int c0 = p.h0 + lane, c1 = c0 + per_layer;
+    // four per-lane row pointers, so that every store below is base + compile-time offset (no 64-bit address math per store)
+    float* const po[2] = {obs_row + c0, obs_row + c1};
+    float* const ph[2] = {hist_new + c0, hist_new + c1};
     const float* nz = NOISE == 1 ? p.noise_uniforms + (size_t)ie * no : nullptr;
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
@@ -626,8 +631,8 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
                     }
                 }
                 const float o = lt_obs_finish_dev<(HN ? NOISE : 0)>(h, u, (HN && NOISE) ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
-                obs_row[col] = o;
-                hist_new[col] = o;
+                po[layer][32 * k] = o;
+                ph[layer][32 * k] = o;
             }
         }
     }
