@@ -55,41 +55,60 @@ __global__ void __launch_bounds__(LT_TER_THREADS) lt_tunnel_tiles_kernel(const i
     __syncthreads();
     const double vs = consts[0], ceil_over_vs = consts[1], min_top = consts[2];
     const double border = layer == 0 ? consts[3] : consts[4];
+    const float border_f = __double2float_rn(__dmul_rn(border, vs));
     const int r0 = window[2 * (tl >> 1)], c0 = window[2 * (tl >> 1) + 1];
     float* o = out + (size_t)tl * tile_rows * tile_cols;
-    const int cells = tile_rows * tile_cols;
-    for (int k = threadIdx.x; k < cells; k += LT_TER_THREADS) {
-        const int r = k / tile_cols, cc = k - r * tile_cols;
-        const int u = r - r0, v = cc - c0;                      // u: along the tunnel (py of the sub-terrain), v: across (px)
-        double val = border;
-        if (u >= 0 && u < sub_rows && v >= 0 && v < sub_cols) {
-            double h;
-            if (layer == 1 && (u == 0 || u == sub_rows - 1 || v == 0 || v == sub_cols - 1)) {
-                h = 0.5;                                         // tunnel_fn.py:155-159: the floor patch is walled in
-            } else {
-                const double x = xs[u], y = ys[v];
-                h = 0.0;
-                for (int q = 0; q < np; ++q) {
-                    double m = __longlong_as_double(0x7ff0000000000000ll);
+    // one cell of the patch: u along the tunnel (py of the sub-terrain), v across (px)
+    auto cell = [&](int u, int v) -> float {
+        double h;
+        if (layer == 1 && (u == 0 || u == sub_rows - 1 || v == 0 || v == sub_cols - 1)) {
+            h = 0.5;                                             // tunnel_fn.py:155-159: the floor patch is walled in
+        } else {
+            const double x = xs[u], y = ys[v];
+            h = 0.0;
+            for (int q = 0; q < np; ++q) {
+                double m = __longlong_as_double(0x7ff0000000000000ll);
 #pragma unroll
-                    for (int f = 0; f < 4; ++f) {
-                        const lt_plane P = s_plane[q][f];
-                        double t = __dsub_rn(__dsub_rn(P.dc, __dmul_rn(P.ac, x)), __dmul_rn(P.bc, y));
-                        t = t < 0.0 ? 0.0 : t;                   // np.clip(., 0, inf)
-                        m = t < m ? t : m;
-                    }
-                    h = (q == 0 || m > h) ? m : h;
+                for (int f = 0; f < 4; ++f) {
+                    const lt_plane P = s_plane[q][f];
+                    double t = __dsub_rn(__dsub_rn(P.dc, __dmul_rn(P.ac, x)), __dmul_rn(P.bc, y));
+                    t = t < 0.0 ? 0.0 : t;                       // np.clip(., 0, inf)
+                    m = t < m ? t : m;
                 }
-            }
-            const double hi = (double)(long long)__ddiv_rn(h, vs);            // (h / vertical_scale).astype(int)
-            if (layer == 0) {
-                const double t = __dsub_rn(ceil_over_vs, hi);                 // tunnel.py:95: flip at the ceiling
-                val = t < min_top ? min_top : t;                              // tunnel.py:97: keep 0.05 m of clearance
-            } else {
-                val = hi;
+                h = (q == 0 || m > h) ? m : h;
             }
         }
-        o[k] = __double2float_rn(__dmul_rn(val, vs));                         // LR:1838-1840
+        const double hi = (double)(long long)__ddiv_rn(h, vs);                // (h / vertical_scale).astype(int)
+        double val = hi;
+        if (layer == 0) {
+            const double t = __dsub_rn(ceil_over_vs, hi);                     // tunnel.py:95: flip at the ceiling
+            val = t < min_top ? min_top : t;                                  // tunnel.py:97: keep 0.05 m of clearance
+        }
+        return __double2float_rn(__dmul_rn(val, vs));                         // LR:1838-1840
+    };
+    if ((tile_cols & 3) == 0) {
+        // 16-byte stores: a thread owns chunks of 4 consecutive cells of a row; three quarters of a tile are border constants
+        const int cols4 = tile_cols >> 2, chunks = tile_rows * cols4;
+        float4* o4 = reinterpret_cast<float4*>(o);
+        for (int q = threadIdx.x; q < chunks; q += LT_TER_THREADS) {
+            const int r = q / cols4, cc = (q - r * cols4) << 2;
+            const int u = r - r0, v = cc - c0;
+            float e[4] = {border_f, border_f, border_f, border_f};
+            if (u >= 0 && u < sub_rows && v + 3 >= 0 && v < sub_cols) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (v + k >= 0 && v + k < sub_cols) e[k] = cell(u, v + k);
+            }
+            const float4 w = make_float4(e[0], e[1], e[2], e[3]);
+            o4[q] = w;
+        }
+    } else {
+        const int cells = tile_rows * tile_cols;
+        for (int k = threadIdx.x; k < cells; k += LT_TER_THREADS) {
+            const int r = k / tile_cols, cc = k - r * tile_cols;
+            const int u = r - r0, v = cc - c0;
+            o[k] = (u >= 0 && u < sub_rows && v >= 0 && v < sub_cols) ? cell(u, v) : border_f;
+        }
     }
 }
 
