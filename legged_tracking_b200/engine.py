@@ -318,3 +318,57 @@ class StepEngine:
                 out["command_sums/" + name] = self.state["command_sums"][r].cpu()
         out["common_step_counter"] = torch.tensor(self.gravity.common_step_counter)
         return out
+
+
+class HostStepPipeline:
+    """The step for callers whose simulator state lives in HOST memory (the reference-facing path bench.py reports as `e2e`).
+
+    One policy step moves ~0.75 KB per env up (actions, 4 x dof_state, root_states, contact forces) and ~1.05 KB per env down
+    (obs, privileged obs, reward, done), so with a single engine the step is three serial phases -- H2D, kernels, D2H -- and the
+    PCIe link idles in one direction at any time.  Envs are independent, so the batch is cut into
+    `n_chunks` contiguous env shards, each with its own StepEngine on its own CUDA stream: while shard k's results go down,
+    shard k+1's inputs come up and shard k+2's kernels run.  Results are identical to n_chunks independent engines (the same
+    sharding rule as across GPUs: shard sizes must keep env -> tile = i mod tiles, i.e. be multiples of rows * cols).
+
+    host_in (pinned, per shard k):  actions [M,12], dof [decimation][M*12,2], root [M*A,13], contact [M,B,3]
+    host_out (pinned, per shard k): obs [M,num_obs], priv [M,num_priv], rew [M], done [M] bool
+    """
+
+    def __init__(self, engines):
+        self.engines = list(engines)
+        dev = self.engines[0].device
+        self.streams = [torch.cuda.Stream(device=dev) for _ in self.engines]
+        self.dev_in = []
+        for e in self.engines:
+            f = e.flat
+            own = {"actions": torch.empty(e.N, 12, device=dev), "dof": torch.empty(e.N * 12, 2, device=dev),
+                   "root": torch.empty(e.N * f["num_actors"], 13, device=dev),
+                   "contact": torch.empty(e.N, f["num_bodies"], 3, device=dev)}
+            e.bind_sim(root_states=own["root"], dof_state=own["dof"], contact_forces=own["contact"])
+            self.dev_in.append(own)
+
+    @property
+    def num_envs(self):
+        return sum(e.N for e in self.engines)
+
+    def step(self, host_in, host_out):
+        """Issue every shard's copies and kernels on its stream, then wait for all of them (the caller needs obs / rew / done
+        of every env before it can act again)."""
+        cur = torch.cuda.current_stream()
+        for s in self.streams:
+            s.wait_stream(cur)
+        for e, s, own, hi, ho in zip(self.engines, self.streams, self.dev_in, host_in, host_out):
+            with torch.cuda.stream(s):
+                own["actions"].copy_(hi["actions"], non_blocking=True)
+                for sub, dof in enumerate(hi["dof"]):
+                    own["dof"].copy_(dof, non_blocking=True)          # what PhysX hands back after sub-step `sub`
+                    e.compute_torques(own["actions"], sub)
+                own["root"].copy_(hi["root"], non_blocking=True)
+                own["contact"].copy_(hi["contact"], non_blocking=True)
+                e.post_physics_step()
+                ho["obs"].copy_(e.state["obs_buf"], non_blocking=True)
+                ho["priv"].copy_(e.state["privileged_obs_buf"], non_blocking=True)
+                ho["rew"].copy_(e.state["rew_buf"], non_blocking=True)
+                ho["done"].copy_(e.state["reset_buf"], non_blocking=True)
+        for s in self.streams:
+            s.synchronize()

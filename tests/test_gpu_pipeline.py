@@ -1,0 +1,52 @@
+"""-m gpu: engine.HostStepPipeline (env shards on separate CUDA streams, host buffers in / out) returns exactly what the same
+shards give when stepped one after the other on the default stream."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _shard(seed, n):
+    from legged_tracking_b200 import workload
+    from legged_tracking_b200.engine import StepEngine
+    flat, terrain, act, synth = workload.make("cfg2", num_envs=n, seed=seed, tile_grid=(4, 4))
+    eng = StepEngine(flat, terrain, act, device="cuda:0", seed=seed)
+    eng.state["episode_length_buf"].copy_(synth.initial_episode_length(flat["max_episode_length"]).cuda())
+    return flat, eng, synth
+
+
+def _host_inputs(flat, synth, k, n):
+    A = flat["num_actors"]
+    root = torch.zeros(n, A, 13)
+    root[:, :, 6] = 1.0
+    root[:, 0, :] = synth.root(k)
+    return {"actions": synth.actions(k).contiguous().pin_memory(),
+            "dof": [synth.dof_state(k, s).pin_memory() for s in range(flat["decimation"])],
+            "root": root.view(n * A, 13).contiguous().pin_memory(), "contact": synth.contact(k).pin_memory()}
+
+
+def test_pipeline_equals_sequential_shards():
+    from legged_tracking_b200.engine import HostStepPipeline
+    n, shards = 512, 3
+    a = [_shard(40 + c, n) for c in range(shards)]
+    b = [_shard(40 + c, n) for c in range(shards)]
+    pipe = HostStepPipeline([e for _, e, _ in a])
+    assert pipe.num_envs == n * shards
+    for k in range(3):
+        h_in = [_host_inputs(flat, synth, k, n) for flat, _, synth in a]
+        h_out = [{"obs": torch.empty(n, flat["num_obs"]).pin_memory(), "priv": torch.empty(n, flat["num_privileged_obs"]).pin_memory(),
+                  "rew": torch.empty(n).pin_memory(), "done": torch.empty(n, dtype=torch.bool).pin_memory()} for flat, _, _ in a]
+        pipe.step(h_in, h_out)
+        for (flat, eng, _), hi, ho in zip(b, h_in, h_out):
+            act = hi["actions"].cuda()
+            for s, dof in enumerate(hi["dof"]):
+                eng.dof_state.copy_(dof.cuda())
+                eng.compute_torques(act, s)
+            eng.root_states.copy_(hi["root"].cuda())
+            eng.contact_forces.copy_(hi["contact"].cuda())
+            eng.post_physics_step()
+            torch.cuda.synchronize()
+            assert torch.equal(ho["obs"], eng.state["obs_buf"].cpu()), k
+            assert torch.equal(ho["rew"], eng.state["rew_buf"].cpu()), k
+            assert torch.equal(ho["done"], eng.state["reset_buf"].cpu().bool()), k
+            assert torch.equal(ho["priv"], eng.state["privileged_obs_buf"].cpu()), k
