@@ -18,15 +18,7 @@ VARIANTS = {
     "mma_exp2_hihi": ["LT_MMA_EXP=2"],
     "mma_exp3_both": ["LT_MMA_EXP=3"],
 }
-OLD_VARIANTS = {
-    "spt2_b4": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=4"],
-    "spt2_b5": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=5"],
-    "spt2_b6": ["LT_TORQUE_SPT=2", "LT_TORQUE_MINB=6"],
-    "spt2_t64_b8": ["LT_TORQUE_SPT=2", "LT_TORQUE_THREADS=64", "LT_TORQUE_MINB=8"],
-    "spt2_t64_b10": ["LT_TORQUE_SPT=2", "LT_TORQUE_THREADS=64", "LT_TORQUE_MINB=10"],
-    "spt4_b2": ["LT_TORQUE_SPT=4", "LT_TORQUE_MINB=2"],
-    "spt4_b3": ["LT_TORQUE_SPT=4", "LT_TORQUE_MINB=3"],
-}
+# FP32-pipe torque kernel variants tuned in an earlier pass (build with only=None): LT_TORQUE_SPT / LT_TORQUE_MINB / LT_TORQUE_THREADS
 
 
 def build():
