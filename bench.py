@@ -443,18 +443,22 @@ def run_b200(args, rank, world, local_rank):
     ms_step = ms / args.steps
     value = world * n_env * args.steps / (ms * 1e-3)
     torque_total = ms_torque * flat["decimation"]
-    dominant = "lt_torque_kernel" if torque_total > ms_post else "lt_step_kernel"
+    dominant = "lt_torque_kernel" if torque_total > ms_post else "lt_step_kernel"          # class of the dominant kernel
     tr = ncu_traffic() if n_env == 65536 else {}          # the capture was taken at 65,536 envs
     tr_post = [tr.get(k) for k in ("lt_step_kernel", "lt_obs_kernel", "lt_compact_kernel")]
     k_post = {"kernel": "post-physics chain: lt_step_kernel + lt_obs_kernel + lt_compact_kernel", "ms_per_launch": ms_post,
               "achieved": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9,
               "traffic": None if None in tr_post else sum(tr_post)}
-    k_tq = {"kernel": "lt_torque_mma_kernel", "ms_per_launch": ms_torque,
+    # lt_compute_torques picks the tcgen05 kernel from LT_TC5_MIN_ENVS (csrc/lt_kernels.cu) envs per GPU, else the mma.sync kernel
+    forced = os.environ.get("LT_TORQUE_TC5")
+    tq_name = "lt_torque_tc5_kernel" if (forced == "1" or (forced is None and n_env >= 40960)) else "lt_torque_mma_kernel"
+    k_tq = {"kernel": tq_name, "ms_per_launch": ms_torque,
             "achieved": alg["torque_substep"] * n_env / (ms_torque * 1e-3) / 1e9,
             "fp32_equiv_tflops": alg["torque_flops_substep"] * n_env / (ms_torque * 1e-3) / 1e12,
-            "traffic": tr.get("lt_torque_mma_kernel"),
-            "note": "actuator net on the tensor pipe (fp16-split x3 HMMA.16816, fp32 accumulate); bounded by XU (64 MUFU.RCP per "
-                    "sample) + tensor + issue, not by HBM: see profiles/ and DESIGN.md section 4"}
+            "traffic": tr.get(tq_name),
+            "note": "actuator net on the tensor cores (fp16-split x3, fp32 accumulate; tcgen05.mma with A and D in TMEM for large "
+                    "shards, mma.sync m16n8k16 for small ones); bounded by XU (64 MUFU.RCP per sample) + issue, not by HBM: see "
+                    "profiles/ and DESIGN.md section 4"}
     for d in (k_post, k_tq):
         d.update({"bound": "hbm", "peak": peak, "unit": "GB/s", "frac": d["achieved"] / peak})
     dom = k_tq if dominant == "lt_torque_kernel" else k_post

@@ -10,7 +10,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 OUT = os.path.join(PKG_DIR, "liblt_b200.so")
-SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_rollout.cu", "lt_terrain.cu"]
+SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_torque_tc5.cu", "lt_rollout.cu", "lt_terrain.cu"]
 HEADERS = ["lt_core.cuh", "lt_torque_mma.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-I", os.path.join(REPO, "include")]

@@ -35,6 +35,9 @@
 #ifndef LT_TORQUE_MMA
 #define LT_TORQUE_MMA 1            // actuator net on the tensor pipe (lt_torque_mma.cu); 0 = FP32-pipe kernels below
 #endif
+#ifndef LT_TC5_MIN_ENVS
+#define LT_TC5_MIN_ENVS 40960      // shard size from which lt_compute_torques picks the tcgen05 kernel
+#endif
 #define LT_COMPACT_THREADS 1024
 #define LT_OBS_THREADS 256
 
@@ -94,6 +97,8 @@ struct lt_handle {
     uint8_t* d_scratch;
     uint32_t* d_ptlut;
     float* d_act_frag;               // [LT_MMA_FRAG_REGS, 32] pre-split fp16 weight fragments of the actuator net
+    uint8_t* d_tc5_blob;             // B operands of the tcgen05 torque kernel (canonical K-major core-matrix layout)
+    int torque_impl;                 // LT_TORQUE_TC5: unset = by shard size, 0 = mma.sync kernel, 1 = tcgen05 kernel
     cudaStream_t side;               // lt_compact_kernel runs here, beside lt_obs_kernel (both depend only on lt_step_kernel)
     cudaEvent_t ev_fork, ev_join;
     bool fork_compact;
@@ -973,6 +978,14 @@ int lt_create(const lt_config* cfg, const lt_tables* tables, lt_handle** out) {
         if (e == cudaSuccess) e = cudaMalloc(&h->d_act_frag, fr.size());
         if (e == cudaSuccess) e = cudaMemcpy(h->d_act_frag, fr.data(), fr.size(), cudaMemcpyHostToDevice);
     }
+    {
+        std::string blob((size_t)LT_TC5_BLOB_BYTES, '\0');
+        lt_torque_tc5_build_blob(h->W, reinterpret_cast<uint8_t*>(&blob[0]));
+        if (e == cudaSuccess) e = cudaMalloc(&h->d_tc5_blob, blob.size());
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_tc5_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice);
+        const char* t5 = getenv("LT_TORQUE_TC5");
+        h->torque_impl = t5 ? atoi(t5) : -1;
+    }
     h->sm_count = prop.multiProcessorCount;
     {
         const char* f = getenv("LT_FORK_COMPACT");
@@ -998,6 +1011,7 @@ void lt_destroy(lt_handle* h) {
     cudaFree(h->d_scratch);
     cudaFree(h->d_ptlut);
     cudaFree(h->d_act_frag);
+    cudaFree(h->d_tc5_blob);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->side) cudaStreamDestroy(h->side);
@@ -1097,6 +1111,15 @@ int lt_compute_torques(lt_handle* h, const float* actions, int32_t substep, void
     p.substep = substep;
     const size_t n = (size_t)h->c.num_envs * LT_ND;
 #if LT_TORQUE_MMA
+    // tcgen05 kernel for large shards, mma.sync kernel for small ones: the former pays ~1.3 us per launch for the TMEM allocation,
+    // the weight copy to shared memory and the barrier set-up and only wins once a CTA has many tiles (profiles/r01e_tc5.md)
+    const bool tc5 = h->torque_impl > 0 || (h->torque_impl < 0 && h->c.num_envs >= LT_TC5_MIN_ENVS);
+    if (h->c.control_type == LT_CONTROL_ACTUATOR_NET && tc5) {
+        LT_CUDA(h, lt_torque_tc5_launch(h->c, h->W, h->d_tc5_blob, actions, h->sim.dof_state, h->st, h->d_counters, substep, h->sm_count,
+                                        0, (cudaStream_t)stream));
+        h->substeps_pending += 1;
+        return LT_OK;
+    }
     if (h->c.control_type == LT_CONTROL_ACTUATOR_NET) {
         LT_CUDA(h, lt_torque_mma_launch(h->c, h->d_act_frag, actions, h->sim.dof_state, h->st, h->d_counters, substep, h->sm_count,
                                         (cudaStream_t)stream));

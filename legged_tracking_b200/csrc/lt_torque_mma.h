@@ -16,6 +16,13 @@ LT_HIDDEN_SYM cudaError_t lt_torque_mma_launch(const lt_config& c, const float* 
                                                const lt_state_ptrs& st, const int32_t* counters, int substep, int sm_count,
                                                cudaStream_t stream);
 
+// ---- tcgen05 variant (lt_torque_tc5.cu): accumulators and the A operand in tensor memory, weights (B) in shared memory
+#define LT_TC5_BLOB_BYTES 8192
+LT_HIDDEN_SYM void lt_torque_tc5_build_blob(const lt_act_weights& W, uint8_t* blob);
+LT_HIDDEN_SYM cudaError_t lt_torque_tc5_launch(const lt_config& c, const lt_act_weights& W, const uint8_t* blob, const float* actions,
+                                               const float* dof_state, const lt_state_ptrs& st, const int32_t* counters, int substep,
+                                               int sm_count, int swap_lbo_sbo, cudaStream_t stream);
+
 // ---- programmatic dependent launch (PDL): the next kernel of the post-physics chain may be launched while the previous one
 // drains; every kernel of the chain calls lt_pdl_wait() before its first access to memory a predecessor writes, so stream
 // order is kept.  OFF by default, LT_PDL=1 in the environment turns it on.  Measured on a B200 (profiles/r01c_pdl.md): it
