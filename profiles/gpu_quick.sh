@@ -1,8 +1,2 @@
 mkdir -p gpurun_out
-LT_TORQUE_TC5=1 timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_tc5.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu_tc5.log
-: > gpurun_out/q.log
-for n in 16384 32768 65536; do for v in 1; do
-  LT_TORQUE_TC5=$v timeout 300 python bench.py --no-ppo --no-cpu --steps 1000 --envs-per-gpu $n 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('tc5',$v,$n,round(d['value']/1e6,1),'M/s step_us',round(d['ms_per_step']*1e3,1),'post_us',round(d['post_physics_only']['ms_per_step']*1e3,1))" >> gpurun_out/q.log
-done; done
-nvidia-smi --query-gpu=name --format=csv,noheader > gpurun_out/alive.txt 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_8192.csv python profiles/run_step.py 8192 6 > gpurun_out/ncu_launch.log 2>&1
