@@ -422,9 +422,17 @@ def run_b200(args, rank, world, local_rank):
                           "rew": torch.empty(M).pin_memory(), "done": torch.empty(M, dtype=torch.bool).pin_memory()})
             del rs_c
         pipe = HostStepPipeline(engines)
+        packed = [pipe.alloc_host_inputs() for _ in range(2)]          # the replayed simulator state, kept in the pipeline's pinned layout
+        for r in range(2):
+            for c in range(n_chunks):
+                dst, src = packed[r][c], h_in[c][r]
+                dst["actions"].copy_(src["actions"]); dst["root"].copy_(src["root"]); dst["contact"].copy_(src["contact"])
+                for a, b in zip(dst["dof"], src["dof"]):
+                    a.copy_(b)
+        h_in = None
 
         def e2e_pipe(k):
-            pipe.step([h[k % 2] for h in h_in], h_out)
+            pipe.step(packed[k % 2], h_out)
         for k in range(3):
             e2e_pipe(k)
         if dist:

@@ -36,7 +36,15 @@ def test_pipeline_equals_sequential_shards():
         h_in = [_host_inputs(flat, synth, k, n) for flat, _, synth in a]
         h_out = [{"obs": torch.empty(n, flat["num_obs"]).pin_memory(), "priv": torch.empty(n, flat["num_privileged_obs"]).pin_memory(),
                   "rew": torch.empty(n).pin_memory(), "done": torch.empty(n, dtype=torch.bool).pin_memory()} for flat, _, _ in a]
-        pipe.step(h_in, h_out)
+        if k == 1:                                             # the single-copy path: inputs kept in the pipeline's pinned layout
+            packed = pipe.alloc_host_inputs()
+            for dst, src in zip(packed, h_in):
+                dst["actions"].copy_(src["actions"]); dst["root"].copy_(src["root"]); dst["contact"].copy_(src["contact"])
+                for a_, b_ in zip(dst["dof"], src["dof"]):
+                    a_.copy_(b_)
+            pipe.step(packed, h_out)
+        else:
+            pipe.step(h_in, h_out)
         for (flat, eng, _), hi, ho in zip(b, h_in, h_out):
             act = hi["actions"].cuda()
             for s, dof in enumerate(hi["dof"]):
