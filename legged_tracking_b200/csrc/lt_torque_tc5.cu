@@ -98,6 +98,9 @@ __device__ __forceinline__ void tc5_commit(uint64_t* bar) {
 }
 // D[tmem] (+)= A[tmem] * B[smem descriptor]
 __device__ __forceinline__ void tc5_mma(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+#if TC5_EXP & 2
+    return;
+#endif
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
@@ -137,13 +140,24 @@ __device__ __forceinline__ uint64_t tc5_desc(uint32_t smem_addr, uint32_t lbo, u
     return (uint64_t)((smem_addr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
 }
 __device__ __forceinline__ void tc5_split(float x0, float x1, uint32_t& hi, uint32_t& lo) {      // as lt_torque_mma.cu
+#if TC5_EXP & 1
+    hi = __float_as_uint(x0) ^ __float_as_uint(x1);
+    lo = 0u;
+    return;
+#endif
     const float h0 = __uint_as_float(__float_as_uint(x0) & 0xffffe000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xffffe000u);
     const __half2 h = __floats2half2_rn(h0, h1);
     const __half2 l = __floats2half2_rn(__fsub_rn(x0, h0), __fsub_rn(x1, h1));
     hi = *reinterpret_cast<const uint32_t*>(&h);
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
+#ifndef TC5_EXP
+#define TC5_EXP 0                   // timing ablations only (profiles/variants.py): 1 = no softsign / split arithmetic, 2 = no MMAs
+#endif
 __device__ __forceinline__ float tc5_softsign(float x) {
+#if TC5_EXP & 1
+    return x;
+#endif
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fabsf(x) + 1.0f));
     return x * r;

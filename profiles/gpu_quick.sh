@@ -1,8 +1,8 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_pipeline.py -m gpu -x -q > gpurun_out/t_pipe.log 2>&1; echo "rc=$?" >> gpurun_out/t_pipe.log
-
+LT_TORQUE_TC5=1 timeout 120 python -m pytest tests/test_gpu_step.py -m gpu -x -q -s -k "torque_kernel" > gpurun_out/t_tc5_1.log 2>&1; echo "rc=$?" >> gpurun_out/t_tc5_1.log
+nvidia-smi --query-gpu=name --format=csv,noheader > gpurun_out/alive.txt 2>&1
 : > gpurun_out/q.log
-for c in 2 4 8; do
-  timeout 300 python bench.py --no-ppo --no-cpu --steps 300 --e2e-chunks $c 2>gpurun_out/bench_e2e_$c.err | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('chunks',$c,'e2e',round(d['e2e']['value']/1e6,2),'ms',round(d['e2e']['ms_per_step'],3),'single',round(d['e2e']['single_stream']['value']/1e6,2))" >> gpurun_out/q.log
-done
+for n in 65536; do for v in 1; do
+  LT_TORQUE_TC5=$v timeout 300 python bench.py --no-ppo --no-cpu --steps 1000 --envs-per-gpu $n 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('tc5',$v,$n,round(d['value']/1e6,1),'M/s step_us',round(d['ms_per_step']*1e3,1),'post_us',round(d['post_physics_only']['ms_per_step']*1e3,1))" >> gpurun_out/q.log
+done; done

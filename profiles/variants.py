@@ -11,12 +11,12 @@ import sys
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
 VDIR = os.path.join(REPO, "build", "variants")
-MMA_ONLY = ("lt_torque_mma.cu",)          # variants whose defines touch only the tensor-pipe torque kernel
+MMA_ONLY = ("lt_torque_mma.cu", "lt_torque_tc5.cu")          # variants whose defines touch only the tensor-pipe torque kernel
 VARIANTS = {
-    "mma_base": [],
-    "mma_exp1_nomufu": ["LT_MMA_EXP=1"],
-    "mma_exp2_hihi": ["LT_MMA_EXP=2"],
-    "mma_exp3_both": ["LT_MMA_EXP=3"],
+    "tc5_base": [],
+    "tc5_exp1_noalu": ["TC5_EXP=1"],
+    "tc5_exp2_nomma": ["TC5_EXP=2"],
+    "tc5_exp3_neither": ["TC5_EXP=3"],
 }
 # FP32-pipe torque kernel variants tuned in an earlier pass (build with only=None): LT_TORQUE_SPT / LT_TORQUE_MINB / LT_TORQUE_THREADS
 
@@ -28,7 +28,7 @@ def build():
 
     def one(item):
         name, defs = item
-        b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"), only=MMA_ONLY if name.startswith("mma_") else None)
+        b.build(force=True, defines=defs, out=os.path.join(VDIR, name + ".so"), only=MMA_ONLY if name.startswith(("mma_", "tc5_")) else None)
         print("built", name, flush=True)
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         list(ex.map(one, VARIANTS.items()))
