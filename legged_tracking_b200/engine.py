@@ -12,6 +12,7 @@ import numpy as np
 import torch
 
 from . import _abi, cconfig
+from . import dist as ltd
 
 _TORCH_DTYPES = {"f32": torch.float32, "i64": torch.int64, "bool": torch.bool, "i32": torch.int32}
 
@@ -158,6 +159,12 @@ class StepEngine:
         self.n_external = sum(1 for n in self.reward_names if n == "external" or n in flat.get("external_reward_names", ()))
         self.sum_names = self.reward_names + ["total", "total_pos", "total_neg"]
         self._keepalive = []
+        # LR:332-335 buckets a term by the sign of its ALL-ENV sum.  When this engine holds only a shard of the envs (one rank
+        # of an env-sharded job, or one chunk of a HostStepPipeline) the shard-local sums of the sign-indefinite terms must be
+        # combined before the step kernel reads them: lt_reward_sign_prepass -> exchange -> lt_post_physics_step.
+        self.any_bucket_by_sum = any(int(self.cfg.term_bucket[i]) == _abi.ENUMS["LT_BUCKET_BY_SUM"] for i in range(self.cfg.n_terms))
+        self.term_sums = self._wrap_f32(self.lib.lt_term_sum_buffer(self.handle), _abi.DEFINES["LT_MAX_TERMS"])
+        self.term_sum_exchange = None         # callable(float32[LT_MAX_TERMS] device tensor) -> None (in place); None = dist all-reduce
 
     def _wrap_i32(self, ptr, n):
         """torch view of a library-owned device int32 array (read-only use)."""
@@ -165,6 +172,13 @@ class StepEngine:
             pass
         h = _Holder()
         h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+        return torch.as_tensor(h, device=self.device)
+
+    def _wrap_f32(self, ptr, n):
+        class _Holder:
+            pass
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
         return torch.as_tensor(h, device=self.device)
 
     def __del__(self):
@@ -244,6 +258,13 @@ class StepEngine:
         if new_g is not None:
             g_host = (C.c_float * 3)(*[float(v) for v in new_g])
             args.new_gravity = C.cast(g_host, C.c_void_p)
+        if self.any_bucket_by_sum and (self.term_sum_exchange is not None or ltd.world_size() > 1):
+            self.sign_prepass(args, stream)
+            with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
+                if self.term_sum_exchange is not None:
+                    self.term_sum_exchange(self.term_sums)
+                else:
+                    ltd.allreduce_sum_(self.term_sums)
         _abi.check(self.lib.lt_post_physics_step(self.handle, C.byref(args), self._stream_ptr(stream)), self.handle,
                    "lt_post_physics_step")
         if new_g is not None:
@@ -251,6 +272,14 @@ class StepEngine:
             self.state["gravity_vec"].copy_(GravitySchedule.gravity_vec_of(new_g), non_blocking=False)
         if advance_gravity and self.curriculum.advance(self.gravity.common_step_counter):
             self.set_reward_scales(self.curriculum.term_scales())
+
+    def sign_prepass(self, args=None, stream=None):
+        """lt_reward_sign_prepass: shard-local sums of the sign-indefinite terms -> self.term_sums (device float32[LT_MAX_TERMS]).
+        The next lt_post_physics_step uses whatever that buffer then holds instead of recomputing it."""
+        if args is None:
+            args = _abi.lt_step_args()
+        _abi.check(self.lib.lt_reward_sign_prepass(self.handle, C.byref(args), self._stream_ptr(stream)), self.handle,
+                   "lt_reward_sign_prepass")
 
     def set_reward_scales(self, scales):
         """New per-term scales (already multiplied by dt, order of reward_names) for the following steps (LR:171-183)."""

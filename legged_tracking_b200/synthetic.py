@@ -41,7 +41,7 @@ class SyntheticState:
     """Deterministic function (seed, step[, substep]) -> state tensors, generated on CPU."""
 
     def __init__(self, num_envs, env_origins, num_bodies=18, seed=1000, feet_indices=(4, 8, 12, 16),
-                 z_range=(0.15, 0.40), x_span=2.6, y_span=0.4, action_std=1.5):
+                 z_range=(0.15, 0.40), x_span=2.6, y_span=0.4, action_std=1.5, rp_range=0.3):
         self.n = int(num_envs)
         self.nb = int(num_bodies)
         self.seed = int(seed)
@@ -51,6 +51,7 @@ class SyntheticState:
         self.x_span = x_span
         self.y_span = y_span
         self.action_std = action_std
+        self.rp_range = float(rp_range)     # roll / pitch ~ U(+-rp_range); > pi/2 turns some robots over (LR:215-216)
         self.default_dof = torch.from_numpy(DEFAULT_DOF_POS)
         self.lo = torch.from_numpy(DOF_LOWER)
         self.hi = torch.from_numpy(DOF_UPPER)
@@ -87,7 +88,7 @@ class SyntheticState:
         pos[:, 0] += u[:, 0] * self.x_span
         pos[:, 1] += (2 * u[:, 1] - 1) * self.y_span
         pos[:, 2] = self.z_range[0] + u[:, 2] * (self.z_range[1] - self.z_range[0])
-        rpy = (2 * u[:, 3:6] - 1) * torch.tensor([0.3, 0.3, math.pi])
+        rpy = (2 * u[:, 3:6] - 1) * torch.tensor([self.rp_range, self.rp_range, math.pi])
         quat = _quat_from_rpy(rpy[:, 0], rpy[:, 1], rpy[:, 2])
         lin = torch.randn(self.n, 3, generator=g) * 0.5
         ang = torch.randn(self.n, 3, generator=g) * 1.0

@@ -40,6 +40,9 @@ def snapshot(env, wrapped, prefix, out):
     """Copy the reference env's state into out[prefix + name] using the port's state names."""
     n = env.num_envs
     for a in F32_ATTRS:
+        if not hasattr(env, a) and a.startswith("joint_"):      # actuator-net histories only exist for control_type actuator_net (LR:1307-1327)
+            out[prefix + a] = np.zeros((n, env.num_dof), np.float32)
+            continue
         out[prefix + a] = getattr(env, a).detach().float().numpy().copy()
     out[prefix + "friction_coeffs"] = env.friction_coeffs[:, :1].numpy().copy()
     out[prefix + "restitutions"] = env.restitutions[:, :1].numpy().copy()
@@ -215,11 +218,11 @@ def actuator_from_reference():
 
 
 def record_run(argv, num_envs, num_rows=None, num_cols=None, steps=6, overrides=None, synth_seed=1000,
-               full_state_every=2, near_timeout_frac=0.3, start_counter=0):
+               full_state_every=2, near_timeout_frac=0.3, start_counter=0, synth_kwargs=None):
     """Run the reference for `steps` policy steps; return the fixture dict (numpy arrays + 'flat' JSON string)."""
     import isaacgym.gymapi as gymapi
     wrapped, env, replay, Cfg, args = H.make_env(argv, num_envs, num_rows, num_cols, synth_seed=synth_seed,
-                                                 overrides=overrides)
+                                                 overrides=overrides, synth_kwargs=synth_kwargs)
     import go1_gym.envs.base.legged_robot_trajectory_tracking as LRmod
     rng = TaggedRng(env)
     hidx = {}
@@ -329,6 +332,60 @@ FIXTURES = {
                                              "terrain.y_init_range": 0.1, "terrain.yaw_init_range": 0.5,
                                              "env.observe_two_prev_actions": True,
                                              "env.num_observations": 504 + 12, "env.num_scalar_observations": 504 + 12}),
+    # the OTHER shipped reward container (trajectory_tracking_reward.py:17-171; selected by
+    # runs/trajectory_tracking/run-20230904_112307-rhi1my71/config.yaml): every term of it that the fused kernel claims,
+    # with the shipped run's scales where it has them; thresholds chosen so that both branches of each gate fire on the
+    # synthetic state (T_reach below / above the episode phases, small_vel / large_dist in the middle of the ranges)
+    "ttr_container_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path"],
+                             num_envs=32, num_rows=4, num_cols=4, steps=6,
+                             overrides={"rewards.reward_container_name": "TrajectoryTrackingRewards",
+                                        "rewards.T_reach": 200, "rewards.small_vel_threshold": 0.4,
+                                        "rewards.large_dist_threshold": 1.5, "rewards.target_ang_vel": np.pi / 2.0,
+                                        "rewards.tracking_sigma_ang": 0.5, "commands.switch_dist": 0.6,
+                                        "reward_scales.e2e": 0.0, "reward_scales.exploration_lin": 0.0,
+                                        "reward_scales.exploration_yaw": 0.0, "reward_scales.base_height": 0.0,
+                                        "reward_scales.large_vel": 0.0,
+                                        "reward_scales.torques": -2e-5, "reward_scales.dof_acc": -5e-7,
+                                        "reward_scales.collision": -1.0, "reward_scales.action_rate": -0.01,
+                                        "reward_scales.dof_pos_limits": -20.0, "reward_scales.orientation": -0.5,
+                                        "reward_scales.dof_vel": -1e-4, "reward_scales.dof_pos": -0.01,
+                                        "reward_scales.task_old": 1.0, "reward_scales.reach_goal": 200.0,
+                                        "reward_scales.reach_goal_t": 0.1, "reward_scales.reach_goal_T": 5.0,
+                                        "reward_scales.task": 1.0, "reward_scales.exploration": 1.0,
+                                        "reward_scales.stalling": 1.0, "reward_scales.linear_vel": -1.0,
+                                        "reward_scales.lin_vel_z": -2.0, "reward_scales.ang_vel_xy": -0.05,
+                                        "reward_scales.feet_air_time": 1.0, "reward_scales.survive": 0.1,
+                                        "reward_scales.reaching_linear_vel": 0.6, "reward_scales.reaching_z": -0.5,
+                                        "reward_scales.reaching_roll": -0.5,
+                                        "reward_scales.reaching_pitch": -0.5, "reward_scales.reaching_yaw_abs": -0.3,
+                                        "reward_scales.reaching_yaw": 0.3}),
+    # same container with the l1 form of reaching_linear_vel (trajectory_tracking_reward.py:146-147) and the
+    # ji22 positive/negative combination (LR:343-344)
+    "ttr_l1_ji22_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path",
+                                          "--lin_vel_form", "l1"],
+                           num_envs=32, num_rows=4, num_cols=4, steps=4,
+                           overrides={"rewards.reward_container_name": "TrajectoryTrackingRewards",
+                                      "rewards.only_positive_rewards": False,
+                                      "rewards.only_positive_rewards_ji22_style": True, "rewards.sigma_rew_neg": 5.0,
+                                      "reward_scales.e2e": 0.0, "reward_scales.exploration_lin": 0.0,
+                                      "reward_scales.exploration_yaw": 0.0, "reward_scales.base_height": 0.0,
+                                      "reward_scales.large_vel": 0.0, "reward_scales.reaching_linear_vel": -0.6,
+                                      "reward_scales.exploration": 1.0, "reward_scales.survive": 0.5,
+                                      "reward_scales.feet_air_time": 1.0, "reward_scales.stalling": 1.0,
+                                      "rewards.small_vel_threshold": 0.4, "rewards.large_dist_threshold": 1.5}),
+    # option coverage 2: random_goal trajectories (trajectory_function.py:28-40), the PD controller instead of the
+    # actuator net (LR:989-991) with Kp/Kd factor randomisation, termination on body rotation (LR:215-216), the ji22
+    # reward combination on the crawling container
+    "opts_random_goal_P_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path"],
+                                  num_envs=32, num_rows=4, num_cols=4, steps=6, synth_kwargs={"rp_range": 1.9},
+                                  overrides={"commands.traj_function": "random_goal", "commands.x_mean": 1.5,
+                                             "commands.x_range": 1.0, "commands.y_mean": 0.0, "commands.y_range": 0.6,
+                                             "commands.yaw_range": 0.5, "control.control_type": "P",
+                                             "domain_rand.randomize_Kp_factor": True,
+                                             "domain_rand.randomize_Kd_factor": True,
+                                             "env.use_terminal_body_rotation": True,
+                                             "rewards.only_positive_rewards": False,
+                                             "rewards.only_positive_rewards_ji22_style": True}),
 }
 
 

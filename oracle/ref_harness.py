@@ -191,7 +191,7 @@ class Replay:
 
 
 def make_env(argv, num_envs, num_rows=None, num_cols=None, seed=11, synth_seed=1000, overrides=None,
-             history_wrapper=True):
+             history_wrapper=True, synth_kwargs=None):
     """Build the reference TrajectoryTrackingEnv on CPU, seeded like scripts/train.py:31-40."""
     install()
     import random
@@ -206,7 +206,8 @@ def make_env(argv, num_envs, num_rows=None, num_cols=None, seed=11, synth_seed=1
     gym = gymapi.acquire_gym()
     gym.set_replay(None)
     env = TrajectoryTrackingEnv(sim_device="cpu", headless=True, cfg=Cfg)
-    synth = SyntheticState(env.num_envs, env.env_origins.numpy(), num_bodies=gym.num_bodies_per_env, seed=synth_seed)
+    synth = SyntheticState(env.num_envs, env.env_origins.numpy(), num_bodies=gym.num_bodies_per_env, seed=synth_seed,
+                           **(synth_kwargs or {}))
     replay = Replay(synth, decimation=Cfg.control.decimation, num_actor=env.num_actor)
     gym.set_replay(replay)
     wrapped = HistoryWrapper(env) if history_wrapper else env
