@@ -15,6 +15,7 @@ import re
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 HEADER = os.path.join(REPO, "include", "lt_b200.h")
+POLICY_HEADER = os.path.join(REPO, "include", "lt_policy.h")       # actor-critic / PPO half of the same library
 LIB_PATH = os.environ.get("LT_B200_LIB") or os.path.join(PKG_DIR, "liblt_b200.so")     # override: tuning variants only
 
 _SCALARS = {"int32_t": C.c_int32, "uint32_t": C.c_uint32, "float": C.c_float, "int64_t": C.c_int64,
@@ -29,6 +30,8 @@ def _strip_comments(src):
 def parse_header(path=HEADER):
     """-> (defines: {name: int}, structs: {name: [(member, ctype)]}, member kinds for pointer structs)"""
     src = _strip_comments(open(path).read())
+    if path == HEADER:
+        src += "\n" + _strip_comments(open(POLICY_HEADER).read())
     defines = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define\s+(LT_\w+)\s+(-?\d+)\s", src)}
     enums = {}
     for body in re.findall(r"enum\s*\{(.*?)\}", src, flags=re.S) + re.findall(r"typedef enum\s*\{(.*?)\}", src, flags=re.S):
@@ -91,6 +94,9 @@ lt_state_ptrs = _mk("lt_state_ptrs")
 lt_step_args = _mk("lt_step_args")
 lt_rollout_ptrs = _mk("lt_rollout_ptrs")
 lt_transition_ptrs = _mk("lt_transition_ptrs")
+lt_policy_config = _mk("lt_policy_config")
+lt_ppo_hparams = _mk("lt_ppo_hparams")
+lt_ppo_batch_ptrs = _mk("lt_ppo_batch_ptrs")
 
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
            "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
@@ -98,9 +104,9 @@ EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_crea
            "lt_normalize_advantages", "lt_build_tunnel_tiles"]
 
 
-def declared_functions(path=HEADER):
-    """Names of every function the header declares (used by the symbol-export test)."""
-    src = _strip_comments(open(path).read())
+def declared_functions(path=None):
+    """Names of every function the headers declare (used by the symbol-export test)."""
+    src = "\n".join(_strip_comments(open(h).read()) for h in ((HEADER, POLICY_HEADER) if path is None else (path,)))
     src = re.sub(r"typedef struct \w+ \{.*?\}\s*\w+;", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(lt_\w+)\s*\(", src)))
 
@@ -147,12 +153,39 @@ def load(path=LIB_PATH):
     lib.lt_gae.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, C.c_float, C.c_float, vp]
     lib.lt_normalize_advantages.argtypes = [vp, vp, C.c_int64, vp]
     lib.lt_build_tunnel_tiles.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    i64, f32 = C.c_int64, C.c_float
+    lib.lt_policy_config_bytes.restype = C.c_int
+    lib.lt_policy_create.argtypes = [C.POINTER(lt_policy_config), C.POINTER(vp)]
+    lib.lt_policy_destroy.argtypes = [vp]
+    lib.lt_policy_destroy.restype = None
+    lib.lt_policy_last_error.argtypes = [vp]
+    lib.lt_policy_last_error.restype = C.c_char_p
+    lib.lt_policy_num_params.argtypes = [vp]
+    lib.lt_policy_num_params.restype = i64
+    lib.lt_policy_bind_params.argtypes = [vp, vp, vp]
+    lib.lt_policy_refresh.argtypes = [vp, vp]
+    lib.lt_policy_forward.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp]
+    lib.lt_policy_act.argtypes = [vp, vp, vp, i32, vp, vp, C.c_uint64, C.c_uint64, vp, vp, vp, vp, vp, vp]
+    lib.lt_ppo_minibatch_grad.argtypes = [vp, C.POINTER(lt_ppo_batch_ptrs), vp, i32, C.POINTER(lt_ppo_hparams), i32, vp, vp]
+    lib.lt_ppo_minibatch_apply.argtypes = [vp, C.POINTER(lt_ppo_hparams), vp, vp, vp, vp, i32, vp, vp]
+    lib.lt_adaptation_grad.argtypes = [vp, C.POINTER(lt_ppo_batch_ptrs), vp, i32, i32, i32, vp, vp]
+    lib.lt_adaptation_apply.argtypes = [vp, C.POINTER(lt_ppo_hparams), f32, vp, vp, i32, vp]
+    lib.lt_policy_adaptation_slice.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    lib.lt_linear_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    if lib.lt_policy_config_bytes() != C.sizeof(lt_policy_config):
+        raise LtError("sizeof(lt_policy_config) differs between the library and the binding: rebuild")
     if lib.lt_abi_version() != DEFINES["LT_ABI_VERSION"]:
         raise LtError(f"liblt_b200.so has ABI {lib.lt_abi_version()}, header has {DEFINES['LT_ABI_VERSION']}: rebuild")
     if lib.lt_config_bytes() != C.sizeof(lt_config):
         raise LtError(f"sizeof(lt_config) = {lib.lt_config_bytes()} in the library but {C.sizeof(lt_config)} in the binding")
     _lib = lib
     return lib
+
+
+def check_policy(rc, handle=None, what="liblt_b200 policy"):
+    if rc != 0:
+        msg = load().lt_policy_last_error(handle)
+        raise LtError(f"{what} failed with status {rc}: {msg.decode() if msg else '?'}")
 
 
 def check(rc, handle=None, what="liblt_b200"):

@@ -10,8 +10,11 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 OUT = os.path.join(PKG_DIR, "liblt_b200.so")
-SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_torque_tc5.cu", "lt_rollout.cu", "lt_terrain.cu"]
+SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_torque_tc5.cu", "lt_rollout.cu", "lt_terrain.cu", "lt_policy.cu"]
 HEADERS = ["lt_core.cuh", "lt_torque_mma.h"]
+# per-source header dependencies (a change to the GEMM header must not recompile the 3-minute step kernels)
+DEPS = {"lt_policy.cu": [os.path.join(CSRC, "lt_gemm.cuh"), os.path.join(REPO, "include", "lt_policy.h"),
+                         os.path.join(REPO, "include", "lt_b200.h")]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-I", os.path.join(REPO, "include")]
 OBJ_DIR = os.path.join(REPO, "build", "obj")
@@ -44,7 +47,7 @@ def build(force=False, verbose=False, defines=(), out=OUT, only=None):
         mine = only is None or os.path.basename(src) in only
         if not mine and os.path.exists(obj):
             return
-        if not force and not _stale(obj, [src] + hdrs):
+        if not force and not _stale(obj, [src] + DEPS.get(os.path.basename(src), hdrs)):
             return
         cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in (defines if mine else ())] + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
         r = subprocess.run(cmd, capture_output=True, text=True)

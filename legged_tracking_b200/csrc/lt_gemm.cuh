@@ -1,0 +1,420 @@
+// lt_gemm.cuh -- the dense contraction of the actor-critic MLPs (go1_gym_learn/ppo_cse/actor_critic.py:43-82 nn.Linear
+// stacks; forward, input-gradient and weight-gradient products of ppo.py:104-148) on the 5th-generation tensor cores.
+//
+//   D[M, N] = A[M, K] * B[N, K]^T        A, B: K-major, each stored as TWO fp16 planes (hi, lo) with a * s = hi + lo
+//
+// fp32-equivalent arithmetic on fp16 operands: every product is three tcgen05.mma (hi*hi + hi*lo + lo*hi, the lo*lo term is
+// below 2^-22 of the product) accumulated in fp32 in tensor memory; the power-of-two operand scales s are undone exactly in
+// the epilogue.  The reference runs these GEMMs in fp32 (TF32 off), so single-pass fp16/bf16/tf32 would be a precision drop.
+//
+// Structure (one persistent CTA per SM, 192 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor.3d loads a [2 planes, 128 rows, 64 k] box of A and a [2, bn, 64] box of B
+//               per k-block into a 128B-swizzled STAGES-deep shared-memory ring (mbarrier complete_tx)
+//   warp 1      MMA issuer: one elected lane, 4 k16 steps x 3 products per k-block, tcgen05.commit frees the ring slot;
+//               accumulators double-buffered in TMEM (2 x BN_MAX columns) so tile i+1's main loop overlaps tile i's epilogue
+//   warps 2..5  epilogue: thread <-> accumulator row (TMEM lane); tcgen05.ld 32 columns at a time, then one of
+//               EPI_F32      out = acc * scale + bias                                    -> fp32 [M, ld]
+//               EPI_ELU      y = ELU(acc * scale + bias)                                 -> fp16 planes, row-major (+ transposed)
+//               EPI_BWD      dz = acc * scale * ELU'(y_prev), ELU'(y) = y > 0 ? 1 : y+1   -> fp16 planes, row-major (+ transposed)
+//               EPI_PARTIAL  acc * scale -> fp32 split-K partial [split][M, ld]
+// Tiles are (split, m-block, n-block) triples, n fastest, so that the CTAs running at the same time share A rows in L2.
+// Rows / columns / k beyond the tensor bounds are zero-filled by TMA and masked in the epilogue: no padding requirements
+// beyond 16-byte row pitches.
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ltg {
+
+constexpr int BM = 128;          // rows per tile = TMEM lanes
+constexpr int BK = 64;           // k per ring slot = one 128-byte swizzle row of fp16
+constexpr int THREADS = 192;
+constexpr float OPERAND_MAX = 60000.0f;      // fp16 planes saturate here instead of overflowing to inf
+
+enum { EPI_F32 = 0, EPI_ELU = 1, EPI_BWD = 2, EPI_PARTIAL = 3 };
+
+struct Params {
+    CUtensorMap tma_a, tma_b;            // 3-D maps {k, row, plane}; box {64, 128, 2} / {64, bn, 2}; SWIZZLE_128B; zero OOB fill
+    int32_t M, N, K;
+    int32_t bn;                          // N tile = UMMA N (multiple of 16, <= BN_MAX)
+    int32_t splits, kb_per_split;        // split-K: k-blocks [s * kb_per_split, (s+1) * kb_per_split) go to partial s
+    int32_t mode;
+    float out_scale;                     // 1 / (s_a * s_b)
+    const float* bias;                   // [N] or NULL
+    float* out_f32;                      // EPI_F32 / EPI_PARTIAL
+    int64_t ld_f32, split_stride;
+    __half* out_h;                       // row-major planes [2][rows][ld_h]
+    int64_t ld_h, plane_h;
+    __half* out_t;                       // transposed planes [2][cols][ld_t] or NULL
+    int64_t ld_t, plane_t;
+    float split_scale;                   // scale of the fp16 planes written by EPI_ELU / EPI_BWD
+    const __half* act_h;                 // EPI_BWD: y_prev planes (row-major, scale 1 / act_inv_scale)
+    int64_t ld_act, plane_act;
+    float act_inv_scale;
+};
+
+// ---------------------------------------------------------------------------------------------------------------- PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1, int32_t c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B (8-row x 128-byte atoms, 1024 bytes between 8-row groups), version 1
+__device__ __forceinline__ uint64_t sw128_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+          "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+          "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]),
+          "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+          "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+// a * s = hi + lo in fp16 (hi rounded to nearest, lo the rounded residual: 22 significand bits in total)
+__device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+    x0 = fminf(fmaxf(x0, -OPERAND_MAX), OPERAND_MAX);
+    x1 = fminf(fmaxf(x1, -OPERAND_MAX), OPERAND_MAX);
+    const __half2 h = __floats2half2_rn(x0, x1);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(x0 - hf.x, x1 - hf.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+__device__ __forceinline__ float elu1(float z) { return z > 0.0f ? z : expm1f(z); }      // nn.ELU(alpha = 1)
+
+template <int BN_MAX, int STAGES>
+struct Smem {
+    static constexpr uint32_t A_BYTES = 2u * BM * BK * 2u;           // both planes of the A box
+    static constexpr uint32_t B_BYTES = 2u * BN_MAX * BK * 2u;
+    static constexpr uint32_t STAGE = A_BYTES + B_BYTES;
+    static constexpr uint32_t BARS = STAGES * STAGE;                 // full[STAGES] empty[STAGES] tfull[2] tempty[2] tmem slot
+    static constexpr uint32_t TOTAL = BARS + (2 * STAGES + 4) * 8 + 16 + 1024;     // + alignment slack
+};
+
+template <int BN_MAX, int STAGES>
+__global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_constant__ Params p) {
+    using S = Smem<BN_MAX, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + S::BARS;
+    auto full = [&](int s) { return bars + 8u * s; };
+    auto empty = [&](int s) { return bars + 8u * (STAGES + s); };
+    auto tfull = [&](int s) { return bars + 8u * (2 * STAGES + s); };
+    auto tempty = [&](int s) { return bars + 8u * (2 * STAGES + 2 + s); };
+    const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full(s), 1);
+            mbar_init(empty(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull(s), 1);
+            mbar_init(tempty(s), 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(2 * BN_MAX) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(tmem_slot));
+
+    const int m_tiles = (p.M + BM - 1) / BM, n_tiles = (p.N + p.bn - 1) / p.bn;
+    const int kb_total = (p.K + BK - 1) / BK;
+    const int n_work = m_tiles * n_tiles * p.splits;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&p.tma_a)) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&p.tma_b)) : "memory");
+            const uint32_t tx = S::A_BYTES + 2u * (uint32_t)p.bn * BK * 2u;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+                const int n_blk = w % n_tiles, m_blk = (w / n_tiles) % m_tiles, split = w / (n_tiles * m_tiles);
+                const int kb0 = split * p.kb_per_split, kb1 = min(kb_total, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(empty(stage), phase ^ 1u);
+                    mbar_expect_tx(full(stage), tx);
+                    const uint32_t sa = base + (uint32_t)stage * S::STAGE;
+                    tma_load_3d(sa, &p.tma_a, full(stage), kb * BK, m_blk * BM, 0);
+                    tma_load_3d(sa + S::A_BYTES, &p.tma_b, full(stage), kb * BK, n_blk * p.bn, 0);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------------------------------ MMA issuer
+        // instruction descriptor: D = F32, A = B = F16, both K-major, N = bn, M = 128
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        const uint32_t b_plane = (uint32_t)p.bn * BK * 2u;
+        int stage = 0, as = 0;
+        uint32_t phase = 0, aphase = 0;
+        for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+            const int split = w / (n_tiles * m_tiles);
+            const int kb0 = split * p.kb_per_split, kb1 = min(kb_total, kb0 + p.kb_per_split);
+            mbar_wait(tempty(as), aphase ^ 1u);
+            fence_after();
+            const uint32_t d_tmem = tmem + (uint32_t)as * BN_MAX;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(full(stage), phase);
+                fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = base + (uint32_t)stage * S::STAGE, sb = sa + S::A_BYTES;
+                    const uint64_t a_hi = sw128_desc(sa), a_lo = sw128_desc(sa + BM * BK * 2u);
+                    const uint64_t b_hi = sw128_desc(sb), b_lo = sw128_desc(sb + b_plane);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t adv = (uint64_t)((k * 32) >> 4);          // 16 fp16 = 32 bytes inside the swizzle row
+                        umma_ss(d_tmem, a_lo + adv, b_hi + adv, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        umma_ss(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+                        umma_ss(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+                    }
+                    umma_commit(empty(stage));                                    // slot free once these MMAs have read it
+                    if (kb == kb1 - 1) umma_commit(tfull(as));
+                }
+                __syncwarp();
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+            }
+            if (kb1 <= kb0 && lane == 0) umma_commit(tfull(as));                  // empty k range (never with a valid split plan)
+            if (++as == 2) {
+                as = 0;
+                aphase ^= 1u;
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------------------------------ epilogue
+        const int q = warp & 3;                                                   // TMEM lane quarter this warp may read
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+            const int n_blk = w % n_tiles, m_blk = (w / n_tiles) % m_tiles, split = w / (n_tiles * m_tiles);
+            const int row = m_blk * BM + q * 32 + lane;
+            const bool row_ok = row < p.M;
+            const int n0 = n_blk * p.bn;
+            mbar_wait(tfull(as), aphase);
+            fence_after();
+            const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * BN_MAX;
+            for (int c = 0; c < p.bn; c += 32) {
+                uint32_t r[32];
+                const int width = min(32, p.bn - c);                              // 32 or 16 (bn is a multiple of 16)
+                if (width == 32) tmem_ld32(taddr + c, r);
+                else tmem_ld16(taddr + c, r);
+                const int col0 = n0 + c;
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.out_scale;
+                if (p.mode == EPI_F32 || p.mode == EPI_PARTIAL) {
+                    float* out = p.out_f32 + (p.mode == EPI_PARTIAL ? (int64_t)split * p.split_stride : 0) + (int64_t)row * p.ld_f32;
+                    if (row_ok) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int n = col0 + j;
+                            if (j < width && n < p.N) out[n] = v[j] + ((p.bias && p.mode == EPI_F32) ? __ldg(p.bias + n) : 0.0f);
+                        }
+                    }
+                } else {
+                    if (p.mode == EPI_ELU) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int n = col0 + j;
+                            const float b = (p.bias && j < width && n < p.N) ? __ldg(p.bias + n) : 0.0f;
+                            v[j] = elu1(v[j] + b);
+                        }
+                    } else if (p.act_h) {                                         // EPI_BWD: times ELU'(y_prev); act_h == NULL: linear layer
+                        if (row_ok) {
+                            const __half* ah = p.act_h + (int64_t)row * p.ld_act + col0;
+                            const __half* al = ah + p.plane_act;
+                            if (col0 + width <= p.N && (p.ld_act & 7) == 0 && (col0 & 7) == 0) {
+#pragma unroll
+                                for (int g = 0; g < 4; ++g) {
+                                    if (g * 8 < width) {
+                                        const uint4 qh = __ldg(reinterpret_cast<const uint4*>(ah) + g), ql = __ldg(reinterpret_cast<const uint4*>(al) + g);
+                                        const uint32_t wh[4] = {qh.x, qh.y, qh.z, qh.w}, wl[4] = {ql.x, ql.y, ql.z, ql.w};
+#pragma unroll
+                                        for (int e = 0; e < 4; ++e) {
+                                            const float2 fh = __half22float2(*reinterpret_cast<const __half2*>(&wh[e]));
+                                            const float2 fl = __half22float2(*reinterpret_cast<const __half2*>(&wl[e]));
+                                            const float y0 = (fh.x + fl.x) * p.act_inv_scale, y1 = (fh.y + fl.y) * p.act_inv_scale;
+                                            v[g * 8 + 2 * e] *= (y0 > 0.0f ? 1.0f : y0 + 1.0f);
+                                            v[g * 8 + 2 * e + 1] *= (y1 > 0.0f ? 1.0f : y1 + 1.0f);
+                                        }
+                                    }
+                                }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) {
+                                    const int n = col0 + j;
+                                    if (j < width && n < p.N) {
+                                        const float y = (__half2float(ah[j]) + __half2float(al[j])) * p.act_inv_scale;
+                                        v[j] *= (y > 0.0f ? 1.0f : y + 1.0f);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    uint32_t hi[16], lo[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) split_pair(v[2 * j] * p.split_scale, v[2 * j + 1] * p.split_scale, hi[j], lo[j]);
+                    if (row_ok) {
+                        // row-major planes: this thread's 32 (or 16) consecutive columns, 16-byte stores where the row pitch allows
+                        __half* oh = p.out_h + (int64_t)row * p.ld_h + col0;
+                        __half* ol = oh + p.plane_h;
+                        if (col0 + width <= p.N && (p.ld_h & 7) == 0 && (col0 & 7) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                if (j * 8 < width) {
+                                    reinterpret_cast<uint4*>(oh)[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+                                    reinterpret_cast<uint4*>(ol)[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (j < width && col0 + j < p.N) {
+                                    reinterpret_cast<uint16_t*>(oh)[j] = (uint16_t)(hi[j >> 1] >> ((j & 1) * 16));
+                                    reinterpret_cast<uint16_t*>(ol)[j] = (uint16_t)(lo[j >> 1] >> ((j & 1) * 16));
+                                }
+                            }
+                        }
+                        if (p.out_t) {
+                            // transposed planes: for a fixed column the warp's 32 rows are consecutive -> coalesced 64-byte stores
+                            uint16_t* th = reinterpret_cast<uint16_t*>(p.out_t) + (int64_t)col0 * p.ld_t + row;
+                            uint16_t* tl = th + p.plane_t;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (j < width && col0 + j < p.N) {
+                                    th[(int64_t)j * p.ld_t] = (uint16_t)(hi[j >> 1] >> ((j & 1) * 16));
+                                    tl[(int64_t)j * p.ld_t] = (uint16_t)(lo[j >> 1] >> ((j & 1) * 16));
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(as));
+            if (++as == 2) {
+                as = 0;
+                aphase ^= 1u;
+            }
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(2 * BN_MAX) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------------- host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// planes [2][rows][ld] fp16 at `base`; logical extent rows x k; box {64, box_rows, 2}
+inline bool make_operand_map(CUtensorMap* map, const __half* base, int64_t rows, int64_t k, int64_t ld, int64_t plane, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, 2};
+    const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane * 2};
+    const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 2};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN_MAX, int STAGES>
+inline cudaError_t launch_t(const Params& p, int sm_count, cudaStream_t stream) {
+    using S = Smem<BN_MAX, STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(lt_gemm_kernel<BN_MAX, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::TOTAL);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const int m_tiles = (p.M + BM - 1) / BM, n_tiles = (p.N + p.bn - 1) / p.bn;
+    const int n_work = m_tiles * n_tiles * p.splits;
+    if (n_work <= 0) return cudaSuccess;
+    lt_gemm_kernel<BN_MAX, STAGES><<<n_work < sm_count ? n_work : sm_count, THREADS, S::TOTAL, stream>>>(p);
+    return cudaGetLastError();
+}
+
+inline cudaError_t launch(const Params& p, int sm_count, cudaStream_t stream) {
+    if (p.bn > 128) return launch_t<256, 2>(p, sm_count, stream);
+    return launch_t<128, 3>(p, sm_count, stream);
+}
+
+}   // namespace ltg

@@ -1,0 +1,1029 @@
+// lt_policy.cu -- actor-critic forward and the PPO minibatch step (include/lt_policy.h) on top of the tcgen05 contraction
+// kernel of lt_gemm.cuh.  AC = go1_gym_learn/ppo_cse/actor_critic.py, PPO = go1_gym_learn/ppo_cse/ppo.py of the reference.
+//
+// Data layout.  Every GEMM operand is a pair of fp16 planes [2][rows][ld] (value * scale = hi + lo).  One shared input
+// buffer X0 = [obs_history | latent | privileged_obs] feeds the first layer of all three MLPs; their first-layer weights
+// are stored expanded to that width with zeros in the columns a network does not read (adaptation: obs_history only;
+// actor: obs_history | latent, AC:130; critic: obs_history | privileged_obs, AC:158).  Hidden activations Y_l are written by
+// the GEMM epilogue already split (and, when training, also transposed with a constant-one row appended, which is what the
+// weight-gradient GEMM dW_l^T = [Y_{l-1}^T; 1] * dZ_l consumes: the bias gradient is its last column).
+// Scales are powers of two, undone exactly in the epilogues: activations 2^4, weights 2^6, gradients 2^ceil(log2(rows)).
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/lt_b200.h"
+#include "../../include/lt_policy.h"
+#include "lt_gemm.cuh"
+
+namespace {
+
+constexpr float S_X = 16.0f;          // activations / inputs
+constexpr float S_W = 64.0f;          // weights
+constexpr int HEAD_THREADS = 256;
+constexpr int STAT_SLOTS = 48;        // per-block partial row of the head kernels: 3 loss sums + up to 45 action columns
+
+std::string g_policy_error;
+
+struct Planes {
+    __half* p = nullptr;
+    int64_t rows = 0, ld = 0, plane = 0;          // [2][rows][ld]; plane = rows * ld
+    __half* lo() const { return p + plane; }
+};
+
+struct Layer {
+    int K = 0, N = 0;                 // GEMM reduction width (expanded for first layers) and outputs
+    int k_real = 0;                   // in_features of the nn.Linear
+    int c1 = 0, s2 = 0, c2 = 0;       // param cols [0,c1) <- gemm cols [0,c1); param cols [c1,c1+c2) <- gemm cols [s2,s2+c2)
+    int64_t w_off = 0, b_off = 0;     // offsets in the flat parameter vector
+    Planes W, WT;                     // [2][N][ld(K)] and [2][K][ld(N)]
+};
+
+struct Mlp {
+    int n = 0;                                    // number of Linear layers
+    Layer L[LT_POLICY_MAX_HIDDEN + 1];
+    Planes Y[LT_POLICY_MAX_HIDDEN], YT[LT_POLICY_MAX_HIDDEN];          // hidden activations, row-major and [N_l + 1][R] transposed
+    Planes dZ[LT_POLICY_MAX_HIDDEN + 1], dZT[LT_POLICY_MAX_HIDDEN + 1];
+    float* out = nullptr;                         // [R][N_last] fp32
+};
+
+}   // namespace
+
+struct lt_policy {
+    lt_policy_config c;
+    int sm_count = 0;
+    int64_t R = 0;                                // row capacity (multiple of 128)
+    int Din = 0, P = 0, A = 0, K0 = 0;
+    Mlp adapt, actor, critic;
+    Planes X0, X0T;                               // [2][R][ld(K0)], [2][K0 + 1][R]
+    float* partial = nullptr;                     // split-K workspace
+    int64_t partial_floats = 0;
+    float* head_partial = nullptr;                // [blocks][STAT_SLOTS]
+    float* norm_partial = nullptr;                // [blocks]
+    float* scalars = nullptr;                     // device float[8]: [0] clip coefficient, [1] total norm
+    int64_t n_params = 0;
+    float *params = nullptr, *grads = nullptr;
+    std::vector<void*> allocs;
+    std::string err;
+};
+
+namespace {
+
+void set_error(lt_policy* P, const std::string& m) {
+    if (P) P->err = m; else g_policy_error = m;
+}
+
+#define LTP_CUDA(P, call)                                                                                       \
+    do {                                                                                                        \
+        cudaError_t e_ = (call);                                                                                \
+        if (e_ != cudaSuccess) {                                                                                \
+            std::string m_ = std::string(#call) + ": " + cudaGetErrorString(e_);                                \
+            set_error((lt_policy*)(P), m_);                                                                     \
+            return LT_ERR_CUDA;                                                                                 \
+        }                                                                                                       \
+    } while (0)
+
+int fail(lt_policy* P, int code, const std::string& msg) {
+    set_error(P, msg);
+    return code;
+}
+
+inline int64_t up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+int alloc_planes(lt_policy* P, Planes& pl, int64_t rows, int64_t width) {
+    pl.rows = rows;
+    pl.ld = up(width, 8);
+    pl.plane = pl.rows * pl.ld;
+    void* d = nullptr;
+    LTP_CUDA(P, cudaMalloc(&d, (size_t)(2 * pl.plane) * sizeof(__half)));
+    LTP_CUDA(P, cudaMemset(d, 0, (size_t)(2 * pl.plane) * sizeof(__half)));
+    P->allocs.push_back(d);
+    pl.p = (__half*)d;
+    return LT_OK;
+}
+template <typename T>
+int alloc_dev(lt_policy* P, T*& out, int64_t n) {
+    void* d = nullptr;
+    LTP_CUDA(P, cudaMalloc(&d, (size_t)n * sizeof(T)));
+    LTP_CUDA(P, cudaMemset(d, 0, (size_t)n * sizeof(T)));
+    P->allocs.push_back(d);
+    out = (T*)d;
+    return LT_OK;
+}
+
+inline int pick_bn(int n) {                      // smallest multiple of 16 that covers n in ceil(n / 256) equal tiles
+    const int tiles = (n + 255) / 256;
+    return (int)up((n + tiles - 1) / tiles, 16);
+}
+
+// ------------------------------------------------------------------------------------------------------------ kernels
+__device__ __forceinline__ void split1(float x, __half& hi, __half& lo) {
+    x = fminf(fmaxf(x, -ltg::OPERAND_MAX), ltg::OPERAND_MAX);
+    hi = __float2half_rn(x);
+    lo = __float2half_rn(x - __half2float(hi));
+}
+
+// master weights -> operand planes W [N][K] and WT [K][N] of one layer (expanded column map for first layers)
+__global__ void split_weights_kernel(const float* __restrict__ w, int N, int K, int k_real, int c1, int s2, int c2, __half* W, int64_t ldW,
+                                     int64_t planeW, __half* WT, int64_t ldT, int64_t planeT) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)N * K) return;
+    const int n = (int)(i / K), k = (int)(i % K);
+    int src = -1;
+    if (k < c1) src = k;
+    else if (k >= s2 && k < s2 + c2) src = c1 + (k - s2);
+    const float v = src >= 0 ? w[(int64_t)n * k_real + src] * S_W : 0.0f;
+    __half hi, lo;
+    split1(v, hi, lo);
+    W[(int64_t)n * ldW + k] = hi;
+    W[planeW + (int64_t)n * ldW + k] = lo;
+    if (WT) {
+        WT[(int64_t)k * ldT + n] = hi;
+        WT[planeT + (int64_t)k * ldT + n] = lo;
+    }
+}
+
+// Gather + split the shared first-layer input: X0[r] = [obs_history[src] | 0 (or privileged_obs, teacher mode) | privileged_obs[src]]
+// and, when xt != NULL, its transpose.  Block = 32 rows; 8 warps sweep 32-column chunks through a shared-memory tile so that
+// both the row-major and the transposed planes are written with consecutive lanes on consecutive addresses.
+__global__ void __launch_bounds__(256) pack_x0_kernel(const float* __restrict__ obs_history, const float* __restrict__ priv,
+                                                      const int64_t* __restrict__ indices, int rows, int Din, int P, int teacher,
+                                                      __half* x, int64_t ldx, int64_t planex, __half* xt, int64_t ldt, int64_t planet) {
+    __shared__ float tile[32][33];
+    __shared__ int64_t src_row[32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int row0 = blockIdx.x * 32;
+    if (threadIdx.x < 32) {
+        const int r = row0 + threadIdx.x;
+        src_row[threadIdx.x] = r < rows ? (indices ? indices[r] : (int64_t)r) : -1;
+    }
+    __syncthreads();
+    const int K0 = Din + 2 * P;
+    for (int c0 = 0; c0 < K0; c0 += 32) {
+        const int col = c0 + tx;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int lr = ty * 4 + i;
+            const int64_t s = src_row[lr];
+            float v = 0.0f;
+            if (s >= 0 && col < K0) {
+                if (col < Din) v = obs_history[s * Din + col];
+                else if (col < Din + P) v = (teacher && priv) ? priv[s * P + (col - Din)] : 0.0f;
+                else v = priv ? priv[s * P + (col - Din - P)] : 0.0f;
+                v *= S_X;
+                __half hi, lo;
+                split1(v, hi, lo);
+                const int64_t o = (int64_t)(row0 + lr) * ldx + col;
+                x[o] = hi;
+                x[planex + o] = lo;
+            }
+            tile[lr][tx] = v;
+        }
+        __syncthreads();
+        if (xt) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int lc = ty * 4 + i;
+                const int r = row0 + tx;
+                if (c0 + lc < K0 && r < rows) {
+                    __half hi, lo;
+                    split1(tile[tx][lc], hi, lo);
+                    const int64_t o = (int64_t)(c0 + lc) * ldt + r;
+                    xt[o] = hi;
+                    xt[planet + o] = lo;
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// constant-one row (value 1 * S_X) of a transposed activation buffer: carries the bias gradient through the dW GEMM
+__global__ void ones_row_kernel(__half* row_hi, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) row_hi[i] = __float2half_rn(S_X);
+}
+
+// latent (adaptation module output, fp32) -> its columns of X0 / X0T (AC:129-130: actor input = cat(obs_history, latent))
+__global__ void scatter_latent_kernel(const float* __restrict__ latent, int rows, int P, int Din, __half* x, int64_t ldx, int64_t planex,
+                                      __half* xt, int64_t ldt, int64_t planet) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    for (int j = 0; j < P; ++j) {
+        __half hi, lo;
+        split1(latent[(int64_t)r * P + j] * S_X, hi, lo);
+        const int64_t o = (int64_t)r * ldx + Din + j;
+        x[o] = hi;
+        x[planex + o] = lo;
+        if (xt) {
+            const int64_t t = (int64_t)(Din + j) * ldt + r;
+            xt[t] = hi;
+            xt[planet + t] = lo;
+        }
+    }
+}
+
+// split-K partials of dW^T ... summed in a fixed order into the flat gradient: partial[s][n][k], k < K -> weight (through the
+// first-layer column map), k == K -> bias
+__global__ void reduce_dw_kernel(const float* __restrict__ partial, int splits, int64_t split_stride, int64_t ldp, int N, int K, int k_real,
+                                 int c1, int s2, int c2, float* __restrict__ gw, float* __restrict__ gb) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)N * (K + 1)) return;
+    const int n = (int)(i / (K + 1)), k = (int)(i % (K + 1));
+    int dst = -1;
+    if (k == K) dst = -2;
+    else if (k < c1) dst = k;
+    else if (k >= s2 && k < s2 + c2) dst = c1 + (k - s2);
+    if (dst == -1) return;
+    float acc = 0.0f;
+    const float* src = partial + (int64_t)n * ldp + k;
+    for (int s = 0; s < splits; ++s) acc += src[(int64_t)s * split_stride];
+    if (dst == -2) gb[n] = acc;
+    else gw[(int64_t)n * k_real + dst] = acc;
+}
+
+__global__ void sum_partials_kernel(const float* __restrict__ partial, int splits, int64_t n, int N, const float* __restrict__ bias, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float acc = 0.0f;
+    for (int s = 0; s < splits; ++s) acc += partial[(int64_t)s * n + i];
+    out[i] = acc + (bias ? bias[i % N] : 0.0f);
+}
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {            // deterministic: fixed tree
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    float t = 0.0f;
+    if (threadIdx.x < 32) {
+        t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.0f;
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    }
+    return t;                                                               // valid in thread 0
+}
+
+struct HeadParams {
+    lt_ppo_batch_ptrs b;
+    const int64_t* indices;
+    int count, A;
+    const float* mu;            // [count][A] actor output
+    const float* value;         // [count]
+    const float* std;           // [A]
+    lt_ppo_hparams hp;
+    float inv_count;            // 1 / (count * grad_world)
+    float s_g;
+    __half *dmu, *dmut, *dv, *dvt;                    // planes
+    int64_t ld_dmu, plane_dmu, ld_dmut, plane_dmut, ld_dv, plane_dv, ld_dvt, plane_dvt;
+    float* partial;             // [blocks][STAT_SLOTS]
+};
+
+// Loss head of one minibatch (PPO:104-141) and its gradient with respect to the actor mean, the critic value and std.
+__global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_constant__ HeadParams p) {
+    __shared__ float sh[HEAD_THREADS / 32];
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool ok = r < p.count;
+    float surr = 0.0f, vl = 0.0f, kl = 0.0f, g_logp = 0.0f;
+    float dstd[32];
+    const int A = p.A;
+    int64_t s = 0;
+    if (ok) {
+        s = p.indices ? p.indices[r] : (int64_t)r;
+        float logp = 0.0f;
+        for (int j = 0; j < A; ++j) {
+            const float mu = p.mu[(int64_t)r * A + j], sg = p.std[j], a = p.b.actions[s * A + j];
+            const float d = a - mu;
+            logp += -(d * d) / (2.0f * sg * sg) - logf(sg) - 0.91893853320467274178f;            // Normal.log_prob
+            const float omu = p.b.old_mu[s * A + j], osg = p.b.old_sigma[s * A + j];
+            kl += logf(sg / osg + 1.e-5f) + (osg * osg + (omu - mu) * (omu - mu)) / (2.0f * sg * sg) - 0.5f;     // PPO:112-116
+        }
+        const float adv = p.b.advantages[s], ratio = expf(logp - p.b.old_actions_log_prob[s]);
+        const float lo = 1.0f - p.hp.clip_param, hi = 1.0f + p.hp.clip_param;
+        const float s1 = -adv * ratio, s2 = -adv * fminf(fmaxf(ratio, lo), hi);
+        surr = fmaxf(s1, s2);
+        const bool inside = ratio >= lo && ratio <= hi;
+        g_logp = (inside || s1 > s2) ? s1 : 0.0f;                    // d surrogate / d logp = -adv * ratio where the max picks the unclipped branch
+        const float v = p.value[r], R = p.b.returns[s];
+        float gv;
+        if (p.hp.use_clipped_value_loss) {
+            const float V = p.b.values[s];
+            const float dv = v - V;
+            const float vc = V + fminf(fmaxf(dv, -p.hp.clip_param), p.hp.clip_param);
+            const float l1 = (v - R) * (v - R), l2 = (vc - R) * (vc - R);
+            vl = fmaxf(l1, l2);
+            const bool in_v = dv >= -p.hp.clip_param && dv <= p.hp.clip_param;
+            if (in_v || l1 > l2) gv = 2.0f * (v - R);
+            else if (l1 < l2) gv = 0.0f;
+            else gv = (v - R);                                       // tie with a clipped value: torch.max splits the gradient
+        } else {
+            vl = (R - v) * (R - v);
+            gv = 2.0f * (v - R);
+        }
+        // gradients of loss = mean(surr) + c_v * mean(vl) - c_e * mean(entropy)
+        const float gs = g_logp * p.inv_count;
+        for (int j = 0; j < A; ++j) {
+            const float mu = p.mu[(int64_t)r * A + j], sg = p.std[j], a = p.b.actions[s * A + j];
+            const float d = a - mu;
+            const float gmu = gs * d / (sg * sg);
+            __half h, l;
+            split1(gmu * p.s_g, h, l);
+            p.dmu[(int64_t)r * p.ld_dmu + j] = h;
+            p.dmu[p.plane_dmu + (int64_t)r * p.ld_dmu + j] = l;
+            p.dmut[(int64_t)j * p.ld_dmut + r] = h;
+            p.dmut[p.plane_dmut + (int64_t)j * p.ld_dmut + r] = l;
+            dstd[j] = gs * (d * d - sg * sg) / (sg * sg * sg);
+        }
+        const float gval = p.hp.value_loss_coef * gv * p.inv_count;
+        __half h, l;
+        split1(gval * p.s_g, h, l);
+        p.dv[(int64_t)r * p.ld_dv] = h;
+        p.dv[p.plane_dv + (int64_t)r * p.ld_dv] = l;
+        p.dvt[r] = h;
+        p.dvt[p.plane_dvt + r] = l;
+    } else {
+        for (int j = 0; j < A; ++j) dstd[j] = 0.0f;
+    }
+    float* out = p.partial + (int64_t)blockIdx.x * STAT_SLOTS;
+    float t = block_sum(surr, sh);
+    if (threadIdx.x == 0) out[0] = t;
+    t = block_sum(vl, sh);
+    if (threadIdx.x == 0) out[1] = t;
+    t = block_sum(kl, sh);
+    if (threadIdx.x == 0) out[2] = t;
+    for (int j = 0; j < A; ++j) {
+        t = block_sum(dstd[j], sh);
+        if (threadIdx.x == 0) out[3 + j] = t;
+    }
+}
+
+// sums the per-block rows in block order; stats[0..3] and the std gradient (entropy term: d/dsigma of -c_e * mean(entropy) = -c_e / sigma)
+__global__ void ppo_head_reduce_kernel(const float* __restrict__ partial, int blocks, int A, const float* __restrict__ std, float entropy_coef,
+                                       float world_inv, int count, float* __restrict__ stats, float* __restrict__ gstd) {
+    const int j = threadIdx.x;
+    if (j >= 3 + A) return;
+    float acc = 0.0f;
+    for (int b = 0; b < blocks; ++b) acc += partial[(int64_t)b * STAT_SLOTS + j];
+    if (j < 3) stats[j] = acc;
+    else gstd[j - 3] = acc - entropy_coef * world_inv / std[j - 3];
+    if (j == 0) stats[3] = (float)count;
+}
+
+struct AdaptHeadParams {
+    const float* pred;          // [count][P]
+    const float* priv;          // storage [*, P]
+    const int64_t* indices;
+    int count, P, num_train;
+    float inv_train;            // 1 / (num_train * P * grad_world)
+    float s_g;
+    __half *dz, *dzt;
+    int64_t ld_dz, plane_dz, ld_dzt, plane_dzt;
+    float* partial;
+};
+
+// F.mse_loss(pred[:num_train], target[:num_train]) and its gradient; test loss on the remaining rows (PPO:166-167)
+__global__ void __launch_bounds__(HEAD_THREADS) adapt_head_kernel(const __grid_constant__ AdaptHeadParams p) {
+    __shared__ float sh[HEAD_THREADS / 32];
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    float tr = 0.0f, te = 0.0f;
+    if (r < p.count) {
+        const int64_t s = p.indices ? p.indices[r] : (int64_t)r;
+        for (int j = 0; j < p.P; ++j) {
+            const float d = p.pred[(int64_t)r * p.P + j] - p.priv[s * p.P + j];
+            const float g = r < p.num_train ? 2.0f * d * p.inv_train : 0.0f;
+            if (r < p.num_train) tr += d * d; else te += d * d;
+            __half h, l;
+            split1(g * p.s_g, h, l);
+            p.dz[(int64_t)r * p.ld_dz + j] = h;
+            p.dz[p.plane_dz + (int64_t)r * p.ld_dz + j] = l;
+            p.dzt[(int64_t)j * p.ld_dzt + r] = h;
+            p.dzt[p.plane_dzt + (int64_t)j * p.ld_dzt + r] = l;
+        }
+    }
+    float* out = p.partial + (int64_t)blockIdx.x * STAT_SLOTS;
+    float t = block_sum(tr, sh);
+    if (threadIdx.x == 0) out[0] = t;
+    t = block_sum(te, sh);
+    if (threadIdx.x == 0) out[1] = t;
+}
+__global__ void adapt_head_reduce_kernel(const float* __restrict__ partial, int blocks, int count, int num_train, int P, float* __restrict__ stats) {
+    if (threadIdx.x >= 2) return;
+    float acc = 0.0f;
+    for (int b = 0; b < blocks; ++b) acc += partial[(int64_t)b * STAT_SLOTS + threadIdx.x];
+    stats[4 + 2 * threadIdx.x] = acc;
+    stats[5 + 2 * threadIdx.x] = threadIdx.x == 0 ? (float)num_train * P : (float)(count - num_train) * P;
+}
+
+// Philox4x32-10 (Salmon et al. 2011) for the action sample when no noise is injected
+__device__ __forceinline__ void philox4(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t (&o)[4]) {
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const uint32_t h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        const uint32_t h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
+}
+
+// PPO.act head (PPO:65-77, AC:131-138): sample, log-prob, sigma
+__global__ void act_head_kernel(const float* __restrict__ mean, const float* __restrict__ std, const float* __restrict__ noise,
+                                const float* __restrict__ actions_in, int rows, int A, uint64_t seed, uint64_t step, float* __restrict__ actions,
+                                float* __restrict__ logp_out, float* __restrict__ mean_out, float* __restrict__ sigma_out) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    float logp = 0.0f;
+    for (int j = 0; j < A; ++j) {
+        const float mu = mean[(int64_t)r * A + j], sg = std[j];
+        float a;
+        if (actions_in) a = actions_in[(int64_t)r * A + j];
+        else {
+            float z;
+            if (noise) z = noise[(int64_t)r * A + j];
+            else {
+                uint32_t o[4];
+                philox4((uint32_t)r, (uint32_t)j, (uint32_t)step, (uint32_t)(step >> 32), (uint32_t)seed, (uint32_t)(seed >> 32), o);
+                const float u1 = ((float)(o[0] >> 8) + 0.5f) * (1.0f / 16777216.0f), u2 = ((float)(o[1] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+                z = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+            }
+            a = mu + sg * z;
+        }
+        const float d = a - mu;
+        logp += -(d * d) / (2.0f * sg * sg) - logf(sg) - 0.91893853320467274178f;
+        if (actions) actions[(int64_t)r * A + j] = a;
+        if (mean_out && mean_out != mean) mean_out[(int64_t)r * A + j] = mu;
+        if (sigma_out) sigma_out[(int64_t)r * A + j] = sg;
+    }
+    if (logp_out) logp_out[r] = logp;
+}
+
+// sum of squares of a range of the gradient, per block (fixed order), then the finalisation below
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ partial) {
+    __shared__ float sh[8];
+    float acc = 0.0f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) acc += g[i] * g[i];
+    const float t = block_sum(acc, sh);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+// total norm, clip coefficient (nn.utils.clip_grad_norm_) and the adaptive-KL learning-rate decision (PPO:111-125)
+__global__ void prepare_step_kernel(const float* __restrict__ partial, int blocks, lt_ppo_hparams hp, const float* __restrict__ stats,
+                                    float* __restrict__ lr, float* __restrict__ scalars, float* __restrict__ grad_norm_out) {
+    if (threadIdx.x != 0) return;
+    float ss = 0.0f;
+    for (int b = 0; b < blocks; ++b) ss += partial[b];
+    const float norm = sqrtf(ss);
+    scalars[0] = fminf(hp.max_grad_norm / (norm + 1e-6f), 1.0f);
+    scalars[1] = norm;
+    if (grad_norm_out) *grad_norm_out = norm;
+    if (hp.adaptive_schedule && stats) {
+        const float kl_mean = stats[2] / stats[3];
+        float v = *lr;
+        if (kl_mean > hp.desired_kl * 2.0f) v = fmaxf(hp.lr_min, v / hp.lr_factor);
+        else if (kl_mean < hp.desired_kl / 2.0f && kl_mean > 0.0f) v = fminf(hp.lr_max, v * hp.lr_factor);
+        *lr = v;
+    }
+}
+// torch.optim.Adam (no weight decay, no amsgrad) over params[lo, hi)
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ m,
+                                                   float* __restrict__ v, int64_t lo, int64_t hi, const float* __restrict__ lr_dev, float lr_host,
+                                                   const float* __restrict__ clip, float beta1, float beta2, float eps, float bc1, float bc2_sqrt) {
+    const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= hi) return;
+    const float lr = lr_dev ? *lr_dev : lr_host;
+    const float g = grads[i] * (clip ? *clip : 1.0f);
+    const float mi = beta1 * m[i] + (1.0f - beta1) * g;
+    const float vi = beta2 * v[i] + (1.0f - beta2) * g * g;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    params[i] -= (lr / bc1) * (mi / denom);
+}
+
+__global__ void split_f32_kernel(const float* __restrict__ src, int64_t rows, int cols, float scale, __half* dst, int64_t ld, int64_t plane) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * cols) return;
+    const int64_t r = i / cols;
+    const int c = (int)(i % cols);
+    __half hi, lo;
+    split1(src[i] * scale, hi, lo);
+    dst[r * ld + c] = hi;
+    dst[plane + r * ld + c] = lo;
+}
+
+// ------------------------------------------------------------------------------------------------------------ host side
+struct Operand {
+    const __half* base;
+    int64_t rows, ld, plane;
+};
+inline Operand op(const Planes& pl, int64_t rows) { return Operand{pl.p, rows, pl.ld, pl.plane}; }
+
+// D[M, N] = A[M, K] * B[N, K]^T with the epilogue fields of `p` already set
+int run_gemm(lt_policy* P, const Operand& A, int M, const Operand& B, int N, int K, int splits, ltg::Params& p, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return LT_OK;
+    p.M = M;
+    p.N = N;
+    p.K = K;
+    p.bn = pick_bn(N);
+    const int kb_total = (K + ltg::BK - 1) / ltg::BK;
+    splits = splits < 1 ? 1 : (splits > kb_total ? kb_total : splits);
+    p.kb_per_split = (kb_total + splits - 1) / splits;
+    p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
+    if (!ltg::make_operand_map(&p.tma_a, A.base, M, K, A.ld, A.plane, ltg::BM) ||
+        !ltg::make_operand_map(&p.tma_b, B.base, N, K, B.ld, B.plane, p.bn))
+        return fail(P, LT_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand geometry)");
+    LTP_CUDA(P, ltg::launch(p, P ? P->sm_count : 148, stream));
+    return LT_OK;
+}
+
+int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_out, int k_real0, int c1, int s2, int c2, int64_t& off) {
+    m.n = n_hidden + 1;
+    int prev = k_real0;
+    for (int l = 0; l < m.n; ++l) {
+        Layer& L = m.L[l];
+        L.N = l < n_hidden ? hidden[l] : n_out;
+        L.k_real = prev;
+        if (l == 0) {
+            L.K = P->K0;
+            L.c1 = c1;
+            L.s2 = s2;
+            L.c2 = c2;
+        } else {
+            L.K = prev;
+            L.c1 = prev;
+        }
+        L.w_off = off;
+        off += (int64_t)L.N * L.k_real;
+        L.b_off = off;
+        off += L.N;
+        int rc = alloc_planes(P, L.W, L.N, L.K);
+        if (rc) return rc;
+        if (P->c.training) {
+            rc = alloc_planes(P, L.WT, L.K, L.N);
+            if (rc) return rc;
+        }
+        if (l < n_hidden) {
+            rc = alloc_planes(P, m.Y[l], P->R, L.N);
+            if (rc) return rc;
+            if (P->c.training) {
+                rc = alloc_planes(P, m.YT[l], L.N + 1, P->R);
+                if (rc) return rc;
+                ones_row_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(m.YT[l].p + (int64_t)L.N * m.YT[l].ld, P->R);
+            }
+        }
+        if (P->c.training) {
+            rc = alloc_planes(P, m.dZ[l], P->R, up(L.N, 16));
+            if (rc) return rc;
+            rc = alloc_planes(P, m.dZT[l], L.N, P->R);
+            if (rc) return rc;
+        }
+        prev = L.N;
+    }
+    return alloc_dev(P, m.out, P->R * m.L[m.n - 1].N);
+}
+
+int refresh_mlp(lt_policy* P, Mlp& m, cudaStream_t s) {
+    for (int l = 0; l < m.n; ++l) {
+        Layer& L = m.L[l];
+        const int64_t n = (int64_t)L.N * L.K;
+        split_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->params + L.w_off, L.N, L.K, L.k_real, L.c1, L.s2, L.c2, L.W.p, L.W.ld,
+                                                                        L.W.plane, L.WT.p, L.WT.ld, L.WT.plane);
+    }
+    LTP_CUDA(P, cudaGetLastError());
+    return LT_OK;
+}
+
+// forward of one MLP on `rows` rows of X0; the last layer's fp32 output goes to m.out
+int forward_mlp(lt_policy* P, Mlp& m, int rows, bool train, cudaStream_t s) {
+    for (int l = 0; l < m.n; ++l) {
+        Layer& L = m.L[l];
+        ltg::Params p;
+        memset(&p, 0, sizeof p);
+        p.out_scale = 1.0f / (S_X * S_W);
+        p.bias = P->params + L.b_off;
+        const Operand A = l == 0 ? op(P->X0, rows) : op(m.Y[l - 1], rows);
+        if (l < m.n - 1) {
+            p.mode = ltg::EPI_ELU;
+            p.out_h = m.Y[l].p;
+            p.ld_h = m.Y[l].ld;
+            p.plane_h = m.Y[l].plane;
+            if (train) {
+                p.out_t = m.YT[l].p;
+                p.ld_t = m.YT[l].ld;
+                p.plane_t = m.YT[l].plane;
+            }
+            p.split_scale = S_X;
+        } else {
+            p.mode = ltg::EPI_F32;
+            p.out_f32 = m.out;
+            p.ld_f32 = L.N;
+        }
+        const int rc = run_gemm(P, A, rows, op(L.W, L.N), L.N, L.K, 1, p, s);
+        if (rc) return rc;
+    }
+    return LT_OK;
+}
+
+int dw_splits(lt_policy* P, int N, int Kp1, int count) {
+    const int tiles = ((N + ltg::BM - 1) / ltg::BM) * ((Kp1 + pick_bn(Kp1) - 1) / pick_bn(Kp1));
+    const int kb_total = (count + ltg::BK - 1) / ltg::BK;
+    int s = (2 * P->sm_count + tiles - 1) / tiles;
+    if (s > kb_total) s = kb_total;
+    return s < 1 ? 1 : s;
+}
+
+// backward of one MLP: m.dZ[n-1] / m.dZT[n-1] hold the (scaled) gradient of the last layer's output
+int backward_mlp(lt_policy* P, Mlp& m, int count, float s_g, cudaStream_t s) {
+    for (int l = m.n - 1; l >= 0; --l) {
+        Layer& L = m.L[l];
+        {   // dW_l and db_l:  [N_l, K_l + 1] = dZ_l^T [N_l, count] * [X_{l-1}^T; 1] [K_l + 1, count]^T
+            const Planes& XT = l == 0 ? P->X0T : m.YT[l - 1];
+            const int Kp1 = L.K + 1;
+            ltg::Params p;
+            memset(&p, 0, sizeof p);
+            p.mode = ltg::EPI_PARTIAL;
+            p.out_scale = 1.0f / (s_g * S_X);
+            p.out_f32 = P->partial;
+            p.ld_f32 = up(Kp1, 4);
+            p.split_stride = (int64_t)L.N * p.ld_f32;
+            const int splits = dw_splits(P, L.N, Kp1, count);
+            if ((int64_t)splits * p.split_stride > P->partial_floats) return fail(P, LT_ERR_INVALID, "split-K workspace too small");
+            int rc = run_gemm(P, op(m.dZT[l], L.N), L.N, op(XT, Kp1), Kp1, count, splits, p, s);
+            if (rc) return rc;
+            const int64_t n = (int64_t)L.N * Kp1;
+            reduce_dw_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->partial, p.splits, p.split_stride, p.ld_f32, L.N, L.K, L.k_real, L.c1,
+                                                                        L.s2, L.c2, P->grads + L.w_off, P->grads + L.b_off);
+        }
+        if (l > 0) {   // dZ_{l-1} = (dZ_l * W_l) .* ELU'(Y_{l-1})
+            ltg::Params p;
+            memset(&p, 0, sizeof p);
+            p.mode = ltg::EPI_BWD;
+            p.out_scale = 1.0f / (s_g * S_W);
+            p.split_scale = s_g;
+            p.out_h = m.dZ[l - 1].p;
+            p.ld_h = m.dZ[l - 1].ld;
+            p.plane_h = m.dZ[l - 1].plane;
+            p.out_t = m.dZT[l - 1].p;
+            p.ld_t = m.dZT[l - 1].ld;
+            p.plane_t = m.dZT[l - 1].plane;
+            p.act_h = m.Y[l - 1].p;
+            p.ld_act = m.Y[l - 1].ld;
+            p.plane_act = m.Y[l - 1].plane;
+            p.act_inv_scale = 1.0f / S_X;
+            const int rc = run_gemm(P, op(m.dZ[l], count), count, op(L.WT, L.K), L.K, L.N, 1, p, s);
+            if (rc) return rc;
+        }
+    }
+    LTP_CUDA(P, cudaGetLastError());
+    return LT_OK;
+}
+
+int pack(lt_policy* P, const float* obs_history, const float* priv, const int64_t* indices, int rows, int teacher, bool train, cudaStream_t s) {
+    pack_x0_kernel<<<(unsigned)((rows + 31) / 32), 256, 0, s>>>(obs_history, priv, indices, rows, P->Din, P->P, teacher, P->X0.p, P->X0.ld, P->X0.plane,
+                                                               train ? P->X0T.p : nullptr, P->X0T.ld, P->X0T.plane);
+    LTP_CUDA(P, cudaGetLastError());
+    return LT_OK;
+}
+int scatter_latent(lt_policy* P, int rows, bool train, cudaStream_t s) {
+    scatter_latent_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(P->adapt.out, rows, P->P, P->Din, P->X0.p, P->X0.ld, P->X0.plane,
+                                                                        train ? P->X0T.p : nullptr, P->X0T.ld, P->X0T.plane);
+    LTP_CUDA(P, cudaGetLastError());
+    return LT_OK;
+}
+
+int check_ready(lt_policy* P, int rows) {
+    if (!P) return LT_ERR_INVALID;
+    if (!P->params) return fail(P, LT_ERR_UNBOUND, "lt_policy_bind_params was never called");
+    if (rows <= 0 || rows > P->R) return fail(P, LT_ERR_INVALID, "rows outside (0, max_rows]");
+    return LT_OK;
+}
+
+float grad_scale_for(int count) {
+    int e = 0;
+    while ((1ll << e) < count) ++e;
+    return ldexpf(1.0f, e);
+}
+
+}   // namespace
+
+// ================================================================================================================ C ABI
+extern "C" {
+
+int lt_policy_config_bytes(void) { return (int)sizeof(lt_policy_config); }
+
+const char* lt_policy_last_error(const lt_policy* p) { return p ? p->err.c_str() : g_policy_error.c_str(); }
+
+int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
+    if (!cfg || !out) return LT_ERR_INVALID;
+    *out = nullptr;
+    if (cfg->struct_bytes != (int)sizeof(lt_policy_config)) return fail(nullptr, LT_ERR_INVALID, "lt_policy_config size mismatch: rebuild");
+    int dev = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, LT_ERR_NO_DEVICE, "no sm_100 device: the actor-critic kernels have no CPU fallback");
+    if (cfg->num_obs_history <= 0 || cfg->num_privileged_obs <= 0 || cfg->num_actions <= 0 || cfg->num_actions > STAT_SLOTS - 3 ||
+        cfg->num_actions > 32 || cfg->max_rows <= 0 || cfg->n_adaptation_hidden < 1 || cfg->n_actor_hidden < 1 || cfg->n_critic_hidden < 1 ||
+        cfg->n_adaptation_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_actor_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_critic_hidden > LT_POLICY_MAX_HIDDEN)
+        return fail(nullptr, LT_ERR_INVALID, "unsupported actor-critic geometry");
+    if (!ltg::encode_fn()) return fail(nullptr, LT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    lt_policy* P = new lt_policy();
+    P->c = *cfg;
+    P->sm_count = prop.multiProcessorCount;
+    P->R = up(cfg->max_rows, 128);
+    P->Din = cfg->num_obs_history;
+    P->P = cfg->num_privileged_obs;
+    P->A = cfg->num_actions;
+    P->K0 = P->Din + 2 * P->P;
+    int rc = alloc_planes(P, P->X0, P->R, P->K0);
+    if (!rc && cfg->training) {
+        rc = alloc_planes(P, P->X0T, P->K0 + 1, P->R);
+        if (!rc) ones_row_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(P->X0T.p + (int64_t)P->K0 * P->X0T.ld, P->R);
+    }
+    int64_t off = P->A;                                         // std first
+    if (!rc) rc = build_mlp(P, P->adapt, cfg->n_adaptation_hidden, cfg->adaptation_hidden, P->P, P->Din, P->Din, 0, 0, off);
+    if (!rc) rc = build_mlp(P, P->actor, cfg->n_actor_hidden, cfg->actor_hidden, P->A, P->Din + P->P, P->Din + P->P, 0, 0, off);
+    if (!rc) rc = build_mlp(P, P->critic, cfg->n_critic_hidden, cfg->critic_hidden, 1, P->Din + P->P, P->Din, P->Din + P->P, P->P, off);
+    P->n_params = off;
+    if (!rc && cfg->training) {
+        int64_t need = 0;
+        Mlp* ms[3] = {&P->adapt, &P->actor, &P->critic};
+        for (Mlp* m : ms)
+            for (int l = 0; l < m->n; ++l) {
+                const int Kp1 = m->L[l].K + 1;
+                const int64_t f = (int64_t)dw_splits(P, m->L[l].N, Kp1, (int)P->R) * m->L[l].N * up(Kp1, 4);
+                if (f > need) need = f;
+            }
+        P->partial_floats = need;
+        rc = alloc_dev(P, P->partial, need);
+    }
+    const int64_t head_blocks = (P->R + HEAD_THREADS - 1) / HEAD_THREADS;
+    if (!rc) rc = alloc_dev(P, P->head_partial, head_blocks * STAT_SLOTS);
+    if (!rc) rc = alloc_dev(P, P->norm_partial, 1024);
+    if (!rc) rc = alloc_dev(P, P->scalars, 8);
+    if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = fail(P, LT_ERR_CUDA, "initialisation kernels failed");
+    if (rc) {
+        g_policy_error = P->err;
+        lt_policy_destroy(P);
+        return rc;
+    }
+    *out = P;
+    return LT_OK;
+}
+
+void lt_policy_destroy(lt_policy* p) {
+    if (!p) return;
+    for (void* d : p->allocs) cudaFree(d);
+    delete p;
+}
+
+int64_t lt_policy_num_params(const lt_policy* p) { return p ? p->n_params : 0; }
+
+int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi) {
+    if (!p || !lo || !hi) return LT_ERR_INVALID;
+    *lo = p->adapt.L[0].w_off;
+    *hi = p->actor.L[0].w_off;
+    return LT_OK;
+}
+
+int lt_policy_bind_params(lt_policy* p, float* params, float* grads) {
+    if (!p || !params) return LT_ERR_INVALID;
+    if (p->c.training && !grads) return fail(p, LT_ERR_INVALID, "a training policy needs a gradient buffer");
+    p->params = params;
+    p->grads = grads;
+    return LT_OK;
+}
+
+int lt_policy_refresh(lt_policy* p, void* stream) {
+    if (!p) return LT_ERR_INVALID;
+    if (!p->params) return fail(p, LT_ERR_UNBOUND, "lt_policy_bind_params was never called");
+    int rc = refresh_mlp(p, p->adapt, (cudaStream_t)stream);
+    if (!rc) rc = refresh_mlp(p, p->actor, (cudaStream_t)stream);
+    if (!rc) rc = refresh_mlp(p, p->critic, (cudaStream_t)stream);
+    return rc;
+}
+
+int lt_policy_forward(lt_policy* p, const float* obs_history, const float* privileged_obs, int32_t rows, int32_t teacher_latent, float* latent,
+                      float* action_mean, float* value, void* stream) {
+    int rc = check_ready(p, rows);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!obs_history) return fail(p, LT_ERR_INVALID, "obs_history is NULL");
+    if ((value || teacher_latent) && !privileged_obs) return fail(p, LT_ERR_INVALID, "privileged_obs is NULL but the critic / teacher needs it");
+    rc = pack(p, obs_history, privileged_obs, nullptr, rows, teacher_latent, false, s);
+    if (rc) return rc;
+    if (latent || (action_mean && !teacher_latent)) {
+        rc = forward_mlp(p, p->adapt, rows, false, s);
+        if (rc) return rc;
+        if (latent) LTP_CUDA(p, cudaMemcpyAsync(latent, p->adapt.out, (size_t)rows * p->P * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        if (action_mean && !teacher_latent) {
+            rc = scatter_latent(p, rows, false, s);
+            if (rc) return rc;
+        }
+    }
+    if (action_mean) {
+        rc = forward_mlp(p, p->actor, rows, false, s);
+        if (rc) return rc;
+        LTP_CUDA(p, cudaMemcpyAsync(action_mean, p->actor.out, (size_t)rows * p->A * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    }
+    if (value) {
+        rc = forward_mlp(p, p->critic, rows, false, s);
+        if (rc) return rc;
+        LTP_CUDA(p, cudaMemcpyAsync(value, p->critic.out, (size_t)rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    }
+    return LT_OK;
+}
+
+int lt_policy_act(lt_policy* p, const float* obs_history, const float* privileged_obs, int32_t rows, const float* normal_noise,
+                  const float* actions_in, uint64_t seed, uint64_t step, float* actions, float* actions_log_prob, float* action_mean,
+                  float* action_sigma, float* value, void* stream) {
+    int rc = check_ready(p, rows);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!obs_history || !privileged_obs) return fail(p, LT_ERR_INVALID, "obs_history / privileged_obs is NULL");
+    rc = pack(p, obs_history, privileged_obs, nullptr, rows, 0, false, s);
+    if (!rc) rc = forward_mlp(p, p->adapt, rows, false, s);
+    if (!rc) rc = scatter_latent(p, rows, false, s);
+    if (!rc) rc = forward_mlp(p, p->actor, rows, false, s);
+    if (!rc) rc = forward_mlp(p, p->critic, rows, false, s);
+    if (rc) return rc;
+    act_head_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(p->actor.out, p->params, normal_noise, actions_in, rows, p->A, seed, step, actions,
+                                                                  actions_log_prob, action_mean, action_sigma);
+    LTP_CUDA(p, cudaGetLastError());
+    if (value) LTP_CUDA(p, cudaMemcpyAsync(value, p->critic.out, (size_t)rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    return LT_OK;
+}
+
+int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64_t* indices, int32_t count, const lt_ppo_hparams* hp,
+                          int32_t grad_world, float* stats, void* stream) {
+    int rc = check_ready(p, count);
+    if (rc) return rc;
+    if (!p->c.training) return fail(p, LT_ERR_INVALID, "policy was created with training = 0");
+    if (!batch || !hp || !stats) return LT_ERR_INVALID;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int world = grad_world > 1 ? grad_world : 1;
+    const float s_g = grad_scale_for(count * world);
+    rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
+    if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
+    if (!rc) rc = scatter_latent(p, count, true, s);
+    if (!rc) rc = forward_mlp(p, p->actor, count, true, s);
+    if (!rc) rc = forward_mlp(p, p->critic, count, true, s);
+    if (rc) return rc;
+    const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
+    {
+        HeadParams h;
+        memset(&h, 0, sizeof h);
+        h.b = *batch;
+        h.indices = indices;
+        h.count = count;
+        h.A = p->A;
+        h.mu = p->actor.out;
+        h.value = p->critic.out;
+        h.std = p->params;
+        h.hp = *hp;
+        h.inv_count = 1.0f / ((float)count * (float)world);
+        h.s_g = s_g;
+        const Mlp &a = p->actor, &c = p->critic;
+        h.dmu = a.dZ[a.n - 1].p; h.ld_dmu = a.dZ[a.n - 1].ld; h.plane_dmu = a.dZ[a.n - 1].plane;
+        h.dmut = a.dZT[a.n - 1].p; h.ld_dmut = a.dZT[a.n - 1].ld; h.plane_dmut = a.dZT[a.n - 1].plane;
+        h.dv = c.dZ[c.n - 1].p; h.ld_dv = c.dZ[c.n - 1].ld; h.plane_dv = c.dZ[c.n - 1].plane;
+        h.dvt = c.dZT[c.n - 1].p; h.ld_dvt = c.dZT[c.n - 1].ld; h.plane_dvt = c.dZT[c.n - 1].plane;
+        h.partial = p->head_partial;
+        ppo_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
+        ppo_head_reduce_kernel<<<1, 64, 0, s>>>(p->head_partial, blocks, p->A, p->params, hp->entropy_coef, 1.0f / (float)world, count, stats,
+                                                p->grads);
+        LTP_CUDA(p, cudaGetLastError());
+    }
+    rc = backward_mlp(p, p->critic, count, s_g, s);
+    if (!rc) rc = backward_mlp(p, p->actor, count, s_g, s);
+    if (rc) return rc;
+    {   // the latent columns of the actor's input gradient are the adaptation module's output gradient (AC:129-130)
+        Mlp& a = p->actor;
+        Mlp& ad = p->adapt;
+        Layer& L = a.L[0];
+        ltg::Params g;
+        memset(&g, 0, sizeof g);
+        g.mode = ltg::EPI_BWD;                                   // act_h == NULL: no activation derivative (last layer is linear)
+        g.out_scale = 1.0f / (s_g * S_W);
+        g.split_scale = s_g;
+        Planes& dz = ad.dZ[ad.n - 1];
+        Planes& dzt = ad.dZT[ad.n - 1];
+        g.out_h = dz.p; g.ld_h = dz.ld; g.plane_h = dz.plane;
+        g.out_t = dzt.p; g.ld_t = dzt.ld; g.plane_t = dzt.plane;
+        Operand B{L.WT.p + (int64_t)p->Din * L.WT.ld, p->P, L.WT.ld, L.WT.plane};
+        rc = run_gemm(p, op(a.dZ[0], count), count, B, p->P, L.N, 1, g, s);
+        if (!rc) rc = backward_mlp(p, ad, count, s_g, s);
+    }
+    return rc;
+}
+
+int lt_ppo_minibatch_apply(lt_policy* p, const lt_ppo_hparams* hp, const float* stats, float* lr, float* adam_m, float* adam_v, int32_t adam_step,
+                           float* grad_norm_out, void* stream) {
+    if (!p || !hp || !lr || !adam_m || !adam_v || adam_step < 1) return LT_ERR_INVALID;
+    if (!p->params || !p->grads) return fail(p, LT_ERR_UNBOUND, "lt_policy_bind_params was never called");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int nb = 512;
+    sumsq_kernel<<<nb, 256, 0, s>>>(p->grads, p->n_params, p->norm_partial);
+    prepare_step_kernel<<<1, 32, 0, s>>>(p->norm_partial, nb, *hp, stats, lr, p->scalars, grad_norm_out);
+    const float bc1 = 1.0f - powf(hp->adam_beta1, (float)adam_step);
+    const float bc2 = sqrtf(1.0f - powf(hp->adam_beta2, (float)adam_step));
+    adam_kernel<<<(unsigned)((p->n_params + 255) / 256), 256, 0, s>>>(p->params, p->grads, adam_m, adam_v, 0, p->n_params, lr, 0.0f, p->scalars,
+                                                                     hp->adam_beta1, hp->adam_beta2, hp->adam_eps, bc1, bc2);
+    LTP_CUDA(p, cudaGetLastError());
+    return lt_policy_refresh(p, stream);
+}
+
+int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64_t* indices, int32_t count, int32_t num_train, int32_t grad_world,
+                       float* stats, void* stream) {
+    int rc = check_ready(p, count);
+    if (rc) return rc;
+    if (!p->c.training) return fail(p, LT_ERR_INVALID, "policy was created with training = 0");
+    if (!batch || !stats || num_train < 0 || num_train > count) return LT_ERR_INVALID;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int world = grad_world > 1 ? grad_world : 1;
+    const float s_g = grad_scale_for(count * world);
+    rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
+    if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
+    if (rc) return rc;
+    const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
+    AdaptHeadParams h;
+    memset(&h, 0, sizeof h);
+    h.pred = p->adapt.out;
+    h.priv = batch->privileged_obs;
+    h.indices = indices;
+    h.count = count;
+    h.P = p->P;
+    h.num_train = num_train;
+    h.inv_train = num_train > 0 ? 1.0f / ((float)num_train * (float)p->P * (float)world) : 0.0f;
+    h.s_g = s_g;
+    Mlp& ad = p->adapt;
+    h.dz = ad.dZ[ad.n - 1].p; h.ld_dz = ad.dZ[ad.n - 1].ld; h.plane_dz = ad.dZ[ad.n - 1].plane;
+    h.dzt = ad.dZT[ad.n - 1].p; h.ld_dzt = ad.dZT[ad.n - 1].ld; h.plane_dzt = ad.dZT[ad.n - 1].plane;
+    h.partial = p->head_partial;
+    adapt_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
+    adapt_head_reduce_kernel<<<1, 32, 0, s>>>(p->head_partial, blocks, count, num_train, p->P, stats);
+    LTP_CUDA(p, cudaGetLastError());
+    return backward_mlp(p, ad, count, s_g, s);
+}
+
+int lt_adaptation_apply(lt_policy* p, const lt_ppo_hparams* hp, float lr, float* adam_m, float* adam_v, int32_t adam_step, void* stream) {
+    if (!p || !hp || !adam_m || !adam_v || adam_step < 1) return LT_ERR_INVALID;
+    if (!p->params || !p->grads) return fail(p, LT_ERR_UNBOUND, "lt_policy_bind_params was never called");
+    cudaStream_t s = (cudaStream_t)stream;
+    int64_t lo, hi;
+    lt_policy_adaptation_slice(p, &lo, &hi);
+    const float bc1 = 1.0f - powf(hp->adam_beta1, (float)adam_step);
+    const float bc2 = sqrtf(1.0f - powf(hp->adam_beta2, (float)adam_step));
+    adam_kernel<<<(unsigned)((hi - lo + 255) / 256), 256, 0, s>>>(p->params, p->grads, adam_m, adam_v, lo, hi, nullptr, lr, nullptr, hp->adam_beta1,
+                                                                 hp->adam_beta2, hp->adam_eps, bc1, bc2);
+    LTP_CUDA(p, cudaGetLastError());
+    return refresh_mlp(p, p->adapt, s);
+}
+
+int lt_linear_f32(const float* a, const float* b, const float* bias, float* out, int32_t M, int32_t N, int32_t K, int32_t splits, void* stream) {
+    if (!a || !b || !out || M <= 0 || N <= 0 || K <= 0) return LT_ERR_INVALID;
+    int dev = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, LT_ERR_NO_DEVICE, "no sm_100 device");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t ld = up(K, 8);
+    __half *pa = nullptr, *pb = nullptr;
+    float* part = nullptr;
+    LTP_CUDA(nullptr, cudaMalloc(&pa, (size_t)2 * M * ld * 2));
+    LTP_CUDA(nullptr, cudaMalloc(&pb, (size_t)2 * N * ld * 2));
+    LTP_CUDA(nullptr, cudaMemsetAsync(pa, 0, (size_t)2 * M * ld * 2, s));
+    LTP_CUDA(nullptr, cudaMemsetAsync(pb, 0, (size_t)2 * N * ld * 2, s));
+    split_f32_kernel<<<(unsigned)(((int64_t)M * K + 255) / 256), 256, 0, s>>>(a, M, K, S_X, pa, ld, (int64_t)M * ld);
+    split_f32_kernel<<<(unsigned)(((int64_t)N * K + 255) / 256), 256, 0, s>>>(b, N, K, S_W, pb, ld, (int64_t)N * ld);
+    ltg::Params p;
+    memset(&p, 0, sizeof p);
+    p.out_scale = 1.0f / (S_X * S_W);
+    int rc;
+    if (splits <= 1) {
+        p.mode = ltg::EPI_F32;
+        p.bias = bias;
+        p.out_f32 = out;
+        p.ld_f32 = N;
+        rc = run_gemm(nullptr, Operand{pa, M, ld, (int64_t)M * ld}, M, Operand{pb, N, ld, (int64_t)N * ld}, N, K, 1, p, s);
+    } else {
+        LTP_CUDA(nullptr, cudaMalloc(&part, (size_t)splits * M * N * 4));
+        p.mode = ltg::EPI_PARTIAL;
+        p.out_f32 = part;
+        p.ld_f32 = N;
+        p.split_stride = (int64_t)M * N;
+        rc = run_gemm(nullptr, Operand{pa, M, ld, (int64_t)M * ld}, M, Operand{pb, N, ld, (int64_t)N * ld}, N, K, splits, p, s);
+        if (!rc) sum_partials_kernel<<<(unsigned)(((int64_t)M * N + 255) / 256), 256, 0, s>>>(part, p.splits, (int64_t)M * N, N, bias, out);
+    }
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(pa);
+    cudaFree(pb);
+    if (part) cudaFree(part);
+    if (rc) return rc;
+    LTP_CUDA(nullptr, e);
+    return LT_OK;
+}
+
+}   // extern "C"

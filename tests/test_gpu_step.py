@@ -243,6 +243,8 @@ def test_sharded_engines_bucket_by_the_all_env_sum():
             v = np.asarray(v)
             if key == "tile_heights":
                 o[key] = v
+            elif key in ("root_states", "dof_state"):            # Isaac Gym layouts: [N * actors, 13], [N * dofs, 2]
+                o[key] = v.reshape(N, -1, v.shape[-1])[ids].reshape(-1, v.shape[-1])
             elif v.ndim >= 1 and v.shape[0] == N:
                 o[key] = v[ids]
             elif v.ndim >= 2 and v.shape[1] == N:
