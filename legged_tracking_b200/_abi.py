@@ -101,7 +101,11 @@ lt_ppo_batch_ptrs = _mk("lt_ppo_batch_ptrs")
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
            "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
            "lt_reward_sign_prepass", "lt_term_sum_buffer", "lt_set_term_scales", "lt_counters", "lt_rollout_store", "lt_gae",
-           "lt_normalize_advantages", "lt_build_tunnel_tiles"]
+           "lt_normalize_advantages", "lt_build_tunnel_tiles",
+           # include/lt_policy.h
+           "lt_policy_config_bytes", "lt_policy_create", "lt_policy_destroy", "lt_policy_last_error", "lt_policy_num_params",
+           "lt_policy_bind_params", "lt_policy_refresh", "lt_policy_forward", "lt_policy_act", "lt_ppo_minibatch_grad",
+           "lt_ppo_minibatch_apply", "lt_adaptation_grad", "lt_adaptation_apply", "lt_policy_adaptation_slice", "lt_linear_f32"]
 
 
 def declared_functions(path=None):
