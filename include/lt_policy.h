@@ -118,6 +118,19 @@ int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi);
 int lt_linear_f32(const float* a, const float* b, const float* bias, float* out, int32_t M, int32_t N, int32_t K, int32_t splits,
                   void* stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contraction as lt_linear_f32 with splits = 1 --
+ * out[M, N] = a[M, K] * b[N, K]^T (+ bias), fp32 in / out on the device, same kernel, same operand scales, bit-identical
+ * result -- but the call allocates NOTHING (no cudaMalloc / cudaFree / allocating library routine): the fp16 operand planes
+ * live in a static device array of LT_LINEAR_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   - limit: 4 * (M + N) * roundup(K, 8) bytes (each operand rounded up to 256) must fit in the array; larger shapes are
+ *     rejected with LT_ERR_INVALID and a message in lt_policy_last_error(NULL) -- use lt_linear_f32 for those;
+ *   - asynchronous on `stream`, no host synchronisation (lt_linear_f32 synchronises because it frees its buffers);
+ *   - ALL calls on a device share the one array and it keeps the last call's contents (the call clears what it uses first):
+ *     two calls that overlap on the GPU (different streams, or graph branches) race -- serialise them. */
+#define LT_LINEAR_STATIC_SCRATCH_BYTES 8388608
+int lt_linear_f32_static(const float* a, const float* b, const float* bias, float* out, int32_t M, int32_t N, int32_t K, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

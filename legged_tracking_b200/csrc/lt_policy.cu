@@ -709,6 +709,36 @@ float grad_scale_for(int count) {
 
 }   // namespace
 
+// ---------------------------------------------------------------------------------------------------------------- static scratch
+// Scratch of lt_linear_f32_static (include/lt_policy.h): the fp16 operand planes of ONE call, in a fixed array instead of
+// cudaMalloc'd buffers.  Every GPU that loads the library holds these LT_LINEAR_STATIC_SCRATCH_BYTES until the process exits.
+// In HOST code the name below is only a stand-in for the symbol, not a device address: the address handed to kernels and TMA
+// maps comes from cudaGetSymbolAddress, looked up once per device with that device current (static_scratch_ptr).
+static __device__ __align__(256) unsigned char g_linear_static_scratch[LT_LINEAR_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+unsigned char* g_static_scratch_ptr[MAX_DEVICES] = {nullptr};
+
+// device address of g_linear_static_scratch on the CURRENT device (cached per device ordinal); NULL + message on failure
+unsigned char* static_scratch_ptr(int dev) {
+    if (dev < 0 || dev >= MAX_DEVICES) {
+        set_error(nullptr, "lt_linear_f32_static: device ordinal outside the per-device address table");
+        return nullptr;
+    }
+    if (!g_static_scratch_ptr[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_linear_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_error(nullptr, std::string("cudaGetSymbolAddress(g_linear_static_scratch): ") + cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_static_scratch_ptr[dev] = static_cast<unsigned char*>(ptr);
+    }
+    return g_static_scratch_ptr[dev];
+}
+}   // namespace
+
 // ================================================================================================================ C ABI
 extern "C" {
 
@@ -1024,6 +1054,39 @@ int lt_linear_f32(const float* a, const float* b, const float* bias, float* out,
     if (rc) return rc;
     LTP_CUDA(nullptr, e);
     return LT_OK;
+}
+
+int lt_linear_f32_static(const float* a, const float* b, const float* bias, float* out, int32_t M, int32_t N, int32_t K, void* stream) {
+    if (!a || !b || !out || M <= 0 || N <= 0 || K <= 0) return fail(nullptr, LT_ERR_INVALID, "lt_linear_f32_static: NULL operand or empty shape");
+    int dev = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, LT_ERR_NO_DEVICE, "no sm_100 device");
+    const int64_t ld = up(K, 8);
+    const int64_t a_bytes = up((int64_t)2 * M * ld * 2, 256), b_bytes = up((int64_t)2 * N * ld * 2, 256);
+    if (a_bytes + b_bytes > (int64_t)LT_LINEAR_STATIC_SCRATCH_BYTES)
+        return fail(nullptr, LT_ERR_INVALID,
+                    "lt_linear_f32_static: the fp16 operand planes of this shape need " + std::to_string(a_bytes + b_bytes) +
+                        " bytes of scratch, the static array holds " + std::to_string((long long)LT_LINEAR_STATIC_SCRATCH_BYTES) +
+                        " (4 * (M + N) * roundup(K, 8) must fit); use lt_linear_f32");
+    unsigned char* scratch = static_scratch_ptr(dev);
+    if (!scratch) return LT_ERR_CUDA;
+    cudaStream_t s = (cudaStream_t)stream;
+    __half* pa = reinterpret_cast<__half*>(scratch);
+    __half* pb = reinterpret_cast<__half*>(scratch + a_bytes);
+    // the array keeps the previous call's planes: the pad columns K..ld of this call's rows must read as zero
+    LTP_CUDA(nullptr, cudaMemsetAsync(scratch, 0, (size_t)(a_bytes + b_bytes), s));
+    split_f32_kernel<<<(unsigned)(((int64_t)M * K + 255) / 256), 256, 0, s>>>(a, M, K, S_X, pa, ld, (int64_t)M * ld);
+    split_f32_kernel<<<(unsigned)(((int64_t)N * K + 255) / 256), 256, 0, s>>>(b, N, K, S_W, pb, ld, (int64_t)N * ld);
+    LTP_CUDA(nullptr, cudaGetLastError());
+    ltg::Params p;
+    memset(&p, 0, sizeof p);
+    p.out_scale = 1.0f / (S_X * S_W);
+    p.mode = ltg::EPI_F32;
+    p.bias = bias;
+    p.out_f32 = out;
+    p.ld_f32 = N;
+    return run_gemm(nullptr, Operand{pa, M, ld, (int64_t)M * ld}, M, Operand{pb, N, ld, (int64_t)N * ld}, N, K, 1, p, s);
 }
 
 }   // extern "C"
