@@ -17,8 +17,8 @@ import sys
 import threading
 import time
 
-# rank 0 prints exactly ONE line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION in this image) off it
-os.environ["NCCL_DEBUG"] = os.environ.get("LT_NCCL_DEBUG", "WARN")
+# rank 0 prints exactly ONE line on stdout.  NCCL_DEBUG is left as the caller set it: _quiet_stdout() below points fd 1 at stderr
+# for the whole run, so NCCL's banner / INFO log cannot land on stdout.
 
 import numpy as np
 import torch
@@ -254,24 +254,37 @@ def ppo_iteration(eng, rs, graphs, flat, dev, dist, iters):
         losses = alg.update()
         ev[3].record()
         torch.cuda.synchronize()
-        return [ev[i].elapsed_time(ev[i + 1]) for i in range(3)], losses
-    iteration(0)                                             # warm-up (cuBLAS heuristics, allocator)
+        return [ev[i].elapsed_time(ev[i + 1]) for i in range(3)] + [alg.exchange.seconds() * 1e3], losses
+    alg.exchange.timed = True
+    iteration(0)                                             # warm-up (workspaces, allocator, NCCL channels)
     if dist:
         dist.barrier()
+    alg.exchange.calls = alg.exchange.bytes = 0
     parts, losses = [], None
     for it in range(iters):
         p_, losses = iteration(1 + it * T)
         parts.append(p_)
     parts = np.asarray(parts).mean(axis=0)
-    tot = torch.tensor([float(parts.sum())] + [float(x) for x in parts], device=dev)
+    tot = torch.tensor([float(parts[:3].sum())] + [float(x) for x in parts], device=dev)
     if dist:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     tot = tot.tolist()
+    calls, nbytes = alg.exchange.calls // max(iters, 1), alg.exchange.bytes // max(iters, 1)
+    n_params = ac.num_params
+    flop_fwd = 2.0 * sum(int(np.prod(shape)) for key, shape, _, _ in ac.layout if key.endswith(".weight"))
+    mb_rows = N * T // ppo.PPO_Args.num_mini_batches
+    n_mb = ppo.PPO_Args.num_learning_epochs * ppo.PPO_Args.num_mini_batches
+    ad_w = 2.0 * sum(int(np.prod(shape)) for key, shape, _, _ in ac.layout if key.startswith("adaptation_module") and key.endswith(".weight"))
+    update_flop = n_mb * mb_rows * (3.0 * flop_fwd + 3.0 * ad_w)         # fwd + dX + dW of the three bodies, + the adaptation step
     del alg, ac
     torch.cuda.empty_cache()
     return {"iter_ms": tot[0], "rollout_ms": tot[1], "gae_ms": tot[2], "update_ms": tot[3], "iters_timed": iters,
+            "allreduce_ms": tot[4], "allreduce_calls": calls, "allreduce_bytes": nbytes,
             "num_steps_per_env": T, "epochs": ppo.PPO_Args.num_learning_epochs, "mini_batches": ppo.PPO_Args.num_mini_batches,
-            "samples_per_iter_per_gpu": N * T, "gemm": "fp32 cuBLAS via torch autograd (TF32 off, as the reference)",
+            "samples_per_iter_per_gpu": N * T, "params": n_params,
+            "gemm": "hand-written tcgen05 kernel (csrc/lt_gemm.cuh): fp16-split x3 products, fp32 accumulation in TMEM, TMA-fed",
+            "update_fp32_equiv_tflops": update_flop / (tot[3] * 1e-3) / 1e12 if tot[3] > 0 else None,
+            "update_tensor_tflops": 3.0 * update_flop / (tot[3] * 1e-3) / 1e12 if tot[3] > 0 else None,
             "finite": bool(all(np.isfinite(x) for x in losses))}
 
 

@@ -28,6 +28,14 @@ extern "C" {
 
 #define LT_POLICY_MAX_HIDDEN 4
 
+/* AC_Args.activation through get_activation (AC:162-178); 'crelu' maps to ReLU there */
+#define LT_ACT_ELU 0
+#define LT_ACT_SELU 1
+#define LT_ACT_RELU 2
+#define LT_ACT_LRELU 3
+#define LT_ACT_TANH 4
+#define LT_ACT_SIGMOID 5
+
 typedef struct lt_policy_config {
     int32_t struct_bytes;                 /* sizeof(lt_policy_config): ABI check */
     int32_t num_obs_history;              /* H * num_obs: width of the observation history (AC:43, 57) */
@@ -38,6 +46,7 @@ typedef struct lt_policy_config {
     int32_t n_critic_hidden, critic_hidden[LT_POLICY_MAX_HIDDEN];             /* AC_Args.critic_hidden_dims */
     int32_t max_rows;                     /* row capacity of the workspaces: >= envs per act() and >= minibatch size */
     int32_t training;                     /* 0: inference only (no gradient workspaces) */
+    int32_t activation;                   /* LT_ACT_*: between the Linear layers of all three bodies (AC:40) */
 } lt_policy_config;
 
 /* PPO_Args (PPO:13-30) + torch.optim.Adam defaults */
@@ -84,7 +93,8 @@ int lt_policy_forward(lt_policy* p, const float* obs_history, const float* privi
 
 /* PPO.act (PPO:65-77) fused: forward, Normal(mean, std) sample, log-prob, value.  normal_noise: [rows, num_actions] standard
  * normal draws or NULL -> in-kernel Philox4x32-10 + Box-Muller keyed (seed, step, row, action).  actions_in != NULL replays
- * given actions instead of sampling (parity tests).  Outputs: actions, action_mean, action_sigma [rows, A]; log_prob, value [rows]. */
+ * given actions instead of sampling (parity tests).  Outputs: actions, action_mean, action_sigma [rows, A]; log_prob, value [rows];
+ * any of them may be NULL.  value == NULL skips the critic (ActorCritic.act alone, AC:133-135) and privileged_obs may then be NULL. */
 int lt_policy_act(lt_policy* p, const float* obs_history, const float* privileged_obs, int32_t rows, const float* normal_noise,
                   const float* actions_in, uint64_t seed, uint64_t step, float* actions, float* actions_log_prob, float* action_mean,
                   float* action_sigma, float* value, void* stream);
@@ -110,6 +120,10 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
                        int32_t grad_world, float* stats, void* stream);
 /* Second half: Adam step (no clipping) on the adaptation slice with its own state (same flat indexing as params), lr host value. */
 int lt_adaptation_apply(lt_policy* p, const lt_ppo_hparams* hp, float lr, float* adam_m, float* adam_v, int32_t adam_step, void* stream);
+/* Diagnostic: DEVICE float[2][3 * (LT_POLICY_MAX_HIDDEN + 1)], the per-tensor power-of-two scales the backward passes of
+ * lt_ppo_minibatch_grad ([0]) and lt_adaptation_grad ([1]) currently use for the gradient operand planes (rows: adaptation
+ * module, actor, critic; columns: layer).  See "gradient scales" in csrc/lt_policy.cu. */
+const float* lt_policy_grad_scales(const lt_policy* p);
 /* [lo, hi) of the adaptation module inside the flat parameter vector */
 int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi);
 

@@ -14,8 +14,8 @@
 //               accumulators double-buffered in TMEM (2 x BN_MAX columns) so tile i+1's main loop overlaps tile i's epilogue
 //   warps 2..5  epilogue: thread <-> accumulator row (TMEM lane); tcgen05.ld 32 columns at a time, then one of
 //               EPI_F32      out = acc * scale + bias                                    -> fp32 [M, ld]
-//               EPI_ELU      y = ELU(acc * scale + bias)                                 -> fp16 planes, row-major (+ transposed)
-//               EPI_BWD      dz = acc * scale * ELU'(y_prev), ELU'(y) = y > 0 ? 1 : y+1   -> fp16 planes, row-major (+ transposed)
+//               EPI_ELU      y = act(acc * scale + bias), act = ELU unless Params::act says else -> fp16 planes, row-major (+ transposed)
+//               EPI_BWD      dz = acc * scale * act'(y_prev), e.g. ELU'(y) = y > 0 ? 1 : y+1   -> fp16 planes, row-major (+ transposed)
 //               EPI_PARTIAL  acc * scale -> fp32 split-K partial [split][M, ld]
 // Tiles are (split, m-block, n-block) triples, n fastest, so that the CTAs running at the same time share A rows in L2.
 // Rows / columns / k beyond the tensor bounds are zero-filled by TMA and masked in the epilogue: no padding requirements
@@ -33,7 +33,9 @@ constexpr int BK = 64;           // k per ring slot = one 128-byte swizzle row o
 constexpr int THREADS = 192;
 constexpr float OPERAND_MAX = 60000.0f;      // fp16 planes saturate here instead of overflowing to inf
 
-enum { EPI_F32 = 0, EPI_ELU = 1, EPI_BWD = 2, EPI_PARTIAL = 3 };
+enum { EPI_F32 = 0, EPI_ELU = 1, EPI_BWD = 2, EPI_PARTIAL = 3 };        // EPI_ELU: "activation" epilogue (ELU is the reference default)
+// get_activation (go1_gym_learn/ppo_cse/actor_critic.py:162-178); values = LT_ACT_* of include/lt_policy.h
+enum { ACT_ELU = 0, ACT_SELU = 1, ACT_RELU = 2, ACT_LRELU = 3, ACT_TANH = 4, ACT_SIGMOID = 5 };
 
 struct Params {
     CUtensorMap tma_a, tma_b;            // 3-D maps {k, row, plane}; box {64, 128, 2} / {64, bn, 2}; SWIZZLE_128B; zero OOB fill
@@ -41,6 +43,7 @@ struct Params {
     int32_t bn;                          // N tile = UMMA N (multiple of 16, <= BN_MAX)
     int32_t splits, kb_per_split;        // split-K: k-blocks [s * kb_per_split, (s+1) * kb_per_split) go to partial s
     int32_t mode;
+    int32_t act;                         // ACT_*: activation of EPI_ELU, its derivative (from the stored OUTPUT y) in EPI_BWD
     float out_scale;                     // 1 / (s_a * s_b)
     const float* bias;                   // [N] or NULL
     float* out_f32;                      // EPI_F32 / EPI_PARTIAL
@@ -50,6 +53,11 @@ struct Params {
     __half* out_t;                       // transposed planes [2][cols][ld_t] or NULL
     int64_t ld_t, plane_t;
     float split_scale;                   // scale of the fp16 planes written by EPI_ELU / EPI_BWD
+    // gradient operands carry a per-tensor power-of-two scale that lives on the DEVICE (chosen from the tensor's measured
+    // largest entry, see lt_policy.cu "gradient scales"), so that no host synchronisation is needed to pick it:
+    const float* a_scale_ptr;            // != NULL: the A planes were written with this scale -> out_scale is divided by it
+    const float* split_scale_ptr;        // != NULL: overrides split_scale for the planes EPI_BWD writes
+    uint32_t* amax_out;                  // != NULL: EPI_BWD records max |dz| (fp32 bit pattern, atomicMax) of what it writes
     const __half* act_h;                 // EPI_BWD: y_prev planes (row-major, scale 1 / act_inv_scale)
     int64_t ld_act, plane_act;
     float act_inv_scale;
@@ -129,7 +137,35 @@ __device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uin
     hi = *reinterpret_cast<const uint32_t*>(&h);
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
-__device__ __forceinline__ float elu1(float z) { return z > 0.0f ? z : expm1f(z); }      // nn.ELU(alpha = 1)
+constexpr float SELU_ALPHA = 1.6732632423543772848170429916717f, SELU_SCALE = 1.0507009873554804934193349852946f;
+template <int ACT>
+__device__ __forceinline__ float act_fwd(float z) {
+    if (ACT == ACT_ELU) return z > 0.0f ? z : expm1f(z);                                   // nn.ELU(alpha = 1)
+    if (ACT == ACT_SELU) return SELU_SCALE * (z > 0.0f ? z : SELU_ALPHA * expm1f(z));
+    if (ACT == ACT_RELU) return fmaxf(z, 0.0f);
+    if (ACT == ACT_LRELU) return z > 0.0f ? z : 0.01f * z;                                  // nn.LeakyReLU default slope
+    if (ACT == ACT_TANH) return tanhf(z);
+    return 1.0f / (1.0f + expf(-z));
+}
+// derivative with respect to the pre-activation, written in terms of the OUTPUT y (the only thing the forward pass keeps)
+template <int ACT>
+__device__ __forceinline__ float act_bwd(float y) {
+    if (ACT == ACT_ELU) return y > 0.0f ? 1.0f : y + 1.0f;
+    if (ACT == ACT_SELU) return y > 0.0f ? SELU_SCALE : y + SELU_SCALE * SELU_ALPHA;
+    if (ACT == ACT_RELU) return y > 0.0f ? 1.0f : 0.0f;
+    if (ACT == ACT_LRELU) return y > 0.0f ? 1.0f : 0.01f;
+    if (ACT == ACT_TANH) return 1.0f - y * y;
+    return y * (1.0f - y);
+}
+#define LTG_ACT_SWITCH(act, BODY)                                        \
+    switch (act) {                                                       \
+        case ACT_SELU: { constexpr int A_ = ACT_SELU; BODY } break;      \
+        case ACT_RELU: { constexpr int A_ = ACT_RELU; BODY } break;      \
+        case ACT_LRELU: { constexpr int A_ = ACT_LRELU; BODY } break;    \
+        case ACT_TANH: { constexpr int A_ = ACT_TANH; BODY } break;      \
+        case ACT_SIGMOID: { constexpr int A_ = ACT_SIGMOID; BODY } break;\
+        default: { constexpr int A_ = ACT_ELU; BODY } break;             \
+    }
 
 template <int BN_MAX, int STAGES>
 struct Smem {
@@ -257,6 +293,9 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
             mbar_wait(tfull(as), aphase);
             fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)as * BN_MAX;
+            const float out_scale = p.a_scale_ptr ? p.out_scale / __ldg(p.a_scale_ptr) : p.out_scale;
+            const float split_scale = p.split_scale_ptr ? __ldg(p.split_scale_ptr) : p.split_scale;
+            float tile_amax = 0.0f;
             for (int c = 0; c < p.bn; c += 32) {
                 uint32_t r[32];
                 const int width = min(32, p.bn - c);                              // 32 or 16 (bn is a multiple of 16)
@@ -265,7 +304,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                 const int col0 = n0 + c;
                 float v[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.out_scale;
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * out_scale;
                 if (p.mode == EPI_F32 || p.mode == EPI_PARTIAL) {
                     float* out = p.out_f32 + (p.mode == EPI_PARTIAL ? (int64_t)split * p.split_stride : 0) + (int64_t)row * p.ld_f32;
                     if (row_ok) {
@@ -280,9 +319,9 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const int n = col0 + j;
-                            const float b = (p.bias && j < width && n < p.N) ? __ldg(p.bias + n) : 0.0f;
-                            v[j] = elu1(v[j] + b);
+                            v[j] += (p.bias && j < width && n < p.N) ? __ldg(p.bias + n) : 0.0f;
                         }
+                        LTG_ACT_SWITCH(p.act, _Pragma("unroll") for (int j = 0; j < 32; ++j) v[j] = act_fwd<A_>(v[j]);)
                     } else if (p.act_h) {                                         // EPI_BWD: times ELU'(y_prev); act_h == NULL: linear layer
                         if (row_ok) {
                             const __half* ah = p.act_h + (int64_t)row * p.ld_act + col0;
@@ -298,8 +337,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                                             const float2 fh = __half22float2(*reinterpret_cast<const __half2*>(&wh[e]));
                                             const float2 fl = __half22float2(*reinterpret_cast<const __half2*>(&wl[e]));
                                             const float y0 = (fh.x + fl.x) * p.act_inv_scale, y1 = (fh.y + fl.y) * p.act_inv_scale;
-                                            v[g * 8 + 2 * e] *= (y0 > 0.0f ? 1.0f : y0 + 1.0f);
-                                            v[g * 8 + 2 * e + 1] *= (y1 > 0.0f ? 1.0f : y1 + 1.0f);
+                                            LTG_ACT_SWITCH(p.act, v[g * 8 + 2 * e] *= act_bwd<A_>(y0); v[g * 8 + 2 * e + 1] *= act_bwd<A_>(y1);)
                                         }
                                     }
                                 }
@@ -309,15 +347,19 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                                     const int n = col0 + j;
                                     if (j < width && n < p.N) {
                                         const float y = (__half2float(ah[j]) + __half2float(al[j])) * p.act_inv_scale;
-                                        v[j] *= (y > 0.0f ? 1.0f : y + 1.0f);
+                                        LTG_ACT_SWITCH(p.act, v[j] *= act_bwd<A_>(y);)
                                     }
                                 }
                             }
                         }
                     }
+                    if (p.amax_out) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) tile_amax = fmaxf(tile_amax, j < width ? fabsf(v[j]) : 0.0f);      // fmaxf drops NaNs; x16 loads leave r[16..] unset
+                    }
                     uint32_t hi[16], lo[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) split_pair(v[2 * j] * p.split_scale, v[2 * j + 1] * p.split_scale, hi[j], lo[j]);
+                    for (int j = 0; j < 16; ++j) split_pair(v[2 * j] * split_scale, v[2 * j + 1] * split_scale, hi[j], lo[j]);
                     if (row_ok) {
                         // row-major planes: this thread's 32 (or 16) consecutive columns, 16-byte stores where the row pitch allows
                         __half* oh = p.out_h + (int64_t)row * p.ld_h + col0;
@@ -353,6 +395,10 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                         }
                     }
                 }
+            }
+            if (p.amax_out) {
+                const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(fminf(tile_amax, 3.0e38f)));
+                if (lane == 0 && m) atomicMax(p.amax_out, m);
             }
             fence_before();
             __syncwarp();

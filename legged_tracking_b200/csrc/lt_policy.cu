@@ -7,7 +7,15 @@
 // actor: obs_history | latent, AC:130; critic: obs_history | privileged_obs, AC:158).  Hidden activations Y_l are written by
 // the GEMM epilogue already split (and, when training, also transposed with a constant-one row appended, which is what the
 // weight-gradient GEMM dW_l^T = [Y_{l-1}^T; 1] * dZ_l consumes: the bias gradient is its last column).
-// Scales are powers of two, undone exactly in the epilogues: activations 2^4, weights 2^6, gradients 2^ceil(log2(rows)).
+// Scales are powers of two, undone exactly in the epilogues: activations 2^4, weights 2^6.
+//
+// Gradient scales.  A gradient tensor dZ_l spans many orders of magnitude across layers (the adaptation module sees the actor's
+// gradient through four weight matrices), and an fp16 "lo" plane keeps its 11 bits only while value * scale stays above 2^-14
+// * 2^11: so every dZ tensor gets its OWN power-of-two scale, kept in a small device table and chosen so that the tensor's
+// largest entry lands in [32, 64) -- three decades of headroom below the 60000 clamp, five above the subnormal floor.  The
+// largest entry is measured by the kernels that write the tensor (atomicMax in the epilogue / head); the scales used by a call
+// are the ones measured by the previous call of the same kind, and the very first call runs its backward pass twice (once at
+// 2^ceil(log2(rows)) to measure).  No host synchronisation anywhere.
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
@@ -48,7 +56,12 @@ struct Mlp {
     Planes Y[LT_POLICY_MAX_HIDDEN], YT[LT_POLICY_MAX_HIDDEN];          // hidden activations, row-major and [N_l + 1][R] transposed
     Planes dZ[LT_POLICY_MAX_HIDDEN + 1], dZT[LT_POLICY_MAX_HIDDEN + 1];
     float* out = nullptr;                         // [R][N_last] fp32
+    int idx = 0;                                  // 0 adaptation, 1 actor, 2 critic: row of the gradient-scale table
 };
+
+constexpr int GS_PER_MLP = LT_POLICY_MAX_HIDDEN + 1;
+constexpr int GS_N = 3 * GS_PER_MLP;              // one scale per dZ tensor
+enum { CTX_PPO = 0, CTX_ADAPT = 1 };              // lt_ppo_minibatch_grad and lt_adaptation_grad see different magnitudes
 
 }   // namespace
 
@@ -64,6 +77,11 @@ struct lt_policy {
     float* head_partial = nullptr;                // [blocks][STAT_SLOTS]
     float* norm_partial = nullptr;                // [blocks]
     float* scalars = nullptr;                     // device float[8]: [0] clip coefficient, [1] total norm
+    float* gscale = nullptr;                      // device float[2][GS_N]: gradient scales per call kind
+    uint32_t* gamax = nullptr;                    // device uint32[2][GS_N]: measured max |dz| (fp32 bits) of the running call
+    bool calibrated[2] = {false, false};
+    float* gs(int ctx, const Mlp& m, int l) const { return gscale + ctx * GS_N + m.idx * GS_PER_MLP + l; }
+    uint32_t* ga(int ctx, const Mlp& m, int l) const { return gamax + ctx * GS_N + m.idx * GS_PER_MLP + l; }
     int64_t n_params = 0;
     float *params = nullptr, *grads = nullptr;
     std::vector<void*> allocs;
@@ -267,6 +285,28 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {            // d
     return t;                                                               // valid in thread 0
 }
 
+// warp max of |v| -> one atomicMax per warp on the fp32 bit pattern (non-negative floats order like unsigned integers)
+__device__ __forceinline__ void record_amax(uint32_t* dst, float v) {
+    const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(fminf(v, 3.0e38f)));
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(dst, m);
+}
+
+// scale <- the power of two that puts the measured largest entry into [32, 64); the measurement is cleared for the next call
+__global__ void update_scales_kernel(uint32_t* __restrict__ amax, float* __restrict__ scale, int n) {
+    const int i = threadIdx.x;
+    if (i >= n) return;
+    const float a = __uint_as_float(amax[i]);
+    if (a > 0.0f && a < 3.0e38f) {
+        int e;
+        frexpf(a, &e);                                            // a = m * 2^e, m in [0.5, 1)
+        scale[i] = ldexpf(1.0f, min(max(6 - e, -100), 100));
+    }
+    amax[i] = 0u;
+}
+__global__ void fill_kernel(float* __restrict__ dst, float v, int n) {
+    if ((int)threadIdx.x < n) dst[threadIdx.x] = v;
+}
+
 struct HeadParams {
     lt_ppo_batch_ptrs b;
     const int64_t* indices;
@@ -276,7 +316,8 @@ struct HeadParams {
     const float* std;           // [A]
     lt_ppo_hparams hp;
     float inv_count;            // 1 / (count * grad_world)
-    float s_g;
+    const float *s_mu, *s_v;    // device: scales of the two head gradient tensors
+    uint32_t *amax_mu, *amax_v;
     __half *dmu, *dmut, *dv, *dvt;                    // planes
     int64_t ld_dmu, plane_dmu, ld_dmut, plane_dmut, ld_dv, plane_dv, ld_dvt, plane_dvt;
     float* partial;             // [blocks][STAT_SLOTS]
@@ -289,6 +330,8 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
     const bool ok = r < p.count;
     float surr = 0.0f, vl = 0.0f, kl = 0.0f, g_logp = 0.0f;
     float dstd[32];
+    float amax_mu = 0.0f, amax_v = 0.0f;
+    const float s_mu = __ldg(p.s_mu), s_v = __ldg(p.s_v);
     const int A = p.A;
     int64_t s = 0;
     if (ok) {
@@ -329,8 +372,9 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
             const float mu = p.mu[(int64_t)r * A + j], sg = p.std[j], a = p.b.actions[s * A + j];
             const float d = a - mu;
             const float gmu = gs * d / (sg * sg);
+            amax_mu = fmaxf(amax_mu, fabsf(gmu));
             __half h, l;
-            split1(gmu * p.s_g, h, l);
+            split1(gmu * s_mu, h, l);
             p.dmu[(int64_t)r * p.ld_dmu + j] = h;
             p.dmu[p.plane_dmu + (int64_t)r * p.ld_dmu + j] = l;
             p.dmut[(int64_t)j * p.ld_dmut + r] = h;
@@ -338,8 +382,9 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
             dstd[j] = gs * (d * d - sg * sg) / (sg * sg * sg);
         }
         const float gval = p.hp.value_loss_coef * gv * p.inv_count;
+        amax_v = fabsf(gval);
         __half h, l;
-        split1(gval * p.s_g, h, l);
+        split1(gval * s_v, h, l);
         p.dv[(int64_t)r * p.ld_dv] = h;
         p.dv[p.plane_dv + (int64_t)r * p.ld_dv] = l;
         p.dvt[r] = h;
@@ -347,6 +392,8 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
     } else {
         for (int j = 0; j < A; ++j) dstd[j] = 0.0f;
     }
+    record_amax(p.amax_mu, amax_mu);
+    record_amax(p.amax_v, amax_v);
     float* out = p.partial + (int64_t)blockIdx.x * STAT_SLOTS;
     float t = block_sum(surr, sh);
     if (threadIdx.x == 0) out[0] = t;
@@ -378,7 +425,8 @@ struct AdaptHeadParams {
     const int64_t* indices;
     int count, P, num_train;
     float inv_train;            // 1 / (num_train * P * grad_world)
-    float s_g;
+    const float* s_g;           // device: scale of the head gradient tensor
+    uint32_t* amax;
     __half *dz, *dzt;
     int64_t ld_dz, plane_dz, ld_dzt, plane_dzt;
     float* partial;
@@ -388,21 +436,24 @@ struct AdaptHeadParams {
 __global__ void __launch_bounds__(HEAD_THREADS) adapt_head_kernel(const __grid_constant__ AdaptHeadParams p) {
     __shared__ float sh[HEAD_THREADS / 32];
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    float tr = 0.0f, te = 0.0f;
+    float tr = 0.0f, te = 0.0f, amax = 0.0f;
+    const float s_g = __ldg(p.s_g);
     if (r < p.count) {
         const int64_t s = p.indices ? p.indices[r] : (int64_t)r;
         for (int j = 0; j < p.P; ++j) {
             const float d = p.pred[(int64_t)r * p.P + j] - p.priv[s * p.P + j];
             const float g = r < p.num_train ? 2.0f * d * p.inv_train : 0.0f;
             if (r < p.num_train) tr += d * d; else te += d * d;
+            amax = fmaxf(amax, fabsf(g));
             __half h, l;
-            split1(g * p.s_g, h, l);
+            split1(g * s_g, h, l);
             p.dz[(int64_t)r * p.ld_dz + j] = h;
             p.dz[p.plane_dz + (int64_t)r * p.ld_dz + j] = l;
             p.dzt[(int64_t)j * p.ld_dzt + r] = h;
             p.dzt[p.plane_dzt + (int64_t)j * p.ld_dzt + r] = l;
         }
     }
+    record_amax(p.amax, amax);
     float* out = p.partial + (int64_t)blockIdx.x * STAT_SLOTS;
     float t = block_sum(tr, sh);
     if (threadIdx.x == 0) out[0] = t;
@@ -607,6 +658,7 @@ int forward_mlp(lt_policy* P, Mlp& m, int rows, bool train, cudaStream_t s) {
         const Operand A = l == 0 ? op(P->X0, rows) : op(m.Y[l - 1], rows);
         if (l < m.n - 1) {
             p.mode = ltg::EPI_ELU;
+            p.act = P->c.activation;
             p.out_h = m.Y[l].p;
             p.ld_h = m.Y[l].ld;
             p.plane_h = m.Y[l].plane;
@@ -636,7 +688,7 @@ int dw_splits(lt_policy* P, int N, int Kp1, int count) {
 }
 
 // backward of one MLP: m.dZ[n-1] / m.dZT[n-1] hold the (scaled) gradient of the last layer's output
-int backward_mlp(lt_policy* P, Mlp& m, int count, float s_g, cudaStream_t s) {
+int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
     for (int l = m.n - 1; l >= 0; --l) {
         Layer& L = m.L[l];
         {   // dW_l and db_l:  [N_l, K_l + 1] = dZ_l^T [N_l, count] * [X_{l-1}^T; 1] [K_l + 1, count]^T
@@ -645,7 +697,8 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, float s_g, cudaStream_t s) {
             ltg::Params p;
             memset(&p, 0, sizeof p);
             p.mode = ltg::EPI_PARTIAL;
-            p.out_scale = 1.0f / (s_g * S_X);
+            p.out_scale = 1.0f / S_X;
+            p.a_scale_ptr = P->gs(ctx, m, l);
             p.out_f32 = P->partial;
             p.ld_f32 = up(Kp1, 4);
             p.split_stride = (int64_t)L.N * p.ld_f32;
@@ -661,8 +714,11 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, float s_g, cudaStream_t s) {
             ltg::Params p;
             memset(&p, 0, sizeof p);
             p.mode = ltg::EPI_BWD;
-            p.out_scale = 1.0f / (s_g * S_W);
-            p.split_scale = s_g;
+            p.act = P->c.activation;
+            p.out_scale = 1.0f / S_W;
+            p.a_scale_ptr = P->gs(ctx, m, l);
+            p.split_scale_ptr = P->gs(ctx, m, l - 1);
+            p.amax_out = P->ga(ctx, m, l - 1);
             p.out_h = m.dZ[l - 1].p;
             p.ld_h = m.dZ[l - 1].ld;
             p.plane_h = m.dZ[l - 1].plane;
@@ -705,6 +761,20 @@ float grad_scale_for(int count) {
     int e = 0;
     while ((1ll << e) < count) ++e;
     return ldexpf(1.0f, e);
+}
+
+// scales of call kind `ctx` for this call: measured by the previous call, or (first call) the row-count default
+int begin_grad_scales(lt_policy* P, int ctx, int count_world, cudaStream_t s) {
+    if (P->calibrated[ctx]) return 0;
+    fill_kernel<<<1, 32, 0, s>>>(P->gscale + ctx * GS_N, grad_scale_for(count_world), GS_N);
+    LTP_CUDA(P, cudaMemsetAsync(P->gamax + ctx * GS_N, 0, GS_N * sizeof(uint32_t), s));
+    return 1;                                                   // caller runs its backward pass once more after end_grad_scales
+}
+int end_grad_scales(lt_policy* P, int ctx, cudaStream_t s) {
+    update_scales_kernel<<<1, 32, 0, s>>>(P->gamax + ctx * GS_N, P->gscale + ctx * GS_N, GS_N);
+    LTP_CUDA(P, cudaGetLastError());
+    P->calibrated[ctx] = true;
+    return LT_OK;
 }
 
 }   // namespace
@@ -755,8 +825,9 @@ int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
     if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
         return fail(nullptr, LT_ERR_NO_DEVICE, "no sm_100 device: the actor-critic kernels have no CPU fallback");
     if (cfg->num_obs_history <= 0 || cfg->num_privileged_obs <= 0 || cfg->num_actions <= 0 || cfg->num_actions > STAT_SLOTS - 3 ||
-        cfg->num_actions > 32 || cfg->max_rows <= 0 || cfg->n_adaptation_hidden < 1 || cfg->n_actor_hidden < 1 || cfg->n_critic_hidden < 1 ||
-        cfg->n_adaptation_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_actor_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_critic_hidden > LT_POLICY_MAX_HIDDEN)
+        cfg->num_actions > 32 || GS_N > 32 || cfg->max_rows <= 0 || cfg->n_adaptation_hidden < 1 || cfg->n_actor_hidden < 1 || cfg->n_critic_hidden < 1 ||
+        cfg->n_adaptation_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_actor_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_critic_hidden > LT_POLICY_MAX_HIDDEN ||
+        cfg->activation < LT_ACT_ELU || cfg->activation > LT_ACT_SIGMOID)
         return fail(nullptr, LT_ERR_INVALID, "unsupported actor-critic geometry");
     if (!ltg::encode_fn()) return fail(nullptr, LT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
     lt_policy* P = new lt_policy();
@@ -793,6 +864,11 @@ int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
     if (!rc) rc = alloc_dev(P, P->head_partial, head_blocks * STAT_SLOTS);
     if (!rc) rc = alloc_dev(P, P->norm_partial, 1024);
     if (!rc) rc = alloc_dev(P, P->scalars, 8);
+    if (!rc) rc = alloc_dev(P, P->gscale, 2 * GS_N);
+    if (!rc) rc = alloc_dev(P, P->gamax, 2 * GS_N);
+    P->adapt.idx = 0;
+    P->actor.idx = 1;
+    P->critic.idx = 2;
     if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = fail(P, LT_ERR_CUDA, "initialisation kernels failed");
     if (rc) {
         g_policy_error = P->err;
@@ -817,6 +893,8 @@ int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi) {
     *hi = p->actor.L[0].w_off;
     return LT_OK;
 }
+
+const float* lt_policy_grad_scales(const lt_policy* p) { return p ? p->gscale : nullptr; }
 
 int lt_policy_bind_params(lt_policy* p, float* params, float* grads) {
     if (!p || !params) return LT_ERR_INVALID;
@@ -872,12 +950,13 @@ int lt_policy_act(lt_policy* p, const float* obs_history, const float* privilege
     int rc = check_ready(p, rows);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    if (!obs_history || !privileged_obs) return fail(p, LT_ERR_INVALID, "obs_history / privileged_obs is NULL");
+    if (!obs_history) return fail(p, LT_ERR_INVALID, "obs_history is NULL");
+    if (value && !privileged_obs) return fail(p, LT_ERR_INVALID, "privileged_obs is NULL but the critic needs it");
     rc = pack(p, obs_history, privileged_obs, nullptr, rows, 0, false, s);
     if (!rc) rc = forward_mlp(p, p->adapt, rows, false, s);
     if (!rc) rc = scatter_latent(p, rows, false, s);
     if (!rc) rc = forward_mlp(p, p->actor, rows, false, s);
-    if (!rc) rc = forward_mlp(p, p->critic, rows, false, s);
+    if (!rc && value) rc = forward_mlp(p, p->critic, rows, false, s);
     if (rc) return rc;
     act_head_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(p->actor.out, p->params, normal_noise, actions_in, rows, p->A, seed, step, actions,
                                                                   actions_log_prob, action_mean, action_sigma);
@@ -894,7 +973,6 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
     if (!batch || !hp || !stats) return LT_ERR_INVALID;
     cudaStream_t s = (cudaStream_t)stream;
     const int world = grad_world > 1 ? grad_world : 1;
-    const float s_g = grad_scale_for(count * world);
     rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (!rc) rc = scatter_latent(p, count, true, s);
@@ -902,20 +980,24 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
     if (!rc) rc = forward_mlp(p, p->critic, count, true, s);
     if (rc) return rc;
     const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
-    {
+    const int passes = 1 + begin_grad_scales(p, CTX_PPO, count * world, s);
+    for (int pass = 0; pass < passes; ++pass) {
+        Mlp &a = p->actor, &c = p->critic, &ad = p->adapt;
         HeadParams h;
         memset(&h, 0, sizeof h);
         h.b = *batch;
         h.indices = indices;
         h.count = count;
         h.A = p->A;
-        h.mu = p->actor.out;
-        h.value = p->critic.out;
+        h.mu = a.out;
+        h.value = c.out;
         h.std = p->params;
         h.hp = *hp;
         h.inv_count = 1.0f / ((float)count * (float)world);
-        h.s_g = s_g;
-        const Mlp &a = p->actor, &c = p->critic;
+        h.s_mu = p->gs(CTX_PPO, a, a.n - 1);
+        h.s_v = p->gs(CTX_PPO, c, c.n - 1);
+        h.amax_mu = p->ga(CTX_PPO, a, a.n - 1);
+        h.amax_v = p->ga(CTX_PPO, c, c.n - 1);
         h.dmu = a.dZ[a.n - 1].p; h.ld_dmu = a.dZ[a.n - 1].ld; h.plane_dmu = a.dZ[a.n - 1].plane;
         h.dmut = a.dZT[a.n - 1].p; h.ld_dmut = a.dZT[a.n - 1].ld; h.plane_dmut = a.dZT[a.n - 1].plane;
         h.dv = c.dZ[c.n - 1].p; h.ld_dv = c.dZ[c.n - 1].ld; h.plane_dv = c.dZ[c.n - 1].plane;
@@ -925,28 +1007,30 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
         ppo_head_reduce_kernel<<<1, 64, 0, s>>>(p->head_partial, blocks, p->A, p->params, hp->entropy_coef, 1.0f / (float)world, count, stats,
                                                 p->grads);
         LTP_CUDA(p, cudaGetLastError());
+        rc = backward_mlp(p, c, count, CTX_PPO, s);
+        if (!rc) rc = backward_mlp(p, a, count, CTX_PPO, s);
+        if (rc) return rc;
+        {   // the latent columns of the actor's input gradient are the adaptation module's output gradient (AC:129-130)
+            Layer& L = a.L[0];
+            ltg::Params g;
+            memset(&g, 0, sizeof g);
+            g.mode = ltg::EPI_BWD;                                   // act_h == NULL: no activation derivative (last layer is linear)
+            g.out_scale = 1.0f / S_W;
+            g.a_scale_ptr = p->gs(CTX_PPO, a, 0);
+            g.split_scale_ptr = p->gs(CTX_PPO, ad, ad.n - 1);
+            g.amax_out = p->ga(CTX_PPO, ad, ad.n - 1);
+            Planes& dz = ad.dZ[ad.n - 1];
+            Planes& dzt = ad.dZT[ad.n - 1];
+            g.out_h = dz.p; g.ld_h = dz.ld; g.plane_h = dz.plane;
+            g.out_t = dzt.p; g.ld_t = dzt.ld; g.plane_t = dzt.plane;
+            Operand B{L.WT.p + (int64_t)p->Din * L.WT.ld, p->P, L.WT.ld, L.WT.plane};
+            rc = run_gemm(p, op(a.dZ[0], count), count, B, p->P, L.N, 1, g, s);
+            if (!rc) rc = backward_mlp(p, ad, count, CTX_PPO, s);
+        }
+        if (!rc) rc = end_grad_scales(p, CTX_PPO, s);
+        if (rc) return rc;
     }
-    rc = backward_mlp(p, p->critic, count, s_g, s);
-    if (!rc) rc = backward_mlp(p, p->actor, count, s_g, s);
-    if (rc) return rc;
-    {   // the latent columns of the actor's input gradient are the adaptation module's output gradient (AC:129-130)
-        Mlp& a = p->actor;
-        Mlp& ad = p->adapt;
-        Layer& L = a.L[0];
-        ltg::Params g;
-        memset(&g, 0, sizeof g);
-        g.mode = ltg::EPI_BWD;                                   // act_h == NULL: no activation derivative (last layer is linear)
-        g.out_scale = 1.0f / (s_g * S_W);
-        g.split_scale = s_g;
-        Planes& dz = ad.dZ[ad.n - 1];
-        Planes& dzt = ad.dZT[ad.n - 1];
-        g.out_h = dz.p; g.ld_h = dz.ld; g.plane_h = dz.plane;
-        g.out_t = dzt.p; g.ld_t = dzt.ld; g.plane_t = dzt.plane;
-        Operand B{L.WT.p + (int64_t)p->Din * L.WT.ld, p->P, L.WT.ld, L.WT.plane};
-        rc = run_gemm(p, op(a.dZ[0], count), count, B, p->P, L.N, 1, g, s);
-        if (!rc) rc = backward_mlp(p, ad, count, s_g, s);
-    }
-    return rc;
+    return LT_OK;
 }
 
 int lt_ppo_minibatch_apply(lt_policy* p, const lt_ppo_hparams* hp, const float* stats, float* lr, float* adam_m, float* adam_v, int32_t adam_step,
@@ -973,29 +1057,35 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
     if (!batch || !stats || num_train < 0 || num_train > count) return LT_ERR_INVALID;
     cudaStream_t s = (cudaStream_t)stream;
     const int world = grad_world > 1 ? grad_world : 1;
-    const float s_g = grad_scale_for(count * world);
     rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (rc) return rc;
     const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
-    AdaptHeadParams h;
-    memset(&h, 0, sizeof h);
-    h.pred = p->adapt.out;
-    h.priv = batch->privileged_obs;
-    h.indices = indices;
-    h.count = count;
-    h.P = p->P;
-    h.num_train = num_train;
-    h.inv_train = num_train > 0 ? 1.0f / ((float)num_train * (float)p->P * (float)world) : 0.0f;
-    h.s_g = s_g;
     Mlp& ad = p->adapt;
-    h.dz = ad.dZ[ad.n - 1].p; h.ld_dz = ad.dZ[ad.n - 1].ld; h.plane_dz = ad.dZ[ad.n - 1].plane;
-    h.dzt = ad.dZT[ad.n - 1].p; h.ld_dzt = ad.dZT[ad.n - 1].ld; h.plane_dzt = ad.dZT[ad.n - 1].plane;
-    h.partial = p->head_partial;
-    adapt_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
-    adapt_head_reduce_kernel<<<1, 32, 0, s>>>(p->head_partial, blocks, count, num_train, p->P, stats);
-    LTP_CUDA(p, cudaGetLastError());
-    return backward_mlp(p, ad, count, s_g, s);
+    const int passes = 1 + begin_grad_scales(p, CTX_ADAPT, num_train > 0 ? num_train * p->P * world : 1, s);
+    for (int pass = 0; pass < passes; ++pass) {
+        AdaptHeadParams h;
+        memset(&h, 0, sizeof h);
+        h.pred = ad.out;
+        h.priv = batch->privileged_obs;
+        h.indices = indices;
+        h.count = count;
+        h.P = p->P;
+        h.num_train = num_train;
+        h.inv_train = num_train > 0 ? 1.0f / ((float)num_train * (float)p->P * (float)world) : 0.0f;
+        h.s_g = p->gs(CTX_ADAPT, ad, ad.n - 1);
+        h.amax = p->ga(CTX_ADAPT, ad, ad.n - 1);
+        h.dz = ad.dZ[ad.n - 1].p; h.ld_dz = ad.dZ[ad.n - 1].ld; h.plane_dz = ad.dZ[ad.n - 1].plane;
+        h.dzt = ad.dZT[ad.n - 1].p; h.ld_dzt = ad.dZT[ad.n - 1].ld; h.plane_dzt = ad.dZT[ad.n - 1].plane;
+        h.partial = p->head_partial;
+        adapt_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
+        adapt_head_reduce_kernel<<<1, 32, 0, s>>>(p->head_partial, blocks, count, num_train, p->P, stats);
+        LTP_CUDA(p, cudaGetLastError());
+        rc = backward_mlp(p, ad, count, CTX_ADAPT, s);
+        if (!rc) rc = end_grad_scales(p, CTX_ADAPT, s);
+        if (rc) return rc;
+    }
+    return LT_OK;
 }
 
 int lt_adaptation_apply(lt_policy* p, const lt_ppo_hparams* hp, float lr, float* adam_m, float* adam_v, int32_t adam_step, void* stream) {

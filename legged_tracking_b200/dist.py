@@ -6,9 +6,9 @@ couples all environments:
     LT_MAX_TERMS float sums between lt_reward_sign_prepass and lt_post_physics_step;
   * advantage normalisation over the whole [T,N] rollout (rollout_storage.py:89-90) -> all-reduce of the
     {sum, sum of squares, count} doubles lt_gae leaves on the device;
-  * the PPO gradient step (ppo.py:144-148) -> mean all-reduce of one flat gradient bucket;
-  * the adaptive-KL learning-rate decision (ppo.py:111-125) -> mean all-reduce of the scalar KL so that every rank
-    takes the same branch.
+  * the PPO gradient step (ppo.py:144-148) and the adaptive-KL learning-rate decision (ppo.py:111-125) -> ONE sum all-reduce
+    of the [loss / KL sums | flat gradient] buffer per minibatch (GradExchange), so every rank takes the same branch;
+  * the initial parameters -> broadcast from rank 0 (replicas must not depend on per-rank seeds).
 
 Everything here works on whatever device the tensors live on (NCCL for CUDA, gloo for the CPU tests)."""
 import os
@@ -68,31 +68,60 @@ def allreduce_mean_scalar(t):
     return t
 
 
-class GradBucket:
-    """One flat fp32 buffer aliased by every parameter's .grad, so the gradient exchange is ONE all-reduce per
-    minibatch instead of one per tensor (26 tensors in the default ActorCritic)."""
+def broadcast_(t, src=0):
+    if world_size() > 1:
+        dist.broadcast(t, src=src)
+    return t
 
-    def __init__(self, params):
-        self.params = [p for p in params if p.requires_grad]
-        n = sum(p.numel() for p in self.params)
-        p0 = self.params[0]
-        self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
-        self.views = []
-        o = 0
-        for p in self.params:
-            self.views.append(self.flat[o:o + p.numel()].view_as(p))
-            o += p.numel()
 
-    def attach(self):
-        """Point every .grad at its slice (zeroed).  Call instead of optimizer.zero_grad()."""
-        self.flat.zero_()
-        for p, v in zip(self.params, self.views):
-            p.grad = v
+class GradExchange:
+    """The one buffer the PPO update exchanges between env-sharded ranks: [stats (LT_PPO_STATS floats) | flat gradient].
+    lt_ppo_minibatch_grad / lt_adaptation_grad (include/lt_policy.h) write per-rank SUMS scaled by 1 / (count * world) into it,
+    so a single SUM all-reduce per call yields the whole job's mean gradient, loss sums, KL sum and row count -- every rank then
+    takes the same learning-rate branch and applies the same Adam step (replicas stay bit-identical).
 
-    def allreduce_mean(self):
-        if world_size() > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            self.flat /= world_size()
+    main step        all-reduce of the whole buffer (stats[0..4) + every gradient)
+    adaptation step  all-reduce of stats[4..16) + gradient[0 .. adaptation_hi): the slice is contiguous with the tail of the
+                     stats because std and the adaptation module come first in the flat layout; stats[0..4) of the main step
+                     are NOT touched again (they are already global sums)
+    `timed = True` brackets every exchange with CUDA events (bench.py reads seconds() after a synchronize)."""
+
+    MAIN_STATS = 4
+
+    def __init__(self, n_params, device, stats=16):
+        self.n_stats = int(stats)
+        self.buf = torch.zeros(self.n_stats + int(n_params), dtype=torch.float32, device=device)
+        self.stats = self.buf[:self.n_stats]
+        self.grads = self.buf[self.n_stats:]
+        self.timed = False
+        self.calls, self.bytes = 0, 0
+        self._events = []
+
+    def _allreduce(self, view):
+        if world_size() <= 1:
+            return
+        self.calls += 1
+        self.bytes += view.numel() * view.element_size()
+        if self.timed and view.is_cuda:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.all_reduce(view, op=dist.ReduceOp.SUM)
+            e1.record()
+            self._events.append((e0, e1))
+        else:
+            dist.all_reduce(view, op=dist.ReduceOp.SUM)
+
+    def exchange_main(self):
+        self._allreduce(self.buf)
+
+    def exchange_adaptation(self, adaptation_hi):
+        self._allreduce(self.buf[self.MAIN_STATS:self.n_stats + int(adaptation_hi)])
+
+    def seconds(self):
+        """Device time spent inside the all-reduces since the last call (needs timed = True and a prior synchronize)."""
+        t = sum(a.elapsed_time(b) for a, b in self._events) * 1e-3
+        self._events = []
+        return t
 
 
 def merge_moments(stats):

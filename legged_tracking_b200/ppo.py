@@ -1,26 +1,25 @@
 """PPO rows of the path behind the reference's own class names and call signatures.
 
-  AC_Args / ActorCritic      go1_gym_learn/ppo_cse/actor_critic.py:9-160   (same state_dict keys: a checkpoint of either
-                                                                           loads into the other)
+  AC_Args / ActorCritic      go1_gym_learn/ppo_cse/actor_critic.py:9-160   (same constructor, method names and state_dict keys: a
+                                                                           checkpoint of either loads into the other)
   RolloutStorage             go1_gym_learn/ppo_cse/rollout_storage.py       ([T,N,*] buffers in HBM; add_transitions,
                                                                            compute_returns run as liblt_b200 kernels)
   PPO_Args / PPO             go1_gym_learn/ppo_cse/ppo.py                   (act / process_env_step / compute_returns / update)
   RunnerArgs / Runner        go1_gym_learn/ppo_cse/__init__.py:46-357       (learn loop; logging back-ends left to the caller)
 
-Storage and GAE have no CPU fallback: RolloutStorage raises on a non-CUDA device.  The MLP forward/backward GEMMs go
-through torch autograd (cuBLAS) -- plumbing the reference shares; what is new here is the storage/GAE kernels, the
-single flat parameter/gradient bucket (one Adam launch, one clip, one all-reduce per minibatch) and env sharding.
+Nothing here computes: every forward, loss, backward, clip and Adam step is a call into liblt_b200.so (include/lt_policy.h --
+tcgen05 split-fp16 contractions with fp32 accumulation, fused heads), and the rollout buffers are written by
+lt_rollout_store / lt_policy_act.  There is no CPU path and no torch autograd path: on a non-CUDA device the classes raise.
+This module owns the memory (one flat parameter vector, one [stats | gradient] exchange buffer, Adam moments, the rollout
+buffers), maps the reference's state_dict keys onto the flat vector, and runs the cross-rank exchange (dist.GradExchange).
 """
-import copy
 import ctypes as C
+import math
 import os
 import time
-from collections import deque
+from collections import OrderedDict, deque
 
 import torch
-import torch.nn as nn
-import torch.nn.functional as F
-from torch.distributions import Normal
 
 from . import _abi, dist as ltd
 from .params import PrefixProto
@@ -68,25 +67,42 @@ class RunnerArgs(PrefixProto, cli=False):       # ppo_cse/__init__.py:46-62
     resume_curriculum = True
 
 
-def get_activation(act_name):                   # actor_critic.py:162-178
-    table = {"elu": nn.ELU, "selu": nn.SELU, "relu": nn.ReLU, "crelu": nn.ReLU, "lrelu": nn.LeakyReLU,
-             "tanh": nn.Tanh, "sigmoid": nn.Sigmoid}
-    if act_name not in table:
-        raise ValueError(f"invalid activation function {act_name!r}")
-    return table[act_name]()
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
 
 
-def _mlp(n_in, hidden, n_out, activation):
-    """Linear/activation pairs with a bare last Linear; module indices 0,2,4,... as in actor_critic.py:43-82."""
-    dims = [n_in] + list(hidden)
-    layers = []
-    for a, b in zip(dims[:-1], dims[1:]):
-        layers += [nn.Linear(a, b), activation]
-    layers.append(nn.Linear(dims[-1], n_out))
-    return nn.Sequential(*layers)
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
-class ActorCritic(nn.Module):
+def _f32c(t, device, what):
+    """The kernels read float32, contiguous, on the policy's device; anything else is the caller's bug, not a silent copy
+    chain -- except dtype / layout, which the reference also accepts."""
+    if t is None:
+        return None
+    if t.device != device:
+        raise _abi.LtError(f"{what} is on {t.device}, the policy on {device}")
+    t = t.detach()
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.float().contiguous()
+    return t
+
+
+_BODIES = (("adaptation_module", "adaptation_module_branch_hidden_dims"), ("actor_body", "actor_hidden_dims"),
+           ("critic_body", "critic_hidden_dims"))
+_LOG_SQRT_2PI = math.log(math.sqrt(2.0 * math.pi))
+# get_activation (actor_critic.py:162-178) -> LT_ACT_* of include/lt_policy.h
+_ACTIVATIONS = dict(elu="LT_ACT_ELU", selu="LT_ACT_SELU", relu="LT_ACT_RELU", crelu="LT_ACT_RELU", lrelu="LT_ACT_LRELU",
+                    tanh="LT_ACT_TANH", sigmoid="LT_ACT_SIGMOID")
+
+
+class ActorCritic:
+    """actor_critic.py:23-159 as a handle on an lt_policy (include/lt_policy.h).
+
+    Parameters live in ONE flat float32 vector laid out as lt_policy.h states (std, then weight/bias of every Linear of the
+    adaptation module, the actor body and the critic body): state_dict() returns views of it under the reference's keys
+    ('std', 'adaptation_module.0.weight', ... 'critic_body.6.bias'), load_state_dict() writes through them.  The MLPs
+    themselves exist only as tensor-core operand planes inside the library."""
     is_recurrent = False
 
     def __init__(self, num_obs, num_privileged_obs, num_obs_history, num_actions, **kwargs):
@@ -94,18 +110,92 @@ class ActorCritic(nn.Module):
             print("ActorCritic.__init__ got unexpected arguments, which will be ignored: " + str(list(kwargs)))
         if AC_Args.use_decoder or AC_Args.normalize_obs:
             raise NotImplementedError("use_decoder / normalize_obs are off in every reference config (actor_critic.py:18-20)")
-        self.decoder = AC_Args.use_decoder
-        super().__init__()
-        self.num_obs_history = num_obs_history
-        self.num_privileged_obs = num_privileged_obs
-        act = get_activation(AC_Args.activation)
-        self.adaptation_module = _mlp(num_obs_history, AC_Args.adaptation_module_branch_hidden_dims, num_privileged_obs, act)
-        self.actor_body = _mlp(num_privileged_obs + num_obs_history, AC_Args.actor_hidden_dims, num_actions, act)
-        self.critic_body = _mlp(num_privileged_obs + num_obs_history, AC_Args.critic_hidden_dims, 1, act)
-        self.std = nn.Parameter(AC_Args.init_noise_std * torch.ones(num_actions))
-        self.distribution = None
-        Normal.set_default_validate_args = False
+        if AC_Args.activation not in _ACTIVATIONS:
+            raise ValueError(f"invalid activation function {AC_Args.activation!r}")         # actor_critic.py:177-178
+        self.activation = AC_Args.activation
+        self.decoder = False
         self.normalize_obs = False
+        self.num_obs, self.num_obs_history = int(num_obs), int(num_obs_history)
+        self.num_privileged_obs, self.num_actions = int(num_privileged_obs), int(num_actions)
+        self.hidden = {name: [int(h) for h in getattr(AC_Args, attr)] for name, attr in _BODIES}
+        n_in = dict(adaptation_module=self.num_obs_history, actor_body=self.num_privileged_obs + self.num_obs_history,
+                    critic_body=self.num_privileged_obs + self.num_obs_history)
+        n_out = dict(adaptation_module=self.num_privileged_obs, actor_body=self.num_actions, critic_body=1)
+        # flat layout (lt_policy.h): [(key, shape, lo, hi)]
+        self.layout = [("std", (self.num_actions,), 0, self.num_actions)]
+        o = self.num_actions
+        self.body_slices = {}
+        for name, _ in _BODIES:
+            lo_body = o
+            dims = [n_in[name]] + self.hidden[name] + [n_out[name]]
+            for l, (a, b) in enumerate(zip(dims[:-1], dims[1:])):
+                self.layout.append((f"{name}.{2 * l}.weight", (b, a), o, o + a * b))
+                o += a * b
+                self.layout.append((f"{name}.{2 * l}.bias", (b,), o, o + b))
+                o += b
+            self.body_slices[name] = (lo_body, o)
+        self.num_params = o
+        self.device = torch.device("cpu")
+        self.flat = torch.empty(o, dtype=torch.float32)
+        self._init_parameters()
+        self.grads = None                 # bound by PPO (dist.GradExchange.grads)
+        self._h, self._cap, self._training, self._dirty = None, 0, False, True
+        self._dist = None                 # (mean, sigma) of the last act(): the reference's self.distribution
+
+    def _init_parameters(self):
+        """torch.nn.Linear's default initialisation, drawn in the order the reference constructs its layers (adaptation
+        module, actor, critic; weight then bias; actor_critic.py:43-82), so a seeded run starts from the same weights."""
+        views = self._views()
+        for key, shape, _, _ in self.layout:
+            if key.endswith(".weight"):
+                lin = torch.nn.Linear(shape[1], shape[0])          # used as the initialiser only
+                views[key].copy_(lin.weight.detach())
+                views[key[:-6] + "bias"].copy_(lin.bias.detach())
+        views["std"].fill_(float(AC_Args.init_noise_std))
+
+    def _views(self):
+        return OrderedDict((key, self.flat[lo:hi].view(shape)) for key, shape, lo, hi in self.layout)
+
+    # ------------------------------------------------------------------------------------------ nn.Module look-alikes
+    def state_dict(self):
+        return self._views()
+
+    def load_state_dict(self, state_dict, strict=True):
+        views = self._views()
+        missing, unexpected = [k for k in views if k not in state_dict], [k for k in state_dict if k not in views]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"ActorCritic.load_state_dict: missing keys {missing}, unexpected keys {unexpected}")
+        for k, v in views.items():
+            if k in state_dict:
+                src = torch.as_tensor(state_dict[k])
+                if tuple(src.shape) != tuple(v.shape):
+                    raise RuntimeError(f"ActorCritic.load_state_dict: {k} has shape {tuple(src.shape)}, expected {tuple(v.shape)}")
+                v.copy_(src)
+        self._dirty = True
+
+    def parameters(self):
+        return iter(self._views().values())
+
+    @property
+    def std(self):
+        return self.flat[:self.num_actions]
+
+    def to(self, device):
+        device = torch.device(device)
+        if device.type == "cuda" and device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        if device != self.device:
+            self._release()
+            self.flat = self.flat.to(device)
+            self.grads = None
+            self.device = device
+        return self
+
+    def train(self, mode=True):
+        return self
+
+    def eval(self):
+        return self
 
     def reset(self, dones=None):
         pass
@@ -113,29 +203,132 @@ class ActorCritic(nn.Module):
     def forward(self):
         raise NotImplementedError
 
+    def parameters_changed(self):
+        """Call after writing self.flat from outside (broadcast, checkpoint surgery): the operand planes are re-derived
+        before the next launch."""
+        self._dirty = True
+
+    # ------------------------------------------------------------------------------------------ library handle
+    def _release(self):
+        if self._h is not None:
+            _abi.load().lt_policy_destroy(self._h)
+        self._h, self._cap, self._training = None, 0, False
+
+    def __del__(self):
+        try:
+            self._release()
+        except Exception:
+            pass
+
+    def reserve(self, rows, training=False):
+        """Size the library's workspaces for `rows` samples per call (and for gradients)."""
+        if self.device.type != "cuda":
+            raise _abi.LtError("the actor-critic runs as sm_100a kernels only: move it to a CUDA device (there is no CPU path)")
+        rows = int(rows)
+        if self._h is not None and rows <= self._cap and (self._training or not training):
+            return
+        training = training or self._training
+        rows = max(rows, self._cap)
+        lib = _abi.load()
+        if self._h is not None:
+            torch.cuda.synchronize(self.device)
+            self._release()
+        cfg = _abi.lt_policy_config()
+        cfg.struct_bytes = C.sizeof(_abi.lt_policy_config)
+        cfg.num_obs_history, cfg.num_privileged_obs, cfg.num_actions = self.num_obs_history, self.num_privileged_obs, self.num_actions
+        for cname, name in (("adaptation", "adaptation_module"), ("actor", "actor_body"), ("critic", "critic_body")):
+            h = self.hidden[name]
+            if not 1 <= len(h) <= _abi.DEFINES["LT_POLICY_MAX_HIDDEN"]:
+                raise _abi.LtError(f"{name}: {len(h)} hidden layers, the kernels take 1..{_abi.DEFINES['LT_POLICY_MAX_HIDDEN']}")
+            setattr(cfg, f"n_{cname}_hidden", len(h))
+            arr = getattr(cfg, f"{cname}_hidden")
+            for i, w in enumerate(h):
+                arr[i] = w
+        cfg.max_rows, cfg.training = rows, 1 if training else 0
+        cfg.activation = _abi.DEFINES[_ACTIVATIONS[self.activation]]
+        handle = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _abi.check_policy(lib.lt_policy_create(C.byref(cfg), C.byref(handle)), None, "lt_policy_create")
+        self._h, self._cap, self._training = handle, rows, training
+        if lib.lt_policy_num_params(handle) != self.num_params:
+            raise _abi.LtError("flat parameter layout differs between ppo.py and the library")
+        if training and self.grads is None:
+            self.grads = torch.zeros(self.num_params, dtype=torch.float32, device=self.device)
+        self._bind()
+
+    def _bind(self):
+        if self._h is not None:
+            _abi.check_policy(_abi.load().lt_policy_bind_params(self._h, _ptr(self.flat), _ptr(self.grads)), self._h, "lt_policy_bind_params")
+            self._dirty = True
+
+    def bind_grads(self, grads):
+        self.grads = grads
+        self._bind()
+
+    def _ready(self, rows, training=False):
+        self.reserve(rows, training)
+        if self._dirty:
+            _abi.check_policy(_abi.load().lt_policy_refresh(self._h, _stream(self.device)), self._h, "lt_policy_refresh")
+            self._dirty = False
+        return _abi.load()
+
+    # ------------------------------------------------------------------------------------------ forward entry points
+    def _forward(self, obs_history, privileged_obs, teacher, want_latent, want_mean, want_value):
+        oh = _f32c(obs_history, self.device, "obs_history")
+        pv = _f32c(privileged_obs, self.device, "privileged_obs")
+        rows = oh.shape[0]
+        lib = self._ready(rows)
+        new = lambda w: torch.empty(rows, w, dtype=torch.float32, device=self.device)
+        latent = new(self.num_privileged_obs) if want_latent else None
+        mean = new(self.num_actions) if want_mean else None
+        value = new(1) if want_value else None
+        _abi.check_policy(lib.lt_policy_forward(self._h, _ptr(oh), _ptr(pv), rows, 1 if teacher else 0, _ptr(latent), _ptr(mean),
+                                                _ptr(value), _stream(self.device)), self._h, "lt_policy_forward")
+        return latent, mean, value
+
+    def act_into(self, obs_history, privileged_obs, out, actions_in=None, normal_noise=None, seed=0, step=0):
+        """PPO.act fused (ppo.py:65-77): forward, sample, log-prob, value, written straight into the tensors of `out`
+        (keys actions, actions_log_prob, action_mean, action_sigma, value; any may be missing)."""
+        oh = _f32c(obs_history, self.device, "obs_history")
+        pv = _f32c(privileged_obs, self.device, "privileged_obs")
+        rows = oh.shape[0]
+        lib = self._ready(rows)
+        given = _f32c(actions_in, self.device, "actions")
+        noise = _f32c(normal_noise, self.device, "normal_noise")
+        o = lambda k: _ptr(out.get(k))
+        _abi.check_policy(lib.lt_policy_act(self._h, _ptr(oh), _ptr(pv), rows, _ptr(noise), _ptr(given), C.c_uint64(seed), C.c_uint64(step),
+                                            o("actions"), o("actions_log_prob"), o("action_mean"), o("action_sigma"), o("value"),
+                                            _stream(self.device)), self._h, "lt_policy_act")
+        self._keep = (oh, pv, given, noise)          # inputs stay referenced until the next call (asynchronous launch)
+
+    def update_distribution(self, observation_history):
+        _, mean, _ = self._forward(observation_history, None, False, False, True, False)
+        self._dist = (mean, self.std.expand_as(mean))
+
+    def act(self, observation_history, **kwargs):
+        rows = observation_history.shape[0]
+        new = lambda: torch.empty(rows, self.num_actions, dtype=torch.float32, device=self.device)
+        out = dict(actions=new(), action_mean=new(), action_sigma=new())
+        self._act_step = getattr(self, "_act_step", 0) + 1
+        self.act_into(observation_history, None, out, seed=torch.initial_seed() & (2 ** 63 - 1), step=self._act_step)
+        self._dist = (out["action_mean"], out["action_sigma"])
+        return out["actions"]
+
     @property
     def action_mean(self):
-        return self.distribution.mean
+        return self._dist[0]
 
     @property
     def action_std(self):
-        return self.distribution.stddev
+        return self._dist[1]
 
     @property
     def entropy(self):
-        return self.distribution.entropy().sum(dim=-1)
-
-    def update_distribution(self, observation_history):
-        latent = self.adaptation_module(observation_history)
-        mean = self.actor_body(torch.cat((observation_history, latent), dim=-1))
-        self.distribution = Normal(mean, mean * 0. + self.std)
-
-    def act(self, observation_history, **kwargs):
-        self.update_distribution(observation_history)
-        return self.distribution.sample()
+        return (0.5 + _LOG_SQRT_2PI + torch.log(self._dist[1])).sum(dim=-1)
 
     def get_actions_log_prob(self, actions):
-        return self.distribution.log_prob(actions).sum(dim=-1)
+        mean, sigma = self._dist
+        return (-((actions - mean) ** 2) / (2 * sigma ** 2) - torch.log(sigma) - _LOG_SQRT_2PI).sum(dim=-1)
 
     def act_expert(self, ob, policy_info={}):
         return self.act_teacher(ob["obs_history"], ob["privileged_obs"])
@@ -144,29 +337,38 @@ class ActorCritic(nn.Module):
         return self.act_student(ob["obs_history"], policy_info=policy_info)
 
     def act_student(self, observation_history, policy_info={}):
-        latent = self.adaptation_module(observation_history)
-        actions_mean = self.actor_body(torch.cat((observation_history, latent), dim=-1))
-        policy_info["latents"] = latent.detach().cpu().numpy()
-        return actions_mean
+        latent, mean, _ = self._forward(observation_history, None, False, True, True, False)
+        policy_info["latents"] = latent.cpu().numpy()
+        return mean
 
     def act_teacher(self, observation_history, privileged_info, policy_info={}):
-        actions_mean = self.actor_body(torch.cat((observation_history, privileged_info), dim=-1))
+        _, mean, _ = self._forward(observation_history, privileged_info, True, False, True, False)
         policy_info["latents"] = privileged_info
-        return actions_mean
+        return mean
 
     def evaluate(self, observation_history, privileged_observations, **kwargs):
-        return self.critic_body(torch.cat((observation_history, privileged_observations), dim=-1))
+        return self._forward(observation_history, privileged_observations, False, False, False, True)[2]
 
     def get_student_latent(self, observation_history):
-        return self.adaptation_module(observation_history)
+        return self._forward(observation_history, None, False, True, False, False)[0]
 
-
-def _ptr(t):
-    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
-
-
-def _stream(device):
-    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    # ------------------------------------------------------------------------------------------ deployment export
+    def export_module(self, name):
+        """One body as a torch.nn.Sequential on the CPU (Linear / ELU pairs, module indices as in the reference) for the
+        TorchScript files the deployment code loads (ppo_cse/__init__.py:282-303).  Export only: nothing here calls it."""
+        import torch.nn as nn
+        sd = {k: v.detach().cpu().clone() for k, v in self.state_dict().items() if k.startswith(name + ".")}
+        n_lin = len(sd) // 2
+        layers = []
+        for l in range(n_lin):
+            w = sd[f"{name}.{2 * l}.weight"]
+            layers.append(nn.Linear(w.shape[1], w.shape[0]))
+            if l != n_lin - 1:
+                layers.append(dict(elu=nn.ELU, selu=nn.SELU, relu=nn.ReLU, crelu=nn.ReLU, lrelu=nn.LeakyReLU, tanh=nn.Tanh,
+                                   sigmoid=nn.Sigmoid)[self.activation]())
+        seq = nn.Sequential(*layers)
+        seq.load_state_dict({k[len(name) + 1:]: v for k, v in sd.items()})
+        return seq
 
 
 class RolloutStorage:
@@ -284,6 +486,15 @@ class RolloutStorage:
             raise AssertionError("Rollout buffer overflow")
         self._launch_store(transition, self._POLICY_FIELDS)
 
+    _OBS_FIELDS = ("observations", "privileged_observations", "observation_histories")
+
+    def store_observations(self, transition):
+        """The observation third of a transition, at act() time (PPO.act has lt_policy_act write actions, log-prob, mean,
+        sigma and value into row t itself)."""
+        if self.step >= self.num_transitions_per_env:
+            raise AssertionError("Rollout buffer overflow")
+        self._launch_store(transition, self._OBS_FIELDS)
+
     def store_env_step(self, transition):
         """Second half, after env.step(): rewards (+ time-out bootstrap from the stored values) and dones."""
         self._launch_store(transition, self._ENV_FIELDS)
@@ -311,6 +522,16 @@ class RolloutStorage:
         trajectory_lengths = (done_indices[1:] - done_indices[:-1])
         return trajectory_lengths.float().mean(), self.rewards.mean()
 
+    def batch_ptrs(self):
+        """lt_ppo_batch_ptrs over the flat [T*N, w] views (rollout_storage.py:104-116): a minibatch is a list of row indices."""
+        b = _abi.lt_ppo_batch_ptrs()
+        for field, buf in (("obs_history", self.observation_histories), ("privileged_obs", self.privileged_observations),
+                           ("actions", self.actions), ("values", self.values), ("returns", self.returns),
+                           ("advantages", self.advantages), ("old_actions_log_prob", self.actions_log_prob),
+                           ("old_mu", self.mu), ("old_sigma", self.sigma)):
+            setattr(b, field, buf.data_ptr())
+        return b
+
     def flat_views(self):
         return dict(observations=self.observations.flatten(0, 1), privileged_obs=self.privileged_observations.flatten(0, 1),
                     obs_history=self.observation_histories.flatten(0, 1), actions=self.actions.flatten(0, 1),
@@ -333,99 +554,46 @@ class RolloutStorage:
                        f["old_sigma"][b], None, f["env_bins"][b])
 
 
-def ppo_losses(actor_critic, batch, args=PPO_Args):
-    """Surrogate / value / entropy terms of one minibatch (ppo.py:104-141).  Pure torch, device agnostic.
-    -> (loss, surrogate_loss, value_loss, kl_mean or None)"""
-    (_, _, privileged_obs_batch, obs_history_batch, actions_batch, target_values_batch, advantages_batch, returns_batch,
-     old_actions_log_prob_batch, old_mu_batch, old_sigma_batch, masks_batch, _) = batch
-    actor_critic.act(obs_history_batch, masks=masks_batch)
-    actions_log_prob_batch = actor_critic.get_actions_log_prob(actions_batch)
-    value_batch = actor_critic.evaluate(obs_history_batch, privileged_obs_batch, masks=masks_batch)
-    mu_batch, sigma_batch, entropy_batch = actor_critic.action_mean, actor_critic.action_std, actor_critic.entropy
-    kl_mean = None
-    if args.desired_kl is not None and args.schedule == 'adaptive':
-        with torch.no_grad():
-            kl = torch.sum(torch.log(sigma_batch / old_sigma_batch + 1.e-5)
-                           + (torch.square(old_sigma_batch) + torch.square(old_mu_batch - mu_batch))
-                           / (2.0 * torch.square(sigma_batch)) - 0.5, axis=-1)
-            kl_mean = torch.mean(kl)
-    ratio = torch.exp(actions_log_prob_batch - torch.squeeze(old_actions_log_prob_batch))
-    adv = torch.squeeze(advantages_batch)
-    surrogate = -adv * ratio
-    surrogate_clipped = -adv * torch.clamp(ratio, 1.0 - args.clip_param, 1.0 + args.clip_param)
-    surrogate_loss = torch.max(surrogate, surrogate_clipped).mean()
-    if args.use_clipped_value_loss:
-        value_clipped = target_values_batch + (value_batch - target_values_batch).clamp(-args.clip_param, args.clip_param)
-        value_loss = torch.max((value_batch - returns_batch).pow(2), (value_clipped - returns_batch).pow(2)).mean()
-    else:
-        value_loss = (returns_batch - value_batch).pow(2).mean()
-    loss = surrogate_loss + args.value_loss_coef * value_loss - args.entropy_coef * entropy_batch.mean()
-    return loss, surrogate_loss, value_loss, kl_mean
-
-
-def next_learning_rate(lr, kl_mean, args=PPO_Args):
-    """Adaptive-KL schedule (ppo.py:118-121)."""
-    if kl_mean > args.desired_kl * 2.0:
-        return max(1e-5, lr / 1.5)
-    if kl_mean < args.desired_kl / 2.0 and kl_mean > 0.0:
-        return min(1e-2, lr * 1.5)
-    return lr
-
-
-class FlatParams:
-    """All parameters of a module re-homed as views of ONE flat buffer (and their .grad as views of one flat
-    gradient bucket): Adam, the gradient-norm clip and the cross-rank gradient exchange each become a single
-    launch over ~0.6M floats instead of 26 small ones.  state_dict()/load_state_dict() are unaffected."""
-
-    def __init__(self, module):
-        self.module = module
-        self.plist = list(module.parameters())
-        n = sum(p.numel() for p in self.plist)
-        p0 = self.plist[0]
-        flat = torch.empty(n, dtype=p0.dtype, device=p0.device)
-        self.offsets = {}
-        o = 0
-        for p in self.plist:
-            flat[o:o + p.numel()].copy_(p.data.reshape(-1))
-            p.data = flat[o:o + p.numel()].view_as(p)
-            self.offsets[id(p)] = (o, o + p.numel())
-            o += p.numel()
-        self.flat = nn.Parameter(flat)
-        self.bucket = ltd.GradBucket(self.plist)
-        self.flat.grad = self.bucket.flat
-
-    def slice_of(self, submodule):
-        """(lo, hi) of a submodule's parameters inside the flat buffer (must be contiguous)."""
-        spans = sorted(self.offsets[id(p)] for p in submodule.parameters())
-        for (a, b), (c, d) in zip(spans[:-1], spans[1:]):
-            assert b == c, "submodule parameters are not contiguous in the flat buffer"
-        return spans[0][0], spans[-1][1]
-
-
 class PPO:
-    """ppo.py:33-206."""
+    """ppo.py:33-206.  act() is ONE fused library call that writes the sample, its log-prob, mean, sigma and the value straight
+    into row t of the rollout buffers; update() is, per minibatch, lt_ppo_minibatch_grad -> [cross-rank exchange] ->
+    lt_ppo_minibatch_apply -> lt_adaptation_grad -> [exchange] -> lt_adaptation_apply, with the learning rate, the KL decision,
+    the clip coefficient and every loss sum staying on the device (one host read at the end of the update; the reference
+    synchronises four times per minibatch)."""
 
     def __init__(self, actor_critic, device='cuda:0'):
         self.device = torch.device(device)
-        self.actor_critic = actor_critic
-        self.actor_critic.to(self.device)
-        self.storage = None
-        self.fp = FlatParams(self.actor_critic)
-        self.optimizer = torch.optim.Adam([self.fp.flat], lr=PPO_Args.learning_rate)
-        # ppo.py:45-46 builds the second Adam over ALL parameters, but only the adaptation module ever holds a gradient
-        # when it steps (zero_grad() leaves the others None, which Adam skips): an Adam over that slice is the same update.
-        lo, hi = self.fp.slice_of(self.actor_critic.adaptation_module)
-        self._ad_slice = (lo, hi)
-        self.ad_flat = nn.Parameter(self.fp.flat.data[lo:hi])
-        self.ad_flat.grad = self.fp.bucket.flat[lo:hi]
-        self.adaptation_module_optimizer = torch.optim.Adam([self.ad_flat], lr=PPO_Args.adaptation_module_learning_rate)
-        self.transition = RolloutStorage.Transition()
+        if self.device.type != "cuda":
+            raise _abi.LtError("PPO runs as sm_100a kernels only (liblt_b200.so): there is no CPU path")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = _abi.load()
+        self.actor_critic = actor_critic.to(self.device)
+        n = self.actor_critic.num_params
+        if ltd.world_size() > 1:           # replicas start from rank 0's weights whatever each rank's seed was
+            ltd.broadcast_(self.actor_critic.flat, src=0)
+            self.actor_critic.parameters_changed()
+        self.exchange = ltd.GradExchange(n, self.device, stats=_abi.DEFINES["LT_PPO_STATS"])
+        self.actor_critic.bind_grads(self.exchange.grads)
+        z = lambda: torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.adam_m, self.adam_v = z(), z()                  # torch.optim.Adam state of self.optimizer (ppo.py:44)
+        # ppo.py:45-46 builds the second Adam over ALL parameters, but only the adaptation module ever holds a gradient when it
+        # steps (zero_grad() leaves the others None, which Adam skips): moments over that slice are the same update.
+        self.ad_m, self.ad_v = z(), z()
+        self.adam_step, self.ad_step = 0, 0
         self.learning_rate = PPO_Args.learning_rate
+        self.lr_dev = torch.tensor([self.learning_rate], dtype=torch.float32, device=self.device)
+        self.storage = None
+        self.transition = RolloutStorage.Transition()
         self.last_update_trace = None
+        self.sample_seed = (torch.initial_seed() + 0x9E3779B97F4A7C15 * (ltd.rank() + 1)) & (2 ** 63 - 1)
+        self.act_calls = 0
 
     def init_storage(self, num_envs, num_transitions_per_env, actor_obs_shape, privileged_obs_shape, obs_history_shape, action_shape):
         self.storage = RolloutStorage(num_envs, num_transitions_per_env, actor_obs_shape, privileged_obs_shape,
                                       obs_history_shape, action_shape, self.device)
+        mb = num_envs * num_transitions_per_env // PPO_Args.num_mini_batches
+        self.actor_critic.reserve(max(int(num_envs), int(mb)), training=True)
 
     def test_mode(self):
         self.actor_critic.eval()
@@ -435,18 +603,25 @@ class PPO:
 
     def act(self, obs, privileged_obs, obs_history, actions=None):
         """ppo.py:65-78.  `actions` (tests only) replaces the sample so that a recorded rollout can be replayed."""
-        sampled = self.actor_critic.act(obs_history).detach()
-        self.transition.actions = sampled if actions is None else actions
-        self.transition.values = self.actor_critic.evaluate(obs_history, privileged_obs).detach()
-        self.transition.actions_log_prob = self.actor_critic.get_actions_log_prob(self.transition.actions).detach()
-        self.transition.action_mean = self.actor_critic.action_mean.detach()
-        self.transition.action_sigma = self.actor_critic.action_std.detach()
-        self.transition.observations = obs
-        self.transition.critic_observations = obs
-        self.transition.privileged_observations = privileged_obs
-        self.transition.observation_histories = obs_history
-        self.storage.store_policy_step(self.transition)       # captured now: env.step() rewrites its buffers in place
-        return self.transition.actions
+        st, tr = self.storage, self.transition
+        t = st.step
+        if t >= st.num_transitions_per_env:
+            raise AssertionError("Rollout buffer overflow")
+        if obs_history.shape[0] != st.num_envs:
+            raise ValueError(f"act() got {obs_history.shape[0]} rows, the storage holds {st.num_envs} envs")
+        tr.actions, tr.values, tr.actions_log_prob = st.actions[t], st.values[t], st.actions_log_prob[t]
+        tr.action_mean, tr.action_sigma = st.mu[t], st.sigma[t]
+        self.act_calls += 1
+        self.actor_critic.act_into(obs_history, privileged_obs,
+                                   dict(actions=tr.actions, actions_log_prob=tr.actions_log_prob, action_mean=tr.action_mean,
+                                        action_sigma=tr.action_sigma, value=tr.values),
+                                   actions_in=actions, seed=self.sample_seed, step=self.act_calls)
+        tr.observations = obs
+        tr.critic_observations = obs
+        tr.privileged_observations = privileged_obs
+        tr.observation_histories = obs_history
+        st.store_observations(tr)                 # captured now: env.step() rewrites its buffers in place
+        return tr.actions
 
     def process_env_step(self, rewards, dones, infos):
         """ppo.py:80-93.  The time-out bootstrap rewards += gamma * values * time_outs happens inside lt_rollout_store."""
@@ -458,57 +633,79 @@ class PPO:
         self.actor_critic.reset(dones)
 
     def compute_returns(self, last_critic_obs, last_critic_privileged_obs):
-        last_values = self.actor_critic.evaluate(last_critic_obs, last_critic_privileged_obs).detach()
+        last_values = self.actor_critic.evaluate(last_critic_obs, last_critic_privileged_obs)
         self.storage.compute_returns(last_values, PPO_Args.gamma, PPO_Args.lam)
 
+    @staticmethod
+    def hparams(A=PPO_Args):
+        hp = _abi.lt_ppo_hparams()
+        hp.clip_param, hp.value_loss_coef, hp.entropy_coef = A.clip_param, A.value_loss_coef, A.entropy_coef
+        hp.max_grad_norm = A.max_grad_norm
+        hp.adaptive_schedule = 1 if (A.desired_kl is not None and A.schedule == 'adaptive') else 0
+        hp.desired_kl = A.desired_kl if A.desired_kl is not None else 0.0
+        hp.adam_beta1, hp.adam_beta2, hp.adam_eps = 0.9, 0.999, 1e-8          # torch.optim.Adam defaults (ppo.py:44-46)
+        hp.lr_min, hp.lr_max, hp.lr_factor = 1e-5, 1e-2, 1.5                   # ppo.py:118-121
+        hp.use_clipped_value_loss = 1 if A.use_clipped_value_loss else 0
+        return hp
+
     def update(self, indices=None):
-        """ppo.py:95-206.  `indices` (tests only) injects the minibatch permutation."""
+        """ppo.py:95-206.  `indices` (tests only) injects the minibatch permutation (rollout_storage.py:102 draws ONE
+        torch.randperm per update and reuses it for every epoch)."""
         A = PPO_Args
-        bucket = self.fp.bucket
-        lo, hi = self._ad_slice
-        # per-minibatch scalars stay on the device; one host read at the end (the reference syncs 4x per minibatch)
-        acc = torch.zeros(4, device=self.device)
-        trace = dict(grad_norms=[], lrs=[])
-        n_mb = 0
-        for batch in self.storage.mini_batch_generator(A.num_mini_batches, A.num_learning_epochs, indices=indices):
-            loss, surrogate_loss, value_loss, kl_mean = ppo_losses(self.actor_critic, batch, A)
-            if kl_mean is not None:
-                kl_mean = ltd.allreduce_mean_scalar(kl_mean)          # every rank takes the same branch
-                self.learning_rate = next_learning_rate(self.learning_rate, kl_mean.item(), A)
-                for g in self.optimizer.param_groups:
-                    g['lr'] = self.learning_rate
-            bucket.attach()
-            loss.backward()
-            bucket.allreduce_mean()
-            total_norm = torch.linalg.vector_norm(bucket.flat)
-            bucket.flat.mul_(torch.clamp(A.max_grad_norm / (total_norm + 1e-6), max=1.0))   # nn.utils.clip_grad_norm_
-            self.optimizer.step()
-            trace["grad_norms"].append(total_norm)
-            trace["lrs"].append(self.learning_rate)
-            acc[0] += value_loss.detach()
-            acc[1] += surrogate_loss.detach()
-            privileged_obs_batch, obs_history_batch = batch[2], batch[3]
-            num_train = int(privileged_obs_batch.shape[0] // 5 * 4)
-            for _ in range(A.num_adaptation_module_substeps):
-                pred = self.actor_critic.adaptation_module(obs_history_batch)
-                adaptation_loss = F.mse_loss(pred[:num_train], privileged_obs_batch[:num_train])
-                with torch.no_grad():
-                    adaptation_test_loss = F.mse_loss(pred[num_train:], privileged_obs_batch[num_train:])
-                bucket.flat[lo:hi].zero_()
-                adaptation_loss.backward()
-                if ltd.world_size() > 1:
-                    ltd.allreduce_sum_(bucket.flat[lo:hi]).div_(ltd.world_size())
-                self.adaptation_module_optimizer.step()
-                acc[2] += adaptation_loss.detach()
-                acc[3] += adaptation_test_loss
-            n_mb += 1
+        st, ac, ex, lib = self.storage, self.actor_critic, self.exchange, self.lib
+        batch_size = st.num_envs * st.num_transitions_per_env
+        mb = batch_size // A.num_mini_batches
+        if indices is None:
+            indices = torch.randperm(A.num_mini_batches * mb, device=self.device)
+        indices = indices.to(device=self.device, dtype=torch.int64).contiguous()
+        batch = st.batch_ptrs()
+        hp = self.hparams(A)
+        world = ltd.world_size()
+        ac._ready(mb, training=True)
+        h, s = ac._h, _stream(self.device)
+        n_sub = int(A.num_adaptation_module_substeps)
         num_updates = A.num_learning_epochs * A.num_mini_batches
-        acc = acc.tolist()
-        n_sub = num_updates * A.num_adaptation_module_substeps
-        trace["grad_norms"] = [float(x) for x in torch.stack(trace["grad_norms"]).tolist()] if trace["grad_norms"] else []
-        self.last_update_trace = trace
-        self.storage.clear()
-        return acc[0] / num_updates, acc[1] / num_updates, acc[2] / n_sub, 0.0, 0.0, acc[3] / n_sub, 0.0, 0.0
+        ad_lo, ad_hi = ac.body_slices["adaptation_module"]
+        # per-minibatch records, all on the device: [k] = stats[0..4) | lr | grad norm, and the adaptation sums per substep
+        rec = torch.zeros(num_updates, 6, dtype=torch.float32, device=self.device)
+        rec_ad = torch.zeros(num_updates, max(n_sub, 1), 4, dtype=torch.float32, device=self.device)
+        num_train = int(mb // 5 * 4)                                            # ppo.py:160-161
+        self.lr_dev.fill_(self.learning_rate)
+        k = 0
+        for _epoch in range(A.num_learning_epochs):
+            for i in range(A.num_mini_batches):
+                idx = C.c_void_p(indices.data_ptr() + 8 * i * mb)
+                _abi.check_policy(lib.lt_ppo_minibatch_grad(h, C.byref(batch), idx, mb, C.byref(hp), world, _ptr(ex.stats), s), h,
+                                  "lt_ppo_minibatch_grad")
+                ex.exchange_main()
+                self.adam_step += 1
+                _abi.check_policy(lib.lt_ppo_minibatch_apply(h, C.byref(hp), _ptr(ex.stats), _ptr(self.lr_dev), _ptr(self.adam_m),
+                                                             _ptr(self.adam_v), self.adam_step, C.c_void_p(rec[k, 5:].data_ptr()), s), h,
+                                  "lt_ppo_minibatch_apply")
+                rec[k, :4].copy_(ex.stats[:4])
+                rec[k, 4:5].copy_(self.lr_dev)
+                for sub in range(n_sub):
+                    _abi.check_policy(lib.lt_adaptation_grad(h, C.byref(batch), idx, mb, num_train, world, _ptr(ex.stats), s), h,
+                                      "lt_adaptation_grad")
+                    ex.exchange_adaptation(ad_hi)
+                    self.ad_step += 1
+                    _abi.check_policy(lib.lt_adaptation_apply(h, C.byref(hp), C.c_float(A.adaptation_module_learning_rate), _ptr(self.ad_m),
+                                                              _ptr(self.ad_v), self.ad_step, s), h, "lt_adaptation_apply")
+                    rec_ad[k, sub].copy_(ex.stats[4:8])
+                k += 1
+        ac._dirty = False                          # the apply calls refreshed the operand planes themselves
+        rec_h, ad_h = rec.double().cpu(), rec_ad.double().cpu()                 # the one host read of the update
+        surr, vl, rows = rec_h[:, 0], rec_h[:, 1], rec_h[:, 3]
+        self.learning_rate = float(rec_h[-1, 4]) if num_updates else self.learning_rate
+        self.last_update_trace = dict(grad_norms=rec_h[:, 5].tolist(), lrs=[float(x) for x in rec_h[:, 4].float().tolist()],
+                                      kl_means=(rec_h[:, 2] / rec_h[:, 3]).tolist())
+        mean_value_loss = float((vl / rows).sum()) / num_updates
+        mean_surrogate_loss = float((surr / rows).sum()) / num_updates
+        n_ad = max(num_updates * n_sub, 1)
+        ad_train = float((ad_h[:, :n_sub, 0] / ad_h[:, :n_sub, 1].clamp(min=1)).sum()) / n_ad
+        ad_test = float((ad_h[:, :n_sub, 2] / ad_h[:, :n_sub, 3].clamp(min=1)).sum()) / n_ad
+        st.clear()
+        return mean_value_loss, mean_surrogate_loss, ad_train, 0.0, 0.0, ad_test, 0.0, 0.0
 
 
 class Runner:
@@ -525,7 +722,7 @@ class Runner:
                                    self.env.num_actions).to(self.device)
         if runner_args.resume:
             actor_critic.load_state_dict(torch.load(runner_args.resume, map_location=self.device))
-        self.alg = PPO(actor_critic, device=self.device)
+        self.alg = PPO(actor_critic, device=self.device)         # broadcasts rank 0's weights when env-sharded
         self.num_steps_per_env = runner_args.num_steps_per_env
         self.alg.init_storage(self.env.num_train_envs, self.num_steps_per_env, [self.env.num_obs],
                               [self.env.num_privileged_obs], [self.env.num_obs_history], [self.env.num_actions])
@@ -601,19 +798,19 @@ class Runner:
         """ac_weights.pt + adaptation_module_latest.jit + body_latest.jit (ppo_cse/__init__.py:282-303)."""
         os.makedirs(save_path, exist_ok=True)
         torch.save(self.alg.actor_critic.state_dict(), os.path.join(save_path, "ac_weights.pt"))
-        for name, mod in (("adaptation_module_latest.jit", self.alg.actor_critic.adaptation_module),
-                          ("body_latest.jit", self.alg.actor_critic.actor_body)):
-            m = copy.deepcopy(mod).to('cpu')
-            torch.jit.script(m).save(os.path.join(save_path, name))
+        for name, body in (("adaptation_module_latest.jit", "adaptation_module"), ("body_latest.jit", "actor_body")):
+            torch.jit.script(self.alg.actor_critic.export_module(body)).save(os.path.join(save_path, name))
 
     def get_inference_policy(self, device=None):
-        self.alg.actor_critic.eval()
-        if device is not None and torch.device(device) != self.alg.device:
-            return copy.deepcopy(self.alg.actor_critic).to(device).act_inference      # the live copy stays flat-bucketed
+        """-> callable(obs_dict) on the training GPU.  For another device (deployment) load the TorchScript files save() writes."""
+        self._same_device(device)
         return self.alg.actor_critic.act_inference
 
     def get_expert_policy(self, device=None):
-        self.alg.actor_critic.eval()
-        if device is not None and torch.device(device) != self.alg.device:
-            return copy.deepcopy(self.alg.actor_critic).to(device).act_expert
+        self._same_device(device)
         return self.alg.actor_critic.act_expert
+
+    def _same_device(self, device):
+        if device is not None and torch.device(device).type != "cuda":
+            raise _abi.LtError("the policy runs as sm_100a kernels: for CPU / robot deployment load adaptation_module_latest.jit "
+                               "and body_latest.jit written by Runner.save()")

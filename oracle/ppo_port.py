@@ -75,6 +75,29 @@ def gae(rewards, values, dones, last_values, gamma, lam):
     return returns, (adv - adv.mean()) / (adv.std() + 1e-8)
 
 
+def minibatch_loss(params, act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a):
+    """ppo.py:104-141 for one minibatch.  -> (loss, surrogate_loss, value_loss, kl_mean or None)"""
+    mu, sigma, value = policy_forward(params, act, hist, priv)
+    logp = normal_log_prob(actions, mu, sigma)
+    entropy = normal_entropy(sigma)
+    kl_mean = None
+    if a["desired_kl"] is not None and a["schedule"] == "adaptive":
+        with torch.no_grad():
+            kl = torch.sum(torch.log(sigma / old_sigma + 1.e-5)
+                           + (torch.square(old_sigma) + torch.square(old_mu - mu)) / (2.0 * torch.square(sigma)) - 0.5, axis=-1)
+            kl_mean = torch.mean(kl)
+    ratio = torch.exp(logp - torch.squeeze(old_logp))
+    adv = torch.squeeze(advantages)
+    surrogate_loss = torch.max(-adv * ratio, -adv * torch.clamp(ratio, 1.0 - a["clip_param"], 1.0 + a["clip_param"])).mean()
+    if a["use_clipped_value_loss"]:
+        value_clipped = target_values + (value - target_values).clamp(-a["clip_param"], a["clip_param"])
+        value_loss = torch.max((value - returns).pow(2), (value_clipped - returns).pow(2)).mean()
+    else:
+        value_loss = (returns - value).pow(2).mean()
+    loss = surrogate_loss + a["value_loss_coef"] * value_loss - a["entropy_coef"] * entropy.mean()
+    return loss, surrogate_loss, value_loss, kl_mean
+
+
 class PpoPort:
     """State: params (dict of leaf tensors named as the reference's state_dict), two Adam optimisers over ALL
     parameters (ppo.py:44-46 -- the second one only ever sees adaptation-module gradients), the [T,N,*] storage."""
@@ -144,29 +167,15 @@ class PpoPort:
                 hist, priv, actions = flat["observation_histories"][idx], flat["privileged_observations"][idx], flat["actions"][idx]
                 target_values, advantages, returns = flat["values"][idx], flat["advantages"][idx], flat["returns"][idx]
                 old_logp, old_mu, old_sigma = flat["actions_log_prob"][idx], flat["mu"][idx], flat["sigma"][idx]
-                mu, sigma, value = policy_forward(self.params, self.act, hist, priv)
-                logp = normal_log_prob(actions, mu, sigma)
-                entropy = normal_entropy(sigma)
-                if a["desired_kl"] is not None and a["schedule"] == "adaptive":
-                    with torch.no_grad():
-                        kl = torch.sum(torch.log(sigma / old_sigma + 1.e-5)
-                                       + (torch.square(old_sigma) + torch.square(old_mu - mu)) / (2.0 * torch.square(sigma)) - 0.5, axis=-1)
-                        kl_mean = torch.mean(kl)
-                        if kl_mean > a["desired_kl"] * 2.0:
-                            self.learning_rate = max(1e-5, self.learning_rate / 1.5)
-                        elif kl_mean < a["desired_kl"] / 2.0 and kl_mean > 0.0:
-                            self.learning_rate = min(1e-2, self.learning_rate * 1.5)
-                        for g in self.optimizer.param_groups:
-                            g["lr"] = self.learning_rate
-                ratio = torch.exp(logp - torch.squeeze(old_logp))
-                adv = torch.squeeze(advantages)
-                surrogate_loss = torch.max(-adv * ratio, -adv * torch.clamp(ratio, 1.0 - a["clip_param"], 1.0 + a["clip_param"])).mean()
-                if a["use_clipped_value_loss"]:
-                    value_clipped = target_values + (value - target_values).clamp(-a["clip_param"], a["clip_param"])
-                    value_loss = torch.max((value - returns).pow(2), (value_clipped - returns).pow(2)).mean()
-                else:
-                    value_loss = (returns - value).pow(2).mean()
-                loss = surrogate_loss + a["value_loss_coef"] * value_loss - a["entropy_coef"] * entropy.mean()
+                loss, surrogate_loss, value_loss, kl_mean = minibatch_loss(
+                    self.params, self.act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a)
+                if kl_mean is not None:
+                    if kl_mean > a["desired_kl"] * 2.0:
+                        self.learning_rate = max(1e-5, self.learning_rate / 1.5)
+                    elif kl_mean < a["desired_kl"] / 2.0 and kl_mean > 0.0:
+                        self.learning_rate = min(1e-2, self.learning_rate * 1.5)
+                    for g in self.optimizer.param_groups:
+                        g["lr"] = self.learning_rate
                 self.optimizer.zero_grad()
                 loss.backward()
                 norms.append(float(torch.nn.utils.clip_grad_norm_(plist, a["max_grad_norm"])))

@@ -1,5 +1,7 @@
-"""world_size-2 `gloo` tests (CPU) of the env-sharded N>1 path: shard bounds, advantage-moment merge, the flat gradient
-bucket exchange, and a full PPO.update on two ranks that must reproduce the single-process update."""
+"""world_size-2 `gloo` tests (CPU) of the env-sharded N>1 path: shard bounds, advantage-moment merge, the [stats | gradient]
+exchange buffer of the PPO update, the parameter broadcast and the reward-sign exchange.  The arithmetic on either side of
+these collectives is CUDA-only; tests/test_gpu_policy.py checks on one GPU that two half-minibatch gradients produced with
+grad_world = 2 sum to the full-minibatch gradient."""
 import os
 import socket
 
@@ -88,51 +90,46 @@ def test_advantage_moments_merge_to_global_statistics():
         assert abs(out[r][0]) < 1e-14 and abs(out[r][1]) < 1e-13
 
 
-def _bucket(r, world):
-    torch.manual_seed(0)
-    lin = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 2))
-    x = torch.randn(16, 5)
-    ref = torch.autograd.grad(lin(x).pow(2).mean(), list(lin.parameters()))
-    b = ltd.GradBucket(lin.parameters())
-    b.attach()
-    lin(x[r::world]).pow(2).mean().backward()
-    b.allreduce_mean()
-    return max(float((p.grad - g).abs().max()) for p, g in zip(lin.parameters(), ref))
+def _exchange(r, world):
+    """dist.GradExchange: the [stats | gradient] buffer of the PPO update.  Rank r holds (r + 1) everywhere."""
+    n, hi = 40, 17
+    ex = ltd.GradExchange(n, "cpu", stats=16)
+    assert ex.stats.data_ptr() == ex.buf.data_ptr() and ex.grads.data_ptr() == ex.buf.data_ptr() + 64
+    ex.buf.fill_(float(r + 1))
+    ex.exchange_main()
+    total = float(sum(range(1, world + 1)))
+    ok_main = bool((ex.buf == total).all())
+    # adaptation step: stats[4..16) and gradient[0..hi) are summed again; stats[0..4) (already global) and the rest are not
+    ex.buf.fill_(float(r + 1))
+    ex.stats[:4] = 100.0
+    ex.exchange_adaptation(hi)
+    ok_ad = (bool((ex.stats[:4] == 100.0).all()) and bool((ex.stats[4:] == total).all()) and bool((ex.grads[:hi] == total).all())
+             and bool((ex.grads[hi:] == float(r + 1)).all()))
+    # replicas start from rank 0's parameters whatever each rank drew
+    p = torch.full((5,), float(r + 7))
+    ltd.broadcast_(p, src=0)
+    return ok_main, ok_ad, p.tolist(), ex.calls, ex.bytes
 
 
-def test_grad_bucket_mean_allreduce_equals_full_batch_gradient():
-    out = _spawn(_bucket, 2)
-    assert max(out.values()) < 1e-7
-
-
-def _ppo_update(r, world, name):
-    from legged_tracking_b200 import ppo
-    from tests.helpers_ppo import HostStorage, actor_critic_from_golden, golden_args, load_case
-    g = load_case(name)
-    with golden_args(g):
-        # minibatch 160 -> adaptation train split 128; per rank 80 -> 64: every rank's split is its half of the global one
-        ppo.PPO_Args.num_mini_batches = 2
-        fields = {k: torch.from_numpy(g["storage/" + k][:5]) for k in
-                  ("observations", "privileged_observations", "observation_histories", "actions", "values", "returns",
-                   "actions_log_prob", "advantages", "mu", "sigma")}
-        perm = torch.from_numpy(np.random.default_rng(1).permutation(320))
-        ac = actor_critic_from_golden(g)
-        alg = ppo.PPO(ac, device="cpu")
-        alg.storage = HostStorage(fields, part=(r, world))
-        losses = alg.update(indices=perm)
-        return dict(losses=losses, lrs=alg.last_update_trace["lrs"], sd={k: v.numpy().copy() for k, v in ac.state_dict().items()})
-
-
-def test_two_rank_ppo_update_equals_single_process():
-    name = "ppo_adaptive_64x8"
-    single = _spawn(_ppo_update, 1, name)[0]
-    two = _spawn(_ppo_update, 2, name)
+def test_grad_exchange_sums_the_right_slices_and_broadcast_aligns_replicas():
+    out = _spawn(_exchange, 2)
     for r in (0, 1):
-        assert two[r]["lrs"] == single["lrs"]
-        for k, v in single["sd"].items():
-            np.testing.assert_allclose(two[r]["sd"][k], v, rtol=2e-4, atol=2e-5, err_msg=k)
-    for k, v in two[0]["sd"].items():
-        assert np.array_equal(v, two[1]["sd"][k]), k            # replicas stay bit-identical
-    # loss means: surrogate/value are means of half-batch means
-    np.testing.assert_allclose(0.5 * (np.asarray(two[0]["losses"]) + np.asarray(two[1]["losses"]))[:3],
-                               np.asarray(single["losses"])[:3], rtol=2e-4, atol=1e-6)
+        ok_main, ok_ad, p, calls, nbytes = out[r]
+        assert ok_main and ok_ad
+        assert p == [7.0] * 5
+        assert calls == 2 and nbytes == 4 * (56 + 12 + 17)
+    single = _spawn(_exchange, 1)[0]
+    assert single[0] and single[3] == 0            # world 1: no collective is issued
+
+
+def _sign_exchange(r, world):
+    """StepEngine's all-env reward-sign exchange (legged_robot_trajectory_tracking.py:332-335) on the host side: shard sums
+    of opposite sign must produce the whole job's sign on every rank."""
+    sums = torch.tensor([3.0, -1.0, 0.5] if r == 0 else [-5.0, 4.0, -0.5])
+    ltd.allreduce_sum_(sums)
+    return (sums >= 0).tolist()
+
+
+def test_reward_sign_uses_the_global_sum():
+    out = _spawn(_sign_exchange, 2)
+    assert out[0] == out[1] == [False, True, True]

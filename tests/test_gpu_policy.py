@@ -36,3 +36,293 @@ def test_split_fp16_gemm_matches_float64(M, N, K, splits):
     mag = a.double().abs() @ b.double().abs().T + bias.double().abs()
     rel = ((out.double() - want).abs() / mag).max().item()
     assert rel < 2e-6, f"max error / sum|a||b| = {rel:.3e}"      # measured 2e-7 .. 1e-6 (torch fp32: 2e-7 .. 4e-7)
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# a14 / a15 through legged_tracking_b200.ppo (which only marshals pointers into include/lt_policy.h) against the oracle port
+# evaluated in float64 on the same weights and inputs.
+from tests.helpers_ppo import PPO_CASES, actor_critic_from_golden, golden_args, load_case      # noqa: E402
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _params64(ac):
+    return {k: v.detach().cpu().double().clone().requires_grad_(True) for k, v in ac.state_dict().items()}
+
+
+def _close(got, want, rtol, atol, what):
+    got, want = got.detach().cpu().double().numpy(), want.detach().cpu().double().numpy()
+    err = np.abs(got - want)
+    lim = atol + rtol * np.abs(want)
+    assert np.all(err <= lim), f"{what}: max err {err.max():.3e} (|want| up to {np.abs(want).max():.3e}), worst excess {(err - lim).max():.3e}"
+
+
+@pytest.mark.parametrize("name", PPO_CASES)          # ELU and tanh bodies
+def test_policy_forward_matches_oracle(name):
+    """latent / action mean / value / teacher action of lt_policy_forward: 1e-5 relative (+1e-5 of the largest output, the
+    scale fp32 GEMM error lives on) against the float64 oracle."""
+    from oracle import ppo_port
+    g = load_case(name)
+    with golden_args(g):
+        ac = actor_critic_from_golden(g, _dev())
+        p64 = _params64(ac)
+        act = ppo_port.ACTIVATIONS[ac.activation]
+        T = int(g["meta/sizes"][1])
+        for t in (0, T - 1):
+            hist, priv = torch.from_numpy(g["in/hist"][t]), torch.from_numpy(g["in/priv"][t])
+            with torch.no_grad():
+                mean, _, value = ppo_port.policy_forward(p64, act, hist.double(), priv.double())
+                latent = ppo_port.mlp(p64, "adaptation_module", hist.double(), act)
+                teacher = ppo_port.mlp(p64, "actor_body", torch.cat((hist.double(), priv.double()), dim=-1), act)
+            info = {}
+            got_mean = ac.act_student(hist.to(_dev()), policy_info=info)
+            for got, want, what in ((got_mean, mean, "mean"), (torch.from_numpy(info["latents"]), latent, "latent"),
+                                    (ac.get_student_latent(hist.to(_dev())), latent, "latent2"),
+                                    (ac.evaluate(hist.to(_dev()), priv.to(_dev())), value, "value"),
+                                    (ac.act_teacher(hist.to(_dev()), priv.to(_dev())), teacher, "teacher")):
+                _close(got, want, 1e-5, 1e-5 * float(want.abs().max()), f"{name} t={t} {what}")
+            # and the fp32 reference recording itself
+            np.testing.assert_allclose(got_mean.cpu().numpy(), g["storage/mu"][t], rtol=1e-5, atol=2e-6)
+
+
+def test_act_sampling_log_prob_and_injected_noise():
+    """lt_policy_act: actions = mean + sigma * noise exactly for injected noise; log-prob is Normal.log_prob of the returned
+    actions; the in-kernel Philox + Box-Muller draws are standard normal and differ per (step, row, action)."""
+    from legged_tracking_b200 import ppo
+    torch.manual_seed(3)
+    ac = ppo.ActorCritic(20, 3, 40, 12).to(_dev())
+    ac.load_state_dict({k: (v * 0 + 0.7 if k == "std" else v) for k, v in ac.state_dict().items()})
+    rows = 4096
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    hist = torch.randn(rows, 40, device="cuda", generator=gen)
+    priv = torch.randn(rows, 3, device="cuda", generator=gen)
+    noise = torch.randn(rows, 12, device="cuda", generator=gen)
+    new = lambda *s: torch.full(s, float("nan"), device="cuda")
+    out = dict(actions=new(rows, 12), actions_log_prob=new(rows), action_mean=new(rows, 12), action_sigma=new(rows, 12), value=new(rows, 1))
+    ac.act_into(hist, priv, out, normal_noise=noise)
+    torch.cuda.synchronize()
+    assert torch.equal(out["action_sigma"], ac.std.expand(rows, 12))
+    assert torch.equal(out["actions"], out["action_mean"] + out["action_sigma"] * noise) or \
+        torch.allclose(out["actions"], out["action_mean"] + out["action_sigma"] * noise, rtol=0, atol=1e-6)      # fma contraction
+    want_lp = torch.distributions.Normal(out["action_mean"].double(), out["action_sigma"].double()).log_prob(out["actions"].double()).sum(-1)
+    _close(out["actions_log_prob"], want_lp, 1e-5, 1e-5, "log_prob")
+    _close(out["value"], ac.evaluate(hist, priv), 0, 0, "value")
+    _close(out["action_mean"], ac.act_student(hist), 0, 0, "mean")
+    # Philox path
+    a1, a2 = dict(actions=new(rows, 12), action_mean=new(rows, 12)), dict(actions=new(rows, 12))
+    ac.act_into(hist, priv, a1, seed=5, step=1)
+    ac.act_into(hist, priv, a2, seed=5, step=2)
+    z1 = (a1["actions"] - a1["action_mean"]) / 0.7
+    z2 = (a2["actions"] - a1["action_mean"]) / 0.7
+    assert abs(float(z1.mean())) < 0.02 and abs(float(z1.std()) - 1.0) < 0.02
+    assert abs(float((z1 * z2).mean())) < 0.02                      # steps are independent
+    assert abs(float((z1[:, 0] * z1[:, 1]).mean())) < 0.05         # action columns are independent
+    a3 = dict(actions=new(rows, 12))
+    ac.act_into(hist, priv, a3, seed=5, step=1)
+    assert torch.equal(a3["actions"], a1["actions"])              # keyed, not stateful
+    # ActorCritic.act / get_actions_log_prob / entropy (the reference's distribution API)
+    a = ac.act(hist)
+    lp = ac.get_actions_log_prob(a)
+    want = torch.distributions.Normal(ac.action_mean, ac.action_std)
+    assert torch.allclose(lp, want.log_prob(a).sum(-1), rtol=1e-5, atol=1e-5)
+    assert torch.allclose(ac.entropy, want.entropy().sum(-1), rtol=1e-6)
+
+
+def _random_batch(ac, B, seed, device):
+    gen = torch.Generator().manual_seed(seed)
+    r = lambda *s: torch.randn(*s, generator=gen)
+    A, P, D = ac.num_actions, ac.num_privileged_obs, ac.num_obs_history
+    b = dict(obs_history=r(B, D), privileged_obs=r(B, P), actions=r(B, A), values=r(B, 1), returns=r(B, 1), advantages=r(B, 1),
+             old_actions_log_prob=r(B, 1) * 0.3 - 1.1 * A, old_mu=r(B, A) * 0.5, old_sigma=torch.rand(B, A, generator=gen) + 0.5)
+    return {k: v.to(device) for k, v in b.items()}
+
+
+def _batch_ptrs(b):
+    from legged_tracking_b200 import _abi
+    bp = _abi.lt_ppo_batch_ptrs()
+    for k, v in b.items():
+        setattr(bp, k, v.data_ptr())
+    return bp
+
+
+def _oracle_grads(ac, b, idx, args):
+    from oracle import ppo_port
+    p64 = _params64(ac)
+    act = ppo_port.ACTIVATIONS[ac.activation]
+    s = {k: v.cpu().double()[idx.cpu()] for k, v in b.items()}
+    loss, surr, vl, kl = ppo_port.minibatch_loss(p64, act, s["obs_history"], s["privileged_obs"], s["actions"], s["values"], s["advantages"],
+                                                 s["returns"], s["old_actions_log_prob"], s["old_mu"], s["old_sigma"], args)
+    loss.backward()
+    flat = torch.cat([p64[k].grad.reshape(-1) for k in ac.state_dict()])
+    return flat, float(surr), float(vl), float(kl)
+
+
+def _grad_close(ac, got, want, tol, what):
+    """per tensor: error relative to the largest entry of that tensor's gradient"""
+    got, want = got.detach().cpu().double(), want.detach().cpu().double()
+    for key, _, lo, hi in ac.layout:
+        scale = float(want[lo:hi].abs().max())
+        err = float((got[lo:hi] - want[lo:hi]).abs().max())
+        assert err <= tol * scale + 1e-12, f"{what} {key}: max err {err:.3e} vs largest entry {scale:.3e}"
+
+
+@pytest.mark.parametrize("activation,B,count", [("elu", 700, 517), ("tanh", 300, 300), ("elu", 130, 1), ("relu", 400, 256)])
+def test_minibatch_grad_matches_autograd(activation, B, count):
+    """lt_ppo_minibatch_grad: gather by index, forward, surrogate / clipped value / entropy loss, KL, full backward (tcgen05
+    GEMMs for dX and dW, bias gradient through the constant-one row) against float64 autograd of the oracle's loss."""
+    from legged_tracking_b200 import _abi, ppo
+    from oracle import ppo_port
+    lib = _abi.load()
+    saved = ppo.AC_Args.activation
+    ppo.AC_Args.activation = activation
+    try:
+        torch.manual_seed(11)
+        ac = ppo.ActorCritic(30, 5, 90, 12).to(_dev())
+    finally:
+        ppo.AC_Args.activation = saved
+    b = _random_batch(ac, B, 5, _dev())
+    idx = torch.randperm(B, generator=torch.Generator().manual_seed(2))[:count].to(_dev())
+    ac.grads = torch.full((ac.num_params,), float("nan"), device=_dev())
+    ac._ready(count, training=True)
+    stats = torch.zeros(16, device=_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+    _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(idx), count, C.byref(hp), 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    args = dict(ppo_port.PPO_DEFAULTS)
+    want, surr, vl, kl = _oracle_grads(ac, b, idx, args)
+    assert torch.isfinite(ac.grads).all()
+    _grad_close(ac, ac.grads, want, 1e-4, f"{activation} B={count}")
+    st = stats.cpu().double()
+    assert st[3] == count
+    np.testing.assert_allclose([st[0] / count, st[1] / count, st[2] / count], [surr, vl, kl], rtol=2e-5, atol=1e-6)
+    # adaptation regression step on the same rows (PPO:150-176)
+    num_train = count // 5 * 4
+    ac.grads.zero_()
+    _abi.check_policy(lib.lt_adaptation_grad(ac._h, C.byref(bp), _p(idx), count, num_train, 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    p64 = _params64(ac)
+    hist, priv = b["obs_history"].cpu().double()[idx.cpu()], b["privileged_obs"].cpu().double()[idx.cpu()]
+    pred = ppo_port.mlp(p64, "adaptation_module", hist, ppo_port.ACTIVATIONS[activation])
+    lo, hi = ac.body_slices["adaptation_module"]
+    if num_train > 0:
+        loss = torch.nn.functional.mse_loss(pred[:num_train], priv[:num_train])
+        loss.backward()
+        want_ad = torch.cat([p64[k].grad.reshape(-1) for k in ac.state_dict() if k.startswith("adaptation_module.")])
+        got = ac.grads[lo:hi].cpu().double()
+        for key, _, a, e in ac.layout:
+            if key.startswith("adaptation_module."):
+                scale = float(want_ad[a - lo:e - lo].abs().max())
+                assert float((got[a - lo:e - lo] - want_ad[a - lo:e - lo]).abs().max()) <= 1e-4 * scale + 1e-12, key
+        st = stats.cpu().double()
+        np.testing.assert_allclose(st[4] / st[5], float(loss), rtol=2e-5)
+        if count > num_train:
+            np.testing.assert_allclose(st[6] / st[7], float(torch.nn.functional.mse_loss(pred[num_train:], priv[num_train:])), rtol=2e-5)
+    assert float(ac.grads[hi:].abs().sum()) == 0.0 and float(ac.grads[:lo].abs().sum()) == 0.0      # rest of the bucket untouched
+
+
+def test_sharded_gradients_sum_to_the_full_minibatch_gradient():
+    """Env sharding: two ranks each run half of a minibatch with grad_world = 2; the SUM of their [stats | grads]
+    buffers -- what the all-reduce of dist.GradExchange produces -- equals the single-process result."""
+    from legged_tracking_b200 import _abi, ppo
+    lib = _abi.load()
+    torch.manual_seed(4)
+    ac = ppo.ActorCritic(30, 5, 90, 12).to(_dev())
+    B = 512
+    b = _random_batch(ac, B, 9, _dev())
+    idx = torch.randperm(B, generator=torch.Generator().manual_seed(3)).to(_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+
+    def run(ix, world):
+        ac.grads = torch.zeros(ac.num_params, device=_dev())
+        ac._bind()
+        ac._ready(B, training=True)
+        stats = torch.zeros(16, device=_dev())
+        _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(ix), ix.numel(), C.byref(hp), world, _p(stats), None), ac._h)
+        torch.cuda.synchronize()
+        return ac.grads.clone().double(), stats.clone().double()
+    full_g, full_s = run(idx, 1)
+    g0, s0 = run(idx[0::2].contiguous(), 2)
+    g1, s1 = run(idx[1::2].contiguous(), 2)
+    _grad_close(ac, g0 + g1, full_g, 2e-5, "sharded")
+    np.testing.assert_allclose((s0 + s1)[:4].cpu().numpy(), full_s[:4].cpu().numpy(), rtol=1e-5)
+
+
+def test_minibatch_apply_is_clip_plus_adam_with_the_kl_schedule():
+    """lt_ppo_minibatch_apply against nn.utils.clip_grad_norm_ + torch.optim.Adam on the CPU, three steps, and the three
+    branches of the adaptive-KL learning-rate rule (PPO:111-125)."""
+    from legged_tracking_b200 import _abi, ppo
+    lib = _abi.load()
+    torch.manual_seed(8)
+    ac = ppo.ActorCritic(12, 2, 24, 3).to(_dev())
+    n = ac.num_params
+    ac.grads = torch.zeros(n, device=_dev())
+    ac._ready(8, training=True)
+    ref = torch.nn.Parameter(ac.flat.detach().cpu().clone())
+    opt = torch.optim.Adam([ref], lr=1e-3)
+    m, v = torch.zeros(n, device=_dev()), torch.zeros(n, device=_dev())
+    lr = torch.tensor([1e-3], device=_dev())
+    norm = torch.zeros(1, device=_dev())
+    hp = ppo.PPO.hparams()
+    gen = torch.Generator().manual_seed(0)
+    want_lr = 1e-3
+    for step, (scale, kl) in enumerate([(1e-3, 0.001), (5.0, 0.05), (0.2, 0.01)], start=1):
+        g = torch.randn(n, generator=gen) * scale
+        ac.grads.copy_(g.to(_dev()))
+        stats = torch.tensor([0, 0, kl * 10, 10] + [0] * 12, dtype=torch.float32, device=_dev())
+        _abi.check_policy(lib.lt_ppo_minibatch_apply(ac._h, C.byref(hp), _p(stats), _p(lr), _p(m), _p(v), step, _p(norm), None), ac._h)
+        torch.cuda.synchronize()
+        want_lr = max(1e-5, want_lr / 1.5) if kl > 0.02 else (min(1e-2, want_lr * 1.5) if kl < 0.005 else want_lr)
+        for grp in opt.param_groups:
+            grp["lr"] = want_lr
+        ref.grad = g.clone()
+        tn = torch.nn.utils.clip_grad_norm_([ref], 1.0)
+        opt.step()
+        np.testing.assert_allclose(float(lr), want_lr, rtol=1e-6)
+        np.testing.assert_allclose(float(norm), float(tn), rtol=1e-5)
+        np.testing.assert_allclose(ac.flat.cpu().numpy(), ref.detach().numpy(), rtol=1e-5, atol=1e-7)
+
+
+def test_policy_at_baseline_size_matches_fp32_torch():
+    """BASELINE.json cfg 5 shapes: 65,536 rows through act (obs_history 261, priv 2, the default 512-256-128 / 256-128 bodies)
+    and one 393,216-row minibatch gradient, against torch fp32 (TF32 off) on the same GPU."""
+    from legged_tracking_b200 import _abi, ppo
+    from oracle import ppo_port
+    lib = _abi.load()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(21)
+    ac = ppo.ActorCritic(261, 2, 261, 12).to(_dev())
+    rows, B = 65536, 65536 * 24 // 4
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    hist = torch.randn(rows, 261, device="cuda", generator=gen).clamp_(-3, 3)
+    priv = torch.rand(rows, 2, device="cuda", generator=gen) * 2 - 1
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in ac.state_dict().items()}
+    act = ppo_port.ACTIVATIONS["elu"]
+    with torch.no_grad():
+        mean, _, value = ppo_port.policy_forward(sd, act, hist, priv)
+    got_mean, got_value = ac.act_student(hist), ac.evaluate(hist, priv)
+    _close(got_mean, mean, 1e-5, 1e-5 * float(mean.abs().max()), "mean @65536")
+    _close(got_value, value, 1e-5, 1e-5 * float(value.abs().max()), "value @65536")
+    # one full-size minibatch: rows drawn (with the permutation) out of a 6 x 65,536 slice of a rollout
+    b = _random_batch(ac, B, 1, "cpu")
+    b = {k: v.to(_dev()) for k, v in b.items()}
+    idx = torch.randperm(B, device="cuda", generator=gen)
+    ac.grads = torch.zeros(ac.num_params, device=_dev())
+    ac._ready(B, training=True)
+    stats = torch.zeros(16, device=_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+    _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(idx), B, C.byref(hp), 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    s = {k: v[idx] for k, v in b.items()}
+    loss, surr, vl, kl = ppo_port.minibatch_loss(sd, act, s["obs_history"], s["privileged_obs"], s["actions"], s["values"], s["advantages"],
+                                                 s["returns"], s["old_actions_log_prob"], s["old_mu"], s["old_sigma"], dict(ppo_port.PPO_DEFAULTS))
+    loss.backward()
+    want = torch.cat([sd[k].grad.reshape(-1) for k in ac.state_dict()])
+    _grad_close(ac, ac.grads, want, 2e-4, "393,216-row minibatch")
+    st = stats.cpu().double()
+    np.testing.assert_allclose([st[0] / B, st[1] / B, st[2] / B], [float(surr), float(vl), float(kl)], rtol=1e-4)

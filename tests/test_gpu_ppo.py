@@ -2,7 +2,7 @@
 lt_normalize_advantages and the PPO update, against the vectors recorded from the unmodified reference
 (tests/golden/ppo_*.npz) and against oracle/ppo_port.py on other seeds and sizes.
 Tolerances: copies and masks bit-exact; fp32 arithmetic 1e-5 relative (+2e-6 absolute); quantities that went through
-20 Adam steps of cuBLAS-vs-MKL GEMMs 1e-3."""
+20 Adam steps of tcgen05 split-fp16 vs MKL fp32 GEMMs 1e-3."""
 import numpy as np
 import pytest
 import torch
@@ -23,7 +23,8 @@ def replay_rollout(alg, g):
     alg.init_storage(N, T, [no], [npv], [no * H], [na])
     tn = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(d)
     for t in range(T):
-        alg.act(tn(g["in/obs"][t]), tn(g["in/priv"][t]), tn(g["in/hist"][t]), actions=tn(g["in/actions"][t]))
+        a = alg.act(tn(g["in/obs"][t]), tn(g["in/priv"][t]), tn(g["in/hist"][t]), actions=tn(g["in/actions"][t]))
+        assert a.data_ptr() == alg.storage.actions[t].data_ptr()          # written in place, row t of the rollout buffer
         infos = {"time_outs": tn(g["in/time_outs"][t])} if bool(g["meta/time_outs"]) else {}
         alg.process_env_step(tn(g["in/rewards"][t]), tn(g["in/dones"][t]), infos)
     alg.compute_returns(tn(g["in/hist"][T]), tn(g["in/priv"][T]))
@@ -32,7 +33,6 @@ def replay_rollout(alg, g):
 @pytest.mark.parametrize("name", PPO_CASES)
 def test_rollout_store_and_gae_match_reference(name):
     from legged_tracking_b200 import ppo
-    torch.backends.cuda.matmul.allow_tf32 = False
     g = load_case(name)
     with golden_args(g):
         alg = ppo.PPO(actor_critic_from_golden(g, dev()), device=dev())
@@ -48,7 +48,6 @@ def test_rollout_store_and_gae_match_reference(name):
 @pytest.mark.parametrize("name", PPO_CASES)
 def test_ppo_update_matches_reference(name):
     from legged_tracking_b200 import ppo
-    torch.backends.cuda.matmul.allow_tf32 = False
     g = load_case(name)
     with golden_args(g):
         ac = actor_critic_from_golden(g, dev())
@@ -56,7 +55,8 @@ def test_ppo_update_matches_reference(name):
         replay_rollout(alg, g)
         losses = alg.update(indices=torch.from_numpy(g["update/perm"]).to(dev()))
         tr = alg.last_update_trace
-        np.testing.assert_allclose(tr["lrs"], g["update/lrs"], rtol=1e-12)          # same KL-schedule branch every minibatch
+        np.testing.assert_allclose(tr["lrs"], g["update/lrs"], rtol=1e-6)           # same KL-schedule branch every minibatch (the
+        #                                                                             learning rate lives on the device as fp32)
         np.testing.assert_allclose(tr["grad_norms"], g["update/grad_norms"], rtol=1e-3)
         np.testing.assert_allclose(losses, g["update/losses"], rtol=1e-3, atol=1e-6)
         for k, v in ac.state_dict().items():

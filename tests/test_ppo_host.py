@@ -1,66 +1,83 @@
-"""Host-side logic of the PPO rows against the reference's recorded vectors (CPU, no kernels): ActorCritic layout and
-forward, PPO.update's flat-bucket Adam / clip / KL schedule / adaptation step."""
+"""Host side of the PPO rows without a GPU: the flat parameter layout under the reference's state_dict keys (checked against
+the checkpoint recorded from the unmodified reference), initialisation order, and that nothing computes on the CPU."""
 import numpy as np
 import pytest
 import torch
 
 from legged_tracking_b200 import ppo
-from tests.helpers_ppo import PPO_CASES, HostStorage, actor_critic_from_golden, golden_args, load_case
+from legged_tracking_b200._abi import LtError
+from tests.helpers_ppo import PPO_CASES, actor_critic_from_golden, golden_args, load_case
 
 
 @pytest.mark.parametrize("name", PPO_CASES)
-def test_actor_critic_state_dict_and_forward(name):
+def test_state_dict_keys_shapes_and_flat_layout(name):
     g = load_case(name)
     with golden_args(g):
         ac = actor_critic_from_golden(g)          # strict load: same keys and shapes as the reference's checkpoint
-        T = int(g["meta/sizes"][1])
-        with torch.no_grad():
-            for t in (0, T - 1):
-                hist, priv = torch.from_numpy(g["in/hist"][t]), torch.from_numpy(g["in/priv"][t])
-                ac.act(hist)
-                np.testing.assert_allclose(ac.action_mean.numpy(), g["storage/mu"][t], rtol=1e-5, atol=2e-6)
-                np.testing.assert_allclose(ac.action_std.numpy(), g["storage/sigma"][t], rtol=1e-6)
-                lp = ac.get_actions_log_prob(torch.from_numpy(g["in/actions"][t]))
-                np.testing.assert_allclose(lp.numpy(), g["storage/actions_log_prob"][t, :, 0], rtol=1e-5, atol=2e-6)
-                v = ac.evaluate(hist, priv)
-                np.testing.assert_allclose(v.numpy(), g["storage/values"][t], rtol=1e-5, atol=2e-6)
+        ref_keys = [k[5:] for k in g if k.startswith("init/")]
+        sd = ac.state_dict()
+        assert sorted(sd) == sorted(ref_keys)
+        o = 0
+        for k, v in sd.items():                   # views of ONE vector, in lt_policy.h's order, no gaps
+            assert np.array_equal(v.numpy(), g["init/" + k]), k
+            assert v.data_ptr() == ac.flat.data_ptr() + 4 * o, k
+            o += v.numel()
+        assert o == ac.num_params == ac.flat.numel()
+        assert list(sd)[0] == "std"
+        assert [k.split(".")[0] for k in list(sd)[1:]] == sorted((k.split(".")[0] for k in list(sd)[1:]),
+                                                                 key=["adaptation_module", "actor_body", "critic_body"].index)
+        lo, hi = ac.body_slices["adaptation_module"]
+        assert lo == ac.num_actions and hi == ac.body_slices["actor_body"][0]
 
 
-@pytest.mark.parametrize("name", PPO_CASES)
-def test_update_matches_reference(name):
-    g = load_case(name)
-    with golden_args(g):
-        ac = actor_critic_from_golden(g)
-        alg = ppo.PPO(ac, device="cpu")
-        alg.storage = HostStorage.from_golden(g)
-        losses = alg.update(indices=torch.from_numpy(g["update/perm"]))
-        tr = alg.last_update_trace
-        np.testing.assert_allclose(tr["lrs"], g["update/lrs"], rtol=1e-12)
-        np.testing.assert_allclose(tr["grad_norms"], g["update/grad_norms"], rtol=2e-4)
-        np.testing.assert_allclose(losses, g["update/losses"], rtol=1e-4, atol=1e-7)
-        assert alg.learning_rate == pytest.approx(float(g["update/final_lr"]), rel=1e-12)
-        assert alg.storage.cleared
-        for k, v in ac.state_dict().items():
-            np.testing.assert_allclose(v.numpy(), g["final/" + k], rtol=1e-4, atol=2e-5, err_msg=k)
+def test_default_initialisation_follows_the_reference_draw_order():
+    """nn.Linear default init, layers drawn adaptation -> actor -> critic (actor_critic.py:43-82): same seed, same weights."""
+    torch.manual_seed(7)
+    ac = ppo.ActorCritic(10, 3, 20, 4)
+    torch.manual_seed(7)
+    dims = {"adaptation_module": [20] + ppo.AC_Args.adaptation_module_branch_hidden_dims + [3],
+            "actor_body": [23] + ppo.AC_Args.actor_hidden_dims + [4], "critic_body": [23] + ppo.AC_Args.critic_hidden_dims + [1]}
+    sd = ac.state_dict()
+    for name in ("adaptation_module", "actor_body", "critic_body"):
+        for l, (a, b) in enumerate(zip(dims[name][:-1], dims[name][1:])):
+            lin = torch.nn.Linear(a, b)
+            assert torch.equal(sd[f"{name}.{2 * l}.weight"], lin.weight.detach())
+            assert torch.equal(sd[f"{name}.{2 * l}.bias"], lin.bias.detach())
+    assert torch.equal(sd["std"], torch.full((4,), float(ppo.AC_Args.init_noise_std)))
 
 
-def test_flat_params_alias_and_checkpoint_roundtrip():
-    g = load_case(PPO_CASES[0])
-    with golden_args(g):
-        ac = actor_critic_from_golden(g)
-        before = {k: v.clone() for k, v in ac.state_dict().items()}
-        fp = ppo.FlatParams(ac)
-        for k, v in ac.state_dict().items():
-            assert torch.equal(v, before[k])
-        lo, hi = fp.slice_of(ac.adaptation_module)
-        assert hi - lo == sum(p.numel() for p in ac.adaptation_module.parameters())
-        fp.flat.data.zero_()                          # the flat buffer IS the parameters
-        assert all(float(p.detach().abs().sum()) == 0.0 for p in ac.parameters())
-        ac.load_state_dict(before)                    # loading a checkpoint writes through the views
-        assert float(fp.flat.data.abs().sum()) > 0.0
+def test_load_state_dict_is_strict_and_writes_through():
+    ac = ppo.ActorCritic(10, 3, 20, 4)
+    sd = {k: torch.zeros_like(v) for k, v in ac.state_dict().items()}
+    ac.load_state_dict(sd)
+    assert float(ac.flat.abs().sum()) == 0.0
+    bad = dict(sd)
+    bad.pop("std")
+    with pytest.raises(RuntimeError):
+        ac.load_state_dict(bad)
+    bad = dict(sd)
+    bad["actor_body.0.weight"] = torch.zeros(3, 3)
+    with pytest.raises(RuntimeError):
+        ac.load_state_dict(bad)
 
 
-def test_storage_has_no_cpu_path():
-    from legged_tracking_b200._abi import LtError
+def test_exported_module_matches_reference_layout():
+    """Runner.save's TorchScript export: Linear / ELU pairs with the reference's module indices."""
+    ac = ppo.ActorCritic(10, 3, 20, 4)
+    seq = ac.export_module("actor_body")
+    assert [type(m).__name__ for m in seq] == ["Linear", "ELU", "Linear", "ELU", "Linear", "ELU", "Linear"]
+    for k, v in seq.state_dict().items():
+        assert torch.equal(v, ac.state_dict()["actor_body." + k])
+    torch.jit.script(seq)
+
+
+def test_no_cpu_path():
+    ac = ppo.ActorCritic(10, 3, 20, 4)
+    with pytest.raises(LtError):
+        ac.act(torch.zeros(2, 20))
+    with pytest.raises(LtError):
+        ac.evaluate(torch.zeros(2, 20), torch.zeros(2, 3))
+    with pytest.raises(LtError):
+        ppo.PPO(ac, device="cpu")
     with pytest.raises(LtError):
         ppo.RolloutStorage(4, 2, [3], [1], [6], [2], device="cpu")
