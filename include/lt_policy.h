@@ -115,7 +115,10 @@ int lt_ppo_minibatch_apply(lt_policy* p, const lt_ppo_hparams* hp, const float* 
 
 /* Adaptation-module regression step (PPO:150-176), first half: pred = adaptation_module(obs_history[indices]);
  * loss = mse(pred[:num_train], privileged_obs[:num_train]) back-propagated into the adaptation slice of grads (the rest of
- * grads is left untouched); test loss on rows num_train..count.  Sums into stats[4..8). */
+ * grads is left untouched); test loss on rows num_train..count.  Sums into stats[4..8).
+ * When batch->obs_history, indices (non-NULL) and count are the ones of the immediately preceding lt_ppo_minibatch_grad on this
+ * handle -- the reference's case, PPO:150-176 runs on the minibatch just used -- the rows gathered by that call are reused:
+ * do not rewrite the index array or the rollout buffers between the two calls. */
 int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64_t* indices, int32_t count, int32_t num_train,
                        int32_t grad_world, float* stats, void* stream);
 /* Second half: Adam step (no clipping) on the adaptation slice with its own state (same flat indexing as params), lr host value. */
@@ -131,6 +134,10 @@ int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi);
  * the device; operands are split into fp16 planes internally with the scales the policy uses. */
 int lt_linear_f32(const float* a, const float* b, const float* bias, float* out, int32_t M, int32_t N, int32_t K, int32_t splits,
                   void* stream);
+
+/* Same kernel with both operands MN-major, as the weight-gradient products use it: out[M, N] = a[K, M]^T * b[K, N] (the
+ * contraction runs over the ROWS of the two stored matrices), summed over `splits` split-K partials in a fixed order. */
+int lt_linear_tn_f32(const float* a, const float* b, float* out, int32_t M, int32_t N, int32_t K, int32_t splits, void* stream);
 
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contraction as lt_linear_f32 with splits = 1 --

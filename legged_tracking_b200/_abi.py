@@ -105,7 +105,7 @@ EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_crea
            # include/lt_policy.h
            "lt_policy_config_bytes", "lt_policy_create", "lt_policy_destroy", "lt_policy_last_error", "lt_policy_num_params",
            "lt_policy_bind_params", "lt_policy_refresh", "lt_policy_forward", "lt_policy_act", "lt_ppo_minibatch_grad",
-           "lt_ppo_minibatch_apply", "lt_adaptation_grad", "lt_adaptation_apply", "lt_policy_adaptation_slice", "lt_policy_grad_scales", "lt_linear_f32",
+           "lt_ppo_minibatch_apply", "lt_adaptation_grad", "lt_adaptation_apply", "lt_policy_adaptation_slice", "lt_policy_grad_scales", "lt_linear_f32", "lt_linear_tn_f32",
            "lt_linear_f32_static"]
 
 
@@ -179,6 +179,7 @@ def load(path=LIB_PATH):
     lib.lt_policy_grad_scales.argtypes = [vp]
     lib.lt_policy_grad_scales.restype = vp
     lib.lt_linear_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    lib.lt_linear_tn_f32.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
     lib.lt_linear_f32_static.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp]
     if lib.lt_policy_config_bytes() != C.sizeof(lt_policy_config):
         raise LtError("sizeof(lt_policy_config) differs between the library and the binding: rebuild")

@@ -2,20 +2,24 @@
 // stacks; forward, input-gradient and weight-gradient products of ppo.py:104-148) on the 5th-generation tensor cores.
 //
 //   D[M, N] = A[M, K] * B[N, K]^T        A, B: K-major, each stored as TWO fp16 planes (hi, lo) with a * s = hi + lo
+//   D[M, N] = A[K, M]^T * B[K, N]        Params::mn_major: both operands MN-major (the contraction index is the ROW of the stored
+//                                        matrices) -- the weight-gradient product dW^T = dZ^T * [X | 1] reads the row-major
+//                                        activation / gradient planes as they are, so nothing is ever stored transposed
 //
 // fp32-equivalent arithmetic on fp16 operands: every product is three tcgen05.mma (hi*hi + hi*lo + lo*hi, the lo*lo term is
 // below 2^-22 of the product) accumulated in fp32 in tensor memory; the power-of-two operand scales s are undone exactly in
 // the epilogue.  The reference runs these GEMMs in fp32 (TF32 off), so single-pass fp16/bf16/tf32 would be a precision drop.
 //
-// Structure (one persistent CTA per SM, 192 threads):
+// Structure (one persistent CTA per SM, 320 threads):
 //   warp 0      TMA producer: cp.async.bulk.tensor.3d loads a [2 planes, 128 rows, 64 k] box of A and a [2, bn, 64] box of B
 //               per k-block into a 128B-swizzled STAGES-deep shared-memory ring (mbarrier complete_tx)
 //   warp 1      MMA issuer: one elected lane, 4 k16 steps x 3 products per k-block, tcgen05.commit frees the ring slot;
 //               accumulators double-buffered in TMEM (2 x BN_MAX columns) so tile i+1's main loop overlaps tile i's epilogue
-//   warps 2..5  epilogue: thread <-> accumulator row (TMEM lane); tcgen05.ld 32 columns at a time, then one of
+//   warps 2..9  epilogue: thread <-> accumulator row (TMEM lane), two warps per lane quarter on alternating 32-column chunks;
+//               tcgen05.ld 32 columns at a time, then one of
 //               EPI_F32      out = acc * scale + bias                                    -> fp32 [M, ld]
-//               EPI_ELU      y = act(acc * scale + bias), act = ELU unless Params::act says else -> fp16 planes, row-major (+ transposed)
-//               EPI_BWD      dz = acc * scale * act'(y_prev), e.g. ELU'(y) = y > 0 ? 1 : y+1   -> fp16 planes, row-major (+ transposed)
+//               EPI_ELU      y = act(acc * scale + bias), act = ELU unless Params::act says else -> fp16 planes, row-major
+//               EPI_BWD      dz = acc * scale * act'(y_prev), e.g. ELU'(y) = y > 0 ? 1 : y+1   -> fp16 planes, row-major
 //               EPI_PARTIAL  acc * scale -> fp32 split-K partial [split][M, ld]
 // Tiles are (split, m-block, n-block) triples, n fastest, so that the CTAs running at the same time share A rows in L2.
 // Rows / columns / k beyond the tensor bounds are zero-filled by TMA and masked in the epilogue: no padding requirements
@@ -30,7 +34,8 @@ namespace ltg {
 
 constexpr int BM = 128;          // rows per tile = TMEM lanes
 constexpr int BK = 64;           // k per ring slot = one 128-byte swizzle row of fp16
-constexpr int THREADS = 192;
+constexpr int EPI_WARPS = 8;         // two per TMEM lane quarter, each taking every other 32-column chunk
+constexpr int THREADS = 64 + 32 * EPI_WARPS;
 constexpr float OPERAND_MAX = 60000.0f;      // fp16 planes saturate here instead of overflowing to inf
 
 enum { EPI_F32 = 0, EPI_ELU = 1, EPI_BWD = 2, EPI_PARTIAL = 3 };        // EPI_ELU: "activation" epilogue (ELU is the reference default)
@@ -43,6 +48,7 @@ struct Params {
     int32_t bn;                          // N tile = UMMA N (multiple of 16, <= BN_MAX)
     int32_t splits, kb_per_split;        // split-K: k-blocks [s * kb_per_split, (s+1) * kb_per_split) go to partial s
     int32_t mode;
+    int32_t mn_major;                    // 1: tma_a / tma_b are {col, row, plane} maps with box {64, 64, 2}; contraction over rows
     int32_t act;                         // ACT_*: activation of EPI_ELU, its derivative (from the stored OUTPUT y) in EPI_BWD
     float out_scale;                     // 1 / (s_a * s_b)
     const float* bias;                   // [N] or NULL
@@ -50,8 +56,6 @@ struct Params {
     int64_t ld_f32, split_stride;
     __half* out_h;                       // row-major planes [2][rows][ld_h]
     int64_t ld_h, plane_h;
-    __half* out_t;                       // transposed planes [2][cols][ld_t] or NULL
-    int64_t ld_t, plane_t;
     float split_scale;                   // scale of the fp16 planes written by EPI_ELU / EPI_BWD
     // gradient operands carry a per-tensor power-of-two scale that lives on the DEVICE (chosen from the tensor's measured
     // largest entry, see lt_policy.cu "gradient scales"), so that no host synchronisation is needed to pick it:
@@ -105,6 +109,12 @@ __device__ __forceinline__ void umma_ss(uint32_t d_tmem, uint64_t a_desc, uint64
 __device__ __forceinline__ uint64_t sw128_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
+// MN-major, SWIZZLE_128B: atoms of 64 mn-elements (128 B) x 8 k-rows; 8-row k groups 1024 B apart (stride byte offset), 64-wide mn
+// chunks `chunk_bytes` apart (leading byte offset)
+__device__ __forceinline__ uint64_t sw128_mn_desc(uint32_t smem_addr, uint32_t chunk_bytes) {
+    return (uint64_t)((smem_addr & 0x3ffffu) >> 4) | ((uint64_t)(chunk_bytes >> 4) << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -140,7 +150,12 @@ __device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uin
 constexpr float SELU_ALPHA = 1.6732632423543772848170429916717f, SELU_SCALE = 1.0507009873554804934193349852946f;
 template <int ACT>
 __device__ __forceinline__ float act_fwd(float z) {
-    if (ACT == ACT_ELU) return z > 0.0f ? z : expm1f(z);                                   // nn.ELU(alpha = 1)
+    if (ACT == ACT_ELU) {                                                                  // nn.ELU(alpha = 1)
+        // expm1 for z <= 0 without the slow path: 4th-order series below 1/32 (truncation 3e-10), ex2.approx - 1 beyond (absolute
+        // error 1e-7 on a value of magnitude >= 0.03)
+        const float series = z * (1.0f + z * (0.5f + z * (0.16666667f + z * 0.041666668f)));
+        return z > 0.0f ? z : (z > -0.03125f ? series : __expf(z) - 1.0f);
+    }
     if (ACT == ACT_SELU) return SELU_SCALE * (z > 0.0f ? z : SELU_ALPHA * expm1f(z));
     if (ACT == ACT_RELU) return fmaxf(z, 0.0f);
     if (ACT == ACT_LRELU) return z > 0.0f ? z : 0.01f * z;                                  // nn.LeakyReLU default slope
@@ -186,6 +201,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
     auto empty = [&](int s) { return bars + 8u * (STAGES + s); };
     auto tfull = [&](int s) { return bars + 8u * (2 * STAGES + s); };
     auto tempty = [&](int s) { return bars + 8u * (2 * STAGES + 2 + s); };
+    constexpr uint32_t CHUNK = 2u * 64u * BK * 2u;                   // MN-major: one {64 mn, 64 k, 2 planes} box = 16 KB
     const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -196,7 +212,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull(s), 1);
-            mbar_init(tempty(s), 4);
+            mbar_init(tempty(s), EPI_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -219,7 +235,8 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&p.tma_a)) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&p.tma_b)) : "memory");
-            const uint32_t tx = S::A_BYTES + 2u * (uint32_t)p.bn * BK * 2u;
+            const int b_chunks = (p.bn + 63) / 64;
+            const uint32_t tx = p.mn_major ? (uint32_t)(BM / 64 + b_chunks) * CHUNK : S::A_BYTES + 2u * (uint32_t)p.bn * BK * 2u;
             int stage = 0;
             uint32_t phase = 0;
             for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
@@ -229,8 +246,15 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                     mbar_wait(empty(stage), phase ^ 1u);
                     mbar_expect_tx(full(stage), tx);
                     const uint32_t sa = base + (uint32_t)stage * S::STAGE;
-                    tma_load_3d(sa, &p.tma_a, full(stage), kb * BK, m_blk * BM, 0);
-                    tma_load_3d(sa + S::A_BYTES, &p.tma_b, full(stage), kb * BK, n_blk * p.bn, 0);
+                    if (p.mn_major) {
+#pragma unroll
+                        for (int c = 0; c < BM / 64; ++c) tma_load_3d(sa + c * CHUNK, &p.tma_a, full(stage), m_blk * BM + c * 64, kb * BK, 0);
+                        for (int c = 0; c < b_chunks; ++c)
+                            tma_load_3d(sa + S::A_BYTES + c * CHUNK, &p.tma_b, full(stage), n_blk * p.bn + c * 64, kb * BK, 0);
+                    } else {
+                        tma_load_3d(sa, &p.tma_a, full(stage), kb * BK, m_blk * BM, 0);
+                        tma_load_3d(sa + S::A_BYTES, &p.tma_b, full(stage), kb * BK, n_blk * p.bn, 0);
+                    }
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1u;
@@ -241,7 +265,8 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
     } else if (warp == 1) {
         // ------------------------------------------------------------------------------------------ MMA issuer
         // instruction descriptor: D = F32, A = B = F16, both K-major, N = bn, M = 128
-        const uint32_t idesc = (1u << 4) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        // (bits 15 / 16: A / B are MN-major)
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24) | (p.mn_major ? (3u << 15) : 0u);
         const uint32_t b_plane = (uint32_t)p.bn * BK * 2u;
         int stage = 0, as = 0;
         uint32_t phase = 0, aphase = 0;
@@ -254,7 +279,21 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
             for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(full(stage), phase);
                 fence_after();
-                if (lane == 0) {
+                if (lane == 0 && p.mn_major) {
+                    // smem per operand: [64-wide mn chunk][plane][64 k rows][128 B]; one MMA reads 16 k rows = 2048 B further on
+                    const uint32_t sa = base + (uint32_t)stage * S::STAGE, sb = sa + S::A_BYTES;
+                    const uint64_t a_hi = sw128_mn_desc(sa, CHUNK), a_lo = sw128_mn_desc(sa + CHUNK / 2, CHUNK);
+                    const uint64_t b_hi = sw128_mn_desc(sb, CHUNK), b_lo = sw128_mn_desc(sb + CHUNK / 2, CHUNK);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t adv = (uint64_t)((k * 16 * 128) >> 4);
+                        umma_ss(d_tmem, a_lo + adv, b_hi + adv, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        umma_ss(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+                        umma_ss(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+                    }
+                    umma_commit(empty(stage));
+                    if (kb == kb1 - 1) umma_commit(tfull(as));
+                } else if (lane == 0) {
                     const uint32_t sa = base + (uint32_t)stage * S::STAGE, sb = sa + S::A_BYTES;
                     const uint64_t a_hi = sw128_desc(sa), a_lo = sw128_desc(sa + BM * BK * 2u);
                     const uint64_t b_hi = sw128_desc(sb), b_lo = sw128_desc(sb + b_plane);
@@ -283,6 +322,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
     } else {
         // ------------------------------------------------------------------------------------------ epilogue
         const int q = warp & 3;                                                   // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;                                         // which of the two warps of that quarter
         int as = 0;
         uint32_t aphase = 0;
         for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
@@ -296,7 +336,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
             const float out_scale = p.a_scale_ptr ? p.out_scale / __ldg(p.a_scale_ptr) : p.out_scale;
             const float split_scale = p.split_scale_ptr ? __ldg(p.split_scale_ptr) : p.split_scale;
             float tile_amax = 0.0f;
-            for (int c = 0; c < p.bn; c += 32) {
+            for (int c = 32 * half; c < p.bn; c += 64) {
                 uint32_t r[32];
                 const int width = min(32, p.bn - c);                              // 32 or 16 (bn is a multiple of 16)
                 if (width == 32) tmem_ld32(taddr + c, r);
@@ -381,18 +421,6 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                                 }
                             }
                         }
-                        if (p.out_t) {
-                            // transposed planes: for a fixed column the warp's 32 rows are consecutive -> coalesced 64-byte stores
-                            uint16_t* th = reinterpret_cast<uint16_t*>(p.out_t) + (int64_t)col0 * p.ld_t + row;
-                            uint16_t* tl = th + p.plane_t;
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                if (j < width && col0 + j < p.N) {
-                                    th[(int64_t)j * p.ld_t] = (uint16_t)(hi[j >> 1] >> ((j & 1) * 16));
-                                    tl[(int64_t)j * p.ld_t] = (uint16_t)(lo[j >> 1] >> ((j & 1) * 16));
-                                }
-                            }
-                        }
                     }
                 }
             }
@@ -437,6 +465,18 @@ inline bool make_operand_map(CUtensorMap* map, const __half* base, int64_t rows,
     const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, 2};
     const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane * 2};
     const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 2};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// MN-major operand: planes [2][rows][ld] fp16 at `base`, logical extent rows (contraction) x cols (mn); box {64 cols, 64 rows, 2}
+inline bool make_operand_map_mn(CUtensorMap* map, const __half* base, int64_t rows, int64_t cols, int64_t ld, int64_t plane) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, 2};
+    const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane * 2};
+    const cuuint32_t box[3] = {64, (cuuint32_t)BK, 2};
     const cuuint32_t estr[3] = {1, 1, 1};
     return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;

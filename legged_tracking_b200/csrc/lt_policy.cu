@@ -5,8 +5,10 @@
 // buffer X0 = [obs_history | latent | privileged_obs] feeds the first layer of all three MLPs; their first-layer weights
 // are stored expanded to that width with zeros in the columns a network does not read (adaptation: obs_history only;
 // actor: obs_history | latent, AC:130; critic: obs_history | privileged_obs, AC:158).  Hidden activations Y_l are written by
-// the GEMM epilogue already split (and, when training, also transposed with a constant-one row appended, which is what the
-// weight-gradient GEMM dW_l^T = [Y_{l-1}^T; 1] * dZ_l consumes: the bias gradient is its last column).
+// the GEMM epilogue already split, row-major, with one extra column right of the last feature that holds the constant one
+// (written once, never overwritten): the weight-gradient GEMM dW_l = dZ_l^T * [Y_{l-1} | 1] reads both row-major buffers as
+// MN-major tensor-core operands (the contraction runs over rows), so its last output column is the bias gradient and nothing
+// is ever stored transposed.
 // Scales are powers of two, undone exactly in the epilogues: activations 2^4, weights 2^6.
 //
 // Gradient scales.  A gradient tensor dZ_l spans many orders of magnitude across layers (the adaptation module sees the actor's
@@ -47,14 +49,14 @@ struct Layer {
     int k_real = 0;                   // in_features of the nn.Linear
     int c1 = 0, s2 = 0, c2 = 0;       // param cols [0,c1) <- gemm cols [0,c1); param cols [c1,c1+c2) <- gemm cols [s2,s2+c2)
     int64_t w_off = 0, b_off = 0;     // offsets in the flat parameter vector
-    Planes W, WT;                     // [2][N][ld(K)] and [2][K][ld(N)]
+    Planes W, WT;                     // [2][N][ld(K)] and (training) [2][K][ld(N)] for the input-gradient GEMM
 };
 
 struct Mlp {
     int n = 0;                                    // number of Linear layers
     Layer L[LT_POLICY_MAX_HIDDEN + 1];
-    Planes Y[LT_POLICY_MAX_HIDDEN], YT[LT_POLICY_MAX_HIDDEN];          // hidden activations, row-major and [N_l + 1][R] transposed
-    Planes dZ[LT_POLICY_MAX_HIDDEN + 1], dZT[LT_POLICY_MAX_HIDDEN + 1];
+    Planes Y[LT_POLICY_MAX_HIDDEN];               // hidden activations [R][N_l + 1]: column N_l is the constant one
+    Planes dZ[LT_POLICY_MAX_HIDDEN + 1];
     float* out = nullptr;                         // [R][N_last] fp32
     int idx = 0;                                  // 0 adaptation, 1 actor, 2 critic: row of the gradient-scale table
 };
@@ -71,7 +73,10 @@ struct lt_policy {
     int64_t R = 0;                                // row capacity (multiple of 128)
     int Din = 0, P = 0, A = 0, K0 = 0;
     Mlp adapt, actor, critic;
-    Planes X0, X0T;                               // [2][R][ld(K0)], [2][K0 + 1][R]
+    Planes X0;                                    // [2][R][ld(K0 + 1)]: column K0 is the constant one
+    const void* packed_src = nullptr;             // what X0 currently holds: (obs_history, indices, count) of the last gather
+    const void* packed_idx = nullptr;
+    int packed_count = 0;
     float* partial = nullptr;                     // split-K workspace
     int64_t partial_floats = 0;
     float* head_partial = nullptr;                // [blocks][STAT_SLOTS]
@@ -164,70 +169,43 @@ __global__ void split_weights_kernel(const float* __restrict__ w, int N, int K, 
     }
 }
 
-// Gather + split the shared first-layer input: X0[r] = [obs_history[src] | 0 (or privileged_obs, teacher mode) | privileged_obs[src]]
-// and, when xt != NULL, its transpose.  Block = 32 rows; 8 warps sweep 32-column chunks through a shared-memory tile so that
-// both the row-major and the transposed planes are written with consecutive lanes on consecutive addresses.
+// Gather + split the shared first-layer input: X0[r] = [obs_history[src] | 0 (or privileged_obs, teacher mode) | privileged_obs[src]].
+// One warp per row: lanes sweep the columns, so both the fp32 reads and the fp16 writes are coalesced.
 __global__ void __launch_bounds__(256) pack_x0_kernel(const float* __restrict__ obs_history, const float* __restrict__ priv,
                                                       const int64_t* __restrict__ indices, int rows, int Din, int P, int teacher,
-                                                      __half* x, int64_t ldx, int64_t planex, __half* xt, int64_t ldt, int64_t planet) {
-    __shared__ float tile[32][33];
-    __shared__ int64_t src_row[32];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int row0 = blockIdx.x * 32;
-    if (threadIdx.x < 32) {
-        const int r = row0 + threadIdx.x;
-        src_row[threadIdx.x] = r < rows ? (indices ? indices[r] : (int64_t)r) : -1;
+                                                      __half* __restrict__ x, int64_t ldx, int64_t planex) {
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int64_t src = indices ? indices[r] : (int64_t)r;
+    const float* oh = obs_history + src * Din;
+    __half* xh = x + (int64_t)r * ldx;
+    __half* xl = xh + planex;
+    for (int c = lane; c < Din; c += 32) {
+        __half hi, lo;
+        split1(__ldg(oh + c) * S_X, hi, lo);
+        xh[c] = hi;
+        xl[c] = lo;
     }
-    __syncthreads();
-    const int K0 = Din + 2 * P;
-    for (int c0 = 0; c0 < K0; c0 += 32) {
-        const int col = c0 + tx;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int lr = ty * 4 + i;
-            const int64_t s = src_row[lr];
-            float v = 0.0f;
-            if (s >= 0 && col < K0) {
-                if (col < Din) v = obs_history[s * Din + col];
-                else if (col < Din + P) v = (teacher && priv) ? priv[s * P + (col - Din)] : 0.0f;
-                else v = priv ? priv[s * P + (col - Din - P)] : 0.0f;
-                v *= S_X;
-                __half hi, lo;
-                split1(v, hi, lo);
-                const int64_t o = (int64_t)(row0 + lr) * ldx + col;
-                x[o] = hi;
-                x[planex + o] = lo;
-            }
-            tile[lr][tx] = v;
-        }
-        __syncthreads();
-        if (xt) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int lc = ty * 4 + i;
-                const int r = row0 + tx;
-                if (c0 + lc < K0 && r < rows) {
-                    __half hi, lo;
-                    split1(tile[tx][lc], hi, lo);
-                    const int64_t o = (int64_t)(c0 + lc) * ldt + r;
-                    xt[o] = hi;
-                    xt[planet + o] = lo;
-                }
-            }
-        }
-        __syncthreads();
+    if (lane < 2 * P) {
+        const int j = lane < P ? lane : lane - P;
+        float v = 0.0f;
+        if (priv && (lane >= P || teacher)) v = priv[src * P + j];
+        __half hi, lo;
+        split1(v * S_X, hi, lo);
+        xh[Din + lane] = hi;
+        xl[Din + lane] = lo;
     }
 }
 
-// constant-one row (value 1 * S_X) of a transposed activation buffer: carries the bias gradient through the dW GEMM
-__global__ void ones_row_kernel(__half* row_hi, int64_t n) {
+// constant-one column (value 1 * S_X, hi plane) of an activation buffer: carries the bias gradient through the dW GEMM
+__global__ void ones_col_kernel(__half* col_hi, int64_t rows, int64_t ld) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) row_hi[i] = __float2half_rn(S_X);
+    if (i < rows) col_hi[i * ld] = __float2half_rn(S_X);
 }
 
-// latent (adaptation module output, fp32) -> its columns of X0 / X0T (AC:129-130: actor input = cat(obs_history, latent))
-__global__ void scatter_latent_kernel(const float* __restrict__ latent, int rows, int P, int Din, __half* x, int64_t ldx, int64_t planex,
-                                      __half* xt, int64_t ldt, int64_t planet) {
+// latent (adaptation module output, fp32) -> its columns of X0 (AC:129-130: actor input = cat(obs_history, latent))
+__global__ void scatter_latent_kernel(const float* __restrict__ latent, int rows, int P, int Din, __half* x, int64_t ldx, int64_t planex) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= rows) return;
     for (int j = 0; j < P; ++j) {
@@ -236,11 +214,6 @@ __global__ void scatter_latent_kernel(const float* __restrict__ latent, int rows
         const int64_t o = (int64_t)r * ldx + Din + j;
         x[o] = hi;
         x[planex + o] = lo;
-        if (xt) {
-            const int64_t t = (int64_t)(Din + j) * ldt + r;
-            xt[t] = hi;
-            xt[planet + t] = lo;
-        }
     }
 }
 
@@ -318,8 +291,8 @@ struct HeadParams {
     float inv_count;            // 1 / (count * grad_world)
     const float *s_mu, *s_v;    // device: scales of the two head gradient tensors
     uint32_t *amax_mu, *amax_v;
-    __half *dmu, *dmut, *dv, *dvt;                    // planes
-    int64_t ld_dmu, plane_dmu, ld_dmut, plane_dmut, ld_dv, plane_dv, ld_dvt, plane_dvt;
+    __half *dmu, *dv;                                 // planes
+    int64_t ld_dmu, plane_dmu, ld_dv, plane_dv;
     float* partial;             // [blocks][STAT_SLOTS]
 };
 
@@ -377,8 +350,6 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
             split1(gmu * s_mu, h, l);
             p.dmu[(int64_t)r * p.ld_dmu + j] = h;
             p.dmu[p.plane_dmu + (int64_t)r * p.ld_dmu + j] = l;
-            p.dmut[(int64_t)j * p.ld_dmut + r] = h;
-            p.dmut[p.plane_dmut + (int64_t)j * p.ld_dmut + r] = l;
             dstd[j] = gs * (d * d - sg * sg) / (sg * sg * sg);
         }
         const float gval = p.hp.value_loss_coef * gv * p.inv_count;
@@ -387,8 +358,6 @@ __global__ void __launch_bounds__(HEAD_THREADS) ppo_head_kernel(const __grid_con
         split1(gval * s_v, h, l);
         p.dv[(int64_t)r * p.ld_dv] = h;
         p.dv[p.plane_dv + (int64_t)r * p.ld_dv] = l;
-        p.dvt[r] = h;
-        p.dvt[p.plane_dvt + r] = l;
     } else {
         for (int j = 0; j < A; ++j) dstd[j] = 0.0f;
     }
@@ -427,8 +396,8 @@ struct AdaptHeadParams {
     float inv_train;            // 1 / (num_train * P * grad_world)
     const float* s_g;           // device: scale of the head gradient tensor
     uint32_t* amax;
-    __half *dz, *dzt;
-    int64_t ld_dz, plane_dz, ld_dzt, plane_dzt;
+    __half* dz;
+    int64_t ld_dz, plane_dz;
     float* partial;
 };
 
@@ -449,8 +418,6 @@ __global__ void __launch_bounds__(HEAD_THREADS) adapt_head_kernel(const __grid_c
             split1(g * s_g, h, l);
             p.dz[(int64_t)r * p.ld_dz + j] = h;
             p.dz[p.plane_dz + (int64_t)r * p.ld_dz + j] = l;
-            p.dzt[(int64_t)j * p.ld_dzt + r] = h;
-            p.dzt[p.plane_dzt + (int64_t)j * p.ld_dzt + r] = l;
         }
     }
     record_amax(p.amax, amax);
@@ -590,6 +557,24 @@ int run_gemm(lt_policy* P, const Operand& A, int M, const Operand& B, int N, int
     return LT_OK;
 }
 
+// D[M, N] = A[K, M]^T * B[K, N]: both operands row-major [K rows][cols] planes read MN-major (contraction over rows)
+int run_gemm_mn(lt_policy* P, const Operand& A, int M, const Operand& B, int N, int K, int splits, ltg::Params& p, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return LT_OK;
+    p.M = M;
+    p.N = N;
+    p.K = K;
+    p.mn_major = 1;
+    p.bn = pick_bn(N);
+    const int kb_total = (K + ltg::BK - 1) / ltg::BK;
+    splits = splits < 1 ? 1 : (splits > kb_total ? kb_total : splits);
+    p.kb_per_split = (kb_total + splits - 1) / splits;
+    p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
+    if (!ltg::make_operand_map_mn(&p.tma_a, A.base, K, M, A.ld, A.plane) || !ltg::make_operand_map_mn(&p.tma_b, B.base, K, N, B.ld, B.plane))
+        return fail(P, LT_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand geometry)");
+    LTP_CUDA(P, ltg::launch(p, P ? P->sm_count : 148, stream));
+    return LT_OK;
+}
+
 int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_out, int k_real0, int c1, int s2, int c2, int64_t& off) {
     m.n = n_hidden + 1;
     int prev = k_real0;
@@ -617,18 +602,12 @@ int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_o
             if (rc) return rc;
         }
         if (l < n_hidden) {
-            rc = alloc_planes(P, m.Y[l], P->R, L.N);
+            rc = alloc_planes(P, m.Y[l], P->R, L.N + 1);
             if (rc) return rc;
-            if (P->c.training) {
-                rc = alloc_planes(P, m.YT[l], L.N + 1, P->R);
-                if (rc) return rc;
-                ones_row_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(m.YT[l].p + (int64_t)L.N * m.YT[l].ld, P->R);
-            }
+            ones_col_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(m.Y[l].p + L.N, P->R, m.Y[l].ld);
         }
         if (P->c.training) {
             rc = alloc_planes(P, m.dZ[l], P->R, up(L.N, 16));
-            if (rc) return rc;
-            rc = alloc_planes(P, m.dZT[l], L.N, P->R);
             if (rc) return rc;
         }
         prev = L.N;
@@ -662,11 +641,6 @@ int forward_mlp(lt_policy* P, Mlp& m, int rows, bool train, cudaStream_t s) {
             p.out_h = m.Y[l].p;
             p.ld_h = m.Y[l].ld;
             p.plane_h = m.Y[l].plane;
-            if (train) {
-                p.out_t = m.YT[l].p;
-                p.ld_t = m.YT[l].ld;
-                p.plane_t = m.YT[l].plane;
-            }
             p.split_scale = S_X;
         } else {
             p.mode = ltg::EPI_F32;
@@ -687,12 +661,12 @@ int dw_splits(lt_policy* P, int N, int Kp1, int count) {
     return s < 1 ? 1 : s;
 }
 
-// backward of one MLP: m.dZ[n-1] / m.dZT[n-1] hold the (scaled) gradient of the last layer's output
+// backward of one MLP: m.dZ[n-1] holds the (scaled) gradient of the last layer's output
 int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
     for (int l = m.n - 1; l >= 0; --l) {
         Layer& L = m.L[l];
-        {   // dW_l and db_l:  [N_l, K_l + 1] = dZ_l^T [N_l, count] * [X_{l-1}^T; 1] [K_l + 1, count]^T
-            const Planes& XT = l == 0 ? P->X0T : m.YT[l - 1];
+        {   // dW_l and db_l:  [N_l, K_l + 1] = dZ_l[count, N_l]^T * [X_{l-1} | 1][count, K_l + 1]
+            const Planes& X = l == 0 ? P->X0 : m.Y[l - 1];
             const int Kp1 = L.K + 1;
             ltg::Params p;
             memset(&p, 0, sizeof p);
@@ -704,7 +678,7 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
             p.split_stride = (int64_t)L.N * p.ld_f32;
             const int splits = dw_splits(P, L.N, Kp1, count);
             if ((int64_t)splits * p.split_stride > P->partial_floats) return fail(P, LT_ERR_INVALID, "split-K workspace too small");
-            int rc = run_gemm(P, op(m.dZT[l], L.N), L.N, op(XT, Kp1), Kp1, count, splits, p, s);
+            int rc = run_gemm_mn(P, op(m.dZ[l], count), L.N, op(X, count), Kp1, count, splits, p, s);
             if (rc) return rc;
             const int64_t n = (int64_t)L.N * Kp1;
             reduce_dw_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->partial, p.splits, p.split_stride, p.ld_f32, L.N, L.K, L.k_real, L.c1,
@@ -722,9 +696,6 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
             p.out_h = m.dZ[l - 1].p;
             p.ld_h = m.dZ[l - 1].ld;
             p.plane_h = m.dZ[l - 1].plane;
-            p.out_t = m.dZT[l - 1].p;
-            p.ld_t = m.dZT[l - 1].ld;
-            p.plane_t = m.dZT[l - 1].plane;
             p.act_h = m.Y[l - 1].p;
             p.ld_act = m.Y[l - 1].ld;
             p.plane_act = m.Y[l - 1].plane;
@@ -738,14 +709,16 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
 }
 
 int pack(lt_policy* P, const float* obs_history, const float* priv, const int64_t* indices, int rows, int teacher, bool train, cudaStream_t s) {
-    pack_x0_kernel<<<(unsigned)((rows + 31) / 32), 256, 0, s>>>(obs_history, priv, indices, rows, P->Din, P->P, teacher, P->X0.p, P->X0.ld, P->X0.plane,
-                                                               train ? P->X0T.p : nullptr, P->X0T.ld, P->X0T.plane);
+    (void)train;
+    if (2 * P->P > 32) return fail(P, LT_ERR_INVALID, "num_privileged_obs > 16 is not supported by the gather kernel");
+    pack_x0_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s>>>(obs_history, priv, indices, rows, P->Din, P->P, teacher, P->X0.p, P->X0.ld, P->X0.plane);
     LTP_CUDA(P, cudaGetLastError());
+    P->packed_src = nullptr;
     return LT_OK;
 }
 int scatter_latent(lt_policy* P, int rows, bool train, cudaStream_t s) {
-    scatter_latent_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(P->adapt.out, rows, P->P, P->Din, P->X0.p, P->X0.ld, P->X0.plane,
-                                                                        train ? P->X0T.p : nullptr, P->X0T.ld, P->X0T.plane);
+    (void)train;
+    scatter_latent_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(P->adapt.out, rows, P->P, P->Din, P->X0.p, P->X0.ld, P->X0.plane);
     LTP_CUDA(P, cudaGetLastError());
     return LT_OK;
 }
@@ -838,11 +811,8 @@ int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
     P->P = cfg->num_privileged_obs;
     P->A = cfg->num_actions;
     P->K0 = P->Din + 2 * P->P;
-    int rc = alloc_planes(P, P->X0, P->R, P->K0);
-    if (!rc && cfg->training) {
-        rc = alloc_planes(P, P->X0T, P->K0 + 1, P->R);
-        if (!rc) ones_row_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(P->X0T.p + (int64_t)P->K0 * P->X0T.ld, P->R);
-    }
+    int rc = alloc_planes(P, P->X0, P->R, P->K0 + 1);
+    if (!rc) ones_col_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(P->X0.p + P->K0, P->R, P->X0.ld);
     int64_t off = P->A;                                         // std first
     if (!rc) rc = build_mlp(P, P->adapt, cfg->n_adaptation_hidden, cfg->adaptation_hidden, P->P, P->Din, P->Din, 0, 0, off);
     if (!rc) rc = build_mlp(P, P->actor, cfg->n_actor_hidden, cfg->actor_hidden, P->A, P->Din + P->P, P->Din + P->P, 0, 0, off);
@@ -974,6 +944,11 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
     cudaStream_t s = (cudaStream_t)stream;
     const int world = grad_world > 1 ? grad_world : 1;
     rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
+    if (!rc) {
+        p->packed_src = batch->obs_history;
+        p->packed_idx = indices;
+        p->packed_count = count;
+    }
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (!rc) rc = scatter_latent(p, count, true, s);
     if (!rc) rc = forward_mlp(p, p->actor, count, true, s);
@@ -999,9 +974,7 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
         h.amax_mu = p->ga(CTX_PPO, a, a.n - 1);
         h.amax_v = p->ga(CTX_PPO, c, c.n - 1);
         h.dmu = a.dZ[a.n - 1].p; h.ld_dmu = a.dZ[a.n - 1].ld; h.plane_dmu = a.dZ[a.n - 1].plane;
-        h.dmut = a.dZT[a.n - 1].p; h.ld_dmut = a.dZT[a.n - 1].ld; h.plane_dmut = a.dZT[a.n - 1].plane;
         h.dv = c.dZ[c.n - 1].p; h.ld_dv = c.dZ[c.n - 1].ld; h.plane_dv = c.dZ[c.n - 1].plane;
-        h.dvt = c.dZT[c.n - 1].p; h.ld_dvt = c.dZT[c.n - 1].ld; h.plane_dvt = c.dZT[c.n - 1].plane;
         h.partial = p->head_partial;
         ppo_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
         ppo_head_reduce_kernel<<<1, 64, 0, s>>>(p->head_partial, blocks, p->A, p->params, hp->entropy_coef, 1.0f / (float)world, count, stats,
@@ -1020,9 +993,7 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
             g.split_scale_ptr = p->gs(CTX_PPO, ad, ad.n - 1);
             g.amax_out = p->ga(CTX_PPO, ad, ad.n - 1);
             Planes& dz = ad.dZ[ad.n - 1];
-            Planes& dzt = ad.dZT[ad.n - 1];
             g.out_h = dz.p; g.ld_h = dz.ld; g.plane_h = dz.plane;
-            g.out_t = dzt.p; g.ld_t = dzt.ld; g.plane_t = dzt.plane;
             Operand B{L.WT.p + (int64_t)p->Din * L.WT.ld, p->P, L.WT.ld, L.WT.plane};
             rc = run_gemm(p, op(a.dZ[0], count), count, B, p->P, L.N, 1, g, s);
             if (!rc) rc = backward_mlp(p, ad, count, CTX_PPO, s);
@@ -1057,7 +1028,10 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
     if (!batch || !stats || num_train < 0 || num_train > count) return LT_ERR_INVALID;
     cudaStream_t s = (cudaStream_t)stream;
     const int world = grad_world > 1 ? grad_world : 1;
-    rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
+    // PPO:150-176 runs on the minibatch lt_ppo_minibatch_grad just gathered: its split copy is still in X0 (the adaptation
+    // module reads only the obs_history columns; its first-layer weights are zero on the latent / privileged columns)
+    const bool reuse = p->packed_src == batch->obs_history && p->packed_idx == indices && p->packed_count == count && indices != nullptr;
+    if (!reuse) rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (rc) return rc;
     const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
@@ -1076,7 +1050,6 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
         h.s_g = p->gs(CTX_ADAPT, ad, ad.n - 1);
         h.amax = p->ga(CTX_ADAPT, ad, ad.n - 1);
         h.dz = ad.dZ[ad.n - 1].p; h.ld_dz = ad.dZ[ad.n - 1].ld; h.plane_dz = ad.dZ[ad.n - 1].plane;
-        h.dzt = ad.dZT[ad.n - 1].p; h.ld_dzt = ad.dZT[ad.n - 1].ld; h.plane_dzt = ad.dZT[ad.n - 1].plane;
         h.partial = p->head_partial;
         adapt_head_kernel<<<blocks, HEAD_THREADS, 0, s>>>(h);
         adapt_head_reduce_kernel<<<1, 32, 0, s>>>(p->head_partial, blocks, count, num_train, p->P, stats);
@@ -1141,6 +1114,42 @@ int lt_linear_f32(const float* a, const float* b, const float* bias, float* out,
     cudaFree(pa);
     cudaFree(pb);
     if (part) cudaFree(part);
+    if (rc) return rc;
+    LTP_CUDA(nullptr, e);
+    return LT_OK;
+}
+
+int lt_linear_tn_f32(const float* a, const float* b, float* out, int32_t M, int32_t N, int32_t K, int32_t splits, void* stream) {
+    if (!a || !b || !out || M <= 0 || N <= 0 || K <= 0) return LT_ERR_INVALID;
+    int dev = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, LT_ERR_NO_DEVICE, "no sm_100 device");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t lda = up(M, 8), ldb = up(N, 8);
+    __half *pa = nullptr, *pb = nullptr;
+    float* part = nullptr;
+    LTP_CUDA(nullptr, cudaMalloc(&pa, (size_t)2 * K * lda * 2));
+    LTP_CUDA(nullptr, cudaMalloc(&pb, (size_t)2 * K * ldb * 2));
+    LTP_CUDA(nullptr, cudaMemsetAsync(pa, 0, (size_t)2 * K * lda * 2, s));
+    LTP_CUDA(nullptr, cudaMemsetAsync(pb, 0, (size_t)2 * K * ldb * 2, s));
+    split_f32_kernel<<<(unsigned)(((int64_t)K * M + 255) / 256), 256, 0, s>>>(a, K, M, S_X, pa, lda, (int64_t)K * lda);
+    split_f32_kernel<<<(unsigned)(((int64_t)K * N + 255) / 256), 256, 0, s>>>(b, K, N, S_X, pb, ldb, (int64_t)K * ldb);
+    ltg::Params p;
+    memset(&p, 0, sizeof p);
+    p.out_scale = 1.0f / (S_X * S_X);
+    if (splits < 1) splits = 1;
+    LTP_CUDA(nullptr, cudaMalloc(&part, (size_t)splits * M * N * 4));
+    p.mode = ltg::EPI_PARTIAL;
+    p.out_f32 = part;
+    p.ld_f32 = N;
+    p.split_stride = (int64_t)M * N;
+    int rc = run_gemm_mn(nullptr, Operand{pa, K, lda, (int64_t)K * lda}, M, Operand{pb, K, ldb, (int64_t)K * ldb}, N, K, splits, p, s);
+    if (!rc) sum_partials_kernel<<<(unsigned)(((int64_t)M * N + 255) / 256), 256, 0, s>>>(part, p.splits, (int64_t)M * N, N, nullptr, out);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(pa);
+    cudaFree(pb);
+    cudaFree(part);
     if (rc) return rc;
     LTP_CUDA(nullptr, e);
     return LT_OK;

@@ -38,6 +38,25 @@ def test_split_fp16_gemm_matches_float64(M, N, K, splits):
     assert rel < 2e-6, f"max error / sum|a||b| = {rel:.3e}"      # measured 2e-7 .. 1e-6 (torch fp32: 2e-7 .. 4e-7)
 
 
+@pytest.mark.parametrize("M,N,K,splits", [(128, 64, 64, 1), (128, 256, 128, 1), (512, 266, 1000, 1), (12, 129, 777, 3), (256, 513, 4096, 5),
+                                          (1, 1, 1, 1), (130, 17, 65, 1), (512, 266, 393216, 64)])
+def test_split_fp16_gemm_mn_major_matches_float64(M, N, K, splits):
+    """lt_linear_tn_f32: out = a.T @ b with both operands read MN-major (contraction over rows) -- the form of every weight /
+    bias gradient product.  Ragged M / N / K, several 64-wide operand chunks, split-K."""
+    from legged_tracking_b200 import _abi
+    lib = _abi.load()
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(K, M, device="cuda", generator=g)
+    b = torch.randn(K, N, device="cuda", generator=g) * 0.1
+    out = torch.full((M, N), float("nan"), device="cuda")
+    _abi.check_policy(lib.lt_linear_tn_f32(_p(a), _p(b), _p(out), M, N, K, splits, None), None, "lt_linear_tn_f32")
+    torch.cuda.synchronize()
+    want = a.double().T @ b.double()
+    mag = a.double().abs().T @ b.double().abs()
+    rel = ((out.double() - want).abs() / mag).max().item()
+    assert rel < 2e-6, f"max error / sum|a||b| = {rel:.3e}"
+
+
 # ------------------------------------------------------------------------------------------------------------------------
 # a14 / a15 through legged_tracking_b200.ppo (which only marshals pointers into include/lt_policy.h) against the oracle port
 # evaluated in float64 on the same weights and inputs.
