@@ -147,6 +147,15 @@ __device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uin
     hi = *reinterpret_cast<const uint32_t*>(&h);
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
+// fast-path variant: one saturating pack (F2FP.SATFINITE) per plane instead of four clamps; x - hi is exact in fp32
+__device__ __forceinline__ void split_pair_sat(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(x1), "f"(x0));
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - hf.y), "f"(x0 - hf.x));
+}
+// ELU for the fast path: ex2.approx - 1 below zero.  Absolute error <= 1.2e-7 (one fp32 ulp of the O(1) activations it is added
+// to in the next layer); the series branch of act_fwd<ACT_ELU> only improves the RELATIVE error of outputs below 0.03.
+__device__ __forceinline__ float elu_fast(float z) { return z > 0.0f ? z : __expf(z) - 1.0f; }
 constexpr float SELU_ALPHA = 1.6732632423543772848170429916717f, SELU_SCALE = 1.0507009873554804934193349852946f;
 template <int ACT>
 __device__ __forceinline__ float act_fwd(float z) {
@@ -336,12 +345,78 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
             const float out_scale = p.a_scale_ptr ? p.out_scale / __ldg(p.a_scale_ptr) : p.out_scale;
             const float split_scale = p.split_scale_ptr ? __ldg(p.split_scale_ptr) : p.split_scale;
             float tile_amax = 0.0f;
+            // fast path: ELU bodies (the reference default), whole 32-column chunks inside the matrix, 16-byte aligned rows / bias
+            const bool fast_tile = p.act == ACT_ELU && (p.ld_h & 7) == 0 && (n0 & 7) == 0 &&
+                                   ((p.mode == EPI_ELU && p.bias && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) ||
+                                    (p.mode == EPI_BWD && (!p.act_h || (p.ld_act & 7) == 0)));
             for (int c = 32 * half; c < p.bn; c += 64) {
                 uint32_t r[32];
                 const int width = min(32, p.bn - c);                              // 32 or 16 (bn is a multiple of 16)
+                const int col0 = n0 + c;
+                if (fast_tile && width == 32 && col0 + 32 <= p.N) {
+                    uint32_t hi[16], lo[16];
+                    if (p.mode == EPI_ELU) {
+                        float4 b4[8];
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) b4[g] = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + g);
+                        tmem_ld32(taddr + c, r);
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) {
+                            const float y0 = elu_fast(fmaf(__uint_as_float(r[4 * g]), out_scale, b4[g].x));
+                            const float y1 = elu_fast(fmaf(__uint_as_float(r[4 * g + 1]), out_scale, b4[g].y));
+                            const float y2 = elu_fast(fmaf(__uint_as_float(r[4 * g + 2]), out_scale, b4[g].z));
+                            const float y3 = elu_fast(fmaf(__uint_as_float(r[4 * g + 3]), out_scale, b4[g].w));
+                            split_pair_sat(y0 * split_scale, y1 * split_scale, hi[2 * g], lo[2 * g]);
+                            split_pair_sat(y2 * split_scale, y3 * split_scale, hi[2 * g + 1], lo[2 * g + 1]);
+                        }
+                    } else {
+                        uint4 qh[4], ql[4];
+                        const bool have_act = p.act_h != nullptr;
+                        if (have_act && row_ok) {
+                            const uint4* ah = reinterpret_cast<const uint4*>(p.act_h + (int64_t)row * p.ld_act + col0);
+                            const uint4* al = reinterpret_cast<const uint4*>(p.act_h + p.plane_act + (int64_t)row * p.ld_act + col0);
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                qh[g] = __ldg(ah + g);
+                                ql[g] = __ldg(al + g);
+                            }
+                        } else {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) qh[g] = ql[g] = make_uint4(0u, 0u, 0u, 0u);
+                        }
+                        tmem_ld32(taddr + c, r);
+                        const float sc = split_scale * out_scale;
+                        const float amax_scale = 1.0f / split_scale;
+                        float m = 0.0f;
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const uint32_t wh[4] = {qh[g].x, qh[g].y, qh[g].z, qh[g].w}, wl[4] = {ql[g].x, ql[g].y, ql[g].z, ql[g].w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 fh = __half22float2(*reinterpret_cast<const __half2*>(&wh[e]));
+                                const float2 fl = __half22float2(*reinterpret_cast<const __half2*>(&wl[e]));
+                                const float y0 = (fh.x + fl.x) * p.act_inv_scale, y1 = (fh.y + fl.y) * p.act_inv_scale;
+                                const float d0 = (have_act && y0 <= 0.0f) ? y0 + 1.0f : 1.0f, d1 = (have_act && y1 <= 0.0f) ? y1 + 1.0f : 1.0f;
+                                const float x0 = __uint_as_float(r[g * 8 + 2 * e]) * sc * d0, x1 = __uint_as_float(r[g * 8 + 2 * e + 1]) * sc * d1;
+                                m = fmaxf(m, fmaxf(fabsf(x0), fabsf(x1)));
+                                split_pair_sat(x0, x1, hi[g * 4 + e], lo[g * 4 + e]);
+                            }
+                        }
+                        tile_amax = fmaxf(tile_amax, m * amax_scale);
+                    }
+                    if (row_ok) {
+                        uint4* oh = reinterpret_cast<uint4*>(p.out_h + (int64_t)row * p.ld_h + col0);
+                        uint4* ol = reinterpret_cast<uint4*>(p.out_h + p.plane_h + (int64_t)row * p.ld_h + col0);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            oh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+                            ol[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                        }
+                    }
+                    continue;
+                }
                 if (width == 32) tmem_ld32(taddr + c, r);
                 else tmem_ld16(taddr + c, r);
-                const int col0 = n0 + c;
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * out_scale;

@@ -49,6 +49,7 @@ struct Layer {
     int k_real = 0;                   // in_features of the nn.Linear
     int c1 = 0, s2 = 0, c2 = 0;       // param cols [0,c1) <- gemm cols [0,c1); param cols [c1,c1+c2) <- gemm cols [s2,s2+c2)
     int64_t w_off = 0, b_off = 0;     // offsets in the flat parameter vector
+    float* bias16 = nullptr;          // 16-byte aligned copy of the bias (vector loads in the GEMM epilogue), refreshed with W
     Planes W, WT;                     // [2][N][ld(K)] and (training) [2][K][ld(N)] for the input-gradient GEMM
 };
 
@@ -151,8 +152,10 @@ __device__ __forceinline__ void split1(float x, __half& hi, __half& lo) {
 
 // master weights -> operand planes W [N][K] and WT [K][N] of one layer (expanded column map for first layers)
 __global__ void split_weights_kernel(const float* __restrict__ w, int N, int K, int k_real, int c1, int s2, int c2, __half* W, int64_t ldW,
-                                     int64_t planeW, __half* WT, int64_t ldT, int64_t planeT) {
+                                     int64_t planeW, __half* WT, int64_t ldT, int64_t planeT, const float* __restrict__ bias,
+                                     float* __restrict__ bias16) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) bias16[i] = bias[i];
     if (i >= (int64_t)N * K) return;
     const int n = (int)(i / K), k = (int)(i % K);
     int src = -1;
@@ -596,6 +599,7 @@ int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_o
         L.b_off = off;
         off += L.N;
         int rc = alloc_planes(P, L.W, L.N, L.K);
+        if (!rc) rc = alloc_dev(P, L.bias16, up(L.N, 4));
         if (rc) return rc;
         if (P->c.training) {
             rc = alloc_planes(P, L.WT, L.K, L.N);
@@ -620,7 +624,7 @@ int refresh_mlp(lt_policy* P, Mlp& m, cudaStream_t s) {
         Layer& L = m.L[l];
         const int64_t n = (int64_t)L.N * L.K;
         split_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->params + L.w_off, L.N, L.K, L.k_real, L.c1, L.s2, L.c2, L.W.p, L.W.ld,
-                                                                        L.W.plane, L.WT.p, L.WT.ld, L.WT.plane);
+                                                                        L.W.plane, L.WT.p, L.WT.ld, L.WT.plane, P->params + L.b_off, L.bias16);
     }
     LTP_CUDA(P, cudaGetLastError());
     return LT_OK;
@@ -633,7 +637,7 @@ int forward_mlp(lt_policy* P, Mlp& m, int rows, bool train, cudaStream_t s) {
         ltg::Params p;
         memset(&p, 0, sizeof p);
         p.out_scale = 1.0f / (S_X * S_W);
-        p.bias = P->params + L.b_off;
+        p.bias = L.bias16;
         const Operand A = l == 0 ? op(P->X0, rows) : op(m.Y[l - 1], rows);
         if (l < m.n - 1) {
             p.mode = ltg::EPI_ELU;

@@ -1,6 +1,2 @@
-# scratch script for one-off GPU checks (rewritten freely; the full round is profiles/gpu_round.sh)
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_policy.py -m gpu -q -x -k "gemm" > gpurun_out/pytest_gemm.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gemm.log
-timeout 600 python -m pytest tests/test_gpu_policy.py tests/test_gpu_ppo.py tests/test_gpu_env.py tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/pytest_policy.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_policy.log
-timeout 300 python profiles/run_ppo.py --reps 2 > gpurun_out/run_ppo.log 2>&1
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/ppo_launches.csv python profiles/run_ppo.py --acts 1 > gpurun_out/ncu_ppo.log 2>&1
+timeout 900 ncu --set full --import-source on --clock-control none -k regex:lt_gemm_kernel -s 156 -c 1 -f -o gpurun_out/gemm_fwd python profiles/run_ppo.py --acts 1 --epochs 1 > gpurun_out/ncu_gemm.log 2>&1
