@@ -176,7 +176,7 @@ def time_region(fn, steps, stream_sync=True):
     return e0.elapsed_time(e1)
 
 
-def cpu_oracle_rate(steps, n_envs, config):
+def cpu_oracle_rate(steps, n_envs, config, warmup=1):
     """The reference's torch step path on the host cores (oracle port, faithful per-env height gather): env-steps/s."""
     from oracle.port import OraclePort
     from legged_tracking_b200 import cconfig
@@ -195,7 +195,8 @@ def cpu_oracle_rate(steps, n_envs, config):
     def one(k):
         a, sim = inputs[k % 2]
         port.step(a, sim, U, torch.rand(n, flat["num_obs"]) if flat["add_noise"] else None, torch.rand(3))
-    one(0)
+    for k in range(max(warmup, 1)):
+        one(k)
     t0 = time.perf_counter()
     for k in range(steps):
         one(k + 1)
@@ -203,21 +204,42 @@ def cpu_oracle_rate(steps, n_envs, config):
     return n * steps / dt, dt / steps, torch.get_num_threads()
 
 
+def workload_config(args, world, n_env, touched_mb=None):
+    """The `config` object of the JSON line: names the workload; identical for the B200 arm and the reference arm."""
+    return {"workload": f"{args.config}: single_path tunnel, 2x10x11 front-half heights, camera_zero, e2e reward set, "
+                        f"noise+DR on; full step = 4 x actuator-net torques + fused post-physics step",
+            "envs_per_gpu": n_env, "total_envs": n_env * world, "parallelism": f"env-sharded x{world}, no data-path collective",
+            "cuda_graph": not args.no_graph, "envs_per_warp": args.epw,
+            "l2": f"inputs larger than L2: {touched_mb if touched_mb is not None else 484:.0f} MB touched per step, "
+                  f"{N_REPLAY_SETS} replay sets cycled"}
+
+
 def run_reference(args, rank):
-    """--impl reference: the reference's own CPU implementation of the path (oracle port; /root/reference does not
-    exist on the GPU box), bounded sample per step."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores, all threads.  The UNMODIFIED
+    reference (staged by oracle/make_ref.sh under oracle/_ref/, which travels to the GPU box) when present, else the oracle port.
+    Same configuration and metric as the B200 arm; each step is a BOUNDED sample of the workload (--cpu-envs envs instead of
+    65,536: the reference gathers heights with one kernel launch per env, ~50 us per env-step on these cores, so a full-size
+    step would take > 3 s and the run many minutes).  --steps / --warmup are honoured as given."""
     if rank != 0:
         return
-    n_envs = args.cpu_envs
-    for _ in range(max(args.warmup, 0) and 1):
-        pass
-    rate, s_per_step, cores = cpu_oracle_rate(max(1, min(args.steps, 20)), n_envs, "cfg2")
+    from oracle import ref_arm
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # size the per-step sample so that the whole run stays within a few minutes (~50 us per env-step on these cores)
+    # in multiples of the 32 x 32 tile grid (the reference asserts num_envs % 1024 == 0, LR:1819)
+    n_envs = int(max(1024, min(args.cpu_envs, (200.0 / ((steps + warmup) * 50e-6))) // 1024 * 1024))
+    if ref_arm.available():
+        rate, s_per_step, cores = ref_arm.step_rate(steps, warmup, n_envs)
+        kind, how = "reference", "unmodified reference (oracle/_ref: go1_gym HistoryWrapper(TrajectoryTrackingEnv).step under the isaacgym shims)"
+    else:
+        rate, s_per_step, cores = cpu_oracle_rate(steps, n_envs, "cfg2", warmup=warmup)
+        kind, how = "port", "oracle/port.py with the reference's per-env height gather (oracle/_ref not staged)"
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": max(1, min(args.steps, 20)), "warmup": 1, "ms_per_step": s_per_step * 1e3, "higher_is_better": True,
+            "steps": steps, "warmup": warmup, "ms_per_step": s_per_step * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"cfg5 shape (single_path, 2x10x11 heights, camera_zero, e2e rewards), bounded sample of {n_envs} envs per step on the host CPU"},
-            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{n_envs} envs x {max(1, min(args.steps, 20))} steps, oracle/port.py with the reference's per-env height gather"},
+            "config": workload_config(args, max(1, args.gpus), args.envs_per_gpu),
+            "sample": f"bounded sample: {n_envs} of the {args.envs_per_gpu} envs per step (CPU time is linear in envs)",
+            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": f"{n_envs} envs x {steps} steps after {warmup} warm-up steps, {how}"},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     _emit(json.dumps(line))
 
@@ -309,6 +331,72 @@ def terrain_build_timing(dev):
     nbytes = t.tile_heights.numel() * 4
     return {"tiles": 1024, "kernel_us": ms * 1e3, "written_gb_per_s": nbytes / (ms * 1e-3) / 1e9,
             "host_draws_plus_kernel_ms": wall * 1e3, "bytes": nbytes}
+
+
+def strong_block(args, rank, world, dev, dist, peak):
+    """BASELINE.json configs[4] as the north-star words it: 65,536 envs IN TOTAL, sharded over the `world` GPUs (strong scaling),
+    the full step, and the PPO iteration (T = 24 rollout + GAE + 5 x 4 minibatch update) with its NCCL exchanges timed apart.
+    All times are device times, max over ranks."""
+    from legged_tracking_b200.engine import StepEngine
+    total = 65536
+    n_env = total // world
+    flat, terrain, act, synth = workload.make(args.config, num_envs=n_env, seed=3000 + rank)
+    eng = StepEngine(flat, terrain, act, device=dev, seed=211 + rank, envs_per_warp=args.epw)
+    init_engine_state(eng, synth, flat)
+    rs = ReplaySets(eng, synth, flat, N_REPLAY_SETS)
+    for k in range(3):
+        launch_step(eng, rs.sets[k % N_REPLAY_SETS])
+    torch.cuda.synchronize()
+    graphs = []
+    if not args.no_graph:
+        side = torch.cuda.Stream()
+        for st in rs.sets:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                launch_step(eng, st, eager_gravity=False)
+            graphs.append(g)
+
+    def step_fn(k):
+        i = k % N_REPLAY_SETS
+        if graphs and not eng.gravity.fires_next():
+            graphs[i].replay()
+            eng.gravity.common_step_counter += 1
+        else:
+            launch_step(eng, rs.sets[i])
+
+    def torque_only(k):
+        st = rs.sets[k % N_REPLAY_SETS]
+        for sub, dof in enumerate(st["dof"]):
+            eng.bind_sim(dof_state=dof)
+            eng.compute_torques(st["actions"], sub)
+
+    def post_only(k):
+        st = rs.sets[k % N_REPLAY_SETS]
+        eng.bind_sim(root_states=st["root"], contact_forces=st["contact"], dof_state=st["dof"][-1])
+        eng.post_physics_step(advance_gravity=False)
+    for k in range(3):
+        step_fn(k)
+    steps = max(20, args.steps)
+    dist.barrier()
+    ms = time_region(step_fn, steps) / steps
+    ksub = max(20, min(args.steps, 300))
+    ms_torque = time_region(torque_only, ksub) / (ksub * flat["decimation"])
+    ms_post = time_region(post_only, ksub) / ksub
+    t = torch.tensor([ms, ms_torque, ms_post], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_torque, ms_post = [float(x) for x in t.tolist()]
+    alg = workload.algorithmic_bytes(flat)
+    out = {"total_envs": total, "envs_per_gpu": n_env, "scaling": "strong", "steps": steps, "ms_per_step": ms,
+           "value": total / (ms * 1e-3), "unit": UNIT,
+           "kernels_us": {"torque_substep": ms_torque * 1e3, "post_physics_chain": ms_post * 1e3},
+           "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s",
+                        "post_physics": {"achieved": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9,
+                                         "frac": alg["post_physics"] * n_env / (ms_post * 1e-3) / 1e9 / peak},
+                        "full_step": {"achieved": alg["full_step"] * n_env / (ms * 1e-3) / 1e9,
+                                      "frac": alg["full_step"] * n_env / (ms * 1e-3) / 1e9 / peak}}}
+    if not args.no_ppo:
+        out["ppo_iteration"] = ppo_iteration(eng, rs, graphs, flat, dev, dist, args.ppo_iters)
+    return out
 
 
 def run_b200(args, rank, world, local_rank):
@@ -419,6 +507,7 @@ def run_b200(args, rank, world, local_rank):
     while n_env % n_chunks or (n_env // n_chunks) % 1024:
         n_chunks -= 1
     ms_e2e = ms_e2e_single
+    pipe = engines = None
     if n_chunks > 1:
         from legged_tracking_b200.engine import HostStepPipeline
         M = n_env // n_chunks
@@ -458,9 +547,14 @@ def run_b200(args, rank, world, local_rank):
     h2d = sum(int(x.numel()) * 4 for x in (own["actions"], own["root"], own["contact"])) + flat["decimation"] * own["dof"].numel() * 4
     d2h = sum(int(v.numel()) * v.element_size() for v in out_h.values())
 
+    peak, peak_src = measured_peaks()
+    strong = None
+    if world > 1 and 65536 % world == 0 and (65536 // world) % 1024 == 0:
+        del pipe, engines
+        torch.cuda.empty_cache()
+        strong = strong_block(args, rank, world, dev, dist, peak)
     if rank != 0:
         return
-    peak, peak_src = measured_peaks()
     ms_step = ms / args.steps
     value = world * n_env * args.steps / (ms * 1e-3)
     torque_total = ms_torque * flat["decimation"]
@@ -492,19 +586,19 @@ def run_b200(args, rank, world, local_rank):
                                   "post_physics": ms_post / (torque_total + ms_post)}}
     cpu = None
     if world == 1 and not args.no_cpu:
-        rate, s_per_step, cores = cpu_oracle_rate(args.cpu_steps, args.cpu_envs, "cfg2")
-        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same workload shape, oracle/port.py (torch CPU, "
-                         f"reference's per-env height gather), {s_per_step * 1e3:.1f} ms/step"}
+        from oracle import ref_arm
+        if ref_arm.available():
+            rate, s_per_step, cores = ref_arm.step_rate(args.cpu_steps, 2, args.cpu_envs)
+            kind, how = "reference", "the unmodified reference (oracle/_ref) stepping HistoryWrapper(TrajectoryTrackingEnv) under the isaacgym shims"
+        else:
+            rate, s_per_step, cores = cpu_oracle_rate(args.cpu_steps, args.cpu_envs, "cfg2")
+            kind, how = "port", "oracle/port.py (torch CPU, reference's per-env height gather)"
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same workload shape, {how}, {s_per_step * 1e3:.1f} ms/step"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"{args.config}: single_path tunnel, 2x10x11 front-half heights, camera_zero, e2e reward set, "
-                                   f"noise+DR on; full step = {flat['decimation']} x actuator-net torques + fused post-physics step",
-                       "envs_per_gpu": n_env, "total_envs": n_env * world, "parallelism": f"env-sharded x{world}, no data-path collective",
-                       "cuda_graph": not args.no_graph, "envs_per_warp": args.epw,
-                       "l2": f"inputs larger than L2: {alg['full_step'] * n_env / 1e6:.0f} MB touched per step, "
-                             f"{N_REPLAY_SETS} replay sets cycled"},
+            "config": workload_config(args, world, n_env, alg['full_step'] * n_env / 1e6),
             "clocks": sampler.summary(), "gpu_launches": launches_per_step * args.steps,
             "e2e": {"value": world * n_env * ke / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / ke, "steps": ke,
@@ -519,6 +613,8 @@ def run_b200(args, rank, world, local_rank):
         line["terrain_build"] = {"error": str(e)[:200]}
     if ppo_res:
         line["ppo_iteration"] = ppo_res
+    if strong:
+        line["strong_65536_total"] = strong
     if cpu:
         line["cpu_baseline"] = cpu
     _emit(json.dumps(line))
