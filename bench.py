@@ -264,7 +264,7 @@ def ppo_iteration(eng, rs, graphs, flat, dev, dist, iters):
                 actions = alg.act(st["obs_buf"], st["privileged_obs_buf"], st["obs_history"])
                 s = (k0 + t) % N_REPLAY_SETS
                 rs.sets[s]["actions"].copy_(actions)
-                if graphs and not eng.gravity.fires_next():
+                if graphs and eng.graph_replay_ok():
                     graphs[s].replay()
                     eng.gravity.common_step_counter += 1
                 else:
@@ -358,7 +358,7 @@ def strong_block(args, rank, world, dev, dist, peak):
 
     def step_fn(k):
         i = k % N_REPLAY_SETS
-        if graphs and not eng.gravity.fires_next():
+        if graphs and eng.graph_replay_ok():
             graphs[i].replay()
             eng.gravity.common_step_counter += 1
         else:
@@ -430,7 +430,7 @@ def run_b200(args, rank, world, local_rank):
 
     def step_fn(k):
         s = k % N_REPLAY_SETS
-        if graphs and not eng.gravity.fires_next():
+        if graphs and eng.graph_replay_ok():
             graphs[s].replay()
             eng.gravity.common_step_counter += 1
         else:

@@ -598,10 +598,19 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
     }
     uint32_t rnd[4] = {0u, 0u, 0u, 0u};
     if (HN && NOISE == 2) lt_philox((uint32_t)ie, (uint32_t)lane | LT_STREAM_NOISE, step, 0u, p.seed_lo, p.seed_hi, rnd);
+    const bool hist_alias = p.obs_history == p.obs_buf;          // H == 1: the history block IS the observation row (engine.py)
     float* hist_row = p.obs_history + (size_t)ie * no * H;
     if (H > 1) {
         const int keep = (H - 1) * no;
-        for (int k = lane; k < keep; k += 32) { const float v = hist_row[k + no]; hist_row[k] = v; }
+        // in-place left shift by one block: every lane's read of a round completes before any lane's write of that round, and
+        // a round completes before the next one starts (no reliance on the warp staying converged)
+        for (int k0 = 0; k0 < keep; k0 += 32) {
+            const int k = k0 + lane;
+            const float v = k < keep ? hist_row[k + no] : 0.0f;
+            __syncwarp();
+            if (k < keep) hist_row[k] = v;
+            __syncwarp();
+        }
     }
     // per-lane base pointers: column h0 + lane (ceiling layer) and h0 + per_layer + lane (floor layer)
     float* hist_new = hist_row + (size_t)(H - 1) * no;
@@ -637,7 +646,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
                 }
                 const float o = lt_obs_finish_dev<(HN ? NOISE : 0)>(h, u, (HN && NOISE) ? __ldg(p.noise_scale_vec + col) : 0.0f, clip);
                 po[layer][32 * k] = o;
-                ph[layer][32 * k] = o;
+                if (!hist_alias) ph[layer][32 * k] = o;
             }
         }
     }
@@ -656,7 +665,7 @@ __global__ void __launch_bounds__(LT_OBS_THREADS) lt_obs_kernel(const __grid_con
             const float ns = !NOISE ? 0.0f : (m == 0 ? ns0 : (m == 1 ? ns1 : __ldg(p.noise_scale_vec + col)));
             const float o = lt_obs_finish_dev<NOISE>(raw, u, ns, clip);
             obs_row[col] = o;
-            hist_new[col] = o;
+            if (!hist_alias) hist_new[col] = o;
         }
     };
     // the first two rounds (64 columns: every shipped configuration) with compile-time noise slots; the rest rolled

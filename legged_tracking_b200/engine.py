@@ -86,10 +86,14 @@ class ExplorationCurriculum:
     def term_scales(self):
         return [self.scales[n] for n in self.names]
 
+    def changes_at(self, common_step_counter):
+        """Would advance(common_step_counter) change a scale?  (A captured CUDA graph holds the scales it was captured with.)"""
+        return any(key in self.scales and common_step_counter > self.steps and self.scales[key] > 0 for key in self.KEYS)
+
 
 class StepEngine:
     def __init__(self, flat, terrain, actuator, device="cuda:0", seed=0, envs_per_warp=0, track_command_sums=True,
-                 export_height_indices=False):
+                 export_height_indices=False, alias_history=True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _abi.LtError("StepEngine needs a CUDA device (sm_100a); there is no CPU implementation in this package")
@@ -145,6 +149,12 @@ class StepEngine:
         for name, dt, shape in cconfig.state_spec(flat):
             if name in skip:
                 setattr(ptrs, name, None)
+                continue
+            if name == "obs_history" and alias_history and flat["obs_history_length"] == 1 and "obs_buf" in self.state:
+                # H = 1 (every trajectory-tracking config): obs_history = cat(obs_history[:, num_obs:], obs) IS obs
+                # (history_wrapper.py:22), so the two names share one buffer and the observation row is written once
+                self.state[name] = self.state["obs_buf"]
+                setattr(ptrs, name, self.state["obs_buf"].data_ptr())
                 continue
             buf = torch.full(shape, cconfig.STATE_INIT.get(name, 0), dtype=_TORCH_DTYPES[dt], device=dev)
             self.state[name] = buf
@@ -272,6 +282,20 @@ class StepEngine:
             self.state["gravity_vec"].copy_(GravitySchedule.gravity_vec_of(new_g), non_blocking=False)
         if advance_gravity and self.curriculum.advance(self.gravity.common_step_counter):
             self.set_reward_scales(self.curriculum.term_scales())
+            self._scales_changed = True           # graphs captured before this point hold stale scales (graph_replay_ok)
+
+    def graph_replay_ok(self):
+        """May the NEXT step be a replay of a CUDA graph captured from post_physics_step(advance_gravity=False)?  A captured
+        graph freezes what the host passes by value at capture time: the gravity event flags and the per-term reward scales
+        (lt_config travels as a kernel parameter).  So a step on which _randomize_gravity fires (LR:826-830) or on which
+        update_curriculum changes a scale (LR:171-183) must be launched eagerly (and the graph re-captured once the scales
+        have changed, since later replays would still carry the old ones).  After a replay the caller advances
+        gravity.common_step_counter itself."""
+        return not self.gravity.fires_next() and not self.scales_stale_in_graph()
+
+    def scales_stale_in_graph(self):
+        n = self.gravity.common_step_counter + 1
+        return self.curriculum.changes_at(n) or self.curriculum.changes_at(n - 1) or getattr(self, "_scales_changed", False)
 
     def sign_prepass(self, args=None, stream=None):
         """lt_reward_sign_prepass: shard-local sums of the sign-indefinite terms -> self.term_sums (device float32[LT_MAX_TERMS]).

@@ -203,7 +203,8 @@ class LeggedRobot:
                                  "workload.synth_terrain builds one of the single_path shape")
             terrain = {"env_origins": plane_env_origins(self.num_envs, cfg.env.env_spacing)}
         self.engine = StepEngine(f, terrain, actuator if actuator is not None else workload.load_actuator(), device=self.device,
-                                 seed=seed)
+                                 seed=seed, alias_history=False)      # HistoryWrapper zeroes obs_history rows on reset without
+        #                                                                      touching obs_buf (history_wrapper.py:33-41): separate buffers
         e = self.engine
         self.root_states, self.dof_state = e.root_states, e.dof_state
         self.contact_forces, self.rigid_body_state = e.contact_forces, e.rigid_body_state
