@@ -158,6 +158,23 @@ def state_spec(flat):
     return spec
 
 
+# Which state buffers the post-physics phase of ONE env-step reads / writes (SURVEY.md section 8d's accounting): name -> role.
+# workload.algorithmic_bytes derives the per-env byte counts from state_spec's shapes with this table, so that a buffer that
+# is renamed, resized or dropped changes the figure (tests/test_cfg_flat.py pins it to SURVEY's 4,121 B at cfg 2 / 5).
+# Buffers that are touched only on reset / interval DR (lag_buffer, finished_*, Kp_factors ...) are not part of the figure.
+POST_PHYSICS_TRAFFIC = {
+    "actions": "r", "last_actions": "rw", "last_last_actions": "w", "last_dof_vel": "rw", "torques": "r",
+    "last_root_vel": "w", "base_lin_vel": "w", "base_ang_vel": "w", "projected_gravity": "w", "base_rotation": "rw_row1",
+    "relative_linear": "w", "relative_rotation": "w", "episode_sums": "rw", "command_sums": "rw",
+    "obs_buf": "w", "privileged_obs_buf": "w", "obs_history": "w", "rew_buf": "w",
+    "episode_length_buf": "rw", "curr_pose_index": "rw", "collision_count": "rw",
+    "reset_buf": "w", "time_out_buf": "w", "reached_buf": "w", "switched_buf": "w", "plan_buf": "w",
+    "friction_coeffs": "r", "restitutions": "r",
+    # moved into the torque kernel's last sub-step (LR:151-152): counted with the torque phase
+    "last_joint_pos_target": "torque_w", "last_last_joint_pos_target": "torque_w",
+}
+
+
 # initial values that are not zero (LR:1203-1305)
 STATE_INIT = {"motor_strengths": 1.0, "Kp_factors": 1.0, "Kd_factors": 1.0}
 OPTIONAL_STATE = ("command_sums", "height_px", "height_py")

@@ -50,9 +50,13 @@ class ReplaySim(SimBackend):
     """Seeded synthetic 'PhysX output' (synthetic.SyntheticState), or recorded per-step arrays:
     frames[k] = dict(dof_state=[decimation, N*12, 2], root=[N,13], contact=[N,B,3], rigid=[N*B,13])."""
 
-    def __init__(self, seed=1000, frames=None):
+    def __init__(self, seed=1000, frames=None, device_frames=0):
+        """device_frames > 0: that many synthetic frames are generated once, kept in HBM and cycled with device-to-device
+        copies (what a GPU simulator hands over), instead of a fresh host-generated frame per step."""
         self.seed = seed
         self.frames = frames
+        self.device_frames = int(device_frames)
+        self._dev = None
         self.k = 0
 
     def attach(self, env):
@@ -61,9 +65,20 @@ class ReplaySim(SimBackend):
             self.gen = SyntheticState(env.num_envs, env.env_origins.cpu().numpy(), num_bodies=env.num_bodies, seed=self.seed,
                                       feet_indices=env.feet_indices.tolist())
         self._root = None
+        if self.frames is None and self.device_frames > 0:
+            d, n = env.device, env.num_envs
+            self._dev = []
+            for k in range(1, self.device_frames + 1):
+                root = self.gen.root(k)
+                self._dev.append(dict(dof=[self.gen.dof_state(k, s).reshape(env.dof_state.shape).to(d) for s in range(env.flat["decimation"])],
+                                      root=root.reshape(n, 13).to(d), contact=self.gen.contact(k).reshape(env.contact_forces.shape).to(d),
+                                      rigid=self.gen.rigid(k, root).reshape(env.rigid_body_state.shape).to(d)))
 
     def simulate(self, substep):
         e = self.env
+        if self._dev is not None:
+            e.dof_state.copy_(self._dev[self.k % len(self._dev)]["dof"][substep])
+            return
         if self.frames is not None:
             src = torch.as_tensor(np.ascontiguousarray(self.frames[self.k]["dof_state"][substep], np.float32))
         else:
@@ -72,6 +87,13 @@ class ReplaySim(SimBackend):
 
     def refresh(self):
         e = self.env
+        if self._dev is not None:
+            fr = self._dev[self.k % len(self._dev)]
+            e.root_states.view(e.num_envs, -1, 13)[:, 0, :].copy_(fr["root"])
+            e.contact_forces.copy_(fr["contact"])
+            e.rigid_body_state.copy_(fr["rigid"])
+            self.k += 1
+            return
         if self.frames is not None:
             fr = self.frames[self.k]
             root, contact, rigid = (torch.as_tensor(np.ascontiguousarray(fr[k], np.float32)) for k in ("root", "contact", "rigid"))
@@ -200,7 +222,7 @@ class LeggedRobot:
         if terrain is None:
             if f["mesh_type"] != "plane":
                 raise ValueError("a heightfield terrain needs terrain=dict(tile_heights, env_tile, env_terrain_origin, env_origins); "
-                                 "workload.synth_terrain builds one of the single_path shape")
+                                 "terrain.TunnelTerrain(cfg.terrain).table(num_envs) builds one of the single_path shape")
             terrain = {"env_origins": plane_env_origins(self.num_envs, cfg.env.env_spacing)}
         self.engine = StepEngine(f, terrain, actuator if actuator is not None else workload.load_actuator(), device=self.device,
                                  seed=seed, alias_history=False)      # HistoryWrapper zeroes obs_history rows on reset without

@@ -1,36 +1,24 @@
 """Synthetic workloads of BASELINE.json's configs at full size, for bench.py / scale tests / smoke().
 
-PhysX and the terrain generator are outside the hot path, so a workload is: a flat config (the reference's own,
-recorded off the live reference env into tests/golden/*.npz by oracle/gen_golden.py), a tile table of the
-`single_path` shape ([tiles, 2, 80, 40] float32 metres: layer 0 ceiling, layer 1 floor) and seeded simulator state
-(synthetic.SyntheticState).  The tile table here is SYNTHETIC: the 16 tiles the reference's generator produced for
-the fixture are cycled over the 32x32 grid with a seeded rescaling of every obstacle so that all 1024 tiles differ;
-origins follow the reference's grid (tile (r, c) at (4 r, 2 c) m; robot spawn at +(0.72, 1.0), LR:1808-1847).
+PhysX is outside the hot path, so a workload is: the flat config of one of the reference's argument sets
+(cfg.flat_from_cfg(cfg.preset_cfg(...)): the reference's own defaults + what scripts/train.py changes for those flags), the
+`single_path` tile table ([tiles, 2, 80, 40] float32 metres: layer 0 ceiling, layer 1 floor) built on the device by
+terrain.TunnelTerrain from the reference's random stream (np.random seed 11 like scripts/train.py:33-40; every tile
+differs), and seeded simulator state (synthetic.SyntheticState).  Nothing here reads tests/.
 """
-import json
 import os
 
 import numpy as np
 
-from . import synthetic
+from . import cfg as ltcfg, synthetic
 
-REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-GOLDEN = os.path.join(REPO, "tests", "golden")
-
-# BASELINE.json configs -> (fixture whose flat config is used, num_envs, tile grid)
+# BASELINE.json configs -> (argument-set preset of cfg.py, num_envs, tile grid)
 CONFIGS = {
     "cfg1": ("cfg1_plane_256", 256, None),
     "cfg2": ("cfg2_single_path_64", 4096, (32, 32)),
     "cfg3": ("cfg3_vel_64", 16384, (32, 32)),
     "cfg5": ("cfg2_single_path_64", 65536, (32, 32)),
 }
-
-
-def load_fixture_flat(fixture):
-    z = np.load(os.path.join(GOLDEN, fixture + ".npz"), allow_pickle=False)
-    flat = json.loads(str(z["flat"]))
-    terrain = {k[len("terrain/"):]: z[k] for k in z.files if k.startswith("terrain/")}
-    return flat, terrain
 
 
 def load_actuator():
@@ -40,37 +28,32 @@ def load_actuator():
     return {k: z[k] for k in z.files}
 
 
-def synth_terrain(base_terrain, num_envs, rows, cols, seed=11):
-    """Tile table + per-env origins for a rows x cols grid; env i lives on tile i % (rows*cols) (LR:1816-1823)."""
-    rng = np.random.RandomState(seed)
-    base = np.asarray(base_terrain["tile_heights"], np.float32)           # [16,2,R,C]
-    n_tiles = rows * cols
-    R, C = base.shape[2], base.shape[3]
-    tiles = base[np.arange(n_tiles) % base.shape[0]].copy()
-    ceil_ref = tiles[:, 0].max(axis=(1, 2), keepdims=True)                # free ceiling height of each tile
-    k = rng.uniform(0.5, 1.0, size=(n_tiles, 1, 1)).astype(np.float32)
-    tiles[:, 0] = ceil_ref - (ceil_ref - tiles[:, 0]) * k                 # shrink every hanging obstacle
-    tiles[:, 1] = tiles[:, 1] * rng.uniform(0.5, 1.0, size=(n_tiles, 1, 1)).astype(np.float32)
-    length = R * 0.05
-    width = C * 0.05
-    tr, tc = np.divmod(np.arange(n_tiles), cols)
-    t_origin = np.stack([tr * length, tc * width, np.zeros(n_tiles)], axis=1).astype(np.float32)
-    spawn = np.asarray(base_terrain["env_origins"][0] - base_terrain["env_terrain_origin"][0], np.float32)
-    env_tile = (np.arange(num_envs) % n_tiles).astype(np.int32)
-    return {"tile_heights": np.ascontiguousarray(tiles), "env_tile": env_tile,
-            "env_terrain_origin": np.ascontiguousarray(t_origin[env_tile]),
-            "env_origins": np.ascontiguousarray(t_origin[env_tile] + spawn[None, :])}
+_TABLES = {}
 
 
-def make(config="cfg5", num_envs=None, seed=1000, tile_grid=None):
-    """-> (flat, terrain, actuator, SyntheticState)"""
-    fixture, n_default, grid = CONFIGS[config]
-    flat, base_terrain = load_fixture_flat(fixture)
+def tunnel_table(terrain_cfg, rows, cols, device="cuda:0", seed=11):
+    """Host copy of the device-built tile table + tile origins for a rows x cols grid (cached: the bench builds several engines)."""
+    import torch
+    from .terrain import TunnelTerrain
+    key = (rows, cols, seed, str(device))
+    if key not in _TABLES:
+        terrain_cfg.num_rows, terrain_cfg.num_cols = rows, cols
+        t = TunnelTerrain(terrain_cfg, device=device, rng=np.random.RandomState(seed))
+        torch.cuda.synchronize()
+        _TABLES[key] = (t.tile_heights.cpu().numpy(), t.env_origins.reshape(rows * cols, 3).astype(np.float32),
+                        t.all_terrain_origins.reshape(rows * cols, 3).astype(np.float32))
+    return _TABLES[key]
+
+
+def make(config="cfg5", num_envs=None, seed=1000, tile_grid=None, device="cuda:0"):
+    """-> (flat, terrain, actuator, SyntheticState).  Needs the CUDA device for heightfield configs (the tile table is built by
+    lt_build_tunnel_tiles; there is no CPU generator in the product)."""
+    preset, n_default, grid = CONFIGS[config]
     n = int(num_envs or n_default)
-    flat = dict(flat)
-    flat["num_envs"] = n
+    c = ltcfg.preset_cfg(preset, num_envs=n)
     grid = tile_grid or grid
-    if flat["mesh_type"] == "plane":
+    if c.terrain.mesh_type == "plane":
+        flat = ltcfg.flat_from_cfg(c, num_envs=n)
         side = int(np.floor(np.sqrt(n)))
         rows_ = int(np.ceil(n / side))
         xx, yy = np.meshgrid(np.arange(rows_), np.arange(side), indexing="ij")
@@ -82,8 +65,12 @@ def make(config="cfg5", num_envs=None, seed=1000, tile_grid=None):
         rows, cols = grid
         while n % (rows * cols):                                          # LR:1819 requires divisibility
             rows, cols = max(rows // 2, 1), max(cols // 2, 1)
-        flat["terrain_num_rows"], flat["terrain_num_cols"] = rows, cols
-        terrain = synth_terrain(base_terrain, n, rows, cols)
+        c.terrain.num_rows, c.terrain.num_cols = rows, cols
+        flat = ltcfg.flat_from_cfg(c, num_envs=n)
+        tiles, env_o, tile_o = tunnel_table(c.terrain, rows, cols, device=device)
+        env_tile = (np.arange(n) % (rows * cols)).astype(np.int32)       # LR:1816-1823
+        terrain = {"tile_heights": tiles, "env_tile": env_tile, "env_terrain_origin": np.ascontiguousarray(tile_o[env_tile]),
+                   "env_origins": np.ascontiguousarray(env_o[env_tile])}
     synth = synthetic.SyntheticState(n, terrain["env_origins"], num_bodies=flat["num_bodies"], seed=seed,
                                      feet_indices=flat["feet_indices"])
     return flat, terrain, load_actuator(), synth
@@ -92,26 +79,49 @@ def make(config="cfg5", num_envs=None, seed=1000, tile_grid=None):
 # ---------------------------------------------------------------------------------------------------------------
 # Algorithmic traffic per env (SURVEY.md section 8d accounting), regenerated from the configuration.
 def algorithmic_bytes(flat):
+    """Per-env bytes of one step, derived from the real buffer list (cconfig.state_spec) + cconfig.POST_PHYSICS_TRAFFIC, plus
+    the simulator tensors of the input ABI.  At cfg 2 / 3 / 5 this reproduces SURVEY.md section 8d: 4,121 B post-physics (of
+    which 96 B, the joint-target history shift, are executed by the torque kernel's last sub-step), 816 B per torque sub-step."""
+    from . import cconfig
+    itemsize = {"f32": 4, "i64": 8, "i32": 4, "bool": 1}
+    n = flat["num_envs"]
+    per_env = {}
+    for name, dt, shape in cconfig.state_spec(flat):
+        total = itemsize[dt]
+        for d in shape:
+            total *= d
+        per_env[name] = total // n if n in shape else None
     nd = flat["num_dof"]
-    n_terms = len(flat["reward_names"])
     nx, ny = len(flat["measured_points_x"]), len(flat["measured_points_y"])
     x0 = nx // 2 + 1 if flat["measure_front_half"] else 0
     n_heights = 2 * (nx - x0) * ny if flat["observe_heights"] else 0
     H = flat["obs_history_length"]
+    # simulator tensors (a1) and tables: not in lt_state_ptrs
     reads = {"root row": 52, "dof_state": 8 * nd, "contact (penalised bodies)": 12 * len(flat["penalised_contact_indices"]),
-             "actions": 4 * nd, "last_actions": 4 * nd, "last_dof_vel": 4 * nd, "torques": 4 * nd, "trajectory row": 24,
-             "curr_pose_index": 8, "episode_length_buf": 8, "terrain origin + tile id": 16, "previous pitch": 4,
-             "privileged sources": 4 * flat["num_privileged_obs"], "episode_sums": 4 * (n_terms + 3),
-             "command_sums": 4 * (n_terms + 5), "collision_count": 8, "heights": 4 * n_heights}
-    writes = {"obs_buf": 4 * flat["num_obs"], "privileged_obs_buf": 4 * flat["num_privileged_obs"],
-              "obs_history": 4 * flat["num_obs"] * H, "rew_buf": 4, "masks": 5, "episode_length_buf": 8,
-              "history rows (5 x 12)": 5 * 4 * nd, "last_root_vel": 24, "base_lin_vel/ang_vel/projected_gravity": 36,
-              "base_rotation": 12, "relative_linear/rotation": 24, "episode_sums": 4 * (n_terms + 3),
-              "command_sums": 4 * (n_terms + 5), "curr_pose_index": 8, "collision_count": 8, "arrow root row": 28}
+             "trajectory row": 24, "terrain origin + tile id": 16, "heights": 4 * n_heights}
+    writes = {"arrow root row": 28}
+    torque_shift = 0
+    for name, role in cconfig.POST_PHYSICS_TRAFFIC.items():
+        b = per_env[name]                       # KeyError / None here = the table went out of sync with state_spec
+        if b is None:
+            raise KeyError(name)
+        if name == "command_sums":
+            b += 16                             # SURVEY counts 15 rows: the reference keeps 4 more per-command sums than the fused path
+        if role == "rw_row1":                   # base_rotation: the previous pitch is read (4 B), the row is written
+            reads[name] = 4
+            writes[name] = b
+        elif role == "torque_w":
+            torque_shift += b
+        else:
+            if "r" in role:
+                reads[name] = b
+            if "w" in role:
+                writes[name] = b
     if H > 1:
         reads["obs_history shift"] = 4 * flat["num_obs"] * (H - 1)
-    post = sum(reads.values()) + sum(writes.values())
+    post = sum(reads.values()) + sum(writes.values()) + torque_shift
     torque = (8 * nd + 4 * nd + 4 * nd + 8 * nd + 16 * nd) + (4 * nd + 4 * nd + 16 * nd + 4 * nd)      # SURVEY 8a row a3
-    return {"post_physics": post, "post_physics_reads": reads, "post_physics_writes": writes, "torque_substep": torque,
+    return {"post_physics": post, "post_physics_reads": reads, "post_physics_writes": writes,
+            "post_physics_in_torque_kernel": torque_shift, "torque_substep": torque,
             "full_step": post + flat["decimation"] * torque,
             "torque_flops_substep": nd * 2 * (6 * 32 + 32 * 32 + 32)}

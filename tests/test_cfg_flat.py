@@ -58,3 +58,22 @@ def test_reference_cfg_object_is_accepted_unchanged():
     ref = load_fixture(name)["flat"]
     Cfg, _ = ref_harness.build_cfg(fx["argv"], ref["num_envs"], fx.get("num_rows"), fx.get("num_cols"), fx.get("overrides"))
     assert diff(ltcfg.flat_from_cfg(Cfg), ref) == []
+
+
+def test_algorithmic_bytes_are_derived_from_the_buffer_list_and_match_the_survey():
+    """1,516 B read + 2,605 B written = 4,121 B per env-step (post-physics), 816 B per torque sub-step,
+    7,385 B per full step at cfg 2 / 5.  The figure is computed from cconfig.state_spec's shapes, so it moves when a buffer does."""
+    from legged_tracking_b200 import cconfig, cfg, workload
+    flat = cfg.flat_from_cfg(cfg.preset_cfg("cfg2_single_path_64", num_envs=4096), num_envs=4096)
+    a = workload.algorithmic_bytes(flat)
+    assert sum(a["post_physics_reads"].values()) == 1516
+    assert sum(a["post_physics_writes"].values()) + a["post_physics_in_torque_kernel"] == 2605
+    assert (a["post_physics"], a["torque_substep"], a["full_step"]) == (4121, 816, 7385)
+    names = {n for n, _, _ in cconfig.state_spec(flat)}
+    assert set(cconfig.POST_PHYSICS_TRAFFIC) <= names
+    # drift: a wider observation row or one more reward term must move the figure
+    wider = dict(flat, num_obs=flat["num_obs"] + 1)
+    assert workload.algorithmic_bytes(wider)["post_physics"] == 4121 + 8
+    # H > 1: the history shift is read + the whole history row written (SURVEY 8d, cfg 4 remark)
+    h3 = dict(flat, obs_history_length=3)
+    assert workload.algorithmic_bytes(h3)["post_physics"] == 4121 + 2 * 4 * flat["num_obs"] * 2
