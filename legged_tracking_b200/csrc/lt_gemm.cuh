@@ -44,6 +44,8 @@ enum { ACT_ELU = 0, ACT_SELU = 1, ACT_RELU = 2, ACT_LRELU = 3, ACT_TANH = 4, ACT
 
 struct Params {
     CUtensorMap tma_a, tma_b;            // 3-D maps {k, row, plane}; box {64, 128, 2} / {64, bn, 2}; SWIZZLE_128B; zero OOB fill
+    CUtensorMap tma_out;                 // EPI_ELU / EPI_BWD output planes {col, row, plane}; box {32, 32, 2}; SWIZZLE_64B (store)
+    int32_t use_tma_out;
     int32_t M, N, K;
     int32_t bn;                          // N tile = UMMA N (multiple of 16, <= BN_MAX)
     int32_t splits, kb_per_split;        // split-K: k-blocks [s * kb_per_split, (s+1) * kb_per_split) go to partial s
@@ -91,6 +93,16 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
                  "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
                  : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int32_t c0, int32_t c1, int32_t c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(reinterpret_cast<uint64_t>(map)),
+                 "r"(src), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -196,7 +208,9 @@ struct Smem {
     static constexpr uint32_t A_BYTES = 2u * BM * BK * 2u;           // both planes of the A box
     static constexpr uint32_t B_BYTES = 2u * BN_MAX * BK * 2u;
     static constexpr uint32_t STAGE = A_BYTES + B_BYTES;
-    static constexpr uint32_t BARS = STAGES * STAGE;                 // full[STAGES] empty[STAGES] tfull[2] tempty[2] tmem slot
+    static constexpr uint32_t OUT = STAGES * STAGE;                  // epilogue staging: per warp [2 planes][32 rows][64 B], 64B-swizzled
+    static constexpr uint32_t OUT_WARP = 2u * 32u * 64u;
+    static constexpr uint32_t BARS = OUT + EPI_WARPS * OUT_WARP;     // full[STAGES] empty[STAGES] tfull[2] tempty[2] tmem slot
     static constexpr uint32_t TOTAL = BARS + (2 * STAGES + 4) * 8 + 16 + 1024;     // + alignment slack
 };
 
@@ -212,6 +226,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
     auto tempty = [&](int s) { return bars + 8u * (2 * STAGES + 2 + s); };
     constexpr uint32_t CHUNK = 2u * 64u * BK * 2u;                   // MN-major: one {64 mn, 64 k, 2 planes} box = 16 KB
     const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+    const uint32_t out_stage = base + S::OUT;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -404,7 +419,25 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
                         }
                         tile_amax = fmaxf(tile_amax, m * amax_scale);
                     }
-                    if (row_ok) {
+                    if (p.use_tma_out) {
+                        // stage this warp's [32 rows x 32 columns] x 2 planes in shared memory (64B swizzle: 16-byte chunk j of row r
+                        // sits at chunk j ^ ((r >> 1) & 3): conflict-free 16-byte stores) and hand it to the TMA: one bulk tensor
+                        // store per chunk instead of 8 row-per-lane store instructions of 32 cache lines each; rows / columns
+                        // beyond the matrix are clipped by the tensor map
+                        const uint32_t buf = out_stage + (uint32_t)(warp - 2) * S::OUT_WARP;
+                        if (lane == 0) tma_store_wait_read();                      // the previous chunk's store has read the buffer
+                        __syncwarp();
+                        const uint32_t rowb = buf + (uint32_t)lane * 64u, sw = (uint32_t)((lane >> 1) & 3);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t o = (((uint32_t)j ^ sw) << 4);
+                            st_shared_v4(rowb + o, hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+                            st_shared_v4(rowb + 2048u + o, lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                        }
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) tma_store_3d(&p.tma_out, buf, col0, m_blk * BM + q * 32, 0);
+                    } else if (row_ok) {
                         uint4* oh = reinterpret_cast<uint4*>(p.out_h + (int64_t)row * p.ld_h + col0);
                         uint4* ol = reinterpret_cast<uint4*>(p.out_h + p.plane_h + (int64_t)row * p.ld_h + col0);
 #pragma unroll
@@ -512,6 +545,7 @@ __global__ void __launch_bounds__(THREADS, 1) lt_gemm_kernel(const __grid_consta
             }
         }
     }
+    if (warp >= 2 && lane == 0 && p.use_tma_out) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // stores complete before exit
     fence_before();
     __syncthreads();
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(2 * BN_MAX) : "memory");
@@ -555,6 +589,18 @@ inline bool make_operand_map_mn(CUtensorMap* map, const __half* base, int64_t ro
     const cuuint32_t estr[3] = {1, 1, 1};
     return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// output planes [2][rows][ld] fp16: store map {col, row, plane}, box {32, 32, 2}, SWIZZLE_64B
+inline bool make_out_map(CUtensorMap* map, __half* base, int64_t rows, int64_t cols, int64_t ld, int64_t plane) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, 2};
+    const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane * 2};
+    const cuuint32_t box[3] = {32, 32, 2};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 template <int BN_MAX, int STAGES>

@@ -20,6 +20,7 @@
 // 2^ceil(log2(rows)) to measure).  No host synchronisation anywhere.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -556,6 +557,10 @@ int run_gemm(lt_policy* P, const Operand& A, int M, const Operand& B, int N, int
     if (!ltg::make_operand_map(&p.tma_a, A.base, M, K, A.ld, A.plane, ltg::BM) ||
         !ltg::make_operand_map(&p.tma_b, B.base, N, K, B.ld, B.plane, p.bn))
         return fail(P, LT_ERR_CUDA, "cuTensorMapEncodeTiled failed (driver entry point missing or bad operand geometry)");
+    p.use_tma_out = 0;
+    if ((p.mode == ltg::EPI_ELU || p.mode == ltg::EPI_BWD) && p.out_h && (p.ld_h & 7) == 0 && (p.plane_h & 7) == 0 &&
+        (reinterpret_cast<uintptr_t>(p.out_h) & 15) == 0 && !getenv("LT_GEMM_NO_TMA_STORE"))
+        p.use_tma_out = ltg::make_out_map(&p.tma_out, p.out_h, M, N, p.ld_h, p.plane_h) ? 1 : 0;
     LTP_CUDA(P, ltg::launch(p, P ? P->sm_count : 148, stream));
     return LT_OK;
 }

@@ -1,4 +1,5 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_step.py tests/test_gpu_pipeline.py tests/test_gpu_terrain.py tests/test_gpu_env.py -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-timeout 600 python bench.py --steps 200 --warmup 5 > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; echo "rc=$?" >> gpurun_out/bench_1gpu.err
+timeout 600 python -m pytest tests/test_gpu_policy.py tests/test_gpu_ppo.py tests/test_zz_no_alloc.py -m gpu -q -x > gpurun_out/pytest_policy.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_policy.log
+timeout 300 python profiles/run_ppo.py --reps 2 > gpurun_out/run_ppo.log 2>&1
+LT_GEMM_NO_TMA_STORE=1 timeout 300 python profiles/run_ppo.py --reps 2 > gpurun_out/run_ppo_nostore.log 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum --clock-control none -c 600 --csv --log-file gpurun_out/ppo_launches.csv python profiles/run_ppo.py --acts 1 > gpurun_out/ncu_ppo.log 2>&1
