@@ -345,6 +345,51 @@ def api_step_timing(args, dev, n_env, steps):
     return out
 
 
+def rollout_kernel_timing(flat, dev, n_env, peak):
+    """lt_rollout_store (observation third of a transition + the env third), lt_gae + lt_normalize_advantages, timed alone with
+    CUDA events (20 launches each, inputs larger than L2 across the loop: 24 different rows of the [T, N, *] buffers)."""
+    import ctypes as C
+    from legged_tracking_b200 import _abi, ppo
+    no, npv, H, na = flat["num_obs"], flat["num_privileged_obs"], flat["obs_history_length"], flat["num_actions"]
+    T = ppo.RunnerArgs.num_steps_per_env
+    st = ppo.RolloutStorage(n_env, T, [no], [npv], [no * H], [na], device=dev)
+    g = torch.Generator(device=dev).manual_seed(3)
+    tr = ppo.RolloutStorage.Transition()
+    tr.observations = torch.randn(n_env, no, device=dev, generator=g)
+    tr.privileged_observations = torch.randn(n_env, npv, device=dev, generator=g)
+    tr.observation_histories = torch.randn(n_env, no * H, device=dev, generator=g)
+    tr.rewards = torch.randn(n_env, device=dev, generator=g)
+    tr.dones = torch.rand(n_env, device=dev, generator=g) < 0.05
+    tr.time_outs = tr.dones.clone()
+    st.values.normal_(generator=g)
+    st.rewards.normal_(generator=g)
+
+    def store(k):
+        st.step = k % T
+        tr.values = st.values[st.step]
+        st.store_observations(tr)
+        st.store_env_step(tr)
+    store(0)
+    ms_store = time_region(store, T) / T
+    last = torch.randn(n_env, 1, device=dev, generator=g)
+
+    def gae(k):
+        st.compute_returns(last, 0.99, 0.95)
+    gae(0)
+    ms_gae = time_region(gae, 10) / 10
+    b_store = 4 * (no + npv + no * H) * 2 + (4 + 4 + 1 + 1 + 4 + 1)            # read + write of the copied rows; rewards / values / masks
+    b_gae = T * (4 + 4 + 1 + 4 + 4) + T * 8                                      # lt_gae: r, V, done read; R, A written; normalise: A read + written
+    out = {}
+    for name, ms, b, what in (("rollout_store", ms_store, b_store, "lt_rollout_store_kernel x2 (observation rows at act(), rewards / dones after the step)"),
+                              ("gae", ms_gae, b_gae, "lt_gae_kernel + lt_normalize_kernel over [24, N]")):
+        ach = b * n_env / (ms * 1e-3) / 1e9
+        out[name] = {"kernel": what, "ms_per_launch": ms, "achieved": ach, "bound": "hbm", "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                     "algorithmic_bytes_per_env": b}
+    del st
+    torch.cuda.empty_cache()
+    return out
+
+
 def terrain_build_timing(dev):
     """the 32 x 32 single_path tile table built on the device (the reference: a 3.8 s Python loop)."""
     from legged_tracking_b200 import cfg as ltcfg
@@ -619,6 +664,11 @@ def run_b200(args, rank, world, local_rank):
                 "kernels": {"post_physics": k_post, "torque_substep": k_tq},
                 "share_of_step": {"torque_x%d" % flat["decimation"]: torque_total / (torque_total + ms_post),
                                   "post_physics": ms_post / (torque_total + ms_post)}}
+    if world == 1:
+        try:
+            roofline["kernels"].update(rollout_kernel_timing(flat, dev, n_env, peak))
+        except Exception as e:
+            roofline["kernels"]["rollout_store"] = {"error": str(e)[:300]}
     cpu = None
     if world == 1 and not args.no_cpu:
         from oracle import ref_arm

@@ -290,6 +290,29 @@ int lt_build_tunnel_tiles(const int32_t* n_pyramids, const double* wedges, const
                           const double* ys, const double* consts, float* tile_heights, int32_t n_tiles, int32_t tile_rows,
                           int32_t tile_cols, int32_t sub_rows, int32_t sub_cols, void* stream);
 
+/* sampling-based local planner, LeggedRobot._plan_target_pose with cfg.commands.sampling_based_planning
+ * (legged_robot_trajectory_tracking.py:856-916) and the relative pose of the resulting local target (:914-916, 922-932).
+ * The reference runs a Python loop over the planning envs; this is one CTA per env, threads over the candidate poses.
+ *   target_poses      [N,6]  world-frame goal = trajectories[env, curr_pose_index]
+ *   root_states       robot root row of env e at root_states + e * root_stride (Isaac Gym layout: pos3, quat xyzw4, ...)
+ *   points_xy         [n_points,2] base-frame sample offsets (_init_height_points, :1902-1916; 21 x 11 = 231)
+ *   measured_heights  [N,2,n_points] ceiling / floor heights of _get_heights (:1918-1965) from the previous step
+ *   candidates        [n_cands,6] cfg.commands.candidate_target_poses as float32 (config :167-175; 1,125 poses)
+ *   episode_length_buf, plan_buf [N]: inputs of the replan rule (:858-868); plan_length_buf [N] is advanced / cleared in place
+ *   local_target_poses [N,6] in / out (envs that do not plan keep theirs); local_relative_linear / rotation [N,3] out (may be
+ *   NULL); chosen [N] out (may be NULL): winning candidate index, -1 no valid candidate (global goal used), -2 close to the goal,
+ *   -3 no plan this step.  Ties between equal sort keys go to the lower candidate index (a stable argsort). */
+typedef struct lt_plan_args {
+    const float *target_poses, *root_states, *points_xy, *measured_heights, *candidates;
+    const int64_t* episode_length_buf;
+    const uint8_t* plan_buf;
+    int64_t* plan_length_buf;
+    float *local_target_poses, *local_relative_linear, *local_relative_rotation;
+    int32_t* chosen;
+} lt_plan_args;
+int lt_plan_target_pose(const lt_plan_args* args, int32_t num_envs, int32_t n_points, int32_t n_cands, int32_t plan_interval,
+                        int32_t root_stride, const float* robot_size, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

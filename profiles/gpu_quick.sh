@@ -1,5 +1,2 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_policy.py tests/test_gpu_ppo.py tests/test_zz_no_alloc.py -m gpu -q -x > gpurun_out/pytest_policy.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_policy.log
-timeout 300 python profiles/run_ppo.py --reps 2 > gpurun_out/run_ppo.log 2>&1
-LT_GEMM_NO_TMA_STORE=1 timeout 300 python profiles/run_ppo.py --reps 2 > gpurun_out/run_ppo_nostore.log 2>&1
-timeout 600 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum --clock-control none -c 600 --csv --log-file gpurun_out/ppo_launches.csv python profiles/run_ppo.py --acts 1 > gpurun_out/ncu_ppo.log 2>&1
+timeout 600 python -m pytest tests/test_planner.py tests/test_abi.py -q > gpurun_out/pytest_planner.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_planner.log

@@ -16,7 +16,7 @@ ATOL = 2e-6
 
 def fixture_names():
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_")))
+                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_", "planner_")))
 
 
 def load_fixture(name):
