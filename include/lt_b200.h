@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LT_ABI_VERSION 5
+#define LT_ABI_VERSION 6
 
 #define LT_MAX_DOF 12
 #define LT_MAX_FEET 4
@@ -180,6 +180,9 @@ typedef struct lt_step_args {
     const float* noise_uniforms;     /* [N, num_obs] or NULL -> in-kernel Philox (only read if add_noise) */
     const float* new_gravity;        /* HOST float[3] or NULL: _randomize_gravity fired this step (LR:645-660): written
                                         to `gravities` before the observations are assembled */
+    /* sampling-based planning (LR:856-916): this step's local target and its relative pose, as lt_plan_target_pose left them
+     * ([N,6], [N,3], [N,3]); all three NULL = the local target is the global one (LR:917-920) */
+    const float *local_target_poses, *local_relative_linear, *local_relative_rotation;
 } lt_step_args;
 
 typedef struct lt_handle lt_handle;
@@ -289,6 +292,12 @@ int lt_normalize_advantages(float* advantages, const double* stats, int64_t coun
 int lt_build_tunnel_tiles(const int32_t* n_pyramids, const double* wedges, const int32_t* window, const double* xs,
                           const double* ys, const double* consts, float* tile_heights, int32_t n_tiles, int32_t tile_rows,
                           int32_t tile_cols, int32_t sub_rows, int32_t sub_cols, void* stream);
+
+/* _get_heights over the FULL measured_points grid (LR:1918-1965; the observation path gathers the front half only): out
+ * [N, 2, n_points_x * n_points_y] ceiling / floor heights in metres from the bound terrain, the robot root rows of the bound
+ * simulator tensors and the PREVIOUS step's pitch (state base_rotation, LR:1938: the camera offset uses the not yet refreshed
+ * rotation).  Input of lt_plan_target_pose; call it before lt_post_physics_step of the same step. */
+int lt_measure_heights(lt_handle* h, float* out, void* stream);
 
 /* sampling-based local planner, LeggedRobot._plan_target_pose with cfg.commands.sampling_based_planning
  * (legged_robot_trajectory_tracking.py:856-916) and the relative pose of the resulting local target (:914-916, 922-932).

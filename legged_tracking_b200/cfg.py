@@ -250,6 +250,9 @@ def flat_from_cfg(cfg, model=Go1Model, sim_dt=None, num_envs=None, extra_reward_
                                                      "yaw_range", "switch_dist", "switch_yaw", "switch_interval")},
         switch_upon_reach=bool(c.commands.switch_upon_reach),
         sampling_based_planning=bool(c.commands.sampling_based_planning), global_reference=bool(c.commands.global_reference),
+        plan_interval=int(getattr(c.commands, "plan_interval", 10)),
+        candidate_target_poses=[[float(v) for v in row] for row in np.asarray(getattr(c.commands, "candidate_target_poses", np.zeros((0, 6)))).reshape(-1, 6)]
+        if c.commands.sampling_based_planning else [],
         max_episode_length=max_episode_length,
         use_terminal_body_height=bool(c.rewards.use_terminal_body_height), terminal_body_height=float(c.rewards.terminal_body_height),
         terminate_end_of_trajectory=bool(c.env.terminate_end_of_trajectory), T_reach=float(g(c.rewards, "T_reach", 0)),

@@ -818,10 +818,18 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     for (int k = 0; k < 6; ++k) st.target_poses[(size_t)i * 6 + k] = P.target[k];
     float loc_lin[3] = {P.rel_lin[0], P.rel_lin[1], P.rel_lin[2]};     // local_* = same pose (LR:917-920)
     float loc_rot[3] = {P.rel_rot[0], P.rel_rot[1], P.rel_rot[2]};
-    // goal arrow actor (LR:934-947)
+    const float* local_target = P.target;
+    if (args.local_relative_linear) {                                  // sampling-based planning: lt_plan_target_pose ran first (LR:856-916)
+        for (int k = 0; k < 3; ++k) {
+            loc_lin[k] = args.local_relative_linear[(size_t)i * 3 + k];
+            loc_rot[k] = args.local_relative_rotation[(size_t)i * 3 + k];
+        }
+        local_target = args.local_target_poses + (size_t)i * 6;
+    }
+    // goal arrow actor (LR:800, 934-947): shows the LOCAL target
     if (R.arrow) {
-        R.arrow[0] = P.target[0]; R.arrow[1] = P.target[1]; R.arrow[2] = P.target[2];
-        lt_quat_from_euler(P.target[3], P.target[4], P.target[5], R.arrow + 3);
+        R.arrow[0] = local_target[0]; R.arrow[1] = local_target[1]; R.arrow[2] = local_target[2];
+        lt_quat_from_euler(local_target[3], local_target[4], local_target[5], R.arrow + 3);
     }
     // ---- interval domain randomisation (LR:822-824)
     if (ep % (int64_t)c.rand_interval == 0) lt_randomize_dof_props(c, st, i, U, LT_SLOT_INTERVAL_STRENGTH);

@@ -1166,6 +1166,11 @@ static void lt_fill_step_params(lt_handle* h, const lt_step_args* args, lt_step_
         p.args.extra_reward = args->extra_reward;
         p.args.uniforms = args->uniforms;
         p.args.noise_uniforms = args->noise_uniforms;
+        if (args->local_relative_linear && args->local_relative_rotation && args->local_target_poses) {
+            p.args.local_target_poses = args->local_target_poses;
+            p.args.local_relative_linear = args->local_relative_linear;
+            p.args.local_relative_rotation = args->local_relative_rotation;
+        }
         if (args->new_gravity) {
             p.sc.set_gravity = 1;
             for (int k = 0; k < 3; ++k) p.sc.new_gravity[k] = args->new_gravity[k];
@@ -1176,6 +1181,58 @@ static void lt_fill_step_params(lt_handle* h, const lt_step_args* args, lt_step_
     p.counters = h->d_counters;
     p.scratch = h->d_scratch;
     p.rec_bytes = h->rec_bytes;
+}
+
+// _get_heights over the full measured_points grid (LR:1918-1965): thread per (env, point); same index arithmetic as the
+// observation path (lt_env_step: float32 add, subtract, DIVIDE by the cell size, truncate, clamp to [0, cells - 2])
+struct lt_heights_params {
+    lt_config c;
+    lt_terrain_ptrs ter;
+    const float* root_states;
+    const float* base_rotation;
+    float* out;
+};
+__global__ void __launch_bounds__(256) lt_heights_kernel(const __grid_constant__ lt_heights_params p) {
+    const lt_config& c = p.c;
+    const int np = c.n_points_x * c.n_points_y;
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= (int64_t)c.num_envs * np) return;
+    const int i = (int)(q / np), pt = (int)(q % np), a = pt / c.n_points_y, b = pt % c.n_points_y;
+    float* o = p.out + (size_t)i * 2 * np;
+    if (c.plane) { o[pt] = 1.0f; o[np + pt] = 0.0f; return; }          // LR:1928-1932
+    const float* root = p.root_states + (size_t)i * c.num_actors * 13;
+    float offx = 0.0f, offy = 0.0f;
+    if (c.camera_zero) {
+        const float cp = cosf(p.base_rotation[(size_t)i * 3 + 1]);
+        offx = LT_FMUL(c.camera_offset[0], cp);
+        offy = LT_FMUL(c.camera_offset[1], cp);
+    }
+    float px = LT_FADD(c.points_x[a], root[0]), py = LT_FADD(c.points_y[b], root[1]);
+    if (c.camera_zero) { px = LT_FADD(px, offx); py = LT_FADD(py, offy); }
+    px = LT_FDIV(LT_FSUB(px, p.ter.env_terrain_origin[(size_t)i * 3 + 0]), c.horizontal_scale);
+    py = LT_FDIV(LT_FSUB(py, p.ter.env_terrain_origin[(size_t)i * 3 + 1]), c.horizontal_scale);
+    int ix = (int)px, iy = (int)py;
+    ix = ix < 0 ? 0 : (ix > c.tile_rows - 2 ? c.tile_rows - 2 : ix);
+    iy = iy < 0 ? 0 : (iy > c.tile_cols - 2 ? c.tile_cols - 2 : iy);
+    const size_t cells = (size_t)c.tile_rows * c.tile_cols;
+    const float* tile = p.ter.tile_heights + (size_t)p.ter.env_tile[i] * 2 * cells;
+    o[pt] = tile[(size_t)ix * c.tile_cols + iy];
+    o[np + pt] = tile[cells + (size_t)ix * c.tile_cols + iy];
+}
+
+int lt_measure_heights(lt_handle* h, float* out, void* stream) {
+    const int rc = lt_ready(h);
+    if (rc) return rc;
+    if (!out) return lt_fail(h, LT_ERR_INVALID, "lt_measure_heights: out is NULL");
+    lt_heights_params p;
+    p.c = h->c;
+    p.ter = h->ter;
+    p.root_states = h->sim.root_states;
+    p.base_rotation = h->st.base_rotation;
+    p.out = out;
+    const int64_t n = (int64_t)h->c.num_envs * h->c.n_points_x * h->c.n_points_y;
+    lt_heights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p);
+    return cudaGetLastError() == cudaSuccess ? LT_OK : lt_fail(h, LT_ERR_CUDA, "lt_heights_kernel launch failed");
 }
 
 int lt_reward_sign_prepass(lt_handle* h, const lt_step_args* args, void* stream) {

@@ -163,6 +163,15 @@ class StepEngine:
         _abi.check(self.lib.lt_bind_state(self.handle, C.byref(ptrs)), self.handle, "lt_bind_state")
         self._ptrs = ptrs
         self.counters = self._wrap_i32(self.lib.lt_counters(self.handle), 4)
+        self.planner = None
+        if flat.get("sampling_based_planning"):
+            from .planner import LocalPlanner
+            px, py = np.asarray(flat["measured_points_x"], np.float32), np.asarray(flat["measured_points_y"], np.float32)
+            gx, gy = np.meshgrid(px, py, indexing="ij")                                        # _init_height_points, LR:1902-1916
+            self.planner = LocalPlanner(N, np.stack([gx.reshape(-1), gy.reshape(-1)], axis=1), flat["candidate_target_poses"],
+                                        plan_interval=flat.get("plan_interval", 10), num_actors=flat["num_actors"], device=dev)
+            self.measured_heights = torch.zeros(N, 2, px.size * py.size, device=dev)
+            self._arange = torch.arange(N, device=dev)
         self.gravity = GravitySchedule(flat)
         self.curriculum = ExplorationCurriculum(flat)
         self.reward_names = list(flat["reward_names"])
@@ -261,6 +270,8 @@ class StepEngine:
                     tns = tns.view(1, -1)
                 assert tns.is_cuda and tns.dtype == torch.float32 and tns.is_contiguous() and tuple(tns.shape) == shape, name
                 setattr(args, name, tns.data_ptr())
+        if self.planner is not None:
+            self._plan(args, stream)
         new_g = None
         if advance_gravity:
             draw = (lambda: gravity_uniform) if gravity_uniform is not None else (lambda: torch.rand(3))
@@ -283,6 +294,22 @@ class StepEngine:
         if advance_gravity and self.curriculum.advance(self.gravity.common_step_counter):
             self.set_reward_scales(self.curriculum.term_scales())
             self._scales_changed = True           # graphs captured before this point hold stale scales (graph_replay_ok)
+
+    def _plan(self, args, stream):
+        """Sampling-based planning (LR:786-799, 856-916) ahead of the fused step: full-grid heights (lt_measure_heights), the planner
+        kernel (lt_plan_target_pose), and this step's local target handed to lt_post_physics_step through lt_step_args."""
+        st, pl = self.state, self.planner
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(s):
+            _abi.check(self.lib.lt_measure_heights(self.handle, C.c_void_p(self.measured_heights.data_ptr()), C.c_void_p(s.cuda_stream)),
+                       self.handle, "lt_measure_heights")
+            target = st["trajectories"][self._arange, st["curr_pose_index"]].contiguous()        # LR:854
+            ep = st["episode_length_buf"] + 1                                                  # LR:126 precedes the callback
+            pl.plan(target, self.root_states, self.measured_heights, ep, st["plan_buf"].view(torch.uint8), stream=s)
+        self._plan_keep = (target, ep)
+        args.local_target_poses = pl.local_target_poses.data_ptr()
+        args.local_relative_linear = pl.local_relative_linear.data_ptr()
+        args.local_relative_rotation = pl.local_relative_rotation.data_ptr()
 
     def graph_replay_ok(self):
         """May the NEXT step be a replay of a CUDA graph captured from post_physics_step(advance_gravity=False)?  A captured
@@ -357,6 +384,11 @@ class StepEngine:
             self.gravity.gravities = torch.as_tensor(np.asarray(st["gravities"]), dtype=torch.float32).reshape(-1, 3)[0].clone()
         if "common_step_counter" in st:
             self.gravity.common_step_counter = int(st["common_step_counter"])
+        if self.planner is not None:
+            if "plan_length_buf" in st:
+                put(self.planner.plan_length_buf, st["plan_length_buf"])
+            if "local_target_poses" in st:
+                put(self.planner.local_target_poses, st["local_target_poses"])
 
     def export_state(self):
         out = {k: v.detach().cpu() for k, v in self.state.items()
@@ -370,6 +402,9 @@ class StepEngine:
             for r, name in enumerate(self.reward_names + ["ep_timesteps"]):
                 out["command_sums/" + name] = self.state["command_sums"][r].cpu()
         out["common_step_counter"] = torch.tensor(self.gravity.common_step_counter)
+        if self.planner is not None:
+            out["plan_length_buf"] = self.planner.plan_length_buf.cpu()
+            out["local_target_poses"] = self.planner.local_target_poses.cpu()
         return out
 
 

@@ -257,6 +257,11 @@ class LeggedRobot:
                 return st[name]
             if name in LeggedRobot._ALIASES:
                 return st[LeggedRobot._ALIASES[name]]
+            pl = getattr(eng, "planner", None)              # sampling-based planning state (LR:1212-1214, 1263)
+            if pl is not None and name in ("local_target_poses", "plan_length_buf"):
+                return getattr(pl, name)
+            if pl is not None and name == "measured_heights":
+                return eng.measured_heights.view(eng.N, 2, len(eng.flat["measured_points_x"]), len(eng.flat["measured_points_y"]))
         raise AttributeError(name)
 
     def __setattr__(self, name, value):

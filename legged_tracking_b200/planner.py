@@ -2,9 +2,12 @@
 cfg.commands.sampling_based_planning (go1_gym/envs/base/legged_robot_trajectory_tracking.py:850-920) as ONE kernel launch
 (lt_plan_target_pose, csrc/lt_planner.cu) instead of a Python loop over the planning envs.  CUDA only.
 
-Not yet wired into StepEngine: the fused step kernel still takes local target = global target (the non-planning branch, LR:917-920),
-and the full 2 x 21 x 11 measured_heights grid the planner reads is not kept by the observation kernel (it gathers the front half
-only).  flatcfg.check_supported therefore still rejects sampling_based_planning for the fused env; this class is the planner alone.
+engine.StepEngine creates one when the flat config has sampling_based_planning (cfg.commands.sampling_based_planning with its
+candidate table): per step lt_measure_heights (the full 2 x 21 x 11 grid of _get_heights, LR:786-787) -> LocalPlanner.plan ->
+lt_post_physics_step, which takes this step's local target and its relative pose through lt_step_args (commands, rewards, plan_buf
+and the goal arrow then follow the LOCAL target as in the reference, LR:800-802, 845-847).  Ties between equal sort keys (the key
+ignores the candidate's z) go to the lowest candidate index; the reference's torch.argsort leaves that order to its sort
+implementation, so a tied pick can differ from the reference in the local target's z (tests/test_planner.py).
 """
 import ctypes as C
 

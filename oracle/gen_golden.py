@@ -60,6 +60,9 @@ def snapshot(env, wrapped, prefix, out):
     out[prefix + "gravity_vec"] = env.gravity_vec[0].numpy().copy()
     out[prefix + "obs_history"] = wrapped.obs_history.numpy().copy()
     out[prefix + "common_step_counter"] = np.int64(env.common_step_counter)
+    if getattr(env.cfg.commands, "sampling_based_planning", False):
+        out[prefix + "plan_length_buf"] = env.plan_length_buf.numpy().astype(np.int64).copy()
+        out[prefix + "local_target_poses"] = env.local_target_poses.detach().float().numpy().copy()
     for k, v in env.episode_sums.items():
         out[prefix + "episode_sums/" + k] = v.numpy().copy()
     for k, v in env.command_sums.items():
@@ -218,7 +221,7 @@ def actuator_from_reference():
 
 
 def record_run(argv, num_envs, num_rows=None, num_cols=None, steps=6, overrides=None, synth_seed=1000,
-               full_state_every=2, near_timeout_frac=0.3, start_counter=0, synth_kwargs=None):
+               full_state_every=2, near_timeout_frac=0.3, start_counter=0, synth_kwargs=None, init_hook=None):
     """Run the reference for `steps` policy steps; return the fixture dict (numpy arrays + 'flat' JSON string)."""
     import isaacgym.gymapi as gymapi
     wrapped, env, replay, Cfg, args = H.make_env(argv, num_envs, num_rows, num_cols, synth_seed=synth_seed,
@@ -254,6 +257,8 @@ def record_run(argv, num_envs, num_rows=None, num_cols=None, steps=6, overrides=
             ep[1::16] = ri - 1 - (torch.arange(len(ep[1::16])) % 3)      # interval-DR (LR:822-824) fires in-fixture
             env.episode_length_buf[:] = ep
             env.common_step_counter = int(start_counter)
+            if init_hook is not None:
+                init_hook(env)
             rng.take()
             # start the interval-DR clock where it will fire for a few envs too
             flat = H.flat_from_reference_env(env)
@@ -299,6 +304,13 @@ def record_run(argv, num_envs, num_rows=None, num_cols=None, steps=6, overrides=
         LRmod.stack_heights = orig_stack
         gymapi.acquire_gym().set_replay(None)
     return fx
+
+
+def _planning_init(env):
+    """Start the planning recording where the replan rule fires (LR:861-865): every env believes it reached its local target, and
+    the interval counters sit at 7..9, so that the first three steps run the candidate search for a third of the envs each."""
+    env.plan_buf = torch.ones(env.num_envs, dtype=torch.long)
+    env.plan_length_buf = 7 + (torch.arange(env.num_envs) % 3)
 
 
 COMMON = ["--old_ppo", "--measure_front_half"]
@@ -376,6 +388,11 @@ FIXTURES = {
     # option coverage 2: random_goal trajectories (trajectory_function.py:28-40), the PD controller instead of the
     # actuator net (LR:989-991) with Kp/Kd factor randomisation, termination on body rotation (LR:215-216), the ji22
     # reward combination on the crawling container
+    # sampling-based local planner inside the env step (LR:856-916): every env plans at its first step and on the
+    # 10-step interval; the tunnel's hanging / standing wedges invalidate part of the 1,575 candidate poses
+    "planning_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path", "--penalty_scaler", "1.0"],
+                        num_envs=32, num_rows=4, num_cols=4, steps=12, full_state_every=1, near_timeout_frac=0.7,
+                        overrides={"commands.sampling_based_planning": True}, init_hook=_planning_init),
     "opts_random_goal_P_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path"],
                                   num_envs=32, num_rows=4, num_cols=4, steps=6, synth_kwargs={"rp_range": 1.9},
                                   overrides={"commands.traj_function": "random_goal", "commands.x_mean": 1.5,

@@ -226,6 +226,9 @@ class OraclePort:
         self.privileged_obs_buf = torch.zeros(N, f["num_privileged_obs"])
         self.obs_history = torch.zeros(N, f["num_obs"] * f["obs_history_length"])
         self.measured_heights = None
+        self.plan_length_buf = torch.zeros(N, dtype=torch.long)               # LR:1214
+        self.planned_target_poses = torch.zeros(N, 6)                         # local_target_poses, LR:1263
+        self.planner_stable = False    # False = the reference's torch.argsort (unstable ties); True = the kernel's lowest-index rule
         self.finished_episodes = []     # per step: dict(env_ids, sums...) -- what the reference pushes into extras deques
 
     # ------------------------------------------------------------------ state import / export
@@ -240,6 +243,8 @@ class OraclePort:
         for k, v in self.command_sums.items():
             out["command_sums/" + k] = v.clone()
         out["common_step_counter"] = torch.tensor(self.common_step_counter)
+        out["plan_length_buf"] = self.plan_length_buf.clone()
+        out["local_target_poses"] = self.planned_target_poses.clone()
         return out
 
     def load_state(self, st):
@@ -257,6 +262,10 @@ class OraclePort:
                 self.command_sums[k].copy_(torch.as_tensor(st["command_sums/" + k]))
         if "common_step_counter" in st:
             self.common_step_counter = int(st["common_step_counter"])
+        if "plan_length_buf" in st:
+            self.plan_length_buf = torch.as_tensor(st["plan_length_buf"]).long().clone()
+        if "local_target_poses" in st:
+            self.planned_target_poses = torch.as_tensor(st["local_target_poses"]).float().clone()
 
     # ------------------------------------------------------------------ a3: torques
     def actuator_network(self, xs):
@@ -431,9 +440,22 @@ class OraclePort:
         idx = self.curr_pose_index
         self.target_poses = self.trajectories[torch.arange(self.N), idx, :]                 # LR:854
         self.relative_linear, self.relative_rotation = self.compute_relative_target_pose(self.target_poses)
-        self.local_target_poses = self.target_poses                                          # LR:918-920
-        self.local_relative_linear, self.local_relative_rotation = \
-            self.compute_relative_target_pose(self.local_target_poses)
+        if f.get("sampling_based_planning"):                                                 # LR:856-916
+            from oracle import planner_port
+            root = self.robot_root
+            out = planner_port.plan(self.target_poses, root[:, :3].clone(), root[:, 3:7].clone(), self.height_points[0].reshape(-1, 3)[:, :2],
+                                    self.measured_heights.reshape(self.N, 2, -1), torch.tensor(f["candidate_target_poses"], dtype=torch.float64),
+                                    self.episode_length_buf, self.plan_buf.long(), self.plan_length_buf, self.planned_target_poses,
+                                    plan_interval=int(f["plan_interval"]), stable=self.planner_stable)
+            self.plan_length_buf = out["plan_length_buf"]
+            self.planned_target_poses = out["local_target_poses"]
+            self.local_target_poses = self.planned_target_poses
+            self.local_relative_linear, self.local_relative_rotation = out["local_relative_linear"], out["local_relative_rotation"]
+            self.planner_chosen = out["chosen"]
+        else:
+            self.local_target_poses = self.target_poses                                      # LR:918-920
+            self.local_relative_linear, self.local_relative_rotation = \
+                self.compute_relative_target_pose(self.local_target_poses)
         # _set_the_target_pose_visual LR:934-947
         arrow = self.root_states.view(self.N, self.A, 13)[:, self.A - 1, :]
         arrow[:, :3] = self.local_target_poses[:, :3]

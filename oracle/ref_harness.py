@@ -259,6 +259,9 @@ def flat_from_reference_env(env):
         switch_upon_reach=bool(c.commands.switch_upon_reach), switch_dist=float(c.commands.switch_dist),
         switch_yaw=float(c.commands.switch_yaw), switch_interval=float(c.commands.switch_interval),
         sampling_based_planning=bool(c.commands.sampling_based_planning), global_reference=bool(c.commands.global_reference),
+        plan_interval=int(c.commands.plan_interval),
+        candidate_target_poses=[[float(v) for v in row] for row in np.asarray(c.commands.candidate_target_poses).reshape(-1, 6)]
+        if c.commands.sampling_based_planning else [],
         max_episode_length=float(env.max_episode_length),
         use_terminal_body_height=bool(c.rewards.use_terminal_body_height),
         terminal_body_height=float(c.rewards.terminal_body_height),

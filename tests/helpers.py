@@ -14,9 +14,12 @@ RTOL = 1e-5
 ATOL = 2e-6
 
 
-def fixture_names():
+def fixture_names(planning=False):
+    """Env-step fixtures.  planning=True adds the sampling-based-planning recording, which only the oracle / config tests and
+    tests/test_planner.py take: the per-env host mirror has no planner, and the CUDA planner resolves the reference's tied sort
+    keys by its own documented rule (tests/test_planner.py)."""
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_", "planner_")))
+                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_", "planner_") + (() if planning else ("planning_",))))
 
 
 def load_fixture(name):

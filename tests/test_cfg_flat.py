@@ -15,7 +15,7 @@ def diff(a, b):
     return sorted(k for k in set(a) | set(b) if a.get(k) != b.get(k))
 
 
-@pytest.mark.parametrize("name", fixture_names())
+@pytest.mark.parametrize("name", fixture_names(planning=True))
 def test_preset_flat_equals_reference_flat(name):
     ref = load_fixture(name)["flat"]
     c = ltcfg.preset_cfg(name, ref["num_envs"])

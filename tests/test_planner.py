@@ -107,3 +107,47 @@ def test_planner_kernel_matches_oracle_on_other_states(N, seed):
     assert np.array_equal(pl.chosen.cpu().numpy(), want["chosen"].numpy())
     for k in ("local_target_poses", "local_relative_linear", "local_relative_rotation"):
         np.testing.assert_allclose(getattr(pl, k).cpu().numpy(), want[k].numpy(), rtol=1e-5, atol=2e-6, err_msg=k)
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# the planner INSIDE the env step: tests/golden/planning_32.npz is 12 steps of the unmodified reference with
+# cfg.commands.sampling_based_planning = True (oracle/gen_golden.py); tests/test_oracle_golden.py pins the oracle to it bit for bit.
+@pytest.mark.gpu
+def test_env_step_with_planning_matches_the_oracle_and_the_reference():
+    """lt_measure_heights -> lt_plan_target_pose -> lt_post_physics_step (local target through lt_step_args) against the oracle
+    port run side by side with the kernel's tie rule (planner_stable), every step, every state array; and against the reference
+    recording itself on everything a tie cannot touch (a tie changes only the local target's z: observations, rewards, resets,
+    commands and every x / y / rotation entry are the reference's)."""
+    from legged_tracking_b200.engine import StepEngine
+    from tests import helpers as T
+    fx = T.load_fixture("planning_32")
+    eng = StepEngine(fx["flat"], T.sub(fx, "terrain/"), T.load_actuator(), device="cuda:0", export_height_indices=True)
+    eng.load_state(T.sub(fx, "init/"))
+    port = T.make_oracle(fx)
+    port.planner_stable = True
+    xp = lambda a: torch.as_tensor(a).cuda()        # noqa: E731
+    n_planned = 0
+    for k in range(T.num_steps(fx)):
+        inp = T.step_inputs(fx, k)
+        obs, priv, rew, reset = port.step(inp["actions"], inp["sim"], inp["uniforms"], inp["noise_uniforms"], inp["gravity_uniform"])
+        tq = T.engine_feed_and_step(eng, fx, k, xp)
+        torch.cuda.synchronize()
+        n_planned += int((port.planner_chosen >= 0).sum())
+        assert np.array_equal(eng.planner.chosen.cpu().numpy(), port.planner_chosen.numpy()), f"step{k}: chosen candidates"
+        want_port = {kk: v.numpy() for kk, v in port.export_state().items() if kk not in ("camera_pitch_angle",)}
+        want_port["gravity_vec"] = port.gravity_vec[0].numpy()
+        T.check_engine_state(eng, want_port, f"step{k}/vs_port")
+        st = eng.state
+        out = T.sub(fx, f"step{k}/out/")
+        T.assert_close(f"step{k}/done", T.to_np(st["reset_buf"]).astype(bool), out["done"])
+        T.assert_close(f"step{k}/reset_env_ids", T.to_np(eng.reset_env_ids()), out["reset_env_ids"])
+        T.assert_close(f"step{k}/rew", T.to_np(st["rew_buf"]), out["rew"])
+        T.assert_close(f"step{k}/obs", T.to_np(st["obs_buf"]), out["obs"])
+        T.assert_close(f"step{k}/all_torques", tq, out["all_torques"], atol=T.TORQUE_ATOL)
+        want = T.sub(fx, f"step{k}/out/state/")
+        T.assert_close(f"step{k}/plan_length_buf", T.to_np(eng.planner.plan_length_buf), want["plan_length_buf"])
+        T.assert_close(f"step{k}/local_target xy rpy", T.to_np(eng.planner.local_target_poses)[:, [0, 1, 3, 4, 5]], want["local_target_poses"][:, [0, 1, 3, 4, 5]])
+        T.assert_close(f"step{k}/local_relative_linear xy", T.to_np(st["local_relative_linear"])[:, :2], want["local_relative_linear"][:, :2])
+        T.assert_close(f"step{k}/local_relative_rotation", T.to_np(st["local_relative_rotation"]), want["local_relative_rotation"])
+        T.assert_close(f"step{k}/plan_buf", T.to_np(st["plan_buf"]).astype(bool), want["plan_buf"].astype(bool))
+    assert n_planned >= 10           # the recording does exercise the candidate search (17 searches, 10 close-to-goal plans)
