@@ -322,6 +322,68 @@ typedef struct lt_plan_args {
 int lt_plan_target_pose(const lt_plan_args* args, int32_t num_envs, int32_t n_points, int32_t n_cands, int32_t plan_interval,
                         int32_t root_stride, const float* robot_size, void* stream);
 
+/* -------------------------------------------------------------------------------------------------------------
+ * velocity-tracking specifics (LRV = go1_gym/envs/base/legged_robot_velocity_tracking.py,
+ * CR = go1_gym/envs/rewards/corl_rewards.py) */
+
+/* LeggedRobot._step_contact_targets (LRV:844-923): gait phase advance, per-foot phase, duration-warped clock inputs
+ * (sin of 2 pi / 4 pi / pi x warped phase) and the Normal-CDF smoothed desired contact states.  commands [N, num_commands]
+ * (columns 4..8 = frequency, phase, offset, bound, duration); gait_indices [N] in / out; the other five [N,4] out. */
+typedef struct lt_gait_ptrs {
+    const float* commands;
+    float *gait_indices, *foot_indices, *clock_inputs, *doubletime_clock_inputs, *halftime_clock_inputs, *desired_contact_states;
+} lt_gait_ptrs;
+int lt_step_contact_targets(const lt_gait_ptrs* ptrs, int32_t num_envs, int32_t num_commands, float dt, float kappa,
+                            int32_t pacing_offset, void* stream);
+
+/* CoRLRewards._reward_<name> (CR:15-201): ids in the order the container defines them */
+#define LT_CORL_TRACKING_LIN_VEL 0
+#define LT_CORL_TRACKING_ANG_VEL 1
+#define LT_CORL_LIN_VEL_Z 2
+#define LT_CORL_ANG_VEL_XY 3
+#define LT_CORL_ORIENTATION 4
+#define LT_CORL_TORQUES 5
+#define LT_CORL_DOF_ACC 6
+#define LT_CORL_ACTION_RATE 7
+#define LT_CORL_COLLISION 8
+#define LT_CORL_DOF_POS_LIMITS 9
+#define LT_CORL_JUMP 10
+#define LT_CORL_TRACKING_CONTACTS_SHAPED_FORCE 11
+#define LT_CORL_TRACKING_CONTACTS_SHAPED_VEL 12
+#define LT_CORL_DOF_POS 13
+#define LT_CORL_DOF_VEL 14
+#define LT_CORL_ACTION_SMOOTHNESS_1 15
+#define LT_CORL_ACTION_SMOOTHNESS_2 16
+#define LT_CORL_FEET_SLIP 17
+#define LT_CORL_FEET_CONTACT_VEL 18
+#define LT_CORL_FEET_CONTACT_FORCES 19
+#define LT_CORL_FEET_CLEARANCE_CMD_LINEAR 20
+#define LT_CORL_FEET_IMPACT_VEL 21
+#define LT_CORL_ORIENTATION_CONTROL 22
+#define LT_CORL_RAIBERT_HEURISTIC 23
+#define LT_CORL_MAX_TERMS 32
+typedef struct lt_corl_cfg {
+    int32_t num_envs, num_commands, num_bodies, n_terms, n_penalised;
+    int32_t term_ids[LT_CORL_MAX_TERMS];              /* LT_CORL_*: row t of `out` is term term_ids[t] */
+    int32_t feet_indices[4], penalised[LT_CORL_MAX_TERMS];
+    float dt, tracking_sigma, tracking_sigma_yaw, base_height_target, gait_force_sigma, gait_vel_sigma, max_contact_force;   /* cfg.rewards */
+} lt_corl_cfg;
+/* env attributes the container reads (CR; shapes per env): commands [num_commands], base_lin_vel / base_ang_vel /
+ * projected_gravity / gravity_vec / base_pos [3], base_quat [4], the [12] dof / action / joint-target rows, contact_forces
+ * [num_bodies,3], foot_positions / foot_velocities / prev_foot_velocities [4,3], foot_indices / desired_contact_states [4];
+ * default_dof_pos [12] and dof_pos_limits [12,2] are shared by all envs.  last_contacts [N,4] (bool) is read AND written by
+ * feet_slip (CR:107-113).  out [n_terms, N]: unscaled term values, the layout of lt_step_args.extra_reward. */
+typedef struct lt_corl_ptrs {
+    const float *commands, *base_lin_vel, *base_ang_vel, *projected_gravity, *gravity_vec, *base_pos, *base_quat;
+    const float *torques, *dof_pos, *dof_vel, *last_dof_vel, *actions, *last_actions, *last_last_actions;
+    const float *joint_pos_target, *last_joint_pos_target, *last_last_joint_pos_target, *contact_forces;
+    const float *foot_positions, *foot_velocities, *prev_foot_velocities, *foot_indices, *desired_contact_states;
+    const float *default_dof_pos, *dof_pos_limits;
+    uint8_t* last_contacts;
+    float* out;
+} lt_corl_ptrs;
+int lt_corl_rewards(const lt_corl_cfg* cfg, const lt_corl_ptrs* ptrs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
