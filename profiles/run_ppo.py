@@ -50,6 +50,7 @@ def acts():
 
 def update():
     st.step = a.T
+    alg.compute_returns(obs, priv)          # lt_gae_kernel + lt_normalize_kernel in the launch list too
     alg.update()
 
 
