@@ -16,6 +16,9 @@
  *     adaptation_module: for each Linear:  weight[out, in] row-major, bias[out]           (AC:43-52)
  *     actor_body:        same                                                              (AC:57-68)
  *     critic_body:       same                                                              (AC:71-82)
+ * With height_map_size > 0 (go1_gym_learn/ppo_cse_cnn, CNN: = ppo_cse_cnn/actor_critic.py) the two Linear layers of
+ * HeightMapEncoder.model (CNN:45-52) sit between std and the adaptation module:
+ *     std | height_map_encoder.model.0 | height_map_encoder.model.2 | adaptation_module | actor_body | critic_body
  */
 #ifndef LT_POLICY_H
 #define LT_POLICY_H
@@ -47,6 +50,18 @@ typedef struct lt_policy_config {
     int32_t max_rows;                     /* row capacity of the workspaces: >= envs per act() and >= minibatch size */
     int32_t training;                     /* 0: inference only (no gradient workspaces) */
     int32_t activation;                   /* LT_ACT_*: between the Linear layers of all three bodies (AC:40) */
+    /* ppo_cse_cnn, MLP form of HeightMapEncoder with recurrent_latent_embedding = Identity
+     * (AC_Args.use_cnn = use_gru = False, the defaults, CNN:19-21).  height_map_size = 0 selects ppo_cse and the three fields
+     * after it are ignored.  With the encoder (CNN:181-198, process_obs_history):
+     *     o   = last num_obs row of obs_history;   h = its last height_map_size columns,  s = the columns before them
+     *     emb = act(W2 act(W1 h + b1) + b2)                                    (CNN:45-52: Linear, act, Linear, act)
+     *     policy_input = [s, s, emb]      (s twice: once from lstm_input's last row, once from the explicit cat, CNN:194-197)
+     * and policy_input takes the place of obs_history in the three bodies.  Only the last history row is read: the rows
+     * before it feed the Identity 'recurrent' module and are dropped by recurrent_latent[:, -1, :]. */
+    int32_t height_map_size;              /* prod(AC_Args.height_map_shape); 0 = no encoder */
+    int32_t num_obs;                      /* width of one observation row: num_obs_history = H * num_obs */
+    int32_t encoder_hidden;               /* 256 (CNN:47) */
+    int32_t encoder_embedding;            /* AC_Args.cnn_num_embedding */
 } lt_policy_config;
 
 /* PPO_Args (PPO:13-30) + torch.optim.Adam defaults */
@@ -123,11 +138,12 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
                        int32_t grad_world, float* stats, void* stream);
 /* Second half: Adam step (no clipping) on the adaptation slice with its own state (same flat indexing as params), lr host value. */
 int lt_adaptation_apply(lt_policy* p, const lt_ppo_hparams* hp, float lr, float* adam_m, float* adam_v, int32_t adam_step, void* stream);
-/* Diagnostic: DEVICE float[2][3 * (LT_POLICY_MAX_HIDDEN + 1)], the per-tensor power-of-two scales the backward passes of
+/* Diagnostic: DEVICE float[2][4 * (LT_POLICY_MAX_HIDDEN + 1)], the per-tensor power-of-two scales the backward passes of
  * lt_ppo_minibatch_grad ([0]) and lt_adaptation_grad ([1]) currently use for the gradient operand planes (rows: adaptation
- * module, actor, critic; columns: layer).  See "gradient scales" in csrc/lt_policy.cu. */
+ * module, actor, critic, height-map encoder; columns: layer).  See "gradient scales" in csrc/lt_policy.cu. */
 const float* lt_policy_grad_scales(const lt_policy* p);
-/* [lo, hi) of the adaptation module inside the flat parameter vector */
+/* [lo, hi) of what the adaptation optimiser steps inside the flat parameter vector: the adaptation module, preceded by the
+ * height-map encoder when there is one (with ppo_cse_cnn the regression loss reaches the encoder too, CNN PPO:170-186) */
 int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi);
 
 /* The contraction kernel on its own (tests, roofline measurement): out[M, N] = a[M, K] * b[N, K]^T (+ bias), fp32 in / out on

@@ -45,10 +45,26 @@ struct Planes {
     __half* lo() const { return p + plane; }
 };
 
+// Column map of a first layer: parameter columns [p, p + n) of the nn.Linear <-> GEMM columns [g, g + n) of the shared input
+// planes, up to three runs; GEMM columns outside every run carry zero weights (and their weight gradient is dropped).
+struct SegMap {
+    int n = 0;
+    int p[3] = {0, 0, 0}, g[3] = {0, 0, 0}, len[3] = {0, 0, 0};
+    void add(int pp, int gg, int ll) {
+        if (ll <= 0) return;
+        p[n] = pp; g[n] = gg; len[n] = ll; ++n;
+    }
+};
+__host__ __device__ inline int seg_param_col(const SegMap& m, int k) {           // GEMM column -> parameter column or -1
+    for (int i = 0; i < m.n; ++i)
+        if (k >= m.g[i] && k < m.g[i] + m.len[i]) return m.p[i] + (k - m.g[i]);
+    return -1;
+}
+
 struct Layer {
     int K = 0, N = 0;                 // GEMM reduction width (expanded for first layers) and outputs
     int k_real = 0;                   // in_features of the nn.Linear
-    int c1 = 0, s2 = 0, c2 = 0;       // param cols [0,c1) <- gemm cols [0,c1); param cols [c1,c1+c2) <- gemm cols [s2,s2+c2)
+    SegMap map;
     int64_t w_off = 0, b_off = 0;     // offsets in the flat parameter vector
     float* bias16 = nullptr;          // 16-byte aligned copy of the bias (vector loads in the GEMM epilogue), refreshed with W
     Planes W, WT;                     // [2][N][ld(K)] and (training) [2][K][ld(N)] for the input-gradient GEMM
@@ -60,11 +76,13 @@ struct Mlp {
     Planes Y[LT_POLICY_MAX_HIDDEN];               // hidden activations [R][N_l + 1]: column N_l is the constant one
     Planes dZ[LT_POLICY_MAX_HIDDEN + 1];
     float* out = nullptr;                         // [R][N_last] fp32
-    int idx = 0;                                  // 0 adaptation, 1 actor, 2 critic: row of the gradient-scale table
+    int idx = 0;                                  // 0 adaptation, 1 actor, 2 critic, 3 encoder: row of the gradient-scale table
+    const Planes* X = nullptr;                    // input planes of layer 0
+    const Planes* final_act = nullptr;            // != NULL: the LAST layer is followed by the activation too and lands, split, here
 };
 
 constexpr int GS_PER_MLP = LT_POLICY_MAX_HIDDEN + 1;
-constexpr int GS_N = 3 * GS_PER_MLP;              // one scale per dZ tensor
+constexpr int GS_N = 4 * GS_PER_MLP;              // one scale per dZ tensor
 enum { CTX_PPO = 0, CTX_ADAPT = 1 };              // lt_ppo_minibatch_grad and lt_adaptation_grad see different magnitudes
 
 }   // namespace
@@ -73,9 +91,16 @@ struct lt_policy {
     lt_policy_config c;
     int sm_count = 0;
     int64_t R = 0;                                // row capacity (multiple of 128)
-    int Din = 0, P = 0, A = 0, K0 = 0;
+    int Din = 0, P = 0, A = 0, K0 = 0;            // Din: width of what the bodies see in place of obs_history inside X0
+    int Dhist = 0;                                // width of an obs_history row as the caller stores it
     Mlp adapt, actor, critic;
     Planes X0;                                    // [2][R][ld(K0 + 1)]: column K0 is the constant one
+    // ppo_cse_cnn height-map encoder (include/lt_policy.h): X0 = [emb (E) | s (E0) | s (E0) | latent | privileged | 1]
+    bool has_enc = false;
+    int HM = 0, E = 0, E0 = 0, last_off = 0;      // last_off: first column of the last observation row inside obs_history
+    Mlp enc;
+    Planes XH;                                    // [2][R][ld(HM + 1)]: the height columns of the last observation row
+    float* enc_part = nullptr;                    // [3][R][E] fp32: emb-column input gradients of the three bodies
     const void* packed_src = nullptr;             // what X0 currently holds: (obs_history, indices, count) of the last gather
     const void* packed_idx = nullptr;
     int packed_count = 0;
@@ -152,16 +177,14 @@ __device__ __forceinline__ void split1(float x, __half& hi, __half& lo) {
 }
 
 // master weights -> operand planes W [N][K] and WT [K][N] of one layer (expanded column map for first layers)
-__global__ void split_weights_kernel(const float* __restrict__ w, int N, int K, int k_real, int c1, int s2, int c2, __half* W, int64_t ldW,
+__global__ void split_weights_kernel(const float* __restrict__ w, int N, int K, int k_real, const SegMap map, __half* W, int64_t ldW,
                                      int64_t planeW, __half* WT, int64_t ldT, int64_t planeT, const float* __restrict__ bias,
                                      float* __restrict__ bias16) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < N) bias16[i] = bias[i];
     if (i >= (int64_t)N * K) return;
     const int n = (int)(i / K), k = (int)(i % K);
-    int src = -1;
-    if (k < c1) src = k;
-    else if (k >= s2 && k < s2 + c2) src = c1 + (k - s2);
+    const int src = seg_param_col(map, k);
     const float v = src >= 0 ? w[(int64_t)n * k_real + src] * S_W : 0.0f;
     __half hi, lo;
     split1(v, hi, lo);
@@ -221,17 +244,55 @@ __global__ void scatter_latent_kernel(const float* __restrict__ latent, int rows
     }
 }
 
+// ppo_cse_cnn gather (CNN:181-198): the last observation row of obs_history[src] goes, split, to X0 = [. (emb, written by the
+// encoder) | s | s | . (latent) | privileged] and its height columns to XH.  One warp per row.
+__global__ void __launch_bounds__(256) pack_enc_kernel(const float* __restrict__ obs_history, const float* __restrict__ priv,
+                                                       const int64_t* __restrict__ indices, int rows, int Dhist, int last_off, int E0, int HM, int E,
+                                                       int P, int teacher, __half* __restrict__ x, int64_t ldx, int64_t planex,
+                                                       __half* __restrict__ xh, int64_t ldh, int64_t planeh) {
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int64_t src = indices ? indices[r] : (int64_t)r;
+    const float* o = obs_history + src * Dhist + last_off;
+    __half* x_hi = x + (int64_t)r * ldx;
+    __half* x_lo = x_hi + planex;
+    for (int c = lane; c < E0; c += 32) {
+        __half hi, lo;
+        split1(__ldg(o + c) * S_X, hi, lo);
+        x_hi[E + c] = hi;
+        x_lo[E + c] = lo;
+        x_hi[E + E0 + c] = hi;
+        x_lo[E + E0 + c] = lo;
+    }
+    __half* h_hi = xh + (int64_t)r * ldh;
+    __half* h_lo = h_hi + planeh;
+    for (int c = lane; c < HM; c += 32) {
+        __half hi, lo;
+        split1(__ldg(o + E0 + c) * S_X, hi, lo);
+        h_hi[c] = hi;
+        h_lo[c] = lo;
+    }
+    if (lane < 2 * P) {
+        const int Din = E + 2 * E0;
+        const int j = lane < P ? lane : lane - P;
+        float v = 0.0f;
+        if (priv && (lane >= P || teacher)) v = priv[src * P + j];
+        __half hi, lo;
+        split1(v * S_X, hi, lo);
+        x_hi[Din + lane] = hi;
+        x_lo[Din + lane] = lo;
+    }
+}
+
 // split-K partials of dW^T ... summed in a fixed order into the flat gradient: partial[s][n][k], k < K -> weight (through the
 // first-layer column map), k == K -> bias
 __global__ void reduce_dw_kernel(const float* __restrict__ partial, int splits, int64_t split_stride, int64_t ldp, int N, int K, int k_real,
-                                 int c1, int s2, int c2, float* __restrict__ gw, float* __restrict__ gb) {
+                                 const SegMap map, float* __restrict__ gw, float* __restrict__ gb) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)N * (K + 1)) return;
     const int n = (int)(i / (K + 1)), k = (int)(i % (K + 1));
-    int dst = -1;
-    if (k == K) dst = -2;
-    else if (k < c1) dst = k;
-    else if (k >= s2 && k < s2 + c2) dst = c1 + (k - s2);
+    const int dst = k == K ? -2 : seg_param_col(map, k);
     if (dst == -1) return;
     float acc = 0.0f;
     const float* src = partial + (int64_t)n * ldp + k;
@@ -283,6 +344,43 @@ __global__ void update_scales_kernel(uint32_t* __restrict__ amax, float* __restr
 __global__ void fill_kernel(float* __restrict__ dst, float v, int n) {
     if ((int)threadIdx.x < n) dst[threadIdx.x] = v;
 }
+
+// gradient of the encoder's (activated) output: dz = (sum over the bodies of their emb-column input gradients) .* act'(emb),
+// measured (amax) and split with the tensor's scale into the encoder's last dZ planes.  Thread per (row, 4 columns).
+__global__ void __launch_bounds__(256) enc_grad_kernel(const float* __restrict__ part, int n_parts, int64_t part_stride, int count, int E, int act,
+                                                       const __half* __restrict__ y, int64_t ldy, int64_t planey,
+                                                       const float* __restrict__ scale_ptr, uint32_t* __restrict__ amax,
+                                                       __half* __restrict__ dz, int64_t ldz, int64_t planez) {
+    using namespace ltg;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int q = E >> 2;
+    float m = 0.0f;
+    if (i < (int64_t)count * q) {
+        const int r = (int)(i / q), c = (int)(i % q) * 4;
+        float4 g = *reinterpret_cast<const float4*>(part + (int64_t)r * E + c);
+        for (int s = 1; s < n_parts; ++s) {
+            const float4 t = *reinterpret_cast<const float4*>(part + s * part_stride + (int64_t)r * E + c);
+            g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+        const float scale = __ldg(scale_ptr);
+        const float gv[4] = {g.x, g.y, g.z, g.w};
+        const __half* yh = y + (int64_t)r * ldy + c;
+        __half* zh = dz + (int64_t)r * ldz + c;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float yv = (__half2float(yh[j]) + __half2float(yh[planey + j])) * (1.0f / S_X);
+            float d = gv[j];
+            LTG_ACT_SWITCH(act, d *= act_bwd<A_>(yv);)
+            m = fmaxf(m, fabsf(d));
+            __half hi, lo;
+            split1(d * scale, hi, lo);
+            zh[j] = hi;
+            zh[planez + j] = lo;
+        }
+    }
+    record_amax(amax, m);
+}
+
 
 struct HeadParams {
     lt_ppo_batch_ptrs b;
@@ -583,21 +681,25 @@ int run_gemm_mn(lt_policy* P, const Operand& A, int M, const Operand& B, int N, 
     return LT_OK;
 }
 
-int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_out, int k_real0, int c1, int s2, int c2, int64_t& off) {
+// `X`: input planes of layer 0 (GEMM width K_in, columns mapped onto the k_real0 parameter columns by map0);
+// final_act != NULL: the output layer is activated too and written, split, into those planes instead of m.out
+int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_out, int k_real0, const Planes* X, int K_in, const SegMap& map0,
+              const Planes* final_act, int64_t& off) {
     m.n = n_hidden + 1;
+    m.X = X;
+    m.final_act = final_act;
     int prev = k_real0;
     for (int l = 0; l < m.n; ++l) {
         Layer& L = m.L[l];
         L.N = l < n_hidden ? hidden[l] : n_out;
         L.k_real = prev;
         if (l == 0) {
-            L.K = P->K0;
-            L.c1 = c1;
-            L.s2 = s2;
-            L.c2 = c2;
+            L.K = K_in;
+            L.map = map0;
         } else {
             L.K = prev;
-            L.c1 = prev;
+            L.map = SegMap();
+            L.map.add(0, 0, prev);
         }
         L.w_off = off;
         off += (int64_t)L.N * L.k_real;
@@ -621,14 +723,14 @@ int build_mlp(lt_policy* P, Mlp& m, int n_hidden, const int32_t* hidden, int n_o
         }
         prev = L.N;
     }
-    return alloc_dev(P, m.out, P->R * m.L[m.n - 1].N);
+    return final_act ? LT_OK : alloc_dev(P, m.out, P->R * m.L[m.n - 1].N);
 }
 
 int refresh_mlp(lt_policy* P, Mlp& m, cudaStream_t s) {
     for (int l = 0; l < m.n; ++l) {
         Layer& L = m.L[l];
         const int64_t n = (int64_t)L.N * L.K;
-        split_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->params + L.w_off, L.N, L.K, L.k_real, L.c1, L.s2, L.c2, L.W.p, L.W.ld,
+        split_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->params + L.w_off, L.N, L.K, L.k_real, L.map, L.W.p, L.W.ld,
                                                                         L.W.plane, L.WT.p, L.WT.ld, L.WT.plane, P->params + L.b_off, L.bias16);
     }
     LTP_CUDA(P, cudaGetLastError());
@@ -643,13 +745,14 @@ int forward_mlp(lt_policy* P, Mlp& m, int rows, bool train, cudaStream_t s) {
         memset(&p, 0, sizeof p);
         p.out_scale = 1.0f / (S_X * S_W);
         p.bias = L.bias16;
-        const Operand A = l == 0 ? op(P->X0, rows) : op(m.Y[l - 1], rows);
-        if (l < m.n - 1) {
+        const Operand A = l == 0 ? op(*m.X, rows) : op(m.Y[l - 1], rows);
+        if (l < m.n - 1 || m.final_act) {
+            const Planes& Y = l < m.n - 1 ? m.Y[l] : *m.final_act;
             p.mode = ltg::EPI_ELU;
             p.act = P->c.activation;
-            p.out_h = m.Y[l].p;
-            p.ld_h = m.Y[l].ld;
-            p.plane_h = m.Y[l].plane;
+            p.out_h = Y.p;
+            p.ld_h = Y.ld;
+            p.plane_h = Y.plane;
             p.split_scale = S_X;
         } else {
             p.mode = ltg::EPI_F32;
@@ -675,7 +778,7 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
     for (int l = m.n - 1; l >= 0; --l) {
         Layer& L = m.L[l];
         {   // dW_l and db_l:  [N_l, K_l + 1] = dZ_l[count, N_l]^T * [X_{l-1} | 1][count, K_l + 1]
-            const Planes& X = l == 0 ? P->X0 : m.Y[l - 1];
+            const Planes& X = l == 0 ? *m.X : m.Y[l - 1];
             const int Kp1 = L.K + 1;
             ltg::Params p;
             memset(&p, 0, sizeof p);
@@ -690,8 +793,8 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
             int rc = run_gemm_mn(P, op(m.dZ[l], count), L.N, op(X, count), Kp1, count, splits, p, s);
             if (rc) return rc;
             const int64_t n = (int64_t)L.N * Kp1;
-            reduce_dw_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->partial, p.splits, p.split_stride, p.ld_f32, L.N, L.K, L.k_real, L.c1,
-                                                                        L.s2, L.c2, P->grads + L.w_off, P->grads + L.b_off);
+            reduce_dw_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->partial, p.splits, p.split_stride, p.ld_f32, L.N, L.K, L.k_real, L.map,
+                                                                        P->grads + L.w_off, P->grads + L.b_off);
         }
         if (l > 0) {   // dZ_{l-1} = (dZ_l * W_l) .* ELU'(Y_{l-1})
             ltg::Params p;
@@ -720,7 +823,11 @@ int backward_mlp(lt_policy* P, Mlp& m, int count, int ctx, cudaStream_t s) {
 int pack(lt_policy* P, const float* obs_history, const float* priv, const int64_t* indices, int rows, int teacher, bool train, cudaStream_t s) {
     (void)train;
     if (2 * P->P > 32) return fail(P, LT_ERR_INVALID, "num_privileged_obs > 16 is not supported by the gather kernel");
-    pack_x0_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s>>>(obs_history, priv, indices, rows, P->Din, P->P, teacher, P->X0.p, P->X0.ld, P->X0.plane);
+    if (P->has_enc)
+        pack_enc_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s>>>(obs_history, priv, indices, rows, P->Dhist, P->last_off, P->E0, P->HM, P->E, P->P,
+                                                                   teacher, P->X0.p, P->X0.ld, P->X0.plane, P->XH.p, P->XH.ld, P->XH.plane);
+    else
+        pack_x0_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s>>>(obs_history, priv, indices, rows, P->Din, P->P, teacher, P->X0.p, P->X0.ld, P->X0.plane);
     LTP_CUDA(P, cudaGetLastError());
     P->packed_src = nullptr;
     return LT_OK;
@@ -730,6 +837,40 @@ int scatter_latent(lt_policy* P, int rows, bool train, cudaStream_t s) {
     scatter_latent_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(P->adapt.out, rows, P->P, P->Din, P->X0.p, P->X0.ld, P->X0.plane);
     LTP_CUDA(P, cudaGetLastError());
     return LT_OK;
+}
+
+// encoder forward (CNN:181-187): XH -> emb columns of X0.  No-op without an encoder.
+int forward_enc(lt_policy* P, int rows, bool train, cudaStream_t s) {
+    return P->has_enc ? forward_mlp(P, P->enc, rows, train, s) : LT_OK;
+}
+
+// encoder backward: the emb columns of the first-layer input gradients of `nets` (dZ_0 * W_0[:, emb]) summed in fp32, times the
+// activation derivative -> the encoder's last dZ; then the encoder's own weight gradients.  No-op without an encoder.
+int backward_enc(lt_policy* P, Mlp* const* nets, int n_nets, int count, int ctx, cudaStream_t s) {
+    if (!P->has_enc) return LT_OK;
+    Mlp& e = P->enc;
+    const int64_t stride = P->R * (int64_t)P->E;
+    for (int i = 0; i < n_nets; ++i) {
+        Mlp& m = *nets[i];
+        Layer& L = m.L[0];
+        ltg::Params g;
+        memset(&g, 0, sizeof g);
+        g.mode = ltg::EPI_PARTIAL;
+        g.out_scale = 1.0f / S_W;
+        g.a_scale_ptr = P->gs(ctx, m, 0);
+        g.out_f32 = P->enc_part + i * stride;
+        g.ld_f32 = P->E;
+        g.split_stride = 0;
+        const Operand B{L.WT.p, P->E, L.WT.ld, L.WT.plane};             // rows [0, E) of W_0^T: the emb columns
+        const int rc = run_gemm(P, op(m.dZ[0], count), count, B, P->E, L.N, 1, g, s);
+        if (rc) return rc;
+    }
+    Planes& dz = e.dZ[e.n - 1];
+    const int64_t n = (int64_t)count * (P->E / 4);
+    enc_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(P->enc_part, n_nets, stride, count, P->E, P->c.activation, P->X0.p, P->X0.ld, P->X0.plane,
+                                                               P->gs(ctx, e, e.n - 1), P->ga(ctx, e, e.n - 1), dz.p, dz.ld, dz.plane);
+    LTP_CUDA(P, cudaGetLastError());
+    return backward_mlp(P, e, count, ctx, s);
 }
 
 int check_ready(lt_policy* P, int rows) {
@@ -811,25 +952,67 @@ int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
         cfg->n_adaptation_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_actor_hidden > LT_POLICY_MAX_HIDDEN || cfg->n_critic_hidden > LT_POLICY_MAX_HIDDEN ||
         cfg->activation < LT_ACT_ELU || cfg->activation > LT_ACT_SIGMOID)
         return fail(nullptr, LT_ERR_INVALID, "unsupported actor-critic geometry");
+    if (cfg->height_map_size < 0 ||
+        (cfg->height_map_size > 0 &&
+         (cfg->num_obs <= 0 || cfg->num_obs_history % cfg->num_obs != 0 || cfg->height_map_size > cfg->num_obs || cfg->encoder_hidden <= 0 ||
+          cfg->encoder_embedding <= 0 || cfg->encoder_embedding % 8 != 0)))
+        return fail(nullptr, LT_ERR_INVALID,
+                    "unsupported height-map encoder geometry (height_map_size <= num_obs, num_obs divides num_obs_history, "
+                    "encoder_embedding a multiple of 8)");
     if (!ltg::encode_fn()) return fail(nullptr, LT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
     lt_policy* P = new lt_policy();
     P->c = *cfg;
     P->sm_count = prop.multiProcessorCount;
     P->R = up(cfg->max_rows, 128);
-    P->Din = cfg->num_obs_history;
+    P->Dhist = cfg->num_obs_history;
     P->P = cfg->num_privileged_obs;
     P->A = cfg->num_actions;
+    P->has_enc = cfg->height_map_size > 0;
+    if (P->has_enc) {
+        P->HM = cfg->height_map_size;
+        P->E = cfg->encoder_embedding;
+        P->E0 = cfg->num_obs - cfg->height_map_size;
+        P->last_off = cfg->num_obs_history - cfg->num_obs;
+        P->Din = P->E + 2 * P->E0;
+    } else {
+        P->Din = P->Dhist;
+    }
     P->K0 = P->Din + 2 * P->P;
+    P->adapt.idx = 0;
+    P->actor.idx = 1;
+    P->critic.idx = 2;
+    P->enc.idx = 3;
     int rc = alloc_planes(P, P->X0, P->R, P->K0 + 1);
     if (!rc) ones_col_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(P->X0.p + P->K0, P->R, P->X0.ld);
     int64_t off = P->A;                                         // std first
-    if (!rc) rc = build_mlp(P, P->adapt, cfg->n_adaptation_hidden, cfg->adaptation_hidden, P->P, P->Din, P->Din, 0, 0, off);
-    if (!rc) rc = build_mlp(P, P->actor, cfg->n_actor_hidden, cfg->actor_hidden, P->A, P->Din + P->P, P->Din + P->P, 0, 0, off);
-    if (!rc) rc = build_mlp(P, P->critic, cfg->n_critic_hidden, cfg->critic_hidden, 1, P->Din + P->P, P->Din, P->Din + P->P, P->P, off);
+    // first-layer column maps: parameter columns of the reference's input (obs_history | latent or privileged; with the encoder
+    // [s | s | emb] in place of obs_history) -> columns of X0
+    SegMap base, m_adapt, m_actor, m_critic;
+    if (P->has_enc) {
+        base.add(0, P->E, 2 * P->E0);
+        base.add(2 * P->E0, 0, P->E);
+        SegMap hmap;
+        hmap.add(0, 0, P->HM);
+        const int32_t enc_hidden[1] = {cfg->encoder_hidden};
+        rc = rc ? rc : alloc_planes(P, P->XH, P->R, P->HM + 1);
+        if (!rc) ones_col_kernel<<<(unsigned)((P->R + 255) / 256), 256>>>(P->XH.p + P->HM, P->R, P->XH.ld);
+        if (!rc) rc = build_mlp(P, P->enc, 1, enc_hidden, P->E, P->HM, &P->XH, P->HM, hmap, &P->X0, off);
+        if (!rc && cfg->training) rc = alloc_dev(P, P->enc_part, 3 * P->R * (int64_t)P->E);
+    } else {
+        base.add(0, 0, P->Din);
+    }
+    m_adapt = base;
+    m_actor = base;
+    m_actor.add(P->Din, P->Din, P->P);                          // latent columns
+    m_critic = base;
+    m_critic.add(P->Din, P->Din + P->P, P->P);                  // privileged columns
+    if (!rc) rc = build_mlp(P, P->adapt, cfg->n_adaptation_hidden, cfg->adaptation_hidden, P->P, P->Din, &P->X0, P->K0, m_adapt, nullptr, off);
+    if (!rc) rc = build_mlp(P, P->actor, cfg->n_actor_hidden, cfg->actor_hidden, P->A, P->Din + P->P, &P->X0, P->K0, m_actor, nullptr, off);
+    if (!rc) rc = build_mlp(P, P->critic, cfg->n_critic_hidden, cfg->critic_hidden, 1, P->Din + P->P, &P->X0, P->K0, m_critic, nullptr, off);
     P->n_params = off;
     if (!rc && cfg->training) {
         int64_t need = 0;
-        Mlp* ms[3] = {&P->adapt, &P->actor, &P->critic};
+        Mlp* ms[4] = {&P->adapt, &P->actor, &P->critic, &P->enc};
         for (Mlp* m : ms)
             for (int l = 0; l < m->n; ++l) {
                 const int Kp1 = m->L[l].K + 1;
@@ -845,9 +1028,6 @@ int lt_policy_create(const lt_policy_config* cfg, lt_policy** out) {
     if (!rc) rc = alloc_dev(P, P->scalars, 8);
     if (!rc) rc = alloc_dev(P, P->gscale, 2 * GS_N);
     if (!rc) rc = alloc_dev(P, P->gamax, 2 * GS_N);
-    P->adapt.idx = 0;
-    P->actor.idx = 1;
-    P->critic.idx = 2;
     if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = fail(P, LT_ERR_CUDA, "initialisation kernels failed");
     if (rc) {
         g_policy_error = P->err;
@@ -868,7 +1048,7 @@ int64_t lt_policy_num_params(const lt_policy* p) { return p ? p->n_params : 0; }
 
 int lt_policy_adaptation_slice(const lt_policy* p, int64_t* lo, int64_t* hi) {
     if (!p || !lo || !hi) return LT_ERR_INVALID;
-    *lo = p->adapt.L[0].w_off;
+    *lo = p->has_enc ? p->enc.L[0].w_off : p->adapt.L[0].w_off;
     *hi = p->actor.L[0].w_off;
     return LT_OK;
 }
@@ -887,6 +1067,7 @@ int lt_policy_refresh(lt_policy* p, void* stream) {
     if (!p) return LT_ERR_INVALID;
     if (!p->params) return fail(p, LT_ERR_UNBOUND, "lt_policy_bind_params was never called");
     int rc = refresh_mlp(p, p->adapt, (cudaStream_t)stream);
+    if (!rc && p->has_enc) rc = refresh_mlp(p, p->enc, (cudaStream_t)stream);
     if (!rc) rc = refresh_mlp(p, p->actor, (cudaStream_t)stream);
     if (!rc) rc = refresh_mlp(p, p->critic, (cudaStream_t)stream);
     return rc;
@@ -900,6 +1081,7 @@ int lt_policy_forward(lt_policy* p, const float* obs_history, const float* privi
     if (!obs_history) return fail(p, LT_ERR_INVALID, "obs_history is NULL");
     if ((value || teacher_latent) && !privileged_obs) return fail(p, LT_ERR_INVALID, "privileged_obs is NULL but the critic / teacher needs it");
     rc = pack(p, obs_history, privileged_obs, nullptr, rows, teacher_latent, false, s);
+    if (!rc) rc = forward_enc(p, rows, false, s);
     if (rc) return rc;
     if (latent || (action_mean && !teacher_latent)) {
         rc = forward_mlp(p, p->adapt, rows, false, s);
@@ -932,6 +1114,7 @@ int lt_policy_act(lt_policy* p, const float* obs_history, const float* privilege
     if (!obs_history) return fail(p, LT_ERR_INVALID, "obs_history is NULL");
     if (value && !privileged_obs) return fail(p, LT_ERR_INVALID, "privileged_obs is NULL but the critic needs it");
     rc = pack(p, obs_history, privileged_obs, nullptr, rows, 0, false, s);
+    if (!rc) rc = forward_enc(p, rows, false, s);
     if (!rc) rc = forward_mlp(p, p->adapt, rows, false, s);
     if (!rc) rc = scatter_latent(p, rows, false, s);
     if (!rc) rc = forward_mlp(p, p->actor, rows, false, s);
@@ -958,6 +1141,7 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
         p->packed_idx = indices;
         p->packed_count = count;
     }
+    if (!rc) rc = forward_enc(p, count, true, s);
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (!rc) rc = scatter_latent(p, count, true, s);
     if (!rc) rc = forward_mlp(p, p->actor, count, true, s);
@@ -1007,6 +1191,10 @@ int lt_ppo_minibatch_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const in
             rc = run_gemm(p, op(a.dZ[0], count), count, B, p->P, L.N, 1, g, s);
             if (!rc) rc = backward_mlp(p, ad, count, CTX_PPO, s);
         }
+        if (!rc) {
+            Mlp* nets[3] = {&a, &c, &ad};
+            rc = backward_enc(p, nets, 3, count, CTX_PPO, s);
+        }
         if (!rc) rc = end_grad_scales(p, CTX_PPO, s);
         if (rc) return rc;
     }
@@ -1041,6 +1229,7 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
     // module reads only the obs_history columns; its first-layer weights are zero on the latent / privileged columns)
     const bool reuse = p->packed_src == batch->obs_history && p->packed_idx == indices && p->packed_count == count && indices != nullptr;
     if (!reuse) rc = pack(p, batch->obs_history, batch->privileged_obs, indices, count, 0, true, s);
+    if (!rc) rc = forward_enc(p, count, true, s);                // the encoder's weights moved since the PPO half (CNN PPO:170)
     if (!rc) rc = forward_mlp(p, p->adapt, count, true, s);
     if (rc) return rc;
     const int blocks = (count + HEAD_THREADS - 1) / HEAD_THREADS;
@@ -1064,6 +1253,10 @@ int lt_adaptation_grad(lt_policy* p, const lt_ppo_batch_ptrs* batch, const int64
         adapt_head_reduce_kernel<<<1, 32, 0, s>>>(p->head_partial, blocks, count, num_train, p->P, stats);
         LTP_CUDA(p, cudaGetLastError());
         rc = backward_mlp(p, ad, count, CTX_ADAPT, s);
+        if (!rc) {
+            Mlp* nets[1] = {&ad};
+            rc = backward_enc(p, nets, 1, count, CTX_ADAPT, s);
+        }
         if (!rc) rc = end_grad_scales(p, CTX_ADAPT, s);
         if (rc) return rc;
     }
@@ -1081,6 +1274,10 @@ int lt_adaptation_apply(lt_policy* p, const lt_ppo_hparams* hp, float lr, float*
     adam_kernel<<<(unsigned)((hi - lo + 255) / 256), 256, 0, s>>>(p->params, p->grads, adam_m, adam_v, lo, hi, nullptr, lr, nullptr, hp->adam_beta1,
                                                                  hp->adam_beta2, hp->adam_eps, bc1, bc2);
     LTP_CUDA(p, cudaGetLastError());
+    if (p->has_enc) {
+        const int rc = refresh_mlp(p, p->enc, s);
+        if (rc) return rc;
+    }
     return refresh_mlp(p, p->adapt, s);
 }
 

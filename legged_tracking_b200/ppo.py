@@ -104,35 +104,49 @@ class ActorCritic:
     ('std', 'adaptation_module.0.weight', ... 'critic_body.6.bias'), load_state_dict() writes through them.  The MLPs
     themselves exist only as tensor-core operand planes inside the library."""
     is_recurrent = False
+    ARGS = AC_Args                        # the params_proto class this variant reads its geometry from
 
     def __init__(self, num_obs, num_privileged_obs, num_obs_history, num_actions, **kwargs):
+        args = kwargs.pop("ac_args", None) or self.ARGS
         if kwargs:
             print("ActorCritic.__init__ got unexpected arguments, which will be ignored: " + str(list(kwargs)))
-        if AC_Args.use_decoder or AC_Args.normalize_obs:
+        if args.use_decoder or getattr(args, "normalize_obs", False):
             raise NotImplementedError("use_decoder / normalize_obs are off in every reference config (actor_critic.py:18-20)")
-        if AC_Args.activation not in _ACTIVATIONS:
-            raise ValueError(f"invalid activation function {AC_Args.activation!r}")         # actor_critic.py:177-178
-        self.activation = AC_Args.activation
+        if args.activation not in _ACTIVATIONS:
+            raise ValueError(f"invalid activation function {args.activation!r}")         # actor_critic.py:177-178
+        self.ac_args = args
+        self.activation = args.activation
         self.decoder = False
         self.normalize_obs = False
         self.num_obs, self.num_obs_history = int(num_obs), int(num_obs_history)
         self.num_privileged_obs, self.num_actions = int(num_privileged_obs), int(num_actions)
-        self.hidden = {name: [int(h) for h in getattr(AC_Args, attr)] for name, attr in _BODIES}
-        n_in = dict(adaptation_module=self.num_obs_history, actor_body=self.num_privileged_obs + self.num_obs_history,
-                    critic_body=self.num_privileged_obs + self.num_obs_history)
+        self.hidden = {name: [int(h) for h in getattr(args, attr)] for name, attr in _BODIES}
+        self.encoder = self._encoder_spec(args)          # None, or dict(height_map_size, hidden, embedding): ppo_cnn.ActorCritic
+        # what the three bodies read in place of the observation history (ppo_cse: the history itself)
+        self.policy_input_dim = self.num_obs_history if self.encoder is None else \
+            2 * (self.num_obs - self.encoder["height_map_size"]) + self.encoder["embedding"]
+        n_in = dict(adaptation_module=self.policy_input_dim, actor_body=self.num_privileged_obs + self.policy_input_dim,
+                    critic_body=self.num_privileged_obs + self.policy_input_dim)
         n_out = dict(adaptation_module=self.num_privileged_obs, actor_body=self.num_actions, critic_body=1)
         # flat layout (lt_policy.h): [(key, shape, lo, hi)]
         self.layout = [("std", (self.num_actions,), 0, self.num_actions)]
         o = self.num_actions
-        self.body_slices = {}
-        for name, _ in _BODIES:
-            lo_body = o
-            dims = [n_in[name]] + self.hidden[name] + [n_out[name]]
+
+        def add_linears(name, dims):
+            nonlocal o
             for l, (a, b) in enumerate(zip(dims[:-1], dims[1:])):
                 self.layout.append((f"{name}.{2 * l}.weight", (b, a), o, o + a * b))
                 o += a * b
                 self.layout.append((f"{name}.{2 * l}.bias", (b,), o, o + b))
                 o += b
+        self.body_slices = {}
+        if self.encoder is not None:
+            lo_body = o
+            add_linears("height_map_encoder.model", [self.encoder["height_map_size"], self.encoder["hidden"], self.encoder["embedding"]])
+            self.body_slices["height_map_encoder"] = (lo_body, o)
+        for name, _ in _BODIES:
+            lo_body = o
+            add_linears(name, [n_in[name]] + self.hidden[name] + [n_out[name]])
             self.body_slices[name] = (lo_body, o)
         self.num_params = o
         self.device = torch.device("cpu")
@@ -142,16 +156,19 @@ class ActorCritic:
         self._h, self._cap, self._training, self._dirty = None, 0, False, True
         self._dist = None                 # (mean, sigma) of the last act(): the reference's self.distribution
 
+    def _encoder_spec(self, args):
+        return None
+
     def _init_parameters(self):
-        """torch.nn.Linear's default initialisation, drawn in the order the reference constructs its layers (adaptation
-        module, actor, critic; weight then bias; actor_critic.py:43-82), so a seeded run starts from the same weights."""
+        """torch.nn.Linear's default initialisation, drawn in the order the reference constructs its layers ((encoder,)
+        adaptation module, actor, critic; weight then bias; actor_critic.py:43-82), so a seeded run starts from the same weights."""
         views = self._views()
         for key, shape, _, _ in self.layout:
             if key.endswith(".weight"):
                 lin = torch.nn.Linear(shape[1], shape[0])          # used as the initialiser only
                 views[key].copy_(lin.weight.detach())
                 views[key[:-6] + "bias"].copy_(lin.bias.detach())
-        views["std"].fill_(float(AC_Args.init_noise_std))
+        views["std"].fill_(float(self.ac_args.init_noise_std))
 
     def _views(self):
         return OrderedDict((key, self.flat[lo:hi].view(shape)) for key, shape, lo, hi in self.layout)
@@ -246,6 +263,9 @@ class ActorCritic:
                 arr[i] = w
         cfg.max_rows, cfg.training = rows, 1 if training else 0
         cfg.activation = _abi.DEFINES[_ACTIVATIONS[self.activation]]
+        if self.encoder is not None:
+            cfg.height_map_size, cfg.num_obs = self.encoder["height_map_size"], self.num_obs
+            cfg.encoder_hidden, cfg.encoder_embedding = self.encoder["hidden"], self.encoder["embedding"]
         handle = C.c_void_p()
         with torch.cuda.device(self.device):
             _abi.check_policy(lib.lt_policy_create(C.byref(cfg), C.byref(handle)), None, "lt_policy_create")
@@ -712,14 +732,16 @@ class Runner:
     """ppo_cse/__init__.py:65-357.  wandb / video logging of the reference is replaced by an optional `log_fn(dict, step)`
     callback; checkpoints (ac_weights.pt + the two TorchScript modules) go to `save_dir`."""
 
+    ACTOR_CRITIC = ActorCritic             # ppo_cnn.Runner swaps in the height-map-encoder variant
+
     def __init__(self, env, device='cuda:0', runner_args=RunnerArgs, ac_args=AC_Args, log_fn=None, save_dir="last_run/checkpoints"):
         self.device = device
         self.env = env
         self.runner_args = runner_args
         self.log_fn = log_fn
         self.save_dir = save_dir
-        actor_critic = ActorCritic(self.env.num_obs, self.env.num_privileged_obs, self.env.num_obs_history,
-                                   self.env.num_actions).to(self.device)
+        actor_critic = self.ACTOR_CRITIC(self.env.num_obs, self.env.num_privileged_obs, self.env.num_obs_history,
+                                         self.env.num_actions).to(self.device)
         if runner_args.resume:
             actor_critic.load_state_dict(torch.load(runner_args.resume, map_location=self.device))
         self.alg = PPO(actor_critic, device=self.device)         # broadcasts rank 0's weights when env-sharded

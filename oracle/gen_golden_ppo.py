@@ -41,6 +41,11 @@ CASES = {
                                     num_mini_batches=2, learning_rate=5e-4, entropy_coef=0.0, gamma=0.97, lam=0.9,
                                     max_grad_norm=0.5),
                            time_outs=False),
+    # go1_gym_learn/ppo_cse_cnn (row f4), MLP height-map encoder + Identity: 2 history rows of 20 scalars + 2x5x4 heights
+    "ppo_cnn_48x6": dict(variant="ppo_cse_cnn", N=48, T=6, num_obs=60, num_priv=3, H=2, num_actions=12, seed=21,
+                         ac=dict(actor_hidden_dims=[64, 48, 32], critic_hidden_dims=[64, 32], adaptation_module_branch_hidden_dims=[48, 24],
+                                 height_map_shape=(2, 5, 4), cnn_num_embedding=32, use_cnn=False, use_gru=False),
+                         ppo=dict(num_learning_epochs=3, num_mini_batches=3), time_outs=True),
 }
 
 
@@ -61,8 +66,10 @@ def synth_transitions(case):
 
 def record(case):
     ref_harness.install()
-    import go1_gym_learn.ppo_cse.actor_critic as acmod
-    import go1_gym_learn.ppo_cse.ppo as ppomod
+    import importlib
+    variant = case.get("variant", "ppo_cse")
+    acmod = importlib.import_module(f"go1_gym_learn.{variant}.actor_critic")
+    ppomod = importlib.import_module(f"go1_gym_learn.{variant}.ppo")
     import torch.nn as nn
 
     saved_ac = {k: getattr(acmod.AC_Args, k) for k in vars(acmod.AC_Args)}
@@ -129,6 +136,7 @@ def record(case):
             out["ppo_args/" + k] = np.asarray(getattr(ppomod.PPO_Args, k))
         out["meta/sizes"] = np.asarray([N, T, no, npv, H, na], np.int64)
         out["meta/time_outs"] = np.asarray(bool(case["time_outs"]))
+        out["meta/variant"] = np.asarray(variant)
         return out
     finally:
         for k, v in saved_ac.items():

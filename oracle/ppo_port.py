@@ -11,6 +11,8 @@ Follows, function by function:
   go1_gym_learn/ppo_cse/rollout_storage.py:99-137  mini_batch_generator  -> PpoPort.update (one permutation, reused)
   go1_gym_learn/ppo_cse/actor_critic.py:118-160    update_distribution / evaluate / log-prob / entropy -> policy_forward
   go1_gym_learn/ppo_cse/ppo.py:99-206              update                -> PpoPort.update
+  go1_gym_learn/ppo_cse_cnn/actor_critic.py:27-62, 181-198   HeightMapEncoder (MLP form) / process_obs_history -> policy_input
+      (row f4: the state_dict then holds 'height_map_encoder.model.*'; everything else of ppo_cse_cnn is ppo_cse's code)
 """
 import math
 
@@ -37,9 +39,32 @@ def mlp(params, prefix, x, act):
     return x
 
 
-def policy_forward(params, act, obs_history, privileged_obs=None):
+ENCODER = "height_map_encoder.model"
+
+
+def policy_input(params, act, obs_history, num_obs=None):
+    """What the three bodies read.  ppo_cse: the observation history itself.  ppo_cse_cnn (params hold the encoder,
+    use_cnn = use_gru = False): process_obs_history, ppo_cse_cnn/actor_critic.py:181-198 -- every history row's height columns go
+    through the encoder (Linear, act, Linear, act; :46-52), recurrent_latent_embedding is the Identity, and the result is
+    cat(last row's scalars, [last row's scalars, last row's embedding])."""
+    if ENCODER + ".0.weight" not in params:
+        return obs_history
+    hm = params[ENCODER + ".0.weight"].shape[1]
+    emb_w = params[ENCODER + ".2.weight"].shape[0]
+    batch = obs_history.shape[0]
+    hist = obs_history.view(batch, -1, num_obs)
+    height_map = hist[:, :, -hm:].reshape(-1, hm)
+    emb = act(F.linear(act(F.linear(height_map, params[ENCODER + ".0.weight"], params[ENCODER + ".0.bias"])),
+                       params[ENCODER + ".2.weight"], params[ENCODER + ".2.bias"])).reshape(batch, -1, emb_w)
+    lstm_input = torch.cat([hist[:, :, :-hm], emb], dim=-1)
+    recurrent_latent = lstm_input                                                  # nn.Identity (:103)
+    return torch.cat([hist[:, -1, :-hm], recurrent_latent[:, -1, :]], dim=-1)
+
+
+def policy_forward(params, act, obs_history, privileged_obs=None, num_obs=None):
     """-> (mean, sigma, value).  update_distribution (actor_critic.py:118-121): the actor reads cat(obs_history,
     adaptation_module(obs_history)); evaluate (:155-157): the critic reads cat(obs_history, privileged_obs)."""
+    obs_history = policy_input(params, act, obs_history, num_obs)
     latent = mlp(params, "adaptation_module", obs_history, act)
     mean = mlp(params, "actor_body", torch.cat((obs_history, latent), dim=-1), act)
     sigma = mean * 0.0 + params["std"]
@@ -75,9 +100,9 @@ def gae(rewards, values, dones, last_values, gamma, lam):
     return returns, (adv - adv.mean()) / (adv.std() + 1e-8)
 
 
-def minibatch_loss(params, act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a):
+def minibatch_loss(params, act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a, num_obs=None):
     """ppo.py:104-141 for one minibatch.  -> (loss, surrogate_loss, value_loss, kl_mean or None)"""
-    mu, sigma, value = policy_forward(params, act, hist, priv)
+    mu, sigma, value = policy_forward(params, act, hist, priv, num_obs)
     logp = normal_log_prob(actions, mu, sigma)
     entropy = normal_entropy(sigma)
     kl_mean = None
@@ -123,7 +148,7 @@ class PpoPort:
     @torch.no_grad()
     def store(self, obs, priv, hist, actions, rewards, dones, time_outs=None):
         """PPO.act's bookkeeping (ppo.py:65-78) for GIVEN actions + process_env_step (:80-93) + add_transitions."""
-        mean, sigma, value = policy_forward(self.params, self.act, hist, priv)
+        mean, sigma, value = policy_forward(self.params, self.act, hist, priv, self.num_obs)
         t = self.step
         if t >= self.T:
             raise AssertionError("Rollout buffer overflow")
@@ -145,7 +170,7 @@ class PpoPort:
 
     @torch.no_grad()
     def compute_returns(self, last_hist, last_priv):
-        _, _, last_values = policy_forward(self.params, self.act, last_hist, last_priv)
+        _, _, last_values = policy_forward(self.params, self.act, last_hist, last_priv, self.num_obs)
         self.s["last_values"] = last_values
         self.s["returns"], self.s["advantages"] = gae(self.s["rewards"], self.s["values"], self.s["dones"], last_values,
                                                       self.args["gamma"], self.args["lam"])
@@ -168,7 +193,7 @@ class PpoPort:
                 target_values, advantages, returns = flat["values"][idx], flat["advantages"][idx], flat["returns"][idx]
                 old_logp, old_mu, old_sigma = flat["actions_log_prob"][idx], flat["mu"][idx], flat["sigma"][idx]
                 loss, surrogate_loss, value_loss, kl_mean = minibatch_loss(
-                    self.params, self.act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a)
+                    self.params, self.act, hist, priv, actions, target_values, advantages, returns, old_logp, old_mu, old_sigma, a, self.num_obs)
                 if kl_mean is not None:
                     if kl_mean > a["desired_kl"] * 2.0:
                         self.learning_rate = max(1e-5, self.learning_rate / 1.5)
@@ -185,7 +210,7 @@ class PpoPort:
                 sums["surrogate"] += surrogate_loss.item()
                 num_train = int(priv.shape[0] // 5 * 4)                     # ppo.py:160-161
                 for _sub in range(a["num_adaptation_module_substeps"]):
-                    pred = mlp(self.params, "adaptation_module", hist, self.act)
+                    pred = mlp(self.params, "adaptation_module", policy_input(self.params, self.act, hist, self.num_obs), self.act)
                     ad_loss = F.mse_loss(pred[:num_train], priv[:num_train])
                     ad_test = F.mse_loss(pred[num_train:], priv[num_train:])
                     self.adaptation_optimizer.zero_grad()

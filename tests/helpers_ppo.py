@@ -7,7 +7,13 @@ import numpy as np
 import torch
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-PPO_CASES = ["ppo_adaptive_64x8", "ppo_fixed_32x6"]
+PPO_CASES = ["ppo_adaptive_64x8", "ppo_fixed_32x6", "ppo_cnn_48x6"]      # the last one: go1_gym_learn/ppo_cse_cnn (row f4)
+
+
+def variant_module(g):
+    """legged_tracking_b200.ppo or .ppo_cnn, by the reference package the fixture was recorded from"""
+    from legged_tracking_b200 import ppo, ppo_cnn
+    return ppo_cnn if "meta/variant" in g and str(g["meta/variant"]) == "ppo_cse_cnn" else ppo
 
 
 def load_case(name):
@@ -26,13 +32,13 @@ class golden_args:
         self.g = g
 
     def __enter__(self):
-        from legged_tracking_b200 import ppo
-        self.saved = [(cls, k, getattr(cls, k)) for cls in (ppo.AC_Args, ppo.PPO_Args) for k in vars(cls)]
+        mod = variant_module(self.g)
+        self.saved = [(cls, k, getattr(cls, k)) for cls in (mod.AC_Args, mod.PPO_Args) for k in vars(cls)]
         for k, v in self.g.items():
             if k.startswith("ac_args/"):
-                setattr(ppo.AC_Args, k[8:], _val(v))
+                setattr(mod.AC_Args, k[8:], _val(v))
             elif k.startswith("ppo_args/"):
-                setattr(ppo.PPO_Args, k[9:], _val(v))
+                setattr(mod.PPO_Args, k[9:], _val(v))
         return self
 
     def __exit__(self, *a):
@@ -41,9 +47,8 @@ class golden_args:
 
 
 def actor_critic_from_golden(g, device="cpu"):
-    from legged_tracking_b200 import ppo
     N, T, no, npv, H, na = (int(x) for x in g["meta/sizes"])
-    ac = ppo.ActorCritic(no, npv, no * H, na)
+    ac = variant_module(g).ActorCritic(no, npv, no * H, na)
     sd = {k[5:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("init/")}
     ac.load_state_dict(sd, strict=True)
     return ac.to(device)

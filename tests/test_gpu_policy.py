@@ -92,9 +92,10 @@ def test_policy_forward_matches_oracle(name):
         for t in (0, T - 1):
             hist, priv = torch.from_numpy(g["in/hist"][t]), torch.from_numpy(g["in/priv"][t])
             with torch.no_grad():
-                mean, _, value = ppo_port.policy_forward(p64, act, hist.double(), priv.double())
-                latent = ppo_port.mlp(p64, "adaptation_module", hist.double(), act)
-                teacher = ppo_port.mlp(p64, "actor_body", torch.cat((hist.double(), priv.double()), dim=-1), act)
+                mean, _, value = ppo_port.policy_forward(p64, act, hist.double(), priv.double(), ac.num_obs)
+                pin = ppo_port.policy_input(p64, act, hist.double(), ac.num_obs)       # the history itself unless ppo_cse_cnn
+                latent = ppo_port.mlp(p64, "adaptation_module", pin, act)
+                teacher = ppo_port.mlp(p64, "actor_body", torch.cat((pin, priv.double()), dim=-1), act)
             info = {}
             got_mean = ac.act_student(hist.to(_dev()), policy_info=info)
             for got, want, what in ((got_mean, mean, "mean"), (torch.from_numpy(info["latents"]), latent, "latent"),
@@ -172,7 +173,7 @@ def _oracle_grads(ac, b, idx, args):
     act = ppo_port.ACTIVATIONS[ac.activation]
     s = {k: v.cpu().double()[idx.cpu()] for k, v in b.items()}
     loss, surr, vl, kl = ppo_port.minibatch_loss(p64, act, s["obs_history"], s["privileged_obs"], s["actions"], s["values"], s["advantages"],
-                                                 s["returns"], s["old_actions_log_prob"], s["old_mu"], s["old_sigma"], args)
+                                                 s["returns"], s["old_actions_log_prob"], s["old_mu"], s["old_sigma"], args, ac.num_obs)
     loss.backward()
     flat = torch.cat([p64[k].grad.reshape(-1) for k in ac.state_dict()])
     return flat, float(surr), float(vl), float(kl)
@@ -240,6 +241,108 @@ def test_minibatch_grad_matches_autograd(activation, B, count):
         if count > num_train:
             np.testing.assert_allclose(st[6] / st[7], float(torch.nn.functional.mse_loss(pred[num_train:], priv[num_train:])), rtol=2e-5)
     assert float(ac.grads[hi:].abs().sum()) == 0.0 and float(ac.grads[:lo].abs().sum()) == 0.0      # rest of the bucket untouched
+
+
+def _cnn_actor_critic(num_obs, P, H, A, shape, emb, seed, **ac_over):
+    from legged_tracking_b200 import ppo_cnn
+    args = ppo_cnn.AC_Args
+    saved = {k: getattr(args, k) for k in vars(args)}
+    try:
+        args.height_map_shape, args.cnn_num_embedding = shape, emb
+        for k, v in ac_over.items():
+            setattr(args, k, v)
+        torch.manual_seed(seed)
+        return ppo_cnn.ActorCritic(num_obs, P, num_obs * H, A).to(_dev())
+    finally:
+        for k, v in saved.items():
+            setattr(args, k, v)
+
+
+@pytest.mark.parametrize("activation,H,count", [("elu", 2, 517), ("tanh", 1, 300), ("elu", 3, 1)])
+def test_cnn_variant_minibatch_grad_matches_autograd(activation, H, count):
+    """Row f4 (go1_gym_learn/ppo_cse_cnn, MLP height-map encoder): the PPO minibatch gradient and the adaptation regression
+    gradient -- both reach the encoder through the three bodies' first layers -- against float64 autograd of the oracle."""
+    from legged_tracking_b200 import _abi, ppo
+    from oracle import ppo_port
+    lib = _abi.load()
+    ac = _cnn_actor_critic(44, 3, H, 12, (2, 4, 3), 40, 13, activation=activation, actor_hidden_dims=[96, 64], critic_hidden_dims=[80, 48],
+                           adaptation_module_branch_hidden_dims=[72, 24])
+    B = max(count, 64) + 100
+    b = _random_batch(ac, B, 6, _dev())
+    idx = torch.randperm(B, generator=torch.Generator().manual_seed(4))[:count].to(_dev())
+    ac.grads = torch.full((ac.num_params,), float("nan"), device=_dev())
+    ac._ready(count, training=True)
+    stats = torch.zeros(16, device=_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+    _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(idx), count, C.byref(hp), 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    want, surr, vl, kl = _oracle_grads(ac, b, idx, dict(ppo_port.PPO_DEFAULTS))
+    assert torch.isfinite(ac.grads).all()
+    _grad_close(ac, ac.grads, want, 1e-4, f"cnn {activation} H={H} B={count}")
+    st = stats.cpu().double()
+    np.testing.assert_allclose([st[0] / count, st[1] / count, st[2] / count], [surr, vl, kl], rtol=2e-5, atol=1e-6)
+    # adaptation step: encoder + adaptation module hold the gradient, nothing else is touched (ppo_cse_cnn/ppo.py:170-186)
+    num_train = count // 5 * 4
+    ac.grads.zero_()
+    _abi.check_policy(lib.lt_adaptation_grad(ac._h, C.byref(bp), _p(idx), count, num_train, 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    lo, hi = ac.body_slices["height_map_encoder"][0], ac.body_slices["adaptation_module"][1]
+    assert float(ac.grads[hi:].abs().sum()) == 0.0 and float(ac.grads[:lo].abs().sum()) == 0.0
+    if num_train > 0:
+        p64 = _params64(ac)
+        act = ppo_port.ACTIVATIONS[activation]
+        hist, priv = b["obs_history"].cpu().double()[idx.cpu()], b["privileged_obs"].cpu().double()[idx.cpu()]
+        pred = ppo_port.mlp(p64, "adaptation_module", ppo_port.policy_input(p64, act, hist, ac.num_obs), act)
+        loss = torch.nn.functional.mse_loss(pred[:num_train], priv[:num_train])
+        loss.backward()
+        got = ac.grads.cpu().double()
+        for key, _, a, e in ac.layout:
+            if lo <= a < hi:
+                w = p64[key].grad.reshape(-1)
+                scale = float(w.abs().max())
+                assert float((got[a:e] - w).abs().max()) <= 1e-4 * scale + 1e-12, key
+        st = stats.cpu().double()
+        np.testing.assert_allclose(st[4] / st[5], float(loss), rtol=2e-5)
+    s_lo, s_hi = C.c_int64(), C.c_int64()
+    _abi.check_policy(lib.lt_policy_adaptation_slice(ac._h, C.byref(s_lo), C.byref(s_hi)), ac._h)
+    assert (s_lo.value, s_hi.value) == (lo, hi)
+
+
+def test_cnn_variant_at_train_py_size_matches_fp32_torch():
+    """scripts/train.py without --old_ppo and without --measure_front_half: 503-wide observations (41 scalars + 2x21x11 heights),
+    encoder 462 -> 256 -> 256, default bodies on the 338-wide policy input.  16,384 rows forward and one gradient, against torch
+    fp32 autograd (TF32 off) of the oracle's loss on the same GPU."""
+    from legged_tracking_b200 import _abi, ppo
+    from oracle import ppo_port
+    lib = _abi.load()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    ac = _cnn_actor_critic(503, 2, 1, 12, (2, 21, 11), 256, 5)
+    assert ac.policy_input_dim == 338
+    rows = 16384
+    b = _random_batch(ac, rows, 3, _dev())
+    b["obs_history"].clamp_(-3, 3)
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in ac.state_dict().items()}
+    act = ppo_port.ACTIVATIONS["elu"]
+    with torch.no_grad():
+        mean, _, value = ppo_port.policy_forward(sd, act, b["obs_history"], b["privileged_obs"], 503)
+    _close(ac.act_student(b["obs_history"]), mean, 1e-5, 1e-5 * float(mean.abs().max()), "cnn mean")
+    _close(ac.evaluate(b["obs_history"], b["privileged_obs"]), value, 1e-5, 1e-5 * float(value.abs().max()), "cnn value")
+    idx = torch.randperm(rows, device=_dev())
+    ac.grads = torch.zeros(ac.num_params, device=_dev())
+    ac._ready(rows, training=True)
+    stats = torch.zeros(16, device=_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+    _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(idx), rows, C.byref(hp), 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    s = {k: v[idx] for k, v in b.items()}
+    loss, *_ = ppo_port.minibatch_loss(sd, act, s["obs_history"], s["privileged_obs"], s["actions"], s["values"], s["advantages"], s["returns"],
+                                       s["old_actions_log_prob"], s["old_mu"], s["old_sigma"], dict(ppo_port.PPO_DEFAULTS), 503)
+    loss.backward()
+    want = torch.cat([sd[k].grad.reshape(-1) for k in ac.state_dict()])
+    _grad_close(ac, ac.grads, want, 2e-4, "cnn @16384")          # fp32 torch on the other side: its own rounding is in the budget
 
 
 def test_sharded_gradients_sum_to_the_full_minibatch_gradient():

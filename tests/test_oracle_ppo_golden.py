@@ -9,7 +9,7 @@ import torch
 from oracle import ppo_port
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["ppo_adaptive_64x8", "ppo_fixed_32x6"]
+CASES = ["ppo_adaptive_64x8", "ppo_fixed_32x6", "ppo_cnn_48x6"]
 
 
 def load_case(name):

@@ -25,9 +25,10 @@ def test_state_dict_keys_shapes_and_flat_layout(name):
         assert o == ac.num_params == ac.flat.numel()
         assert list(sd)[0] == "std"
         assert [k.split(".")[0] for k in list(sd)[1:]] == sorted((k.split(".")[0] for k in list(sd)[1:]),
-                                                                 key=["adaptation_module", "actor_body", "critic_body"].index)
+                                                                 key=["height_map_encoder", "adaptation_module", "actor_body", "critic_body"].index)
         lo, hi = ac.body_slices["adaptation_module"]
-        assert lo == ac.num_actions and hi == ac.body_slices["actor_body"][0]
+        first = ac.body_slices["height_map_encoder"][0] if ac.encoder else lo       # the encoder sits in front of the adaptation module
+        assert first == ac.num_actions and hi == ac.body_slices["actor_body"][0]
 
 
 def test_default_initialisation_follows_the_reference_draw_order():
@@ -69,6 +70,37 @@ def test_exported_module_matches_reference_layout():
     for k, v in seq.state_dict().items():
         assert torch.equal(v, ac.state_dict()["actor_body." + k])
     torch.jit.script(seq)
+
+
+def test_cnn_variant_geometry_and_unbuilt_forms_are_loud():
+    """ppo_cse_cnn (row f4): policy_input = [s, s, emb] (ppo_cse_cnn/actor_critic.py:88-91, 194-197), draw order encoder first;
+    the Conv2d and GRU forms raise instead of falling back to torch."""
+    from legged_tracking_b200 import ppo_cnn
+    A = ppo_cnn.AC_Args
+    saved = {k: getattr(A, k) for k in vars(A)}
+    try:
+        A.height_map_shape, A.cnn_num_embedding = (2, 3, 4), 16
+        torch.manual_seed(3)
+        ac = ppo_cnn.ActorCritic(30, 2, 60, 5)
+        assert ac.policy_input_dim == 2 * (30 - 24) + 16 and ac.lstm_input_dim == 30 - 24 + 16
+        sd = ac.state_dict()
+        assert sd["height_map_encoder.model.0.weight"].shape == (256, 24) and sd["height_map_encoder.model.2.weight"].shape == (16, 256)
+        assert sd["adaptation_module.0.weight"].shape[1] == 28 and sd["actor_body.0.weight"].shape[1] == 30
+        torch.manual_seed(3)
+        lin = torch.nn.Linear(24, 256)
+        assert torch.equal(sd["height_map_encoder.model.0.weight"], lin.weight.detach())
+        assert [type(m).__name__ for m in ac.export_module("height_map_encoder.model")] == ["Linear", "ELU", "Linear", "ELU"]
+        for flag in ("use_cnn", "use_gru"):
+            setattr(A, flag, True)
+            with pytest.raises(NotImplementedError):
+                ppo_cnn.ActorCritic(30, 2, 60, 5)
+            setattr(A, flag, False)
+        A.height_map_shape = (2, 21, 11)                # 462 cells out of a 261-wide row: the reference's slice / reshape breaks too
+        with pytest.raises(ValueError):
+            ppo_cnn.ActorCritic(261, 2, 261, 12)
+    finally:
+        for k, v in saved.items():
+            setattr(A, k, v)
 
 
 def test_no_cpu_path():
