@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LT_ABI_VERSION 6
+#define LT_ABI_VERSION 7
 
 #define LT_MAX_DOF 12
 #define LT_MAX_FEET 4
@@ -54,7 +54,8 @@ enum {
     LT_TERM_REACH_GOAL_T, LT_TERM_REACH_GOAL_TT, LT_TERM_TASK, LT_TERM_EXPLORATION, LT_TERM_STALLING,
     LT_TERM_LINEAR_VEL, LT_TERM_LIN_VEL_Z, LT_TERM_FEET_AIR_TIME, LT_TERM_SURVIVE, LT_TERM_REACHING_LINEAR_VEL,
     LT_TERM_REACHING_YAW_ABS, LT_TERM_REACHING_YAW,
-    LT_TERM_EXTERNAL = 31    /* user plugin evaluated by the host in torch on the device: value read from extra_reward */
+    LT_TERM_EXTERNAL = 31,   /* user plugin evaluated by the host in torch on the device: value read from extra_reward */
+    LT_TERM_REACHING_LOCAL_GOAL = 32     /* trajectory_tracking_reward.py:95-97: plan_buf & replan (sampling-based planning only) */
 };
 enum { LT_FORM_EXP = 0, LT_FORM_L1 = 1, LT_FORM_L2 = 2, LT_FORM_PROD = 3 };
 enum { LT_TRAJ_FIXED_TARGET = 0, LT_TRAJ_RANDOM_GOAL = 1, LT_TRAJ_RANDOM_TARGET = 2 };
@@ -183,6 +184,8 @@ typedef struct lt_step_args {
     /* sampling-based planning (LR:856-916): this step's local target and its relative pose, as lt_plan_target_pose left them
      * ([N,6], [N,3], [N,3]); all three NULL = the local target is the global one (LR:917-920) */
     const float *local_target_poses, *local_relative_linear, *local_relative_rotation;
+    const uint8_t* replan;           /* [N] or NULL: this step's `replan` flags (LR:861) as lt_plan_target_pose wrote them; read by
+                                        LT_TERM_REACHING_LOCAL_GOAL only */
 } lt_step_args;
 
 typedef struct lt_handle lt_handle;
@@ -318,6 +321,7 @@ typedef struct lt_plan_args {
     int64_t* plan_length_buf;
     float *local_target_poses, *local_relative_linear, *local_relative_rotation;
     int32_t* chosen;
+    uint8_t* replan;                 /* [N] out or NULL: (plan_length_buf % plan_interval) == 0 after the increment (LR:858-861) */
 } lt_plan_args;
 int lt_plan_target_pose(const lt_plan_args* args, int32_t num_envs, int32_t n_points, int32_t n_cands, int32_t plan_interval,
                         int32_t root_stride, const float* robot_size, void* stream);

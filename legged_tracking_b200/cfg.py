@@ -160,7 +160,7 @@ def fused_reward_names(container_name):
     tracking = ["torques", "dof_vel", "dof_acc", "dof_pos", "collision", "action_rate", "dof_pos_limits", "orientation",
                 "task_old", "reach_goal", "reach_goal_t", "reach_goal_T", "task", "exploration", "stalling", "linear_vel",
                 "lin_vel_z", "ang_vel_xy", "feet_air_time", "survive", "reaching_linear_vel", "reaching_z", "reaching_roll",
-                "reaching_pitch", "reaching_yaw_abs", "reaching_yaw"]
+                "reaching_pitch", "reaching_yaw_abs", "reaching_yaw", "reaching_local_goal"]
     table = {"RewardsCrawling": crawling, "TrajectoryTrackingRewards": tracking}
     if container_name not in table:
         raise NotImplementedError(f"reward container {container_name!r} has no fused implementation (CoRLRewards: cfg 4, DESIGN.md section 8)")

@@ -495,6 +495,7 @@ struct lt_reward_ctx {
     float blv[3], bav[3], pg[3], rel_lin[3], rel_rot[3], loc_lin[3];
     float ep_f;                  // episode_length_buf as float
     int reached, n_collisions;
+    int local_goal;              // plan_buf & replan of this step (LR:847, 861)
 };
 
 // Row of lt_step_args.extra_reward ([n_external, N]) that belongs to term slot t: the k-th LT_TERM_EXTERNAL slot reads row k.
@@ -621,6 +622,7 @@ LT_HD float lt_reward_term(const lt_config& c, const lt_state_ptrs& st, int i, i
     }
     case LT_TERM_SURVIVE: return 1.0f;
     case LT_TERM_EXTERNAL: return extra_reward ? extra_reward[i] : 0.0f;
+    case LT_TERM_REACHING_LOCAL_GOAL: return r.local_goal ? 1.0f : 0.0f;      // trajectory_tracking_reward.py:95-97
     default: return 0.0f;
     }
 }
@@ -865,6 +867,7 @@ LT_HD lt_env_result lt_env_step(const lt_config& c, const lt_layout& L, const lt
     for (int k = 0; k < 3; ++k) { rc.blv[k] = P.blv[k]; rc.bav[k] = P.bav[k]; rc.pg[k] = P.pg[k];
                                   rc.rel_lin[k] = P.rel_lin[k]; rc.rel_rot[k] = P.rel_rot[k]; rc.loc_lin[k] = loc_lin[k]; }
     rc.ep_f = ep_f; rc.reached = reached; rc.n_collisions = n_coll;
+    rc.local_goal = (plan && args.replan && args.replan[i]) ? 1 : 0;
     float rew = 0.0f, rew_pos = 0.0f, rew_neg = 0.0f;
     for (int t = 0; t < c.n_terms; ++t) {
         const float v = lt_reward_term(c, st, i, c.term_ids[t], rc, lt_ext_row(c, args.extra_reward, t), false);

@@ -773,6 +773,7 @@ __global__ void __launch_bounds__(256) lt_sign_kernel(const __grid_constant__ lt
             rc.ep_f = (float)(p.st.episode_length_buf[i] + 1);
             rc.reached = 0;
             rc.n_collisions = 0;
+            rc.local_goal = 0;
             v = lt_reward_term(c, p.st, i, c.term_ids[t], rc, lt_ext_row(c, p.args.extra_reward, t), true) * c.term_scales[t];
         }
 #pragma unroll
@@ -1170,6 +1171,7 @@ static void lt_fill_step_params(lt_handle* h, const lt_step_args* args, lt_step_
             p.args.local_target_poses = args->local_target_poses;
             p.args.local_relative_linear = args->local_relative_linear;
             p.args.local_relative_rotation = args->local_relative_rotation;
+            p.args.replan = args->replan;
         }
         if (args->new_gravity) {
             p.sc.set_gravity = 1;

@@ -59,7 +59,9 @@ __global__ void __launch_bounds__(LT_PLAN_THREADS) lt_plan_kernel(const __grid_c
         // LR:858-868: plan_length_buf += 1; replan on the interval; always at the first step of an episode
         long long pl = a.plan_length_buf[e] + 1;
         const bool ep_start = a.episode_length_buf[e] == 1;
-        bool plan = ep_start || ((pl % p.plan_interval) == 0 && a.plan_buf[e] != 0);
+        const bool replan = (pl % p.plan_interval) == 0;
+        if (a.replan) a.replan[e] = replan ? 1 : 0;
+        bool plan = ep_start || (replan && a.plan_buf[e] != 0);
         if (plan) pl = 0;                             // LR:874
         a.plan_length_buf[e] = pl;
         s_mode = !plan ? 0 : (close ? 1 : 2);

@@ -310,6 +310,7 @@ class StepEngine:
         args.local_target_poses = pl.local_target_poses.data_ptr()
         args.local_relative_linear = pl.local_relative_linear.data_ptr()
         args.local_relative_rotation = pl.local_relative_rotation.data_ptr()
+        args.replan = pl.replan.data_ptr()
 
     def graph_replay_ok(self):
         """May the NEXT step be a replay of a CUDA graph captured from post_physics_step(advance_gravity=False)?  A captured

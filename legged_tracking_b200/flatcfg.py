@@ -27,6 +27,8 @@ REWARD_TERM_IDS = {
     "survive": 27, "reaching_linear_vel": 28, "reaching_yaw_abs": 29, "reaching_yaw": 30,
     # extra addend evaluated by a user plugin in torch on the device (see env.py)
     "external": 31,
+    # TrajectoryTrackingRewards term that exists only under sampling-based planning (trajectory_tracking_reward.py:95-97)
+    "reaching_local_goal": 32,
 }
 LIN_VEL_FORMS = {"exp": 0, "l1": 1, "l2": 2, "prod": 3}
 TRAJ_FUNCTIONS = {"fixed_target": 0, "random_goal": 1, "random_target": 2, "valid_goal": 3}
@@ -155,6 +157,9 @@ def check_supported(flat):
             problems.append(f"{k}=True")
     if flat["traj_function"] not in ("fixed_target", "random_goal", "random_target"):
         problems.append(f"commands.traj_function={flat['traj_function']!r}")
+    if "reaching_local_goal" in flat["reward_names"] and not (flat["sampling_based_planning"] and flat.get("plan_interval", 0) > 0):
+        problems.append("reward term 'reaching_local_goal' without sampling-based planning on a plan interval (the reference has no "
+                        "`replan` attribute then, LR:856-861)")
     for name in flat["reward_names"]:
         if name not in REWARD_TERM_IDS and name not in flat.get("external_reward_names", ()):
             problems.append(f"reward term {name!r} has no fused implementation")

@@ -37,6 +37,7 @@ class LocalPlanner:
         self.local_target_poses = z(self.N, 6)                                            # LR:1263
         self.local_relative_linear, self.local_relative_rotation = z(self.N, 3), z(self.N, 3)
         self.chosen = z(self.N, dt=torch.int32)
+        self.replan = z(self.N, dt=torch.uint8)                                           # LR:861
 
     def plan(self, target_poses, root_states, measured_heights, episode_length_buf, plan_buf, stream=None):
         """One call of _plan_target_pose for all envs.  -> local_target_poses (updated in place; also local_relative_* / chosen)."""
@@ -53,7 +54,8 @@ class LocalPlanner:
                         ("measured_heights", measured_heights), ("candidates", self.candidates),
                         ("episode_length_buf", episode_length_buf), ("plan_buf", pb), ("plan_length_buf", self.plan_length_buf),
                         ("local_target_poses", self.local_target_poses), ("local_relative_linear", self.local_relative_linear),
-                        ("local_relative_rotation", self.local_relative_rotation), ("chosen", self.chosen)):
+                        ("local_relative_rotation", self.local_relative_rotation), ("chosen", self.chosen),
+                        ("replan", self.replan)):
             setattr(a, name, t.data_ptr())
         st = stream if stream is not None else torch.cuda.current_stream(self.device)
         self._keep = pb

@@ -393,6 +393,18 @@ FIXTURES = {
     "planning_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path", "--penalty_scaler", "1.0"],
                         num_envs=32, num_rows=4, num_cols=4, steps=12, full_state_every=1, near_timeout_frac=0.7,
                         overrides={"commands.sampling_based_planning": True}, init_hook=_planning_init),
+    # the same with the TrajectoryTrackingRewards container and its planning-only term reaching_local_goal = plan_buf & replan
+    # (trajectory_tracking_reward.py:95-97; scale as in the archived hierarchical training scripts)
+    "planning_ttr_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path", "--penalty_scaler", "1.0"],
+                            num_envs=32, num_rows=4, num_cols=4, steps=12, full_state_every=1, near_timeout_frac=0.7,
+                            overrides={"commands.sampling_based_planning": True,
+                                       "rewards.reward_container_name": "TrajectoryTrackingRewards",
+                                       "reward_scales.e2e": 0.0, "reward_scales.exploration_lin": 0.0,
+                                       "reward_scales.exploration_yaw": 0.0, "reward_scales.base_height": 0.0,
+                                       "reward_scales.large_vel": 0.0, "reward_scales.reaching_local_goal": 100.0,
+                                       "reward_scales.task": 1.0, "reward_scales.stalling": 1.0,
+                                       "rewards.small_vel_threshold": 0.4, "rewards.large_dist_threshold": 1.5},
+                            init_hook=_planning_init),
     "opts_random_goal_P_32": dict(argv=COMMON + ["--camera_zero", "--strategy", "e2e", "--terrain", "single_path"],
                                   num_envs=32, num_rows=4, num_cols=4, steps=6, synth_kwargs={"rp_range": 1.9},
                                   overrides={"commands.traj_function": "random_goal", "commands.x_mean": 1.5,

@@ -121,4 +121,4 @@ def plan(target_poses, base_pos, base_quat, points_xy, measured_heights, candida
         chosen[e] = c
     lin, rot = relative_pose(local, base_pos, base_quat)                                                          # LR:914-916
     return dict(local_target_poses=local, plan_length_buf=pl, local_relative_linear=lin, local_relative_rotation=rot, chosen=chosen,
-                key_of_chosen=key_of)
+                key_of_chosen=key_of, replan=replan)

@@ -452,6 +452,7 @@ class OraclePort:
             self.local_target_poses = self.planned_target_poses
             self.local_relative_linear, self.local_relative_rotation = out["local_relative_linear"], out["local_relative_rotation"]
             self.planner_chosen = out["chosen"]
+            self.replan = out["replan"]                                                       # LR:861
         else:
             self.local_target_poses = self.target_poses                                      # LR:918-920
             self.local_relative_linear, self.local_relative_rotation = \
@@ -639,6 +640,9 @@ class OraclePort:
         r /= (torch.norm(self.base_lin_vel[:, :2], dim=1) + EPSILON)
         r *= (torch.norm(self.base_lin_vel[:, :2], dim=1) > f["small_vel_threshold"]).float()
         return r
+
+    def _reward_reaching_local_goal(self):                                                    # trajectory_tracking_reward.py:95-97
+        return torch.logical_and(self.plan_buf, self.replan)
 
     def _reward_stalling(self):
         f = self.flat

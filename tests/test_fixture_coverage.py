@@ -7,7 +7,7 @@ from tests import helpers as T
 
 
 def _fixtures():
-    return {n: T.load_fixture(n) for n in T.fixture_names()}
+    return {n: T.load_fixture(n) for n in T.fixture_names(planning=True)}
 
 
 def test_every_fused_reward_term_fires_in_some_fixture():

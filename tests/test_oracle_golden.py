@@ -28,7 +28,7 @@ def compare_state(port, want, tag):
     assert port.common_step_counter == int(want["common_step_counter"])
 
 
-@pytest.mark.parametrize("name", T.fixture_names())
+@pytest.mark.parametrize("name", T.fixture_names(planning=True))
 def test_port_reproduces_reference(name):
     fx = T.load_fixture(name)
     port = T.make_oracle(fx)

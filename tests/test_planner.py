@@ -113,14 +113,15 @@ def test_planner_kernel_matches_oracle_on_other_states(N, seed):
 # the planner INSIDE the env step: tests/golden/planning_32.npz is 12 steps of the unmodified reference with
 # cfg.commands.sampling_based_planning = True (oracle/gen_golden.py); tests/test_oracle_golden.py pins the oracle to it bit for bit.
 @pytest.mark.gpu
-def test_env_step_with_planning_matches_the_oracle_and_the_reference():
+@pytest.mark.parametrize("fixture", ["planning_32", "planning_ttr_32"])      # the second: TrajectoryTrackingRewards with reaching_local_goal
+def test_env_step_with_planning_matches_the_oracle_and_the_reference(fixture):
     """lt_measure_heights -> lt_plan_target_pose -> lt_post_physics_step (local target through lt_step_args) against the oracle
     port run side by side with the kernel's tie rule (planner_stable), every step, every state array; and against the reference
     recording itself on everything a tie cannot touch (a tie changes only the local target's z: observations, rewards, resets,
     commands and every x / y / rotation entry are the reference's)."""
     from legged_tracking_b200.engine import StepEngine
     from tests import helpers as T
-    fx = T.load_fixture("planning_32")
+    fx = T.load_fixture(fixture)
     eng = StepEngine(fx["flat"], T.sub(fx, "terrain/"), T.load_actuator(), device="cuda:0", export_height_indices=True)
     eng.load_state(T.sub(fx, "init/"))
     port = T.make_oracle(fx)
@@ -151,3 +152,7 @@ def test_env_step_with_planning_matches_the_oracle_and_the_reference():
         T.assert_close(f"step{k}/local_relative_rotation", T.to_np(st["local_relative_rotation"]), want["local_relative_rotation"])
         T.assert_close(f"step{k}/plan_buf", T.to_np(st["plan_buf"]).astype(bool), want["plan_buf"].astype(bool))
     assert n_planned >= 10           # the recording does exercise the candidate search (17 searches, 10 close-to-goal plans)
+    if fixture == "planning_ttr_32":     # and the planning-only reward term fired on the device (episode sums compared above)
+        names = fx["flat"]["reward_names"]
+        assert float(eng.state["episode_sums"][names.index("reaching_local_goal")].abs().sum()) > 0 or \
+            float(eng.state["finished_sums"][names.index("reaching_local_goal")].abs().sum()) > 0
