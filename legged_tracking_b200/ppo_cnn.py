@@ -10,7 +10,9 @@ Built: the default form -- AC_Args.use_cnn = False (HeightMapEncoder = Linear, a
 (recurrent_latent_embedding = Identity).  All of it runs inside liblt_b200 (lt_policy_config.height_map_size > 0): the encoder is
 two more tcgen05 contractions in front of the bodies, its gradient the sum of the three bodies' first-layer input gradients.
 Not built: use_cnn = True (two 3x3 convolutions + max-pools, CNN:36-45) and use_gru = True (nn.GRU over the history rows,
-CNN:100-101) -- both raise here; there is no torch fallback.
+CNN:100-101) -- both raise here; there is no torch fallback.  (In the reference the Conv2d form ends in Linear(3360, emb) and
+fails for the 2 x 21 x 11 map scripts/train.py configures; the GRU is seq-first and fed [batch, H, features], so it recurs over
+the batch dimension: DESIGN.md section 8.)
 """
 import math
 
