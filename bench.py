@@ -588,13 +588,18 @@ def run_b200(args, rank, world, local_rank):
     n_chunks = max(1, args.e2e_chunks)
     while n_env % n_chunks or (n_env // n_chunks) % 1024:
         n_chunks -= 1
+    shard_sizes = [n_env // n_chunks] * n_chunks
+    if args.e2e_shards:                       # explicit (uneven) shard sizes: a small first shard shortens the unoverlapped lead-in
+        shard_sizes = [int(x) for x in args.e2e_shards.split(",")]
+        if sum(shard_sizes) != n_env or any(m % 1024 for m in shard_sizes):
+            raise SystemExit("--e2e-shards must be multiples of 1024 that add up to --envs-per-gpu")
+        n_chunks = len(shard_sizes)
     ms_e2e = ms_e2e_single
     pipe = engines = None
     if n_chunks > 1:
         from legged_tracking_b200.engine import HostStepPipeline
-        M = n_env // n_chunks
         engines, h_in, h_out = [], [], []
-        for c in range(n_chunks):
+        for c, M in enumerate(shard_sizes):
             flat_c, terrain_c, act_c, synth_c = workload.make(args.config, num_envs=M, seed=2000 + 16 * rank + c)
             terrain_c = dict(terrain_c, tile_heights=eng.tile_heights) if hasattr(eng, "tile_heights") else terrain_c
             e_c = StepEngine(flat_c, terrain_c, act_c, device=dev, seed=101 + 16 * rank + c, envs_per_warp=args.epw)
@@ -615,8 +620,15 @@ def run_b200(args, rank, world, local_rank):
                     a.copy_(b)
         h_in = None
 
-        def e2e_pipe(k):
+        for k in range(3):
             pipe.step(packed[k % 2], h_out)
+        pipe_graphs = [] if args.no_graph else [pipe.capture(packed[r], h_out) for r in range(2)]
+
+        def e2e_pipe(k):
+            if pipe_graphs and pipe.graph_replay_ok():
+                pipe.replay(pipe_graphs[k % 2])
+            else:
+                pipe.step(packed[k % 2], h_out)
         for k in range(3):
             e2e_pipe(k)
         if dist:
@@ -691,6 +703,7 @@ def run_b200(args, rank, world, local_rank):
                     "ms_per_step": ms_e2e / ke, "steps": ke,
                     "link_gb_per_s_per_rank": (h2d + d2h) * ke / (ms_e2e * 1e-3) / 1e9,
                     "path": f"engine.HostStepPipeline: {n_chunks} env shards on {n_chunks} streams (H2D, kernels and D2H of different shards overlap)"
+                            + ("" if args.no_graph else ", the whole pipelined step replayed as one CUDA graph")
                             if n_chunks > 1 else "single engine, one stream",
                     "single_stream": {"value": world * n_env * ke / (ms_e2e_single * 1e-3), "ms_per_step": ms_e2e_single / ke}},
             "post_physics_only": {"value": world * n_env / (ms_post * 1e-3), "unit": UNIT, "ms_per_step": ms_post},
@@ -723,6 +736,7 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--epw", type=int, default=0, help="envs per warp of the step kernel (0 = auto)")
     ap.add_argument("--e2e-chunks", type=int, default=4, help="env shards of the pipelined host-buffer step (1 = single stream)")
+    ap.add_argument("--e2e-shards", default="", help="explicit env-shard sizes of the pipelined host-buffer step, e.g. 4096,12288,16384,16384,16384")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-ppo", action="store_true", help="skip the PPO-iteration timing (rollout + GAE + update)")

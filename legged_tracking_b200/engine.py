@@ -469,9 +469,8 @@ class HostStepPipeline:
     def num_envs(self):
         return sum(e.N for e in self.engines)
 
-    def step(self, host_in, host_out):
-        """Issue every shard's copies and kernels on its stream, then wait for all of them (the caller needs obs / rew / done
-        of every env before it can act again)."""
+    def _issue(self, host_in, host_out, advance_gravity=True):
+        """Fork from the current stream to the shard streams, issue every shard's copies and kernels, join back."""
         cur = torch.cuda.current_stream()
         for s in self.streams:
             s.wait_stream(cur)
@@ -479,29 +478,48 @@ class HostStepPipeline:
             with torch.cuda.stream(s):
                 if "packed" in hi:
                     blk.copy_(hi["packed"], non_blocking=True)         # the whole shard in one transfer
-                    for sub in range(len(own["dof"])):
-                        e.bind_sim(dof_state=own["dof"][sub])
-                        e.compute_torques(own["actions"], sub)
-                    e.post_physics_step()
-                    ho["obs"].copy_(e.state["obs_buf"], non_blocking=True)
-                    ho["priv"].copy_(e.state["privileged_obs_buf"], non_blocking=True)
-                    ho["rew"].copy_(e.state["rew_buf"], non_blocking=True)
-                    ho["done"].copy_(e.state["reset_buf"], non_blocking=True)
-                    continue
-                # the shard's replayed inputs go up as ONE uninterrupted burst (a copy that waits for the previous sub-step's
-                # kernel leaves the up-link idle for a copy-engine / compute hand-over every sub-step: 34 GB/s instead of ~50)
-                own["actions"].copy_(hi["actions"], non_blocking=True)
-                for sub, dof in enumerate(hi["dof"]):
-                    own["dof"][sub].copy_(dof, non_blocking=True)     # what PhysX hands back after sub-step `sub`
-                own["root"].copy_(hi["root"], non_blocking=True)
-                own["contact"].copy_(hi["contact"], non_blocking=True)
-                for sub in range(len(hi["dof"])):
+                else:
+                    # the shard's replayed inputs go up as ONE uninterrupted burst (a copy that waits for the previous sub-step's
+                    # kernel leaves the up-link idle for a copy-engine / compute hand-over every sub-step: 34 GB/s instead of ~50)
+                    own["actions"].copy_(hi["actions"], non_blocking=True)
+                    for sub, dof in enumerate(hi["dof"]):
+                        own["dof"][sub].copy_(dof, non_blocking=True)     # what PhysX hands back after sub-step `sub`
+                    own["root"].copy_(hi["root"], non_blocking=True)
+                    own["contact"].copy_(hi["contact"], non_blocking=True)
+                for sub in range(len(own["dof"])):
                     e.bind_sim(dof_state=own["dof"][sub])
                     e.compute_torques(own["actions"], sub)
-                e.post_physics_step()
+                e.post_physics_step(advance_gravity=advance_gravity)
                 ho["obs"].copy_(e.state["obs_buf"], non_blocking=True)
                 ho["priv"].copy_(e.state["privileged_obs_buf"], non_blocking=True)
                 ho["rew"].copy_(e.state["rew_buf"], non_blocking=True)
                 ho["done"].copy_(e.state["reset_buf"], non_blocking=True)
         for s in self.streams:
-            s.synchronize()
+            cur.wait_stream(s)
+
+    def step(self, host_in, host_out):
+        """Issue every shard's copies and kernels on its stream, then wait for all of them (the caller needs obs / rew / done
+        of every env before it can act again)."""
+        self._issue(host_in, host_out)
+        torch.cuda.current_stream().synchronize()
+
+    def capture(self, host_in, host_out):
+        """The whole pipelined step -- every shard's upload, kernels and downloads, forked over the shard streams -- as ONE CUDA
+        graph bound to these pinned buffers (a simulator that keeps writing its state into the same alloc_host_inputs() blocks
+        replays it every step).  One graph launch replaces ~15 Python-issued calls per shard, which is what lets more, smaller
+        shards pay off: the first shard's upload + kernels and the last shard's download are the only unoverlapped parts."""
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=self.engines[0].device)
+        with torch.cuda.graph(g, stream=side):
+            self._issue(host_in, host_out, advance_gravity=False)
+        return g
+
+    def graph_replay_ok(self):
+        return all(e.graph_replay_ok() for e in self.engines)
+
+    def replay(self, graph):
+        """One step by graph replay (only when graph_replay_ok(): no gravity event, no reward-scale change on this step)."""
+        graph.replay()
+        for e in self.engines:
+            e.gravity.common_step_counter += 1
+        torch.cuda.current_stream().synchronize()

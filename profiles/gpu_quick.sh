@@ -1,2 +1,8 @@
 mkdir -p gpurun_out
-timeout 900 python profiles/phase_probe.py 65536 300 > gpurun_out/phase_probe.log 2>&1
+rm -f gpurun_out/chunks.log
+for c in 4096,12288,16384,16384,16384 2048,6144,8192,16384,16384,16384 2048,4096,8192,12288,12288,12288,14336 8192,8192,16384,16384,16384; do
+  python bench.py --steps 300 --warmup 5 --no-ppo --no-cpu --e2e-shards $c 2>gpurun_out/bench_err.log | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('shards $c', d['e2e']['value'], d['e2e']['ms_per_step'], d['value'])" >> gpurun_out/chunks.log 2>&1
+done
+tail -n 5 gpurun_out/bench_err.log
