@@ -58,3 +58,48 @@ def test_pipeline_equals_sequential_shards():
             assert torch.equal(ho["rew"], eng.state["rew_buf"].cpu()), k
             assert torch.equal(ho["done"], eng.state["reset_buf"].cpu().bool()), k
             assert torch.equal(ho["priv"], eng.state["privileged_obs_buf"].cpu()), k
+
+
+def test_captured_pipeline_step_equals_the_eager_one():
+    """HostStepPipeline.capture / replay: the whole pipelined step (uploads, kernels and downloads of uneven shards forked over
+    their streams) as one CUDA graph gives what the eagerly issued shards give, step after step, with new host data written
+    into the same pinned blocks before every replay."""
+    from legged_tracking_b200.engine import HostStepPipeline
+    sizes = (256, 768, 512)
+    a = [_shard(60 + c, n) for c, n in enumerate(sizes)]
+    b = [_shard(60 + c, n) for c, n in enumerate(sizes)]
+    pa, pb = HostStepPipeline([e for _, e, _ in a]), HostStepPipeline([e for _, e, _ in b])
+    mk_out = lambda: [{"obs": torch.empty(n, flat["num_obs"]).pin_memory(), "priv": torch.empty(n, flat["num_privileged_obs"]).pin_memory(),   # noqa: E731
+                       "rew": torch.empty(n).pin_memory(), "done": torch.empty(n, dtype=torch.bool).pin_memory()}
+                      for (flat, _, _), n in zip(a, sizes)]
+    out_a, out_b = mk_out(), mk_out()
+    packed_a, packed_b = pa.alloc_host_inputs(), pb.alloc_host_inputs()
+
+    def fill(packed, k):
+        for dst, (flat, _, synth), n in zip(packed, a, sizes):
+            src = _host_inputs(flat, synth, k, n)
+            dst["actions"].copy_(src["actions"]); dst["root"].copy_(src["root"]); dst["contact"].copy_(src["contact"])
+            for a_, b_ in zip(dst["dof"], src["dof"]):
+                a_.copy_(b_)
+    fill(packed_a, 0)
+    fill(packed_b, 0)
+    pa.step(packed_a, out_a)                                   # warm-up step on both, eagerly
+    pb.step(packed_b, out_b)
+    graph = pa.capture(packed_a, out_a)                        # capture does not execute: state is untouched
+    replays = 0
+    for k in range(1, 5):
+        fill(packed_a, k)
+        fill(packed_b, k)
+        if pa.graph_replay_ok():
+            pa.replay(graph)
+            replays += 1
+        else:
+            pa.step(packed_a, out_a)
+        pb.step(packed_b, out_b)
+        for oa, ob in zip(out_a, out_b):
+            for key in ("obs", "priv", "rew", "done"):
+                assert torch.equal(oa[key], ob[key]), (k, key)
+    assert replays >= 3
+    for (_, ea, _), (_, eb, _) in zip(a, b):
+        assert torch.equal(ea.state["episode_sums"], eb.state["episode_sums"])
+        assert ea.gravity.common_step_counter == eb.gravity.common_step_counter
