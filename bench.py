@@ -607,10 +607,9 @@ def run_b200(args, rank, world, local_rank):
             engines.append(e_c)
             rs_c = ReplaySets(e_c, synth_c, flat_c, 2, pinned_host=True)
             h_in.append(rs_c.host)
-            h_out.append({"obs": torch.empty(M, flat["num_obs"]).pin_memory(), "priv": torch.empty(M, flat["num_privileged_obs"]).pin_memory(),
-                          "rew": torch.empty(M).pin_memory(), "done": torch.empty(M, dtype=torch.bool).pin_memory()})
             del rs_c
         pipe = HostStepPipeline(engines)
+        h_out = pipe.alloc_host_outputs()                             # obs / priv / rew / done + the reset write-back rows
         packed = [pipe.alloc_host_inputs() for _ in range(2)]          # the replayed simulator state, kept in the pipeline's pinned layout
         for r in range(2):
             for c in range(n_chunks):
@@ -629,6 +628,9 @@ def run_b200(args, rank, world, local_rank):
                 pipe.replay(pipe_graphs[k % 2])
             else:
                 pipe.step(packed[k % 2], h_out)
+            for ho in h_out:                                          # what a caller does next: more resets than write-back rows?
+                if int(ho["reset_count"][0]) > ho["reset_ids"].shape[0]:
+                    raise RuntimeError("reset write-back capacity exceeded: the bench would have to read the full state tensors")
         for k in range(3):
             e2e_pipe(k)
         if dist:
@@ -640,6 +642,9 @@ def run_b200(args, rank, world, local_rank):
         ms_e2e, ms_e2e_single = [float(x) for x in t.tolist()]
     h2d = sum(int(x.numel()) * 4 for x in (own["actions"], own["root"], own["contact"])) + flat["decimation"] * own["dof"].numel() * 4
     d2h = sum(int(v.numel()) * v.element_size() for v in out_h.values())
+    d2h_writeback = 0
+    if n_chunks > 1:                                                  # the pipelined path also brings the reset rows down
+        d2h_writeback = sum(int(v.numel()) * v.element_size() for ho in h_out for k, v in ho.items() if k.startswith("reset_"))
 
     peak, peak_src = measured_peaks()
     strong = None
@@ -699,9 +704,10 @@ def run_b200(args, rank, world, local_rank):
             "data": "synthetic",
             "config": workload_config(args, world, n_env, alg['full_step'] * n_env / 1e6),
             "clocks": sampler.summary(), "gpu_launches": launches_per_step * args.steps,
-            "e2e": {"value": world * n_env * ke / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "e2e": {"value": world * n_env * ke / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h + d2h_writeback,
                     "ms_per_step": ms_e2e / ke, "steps": ke,
-                    "link_gb_per_s_per_rank": (h2d + d2h) * ke / (ms_e2e * 1e-3) / 1e9,
+                    "reset_writeback_bytes_per_step": d2h_writeback,      # fixed-capacity rows of the envs the step reset (root + dof state)
+                    "link_gb_per_s_per_rank": (h2d + d2h + d2h_writeback) * ke / (ms_e2e * 1e-3) / 1e9,
                     "path": f"engine.HostStepPipeline: {n_chunks} env shards on {n_chunks} streams (H2D, kernels and D2H of different shards overlap)"
                             + ("" if args.no_graph else ", the whole pipelined step replayed as one CUDA graph")
                             if n_chunks > 1 else "single engine, one stream",

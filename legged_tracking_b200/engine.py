@@ -421,6 +421,11 @@ class HostStepPipeline:
 
     host_in (pinned, per shard k):  actions [M,12], dof [decimation][M*12,2], root [M*A,13], contact [M,B,3]
     host_out (pinned, per shard k): obs [M,num_obs], priv [M,num_priv], rew [M], done [M] bool
+      and, optionally, the write-back of what a reset changed inside the simulator state (the reference pushes it with
+      set_actor_root_state_tensor_indexed / set_dof_state_tensor_indexed, LR:1010-1013, 1049-1052) -- alloc_host_outputs(cap):
+      reset_count int32[1], reset_ids int64[cap] (ascending; the first reset_count are valid), reset_root [cap,13], reset_dof
+      [cap,24]: the robot root state and (pos, vel) rows of the envs that were reset this step.  A step with more than `cap`
+      resets in a shard is reported by reset_count > cap; the caller then reads the full tensors (StepEngine.root_states / dof_state).
     """
 
     def __init__(self, engines):
@@ -465,6 +470,40 @@ class HostStepPipeline:
                         "root": views["root"], "contact": views["contact"]})
         return out
 
+    @staticmethod
+    def _tail_views(block, layout):
+        views = {}
+        for name, off, nbytes, dt, shape in layout:
+            views[name] = block[off:off + nbytes].view(dt).view(*shape)
+        return views
+
+    def alloc_host_outputs(self, reset_capacity=None):
+        """Pinned result blocks, one dict per shard: "obs", and "tail" = ONE byte block holding priv | rew | done | reset_count |
+        reset_ids | reset_root | reset_dof (the other keys are views into it), so that a shard's results come down in two
+        transfers -- every extra small copy costs the down-link a hand-over.  reset_capacity = write-back rows per shard
+        (default N/8)."""
+        out = []
+        self._tail_dev = []
+        for e in self.engines:
+            f = e.flat
+            cap = int(reset_capacity) if reset_capacity is not None else max(e.N // 8, 1)
+            cap = min(cap, e.N)
+            segs = [("priv", torch.float32, (e.N, f["num_privileged_obs"])), ("rew", torch.float32, (e.N,)), ("done", torch.bool, (e.N,)),
+                    ("reset_count", torch.int32, (1,)), ("reset_ids", torch.int64, (cap,)), ("reset_root", torch.float32, (cap, 13)),
+                    ("reset_dof", torch.float32, (cap, 2 * f["num_dof"]))]
+            layout, off = [], 0
+            for name, dt, shape in segs:
+                nbytes = int(np.prod(shape)) * torch.empty((), dtype=dt).element_size()
+                layout.append((name, off, nbytes, dt, shape))
+                off = (off + nbytes + 15) // 16 * 16
+            host = torch.zeros(off, dtype=torch.uint8).pin_memory()
+            dev = torch.zeros(off, dtype=torch.uint8, device=e.device)
+            ho = {"obs": torch.zeros(e.N, f["num_obs"]).pin_memory(), "tail": host}
+            ho.update(self._tail_views(host, layout))
+            out.append(ho)
+            self._tail_dev.append((host.data_ptr(), dev, self._tail_views(dev, layout)))
+        return out
+
     @property
     def num_envs(self):
         return sum(e.N for e in self.engines)
@@ -474,7 +513,7 @@ class HostStepPipeline:
         cur = torch.cuda.current_stream()
         for s in self.streams:
             s.wait_stream(cur)
-        for e, s, own, blk, hi, ho in zip(self.engines, self.streams, self.dev_in, self._packed_dev, host_in, host_out):
+        for c, (e, s, own, blk, hi, ho) in enumerate(zip(self.engines, self.streams, self.dev_in, self._packed_dev, host_in, host_out)):
             with torch.cuda.stream(s):
                 if "packed" in hi:
                     blk.copy_(hi["packed"], non_blocking=True)         # the whole shard in one transfer
@@ -491,9 +530,26 @@ class HostStepPipeline:
                     e.compute_torques(own["actions"], sub)
                 e.post_physics_step(advance_gravity=advance_gravity)
                 ho["obs"].copy_(e.state["obs_buf"], non_blocking=True)
-                ho["priv"].copy_(e.state["privileged_obs_buf"], non_blocking=True)
-                ho["rew"].copy_(e.state["rew_buf"], non_blocking=True)
-                ho["done"].copy_(e.state["reset_buf"], non_blocking=True)
+                if "tail" in ho:                                        # alloc_host_outputs: everything else in ONE transfer
+                    key, dev_block, tv = self._tail_dev[c]
+                    if key != ho["tail"].data_ptr():
+                        raise ValueError("host_out was not made by this pipeline's last alloc_host_outputs()")
+                    cap = tv["reset_ids"].shape[0]
+                    ids = e.state["reset_env_ids"][:cap]
+                    safe = ids.clamp(0, e.N - 1)                        # entries past reset_count are stale
+                    tv["priv"].copy_(e.state["privileged_obs_buf"])
+                    tv["rew"].copy_(e.state["rew_buf"])
+                    tv["done"].copy_(e.state["reset_buf"])
+                    tv["reset_count"].copy_(e.state["reset_count"])
+                    tv["reset_ids"].copy_(ids)
+                    # rows the step rewrote on reset, for a host-resident simulator (LR:1010-1013, 1049-1052)
+                    torch.index_select(own["root"].view(e.N, -1, 13)[:, 0, :], 0, safe, out=tv["reset_root"])
+                    torch.index_select(own["dof"][-1].view(e.N, -1), 0, safe, out=tv["reset_dof"])
+                    ho["tail"].copy_(dev_block, non_blocking=True)
+                else:
+                    ho["priv"].copy_(e.state["privileged_obs_buf"], non_blocking=True)
+                    ho["rew"].copy_(e.state["rew_buf"], non_blocking=True)
+                    ho["done"].copy_(e.state["reset_buf"], non_blocking=True)
         for s in self.streams:
             cur.wait_stream(s)
 

@@ -103,3 +103,26 @@ def test_captured_pipeline_step_equals_the_eager_one():
     for (_, ea, _), (_, eb, _) in zip(a, b):
         assert torch.equal(ea.state["episode_sums"], eb.state["episode_sums"])
         assert ea.gravity.common_step_counter == eb.gravity.common_step_counter
+
+
+def test_reset_write_back_rows_are_what_the_step_wrote():
+    """alloc_host_outputs: the rows a reset rewrote inside the simulator state (robot root state, dof pos / vel) come down with
+    the step's results, for exactly the envs of reset_buf.nonzero(), in ascending order (LR:143, 1010-1013, 1049-1052)."""
+    from legged_tracking_b200.engine import HostStepPipeline
+    n = 1024
+    flat, eng, synth = _shard(77, n)
+    eng.state["episode_length_buf"].fill_(int(flat["max_episode_length"]) - 1)          # two steps from a time-out for everyone ...
+    eng.state["episode_length_buf"][::7] = int(flat["max_episode_length"])              # ... and every 7th env times out now
+    pipe = HostStepPipeline([eng])
+    out = pipe.alloc_host_outputs(reset_capacity=256)
+    pipe.step([_host_inputs(flat, synth, 0, n)], out)
+    ho = out[0]
+    cnt = int(ho["reset_count"][0])
+    want_ids = ho["done"].nonzero().flatten()
+    assert cnt == want_ids.numel() and 0 < cnt <= 256
+    assert torch.equal(ho["reset_ids"][:cnt], want_ids)
+    root = eng.root_states.view(n, -1, 13)[:, 0, :].cpu()
+    dof = eng.dof_state.view(n, -1).cpu()
+    assert torch.equal(ho["reset_root"][:cnt], root[want_ids])
+    assert torch.equal(ho["reset_dof"][:cnt], dof[want_ids])
+    assert float(ho["reset_dof"][:cnt, 1::2].abs().max()) == 0.0                          # dof_vel = 0 after _reset_dofs (LR:1008)
