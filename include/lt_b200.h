@@ -388,6 +388,35 @@ typedef struct lt_corl_ptrs {
 } lt_corl_ptrs;
 int lt_corl_rewards(const lt_corl_cfg* cfg, const lt_corl_ptrs* ptrs, void* stream);
 
+/* LeggedRobot._resample_commands (LRV:728-842), the device half.  The curricula (RewardThresholdCurriculum, curriculum.py:113-159:
+ * numpy weight grids, updated from the finished episodes' command_sums and sampled with numpy's RandomState) stay on the host, as
+ * in the reference; what they return -- one sampled command row and one category per resampled env -- comes in here and the call
+ * does everything the reference then does to the env tensors, in ONE launch instead of ~40 indexed torch ops:
+ *   commands[env] = new row (LRV:776-777); the gait-category rewrite of the phase / offset / bound columns 5..7 -- by the env's
+ *   curriculum category when gaitwise_curricula (LRV:780-797), else by a uniform draw per env for exclusive_phase_offset
+ *   (LRV:799-809) or balance_gait_distribution (LRV:811-828); binary_phases rounding round(2c)/2 % 1 (LRV:830-833); zeroing of
+ *   the planar velocity command when its norm is <= 0.2 (LRV:836); command_sums[:, env] = 0 (LRV:839-840). */
+#define LT_GAIT_PRONK 0              /* category_gait values: the reference's category_names (LRV:1319-1321) */
+#define LT_GAIT_TROT 1
+#define LT_GAIT_PACE 2
+#define LT_GAIT_BOUND 3
+#define LT_GAIT_NONE -1              /* 'nominal': no rewrite */
+#define LT_CMD_MAX_CATEGORIES 8
+typedef struct lt_cmd_cfg {
+    int32_t num_envs, num_commands, n_sums;
+    int32_t gaitwise_curricula, exclusive_phase_offset, balance_gait_distribution, binary_phases;     /* cfg.commands.* */
+    int32_t n_categories, category_gait[LT_CMD_MAX_CATEGORIES];
+} lt_cmd_cfg;
+typedef struct lt_cmd_ptrs {
+    const int64_t* env_ids;          /* [count] envs being resampled */
+    const float* new_commands;       /* [count, num_commands]: curriculum.sample()[0][:, :num_commands], row k for env_ids[k] */
+    const int32_t* category;         /* [count] curriculum category of each env (LRV:760-766) */
+    const float* gait_uniform;       /* [count] the second torch.rand draw (LRV:800, 812) or NULL when gaitwise_curricula */
+    float* commands;                 /* [N, num_commands] in / out */
+    float* command_sums;             /* [n_sums, N] or NULL: rows zeroed at env_ids */
+} lt_cmd_ptrs;
+int lt_resample_commands(const lt_cmd_cfg* cfg, const lt_cmd_ptrs* ptrs, int32_t count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

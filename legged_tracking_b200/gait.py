@@ -110,3 +110,71 @@ class CoRLRewardKernel:
         self._keep = keep
         _abi.check(self.lib.lt_corl_rewards(C.byref(c), C.byref(p), C.c_void_p(st.cuda_stream)), None, "lt_corl_rewards")
         return self.out
+
+
+GAIT_IDS = {"pronk": "LT_GAIT_PRONK", "trot": "LT_GAIT_TROT", "pace": "LT_GAIT_PACE", "bound": "LT_GAIT_BOUND"}
+
+
+class CommandResampler:
+    """The device half of LeggedRobot._resample_commands (legged_robot_velocity_tracking.py:776-840) as ONE launch of
+    lt_resample_commands: new command rows into `commands`, the gait-category rewrite of the phase / offset / bound columns,
+    binary-phase rounding, small-velocity zeroing, command_sums reset.  The curricula that produce the rows (RewardThresholdCurriculum,
+    numpy) stay with the caller, as in the reference.
+
+    category_names: the reference's list (['pronk', 'trot', 'pace', 'bound'] under gaitwise_curricula, else ['nominal']);
+    commands [N, num_commands] and command_sums [n_sums, N] (or None) are the env's own tensors, updated in place."""
+
+    def __init__(self, commands, command_sums, category_names, gaitwise_curricula=False, exclusive_phase_offset=False,
+                 balance_gait_distribution=False, binary_phases=False):
+        self.device = _need_cuda(commands.device, "CommandResampler")
+        self.lib = _abi.load()
+        ok = lambda t: t.dtype == torch.float32 and t.is_contiguous() and t.device == self.device      # noqa: E731
+        if not ok(commands) or commands.dim() != 2:
+            raise ValueError("commands: expected a contiguous float32 [N, num_commands] CUDA tensor")
+        if command_sums is not None and (not ok(command_sums) or command_sums.dim() != 2 or command_sums.shape[1] != commands.shape[0]):
+            raise ValueError("command_sums: expected a contiguous float32 [n_sums, N] tensor on the same device")
+        if len(category_names) > _abi.DEFINES["LT_CMD_MAX_CATEGORIES"]:
+            raise ValueError("too many command categories")
+        self.commands, self.command_sums, self.category_names = commands, command_sums, list(category_names)
+        c = _abi.lt_cmd_cfg()
+        c.num_envs, c.num_commands = int(commands.shape[0]), int(commands.shape[1])
+        c.n_sums = int(command_sums.shape[0]) if command_sums is not None else 0
+        c.gaitwise_curricula, c.exclusive_phase_offset = int(bool(gaitwise_curricula)), int(bool(exclusive_phase_offset))
+        c.balance_gait_distribution, c.binary_phases = int(bool(balance_gait_distribution)), int(bool(binary_phases))
+        c.n_categories = len(self.category_names)
+        for i, name in enumerate(self.category_names):
+            c.category_gait[i] = _abi.DEFINES[GAIT_IDS[name]] if name in GAIT_IDS else _abi.DEFINES["LT_GAIT_NONE"]
+        self.cfg = c
+
+    def categories_from_uniform(self, u):
+        """LRV:760-766 on the device: category i takes the envs whose draw lies in [i / n, (i + 1) / n)."""
+        n = len(self.category_names)
+        p = 1.0 / n
+        cat = torch.full(u.shape, -1, dtype=torch.int32, device=u.device)
+        for i in range(n):
+            cat[torch.logical_and(p * i <= u, u < p * (i + 1))] = i
+        return cat
+
+    def apply(self, env_ids, new_commands, category=None, gait_uniform=None, stream=None):
+        """env_ids int64 [K]; new_commands [K, >= num_commands] (what curriculum.sample returned, any float dtype, host or device);
+        category int32 [K] (needed under gaitwise_curricula); gait_uniform float32 [K] (the second torch.rand draw of the
+        exclusive_phase_offset / balance_gait_distribution branches)."""
+        K = int(env_ids.numel())
+        if K == 0:
+            return
+        dev = self.device
+        ids = env_ids.to(device=dev, dtype=torch.int64).contiguous()
+        new = torch.as_tensor(new_commands)[:, :self.cfg.num_commands].to(device=dev, dtype=torch.float32).contiguous()
+        if new.shape[0] != K:
+            raise ValueError("new_commands: one row per resampled env")
+        cat = None if category is None else torch.as_tensor(category).to(device=dev, dtype=torch.int32).contiguous()
+        gu = None if gait_uniform is None else torch.as_tensor(gait_uniform).to(device=dev, dtype=torch.float32).contiguous()
+        p = _abi.lt_cmd_ptrs()
+        p.env_ids, p.new_commands = ids.data_ptr(), new.data_ptr()
+        p.category = cat.data_ptr() if cat is not None else None
+        p.gait_uniform = gu.data_ptr() if gu is not None else None
+        p.commands = self.commands.data_ptr()
+        p.command_sums = self.command_sums.data_ptr() if self.command_sums is not None else None
+        st = stream if stream is not None else torch.cuda.current_stream(dev)
+        self._keep = (ids, new, cat, gu)
+        _abi.check(self.lib.lt_resample_commands(C.byref(self.cfg), C.byref(p), K, C.c_void_p(st.cuda_stream)), None, "lt_resample_commands")
