@@ -417,6 +417,65 @@ typedef struct lt_cmd_ptrs {
 } lt_cmd_ptrs;
 int lt_resample_commands(const lt_cmd_cfg* cfg, const lt_cmd_ptrs* ptrs, int32_t count, void* stream);
 
+/* -------------------------------------------------------------------------------------------------------------
+ * cfg 4: LeggedRobot.post_physics_step of the velocity-tracking env (LRV:108-154) as a chain of launches around the three
+ * calls above.  Order of one step (legged_tracking_b200/vel_env.py is the host mirror):
+ *   lt_vel_pre                episode_length_buf += 1, body-frame velocities, projected gravity, foot positions / velocities,
+ *                             check_termination (LRV:156-167), the callback's two interval masks (LRV:702-703, 715-716)
+ *   [host]                    _resample_commands of the due envs: curricula on the host, lt_resample_commands
+ *   lt_step_contact_targets   LRV:705
+ *   lt_corl_rewards           every active CoRLRewards term, unscaled, [n_terms, N]
+ *   lt_vel_reward             compute_reward (LRV:281-318): scales, all-env sign buckets, episode / command sums, ji22 or clip
+ *   [host]                    reset_idx of reset_buf.nonzero() (LRV:169-265): rare path, indexed writes
+ *   lt_vel_observe            compute_observations (LRV:320-470) + noise, the last_* shifts (LRV:143-148), the obs clip of
+ *                             step() (LRV:102-105) and HistoryWrapper's shift-and-append (history_wrapper.py:23) */
+typedef struct lt_vel_cfg {
+    int32_t num_envs, num_bodies, num_commands, num_obs, num_privileged_obs, obs_history_length;
+    int32_t feet_indices[4];
+    int32_t n_termination, termination_indices[8];            /* termination_contact_indices (LRV:158) */
+    int32_t use_terminal_body_height;
+    float terminal_body_height, max_episode_length;
+    int32_t sample_interval, rand_interval;                   /* int(resampling_time / dt), int(domain_rand.rand_interval) */
+    int32_t n_terms;                                          /* rows of the lt_corl_rewards block, in reward_names order */
+    int32_t command_sum_adds_scale[LT_CORL_MAX_TERMS];        /* 1 for tracking_contacts_shaped_force / _vel (LRV:296-297) */
+    float term_scales[LT_CORL_MAX_TERMS];                     /* reward_scales[name] * dt (LRV:1243) */
+    int32_t only_positive_rewards, only_positive_rewards_ji22_style;
+    float sigma_rew_neg;
+    int32_t observe_command, observe_two_prev_actions, observe_timing_parameter, observe_clock_inputs, add_noise;
+    float clip_observations, obs_scale_dof_pos, obs_scale_dof_vel;
+    int32_t priv_observe_friction, priv_observe_restitution;
+    float friction_scale, friction_shift, restitution_scale, restitution_shift;     /* get_scale_shift of cfg.normalization.* */
+    uint32_t seed_lo, seed_hi;                                /* Philox key of the in-kernel observation noise */
+} lt_vel_cfg;
+typedef struct lt_vel_ptrs {
+    /* simulator tensors (LRV:1124-1150): root_states [N,13], rigid_body_state [N,B,13], contact_forces [N,B,3], dof_state [N,12,2] */
+    const float *root_states, *rigid_body_state, *contact_forces, *dof_state;
+    const float *gravity_vec;                                 /* [N,3] */
+    const float *measured_height_mean;                        /* [N] or NULL (= 0: cfg.terrain.measure_heights off) */
+    int64_t* episode_length_buf;                              /* [N] in / out */
+    float *base_pos, *base_quat, *base_lin_vel, *base_ang_vel, *projected_gravity;        /* [N,3] [N,4] [N,3] x3 */
+    float *foot_positions, *foot_velocities, *prev_foot_velocities;                       /* [N,4,3] */
+    uint8_t *reset_buf, *time_out_buf, *body_height_buf, *resample_due, *dr_due;          /* [N] */
+    /* rewards */
+    const float* commands;                                    /* [N, num_commands] */
+    float *rew_buf, *rew_buf_pos, *rew_buf_neg;               /* [N] */
+    float* episode_sums;                                      /* [n_terms + 1, N]: terms, total */
+    float* command_sums;                                      /* [n_terms + 5, N]: terms, lin_vel_raw, ang_vel_raw, lin_vel_residual, ang_vel_residual, ep_timesteps */
+    double* term_sums;                                        /* [n_terms] scratch: all-env sums of the scaled terms */
+    /* observations */
+    const float *commands_scale, *default_dof_pos, *noise_scale_vec;      /* [num_commands] [12] [num_obs] */
+    const float *actions, *joint_pos_target, *gait_indices, *clock_inputs, *friction_coeffs, *restitutions;   /* [N,12] [N,12] [N] [N,4] [N] [N] */
+    float *last_actions, *last_last_actions, *last_joint_pos_target, *last_last_joint_pos_target, *last_dof_vel, *last_root_vel;
+    float *obs_buf, *privileged_obs_buf;                      /* [N,num_obs] [N,num_privileged_obs] */
+    const float* obs_history_in;                              /* [N, H * num_obs] */
+    float* obs_history_out;                                   /* [N, H * num_obs], a different buffer: the host ping-pongs the two */
+} lt_vel_ptrs;
+int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream);
+/* term_values: the [n_terms, N] block lt_corl_rewards wrote */
+int lt_vel_reward(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* term_values, void* stream);
+/* noise_uniforms [N, num_obs] in [0,1) or NULL -> Philox4x32-10 keyed (seed, step, env, column / 4); read only if add_noise */
+int lt_vel_observe(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* noise_uniforms, uint32_t step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

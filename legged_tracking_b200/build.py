@@ -10,7 +10,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 OUT = os.path.join(PKG_DIR, "liblt_b200.so")
-SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_torque_tc5.cu", "lt_rollout.cu", "lt_terrain.cu", "lt_policy.cu", "lt_planner.cu", "lt_gait.cu"]
+SOURCES = ["lt_kernels.cu", "lt_torque_mma.cu", "lt_torque_tc5.cu", "lt_rollout.cu", "lt_terrain.cu", "lt_policy.cu", "lt_planner.cu", "lt_gait.cu", "lt_vel.cu"]
 HEADERS = ["lt_core.cuh", "lt_torque_mma.h"]
 # per-source header dependencies (a change to the GEMM header must not recompile the 3-minute step kernels)
 DEPS = {"lt_policy.cu": [os.path.join(CSRC, "lt_gemm.cuh"), os.path.join(REPO, "include", "lt_policy.h"),

@@ -1,0 +1,252 @@
+// lt_vel.cu -- cfg 4: the dense per-step parts of LeggedRobot.post_physics_step of the velocity-tracking env
+// (go1_gym/envs/base/legged_robot_velocity_tracking.py:108-154, LRV below) that are not already lt_step_contact_targets /
+// lt_corl_rewards / lt_resample_commands (csrc/lt_gait.cu).  All of it is HBM-bound row work: thread per env for the scalar
+// logic, thread per element for the observation rows and the 30-row history shift (the one large transfer: 8.4 KB read + 8.4 KB
+// written per env at cfg 4's 70 x 30 history).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "lt_core.cuh"
+
+struct lt_vel_params {
+    lt_vel_cfg c;
+    lt_vel_ptrs p;
+    const float* aux;          // term values (reward) / noise uniforms (observe)
+    uint32_t step;
+};
+
+// ------------------------------------------------------------------------------------------------ LRV:117-132, 156-167, 702-716
+__global__ void __launch_bounds__(128) lt_vel_pre_kernel(const __grid_constant__ lt_vel_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const lt_vel_cfg& c = a.c;
+    if (i >= c.num_envs) return;
+    const lt_vel_ptrs& p = a.p;
+    const int64_t ep = p.episode_length_buf[i] + 1;                                   // LRV:117
+    p.episode_length_buf[i] = ep;
+    const float* root = p.root_states + (size_t)i * 13;
+    float q[4], o[3];
+    for (int k = 0; k < 3; ++k) p.base_pos[(size_t)i * 3 + k] = root[k];
+    for (int k = 0; k < 4; ++k) { q[k] = root[3 + k]; p.base_quat[(size_t)i * 4 + k] = q[k]; }
+    lt_quat_rotate_inverse(q, root + 7, o);
+    for (int k = 0; k < 3; ++k) p.base_lin_vel[(size_t)i * 3 + k] = o[k];
+    lt_quat_rotate_inverse(q, root + 10, o);
+    for (int k = 0; k < 3; ++k) p.base_ang_vel[(size_t)i * 3 + k] = o[k];
+    lt_quat_rotate_inverse(q, p.gravity_vec + (size_t)i * 3, o);
+    for (int k = 0; k < 3; ++k) p.projected_gravity[(size_t)i * 3 + k] = o[k];
+    for (int f = 0; f < 4; ++f) {                                                     // LRV:127-130; prev_foot_velocities: LRV:74
+        const float* rb = p.rigid_body_state + ((size_t)i * c.num_bodies + c.feet_indices[f]) * 13;
+        for (int k = 0; k < 3; ++k) {
+            const size_t d = ((size_t)i * 4 + f) * 3 + k;
+            p.prev_foot_velocities[d] = p.foot_velocities[d];
+            p.foot_positions[d] = rb[k];
+            p.foot_velocities[d] = rb[7 + k];
+        }
+    }
+    // check_termination (LRV:156-167)
+    bool reset = false;
+    for (int t = 0; t < c.n_termination; ++t) {
+        const float* f = p.contact_forces + ((size_t)i * c.num_bodies + c.termination_indices[t]) * 3;
+        reset = reset || (lt_norm3(f[0], f[1], f[2]) > 1.0f);
+    }
+    const bool time_out = (float)ep > c.max_episode_length;
+    reset = reset || time_out;
+    bool low = false;
+    if (c.use_terminal_body_height) {
+        const float h = p.measured_height_mean ? p.measured_height_mean[i] : 0.0f;    // mean over one column: the value itself
+        low = LT_FSUB(root[2], h) < c.terminal_body_height;
+        reset = reset || low;
+    }
+    p.time_out_buf[i] = time_out ? 1 : 0;
+    p.body_height_buf[i] = low ? 1 : 0;
+    p.reset_buf[i] = reset ? 1 : 0;
+    p.resample_due[i] = (ep % c.sample_interval) == 0 ? 1 : 0;                        // LRV:702-703
+    p.dr_due[i] = (ep % c.rand_interval) == 0 ? 1 : 0;                                // LRV:715-716
+}
+
+// ------------------------------------------------------------------------------------------------ compute_reward (LRV:281-318)
+// all-env sum of every scaled term: only its sign is used (LRV:291-294)
+__global__ void __launch_bounds__(256) lt_vel_term_sums_kernel(const __grid_constant__ lt_vel_params a) {
+    __shared__ double s_part[8];
+    const lt_vel_cfg& c = a.c;
+    const int t = blockIdx.y;
+    double v = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < c.num_envs; i += gridDim.x * blockDim.x)
+        v += (double)LT_FMUL(a.aux[(size_t)t * c.num_envs + i], c.term_scales[t]);
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < 8; ++w) s += s_part[w];
+        atomicAdd(a.p.term_sums + t, s);
+    }
+}
+
+__global__ void __launch_bounds__(128) lt_vel_reward_kernel(const __grid_constant__ lt_vel_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const lt_vel_cfg& c = a.c;
+    if (i >= c.num_envs) return;
+    const lt_vel_ptrs& p = a.p;
+    const size_t N = (size_t)c.num_envs;
+    float rew = 0.0f, pos = 0.0f, neg = 0.0f;
+    for (int t = 0; t < c.n_terms; ++t) {
+        const float r = LT_FMUL(a.aux[(size_t)t * N + i], c.term_scales[t]);
+        rew = LT_FADD(rew, r);
+        const double s = p.term_sums[t];
+        if (s >= 0.0) pos = LT_FADD(pos, r);
+        else if (s <= 0.0) neg = LT_FADD(neg, r);
+        p.episode_sums[(size_t)t * N + i] = LT_FADD(p.episode_sums[(size_t)t * N + i], r);
+        const float add = c.command_sum_adds_scale[t] ? LT_FADD(c.term_scales[t], r) : r;         // LRV:296-299
+        p.command_sums[(size_t)t * N + i] = LT_FADD(p.command_sums[(size_t)t * N + i], add);
+    }
+    if (c.only_positive_rewards) rew = fmaxf(rew, 0.0f);                                          // LRV:300-301
+    else if (c.only_positive_rewards_ji22_style) rew = LT_FMUL(pos, expf(LT_FDIV(neg, c.sigma_rew_neg)));      // LRV:302-303
+    p.rew_buf[i] = rew;
+    p.rew_buf_pos[i] = pos;
+    p.rew_buf_neg[i] = neg;
+    const size_t T = (size_t)c.n_terms;
+    p.episode_sums[T * N + i] = LT_FADD(p.episode_sums[T * N + i], rew);                          // "total" (LRV:304)
+    const float vx = p.base_lin_vel[(size_t)i * 3], wz = p.base_ang_vel[(size_t)i * 3 + 2];
+    const float* cmd = p.commands + (size_t)i * c.num_commands;
+    float* cs = p.command_sums + T * N + i;                                                       // LRV:312-316
+    cs[0] = LT_FADD(cs[0], vx);
+    cs[N] = LT_FADD(cs[N], wz);
+    const float dx = LT_FSUB(vx, cmd[0]), dz = LT_FSUB(wz, cmd[2]);
+    cs[2 * N] = LT_FADD(cs[2 * N], LT_FMUL(dx, dx));
+    cs[3 * N] = LT_FADD(cs[3 * N], LT_FMUL(dz, dz));
+    cs[4 * N] = LT_FADD(cs[4 * N], 1.0f);
+}
+
+// ------------------------------------------------------------------------------------------------ compute_observations (LRV:320-470)
+// thread per (env, observation column): the column's value, noise, the clip of step() (LRV:102-103), obs_buf and the newest
+// history row; the same grid then copies the H - 1 older rows one slot towards the past (history_wrapper.py:23).
+__global__ void __launch_bounds__(256) lt_vel_observe_kernel(const __grid_constant__ lt_vel_params a) {
+    const lt_vel_cfg& c = a.c;
+    const lt_vel_ptrs& p = a.p;
+    const int no = c.num_obs, H = c.obs_history_length;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t total = (int64_t)c.num_envs * H * no;
+    if (idx >= total) return;
+    const int i = (int)(idx / ((int64_t)H * no));
+    const int w = (int)(idx % ((int64_t)H * no));
+    float* hist = p.obs_history_out + (size_t)i * H * no;
+    if (w < (H - 1) * no) {                                                           // older rows: shifted by one observation
+        hist[w] = p.obs_history_in[(size_t)i * H * no + w + no];
+        return;
+    }
+    const int col = w - (H - 1) * no;
+    const int nc = c.observe_command ? c.num_commands : 0;
+    float v;
+    int k = col;
+    if (k < 3) v = p.projected_gravity[(size_t)i * 3 + k];
+    else if ((k -= 3) < nc) v = LT_FMUL(p.commands[(size_t)i * c.num_commands + k], p.commands_scale[k]);
+    else if ((k -= nc) < 12) v = LT_FMUL(LT_FSUB(p.dof_state[((size_t)i * 12 + k) * 2], p.default_dof_pos[k]), c.obs_scale_dof_pos);
+    else if ((k -= 12) < 12) v = LT_FMUL(p.dof_state[((size_t)i * 12 + k) * 2 + 1], c.obs_scale_dof_vel);
+    else if ((k -= 12) < 12) v = p.actions[(size_t)i * 12 + k];
+    else {
+        k -= 12;
+        const int n_prev = c.observe_two_prev_actions ? 12 : 0, n_tim = c.observe_timing_parameter ? 1 : 0;
+        if (k < n_prev) v = p.last_actions[(size_t)i * 12 + k];                        // the pre-shift last_actions (LRV:347-349, 143)
+        else if ((k -= n_prev) < n_tim) v = p.gait_indices[i];
+        else { k -= n_tim; v = p.clock_inputs[(size_t)i * 4 + k]; }
+    }
+    if (c.add_noise) {                                                                // LRV:391-392
+        float u;
+        if (a.aux) u = a.aux[(size_t)i * no + col];
+        else {
+            uint32_t r[4];
+            lt_philox((uint32_t)i, (uint32_t)(col >> 2), a.step, 0x56454c4fu, c.seed_lo, c.seed_hi, r);
+            u = lt_u01(r[col & 3]);
+        }
+        v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), p.noise_scale_vec[col]));
+    }
+    v = fminf(fmaxf(v, -c.clip_observations), c.clip_observations);                   // LRV:102-103
+    p.obs_buf[(size_t)i * no + col] = v;
+    hist[w] = v;
+}
+
+// thread per env: privileged observations (LRV:396-426 for the two flags cfg 4 sets) and the last_* shifts (LRV:143-148)
+__global__ void __launch_bounds__(128) lt_vel_shift_kernel(const __grid_constant__ lt_vel_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const lt_vel_cfg& c = a.c;
+    if (i >= c.num_envs) return;
+    const lt_vel_ptrs& p = a.p;
+    int k = 0;
+    float* pr = p.privileged_obs_buf + (size_t)i * c.num_privileged_obs;
+    const float clip = c.clip_observations;
+    if (c.priv_observe_friction) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(p.friction_coeffs[i], c.friction_shift), c.friction_scale), -clip), clip);
+    if (c.priv_observe_restitution) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(p.restitutions[i], c.restitution_shift), c.restitution_scale), -clip), clip);
+    for (int d = 0; d < 12; ++d) {
+        const size_t o = (size_t)i * 12 + d;
+        p.last_last_actions[o] = p.last_actions[o];
+        p.last_actions[o] = p.actions[o];
+        p.last_last_joint_pos_target[o] = p.last_joint_pos_target[o];
+        p.last_joint_pos_target[o] = p.joint_pos_target[o];
+        p.last_dof_vel[o] = p.dof_state[o * 2 + 1];
+    }
+    for (int d = 0; d < 6; ++d) p.last_root_vel[(size_t)i * 6 + d] = p.root_states[(size_t)i * 13 + 7 + d];
+}
+
+static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
+    return c && c->num_envs > 0 && c->num_bodies > 0 && c->num_commands >= 3 && c->num_obs > 0 && c->obs_history_length >= 1 &&
+           c->n_terms >= 0 && c->n_terms <= LT_CORL_MAX_TERMS && c->n_termination >= 0 && c->n_termination <= 8 && c->sample_interval > 0 &&
+           c->rand_interval > 0;
+}
+
+extern "C" {
+
+int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream) {
+    if (!lt_vel_cfg_ok(cfg) || !ptrs) return LT_ERR_INVALID;
+    const lt_vel_ptrs& p = *ptrs;
+    if (!p.root_states || !p.rigid_body_state || !p.contact_forces || !p.gravity_vec || !p.episode_length_buf || !p.base_pos || !p.base_quat ||
+        !p.base_lin_vel || !p.base_ang_vel || !p.projected_gravity || !p.foot_positions || !p.foot_velocities || !p.prev_foot_velocities ||
+        !p.reset_buf || !p.time_out_buf || !p.body_height_buf || !p.resample_due || !p.dr_due)
+        return LT_ERR_INVALID;
+    lt_vel_params a;
+    a.c = *cfg; a.p = p; a.aux = nullptr; a.step = 0;
+    lt_vel_pre_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(a);
+    return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
+}
+
+int lt_vel_reward(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* term_values, void* stream) {
+    if (!lt_vel_cfg_ok(cfg) || !ptrs) return LT_ERR_INVALID;
+    const lt_vel_ptrs& p = *ptrs;
+    if ((cfg->n_terms > 0 && !term_values) || !p.term_sums || !p.rew_buf || !p.rew_buf_pos || !p.rew_buf_neg || !p.episode_sums || !p.command_sums ||
+        !p.base_lin_vel || !p.base_ang_vel || !p.commands)
+        return LT_ERR_INVALID;
+    cudaStream_t s = (cudaStream_t)stream;
+    lt_vel_params a;
+    a.c = *cfg; a.p = p; a.aux = term_values; a.step = 0;
+    if (cfg->n_terms > 0) {
+        if (cudaMemsetAsync(p.term_sums, 0, sizeof(double) * cfg->n_terms, s) != cudaSuccess) return LT_ERR_CUDA;
+        int bx = (cfg->num_envs + 255) / 256;
+        if (bx > 64) bx = 64;
+        lt_vel_term_sums_kernel<<<dim3(bx, cfg->n_terms), 256, 0, s>>>(a);
+    }
+    lt_vel_reward_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, s>>>(a);
+    return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
+}
+
+int lt_vel_observe(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* noise_uniforms, uint32_t step, void* stream) {
+    if (!lt_vel_cfg_ok(cfg) || !ptrs) return LT_ERR_INVALID;
+    const lt_vel_ptrs& p = *ptrs;
+    const int width = 3 + (cfg->observe_command ? cfg->num_commands : 0) + 36 + (cfg->observe_two_prev_actions ? 12 : 0) +
+                      (cfg->observe_timing_parameter ? 1 : 0) + (cfg->observe_clock_inputs ? 4 : 0);
+    if (width != cfg->num_obs) return LT_ERR_INVALID;                                  // LRV:1119 (assert on the layout)
+    if (cfg->num_privileged_obs != (cfg->priv_observe_friction ? 1 : 0) + (cfg->priv_observe_restitution ? 1 : 0)) return LT_ERR_INVALID;
+    if (!p.projected_gravity || !p.commands || !p.commands_scale || !p.dof_state || !p.default_dof_pos || !p.actions || !p.last_actions ||
+        !p.last_last_actions || !p.joint_pos_target || !p.last_joint_pos_target || !p.last_last_joint_pos_target || !p.last_dof_vel ||
+        !p.last_root_vel || !p.root_states || !p.gait_indices || !p.clock_inputs || !p.obs_buf || !p.privileged_obs_buf || !p.obs_history_in ||
+        !p.obs_history_out || p.obs_history_in == p.obs_history_out || (cfg->add_noise && !p.noise_scale_vec) ||
+        (cfg->priv_observe_friction && !p.friction_coeffs) || (cfg->priv_observe_restitution && !p.restitutions))
+        return LT_ERR_INVALID;
+    cudaStream_t s = (cudaStream_t)stream;
+    lt_vel_params a;
+    a.c = *cfg; a.p = p; a.aux = noise_uniforms; a.step = step;
+    const int64_t total = (int64_t)cfg->num_envs * cfg->obs_history_length * cfg->num_obs;
+    lt_vel_observe_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(a);
+    lt_vel_shift_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, s>>>(a);               // after the observation read last_actions
+    return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
+}
+
+}   // extern "C"

@@ -1,0 +1,394 @@
+"""BASELINE config 4: the post-physics step of the velocity-tracking env (walk-these-ways; go1_gym/envs/base/
+legged_robot_velocity_tracking.py, LRV below; scripts/train_velocity_tracking.py) as a chain of liblt_b200 launches.
+
+  step(actions, sim)   LRV:60-105 (LeggedRobot.step) + :108-154 (post_physics_step) + history_wrapper.py:19-24
+      lt_compute_torques x decimation   the same kernel and state as the trajectory env (_compute_torques is identical in both files)
+      lt_vel_pre                        episode counter, body-frame velocities, foot states, check_termination, interval masks
+      lt_resample_commands              for the envs whose resampling interval elapsed (commands drawn by the caller's source)
+      lt_step_contact_targets           gait clock
+      lt_corl_rewards + lt_vel_reward   the CoRLRewards terms and compute_reward
+      reset_idx                         indexed torch writes on the device for reset_buf.nonzero() -- the rare path, host-orchestrated
+                                        exactly like the reference's (it needs the host curricula anyway)
+      lt_vel_observe                    70-column observation + noise, last_* shifts, obs clip, the 30-row history shift
+
+What stays on the host, as in the reference: the command curricula (`command_source`: anything with update() / sample(), e.g.
+CurriculumAdapter around the reference's own RewardThresholdCurriculum objects), the gravity-randomisation schedule, the choice of
+env ids for the three indexed paths (one nonzero() each, a host sync the reference has too).
+
+Scope: the configuration scripts/train_velocity_tracking.py sets (no height observations, push_robots off, no rigid-body
+re-randomisation, flat origins); other switches raise.  There is no CPU path.
+"""
+import ctypes as C
+import json
+import math
+import os
+
+import numpy as np
+import torch
+
+from . import _abi
+from .gait import CommandResampler, CoRLRewardKernel, GaitClock
+
+DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+RAW_SUMS = ["lin_vel_raw", "ang_vel_raw", "lin_vel_residual", "ang_vel_residual", "ep_timesteps"]       # LRV:312-316
+CURRICULUM_KEYS = ["tracking_lin_vel", "tracking_ang_vel", "tracking_contacts_shaped_force", "tracking_contacts_shaped_vel"]   # LRV:746-747
+LOCAL_RANGE = [0.55, 0.55, 0.55, 0.55, 0.35, 0.25, 0.25, 0.25, 0.25, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0]       # LRV:755-757
+
+
+def cfg4_config():
+    """What _parse_cfg / _init_buffers / _prepare_reward_function derive from scripts/train_velocity_tracking.py's Cfg (recorded off
+    the live reference env by oracle/gen_golden_vel.py; a config table, not code)."""
+    return json.load(open(os.path.join(DATA, "vel_cfg4.json")))
+
+
+def scale_shift(rng):
+    return 2.0 / (rng[1] - rng[0]), (rng[1] + rng[0]) / 2.0            # go1_gym/utils/math_utils.py:35-38
+
+
+class UniformCommandSource:
+    """A command source without a curriculum: every command uniform inside [low, high] (what curriculum.sample degenerates to when
+    every bin has weight 1).  For benchmarks and smoke runs."""
+
+    def __init__(self, low, high, seed=0):
+        self.low, self.high = np.asarray(low, np.float64), np.asarray(high, np.float64)
+        self.rng = np.random.RandomState(seed)
+
+    def update(self, category, old_bins, task_rewards, success_thresholds):
+        pass
+
+    def sample(self, category, batch_size):
+        return self.rng.uniform(self.low, self.high, size=(batch_size, len(self.low))), np.zeros(batch_size, np.int64)
+
+
+class CurriculumAdapter:
+    """The reference's curricula (go1_gym/envs/base/curriculum.py objects, one per category) behind the source protocol."""
+
+    def __init__(self, curricula):
+        self.curricula = list(curricula)
+
+    def update(self, category, old_bins, task_rewards, success_thresholds):
+        self.curricula[category].update(old_bins, task_rewards, success_thresholds, local_range=np.array(LOCAL_RANGE))
+
+    def sample(self, category, batch_size):
+        return self.curricula[category].sample(batch_size=batch_size)
+
+
+class VelocityStepEngine:
+    def __init__(self, cfg, num_envs, env_origins, actuator, command_source, device="cuda:0", seed=0, rng=None):
+        from . import cfg as ltcfg
+        from .engine import StepEngine
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _abi.LtError("VelocityStepEngine runs as sm_100a kernels: there is no CPU path")
+        self.lib = _abi.load()
+        self.cfg, self.N = dict(cfg), int(num_envs)
+        c, N, dev = self.cfg, self.N, self.device
+        if c["control_type"] != "actuator_net" or c["custom_origins"] or not c["randomize_lag_timesteps"]:
+            raise NotImplementedError("cfg 4 as scripts/train_velocity_tracking.py sets it: actuator_net, lag randomisation, flat origins")
+        self.source = command_source
+        self.rng = rng or (lambda *shape: torch.rand(*shape, device=dev))
+        self.dt = float(c["dt"])
+        # ---- torques: the trajectory env's kernel and state (LRV:925-964 == LR:957-996), through a plane-terrain StepEngine
+        t = ltcfg.preset_cfg("cfg1_plane_256", num_envs=N)
+        flat = ltcfg.flat_from_cfg(t, num_envs=N)
+        flat.update(clip_actions=float(c["clip_actions"]), action_scale=float(c["action_scale"]), hip_scale_reduction=float(c["hip_scale_reduction"]),
+                    lag_timesteps=int(c["lag_timesteps"]), randomize_lag_timesteps=True, control_type="actuator_net", decimation=int(c["decimation"]),
+                    default_dof_pos=[float(x) for x in np.asarray(c["default_dof_pos"]).reshape(-1)],
+                    torque_limits=[float(x) for x in c["torque_limits"]])
+        self.tq = StepEngine(flat, {"env_origins": np.asarray(env_origins, np.float32)}, actuator, device=dev, seed=seed)
+        z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)                 # noqa: E731
+        f32 = lambda a: torch.as_tensor(np.asarray(a, np.float32)).to(dev).contiguous()        # noqa: E731
+        B, nc, no, H = int(c["num_bodies"]), int(c["num_commands"]), int(c["num_obs"]), int(c["obs_history_length"])
+        self.env_origins = f32(env_origins)
+        self.base_init_state = f32(c["base_init_state"])
+        self.root_states, self.rigid_body_state, self.contact_forces = z(N, 13), z(N, B, 13), z(N, B, 3)
+        self.dof_state = z(N, 12, 2)
+        self.gravity_vec = f32([0.0, 0.0, -1.0]).repeat(N, 1).contiguous()
+        self.gravities = z(N, 3)
+        self.episode_length_buf = z(N, dt=torch.int64)
+        self.base_pos, self.base_quat = z(N, 3), z(N, 4)
+        self.base_lin_vel, self.base_ang_vel, self.projected_gravity = z(N, 3), z(N, 3), z(N, 3)
+        self.foot_positions, self.foot_velocities, self.prev_foot_velocities = z(N, 4, 3), z(N, 4, 3), z(N, 4, 3)
+        u8 = lambda: z(N, dt=torch.uint8)                                                       # noqa: E731
+        self.reset_buf, self.time_out_buf, self.body_height_buf, self.resample_due, self.dr_due = u8(), u8(), u8(), u8(), u8()
+        self.commands = z(N, nc)
+        self.commands_scale, self.default_dof_pos = f32(c["commands_scale"]), f32(c["default_dof_pos"]).reshape(-1)
+        self.dof_pos_limits, self.noise_scale_vec = f32(c["dof_pos_limits"]), f32(c["noise_scale_vec"])
+        self.reward_names = list(c["reward_names"])
+        T = len(self.reward_names)
+        self.rew_buf, self.rew_buf_pos, self.rew_buf_neg = z(N), z(N), z(N)
+        self.episode_sums = z(T + 1, N)                                   # rows: reward_names, "total"
+        self.command_sums = z(T + len(RAW_SUMS), N)                       # rows: reward_names, RAW_SUMS
+        self.term_sums = z(max(T, 1), dt=torch.float64)
+        self.last_actions, self.last_last_actions = z(N, 12), z(N, 12)
+        self.last_joint_pos_target, self.last_last_joint_pos_target = z(N, 12), z(N, 12)
+        self.last_dof_vel, self.last_root_vel = z(N, 12), z(N, 6)
+        self.feet_air_time = z(N, 4)
+        self.last_contacts = z(N, 4, dt=torch.bool)
+        self.friction_coeffs, self.restitutions = z(N), z(N)
+        self.obs_buf, self.privileged_obs_buf = z(N, no), z(N, int(c["num_privileged_obs"]))
+        self._hist = [z(N, H * no), z(N, H * no)]
+        self._hist_cur = 0
+        self.common_step_counter = 0
+        self.env_command_bins = np.zeros(N, dtype=np.int64)
+        self.env_command_categories = np.zeros(N, dtype=np.int64)
+        self.category_names = list(c["category_names"])
+        self.extras = {}
+        self.gait = GaitClock(N, self.dt, float(c["kappa_gait_probs"]), pacing_offset=bool(c["pacing_offset"]), device=dev)
+        self.corl = CoRLRewardKernel(self.reward_names, {k: c["rewards/" + k] for k in ("tracking_sigma", "tracking_sigma_yaw", "base_height_target",
+                                                                                          "gait_force_sigma", "gait_vel_sigma", "max_contact_force")},
+                                     self.dt, c["feet_indices"], c["penalised_contact_indices"], device=dev)
+        self.resampler = CommandResampler(self.commands, self.command_sums, self.category_names,
+                                          gaitwise_curricula=c["gaitwise_curricula"], exclusive_phase_offset=c["exclusive_phase_offset"],
+                                          balance_gait_distribution=c["balance_gait_distribution"], binary_phases=c["binary_phases"])
+        self.reward_scales = {n: float(s) for n, s in zip(self.reward_names, c["reward_scales"])}      # already x dt (LRV:1243)
+        self.curriculum_thresholds = dict(tracking_lin_vel=0.8, tracking_ang_vel=0.7, tracking_contacts_shaped_force=0.9,
+                                          tracking_contacts_shaped_vel=0.9)     # train_velocity_tracking.py:24-27
+        self.sample_interval = int(float(c["resampling_time"]) / self.dt)
+        self.step_count = 0
+        self._vc = self._make_cfg(seed)
+        self._keep = None
+
+    # ------------------------------------------------------------------------------------------------ plumbing
+    @property
+    def obs_history(self):
+        return self._hist[self._hist_cur]
+
+    def _make_cfg(self, seed):
+        c, v = self.cfg, _abi.lt_vel_cfg()
+        v.num_envs, v.num_bodies, v.num_commands = self.N, int(c["num_bodies"]), int(c["num_commands"])
+        v.num_obs, v.num_privileged_obs, v.obs_history_length = int(c["num_obs"]), int(c["num_privileged_obs"]), int(c["obs_history_length"])
+        for i, b in enumerate(c["feet_indices"]):
+            v.feet_indices[i] = int(b)
+        term = list(c["termination_contact_indices"])
+        v.n_termination = len(term)
+        for i, b in enumerate(term):
+            v.termination_indices[i] = int(b)
+        v.use_terminal_body_height, v.terminal_body_height = int(bool(c["use_terminal_body_height"])), float(c["terminal_body_height"])
+        v.max_episode_length = float(c["max_episode_length"])
+        v.sample_interval, v.rand_interval = self.sample_interval, int(float(c["rand_interval"]))
+        v.n_terms = len(self.reward_names)
+        for i, n in enumerate(self.reward_names):
+            v.term_scales[i] = self.reward_scales[n]
+            v.command_sum_adds_scale[i] = 1 if n in ("tracking_contacts_shaped_force", "tracking_contacts_shaped_vel") else 0
+        v.only_positive_rewards = int(bool(c["only_positive_rewards"]))
+        v.only_positive_rewards_ji22_style = int(bool(c["only_positive_rewards_ji22_style"]))
+        v.sigma_rew_neg = float(c["sigma_rew_neg"])
+        for k in ("observe_command", "observe_two_prev_actions", "observe_timing_parameter", "observe_clock_inputs", "add_noise",
+                  "priv_observe_friction", "priv_observe_restitution"):
+            setattr(v, k, int(bool(c[k])))
+        v.clip_observations, v.obs_scale_dof_pos, v.obs_scale_dof_vel = float(c["clip_observations"]), float(c["obs_scale_dof_pos"]), float(c["obs_scale_dof_vel"])
+        v.friction_scale, v.friction_shift = scale_shift(c["friction_range"])
+        v.restitution_scale, v.restitution_shift = scale_shift(c["restitution_range"])
+        v.seed_lo, v.seed_hi = seed & 0xffffffff, (seed >> 32) & 0xffffffff
+        return v
+
+    def _ptrs(self):
+        p, tq = _abi.lt_vel_ptrs(), self.tq.state
+        d = dict(root_states=self.root_states, rigid_body_state=self.rigid_body_state, contact_forces=self.contact_forces, dof_state=self.dof_state,
+                 gravity_vec=self.gravity_vec, episode_length_buf=self.episode_length_buf, base_pos=self.base_pos, base_quat=self.base_quat,
+                 base_lin_vel=self.base_lin_vel, base_ang_vel=self.base_ang_vel, projected_gravity=self.projected_gravity,
+                 foot_positions=self.foot_positions, foot_velocities=self.foot_velocities, prev_foot_velocities=self.prev_foot_velocities,
+                 reset_buf=self.reset_buf, time_out_buf=self.time_out_buf, body_height_buf=self.body_height_buf, resample_due=self.resample_due,
+                 dr_due=self.dr_due, commands=self.commands, rew_buf=self.rew_buf, rew_buf_pos=self.rew_buf_pos, rew_buf_neg=self.rew_buf_neg,
+                 episode_sums=self.episode_sums, command_sums=self.command_sums, term_sums=self.term_sums, commands_scale=self.commands_scale,
+                 default_dof_pos=self.default_dof_pos, noise_scale_vec=self.noise_scale_vec, actions=tq["actions"],
+                 joint_pos_target=tq["joint_pos_target"], gait_indices=self.gait.gait_indices, clock_inputs=self.gait.clock_inputs,
+                 friction_coeffs=self.friction_coeffs, restitutions=self.restitutions, last_actions=self.last_actions,
+                 last_last_actions=self.last_last_actions, last_joint_pos_target=self.last_joint_pos_target,
+                 last_last_joint_pos_target=self.last_last_joint_pos_target, last_dof_vel=self.last_dof_vel, last_root_vel=self.last_root_vel,
+                 obs_buf=self.obs_buf, privileged_obs_buf=self.privileged_obs_buf, obs_history_in=self._hist[self._hist_cur],
+                 obs_history_out=self._hist[1 - self._hist_cur])
+        for k, t in d.items():
+            setattr(p, k, t.data_ptr())
+        return p
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ------------------------------------------------------------------------------------------------ the step
+    def step(self, actions, sim, noise_uniforms=None):
+        """actions [N,12]; sim: what PhysX hands back -- dof_state: one [N*12,2] (or [N,12,2]) tensor per sub-step, root [N,13],
+        contact [N,B,3], rigid [N,B,13], all on the device.  -> ({'obs','privileged_obs','obs_history'}, rew, done, extras)"""
+        tq, lib, s = self.tq, self.lib, self._stream()
+        cur = self.dof_state.view(self.N * 12, 2)                                     # what the last refresh left (post reset)
+        for sub, dof in enumerate(sim["dof_state"]):                                  # LRV:76-82: torques, THEN simulate + refresh
+            tq.bind_sim(dof_state=cur)
+            tq.compute_torques(actions, sub)
+            cur = dof.view(self.N * 12, 2)
+        # the lag ring and sub-step counters advance with lt_compact_kernel in the trajectory step; here, by hand
+        cnt, n_sub = tq.counters, len(sim["dof_state"])
+        cnt[2] = (cnt[2] + n_sub) % tq.state["lag_buffer"].shape[0]
+        cnt[1] += n_sub
+        cnt[0] += 1
+        self.dof_state.copy_(sim["dof_state"][-1].view(self.N, 12, 2))
+        self.root_states.copy_(sim["root"])
+        self.contact_forces.copy_(sim["contact"])
+        self.rigid_body_state.copy_(sim["rigid"])
+        self.common_step_counter += 1                                                 # LRV:118
+        _abi.check(lib.lt_vel_pre(C.byref(self._vc), C.byref(self._ptrs()), s), None, "lt_vel_pre")
+        # ---- _post_physics_step_callback (LRV:693-726)
+        self._resample_commands(self.resample_due.nonzero(as_tuple=False).flatten())
+        self.gait.step(self.commands)
+        self._randomize_dof_props(self.dr_due.nonzero(as_tuple=False).flatten())
+        self._gravity_schedule()
+        # ---- compute_reward (LRV:281-318)
+        dof_pos, dof_vel = self.dof_state[..., 0].contiguous(), self.dof_state[..., 1].contiguous()
+        env = dict(commands=self.commands, base_lin_vel=self.base_lin_vel, base_ang_vel=self.base_ang_vel, projected_gravity=self.projected_gravity,
+                   gravity_vec=self.gravity_vec, base_pos=self.base_pos, base_quat=self.base_quat, torques=tq.state["torques"], dof_pos=dof_pos,
+                   dof_vel=dof_vel, last_dof_vel=self.last_dof_vel, actions=tq.state["actions"], last_actions=self.last_actions,
+                   last_last_actions=self.last_last_actions, joint_pos_target=tq.state["joint_pos_target"],
+                   last_joint_pos_target=self.last_joint_pos_target, last_last_joint_pos_target=self.last_last_joint_pos_target,
+                   contact_forces=self.contact_forces, foot_positions=self.foot_positions, foot_velocities=self.foot_velocities,
+                   prev_foot_velocities=self.prev_foot_velocities, foot_indices=self.gait.foot_indices,
+                   desired_contact_states=self.gait.desired_contact_states, default_dof_pos=self.default_dof_pos,
+                   dof_pos_limits=self.dof_pos_limits, last_contacts=self.last_contacts)
+        terms = self.corl(env)
+        _abi.check(lib.lt_vel_reward(C.byref(self._vc), C.byref(self._ptrs()), C.c_void_p(terms.data_ptr()), s), None, "lt_vel_reward")
+        # ---- reset_idx (LRV:169-265)
+        self.reset_idx(self.reset_buf.nonzero(as_tuple=False).flatten())
+        # ---- compute_observations + last_* shifts + obs clip + history (LRV:320-470, 143-148, 102-105; history_wrapper.py:23)
+        self.step_count += 1
+        nz = None
+        if noise_uniforms is not None:
+            nz = noise_uniforms.to(device=self.device, dtype=torch.float32).contiguous()
+        _abi.check(lib.lt_vel_observe(C.byref(self._vc), C.byref(self._ptrs()), C.c_void_p(nz.data_ptr()) if nz is not None else None,
+                                      C.c_uint32(self.step_count & 0xffffffff), s), None, "lt_vel_observe")
+        self._hist_cur = 1 - self._hist_cur
+        self._keep = (dof_pos, dof_vel, nz, terms)
+        self.extras["privileged_obs"] = self.privileged_obs_buf
+        return ({"obs": self.obs_buf, "privileged_obs": self.privileged_obs_buf, "obs_history": self.obs_history}, self.rew_buf,
+                self.reset_buf.bool(), self.extras)
+
+    # ------------------------------------------------------------------------------------------------ host-orchestrated rare paths
+    def _resample_commands(self, env_ids):
+        """LRV:728-842: curriculum update and sampling through the command source (host), everything else in lt_resample_commands."""
+        K = int(env_ids.numel())
+        if K == 0:
+            return
+        c = self.cfg
+        ep_len = min(float(c["max_episode_length"]), self.sample_interval)                  # LRV:732-733
+        ids_cpu = env_ids.cpu()
+        cats_old = self.env_command_categories[ids_cpu.numpy()]
+        rows = {n: self.command_sums[self.reward_names.index(n)] for n in CURRICULUM_KEYS if n in self.reward_names}
+        for i in range(len(self.category_names)):                                           # LRV:736-757
+            sel = ids_cpu[torch.from_numpy(np.atleast_1d(cats_old == i))]
+            if sel.numel() == 0:
+                continue
+            sel_dev = sel.to(self.device)
+            task_rewards = [rows[n][sel_dev] / ep_len for n in rows]
+            thresholds = [self.curriculum_thresholds[n] * self.reward_scales[n] for n in rows]
+            if thresholds:
+                self.source.update(i, self.env_command_bins[sel.numpy()], task_rewards, thresholds)
+        u = self.rng(K)                                                                     # LRV:760
+        cat = self.resampler.categories_from_uniform(u)
+        cat_cpu = cat.cpu().numpy()
+        nc = int(c["num_commands"])
+        new = np.zeros((K, nc), np.float64)
+        for i in range(len(self.category_names)):                                           # LRV:768-777
+            m = cat_cpu == i
+            if not m.any():
+                continue
+            cmds, bins = self.source.sample(i, int(m.sum()))
+            new[m] = np.asarray(cmds)[:, :nc]
+            sel = ids_cpu.numpy()[m]
+            self.env_command_bins[sel] = bins
+            self.env_command_categories[sel] = i
+        gait_u = None
+        if nc > 5 and not c["gaitwise_curricula"] and (c["exclusive_phase_offset"] or c["balance_gait_distribution"]):
+            gait_u = self.rng(K)                                                            # LRV:800, 812
+        self.resampler.apply(env_ids, new, category=cat, gait_uniform=gait_u)
+
+    def _randomize_dof_props(self, env_ids):
+        """LRV:663-683 (the two switches cfg 4 sets); writes the torque kernel's motor tables."""
+        K, c, st = int(env_ids.numel()), self.cfg, self.tq.state
+        if K == 0:
+            return
+        if c["randomize_motor_strength"]:
+            lo, hi = c["motor_strength_range"]
+            st["motor_strengths"][env_ids, :] = self.rng(K).unsqueeze(1) * (hi - lo) + lo
+        if c["randomize_motor_offset"]:
+            lo, hi = c["motor_offset_range"]
+            st["motor_offsets"][env_ids, :] = self.rng(K, 12) * (hi - lo) + lo
+
+    def _gravity_schedule(self):
+        """LRV:719-723 + _randomize_gravity (LRV:565-580)."""
+        c = self.cfg
+        interval, duration = int(float(c["gravity_rand_interval"])), float(c["gravity_rand_duration"])
+        if self.common_step_counter % interval == 0:
+            self._randomize_gravity(None)
+        if int(self.common_step_counter - duration) % interval == 0:
+            self._randomize_gravity(torch.zeros(3, device=self.device))
+
+    def _randomize_gravity(self, external_force):
+        c = self.cfg
+        if external_force is not None:
+            self.gravities[:, :] = external_force.unsqueeze(0)
+        elif c["randomize_gravity"]:
+            lo, hi = c["gravity_range"]
+            self.gravities[:, :] = (self.rng(3) * (hi - lo) + lo).unsqueeze(0)
+        g = self.gravities[0, :] + torch.tensor([0.0, 0.0, -9.8], device=self.device)
+        self.gravity_vec[:, :] = g.unsqueeze(0) / torch.norm(g)
+
+    def reset_idx(self, env_ids):
+        """LRV:169-265."""
+        K = int(env_ids.numel())
+        if K == 0:
+            return
+        c, st = self.cfg, self.tq.state
+        self._resample_commands(env_ids)
+        self._randomize_dof_props(env_ids)
+        # _reset_dofs (LRV:966-981)
+        self.dof_state[env_ids, :, 0] = self.default_dof_pos.unsqueeze(0) * (self.rng(K, 12) * (1.5 - 0.5) + 0.5)
+        self.dof_state[env_ids, :, 1] = 0.0
+        # _reset_root_states (LRV:983-1019), flat origins
+        self.root_states[env_ids] = self.base_init_state
+        self.root_states[env_ids, :3] += self.env_origins[env_ids]
+        yaw_rng = float(c["yaw_init_range"])
+        yaw = self.rng(K, 1) * (yaw_rng - (-yaw_rng)) + (-yaw_rng)
+        half = yaw / 2
+        quat = torch.cat([torch.zeros(K, 2, device=self.device), half.sin(), half.cos()], dim=1)     # quat_from_angle_axis(yaw, z)
+        self.root_states[env_ids, 3:7] = quat
+        self.root_states[env_ids, 7:13] = self.rng(K, 6) * (0.5 - (-0.5)) + (-0.5)
+        # buffers (LRV:192-198)
+        self.last_actions[env_ids] = 0.0
+        self.last_last_actions[env_ids] = 0.0
+        self.last_dof_vel[env_ids] = 0.0
+        self.feet_air_time[env_ids] = 0.0
+        self.episode_length_buf[env_ids] = 0
+        self.reset_buf[env_ids] = 1
+        ep = {}
+        for i, n in enumerate(self.reward_names + ["total"]):                                # LRV:200-205
+            ep["rew_" + n] = torch.mean(self.episode_sums[i][env_ids])
+            self.episode_sums[i][env_ids] = 0.0
+        self.extras["train/episode"] = ep
+        self.extras["time_outs"] = self.time_out_buf.bool()                                  # LRV:255-256
+        self.gait.gait_indices[env_ids] = 0.0                                                # LRV:258
+        st["lag_buffer"][:, env_ids, :] = 0.0                                                # LRV:260-261
+
+    # ------------------------------------------------------------------------------------------------ state import (tests, resume)
+    def load_reference_state(self, st):
+        """`init/*` arrays of tests/golden/vel_cfg4_64.npz (the reference env's attribute names)."""
+        dev = self.device
+        put = lambda dst, src: dst.copy_(torch.as_tensor(np.asarray(src)).to(dst.dtype).reshape(dst.shape).to(dev))      # noqa: E731
+        for k in ("episode_length_buf", "commands", "last_actions", "last_last_actions", "last_dof_vel", "last_root_vel", "last_joint_pos_target",
+                  "last_last_joint_pos_target", "root_states", "dof_state", "gravity_vec", "gravities", "last_contacts", "foot_velocities",
+                  "prev_foot_velocities", "foot_positions", "base_lin_vel", "base_ang_vel", "projected_gravity"):
+            if k in st:
+                put(getattr(self, k), st[k])
+        put(self.gait.gait_indices, st["gait_indices"])
+        put(self.friction_coeffs, np.asarray(st["friction_coeffs"])[:, 0])
+        put(self.restitutions, np.asarray(st["restitutions"])[:, 0])
+        ts = self.tq.state
+        for k in ("motor_strengths", "motor_offsets", "joint_pos_err_last", "joint_pos_err_last_last", "joint_vel_last", "joint_vel_last_last",
+                  "joint_pos_target", "torques", "actions"):
+            put(ts[k], st[k])
+        L = ts["lag_buffer"].shape[0]
+        for s_ in range(L):
+            put(ts["lag_buffer"][s_], st[f"lag_buffer/{s_}"])
+        for i, n in enumerate(self.reward_names + ["total"]):
+            put(self.episode_sums[i], st["episode_sums/" + n])
+        for i, n in enumerate(self.reward_names + RAW_SUMS):
+            put(self.command_sums[i], st["command_sums/" + n])
+        self.common_step_counter = int(st["common_step_counter"])
+        self.env_command_categories = np.asarray(st["env_command_categories"]).astype(np.int64).copy()

@@ -19,7 +19,7 @@ def fixture_names(planning=False):
     tests/test_planner.py take: the per-env host mirror has no planner, and the CUDA planner resolves the reference's tied sort
     keys by its own documented rule (tests/test_planner.py)."""
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_", "planner_", "gait_", "commands_") + (() if planning else ("planning_",))))
+                  if not os.path.basename(p).startswith(("actuator", "ppo_", "terrain_", "planner_", "gait_", "commands_", "vel_") + (() if planning else ("planning_",))))
 
 
 def load_fixture(name):
