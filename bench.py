@@ -413,6 +413,52 @@ def terrain_build_timing(dev):
             "host_draws_plus_kernel_ms": wall * 1e3, "bytes": nbytes}
 
 
+def cfg4_step_timing(dev, n_envs, steps=60):
+    """BASELINE.json configs[3]: the velocity-tracking env's full step (4 x torques + the post-physics launch chain of
+    legged_tracking_b200/vel_env.py, 17 x 11 height grid measured on a synthetic heightfield, 70 x 30 observation history) at
+    `n_envs`, driven from Python like the reference drives its own (three nonzero() host reads per step, resets and command
+    resampling through indexed torch writes).  Device time per step, inputs resident in HBM."""
+    from legged_tracking_b200 import synthetic, vel_env
+    cfg = vel_env.cfg4_config()
+    side = int(np.ceil(np.sqrt(n_envs)))
+    xx, yy = np.meshgrid(np.arange(side), np.arange(side), indexing="ij")
+    origins = np.zeros((n_envs, 3), np.float32)
+    origins[:, 0], origins[:, 1] = 3.0 * xx.flatten()[:n_envs], 3.0 * yy.flatten()[:n_envs]
+    rs = np.random.RandomState(5)
+    field = dict(height_samples=rs.randint(-10, 10, size=(int(3.0 * side / 0.1) + 64, int(3.0 * side / 0.1) + 64)).astype(np.int16),
+                 border_size=2.0, horizontal_scale=0.1, vertical_scale=0.005, measured_points_x=vel_env.CFG4_MEASURED_POINTS_X,
+                 measured_points_y=vel_env.CFG4_MEASURED_POINTS_Y)
+    eng = vel_env.VelocityStepEngine(cfg, n_envs, origins, workload.load_actuator(),
+                                     vel_env.UniformCommandSource(vel_env.CFG4_COMMAND_LOW, vel_env.CFG4_COMMAND_HIGH, seed=1), device=dev,
+                                     seed=9, heightfield=field)
+    synth = synthetic.SyntheticState(n_envs, origins, num_bodies=int(cfg["num_bodies"]), seed=77, feet_indices=list(cfg["feet_indices"]))
+    eng.episode_length_buf.copy_(synth.initial_episode_length(cfg["max_episode_length"]).to(dev))
+    frames = []
+    for k in range(3):
+        root = synth.root(k)
+        frames.append({"actions": synth.actions(k).contiguous().to(dev), "root": root.to(dev), "contact": synth.contact(k).to(dev),
+                       "rigid": synth.rigid(k, root).to(dev), "dof_state": [synth.dof_state(k, s).to(dev) for s in range(int(cfg["decimation"]))]})
+    eng.reset_idx(torch.arange(n_envs, device=dev))                    # first commands for every env, as env.reset() does
+
+    def one(k):
+        f = frames[k % 3]
+        eng.step(f["actions"], f)
+    for k in range(5):
+        one(k)
+    resets0 = int(eng.reset_buf.sum())
+    t0 = time.perf_counter()
+    ms = time_region(one, steps)
+    wall = time.perf_counter() - t0
+    no, H = int(cfg["num_obs"]), int(cfg["obs_history_length"])
+    hist_bytes = 2 * 4 * no * H
+    return {"unit": UNIT, "envs": n_envs, "steps": steps, "value": n_envs * steps / (ms * 1e-3), "ms_per_step": ms / steps,
+            "wall_ms_per_step": wall * 1e3 / steps, "resets_last_warmup_step": resets0,
+            "history_bytes_per_env_step": hist_bytes, "history_gb_per_s": hist_bytes * n_envs * steps / (ms * 1e-3) / 1e9,
+            "path": "vel_env.VelocityStepEngine.step: lt_compute_torques x4, lt_vel_measure_heights, lt_vel_pre, lt_resample_commands, "
+                    "lt_step_contact_targets, lt_corl_rewards, lt_vel_reward, reset_idx (indexed torch writes), lt_vel_observe; eager, "
+                    "three nonzero() host reads per step as in the reference"}
+
+
 def strong_block(args, rank, world, dev, dist, peak):
     """BASELINE.json configs[4] as the north-star words it: 65,536 envs IN TOTAL, sharded over the `world` GPUs (strong scaling),
     the full step, and the PPO iteration (T = 24 rollout + GAE + 5 x 4 minibatch update) with its NCCL exchanges timed apart.
@@ -719,6 +765,11 @@ def run_b200(args, rank, world, local_rank):
             line["api_step"] = api_step_timing(args, dev, n_env, max(20, min(args.steps, 200)))
         except Exception as e:                    # auxiliary number
             line["api_step"] = {"error": str(e)[:300]}
+    if world == 1:
+        try:
+            line["cfg4_step"] = {"n4096": cfg4_step_timing(dev, 4096), "n65536": cfg4_step_timing(dev, 65536, steps=30)}
+        except Exception as e:                    # auxiliary number
+            line["cfg4_step"] = {"error": str(e)[:300]}
     try:
         line["terrain_build"] = terrain_build_timing(dev)
     except Exception as e:                        # auxiliary number: never costs the headline line

@@ -451,7 +451,8 @@ typedef struct lt_vel_ptrs {
     /* simulator tensors (LRV:1124-1150): root_states [N,13], rigid_body_state [N,B,13], contact_forces [N,B,3], dof_state [N,12,2] */
     const float *root_states, *rigid_body_state, *contact_forces, *dof_state;
     const float *gravity_vec;                                 /* [N,3] */
-    const float *measured_height_mean;                        /* [N] or NULL (= 0: cfg.terrain.measure_heights off) */
+    const float *measured_height_mean;                        /* [N]: mean over the height points of root_z - measured height
+                                                                 (lt_vel_measure_heights' height_mean), or NULL: plane, root_z itself */
     int64_t* episode_length_buf;                              /* [N] in / out */
     float *base_pos, *base_quat, *base_lin_vel, *base_ang_vel, *projected_gravity;        /* [N,3] [N,4] [N,3] x3 */
     float *foot_positions, *foot_velocities, *prev_foot_velocities;                       /* [N,4,3] */
@@ -470,6 +471,15 @@ typedef struct lt_vel_ptrs {
     const float* obs_history_in;                              /* [N, H * num_obs] */
     float* obs_history_out;                                   /* [N, H * num_obs], a different buffer: the host ping-pongs the two */
 } lt_vel_ptrs;
+/* LeggedRobot._get_heights of the velocity env (LRV:1790-1824) for heightfield / trimesh terrains: the P grid points
+ * (height_points [P,3], base frame, the same for every env: _init_height_points LRV:1773-1788) rotated by the base yaw and
+ * offset by the base position; cell = trunc((p + border_size) / horizontal_scale) clipped to the field; height = the MINIMUM of
+ * the cells (px, py), (px + 1, py), (px, py + 1) of height_samples (int16 [rows, cols]) x vertical_scale.
+ * measured_heights [N,P] out; height_mean [N] out or NULL: mean over the points of root_z - height, what check_termination
+ * compares with terminal_body_height (LRV:163-165) -- pass it as lt_vel_ptrs.measured_height_mean. */
+int lt_vel_measure_heights(const float* root_states, const float* height_points, const int16_t* height_samples, int32_t num_envs,
+                           int32_t n_points, int32_t rows, int32_t cols, float border_size, float horizontal_scale, float vertical_scale,
+                           float* measured_heights, float* height_mean, void* stream);
 int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream);
 /* term_values: the [n_terms, N] block lt_corl_rewards wrote */
 int lt_vel_reward(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* term_values, void* stream);

@@ -109,7 +109,7 @@ lt_ppo_batch_ptrs = _mk("lt_ppo_batch_ptrs")
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
            "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
            "lt_reward_sign_prepass", "lt_term_sum_buffer", "lt_set_term_scales", "lt_counters", "lt_rollout_store", "lt_gae",
-           "lt_normalize_advantages", "lt_build_tunnel_tiles", "lt_plan_target_pose", "lt_measure_heights", "lt_step_contact_targets", "lt_corl_rewards", "lt_resample_commands", "lt_vel_pre", "lt_vel_reward", "lt_vel_observe",
+           "lt_normalize_advantages", "lt_build_tunnel_tiles", "lt_plan_target_pose", "lt_measure_heights", "lt_step_contact_targets", "lt_corl_rewards", "lt_resample_commands", "lt_vel_pre", "lt_vel_reward", "lt_vel_observe", "lt_vel_measure_heights",
            # include/lt_policy.h
            "lt_policy_config_bytes", "lt_policy_create", "lt_policy_destroy", "lt_policy_last_error", "lt_policy_num_params",
            "lt_policy_bind_params", "lt_policy_refresh", "lt_policy_forward", "lt_policy_act", "lt_ppo_minibatch_grad",
@@ -172,6 +172,7 @@ def load(path=LIB_PATH):
     lib.lt_corl_rewards.argtypes = [C.POINTER(lt_corl_cfg), C.POINTER(lt_corl_ptrs), vp]
     lib.lt_resample_commands.argtypes = [C.POINTER(lt_cmd_cfg), C.POINTER(lt_cmd_ptrs), i32, vp]
     lib.lt_vel_pre.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp]
+    lib.lt_vel_measure_heights.argtypes = [vp, vp, vp, i32, i32, i32, i32, f32, f32, f32, vp, vp, vp]
     lib.lt_vel_reward.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp, vp]
     lib.lt_vel_observe.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp, C.c_uint32, vp]
     lib.lt_plan_target_pose.argtypes = [C.POINTER(lt_plan_args), i32, i32, i32, i32, i32, C.POINTER(C.c_float), vp]

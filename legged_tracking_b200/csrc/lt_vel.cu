@@ -52,8 +52,9 @@ __global__ void __launch_bounds__(128) lt_vel_pre_kernel(const __grid_constant__
     reset = reset || time_out;
     bool low = false;
     if (c.use_terminal_body_height) {
-        const float h = p.measured_height_mean ? p.measured_height_mean[i] : 0.0f;    // mean over one column: the value itself
-        low = LT_FSUB(root[2], h) < c.terminal_body_height;
+        // mean(root_z - measured_heights) (LRV:163-165): lt_vel_measure_heights' height_mean, or root_z itself on a plane
+        const float clearance = p.measured_height_mean ? p.measured_height_mean[i] : root[2];
+        low = clearance < c.terminal_body_height;
         reset = reset || low;
     }
     p.time_out_buf[i] = time_out ? 1 : 0;
@@ -187,6 +188,56 @@ __global__ void __launch_bounds__(128) lt_vel_shift_kernel(const __grid_constant
     for (int d = 0; d < 6; ++d) p.last_root_vel[(size_t)i * 6 + d] = p.root_states[(size_t)i * 13 + 7 + d];
 }
 
+// ------------------------------------------------------------------------------------------------ _get_heights (LRV:1790-1824)
+struct lt_vel_height_params {
+    const float *root_states, *height_points;
+    const int16_t* height_samples;
+    int32_t num_envs, n_points, rows, cols;
+    float border_size, horizontal_scale, vertical_scale;
+    float *measured_heights, *height_mean;
+};
+
+// quat_apply_yaw (math_utils.py:12-16): zero x, y; normalise; quat_apply
+__device__ __forceinline__ void lt_vel_apply_yaw(const float q[4], const float v[3], float o[3]) {
+    float n = LT_FSQRT(LT_FADD(LT_FMUL(q[2], q[2]), LT_FMUL(q[3], q[3])));
+    n = fmaxf(n, 1e-9f);
+    const float qy[4] = {0.0f, 0.0f, LT_FDIV(q[2], n), LT_FDIV(q[3], n)};
+    float t[3], u[3];
+    lt_cross(qy, v, t);
+    for (int k = 0; k < 3; ++k) t[k] = LT_FMUL(t[k], 2.0f);
+    lt_cross(qy, t, u);
+    for (int k = 0; k < 3; ++k) o[k] = LT_FADD(LT_FADD(v[k], LT_FMUL(qy[3], t[k])), u[k]);
+}
+
+// warp per env: lanes sweep the grid points (gathers from the int16 field are L2 hits), then one shuffle reduction for the mean
+__global__ void __launch_bounds__(256) lt_vel_heights_kernel(const __grid_constant__ lt_vel_height_params a) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= a.num_envs) return;
+    const float* root = a.root_states + (size_t)i * 13;
+    const float q[4] = {root[3], root[4], root[5], root[6]};
+    float acc = 0.0f;
+    for (int j = lane; j < a.n_points; j += 32) {
+        float o[3];
+        lt_vel_apply_yaw(q, a.height_points + (size_t)j * 3, o);
+        const float x = LT_FDIV(LT_FADD(LT_FADD(o[0], root[0]), a.border_size), a.horizontal_scale);
+        const float y = LT_FDIV(LT_FADD(LT_FADD(o[1], root[1]), a.border_size), a.horizontal_scale);
+        long long px = (long long)x, py = (long long)y;                              // .long(): truncation towards zero
+        px = px < 0 ? 0 : (px > a.rows - 2 ? a.rows - 2 : px);
+        py = py < 0 ? 0 : (py > a.cols - 2 ? a.cols - 2 : py);
+        const int16_t h1 = a.height_samples[px * a.cols + py], h2 = a.height_samples[(px + 1) * a.cols + py],
+                      h3 = a.height_samples[px * a.cols + py + 1];
+        const int16_t hm = min(min(h1, h2), h3);
+        const float h = LT_FMUL((float)hm, a.vertical_scale);
+        a.measured_heights[(size_t)i * a.n_points + j] = h;
+        acc += LT_FSUB(root[2], h);
+    }
+    if (a.height_mean) {
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) a.height_mean[i] = acc / (float)a.n_points;
+    }
+}
+
 static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
     return c && c->num_envs > 0 && c->num_bodies > 0 && c->num_commands >= 3 && c->num_obs > 0 && c->obs_history_length >= 1 &&
            c->n_terms >= 0 && c->n_terms <= LT_CORL_MAX_TERMS && c->n_termination >= 0 && c->n_termination <= 8 && c->sample_interval > 0 &&
@@ -194,6 +245,18 @@ static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
 }
 
 extern "C" {
+
+int lt_vel_measure_heights(const float* root_states, const float* height_points, const int16_t* height_samples, int32_t num_envs,
+                           int32_t n_points, int32_t rows, int32_t cols, float border_size, float horizontal_scale, float vertical_scale,
+                           float* measured_heights, float* height_mean, void* stream) {
+    if (!root_states || !height_points || !height_samples || !measured_heights || num_envs <= 0 || n_points <= 0 || rows < 2 || cols < 2 ||
+        !(horizontal_scale > 0.0f))
+        return LT_ERR_INVALID;
+    lt_vel_height_params a{root_states, height_points, height_samples, num_envs, n_points, rows, cols, border_size, horizontal_scale,
+                           vertical_scale, measured_heights, height_mean};
+    lt_vel_heights_kernel<<<(num_envs + 7) / 8, 256, 0, (cudaStream_t)stream>>>(a);
+    return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
+}
 
 int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream) {
     if (!lt_vel_cfg_ok(cfg) || !ptrs) return LT_ERR_INVALID;

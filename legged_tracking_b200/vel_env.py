@@ -35,6 +35,14 @@ CURRICULUM_KEYS = ["tracking_lin_vel", "tracking_ang_vel", "tracking_contacts_sh
 LOCAL_RANGE = [0.55, 0.55, 0.55, 0.55, 0.35, 0.25, 0.25, 0.25, 0.25, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0]       # LRV:755-757
 
 
+# command ranges of scripts/train_velocity_tracking.py:158-171 (x, y, yaw velocity, body height, gait frequency, phase, offset, bound,
+# duration, footswing height, pitch, roll, stance width, stance length, aux) -- configuration values for UniformCommandSource
+CFG4_COMMAND_LOW = [-1.0, -0.6, -1.0, -0.25, 2.0, 0.0, 0.0, 0.0, 0.5, 0.03, -0.4, -0.0, 0.10, 0.35, 0.0]
+CFG4_COMMAND_HIGH = [1.0, 0.6, 1.0, 0.15, 4.0, 1.0, 1.0, 1.0, 0.5, 0.35, 0.4, 0.0, 0.45, 0.45, 0.01]
+CFG4_MEASURED_POINTS_X = [round(-0.8 + 0.1 * i, 1) for i in range(17)]      # legged_robot_velocity_tracking_config.py: 17 x 11 grid
+CFG4_MEASURED_POINTS_Y = [round(-0.5 + 0.1 * i, 1) for i in range(11)]
+
+
 def cfg4_config():
     """What _parse_cfg / _init_buffers / _prepare_reward_function derive from scripts/train_velocity_tracking.py's Cfg (recorded off
     the live reference env by oracle/gen_golden_vel.py; a config table, not code)."""
@@ -74,7 +82,10 @@ class CurriculumAdapter:
 
 
 class VelocityStepEngine:
-    def __init__(self, cfg, num_envs, env_origins, actuator, command_source, device="cuda:0", seed=0, rng=None):
+    def __init__(self, cfg, num_envs, env_origins, actuator, command_source, device="cuda:0", seed=0, rng=None, heightfield=None):
+        """heightfield: None (plane: measured heights are zero, LRV:1803-1804) or a dict(height_samples int16 [rows, cols], border_size,
+        horizontal_scale, vertical_scale, measured_points_x, measured_points_y) -- the terrain's sample grid as
+        cfg.terrain / Terrain.height_field_raw hold it (LRV:1806-1824)."""
         from . import cfg as ltcfg
         from .engine import StepEngine
         self.device = torch.device(device)
@@ -146,6 +157,16 @@ class VelocityStepEngine:
                                           tracking_contacts_shaped_vel=0.9)     # train_velocity_tracking.py:24-27
         self.sample_interval = int(float(c["resampling_time"]) / self.dt)
         self.step_count = 0
+        self.heightfield = None
+        if heightfield is not None:
+            hf = dict(heightfield)
+            xs, ys = np.asarray(hf["measured_points_x"], np.float32), np.asarray(hf["measured_points_y"], np.float32)
+            gx, gy = np.meshgrid(xs, ys, indexing="ij")                              # _init_height_points (LRV:1773-1788)
+            pts = np.stack([gx.reshape(-1), gy.reshape(-1), np.zeros(gx.size, np.float32)], axis=1)
+            hs = torch.as_tensor(np.asarray(hf["height_samples"])).to(device=dev, dtype=torch.int16).contiguous()
+            self.heightfield = dict(points=f32(pts), samples=hs, border=float(hf["border_size"]), hscale=float(hf["horizontal_scale"]),
+                                    vscale=float(hf["vertical_scale"]))
+            self.measured_heights, self.measured_height_mean = z(N, pts.shape[0]), z(N)
         self._vc = self._make_cfg(seed)
         self._keep = None
 
@@ -199,6 +220,8 @@ class VelocityStepEngine:
                  last_last_joint_pos_target=self.last_last_joint_pos_target, last_dof_vel=self.last_dof_vel, last_root_vel=self.last_root_vel,
                  obs_buf=self.obs_buf, privileged_obs_buf=self.privileged_obs_buf, obs_history_in=self._hist[self._hist_cur],
                  obs_history_out=self._hist[1 - self._hist_cur])
+        if self.heightfield is not None:
+            d["measured_height_mean"] = self.measured_height_mean
         for k, t in d.items():
             setattr(p, k, t.data_ptr())
         return p
@@ -226,6 +249,14 @@ class VelocityStepEngine:
         self.contact_forces.copy_(sim["contact"])
         self.rigid_body_state.copy_(sim["rigid"])
         self.common_step_counter += 1                                                 # LRV:118
+        if self.heightfield is not None:                                              # LRV:708-709 (reads this step's root state only)
+            hf = self.heightfield
+            _abi.check(lib.lt_vel_measure_heights(C.c_void_p(self.root_states.data_ptr()), C.c_void_p(hf["points"].data_ptr()),
+                                                  C.c_void_p(hf["samples"].data_ptr()), self.N, int(hf["points"].shape[0]),
+                                                  int(hf["samples"].shape[0]), int(hf["samples"].shape[1]), C.c_float(hf["border"]),
+                                                  C.c_float(hf["hscale"]), C.c_float(hf["vscale"]),
+                                                  C.c_void_p(self.measured_heights.data_ptr()), C.c_void_p(self.measured_height_mean.data_ptr()), s),
+                       None, "lt_vel_measure_heights")
         _abi.check(lib.lt_vel_pre(C.byref(self._vc), C.byref(self._ptrs()), s), None, "lt_vel_pre")
         # ---- _post_physics_step_callback (LRV:693-726)
         self._resample_commands(self.resample_due.nonzero(as_tuple=False).flatten())

@@ -57,6 +57,38 @@ def dump_state(env, fx, tag):
     fx[tag + "env_command_categories"] = np.asarray(env.env_command_categories).copy()
 
 
+def record_heights(fx, Cfg):
+    """LeggedRobot._init_height_points / _get_heights (LRV:1773-1824), unbound, on a namespace with a synthetic int16 heightfield
+    (cfg 4's real terrain is a trimesh whose generators are not in this image; the lookup itself only needs the field)."""
+    import types
+    import go1_gym.envs.base.legged_robot_velocity_tracking as LRV
+    g = torch.Generator().manual_seed(12)
+    N, rows, cols = 48, 160, 120
+    ns = types.SimpleNamespace(device="cpu", num_envs=N)
+    saved = Cfg.terrain.mesh_type
+    Cfg.terrain.mesh_type = "trimesh"
+    try:
+        ns.height_points = LRV.LeggedRobot._init_height_points(ns, torch.arange(N), Cfg)
+        ns.height_samples = torch.randint(-40, 200, (rows, cols), generator=g, dtype=torch.int16)
+        ns.terrain = types.SimpleNamespace(cfg=types.SimpleNamespace(border_size=2.5, horizontal_scale=0.1, vertical_scale=0.005))
+        ns.root_states = torch.zeros(N, 13)
+        ns.root_states[:, 0] = torch.rand(N, generator=g) * 16 - 3.0          # some robots past the border: indices get clipped
+        ns.root_states[:, 1] = torch.rand(N, generator=g) * 12 - 3.0
+        ns.root_states[:, 2] = 0.3 + 0.1 * torch.rand(N, generator=g)
+        q = torch.randn(N, 4, generator=g)
+        ns.root_states[:, 3:7] = q / q.norm(dim=1, keepdim=True)
+        ns.base_quat = ns.root_states[:, 3:7]
+        h = LRV.LeggedRobot._get_heights(ns, torch.arange(N), Cfg)
+    finally:
+        Cfg.terrain.mesh_type = saved
+    fx["heights/height_points"] = ns.height_points[0].numpy().copy()
+    fx["heights/height_samples"] = ns.height_samples.numpy().copy()
+    fx["heights/root_states"] = ns.root_states.numpy().copy()
+    fx["heights/scales"] = np.asarray([2.5, 0.1, 0.005])
+    fx["heights/measured_heights"] = h.numpy().copy()
+    fx["heights/body_height_mean"] = torch.mean(ns.root_states[:, 2].unsqueeze(1) - h, dim=1).numpy().copy()      # LRV:164
+
+
 def main(num_envs=64, steps=10):
     H.install()
     if not hasattr(np, "int"):
@@ -184,6 +216,7 @@ def main(num_envs=64, steps=10):
             fx[tag + "out/done"] = done.detach().numpy().copy()
             dump_state(env, fx, tag + "state/")
     fx["meta/steps"] = np.int64(steps)
+    record_heights(fx, Cfg)
     np.savez_compressed(OUT, **fx)
     n_reset = sum(int(fx[f"step{k}/out/done"].sum()) for k in range(steps))
     n_samp = sum(1 for k in fx if k.endswith("/commands") and "/curriculum/" in k)

@@ -1,5 +1,7 @@
 mkdir -p gpurun_out
-python bench.py --steps 500 --warmup 5 --no-ppo --no-cpu --e2e-chunks 1 2>gpurun_out/bench_err.log > gpurun_out/bench_quick.json
-python -c "
-import json
-d=json.loads(open('gpurun_out/bench_quick.json').read().strip().splitlines()[-1]); print(d['value'], d['ms_per_step']); print(json.dumps(d['roofline'])[:900])"
+python - <<'PY' > gpurun_out/cfg4.log 2>&1
+import json, torch, bench
+for n in (4096, 65536):
+    print(json.dumps(bench.cfg4_step_timing("cuda:0", n, steps=40)))
+PY
+tail -n 12 gpurun_out/cfg4.log

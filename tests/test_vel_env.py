@@ -144,3 +144,26 @@ def test_cfg4_step_chain_free_runs_the_reference_recording():
         close(cpu(obs["obs_history"]), g[t + "out/obs_history"], f"{k} obs_history")
         assert np.array_equal(eng.env_command_categories, st["env_command_categories"]), f"{k} categories"
         assert eng.common_step_counter == int(st["common_step_counter"])
+
+
+@pytest.mark.gpu
+def test_measure_heights_kernel_matches_the_reference_method():
+    """lt_vel_measure_heights against LeggedRobot._get_heights (LRV:1790-1824) recorded on a synthetic int16 heightfield: 17 x 11
+    points, yaw rotation, border offset, truncation, index clipping (robots past the border), minimum of three cells.  Cells are
+    integers x 0.005: bit-exact; the body-height mean (LRV:164) to 1e-6."""
+    import ctypes as C
+    from legged_tracking_b200 import _abi
+    g = load()
+    lib = _abi.load()
+    dev = torch.device("cuda", 0)
+    pts, hs, root = (torch.from_numpy(g["heights/" + k]).to(dev).contiguous() for k in ("height_points", "height_samples", "root_states"))
+    border, hscale, vscale = (float(x) for x in g["heights/scales"])
+    N, P = root.shape[0], pts.shape[0]
+    assert P == 17 * 11
+    out, mean = torch.empty(N, P, device=dev), torch.empty(N, device=dev)
+    p = lambda t: C.c_void_p(t.data_ptr())                                           # noqa: E731
+    _abi.check(lib.lt_vel_measure_heights(p(root), p(pts), p(hs), N, P, hs.shape[0], hs.shape[1], C.c_float(border), C.c_float(hscale),
+                                          C.c_float(vscale), p(out), p(mean), None), None, "lt_vel_measure_heights")
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), g["heights/measured_heights"])
+    np.testing.assert_allclose(mean.cpu().numpy(), g["heights/body_height_mean"], rtol=1e-6, atol=1e-6)
