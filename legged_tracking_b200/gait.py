@@ -4,8 +4,10 @@
   CoRLRewardKernel   the CoRLRewards container, go1_gym/envs/rewards/corl_rewards.py:15-201 -- all requested _reward_<name> terms
                      in ONE launch, written as the [n_terms, N] block of unscaled values that lt_step_args.extra_reward takes
 
-Both are pointer marshalling around liblt_b200.so (csrc/lt_gait.cu); CUDA only.  They are the building blocks of the cfg 4
-(VelocityTrackingEasyEnv) step, which is not assembled yet.
+  CommandResampler   the tensor half of LeggedRobot._resample_commands, :776-840
+
+All are pointer marshalling around liblt_b200.so (csrc/lt_gait.cu); CUDA only.  vel_env.VelocityStepEngine chains them into the
+cfg 4 (VelocityTrackingEasyEnv) step.
 """
 import ctypes as C
 
