@@ -56,6 +56,79 @@ def test_recording_exercises_the_rare_paths():
     assert ((ep % 500) > 480).any() and (ep > 990).any()                           # resampling interval and time-outs inside the run
 
 
+def test_oracle_restatement_reproduces_the_recording_step_by_step():
+    """oracle/vel_port.py, teacher-forced: each function is given the recorded state the reference method saw and must return what
+    the reference left (steps without a reset for the post-reset quantities)."""
+    from oracle import gait_port, vel_port
+    g = load()
+    c = cfg_of(g)
+    names = c["reward_names"]
+    scales = dict(zip(names, c["reward_scales"]))
+    feet, term = torch.tensor(c["feet_indices"]), torch.tensor(c["termination_contact_indices"])
+    tn = lambda a: torch.from_numpy(np.ascontiguousarray(a))                       # noqa: E731
+    prev = sub(g, "init/")
+    checked_obs = 0
+    for k in range(int(g["meta/steps"])):
+        t = f"step{k}/"
+        st = sub(g, t + "state/")
+        rigid = tn(g[t + "in/rigid"])
+        pre = vel_port.prepare(tn(g[t + "in/root"]), rigid, tn(g[t + "in/contact"]), tn(prev["gravity_vec"]), tn(prev["episode_length_buf"]), feet, term,
+                               c["max_episode_length"], c["use_terminal_body_height"], c["terminal_body_height"])
+        done = g[t + "out/done"]
+        assert np.array_equal(pre["reset_buf"].numpy(), done), k
+        assert np.array_equal(pre["time_out_buf"].numpy(), st["time_out_buf"]), k
+        keep = ~done                                                                # reset envs are overwritten afterwards
+        for name in ("base_lin_vel", "base_ang_vel", "projected_gravity"):
+            np.testing.assert_allclose(pre[name].numpy(), st[name], rtol=1e-6, atol=1e-7, err_msg=f"{k} {name}")
+        assert np.array_equal(pre["foot_positions"].numpy(), st["foot_positions"]) and np.array_equal(pre["foot_velocities"].numpy(), st["foot_velocities"])
+        assert np.array_equal(pre["episode_length_buf"].numpy()[keep], st["episode_length_buf"][keep])
+        # compute_reward on the CoRL terms evaluated by the (already pinned) gait_port restatement, pre-reset state
+        dof = tn(g[t + f"in/dof_state/{c['decimation'] - 1}"]).view(-1, 12, 2)
+        # commands as the reward saw them are the recorded post-step commands for every env that neither reset nor resampled this step
+        due = (pre["episode_length_buf"].numpy() % int(c["resampling_time"] / c["dt"])) == 0
+        cmp = keep & ~due
+        assert cmp.sum() >= 32
+        if True:
+            e = dict(commands=tn(st["commands"]), base_lin_vel=pre["base_lin_vel"], base_ang_vel=pre["base_ang_vel"],
+                     projected_gravity=pre["projected_gravity"], gravity_vec=tn(st["gravity_vec"]), base_pos=pre["base_pos"], base_quat=pre["base_quat"],
+                     torques=tn(g[t + "out/all_torques"][-1]), dof_pos=dof[..., 0], dof_vel=dof[..., 1], last_dof_vel=tn(prev["last_dof_vel"]),
+                     actions=tn(st["actions"]), last_actions=tn(prev["last_actions"]), last_last_actions=tn(prev["last_last_actions"]),
+                     joint_pos_target=tn(st["joint_pos_target"]), last_joint_pos_target=tn(prev["last_joint_pos_target"]),
+                     last_last_joint_pos_target=tn(prev["last_last_joint_pos_target"]), contact_forces=tn(g[t + "in/contact"]),
+                     foot_positions=pre["foot_positions"], foot_velocities=pre["foot_velocities"], prev_foot_velocities=tn(prev["foot_velocities"]),
+                     foot_indices=tn(st["foot_indices"]), desired_contact_states=tn(st["desired_contact_states"]),
+                     default_dof_pos=tn(np.asarray(c["default_dof_pos"], np.float32)), dof_pos_limits=tn(np.asarray(c["dof_pos_limits"], np.float32)),
+                     last_contacts=tn(prev["last_contacts"]), feet_indices=feet, penalised_contact_indices=torch.tensor(c["penalised_contact_indices"]),
+                     dt=c["dt"])
+            vals, _ = gait_port.corl_terms(e, {kk[len("rewards/"):]: v for kk, v in c.items() if kk.startswith("rewards/")}, names)
+            es = {n: tn(prev["episode_sums/" + n]).clone() for n in names + ["total"]}
+            cs = {n: tn(prev["command_sums/" + n]).clone() for n in names + ["lin_vel_raw", "ang_vel_raw", "lin_vel_residual", "ang_vel_residual", "ep_timesteps"]}
+            rew, pos, neg = vel_port.compute_reward(vals, names, scales, es, cs, pre["base_lin_vel"], pre["base_ang_vel"], e["commands"],
+                                                    c["only_positive_rewards"], c["only_positive_rewards_ji22_style"], c["sigma_rew_neg"])
+            np.testing.assert_allclose(rew.numpy()[cmp], g[t + "out/rew"][cmp], rtol=1e-5, atol=1e-6, err_msg=f"{k} rew")
+            np.testing.assert_allclose(pos.numpy()[cmp], st["rew_buf_pos"][cmp], rtol=1e-5, atol=1e-6, err_msg=f"{k} rew_buf_pos")
+            np.testing.assert_allclose(neg.numpy()[cmp], st["rew_buf_neg"][cmp], rtol=1e-5, atol=1e-6, err_msg=f"{k} rew_buf_neg")
+            for n in es:
+                np.testing.assert_allclose(es[n].numpy()[cmp], st["episode_sums/" + n][cmp], rtol=1e-5, atol=1e-6, err_msg=f"{k} episode_sums/{n}")
+            for n in cs:
+                np.testing.assert_allclose(cs[n].numpy()[cmp], st["command_sums/" + n][cmp], rtol=1e-5, atol=1e-6, err_msg=f"{k} command_sums/{n}")
+        # compute_observations on the post-reset state the reference left
+        noise = [g[key] for key in sorted(x for x in g if x.startswith(t + "rng/"))][-1]
+        post_dof = tn(st["dof_state"]).view(-1, 12, 2)
+        obs, priv = vel_port.compute_observations(c, tn(st["projected_gravity"]), tn(st["commands"]), tn(np.asarray(c["commands_scale"], np.float32)),
+                                                  post_dof[..., 0], post_dof[..., 1], tn(np.asarray(c["default_dof_pos"], np.float32)), tn(st["actions"]),
+                                                  tn(prev["last_actions"]) * tn((~done).astype(np.float32)).unsqueeze(1), tn(st["gait_indices"]),
+                                                  tn(st["clock_inputs"]), tn(noise), tn(np.asarray(c["noise_scale_vec"], np.float32)),
+                                                  tn(st["friction_coeffs"])[:, 0], tn(st["restitutions"])[:, 0])
+        np.testing.assert_allclose(obs.numpy(), g[t + "out/obs"], rtol=1e-6, atol=1e-7, err_msg=f"{k} obs")
+        np.testing.assert_allclose(priv.numpy(), g[t + "out/privileged_obs"], rtol=1e-6, atol=1e-7)
+        checked_obs += 1
+        prev = st
+    assert checked_obs == int(g["meta/steps"])
+    h = vel_port.get_heights(tn(g["heights/root_states"]), tn(g["heights/height_points"]), tn(g["heights/height_samples"]), *[float(x) for x in g["heights/scales"]])
+    assert np.array_equal(h.numpy(), g["heights/measured_heights"])
+
+
 class ReplayRng:
     def __init__(self, draws, device):
         self.q = [torch.from_numpy(d) for d in draws]
@@ -167,3 +240,97 @@ def test_measure_heights_kernel_matches_the_reference_method():
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), g["heights/measured_heights"])
     np.testing.assert_allclose(mean.cpu().numpy(), g["heights/body_height_mean"], rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_cfg4_kernels_match_the_oracle_at_config_4_size():
+    """4,096 envs (BASELINE config 4), random state: lt_vel_pre, lt_vel_reward and lt_vel_observe through the C ABI against
+    oracle/vel_port.py (itself pinned to the reference recording), including the 30-row history shift and a ragged tail."""
+    import ctypes as C
+    from legged_tracking_b200 import _abi, vel_env, workload
+    from oracle import vel_port
+    g = load()
+    c = cfg_of(g)
+    N, dev = 4096 + 37, torch.device("cuda", 0)
+    gen = torch.Generator().manual_seed(17)
+    eng = vel_env.VelocityStepEngine(c, N, np.zeros((N, 3), np.float32), workload.load_actuator(), ReplaySource(), device=dev)
+    lib = _abi.load()
+    r = lambda *s: torch.randn(*s, generator=gen)                                  # noqa: E731
+    B = int(c["num_bodies"])
+    root = r(N, 13)
+    root[:, 3:7] /= root[:, 3:7].norm(dim=1, keepdim=True)
+    root[:, 2] = 0.02 + 0.4 * torch.rand(N, generator=gen)
+    rigid, contact = r(N, B, 13), r(N, B, 3) * 0.8
+    ep = torch.randint(0, 1003, (N,), generator=gen)
+    grav = torch.tensor([0.1, -0.05, -0.99]).repeat(N, 1)
+    for dst, src in ((eng.root_states, root), (eng.rigid_body_state, rigid), (eng.contact_forces, contact), (eng.episode_length_buf, ep), (eng.gravity_vec, grav)):
+        dst.copy_(src.to(dev))
+    _abi.check(lib.lt_vel_pre(C.byref(eng._vc), C.byref(eng._ptrs()), None), None, "lt_vel_pre")
+    torch.cuda.synchronize()
+    want = vel_port.prepare(root, rigid, contact, grav, ep, torch.tensor(c["feet_indices"]), torch.tensor(c["termination_contact_indices"]),
+                            c["max_episode_length"], c["use_terminal_body_height"], c["terminal_body_height"])
+    for k in ("base_lin_vel", "base_ang_vel", "projected_gravity", "foot_positions", "foot_velocities", "episode_length_buf"):
+        close(getattr(eng, k).cpu().numpy(), want[k].numpy(), k)
+    for k in ("reset_buf", "time_out_buf", "body_height_buf"):
+        assert np.array_equal(getattr(eng, k).cpu().numpy().astype(bool), want[k].numpy()), k
+    assert 0 < int(want["reset_buf"].sum()) < N
+    iv = int(c["resampling_time"] / c["dt"])
+    assert np.array_equal(eng.resample_due.cpu().numpy().astype(bool), (want["episode_length_buf"].numpy() % iv) == 0)
+    # ---- compute_reward on random term values, mixed-sign sums
+    names = c["reward_names"]
+    scales = dict(zip(names, c["reward_scales"]))
+    vals = torch.rand(len(names), N, generator=gen) * 3
+    vals[3] *= 0                                                                   # an identically-zero term lands in the positive bucket
+    cmd = r(N, int(c["num_commands"]))
+    eng.commands.copy_(cmd.to(dev))
+    es0, cs0 = r(len(names) + 1, N), r(len(names) + 5, N)
+    eng.episode_sums.copy_(es0.to(dev))
+    eng.command_sums.copy_(cs0.to(dev))
+    vd = vals.to(dev)
+    _abi.check(lib.lt_vel_reward(C.byref(eng._vc), C.byref(eng._ptrs()), C.c_void_p(vd.data_ptr()), None), None, "lt_vel_reward")
+    torch.cuda.synchronize()
+    es = {n: es0[i].clone() for i, n in enumerate(names + ["total"])}
+    cs = {n: cs0[i].clone() for i, n in enumerate(names + vel_env.RAW_SUMS)}
+    rew, pos, neg = vel_port.compute_reward({n: vals[i] for i, n in enumerate(names)}, names, scales, es, cs, want["base_lin_vel"], want["base_ang_vel"],
+                                            cmd, c["only_positive_rewards"], c["only_positive_rewards_ji22_style"], c["sigma_rew_neg"])
+    close(eng.rew_buf_pos.cpu().numpy(), pos.numpy(), "rew_buf_pos")
+    close(eng.rew_buf_neg.cpu().numpy(), neg.numpy(), "rew_buf_neg")
+    close(eng.rew_buf.cpu().numpy(), rew.numpy(), "rew_buf", rtol=2e-5, atol=1e-30)
+    for i, n in enumerate(names + ["total"]):
+        close(eng.episode_sums[i].cpu().numpy(), es[n].numpy(), "episode_sums/" + n)
+    for i, n in enumerate(names + vel_env.RAW_SUMS):
+        close(eng.command_sums[i].cpu().numpy(), cs[n].numpy(), "command_sums/" + n)
+    # ---- compute_observations + history shift
+    dof = r(N, 12, 2)
+    acts, last, gait, clock = r(N, 12), r(N, 12), torch.rand(N, generator=gen), r(N, 4)
+    fric, rest = torch.rand(N, generator=gen) * 3, torch.rand(N, generator=gen) * 0.4
+    hist0 = r(N, 30 * 70)
+    noise = torch.rand(N, 70, generator=gen)
+    for dst, src in ((eng.dof_state, dof), (eng.tq.state["actions"], acts), (eng.last_actions, last), (eng.gait.gait_indices, gait),
+                     (eng.gait.clock_inputs, clock), (eng.friction_coeffs, fric), (eng.restitutions, rest), (eng._hist[eng._hist_cur], hist0)):
+        dst.copy_(src.to(dev))
+    nz = noise.to(dev)
+    _abi.check(lib.lt_vel_observe(C.byref(eng._vc), C.byref(eng._ptrs()), C.c_void_p(nz.data_ptr()), C.c_uint32(1), None), None, "lt_vel_observe")
+    torch.cuda.synchronize()
+    f32 = lambda k: torch.tensor(np.asarray(c[k], np.float32))                      # noqa: E731
+    obs, priv = vel_port.compute_observations(c, want["projected_gravity"], cmd, f32("commands_scale"), dof[..., 0], dof[..., 1], f32("default_dof_pos"),
+                                              acts, last, gait, clock, noise, f32("noise_scale_vec"), fric, rest)
+    close(eng.obs_buf.cpu().numpy(), obs.numpy(), "obs")
+    close(eng.privileged_obs_buf.cpu().numpy(), priv.numpy(), "priv")
+    new_hist = eng._hist[1 - eng._hist_cur].cpu()
+    assert torch.equal(new_hist[:, :29 * 70], hist0[:, 70:]) and torch.equal(new_hist[:, 29 * 70:], eng.obs_buf.cpu())
+    assert torch.equal(eng.last_actions.cpu(), acts) and torch.equal(eng.last_last_actions.cpu(), last)
+    assert torch.equal(eng.last_dof_vel.cpu(), dof[..., 1]) and torch.equal(eng.last_root_vel.cpu(), root[:, 7:13])
+    # in-kernel Philox noise: uniform, column-independent, keyed by step
+    eng.obs_buf.zero_()
+    _abi.check(lib.lt_vel_observe(C.byref(eng._vc), C.byref(eng._ptrs()), None, C.c_uint32(2), None), None, "lt_vel_observe")
+    torch.cuda.synchronize()
+    got = eng.obs_buf.cpu()
+    scale = f32("noise_scale_vec")
+    noisy = scale > 0
+    clean, _ = vel_port.compute_observations(dict(c, add_noise=False), want["projected_gravity"], cmd, f32("commands_scale"), dof[..., 0], dof[..., 1],
+                                             f32("default_dof_pos"), acts, acts, gait, clock, noise, scale, fric, rest)
+    u = ((got - clean)[:, noisy] / scale[noisy] + 1) / 2
+    inside = (clean[:, noisy].abs() < c["clip_observations"] - 1)                   # un-clipped entries only
+    uu = u[inside]
+    assert 0.0 <= float(uu.min()) and float(uu.max()) <= 1.0 and abs(float(uu.mean()) - 0.5) < 0.01 and abs(float(uu.std()) - 0.2887) < 0.01
