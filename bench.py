@@ -449,9 +449,13 @@ def cfg4_step_timing(dev, n_envs, steps=60):
     t0 = time.perf_counter()
     ms = time_region(one, steps)
     wall = time.perf_counter() - t0
+    ms_chain = time_region(lambda k: eng.step(frames[k % 3]["actions"], frames[k % 3], host_paths=False), steps)
     no, H = int(cfg["num_obs"]), int(cfg["obs_history_length"])
     hist_bytes = 2 * 4 * no * H
     return {"unit": UNIT, "envs": n_envs, "steps": steps, "value": n_envs * steps / (ms * 1e-3), "ms_per_step": ms / steps,
+            "launch_chain_only": {"ms_per_step": ms_chain / steps, "value": n_envs * steps / (ms_chain * 1e-3),
+                                  "note": "the same step without the host-orchestrated indexed paths (command resampling, interval DR, "
+                                          "reset_idx) and their three host reads: launches only, still issued eagerly from Python"},
             "wall_ms_per_step": wall * 1e3 / steps, "resets_last_warmup_step": resets0,
             "history_bytes_per_env_step": hist_bytes, "history_gb_per_s": hist_bytes * n_envs * steps / (ms * 1e-3) / 1e9,
             "path": "vel_env.VelocityStepEngine.step: lt_compute_torques x4, lt_vel_measure_heights, lt_vel_pre, lt_resample_commands, "

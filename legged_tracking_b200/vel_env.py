@@ -230,9 +230,11 @@ class VelocityStepEngine:
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # ------------------------------------------------------------------------------------------------ the step
-    def step(self, actions, sim, noise_uniforms=None):
+    def step(self, actions, sim, noise_uniforms=None, host_paths=True):
         """actions [N,12]; sim: what PhysX hands back -- dof_state: one [N*12,2] (or [N,12,2]) tensor per sub-step, root [N,13],
-        contact [N,B,3], rigid [N,B,13], all on the device.  -> ({'obs','privileged_obs','obs_history'}, rew, done, extras)"""
+        contact [N,B,3], rigid [N,B,13], all on the device.  -> ({'obs','privileged_obs','obs_history'}, rew, done, extras)
+        host_paths=False (measurement only) leaves out the three host-orchestrated indexed paths -- command resampling, interval
+        DR, reset_idx -- and with them the three nonzero() host reads: what remains is the launch chain alone."""
         tq, lib, s = self.tq, self.lib, self._stream()
         cur = self.dof_state.view(self.N * 12, 2)                                     # what the last refresh left (post reset)
         for sub, dof in enumerate(sim["dof_state"]):                                  # LRV:76-82: torques, THEN simulate + refresh
@@ -259,9 +261,11 @@ class VelocityStepEngine:
                        None, "lt_vel_measure_heights")
         _abi.check(lib.lt_vel_pre(C.byref(self._vc), C.byref(self._ptrs()), s), None, "lt_vel_pre")
         # ---- _post_physics_step_callback (LRV:693-726)
-        self._resample_commands(self.resample_due.nonzero(as_tuple=False).flatten())
+        if host_paths:
+            self._resample_commands(self.resample_due.nonzero(as_tuple=False).flatten())
         self.gait.step(self.commands)
-        self._randomize_dof_props(self.dr_due.nonzero(as_tuple=False).flatten())
+        if host_paths:
+            self._randomize_dof_props(self.dr_due.nonzero(as_tuple=False).flatten())
         self._gravity_schedule()
         # ---- compute_reward (LRV:281-318)
         dof_pos, dof_vel = self.dof_state[..., 0].contiguous(), self.dof_state[..., 1].contiguous()
@@ -277,7 +281,8 @@ class VelocityStepEngine:
         terms = self.corl(env)
         _abi.check(lib.lt_vel_reward(C.byref(self._vc), C.byref(self._ptrs()), C.c_void_p(terms.data_ptr()), s), None, "lt_vel_reward")
         # ---- reset_idx (LRV:169-265)
-        self.reset_idx(self.reset_buf.nonzero(as_tuple=False).flatten())
+        if host_paths:
+            self.reset_idx(self.reset_buf.nonzero(as_tuple=False).flatten())
         # ---- compute_observations + last_* shifts + obs clip + history (LRV:320-470, 143-148, 102-105; history_wrapper.py:23)
         self.step_count += 1
         nz = None
