@@ -481,6 +481,53 @@ int lt_vel_measure_heights(const float* root_states, const float* height_points,
                            int32_t n_points, int32_t rows, int32_t cols, float border_size, float horizontal_scale, float vertical_scale,
                            float* measured_heights, float* height_mean, void* stream);
 int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream);
+
+/* The three indexed paths of the cfg 4 step -- _resample_commands of the due envs and the interval _randomize_dof_props (the
+ * callback, LRV:701-717: which = LT_VEL_PATH_CALLBACK) and reset_idx of reset_buf (LRV:169-265: which = LT_VEL_PATH_RESET) -- without
+ * the host: mask-driven over all envs (no nonzero(), no id list), with the command curriculum itself on the device.
+ *   curriculum (go1_gym/envs/base/curriculum.py:113-152 RewardThresholdCurriculum, one weight row per command category): update =
+ *   every due env whose four task rewards (command_sums / ep_len) beat their thresholds bumps its own bin once and every bin within
+ *   local_range of it once per env, +0.2 clipped to 1 (same result as the reference's sequential numpy updates: the increments
+ *   are equal and the clip is monotone); sample = a bin drawn in proportion to the weights (Curriculum.sample_bins), a point uniform
+ *   inside the bin (sample_uniform_from_cell).  The draws are Philox4x32-10 keyed (seed, step, env, slot), or injected through
+ *   uniform_rows [N, LT_VEL_SLOTS] (tests): they replace numpy's RandomState, so samples are equal in distribution, not bit-wise.
+ *   reset: _randomize_dof_props (LRV:663-673), _reset_dofs (:966-976), _reset_root_states (:983-1015, flat origins), the buffers
+ *   (:192-198, 258-261); finished episodes' sums are accumulated into episode_acc [n_terms + 2] (sum of every episode_sums row over
+ *   the reset envs, then their count) for the extras the reference averages on the host (:200-205). */
+#define LT_VEL_PATH_CALLBACK 0
+#define LT_VEL_PATH_RESET 1
+#define LT_VEL_SLOTS 52              /* uniform slots per env and path: 0 category, 1 bin, 2..16 cell, 17 gait, 18 strength, 19..30 offsets,
+                                        31..42 dof positions, 43 yaw, 44..49 root velocity */
+#define LT_VEL_MAX_DIMS 16
+typedef struct lt_vel_dev_cfg {
+    int32_t n_bins, n_dims, n_keys;                  /* curriculum bins per category, command dims of the grid (15), task-reward keys (<= 4) */
+    int32_t key_rows[4];                             /* command_sums rows of tracking_lin_vel, tracking_ang_vel, tracking_contacts_shaped_force / _vel */
+    float key_thresholds[4];                         /* curriculum_thresholds[key] * reward_scales[key] (LRV:750) */
+    float ep_len;                                    /* min(max_episode_length, int(resampling_time / dt)) (LRV:732-733) */
+    double local_range[LT_VEL_MAX_DIMS];             /* LRV:755-757 */
+    int32_t randomize_motor_strength, randomize_motor_offset, lag_slots;
+    float motor_strength_lo, motor_strength_span, motor_offset_lo, motor_offset_span, yaw_init_range;   /* span = (float)(high - low), the
+                                                        difference taken in double as python does before it meets the float32 tensor */
+    float base_init_state[13];
+    lt_cmd_cfg cmd;                                  /* the gait switches and category table of lt_resample_commands */
+} lt_vel_dev_cfg;
+typedef struct lt_vel_dev_ptrs {
+    const double *grid, *bin_sizes;                  /* [n_dims, n_bins] bin centres, [n_dims] */
+    double* weights;                                 /* [n_categories, n_bins] */
+    int32_t *hit_self, *hit_adj;                     /* [n_categories, n_bins] scratch, zero between calls */
+    int32_t *env_bins, *env_categories;              /* [N] */
+    float *commands;                                 /* [N, num_commands] (lt_vel_ptrs.commands, writable) */
+    float *dof_state_rw, *root_states_rw;            /* [N,12,2], [N,13]: the simulator rows a reset rewrites */
+    const float* env_origins;                        /* [N,3] */
+    float *motor_strengths, *motor_offsets;          /* [N,12] each: the torque kernel's tables */
+    float *lag_buffer;                               /* [lag_slots, N, 12] */
+    float *gait_indices, *feet_air_time;             /* [N], [N,4] */
+    float* episode_acc;                              /* [n_terms + 2] */
+} lt_vel_dev_ptrs;
+/* sizeof of the cfg 4 structs as compiled (0 lt_vel_cfg, 1 lt_vel_ptrs, 2 lt_vel_dev_cfg, 3 lt_vel_dev_ptrs, 4 lt_cmd_cfg): binding check */
+int lt_vel_struct_bytes(int32_t which);
+int lt_vel_indexed_paths(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const lt_vel_dev_cfg* dcfg, const lt_vel_dev_ptrs* dptrs, int32_t which,
+                         const float* uniform_rows, uint32_t step, void* stream);
 /* term_values: the [n_terms, N] block lt_corl_rewards wrote */
 int lt_vel_reward(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* term_values, void* stream);
 /* noise_uniforms [N, num_obs] in [0,1) or NULL -> Philox4x32-10 keyed (seed, step, env, column / 4); read only if add_noise */

@@ -46,7 +46,7 @@ def parse_header(path=HEADER):
             else:
                 name, val = item, val + 1
             enums[name] = val
-    structs, ptr_types = {}, {}
+    structs, ptr_types, classes = {}, {}, {}
     for m in re.finditer(r"typedef struct (\w+) \{(.*?)\}\s*\1;", src, flags=re.S):
         name, body = m.group(1), m.group(2)
         fields, kinds = [], {}
@@ -68,6 +68,8 @@ def parse_header(path=HEADER):
                 if is_ptr:
                     fields.append((item, C.c_void_p))
                     kinds[item] = typ
+                elif typ in classes:                      # a struct declared earlier in the header, embedded by value
+                    fields.append((item, classes[typ]))
                 elif am:
                     ext = am.group(2)
                     n = int(ext) if ext.isdigit() else defines[ext]
@@ -76,14 +78,15 @@ def parse_header(path=HEADER):
                     fields.append((item, _SCALARS[typ]))
         structs[name] = fields
         ptr_types[name] = kinds
-    return defines, enums, structs, ptr_types
+        classes[name] = type(name, (C.Structure,), {"_fields_": fields})
+    return defines, enums, structs, ptr_types, classes
 
 
-DEFINES, ENUMS, _STRUCTS, PTR_TYPES = parse_header()
+DEFINES, ENUMS, _STRUCTS, PTR_TYPES, _CLASSES = parse_header()
 
 
 def _mk(name):
-    return type(name, (C.Structure,), {"_fields_": _STRUCTS[name]})
+    return _CLASSES[name]
 
 
 lt_config = _mk("lt_config")
@@ -102,6 +105,8 @@ lt_cmd_cfg = _mk("lt_cmd_cfg")
 lt_cmd_ptrs = _mk("lt_cmd_ptrs")
 lt_vel_cfg = _mk("lt_vel_cfg")
 lt_vel_ptrs = _mk("lt_vel_ptrs")
+lt_vel_dev_cfg = _mk("lt_vel_dev_cfg")
+lt_vel_dev_ptrs = _mk("lt_vel_dev_ptrs")
 lt_policy_config = _mk("lt_policy_config")
 lt_ppo_hparams = _mk("lt_ppo_hparams")
 lt_ppo_batch_ptrs = _mk("lt_ppo_batch_ptrs")
@@ -109,7 +114,7 @@ lt_ppo_batch_ptrs = _mk("lt_ppo_batch_ptrs")
 EXPORTS = ["lt_abi_version", "lt_config_bytes", "lt_num_uniform_slots", "lt_create", "lt_destroy", "lt_last_error",
            "lt_bind_sim", "lt_bind_terrain", "lt_bind_state", "lt_compute_torques", "lt_post_physics_step", "lt_reset_idx",
            "lt_reward_sign_prepass", "lt_term_sum_buffer", "lt_set_term_scales", "lt_counters", "lt_rollout_store", "lt_gae",
-           "lt_normalize_advantages", "lt_build_tunnel_tiles", "lt_plan_target_pose", "lt_measure_heights", "lt_step_contact_targets", "lt_corl_rewards", "lt_resample_commands", "lt_vel_pre", "lt_vel_reward", "lt_vel_observe", "lt_vel_measure_heights",
+           "lt_normalize_advantages", "lt_build_tunnel_tiles", "lt_plan_target_pose", "lt_measure_heights", "lt_step_contact_targets", "lt_corl_rewards", "lt_resample_commands", "lt_vel_pre", "lt_vel_reward", "lt_vel_observe", "lt_vel_measure_heights", "lt_vel_indexed_paths", "lt_vel_struct_bytes",
            # include/lt_policy.h
            "lt_policy_config_bytes", "lt_policy_create", "lt_policy_destroy", "lt_policy_last_error", "lt_policy_num_params",
            "lt_policy_bind_params", "lt_policy_refresh", "lt_policy_forward", "lt_policy_act", "lt_ppo_minibatch_grad",
@@ -172,6 +177,8 @@ def load(path=LIB_PATH):
     lib.lt_corl_rewards.argtypes = [C.POINTER(lt_corl_cfg), C.POINTER(lt_corl_ptrs), vp]
     lib.lt_resample_commands.argtypes = [C.POINTER(lt_cmd_cfg), C.POINTER(lt_cmd_ptrs), i32, vp]
     lib.lt_vel_pre.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp]
+    lib.lt_vel_indexed_paths.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), C.POINTER(lt_vel_dev_cfg), C.POINTER(lt_vel_dev_ptrs), i32, vp,
+                                         C.c_uint32, vp]
     lib.lt_vel_measure_heights.argtypes = [vp, vp, vp, i32, i32, i32, i32, f32, f32, f32, vp, vp, vp]
     lib.lt_vel_reward.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp, vp]
     lib.lt_vel_observe.argtypes = [C.POINTER(lt_vel_cfg), C.POINTER(lt_vel_ptrs), vp, C.c_uint32, vp]
@@ -198,6 +205,10 @@ def load(path=LIB_PATH):
     lib.lt_linear_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp]
     lib.lt_linear_tn_f32.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
     lib.lt_linear_f32_static.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp]
+    lib.lt_vel_struct_bytes.argtypes = [i32]
+    for which, cls in enumerate((lt_vel_cfg, lt_vel_ptrs, lt_vel_dev_cfg, lt_vel_dev_ptrs, lt_cmd_cfg)):
+        if lib.lt_vel_struct_bytes(which) != C.sizeof(cls):
+            raise LtError(f"sizeof({cls.__name__}) is {lib.lt_vel_struct_bytes(which)} in the library, {C.sizeof(cls)} in the binding: rebuild")
     if lib.lt_policy_config_bytes() != C.sizeof(lt_policy_config):
         raise LtError("sizeof(lt_policy_config) differs between the library and the binding: rebuild")
     if lib.lt_abi_version() != DEFINES["LT_ABI_VERSION"]:

@@ -15,6 +15,8 @@ HEADERS = ["lt_core.cuh", "lt_torque_mma.h"]
 # per-source header dependencies (a change to the GEMM header must not recompile the 3-minute step kernels)
 DEPS = {"lt_policy.cu": [os.path.join(CSRC, "lt_gemm.cuh"), os.path.join(REPO, "include", "lt_policy.h"),
                          os.path.join(REPO, "include", "lt_b200.h")]}
+for _src in ("lt_gait.cu", "lt_vel.cu"):          # the velocity-env sources also share lt_cmd.cuh
+    DEPS[_src] = [os.path.join(CSRC, h) for h in HEADERS + ["lt_cmd.cuh"]] + [os.path.join(REPO, "include", "lt_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-I", os.path.join(REPO, "include")]
 OBJ_DIR = os.path.join(REPO, "build", "obj")

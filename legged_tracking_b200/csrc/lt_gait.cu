@@ -261,12 +261,7 @@ struct lt_cmd_params {
     int count;
 };
 
-// torch's `x % 1` for float tensors: fmod, then one addition when the signs differ (python modulo)
-__device__ __forceinline__ float lt_mod1(float x) {
-    float r = fmodf(x, 1.0f);
-    if (r != 0.0f && r < 0.0f) r += 1.0f;
-    return r;
-}
+#include "lt_cmd.cuh"
 
 __global__ void __launch_bounds__(128) lt_cmd_kernel(const lt_cmd_params a) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -277,49 +272,7 @@ __global__ void __launch_bounds__(128) lt_cmd_kernel(const lt_cmd_params a) {
     float* cmd = a.p.commands + (size_t)env * nc;
     const float* src = a.p.new_commands + (size_t)k * nc;
     for (int j = 0; j < nc; ++j) cmd[j] = src[j];                                   // LRV:776-777
-    if (nc > 5) {
-        float c5 = cmd[5], c6 = cmd[6], c7 = cmd[7];
-        int gait = LT_GAIT_NONE;
-        bool rewrite = false;
-        if (c.gaitwise_curricula) {                                                  // LRV:780-797: by curriculum category
-            const int cat = a.p.category[k];
-            gait = (cat >= 0 && cat < c.n_categories) ? c.category_gait[cat] : LT_GAIT_NONE;
-            rewrite = true;
-        } else if (c.exclusive_phase_offset) {                                       // LRV:799-809: one non-zero column, untouched
-            const float u = a.p.gait_uniform[k];
-            if (u < 0.34f) { c6 = 0.0f; c7 = 0.0f; }                                 // trotting
-            else if (u < 0.67f) { c5 = 0.0f; c7 = 0.0f; }                            // pacing
-            else { c5 = 0.0f; c6 = 0.0f; }                                           // bounding
-        } else if (c.balance_gait_distribution) {                                    // LRV:811-828
-            const float u = a.p.gait_uniform[k];
-            // pronking: u <= 0.25; trotting: 0.25 <= u < 0.5 (u == 0.25 belongs to both index sets: the pronk rewrite first, then
-            // the trot rewrite on top of it, in the reference's statement order)
-            if (u <= 0.25f) { c5 = lt_mod1(c5 / 2.0f - 0.25f); c6 = lt_mod1(c6 / 2.0f - 0.25f); c7 = lt_mod1(c7 / 2.0f - 0.25f); }
-            const bool trot = 0.25f <= u && u < 0.5f, pace = 0.5f <= u && u < 0.75f, bound = 0.75f <= u;
-            if (trot) { c6 = 0.0f; c7 = 0.0f; }
-            if (pace) { c5 = 0.0f; c7 = 0.0f; }
-            if (bound) { c5 = 0.0f; c6 = 0.0f; }
-            if (trot) c5 = c5 / 2.0f + 0.25f;
-            if (pace) c6 = c6 / 2.0f + 0.25f;
-            if (bound) c7 = c7 / 2.0f + 0.25f;
-        }
-        if (rewrite) {
-            if (gait == LT_GAIT_PRONK) { c5 = lt_mod1(c5 / 2.0f - 0.25f); c6 = lt_mod1(c6 / 2.0f - 0.25f); c7 = lt_mod1(c7 / 2.0f - 0.25f); }
-            else if (gait == LT_GAIT_TROT) { c5 = c5 / 2.0f + 0.25f; c6 = 0.0f; c7 = 0.0f; }
-            else if (gait == LT_GAIT_PACE) { c5 = 0.0f; c6 = c6 / 2.0f + 0.25f; c7 = 0.0f; }
-            else if (gait == LT_GAIT_BOUND) { c5 = 0.0f; c6 = 0.0f; c7 = c7 / 2.0f + 0.25f; }
-        }
-        if (c.binary_phases) {                                                       // LRV:830-833: torch.round = half to even
-            c5 = lt_mod1(rintf(2.0f * c5) / 2.0f);
-            c6 = lt_mod1(rintf(2.0f * c6) / 2.0f);
-            c7 = lt_mod1(rintf(2.0f * c7) / 2.0f);
-        }
-        cmd[5] = c5; cmd[6] = c6; cmd[7] = c7;
-    }
-    // LRV:836: commands[env_ids, :2] *= (norm(commands[env_ids, :2]) > 0.2)
-    const float keep = sqrtf(__fadd_rn(__fmul_rn(cmd[0], cmd[0]), __fmul_rn(cmd[1], cmd[1]))) > 0.2f ? 1.0f : 0.0f;
-    cmd[0] *= keep;
-    cmd[1] *= keep;
+    lt_cmd_rewrite(c, cmd, a.p.category ? a.p.category[k] : 0, a.p.gait_uniform ? a.p.gait_uniform[k] : 0.0f);
     if (a.p.command_sums)
         for (int s = 0; s < c.n_sums; ++s) a.p.command_sums[(size_t)s * c.num_envs + env] = 0.0f;     // LRV:839-840
 }

@@ -238,6 +238,152 @@ __global__ void __launch_bounds__(256) lt_vel_heights_kernel(const __grid_consta
     }
 }
 
+// ------------------------------------------------------------------------------------------------ device-side indexed paths
+#include "lt_cmd.cuh"
+
+struct lt_vel_dev_params {
+    lt_vel_cfg c;
+    lt_vel_ptrs p;
+    lt_vel_dev_cfg d;
+    lt_vel_dev_ptrs q;
+    const float* uniform_rows;
+    uint32_t step;
+    int32_t which;
+};
+
+struct lt_vel_rng {                    // per-env uniform slots: injected row or Philox keyed (seed, step | path, env, slot / 4)
+    const float* row;
+    uint32_t seed_lo, seed_hi, step, env;
+    uint32_t blk = 0xffffffffu, o[4] = {0u, 0u, 0u, 0u};
+    __device__ float get(int slot) {
+        if (row) return row[slot];
+        const uint32_t b = (uint32_t)(slot >> 2);
+        if (b != blk) {
+            lt_philox(env, b, step, 0x52455345u, seed_lo, seed_hi, o);
+            blk = b;
+        }
+        return lt_u01(o[slot & 3]);
+    }
+};
+
+__device__ __forceinline__ bool lt_vel_mask_resample(const lt_vel_dev_params& a, int i) {
+    return (a.which == LT_VEL_PATH_RESET ? a.p.reset_buf[i] : a.p.resample_due[i]) != 0;
+}
+
+// curriculum.update, phase A (curriculum.py:133-152): successes mark their own bin and count into every adjacent bin
+__global__ void __launch_bounds__(128) lt_cur_hits_kernel(const __grid_constant__ lt_vel_dev_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.c.num_envs || !lt_vel_mask_resample(a, i) || a.d.n_keys == 0) return;
+    const size_t N = (size_t)a.c.num_envs;
+    bool ok = true;
+    for (int k = 0; k < a.d.n_keys; ++k)
+        ok = ok && (LT_FDIV(a.p.command_sums[(size_t)a.d.key_rows[k] * N + i], a.d.ep_len) > a.d.key_thresholds[k]);
+    if (!ok) return;
+    const int cat = a.q.env_categories[i], b = a.q.env_bins[i], nb = a.d.n_bins;
+    a.q.hit_self[cat * nb + b] = 1;
+    for (int g = 0; g < nb; ++g) {                                                  // get_local_bins (curriculum.py:122-131)
+        bool adj = true;
+        for (int d = 0; d < a.d.n_dims && adj; ++d) {
+            const double cg = a.q.grid[(size_t)d * nb + g], cb = a.q.grid[(size_t)d * nb + b];
+            adj = (cg >= cb - a.d.local_range[d]) && (cg <= cb + a.d.local_range[d]);
+        }
+        if (adj) atomicAdd(a.q.hit_adj + cat * nb + g, 1);
+    }
+}
+// phase B: weights[b] = clip(weights[b] + 0.2, 0, 1), once for the bin itself and once per adjacent success
+__global__ void lt_cur_apply_kernel(double* w, int32_t* hit_self, int32_t* hit_adj, int n) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int k = hit_self[j] + hit_adj[j];
+    double v = w[j];
+    for (int r = 0; r < k; ++r) v = fmin(fmax(v + 0.2, 0.0), 1.0);
+    w[j] = v;
+    hit_self[j] = 0;
+    hit_adj[j] = 0;
+}
+
+__global__ void __launch_bounds__(128) lt_vel_paths_kernel(const __grid_constant__ lt_vel_dev_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const lt_vel_cfg& c = a.c;
+    if (i >= c.num_envs) return;
+    const lt_vel_dev_cfg& d = a.d;
+    const lt_vel_dev_ptrs& q = a.q;
+    const bool reset = a.which == LT_VEL_PATH_RESET && a.p.reset_buf[i];
+    const bool resample = lt_vel_mask_resample(a, i);
+    const bool dr = a.which == LT_VEL_PATH_RESET ? reset : (a.p.dr_due[i] != 0);
+    if (!resample && !dr) return;
+    const size_t N = (size_t)c.num_envs;
+    lt_vel_rng U;
+    U.row = a.uniform_rows ? a.uniform_rows + (size_t)i * LT_VEL_SLOTS : nullptr;
+    U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.step = (a.step << 1) | (uint32_t)a.which; U.env = (uint32_t)i;
+    if (resample) {                                                                  // LRV:759-840
+        const int n_cat = d.cmd.n_categories, nb = d.n_bins, nc = c.num_commands;
+        const float u = U.get(0);
+        const double pc = 1.0 / (double)n_cat;
+        int cat = n_cat - 1;
+        for (int k = 0; k < n_cat; ++k)
+            if ((float)(pc * k) <= u && u < (float)(pc * (k + 1))) { cat = k; break; }
+        const double* w = q.weights + (size_t)cat * nb;
+        double total = 0.0;
+        for (int g = 0; g < nb; ++g) total += w[g];
+        const double target = (double)U.get(1) * total;                              // Curriculum.sample_bins: choice(p = w / sum)
+        int bin = 0;
+        double acc = 0.0;
+        for (int g = 0; g < nb; ++g) {
+            if (w[g] <= 0.0) continue;
+            bin = g;
+            acc += w[g];
+            if (target < acc) break;
+        }
+        float* cmd = q.commands + (size_t)i * nc;
+        for (int k = 0; k < nc && k < d.n_dims; ++k) {                               // sample_uniform_from_cell: uniform(c + s / 2, c - s / 2)
+            const double ctr = q.grid[(size_t)k * nb + bin], lo = ctr + q.bin_sizes[k] / 2, hi = ctr - q.bin_sizes[k] / 2;
+            cmd[k] = (float)(lo + (hi - lo) * (double)U.get(2 + k));
+        }
+        lt_cmd_rewrite(d.cmd, cmd, cat, U.get(17));
+        q.env_bins[i] = bin;
+        q.env_categories[i] = cat;
+        const int n_rows = c.n_terms + 5;
+        for (int r = 0; r < n_rows; ++r) a.p.command_sums[(size_t)r * N + i] = 0.0f;
+    }
+    if (dr) {                                                                        // LRV:663-673
+        if (d.randomize_motor_strength) {
+            const float v = LT_FADD(LT_FMUL(U.get(18), d.motor_strength_span), d.motor_strength_lo);
+            for (int k = 0; k < 12; ++k) q.motor_strengths[(size_t)i * 12 + k] = v;
+        }
+        if (d.randomize_motor_offset)
+            for (int k = 0; k < 12; ++k)
+                q.motor_offsets[(size_t)i * 12 + k] = LT_FADD(LT_FMUL(U.get(19 + k), d.motor_offset_span), d.motor_offset_lo);
+    }
+    if (!reset) return;
+    for (int k = 0; k < 12; ++k) {                                                   // _reset_dofs (LRV:966-976)
+        q.dof_state_rw[((size_t)i * 12 + k) * 2] = LT_FMUL(a.p.default_dof_pos[k], LT_FADD(LT_FMUL(1.0f, U.get(31 + k)), 0.5f));
+        q.dof_state_rw[((size_t)i * 12 + k) * 2 + 1] = 0.0f;
+    }
+    float* root = q.root_states_rw + (size_t)i * 13;                                 // _reset_root_states (LRV:1003-1015)
+    for (int k = 0; k < 13; ++k) root[k] = d.base_init_state[k];
+    for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], q.env_origins[(size_t)i * 3 + k]);
+    const float yaw = LT_FADD(LT_FMUL(LT_FSUB(d.yaw_init_range, -d.yaw_init_range), U.get(43)), -d.yaw_init_range);
+    const float half = LT_FDIV(yaw, 2.0f);
+    root[3] = 0.0f; root[4] = 0.0f; root[5] = sinf(half); root[6] = cosf(half);      // quat_from_angle_axis(yaw, z)
+    for (int k = 0; k < 6; ++k) root[7 + k] = LT_FADD(LT_FMUL(1.0f, U.get(44 + k)), -0.5f);
+    for (int k = 0; k < 12; ++k) {                                                   // LRV:192-198
+        a.p.last_actions[(size_t)i * 12 + k] = 0.0f;
+        a.p.last_last_actions[(size_t)i * 12 + k] = 0.0f;
+        a.p.last_dof_vel[(size_t)i * 12 + k] = 0.0f;
+    }
+    for (int k = 0; k < 4; ++k) q.feet_air_time[(size_t)i * 4 + k] = 0.0f;
+    a.p.episode_length_buf[i] = 0;
+    for (int r = 0; r <= c.n_terms; ++r) {                                           // LRV:200-205
+        atomicAdd(q.episode_acc + r, a.p.episode_sums[(size_t)r * N + i]);
+        a.p.episode_sums[(size_t)r * N + i] = 0.0f;
+    }
+    atomicAdd(q.episode_acc + c.n_terms + 1, 1.0f);
+    q.gait_indices[i] = 0.0f;                                                        // LRV:258
+    for (int s = 0; s < d.lag_slots; ++s)
+        for (int k = 0; k < 12; ++k) q.lag_buffer[((size_t)s * N + i) * 12 + k] = 0.0f;      // LRV:260-261
+}
+
 static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
     return c && c->num_envs > 0 && c->num_bodies > 0 && c->num_commands >= 3 && c->num_obs > 0 && c->obs_history_length >= 1 &&
            c->n_terms >= 0 && c->n_terms <= LT_CORL_MAX_TERMS && c->n_termination >= 0 && c->n_termination <= 8 && c->sample_interval > 0 &&
@@ -268,6 +414,35 @@ int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream) {
     lt_vel_params a;
     a.c = *cfg; a.p = p; a.aux = nullptr; a.step = 0;
     lt_vel_pre_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(a);
+    return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
+}
+
+int lt_vel_struct_bytes(int32_t which) {
+    const size_t sz[5] = {sizeof(lt_vel_cfg), sizeof(lt_vel_ptrs), sizeof(lt_vel_dev_cfg), sizeof(lt_vel_dev_ptrs), sizeof(lt_cmd_cfg)};
+    return which >= 0 && which < 5 ? (int)sz[which] : -1;
+}
+
+int lt_vel_indexed_paths(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const lt_vel_dev_cfg* dcfg, const lt_vel_dev_ptrs* dptrs, int32_t which,
+                         const float* uniform_rows, uint32_t step, void* stream) {
+    if (!lt_vel_cfg_ok(cfg) || !ptrs || !dcfg || !dptrs || (which != LT_VEL_PATH_CALLBACK && which != LT_VEL_PATH_RESET)) return LT_ERR_INVALID;
+    const lt_vel_dev_cfg& d = *dcfg;
+    if (d.n_bins <= 0 || d.n_dims <= 0 || d.n_dims > LT_VEL_MAX_DIMS || d.n_dims < cfg->num_commands || d.n_keys < 0 || d.n_keys > 4 ||
+        d.cmd.n_categories <= 0 || d.cmd.n_categories > LT_CMD_MAX_CATEGORIES || d.cmd.num_commands != cfg->num_commands || d.lag_slots < 0 || !(d.ep_len > 0.0f))
+        return LT_ERR_INVALID;
+    const void* const* pp = reinterpret_cast<const void* const*>(dptrs);
+    for (size_t k = 0; k < sizeof(lt_vel_dev_ptrs) / sizeof(void*); ++k)
+        if (!pp[k]) return LT_ERR_INVALID;
+    const lt_vel_ptrs& p = *ptrs;
+    if (!p.reset_buf || !p.resample_due || !p.dr_due || !p.command_sums || !p.episode_sums || !p.default_dof_pos || !p.last_actions ||
+        !p.last_last_actions || !p.last_dof_vel || !p.episode_length_buf)
+        return LT_ERR_INVALID;
+    cudaStream_t s = (cudaStream_t)stream;
+    lt_vel_dev_params a;
+    a.c = *cfg; a.p = p; a.d = d; a.q = *dptrs; a.uniform_rows = uniform_rows; a.step = step; a.which = which;
+    const int n = cfg->num_envs, nw = d.cmd.n_categories * d.n_bins;
+    lt_cur_hits_kernel<<<(n + 127) / 128, 128, 0, s>>>(a);
+    lt_cur_apply_kernel<<<(nw + 127) / 128, 128, 0, s>>>(dptrs->weights, dptrs->hit_self, dptrs->hit_adj, nw);
+    lt_vel_paths_kernel<<<(n + 127) / 128, 128, 0, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }
 

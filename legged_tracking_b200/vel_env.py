@@ -53,6 +53,24 @@ def scale_shift(rng):
     return 2.0 / (rng[1] - rng[0]), (rng[1] + rng[0]) / 2.0            # go1_gym/utils/math_utils.py:35-38
 
 
+def curriculum_tables(limits, init_region):
+    """The command grid of go1_gym/envs/base/curriculum.py Curriculum.__init__ (:27-60) and the initial weights of set_to (:16-25,
+    LRV:1382-1400): limits [(low, high, n_bins)] per command dimension, init_region [(low, high)].
+    -> (grid [n_dims, n_bins_total] bin centres, bin_sizes [n_dims], weights0 [n_bins_total])"""
+    axes, sizes = [], []
+    for lo, hi, n in limits:
+        n = int(n)
+        size = (hi - lo) / n
+        axes.append(np.linspace(lo + size / 2, hi - size / 2, n))
+        sizes.append(size)
+    grid = np.stack(np.meshgrid(*axes, indexing="ij")).reshape(len(axes), -1)
+    low, high = np.asarray(init_region, np.float64)[:, 0], np.asarray(init_region, np.float64)[:, 1]
+    inside = np.logical_and(grid >= low[:, None], grid <= high[:, None]).all(axis=0)
+    weights = np.zeros(grid.shape[1])
+    weights[inside] = 1.0
+    return grid, np.asarray(sizes, np.float64), weights
+
+
 class UniformCommandSource:
     """A command source without a curriculum: every command uniform inside [low, high] (what curriculum.sample degenerates to when
     every bin has weight 1).  For benchmarks and smoke runs."""
@@ -83,7 +101,10 @@ class CurriculumAdapter:
 
 class VelocityStepEngine:
     def __init__(self, cfg, num_envs, env_origins, actuator, command_source, device="cuda:0", seed=0, rng=None, heightfield=None):
-        """heightfield: None (plane: measured heights are zero, LRV:1803-1804) or a dict(height_samples int16 [rows, cols], border_size,
+        """command_source: a host command source (update / sample, see CurriculumAdapter) -- the reference's arrangement, three host
+        reads per step -- or the string "device": the RewardThresholdCurriculum itself (weights, success update, bin sampling) and the
+        three indexed paths (interval resampling and DR, reset_idx) run as kernels over masks, with no host read in the step.
+        heightfield: None (plane: measured heights are zero, LRV:1803-1804) or a dict(height_samples int16 [rows, cols], border_size,
         horizontal_scale, vertical_scale, measured_points_x, measured_points_y) -- the terrain's sample grid as
         cfg.terrain / Terrain.height_field_raw hold it (LRV:1806-1824)."""
         from . import cfg as ltcfg
@@ -97,6 +118,7 @@ class VelocityStepEngine:
         if c["control_type"] != "actuator_net" or c["custom_origins"] or not c["randomize_lag_timesteps"]:
             raise NotImplementedError("cfg 4 as scripts/train_velocity_tracking.py sets it: actuator_net, lag randomisation, flat origins")
         self.source = command_source
+        self.device_paths = isinstance(command_source, str) and command_source == "device"
         self.rng = rng or (lambda *shape: torch.rand(*shape, device=dev))
         self.dt = float(c["dt"])
         # ---- torques: the trajectory env's kernel and state (LRV:925-964 == LR:957-996), through a plane-terrain StepEngine
@@ -169,6 +191,8 @@ class VelocityStepEngine:
             self.measured_heights, self.measured_height_mean = z(N, pts.shape[0]), z(N)
         self._vc = self._make_cfg(seed)
         self._keep = None
+        if self.device_paths:
+            self._init_device_paths()
 
     # ------------------------------------------------------------------------------------------------ plumbing
     @property
@@ -226,15 +250,77 @@ class VelocityStepEngine:
             setattr(p, k, t.data_ptr())
         return p
 
+    def _init_device_paths(self):
+        c, dev, N = self.cfg, self.device, self.N
+        grid, sizes, w0 = curriculum_tables(c["curriculum_limits"], c["curriculum_init"])
+        n_cat, nb = len(self.category_names), grid.shape[1]
+        f64 = lambda a: torch.as_tensor(np.ascontiguousarray(a, np.float64)).to(dev)           # noqa: E731
+        self.cur_grid, self.cur_bin_sizes = f64(grid), f64(sizes)
+        self.cur_weights = f64(np.tile(w0, (n_cat, 1)))
+        self._hits = torch.zeros(2, n_cat, nb, dtype=torch.int32, device=dev)
+        self.env_bins_dev = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.env_categories_dev = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.episode_acc = torch.zeros(len(self.reward_names) + 2, device=dev)
+        d = _abi.lt_vel_dev_cfg()
+        d.n_bins, d.n_dims = nb, grid.shape[0]
+        keys = [n for n in CURRICULUM_KEYS if n in self.reward_names]
+        d.n_keys = len(keys)
+        for i, n in enumerate(keys):
+            d.key_rows[i] = self.reward_names.index(n)
+            d.key_thresholds[i] = float(c["curriculum_thresholds"][CURRICULUM_KEYS.index(n)]) * self.reward_scales[n]
+        d.ep_len = min(float(c["max_episode_length"]), self.sample_interval)
+        for i, v in enumerate(LOCAL_RANGE[:grid.shape[0]]):
+            d.local_range[i] = v
+        d.randomize_motor_strength, d.randomize_motor_offset = int(bool(c["randomize_motor_strength"])), int(bool(c["randomize_motor_offset"]))
+        d.motor_strength_lo, d.motor_strength_span = c["motor_strength_range"][0], c["motor_strength_range"][1] - c["motor_strength_range"][0]
+        d.motor_offset_lo, d.motor_offset_span = c["motor_offset_range"][0], c["motor_offset_range"][1] - c["motor_offset_range"][0]
+        d.yaw_init_range = float(c["yaw_init_range"])
+        for i, v in enumerate(np.asarray(c["base_init_state"], np.float32).reshape(-1)):
+            d.base_init_state[i] = float(v)
+        d.lag_slots = int(self.tq.state["lag_buffer"].shape[0])
+        d.cmd = self.resampler.cfg
+        self._dc = d
+        q, st = _abi.lt_vel_dev_ptrs(), self.tq.state
+        for k, t in dict(grid=self.cur_grid, bin_sizes=self.cur_bin_sizes, weights=self.cur_weights, hit_self=self._hits[0], hit_adj=self._hits[1],
+                         env_bins=self.env_bins_dev, env_categories=self.env_categories_dev, commands=self.commands, dof_state_rw=self.dof_state,
+                         root_states_rw=self.root_states, env_origins=self.env_origins, motor_strengths=st["motor_strengths"],
+                         motor_offsets=st["motor_offsets"], lag_buffer=st["lag_buffer"], gait_indices=self.gait.gait_indices,
+                         feet_air_time=self.feet_air_time, episode_acc=self.episode_acc).items():
+            setattr(q, k, t.data_ptr())
+        self._dq = q
+
+    def _device_paths(self, which, uniform_rows=None):
+        u = None
+        if uniform_rows is not None:
+            u = uniform_rows.to(device=self.device, dtype=torch.float32).contiguous()
+            self._keep_u = u
+        _abi.check(self.lib.lt_vel_indexed_paths(C.byref(self._vc), C.byref(self._ptrs()), C.byref(self._dc), C.byref(self._dq), which,
+                                                 C.c_void_p(u.data_ptr()) if u is not None else None, C.c_uint32(self.step_count & 0x7fffffff),
+                                                 self._stream()), None, "lt_vel_indexed_paths")
+
+    def reset_all(self):
+        """env.reset() of the device mode: every env through the reset path (first commands, DR, initial state)."""
+        self.reset_buf.fill_(1)
+        self._device_paths(_abi.DEFINES["LT_VEL_PATH_RESET"])
+
+    def episode_means(self):
+        """extras['train/episode'] of the device-side reset path (LRV:200-205): mean of every episode-sum row over the envs reset since
+        the last call (one host read, on demand)."""
+        acc = self.episode_acc.cpu()
+        self.episode_acc.zero_()
+        n = max(float(acc[-1]), 1.0)
+        return {"rew_" + name: float(acc[i]) / n for i, name in enumerate(self.reward_names + ["total"])}
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # ------------------------------------------------------------------------------------------------ the step
-    def step(self, actions, sim, noise_uniforms=None, host_paths=True):
+    def step(self, actions, sim, noise_uniforms=None, host_paths=True, uniform_rows=None):
         """actions [N,12]; sim: what PhysX hands back -- dof_state: one [N*12,2] (or [N,12,2]) tensor per sub-step, root [N,13],
         contact [N,B,3], rigid [N,B,13], all on the device.  -> ({'obs','privileged_obs','obs_history'}, rew, done, extras)
         host_paths=False (measurement only) leaves out the three host-orchestrated indexed paths -- command resampling, interval
-        DR, reset_idx -- and with them the three nonzero() host reads: what remains is the launch chain alone."""
+        DR, reset_idx -- and with them the three nonzero() host reads: what remains is the launch chain alone.
+        uniform_rows (device mode, tests): two [N, LT_VEL_SLOTS] tensors of uniforms for the callback and the reset path."""
         tq, lib, s = self.tq, self.lib, self._stream()
         cur = self.dof_state.view(self.N * 12, 2)                                     # what the last refresh left (post reset)
         for sub, dof in enumerate(sim["dof_state"]):                                  # LRV:76-82: torques, THEN simulate + refresh
@@ -261,10 +347,12 @@ class VelocityStepEngine:
                        None, "lt_vel_measure_heights")
         _abi.check(lib.lt_vel_pre(C.byref(self._vc), C.byref(self._ptrs()), s), None, "lt_vel_pre")
         # ---- _post_physics_step_callback (LRV:693-726)
-        if host_paths:
+        if self.device_paths:
+            self._device_paths(_abi.DEFINES["LT_VEL_PATH_CALLBACK"], uniform_rows[0] if uniform_rows is not None else None)
+        elif host_paths:
             self._resample_commands(self.resample_due.nonzero(as_tuple=False).flatten())
         self.gait.step(self.commands)
-        if host_paths:
+        if host_paths and not self.device_paths:
             self._randomize_dof_props(self.dr_due.nonzero(as_tuple=False).flatten())
         self._gravity_schedule()
         # ---- compute_reward (LRV:281-318)
@@ -281,7 +369,10 @@ class VelocityStepEngine:
         terms = self.corl(env)
         _abi.check(lib.lt_vel_reward(C.byref(self._vc), C.byref(self._ptrs()), C.c_void_p(terms.data_ptr()), s), None, "lt_vel_reward")
         # ---- reset_idx (LRV:169-265)
-        if host_paths:
+        if self.device_paths:
+            self._device_paths(_abi.DEFINES["LT_VEL_PATH_RESET"], uniform_rows[1] if uniform_rows is not None else None)
+            self.extras["time_outs"] = self.time_out_buf
+        elif host_paths:
             self.reset_idx(self.reset_buf.nonzero(as_tuple=False).flatten())
         # ---- compute_observations + last_* shifts + obs clip + history (LRV:320-470, 143-148, 102-105; history_wrapper.py:23)
         self.step_count += 1

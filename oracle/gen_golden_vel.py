@@ -139,6 +139,16 @@ def main(num_envs=64, steps=10):
         fx["cfg/" + k] = np.asarray(v)
     for k in ("tracking_sigma", "tracking_sigma_yaw", "base_height_target", "gait_force_sigma", "gait_vel_sigma", "max_contact_force"):
         fx["cfg/rewards/" + k] = np.float64(getattr(Cfg.rewards, k))
+    cur0 = env.curricula[0]
+    fx["cfg/curriculum_limits"] = np.array([[cur0.lows[i], cur0.highs[i], cur0.ls[k]] for i, k in enumerate(cur0.keys)], np.float64)    # LRV:1328-1374
+    cc = Cfg.commands
+    fx["cfg/curriculum_init"] = np.array([cc.lin_vel_x, cc.lin_vel_y, cc.ang_vel_yaw, cc.body_height_cmd, cc.gait_frequency_cmd_range,
+                                          cc.gait_phase_cmd_range, cc.gait_offset_cmd_range, cc.gait_bound_cmd_range, cc.gait_duration_cmd_range,
+                                          cc.footswing_height_range, cc.body_pitch_range, cc.body_roll_range, cc.stance_width_range,
+                                          cc.stance_length_range, cc.aux_reward_coef_range], np.float64)                              # LRV:1382-1400
+    fx["cfg/curriculum_thresholds"] = np.array([Cfg.curriculum_thresholds.tracking_lin_vel, Cfg.curriculum_thresholds.tracking_ang_vel,
+                                                Cfg.curriculum_thresholds.tracking_contacts_shaped_force,
+                                                Cfg.curriculum_thresholds.tracking_contacts_shaped_vel], np.float64)
     fx["cfg/reward_names"] = np.array(env.reward_names)
     fx["cfg/reward_scales"] = np.array([float(env.reward_scales[n]) for n in env.reward_names])
     fx["cfg/category_names"] = np.array(env.category_names)
@@ -152,6 +162,26 @@ def main(num_envs=64, steps=10):
     fx["cfg/torque_limits"] = env.torque_limits.detach().numpy().copy()
     fx["cfg/base_init_state"] = env.base_init_state.detach().numpy().copy()
     fx["cfg/env_origins"] = env.env_origins.detach().numpy().copy()
+    # ---- the command curriculum as the reference built it (curriculum.py:27-60, LRV:1317-1400), and two of its update() calls on
+    # seeded inputs (curriculum.py:133-152) for the device-side restatement
+    import copy
+    cur = copy.deepcopy(env.curricula[0])
+    fx["curriculum/grid"] = cur.grid.copy()                                  # [15, n_bins] bin centres
+    fx["curriculum/bin_sizes"] = np.array([*cur.bin_sizes.values()])
+    fx["curriculum/weights0"] = cur.weights.copy()
+    fx["curriculum/local_range"] = np.array([0.55, 0.55, 0.55, 0.55, 0.35, 0.25, 0.25, 0.25, 0.25, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0])    # LRV:755-757
+    gc = torch.Generator().manual_seed(21)
+    for call in range(2):
+        nb = 40
+        active = np.nonzero(cur.weights > 0)[0]
+        bins = active[torch.randint(0, len(active), (nb,), generator=gc).numpy()]
+        rewards = [torch.rand(nb, generator=gc) for _ in range(4)]
+        thresholds = [0.35, 0.3, 0.4, 0.25]
+        cur.update(bins, rewards, thresholds, local_range=fx["curriculum/local_range"])
+        fx[f"curriculum/update{call}/bins"] = bins.copy()
+        fx[f"curriculum/update{call}/rewards"] = torch.stack(rewards).numpy().copy()
+        fx[f"curriculum/update{call}/thresholds"] = np.array(thresholds)
+        fx[f"curriculum/update{call}/weights"] = cur.weights.copy()
     # ---- episode phases: timeouts (max_episode_length) and command resampling (every int(resampling_time / dt) steps) inside the recording
     g = torch.Generator().manual_seed(4)
     sample_interval = int(Cfg.commands.resampling_time / env.dt)

@@ -334,3 +334,134 @@ def test_cfg4_kernels_match_the_oracle_at_config_4_size():
     inside = (clean[:, noisy].abs() < c["clip_observations"] - 1)                   # un-clipped entries only
     uu = u[inside]
     assert 0.0 <= float(uu.min()) and float(uu.max()) <= 1.0 and abs(float(uu.mean()) - 0.5) < 0.01 and abs(float(uu.std()) - 0.2887) < 0.01
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# device mode: the curriculum and the three indexed paths as kernels (lt_vel_indexed_paths), no host read in the step
+def _device_engine(g, N, seed=3):
+    from legged_tracking_b200 import vel_env, workload
+    c = cfg_of(g)
+    origins = np.zeros((N, 3), np.float32)
+    origins[:, 0] = np.arange(N) % 97
+    origins[:, 1] = np.arange(N) // 97
+    return vel_env.VelocityStepEngine(c, N, origins, workload.load_actuator(), "device", device=torch.device("cuda", 0), seed=seed), c
+
+
+@pytest.mark.gpu
+def test_device_curriculum_update_equals_the_reference_class():
+    """RewardThresholdCurriculum.update (curriculum.py:133-152) recorded from the unmodified class on seeded inputs, two calls in a
+    row: the device-side weights after lt_vel_indexed_paths equal the reference's (float64, 1e-12)."""
+    from legged_tracking_b200 import _abi
+    g = load()
+    eng, c = _device_engine(g, 64)
+    np.testing.assert_array_equal(eng.cur_weights[0].cpu().numpy(), g["curriculum/weights0"])
+    for call in range(2):
+        bins, rewards, thr = g[f"curriculum/update{call}/bins"], g[f"curriculum/update{call}/rewards"], g[f"curriculum/update{call}/thresholds"]
+        nb = len(bins)
+        eng._dc.ep_len = 1.0
+        for k in range(4):
+            eng._dc.key_thresholds[k] = float(thr[k])
+            eng.command_sums[eng._dc.key_rows[k]].zero_()
+            eng.command_sums[eng._dc.key_rows[k], :nb] = torch.from_numpy(rewards[k]).cuda()
+        eng.env_bins_dev.zero_()
+        eng.env_bins_dev[:nb] = torch.from_numpy(bins.astype(np.int32)).cuda()
+        eng.env_categories_dev.zero_()
+        eng.resample_due.zero_()
+        eng.resample_due[:nb] = 1
+        eng.dr_due.zero_()
+        eng._device_paths(_abi.DEFINES["LT_VEL_PATH_CALLBACK"])
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(eng.cur_weights[0].cpu().numpy(), g[f"curriculum/update{call}/weights"], rtol=0, atol=1e-12)
+        assert float(eng.cur_weights[1:].sub(torch.from_numpy(g["curriculum/weights0"]).cuda()).abs().max()) == 0.0      # other categories untouched
+        assert int(eng._hits.abs().sum()) == 0
+
+
+@pytest.mark.gpu
+def test_device_sampler_draws_bins_by_weight_and_points_inside_the_bin():
+    """Curriculum.sample (curriculum.py:68-91) on the device: bins in proportion to the weights, a point uniform inside the cell,
+    categories uniform (LRV:760-766), the gait rewrite of lt_resample_commands applied, command_sums zeroed."""
+    g = load()
+    N = 65536
+    eng, c = _device_engine(g, N)
+    grid, sizes = g["curriculum/grid"], g["curriculum/bin_sizes"]
+    w = np.zeros(grid.shape[1])
+    active = np.nonzero(g["curriculum/update1/weights"] > 0)[0]
+    w[active] = g["curriculum/update1/weights"][active] * (1 + (np.arange(len(active)) % 3))        # unequal weights
+    w = np.minimum(w, 1.0)
+    eng.cur_weights.copy_(torch.from_numpy(np.tile(w, (4, 1))).cuda())
+    eng.command_sums.fill_(-1e9)                                                                      # never a curriculum success
+    eng.reset_all()
+    torch.cuda.synchronize()
+    bins, cats, cmd = eng.env_bins_dev.cpu().numpy(), eng.env_categories_dev.cpu().numpy(), eng.commands.cpu().numpy().astype(np.float64)
+    assert set(np.unique(bins)) <= set(active.tolist())
+    freq = np.bincount(bins, minlength=len(w)) / N
+    np.testing.assert_allclose(freq[active], w[active] / w.sum(), atol=4 * np.sqrt(1.0 / (len(active) * N)) + 2e-3)
+    np.testing.assert_allclose(np.bincount(cats, minlength=4) / N, 0.25, atol=0.01)
+    ctr = grid[:, bins].T                                                                             # [N, 15]
+    untouched = [0, 1, 2, 3, 4, 8, 9, 10, 11, 12, 13, 14]                                             # columns the gait rewrite leaves alone
+    moving = (np.linalg.norm(cmd[:, :2], axis=1) > 0)                                                 # small planar commands were zeroed (LRV:836)
+    for k in untouched:
+        rows = moving if k < 2 else slice(None)
+        assert np.all(np.abs(cmd[rows, k] - ctr[rows, k]) <= sizes[k] / 2 + 1e-6), k
+    frac = (cmd[moving, 0] - (ctr[moving, 0] - sizes[0] / 2)) / sizes[0]                              # uniform inside the cell
+    assert abs(frac.mean() - 0.5) < 0.01 and abs(frac.std() - 0.2887) < 0.01
+    assert set(np.unique(cmd[:, 5:8]).tolist()) <= {0.0, 0.5}                                         # binary phases after the gait rewrite
+    trot = cats == 1
+    assert np.all(cmd[trot, 6] == 0) and np.all(cmd[trot, 7] == 0)
+    assert float(eng.command_sums.abs().max()) == 0.0
+    assert float(eng.episode_length_buf.abs().max()) == 0
+
+
+@pytest.mark.gpu
+def test_device_reset_path_equals_the_host_orchestrated_one():
+    """The reset path as a kernel against the torch path that free-runs the reference recording (same uniforms, injected per env):
+    DR tables, dof and root rows, buffers, lag ring, episode bookkeeping; and the callback's interval DR."""
+    from legged_tracking_b200 import _abi, vel_env, workload
+    g = load()
+    N = 1000
+    dev_eng, c = _device_engine(g, N)
+    host_eng = vel_env.VelocityStepEngine(c, N, dev_eng.env_origins.cpu().numpy(), workload.load_actuator(), ReplaySource(), device=torch.device("cuda", 0))
+    gen = torch.Generator().manual_seed(9)
+    U = torch.rand(N, _abi.DEFINES["LT_VEL_SLOTS"], generator=gen)
+    reset = torch.rand(N, generator=gen) < 0.3
+    dr = torch.rand(N, generator=gen) < 0.2
+    ids = reset.nonzero().flatten()
+    for e in (dev_eng, host_eng):                                                   # the same dirty state on both
+        g2 = torch.Generator().manual_seed(4)
+        for t in (e.dof_state, e.root_states, e.last_actions, e.last_last_actions, e.last_dof_vel, e.feet_air_time, e.episode_sums,
+                  e.tq.state["lag_buffer"], e.tq.state["motor_strengths"], e.tq.state["motor_offsets"], e.gait.gait_indices):
+            t.copy_(torch.randn(t.shape, generator=g2).to(t.device))
+        e.episode_length_buf.copy_(torch.randint(1, 900, (N,), generator=g2).cuda())
+        e.reset_buf.copy_(reset.to(torch.uint8).cuda())
+        e.dr_due.copy_(dr.to(torch.uint8).cuda())
+        e.resample_due.zero_()
+    want_means = {"rew_" + n: float(host_eng.episode_sums[i][ids.cuda()].mean()) for i, n in enumerate(host_eng.reward_names + ["total"])}
+    # host path: reset_idx draws, in the reference's order -- category, motor strength, motor offsets, dof positions, yaw, root velocity
+    draws = [U[ids, 0], U[ids, 18], U[ids, 19:31], U[ids, 31:43], U[ids, 43:44], U[ids, 44:50]]
+    host_eng.rng = ReplayRng([d.numpy() for d in draws], torch.device("cuda", 0))
+    host_eng.source.q = [(np.zeros((int((host_eng.resampler.categories_from_uniform(U[ids, 0].cuda()) == k).sum()), 15)), np.zeros(0, np.int64))
+                         for k in range(4) if int((host_eng.resampler.categories_from_uniform(U[ids, 0].cuda()) == k).sum())]
+    host_eng.source.sample = lambda cat, n, q=host_eng.source.q: (q.pop(0)[0], np.zeros(n, np.int64))
+    host_eng.reset_idx(ids.cuda())
+    dev_eng._device_paths(_abi.DEFINES["LT_VEL_PATH_RESET"], U)
+    torch.cuda.synchronize()
+    for name in ("dof_state", "last_actions", "last_last_actions", "last_dof_vel", "feet_air_time", "episode_sums", "episode_length_buf"):
+        assert torch.equal(getattr(dev_eng, name), getattr(host_eng, name)), name
+    np.testing.assert_allclose(dev_eng.root_states.cpu().numpy(), host_eng.root_states.cpu().numpy(), rtol=1e-6, atol=1e-7)     # sin / cos of the yaw
+    for name in ("lag_buffer", "motor_strengths", "motor_offsets"):
+        assert torch.equal(dev_eng.tq.state[name], host_eng.tq.state[name]), name
+    assert torch.equal(dev_eng.gait.gait_indices, host_eng.gait.gait_indices)
+    assert np.array_equal(dev_eng.env_categories_dev.cpu().numpy()[ids], host_eng.env_command_categories[ids])
+    got = dev_eng.episode_means()
+    for k, v in want_means.items():
+        assert got[k] == pytest.approx(v, rel=1e-4, abs=1e-5), k
+    # the callback path: interval DR for the dr_due envs only
+    before = {k: host_eng.tq.state[k].clone() for k in ("motor_strengths", "motor_offsets")}
+    dr_ids = dr.nonzero().flatten()
+    host_eng.rng = ReplayRng([U[dr_ids, 18].numpy(), U[dr_ids, 19:31].numpy()], torch.device("cuda", 0))
+    host_eng._randomize_dof_props(dr_ids.cuda())
+    dev_eng._device_paths(_abi.DEFINES["LT_VEL_PATH_CALLBACK"], U)
+    torch.cuda.synchronize()
+    for name in ("motor_strengths", "motor_offsets"):
+        assert torch.equal(dev_eng.tq.state[name], host_eng.tq.state[name]), name
+        assert not torch.equal(before[name], host_eng.tq.state[name])
