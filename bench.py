@@ -450,9 +450,23 @@ def cfg4_step_timing(dev, n_envs, steps=60):
     ms = time_region(one, steps)
     wall = time.perf_counter() - t0
     ms_chain = time_region(lambda k: eng.step(frames[k % 3]["actions"], frames[k % 3], host_paths=False), steps)
+    # device mode: curriculum, resampling, DR and reset as kernels over masks -- no host read in the step
+    dev_eng = vel_env.VelocityStepEngine(cfg, n_envs, origins, workload.load_actuator(), "device", device=dev, seed=9, heightfield=field)
+    dev_eng.episode_length_buf.copy_(synth.initial_episode_length(cfg["max_episode_length"]).to(dev))
+    dev_eng.reset_all()
+    for k in range(5):
+        dev_eng.step(frames[k % 3]["actions"], frames[k % 3])
+    resets_dev = int(dev_eng.reset_buf.sum())
+    t0 = time.perf_counter()
+    ms_dev = time_region(lambda k: dev_eng.step(frames[k % 3]["actions"], frames[k % 3]), steps)
+    wall_dev = time.perf_counter() - t0
     no, H = int(cfg["num_obs"]), int(cfg["obs_history_length"])
     hist_bytes = 2 * 4 * no * H
     return {"unit": UNIT, "envs": n_envs, "steps": steps, "value": n_envs * steps / (ms * 1e-3), "ms_per_step": ms / steps,
+            "device_mode": {"ms_per_step": ms_dev / steps, "value": n_envs * steps / (ms_dev * 1e-3), "wall_ms_per_step": wall_dev * 1e3 / steps,
+                            "resets_last_warmup_step": resets_dev,
+                            "note": "command curriculum (update + sampling), interval resampling / DR and reset_idx as mask-driven kernels "
+                                    "(lt_vel_indexed_paths): the full step with no host read, launches issued eagerly from Python"},
             "launch_chain_only": {"ms_per_step": ms_chain / steps, "value": n_envs * steps / (ms_chain * 1e-3),
                                   "note": "the same step without the host-orchestrated indexed paths (command resampling, interval DR, "
                                           "reset_idx) and their three host reads: launches only, still issued eagerly from Python"},

@@ -465,3 +465,40 @@ def test_device_reset_path_equals_the_host_orchestrated_one():
     for name in ("motor_strengths", "motor_offsets"):
         assert torch.equal(dev_eng.tq.state[name], host_eng.tq.state[name]), name
         assert not torch.equal(before[name], host_eng.tq.state[name])
+
+
+@pytest.mark.gpu
+def test_device_mode_runs_without_a_host_source_and_keeps_the_invariants():
+    """Twenty full steps in device mode on synthetic simulator state: resets and resampling happen, everything stays finite,
+    reset envs come out of the step with episode length 0 and zeroed buffers, commands stay inside the curriculum's limits, the
+    curriculum's weights only grow and stay in [0, 1], and the observation history is the shifted one."""
+    from legged_tracking_b200 import synthetic
+    g = load()
+    N = 2048
+    eng, c = _device_engine(g, N)
+    synth = synthetic.SyntheticState(N, eng.env_origins.cpu().numpy(), num_bodies=int(c["num_bodies"]), seed=5, feet_indices=list(c["feet_indices"]))
+    eng.episode_length_buf.copy_(synth.initial_episode_length(c["max_episode_length"]).cuda())
+    eng.reset_all()
+    w0 = eng.cur_weights.clone()
+    lim = np.asarray(c["curriculum_limits"])
+    n_resets = 0
+    for k in range(20):
+        root = synth.root(k)
+        sim = {"dof_state": [synth.dof_state(k, s).cuda() for s in range(int(c["decimation"]))], "root": root.cuda(), "contact": synth.contact(k).cuda(),
+               "rigid": synth.rigid(k, root).cuda()}
+        prev_hist = eng.obs_history.clone()
+        obs, rew, done, extras = eng.step(synth.actions(k).contiguous().cuda(), sim)
+        torch.cuda.synchronize()
+        n_resets += int(done.sum())
+        for t in (obs["obs"], obs["obs_history"], obs["privileged_obs"], rew, eng.commands, eng.episode_sums, eng.command_sums):
+            assert torch.isfinite(t).all()
+        assert torch.equal(obs["obs_history"][:, :-70], prev_hist[:, 70:]) and torch.equal(obs["obs_history"][:, -70:], obs["obs"])
+        assert int(eng.episode_length_buf[done].abs().sum()) == 0 and float(eng.last_dof_vel[done].abs().sum()) == 0.0
+        assert float(eng.episode_sums[:, done].abs().sum()) == 0.0
+        cmd = eng.commands.cpu().numpy()
+        for d in (0, 1, 2, 3, 4, 9, 10, 12, 13):
+            assert np.all(cmd[:, d] >= lim[d, 0] - 1e-6) and np.all(cmd[:, d] <= lim[d, 1] + 1e-6), d
+    assert n_resets > 0.02 * N * 20
+    assert bool((eng.cur_weights >= w0).all()) and float(eng.cur_weights.max()) <= 1.0
+    means = eng.episode_means()
+    assert set(means) == {"rew_" + n for n in eng.reward_names + ["total"]} and all(np.isfinite(v) for v in means.values())
