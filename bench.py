@@ -460,11 +460,27 @@ def cfg4_step_timing(dev, n_envs, steps=60):
     t0 = time.perf_counter()
     ms_dev = time_region(lambda k: dev_eng.step(frames[k % 3]["actions"], frames[k % 3]), steps)
     wall_dev = time.perf_counter() - t0
+    # ... and the same step replayed as CUDA graphs of two steps each (eager on the steps around a gravity event)
+    pair = [(frames[0]["actions"], frames[0]), (frames[1]["actions"], frames[1])]
+    while not dev_eng.graph_replay_ok(2):
+        dev_eng.step(*pair[0])
+    graph2 = dev_eng.capture(pair)
+
+    def two_steps(k):
+        if dev_eng.graph_replay_ok(2):
+            dev_eng.replay(graph2)
+        else:
+            for a_, f_ in pair:
+                dev_eng.step(a_, f_)
+    two_steps(0)
+    ms_graph = time_region(two_steps, steps // 2) / 2
     no, H = int(cfg["num_obs"]), int(cfg["obs_history_length"])
     hist_bytes = 2 * 4 * no * H
     return {"unit": UNIT, "envs": n_envs, "steps": steps, "value": n_envs * steps / (ms * 1e-3), "ms_per_step": ms / steps,
             "device_mode": {"ms_per_step": ms_dev / steps, "value": n_envs * steps / (ms_dev * 1e-3), "wall_ms_per_step": wall_dev * 1e3 / steps,
                             "resets_last_warmup_step": resets_dev,
+                            "graph_replay": {"ms_per_step": ms_graph / (steps // 2), "value": n_envs * (steps // 2) / (ms_graph * 1e-3),
+                                             "note": "two steps per CUDA graph (the history buffers ping-pong), device-side Philox step counter"},
                             "note": "command curriculum (update + sampling), interval resampling / DR and reset_idx as mask-driven kernels "
                                     "(lt_vel_indexed_paths): the full step with no host read, launches issued eagerly from Python"},
             "launch_chain_only": {"ms_per_step": ms_chain / steps, "value": n_envs * steps / (ms_chain * 1e-3),

@@ -470,6 +470,10 @@ typedef struct lt_vel_ptrs {
     float *obs_buf, *privileged_obs_buf;                      /* [N,num_obs] [N,num_privileged_obs] */
     const float* obs_history_in;                              /* [N, H * num_obs] */
     float* obs_history_out;                                   /* [N, H * num_obs], a different buffer: the host ping-pongs the two */
+    uint32_t* step_counter;                                   /* device uint32[1] or NULL.  Non-NULL: lt_vel_indexed_paths and lt_vel_observe key
+                                                                 their Philox draws with *step_counter instead of their `step` argument, and
+                                                                 lt_vel_observe adds 1 to it when it is done -- so that a CUDA graph of the
+                                                                 step can be replayed (a by-value step would be frozen at capture) */
 } lt_vel_ptrs;
 /* LeggedRobot._get_heights of the velocity env (LRV:1790-1824) for heightfield / trimesh terrains: the P grid points
  * (height_points [P,3], base frame, the same for every env: _init_height_points LRV:1773-1788) rotated by the base yaw and

@@ -119,51 +119,65 @@ __global__ void __launch_bounds__(128) lt_vel_reward_kernel(const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------ compute_observations (LRV:320-470)
-// thread per (env, observation column): the column's value, noise, the clip of step() (LRV:102-103), obs_buf and the newest
-// history row; the same grid then copies the H - 1 older rows one slot towards the past (history_wrapper.py:23).
+// One observation column of env i (before noise and clip): LRV:320-370 for the switches cfg 4 has.
+__device__ __forceinline__ float lt_vel_obs_value(const lt_vel_cfg& c, const lt_vel_ptrs& p, int i, int col) {
+    const int nc = c.observe_command ? c.num_commands : 0;
+    int k = col;
+    if (k < 3) return p.projected_gravity[(size_t)i * 3 + k];
+    if ((k -= 3) < nc) return LT_FMUL(p.commands[(size_t)i * c.num_commands + k], p.commands_scale[k]);
+    if ((k -= nc) < 12) return LT_FMUL(LT_FSUB(p.dof_state[((size_t)i * 12 + k) * 2], p.default_dof_pos[k]), c.obs_scale_dof_pos);
+    if ((k -= 12) < 12) return LT_FMUL(p.dof_state[((size_t)i * 12 + k) * 2 + 1], c.obs_scale_dof_vel);
+    if ((k -= 12) < 12) return p.actions[(size_t)i * 12 + k];
+    k -= 12;
+    const int n_prev = c.observe_two_prev_actions ? 12 : 0, n_tim = c.observe_timing_parameter ? 1 : 0;
+    if (k < n_prev) return p.last_actions[(size_t)i * 12 + k];                        // the pre-shift last_actions (LRV:347-349, 143)
+    if ((k -= n_prev) < n_tim) return p.gait_indices[i];
+    return p.clock_inputs[(size_t)i * 4 + (k - n_tim)];
+}
+__device__ __forceinline__ float lt_vel_obs_finish(const lt_vel_params& a, int i, int col, float v) {
+    const lt_vel_cfg& c = a.c;
+    if (c.add_noise) {                                                                // LRV:391-392
+        float u;
+        if (a.aux) u = a.aux[(size_t)i * c.num_obs + col];
+        else {
+            uint32_t r[4];
+            const uint32_t step = a.p.step_counter ? *a.p.step_counter : a.step;
+            lt_philox((uint32_t)i, (uint32_t)(col >> 2), step, 0x56454c4fu, c.seed_lo, c.seed_hi, r);
+            u = lt_u01(r[col & 3]);
+        }
+        v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), a.p.noise_scale_vec[col]));
+    }
+    return fminf(fmaxf(v, -c.clip_observations), c.clip_observations);                // LRV:102-103
+}
+
+// One CTA per env: its threads sweep the env's history row -- the H - 1 older observations move one slot towards the past
+// (history_wrapper.py:23), the newest slot and obs_buf get this step's observation.  VEC = 2: float2 accesses (num_obs even, so the
+// shift by one observation keeps 8-byte alignment); VEC = 1: any num_obs.
+template <int VEC>
 __global__ void __launch_bounds__(256) lt_vel_observe_kernel(const __grid_constant__ lt_vel_params a) {
     const lt_vel_cfg& c = a.c;
     const lt_vel_ptrs& p = a.p;
-    const int no = c.num_obs, H = c.obs_history_length;
-    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t total = (int64_t)c.num_envs * H * no;
-    if (idx >= total) return;
-    const int i = (int)(idx / ((int64_t)H * no));
-    const int w = (int)(idx % ((int64_t)H * no));
-    float* hist = p.obs_history_out + (size_t)i * H * no;
-    if (w < (H - 1) * no) {                                                           // older rows: shifted by one observation
-        hist[w] = p.obs_history_in[(size_t)i * H * no + w + no];
-        return;
+    const int no = c.num_obs, H = c.obs_history_length, i = blockIdx.x;
+    const int row = H * no, old = (H - 1) * no;
+    const float* in = p.obs_history_in + (size_t)i * row;
+    float* out = p.obs_history_out + (size_t)i * row;
+    for (int w = threadIdx.x * VEC; w < old; w += blockDim.x * VEC) {
+        if (VEC == 2) *reinterpret_cast<float2*>(out + w) = __ldcs(reinterpret_cast<const float2*>(in + w + no));
+        else out[w] = in[w + no];
     }
-    const int col = w - (H - 1) * no;
-    const int nc = c.observe_command ? c.num_commands : 0;
-    float v;
-    int k = col;
-    if (k < 3) v = p.projected_gravity[(size_t)i * 3 + k];
-    else if ((k -= 3) < nc) v = LT_FMUL(p.commands[(size_t)i * c.num_commands + k], p.commands_scale[k]);
-    else if ((k -= nc) < 12) v = LT_FMUL(LT_FSUB(p.dof_state[((size_t)i * 12 + k) * 2], p.default_dof_pos[k]), c.obs_scale_dof_pos);
-    else if ((k -= 12) < 12) v = LT_FMUL(p.dof_state[((size_t)i * 12 + k) * 2 + 1], c.obs_scale_dof_vel);
-    else if ((k -= 12) < 12) v = p.actions[(size_t)i * 12 + k];
-    else {
-        k -= 12;
-        const int n_prev = c.observe_two_prev_actions ? 12 : 0, n_tim = c.observe_timing_parameter ? 1 : 0;
-        if (k < n_prev) v = p.last_actions[(size_t)i * 12 + k];                        // the pre-shift last_actions (LRV:347-349, 143)
-        else if ((k -= n_prev) < n_tim) v = p.gait_indices[i];
-        else { k -= n_tim; v = p.clock_inputs[(size_t)i * 4 + k]; }
-    }
-    if (c.add_noise) {                                                                // LRV:391-392
-        float u;
-        if (a.aux) u = a.aux[(size_t)i * no + col];
-        else {
-            uint32_t r[4];
-            lt_philox((uint32_t)i, (uint32_t)(col >> 2), a.step, 0x56454c4fu, c.seed_lo, c.seed_hi, r);
-            u = lt_u01(r[col & 3]);
+    for (int col = threadIdx.x * VEC; col < no; col += blockDim.x * VEC) {
+        float v[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) v[e] = lt_vel_obs_finish(a, i, col + e, lt_vel_obs_value(c, p, i, col + e));
+        if (VEC == 2) {
+            const float2 t = make_float2(v[0], v[VEC - 1]);
+            *reinterpret_cast<float2*>(out + old + col) = t;
+            *reinterpret_cast<float2*>(p.obs_buf + (size_t)i * no + col) = t;
+        } else {
+            out[old + col] = v[0];
+            p.obs_buf[(size_t)i * no + col] = v[0];
         }
-        v = LT_FADD(v, LT_FMUL(LT_FSUB(LT_FMUL(2.0f, u), 1.0f), p.noise_scale_vec[col]));
     }
-    v = fminf(fmaxf(v, -c.clip_observations), c.clip_observations);                   // LRV:102-103
-    p.obs_buf[(size_t)i * no + col] = v;
-    hist[w] = v;
 }
 
 // thread per env: privileged observations (LRV:396-426 for the two flags cfg 4 sets) and the last_* shifts (LRV:143-148)
@@ -187,6 +201,8 @@ __global__ void __launch_bounds__(128) lt_vel_shift_kernel(const __grid_constant
     }
     for (int d = 0; d < 6; ++d) p.last_root_vel[(size_t)i * 6 + d] = p.root_states[(size_t)i * 13 + 7 + d];
 }
+// last launch of a step: the device-side step counter moves on (its readers of this step are all behind it on the stream)
+__global__ void lt_vel_step_counter_kernel(uint32_t* counter) { *counter += 1u; }
 
 // ------------------------------------------------------------------------------------------------ _get_heights (LRV:1790-1824)
 struct lt_vel_height_params {
@@ -302,20 +318,15 @@ __global__ void lt_cur_apply_kernel(double* w, int32_t* hit_self, int32_t* hit_a
     hit_adj[j] = 0;
 }
 
-__global__ void __launch_bounds__(128) lt_vel_paths_kernel(const __grid_constant__ lt_vel_dev_params a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ void lt_vel_paths_env(const lt_vel_dev_params& a, int i, bool reset, bool resample, bool dr) {
     const lt_vel_cfg& c = a.c;
-    if (i >= c.num_envs) return;
     const lt_vel_dev_cfg& d = a.d;
     const lt_vel_dev_ptrs& q = a.q;
-    const bool reset = a.which == LT_VEL_PATH_RESET && a.p.reset_buf[i];
-    const bool resample = lt_vel_mask_resample(a, i);
-    const bool dr = a.which == LT_VEL_PATH_RESET ? reset : (a.p.dr_due[i] != 0);
-    if (!resample && !dr) return;
     const size_t N = (size_t)c.num_envs;
     lt_vel_rng U;
     U.row = a.uniform_rows ? a.uniform_rows + (size_t)i * LT_VEL_SLOTS : nullptr;
-    U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.step = (a.step << 1) | (uint32_t)a.which; U.env = (uint32_t)i;
+    U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.env = (uint32_t)i;
+    U.step = ((a.p.step_counter ? *a.p.step_counter : a.step) << 1) | (uint32_t)a.which;
     if (resample) {                                                                  // LRV:759-840
         const int n_cat = d.cmd.n_categories, nb = d.n_bins, nc = c.num_commands;
         const float u = U.get(0);
@@ -374,14 +385,34 @@ __global__ void __launch_bounds__(128) lt_vel_paths_kernel(const __grid_constant
     }
     for (int k = 0; k < 4; ++k) q.feet_air_time[(size_t)i * 4 + k] = 0.0f;
     a.p.episode_length_buf[i] = 0;
-    for (int r = 0; r <= c.n_terms; ++r) {                                           // LRV:200-205
-        atomicAdd(q.episode_acc + r, a.p.episode_sums[(size_t)r * N + i]);
-        a.p.episode_sums[(size_t)r * N + i] = 0.0f;
-    }
-    atomicAdd(q.episode_acc + c.n_terms + 1, 1.0f);
     q.gait_indices[i] = 0.0f;                                                        // LRV:258
     for (int s = 0; s < d.lag_slots; ++s)
         for (int k = 0; k < 12; ++k) q.lag_buffer[((size_t)s * N + i) * 12 + k] = 0.0f;      // LRV:260-261
+}
+
+// thread per env over the masks; the finished episodes' sums (LRV:200-205) are reduced per warp before they reach the accumulators
+__global__ void __launch_bounds__(128) lt_vel_paths_kernel(const __grid_constant__ lt_vel_dev_params a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const lt_vel_cfg& c = a.c;
+    const bool in = i < c.num_envs;
+    const bool reset = in && a.which == LT_VEL_PATH_RESET && a.p.reset_buf[i];
+    const bool resample = in && lt_vel_mask_resample(a, i);
+    const bool dr = in && (a.which == LT_VEL_PATH_RESET ? reset : (a.p.dr_due[i] != 0));
+    if (resample || dr) lt_vel_paths_env(a, i, reset, resample, dr);
+    const unsigned m = __ballot_sync(0xffffffffu, reset);
+    if (m == 0u) return;
+    const size_t N = (size_t)c.num_envs;
+    const int lane = threadIdx.x & 31;
+    for (int r = 0; r <= c.n_terms; ++r) {
+        float v = 0.0f;
+        if (reset) {
+            v = a.p.episode_sums[(size_t)r * N + i];
+            a.p.episode_sums[(size_t)r * N + i] = 0.0f;
+        }
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) atomicAdd(a.q.episode_acc + r, v);
+    }
+    if (lane == 0) atomicAdd(a.q.episode_acc + c.n_terms + 1, (float)__popc(m));
 }
 
 static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
@@ -481,9 +512,14 @@ int lt_vel_observe(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* 
     cudaStream_t s = (cudaStream_t)stream;
     lt_vel_params a;
     a.c = *cfg; a.p = p; a.aux = noise_uniforms; a.step = step;
-    const int64_t total = (int64_t)cfg->num_envs * cfg->obs_history_length * cfg->num_obs;
-    lt_vel_observe_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(a);
+    const int row = cfg->obs_history_length * cfg->num_obs;
+    const bool vec2 = (cfg->num_obs % 2) == 0 && (reinterpret_cast<uintptr_t>(p.obs_history_in) % 8) == 0 &&
+                      (reinterpret_cast<uintptr_t>(p.obs_history_out) % 8) == 0 && (reinterpret_cast<uintptr_t>(p.obs_buf) % 8) == 0;
+    (void)row;
+    if (vec2) lt_vel_observe_kernel<2><<<cfg->num_envs, 256, 0, s>>>(a);
+    else lt_vel_observe_kernel<1><<<cfg->num_envs, 256, 0, s>>>(a);
     lt_vel_shift_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, s>>>(a);               // after the observation read last_actions
+    if (p.step_counter) lt_vel_step_counter_kernel<<<1, 1, 0, s>>>(p.step_counter);
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }
 

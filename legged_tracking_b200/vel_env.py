@@ -246,6 +246,8 @@ class VelocityStepEngine:
                  obs_history_out=self._hist[1 - self._hist_cur])
         if self.heightfield is not None:
             d["measured_height_mean"] = self.measured_height_mean
+        if self.device_paths:
+            d["step_counter"] = self.step_counter_dev
         for k, t in d.items():
             setattr(p, k, t.data_ptr())
         return p
@@ -261,6 +263,7 @@ class VelocityStepEngine:
         self.env_bins_dev = torch.zeros(N, dtype=torch.int32, device=dev)
         self.env_categories_dev = torch.zeros(N, dtype=torch.int32, device=dev)
         self.episode_acc = torch.zeros(len(self.reward_names) + 2, device=dev)
+        self.step_counter_dev = torch.zeros(1, dtype=torch.int32, device=dev)       # Philox step key of the device mode (uint32 bits)
         d = _abi.lt_vel_dev_cfg()
         d.n_bins, d.n_dims = nb, grid.shape[0]
         keys = [n for n in CURRICULUM_KEYS if n in self.reward_names]
@@ -297,6 +300,34 @@ class VelocityStepEngine:
         _abi.check(self.lib.lt_vel_indexed_paths(C.byref(self._vc), C.byref(self._ptrs()), C.byref(self._dc), C.byref(self._dq), which,
                                                  C.c_void_p(u.data_ptr()) if u is not None else None, C.c_uint32(self.step_count & 0x7fffffff),
                                                  self._stream()), None, "lt_vel_indexed_paths")
+
+    # ---- CUDA-graph replay of the device-mode step (an even number of steps per graph: the history buffers ping-pong)
+    def graph_replay_ok(self, n_steps=2):
+        """No gravity event (LRV:719-723: a host decision baked into a captured graph) within the next n_steps steps."""
+        c = self.cfg
+        interval, duration = int(float(c["gravity_rand_interval"])), float(c["gravity_rand_duration"])
+        return not any((k % interval == 0) or (int(k - duration) % interval == 0)
+                       for k in range(self.common_step_counter + 1, self.common_step_counter + n_steps + 1))
+
+    def capture(self, frames):
+        """frames: an even number of (actions, sim) pairs whose tensors stay where they are (the simulator writes into them before every
+        replay).  -> a CUDA graph of those steps.  Capture after a few eager steps, on steps for which graph_replay_ok() holds."""
+        if not self.device_paths or len(frames) % 2 or not self.graph_replay_ok(len(frames)):
+            raise _abi.LtError("capture: device mode, an even number of steps, and no gravity event inside them")
+        saved = (self.common_step_counter, self.step_count)
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=self.device)
+        with torch.cuda.graph(g, stream=side):
+            for actions, sim in frames:
+                self.step(actions, sim)
+        self.common_step_counter, self.step_count = saved            # capturing ran the host bookkeeping, not the kernels
+        self._graph_steps = len(frames)
+        return g
+
+    def replay(self, graph):
+        graph.replay()
+        self.common_step_counter += self._graph_steps
+        self.step_count += self._graph_steps
 
     def reset_all(self):
         """env.reset() of the device mode: every env through the reset path (first commands, DR, initial state)."""

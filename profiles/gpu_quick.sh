@@ -1,7 +1,8 @@
 mkdir -p gpurun_out
-python - <<'PY' > gpurun_out/cfg4.log 2>&1
-import json, torch, bench
-for n in (4096, 65536):
-    print(json.dumps(bench.cfg4_step_timing("cuda:0", n, steps=40)))
+timeout 600 python -m pytest tests/test_vel_env.py -m gpu -q -x 2>&1 | tail -n 8
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_cfg4_launches.csv python profiles/run_cfg4.py 65536 4 > gpurun_out/ncu_cfg4.log 2>&1
+python - <<'PY'
+import json, bench
+print(json.dumps(bench.cfg4_step_timing("cuda:0", 4096, steps=40)["device_mode"]))
+print(json.dumps(bench.cfg4_step_timing("cuda:0", 65536, steps=40)["device_mode"]))
 PY
-tail -n 12 gpurun_out/cfg4.log

@@ -502,3 +502,42 @@ def test_device_mode_runs_without_a_host_source_and_keeps_the_invariants():
     assert bool((eng.cur_weights >= w0).all()) and float(eng.cur_weights.max()) <= 1.0
     means = eng.episode_means()
     assert set(means) == {"rew_" + n for n in eng.reward_names + ["total"]} and all(np.isfinite(v) for v in means.values())
+
+
+@pytest.mark.gpu
+def test_device_mode_graph_replay_equals_eager_steps():
+    """Two steps captured as one CUDA graph (device-side Philox step counter, ping-ponged history) replayed twice give, bit for bit,
+    what four eager steps give."""
+    from legged_tracking_b200 import synthetic
+    g = load()
+    N = 1536
+    engines = []
+    for _ in range(2):
+        eng, c = _device_engine(g, N, seed=21)
+        synth = synthetic.SyntheticState(N, eng.env_origins.cpu().numpy(), num_bodies=int(c["num_bodies"]), seed=6, feet_indices=list(c["feet_indices"]))
+        eng.episode_length_buf.copy_(synth.initial_episode_length(c["max_episode_length"]).cuda())
+        eng.reset_all()
+        frames = []
+        for k in range(2):
+            root = synth.root(k)
+            frames.append((synth.actions(k).contiguous().cuda(),
+                           {"dof_state": [synth.dof_state(k, s).cuda() for s in range(int(c["decimation"]))], "root": root.cuda(),
+                            "contact": synth.contact(k).cuda(), "rigid": synth.rigid(k, root).cuda()}))
+        for a, sim in frames:                                                    # two eager warm-up steps on both
+            eng.step(a, sim)
+        engines.append((eng, frames))
+    (eager, fe), (graphed, fg) = engines
+    for _ in range(2):
+        for a, sim in fe:
+            eager.step(a, sim)
+    assert graphed.graph_replay_ok(2)
+    graph = graphed.capture(fg)
+    for _ in range(2):
+        graphed.replay(graph)
+    torch.cuda.synchronize()
+    assert eager.common_step_counter == graphed.common_step_counter and int(eager.step_counter_dev) == int(graphed.step_counter_dev) == 6
+    for name in ("obs_buf", "obs_history", "rew_buf", "commands", "episode_sums", "command_sums", "episode_length_buf", "root_states", "dof_state",
+                 "last_actions", "last_last_actions", "cur_weights", "env_bins_dev", "reset_buf"):
+        assert torch.equal(getattr(eager, name), getattr(graphed, name)), name
+    assert torch.equal(eager.tq.state["lag_buffer"], graphed.tq.state["lag_buffer"]) and torch.equal(eager.tq.counters, graphed.tq.counters)
+    assert int(eager.reset_buf.sum()) > 0
