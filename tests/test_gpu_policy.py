@@ -243,6 +243,35 @@ def test_minibatch_grad_matches_autograd(activation, B, count):
     assert float(ac.grads[hi:].abs().sum()) == 0.0 and float(ac.grads[:lo].abs().sum()) == 0.0      # rest of the bucket untouched
 
 
+def test_policy_with_the_config_4_history_matches_the_oracle():
+    """BASELINE config 4 feeds the policy a 30-row history of 70-wide observations (scripts/train_velocity_tracking.py:80): 2,100 + 4
+    input columns (33 k-blocks of the first-layer contraction, a ragged last one), 4,096 rows forward and one minibatch gradient."""
+    from legged_tracking_b200 import _abi, ppo
+    from oracle import ppo_port
+    lib = _abi.load()
+    torch.manual_seed(31)
+    ac = ppo.ActorCritic(70, 2, 2100, 12).to(_dev())
+    rows = 4096
+    b = _random_batch(ac, rows, 8, _dev())
+    b["obs_history"].mul_(0.5)
+    p64 = _params64(ac)
+    act = ppo_port.ACTIVATIONS["elu"]
+    with torch.no_grad():
+        mean, _, value = ppo_port.policy_forward(p64, act, b["obs_history"].cpu().double(), b["privileged_obs"].cpu().double())
+    _close(ac.act_student(b["obs_history"]), mean, 1e-5, 1e-5 * float(mean.abs().max()), "cfg4 mean")
+    _close(ac.evaluate(b["obs_history"], b["privileged_obs"]), value, 1e-5, 1e-5 * float(value.abs().max()), "cfg4 value")
+    idx = torch.randperm(rows, generator=torch.Generator().manual_seed(1)).to(_dev())
+    ac.grads = torch.zeros(ac.num_params, device=_dev())
+    ac._ready(rows, training=True)
+    stats = torch.zeros(16, device=_dev())
+    hp = ppo.PPO.hparams()
+    bp = _batch_ptrs(b)
+    _abi.check_policy(lib.lt_ppo_minibatch_grad(ac._h, C.byref(bp), _p(idx), rows, C.byref(hp), 1, _p(stats), None), ac._h)
+    torch.cuda.synchronize()
+    want, surr, vl, kl = _oracle_grads(ac, b, idx, dict(ppo_port.PPO_DEFAULTS))
+    _grad_close(ac, ac.grads, want, 1e-4, "cfg4 history")
+
+
 def _cnn_actor_critic(num_obs, P, H, A, shape, emb, seed, **ac_over):
     from legged_tracking_b200 import ppo_cnn
     args = ppo_cnn.AC_Args
