@@ -352,21 +352,30 @@ class VelocityStepEngine:
         host_paths=False (measurement only) leaves out the three host-orchestrated indexed paths -- command resampling, interval
         DR, reset_idx -- and with them the three nonzero() host reads: what remains is the launch chain alone.
         uniform_rows (device mode, tests): two [N, LT_VEL_SLOTS] tensors of uniforms for the callback and the reset path."""
-        tq, lib, s = self.tq, self.lib, self._stream()
-        cur = self.dof_state.view(self.N * 12, 2)                                     # what the last refresh left (post reset)
         for sub, dof in enumerate(sim["dof_state"]):                                  # LRV:76-82: torques, THEN simulate + refresh
-            tq.bind_sim(dof_state=cur)
-            tq.compute_torques(actions, sub)
-            cur = dof.view(self.N * 12, 2)
+            self.apply_torques(actions, sub)
+            self.dof_state.copy_(dof.view(self.N, 12, 2))
+        self.root_states.copy_(sim["root"])
+        self.contact_forces.copy_(sim["contact"])
+        self.rigid_body_state.copy_(sim["rigid"].view(self.rigid_body_state.shape))
+        return self.post_physics_step(noise_uniforms=noise_uniforms, host_paths=host_paths, uniform_rows=uniform_rows)
+
+    def begin_step(self, actions):
+        """Nothing to prepare: the action clip happens inside the first torque launch (LRV:68-69)."""
+
+    def apply_torques(self, actions, sub):
+        """_compute_torques (LRV:925-964) on the dof_state the last refresh left (post reset at sub-step 0)."""
+        self.tq.bind_sim(dof_state=self.dof_state.view(self.N * 12, 2))
+        self.tq.compute_torques(actions, sub)
+
+    def post_physics_step(self, noise_uniforms=None, host_paths=True, uniform_rows=None):
+        """LRV:108-154 on the simulator tensors as they stand (root_states, dof_state, contact_forces, rigid_body_state)."""
+        tq, lib, s = self.tq, self.lib, self._stream()
         # the lag ring and sub-step counters advance with lt_compact_kernel in the trajectory step; here, by hand
-        cnt, n_sub = tq.counters, len(sim["dof_state"])
+        cnt, n_sub = tq.counters, int(self.cfg["decimation"])
         cnt[2] = (cnt[2] + n_sub) % tq.state["lag_buffer"].shape[0]
         cnt[1] += n_sub
         cnt[0] += 1
-        self.dof_state.copy_(sim["dof_state"][-1].view(self.N, 12, 2))
-        self.root_states.copy_(sim["root"])
-        self.contact_forces.copy_(sim["contact"])
-        self.rigid_body_state.copy_(sim["rigid"])
         self.common_step_counter += 1                                                 # LRV:118
         if self.heightfield is not None:                                              # LRV:708-709 (reads this step's root state only)
             hf = self.heightfield
@@ -550,3 +559,265 @@ class VelocityStepEngine:
             put(self.command_sums[i], st["command_sums/" + n])
         self.common_step_counter = int(st["common_step_counter"])
         self.env_command_categories = np.asarray(st["env_command_categories"]).astype(np.int64).copy()
+
+
+# ------------------------------------------------------------------------------------------------ Cfg tree -> the engine's table
+CORL_TERMS_SET = None
+
+
+def config_from_cfg(Cfg, model=None, sim_dt=None):
+    """What LeggedRobot._parse_cfg (LRV:1488-1530), _init_buffers (:1124-1300), _get_noise_scale_vec (:1071-1135), _process_dof_props,
+    _create_envs and _prepare_reward_function (:1402-1450) derive from a velocity-tracking `Cfg` tree (the reference's own class after
+    scripts/train_velocity_tracking.py edited it, or any object with the same attributes) -- the table VelocityStepEngine takes.
+    cfg4_config() is this function's output for that script, recorded off the live reference env."""
+    from . import cfg as ltcfg
+    from .gait import CORL_TERMS
+    model = model or ltcfg.Go1Model
+    c = Cfg
+    f32 = lambda x: float(np.float32(x))                                                   # noqa: E731
+    sim_dt = f32(0.005) if sim_dt is None else float(sim_dt)
+    dt = c.control.decimation * sim_dt
+    bodies = model.body_names
+    feet = [bodies.index(s) for s in bodies if c.asset.foot_name in s]
+    pen = [bodies.index(s) for n in c.asset.penalize_contacts_on for s in bodies if n in s]
+    term = [bodies.index(s) for n in c.asset.terminate_after_contacts_on for s in bodies if n in s]
+    f = np.float32
+    lim = []
+    for a, b in zip(model.dof_lower, model.dof_upper):                                     # soft limits, float32 (LRV _process_dof_props)
+        a, b = f(a), f(b)
+        m, r = (a + b) / f(2), b - a
+        half = f(f(0.5) * r) * f(c.rewards.soft_dof_pos_limit)
+        lim.append([float(m - half), float(m + half)])
+    default_dof_pos = [f32(c.init_state.default_joint_angles[n]) for n in model.dof_names]
+    osc, ns, lvl = c.obs_scales, c.noise_scales, c.noise.noise_level
+    nc, na = int(c.commands.num_commands), int(c.env.num_actions)
+
+    def ones(n, *factors):
+        v = np.ones(n, np.float32)
+        for x in factors:
+            v = v * np.float32(x)
+        return v
+    body = [ones(3, ns.gravity, lvl)]
+    if c.env.observe_command:
+        body.append(np.zeros(nc, np.float32))
+    body += [ones(12, ns.dof_pos, lvl, osc.dof_pos), ones(12, ns.dof_vel, lvl, osc.dof_vel), np.zeros(na, np.float32)]
+    if c.env.observe_two_prev_actions:
+        body.append(np.zeros(na, np.float32))
+    if c.env.observe_timing_parameter:
+        body.append(np.zeros(1, np.float32))
+    if c.env.observe_clock_inputs:
+        body.append(np.zeros(4, np.float32))
+    for flag in ("observe_vel", "observe_only_lin_vel", "observe_only_ang_vel", "observe_yaw", "observe_contact_states"):
+        if getattr(c.env, flag, False):
+            raise NotImplementedError(f"env.{flag}: not among the observation columns of the cfg 4 kernels")
+    noise_vec = np.concatenate(body)
+    commands_scale = [osc.lin_vel, osc.lin_vel, osc.ang_vel, osc.body_height_cmd, osc.gait_freq_cmd, osc.gait_phase_cmd, osc.gait_phase_cmd,
+                      osc.gait_phase_cmd, osc.gait_phase_cmd, osc.footswing_height_cmd, osc.body_pitch_cmd, osc.body_roll_cmd,
+                      osc.stance_width_cmd, osc.stance_length_cmd, osc.aux_reward_cmd][:nc]
+    names, scales = [], []
+    for k, v in vars(c.reward_scales).items():                                             # LRV:1412-1430: non-zero scales x dt, container order
+        if k.startswith("_") or v == 0 or k == "termination":
+            continue
+        if k not in CORL_TERMS:
+            continue                                                                       # not a method of the container: skipped like LRV:1425-1427
+        names.append(k)
+        scales.append(float(v) * dt)
+    cc = c.commands
+    gri = int(np.ceil(c.domain_rand.gravity_rand_interval_s / dt))
+    init = c.init_state
+    limits = [(cc.limit_vel_x, cc.num_bins_vel_x), (cc.limit_vel_y, cc.num_bins_vel_y), (cc.limit_vel_yaw, cc.num_bins_vel_yaw),
+              (cc.limit_body_height, cc.num_bins_body_height), (cc.limit_gait_frequency, cc.num_bins_gait_frequency),
+              (cc.limit_gait_phase, cc.num_bins_gait_phase), (cc.limit_gait_offset, cc.num_bins_gait_offset),
+              (cc.limit_gait_bound, cc.num_bins_gait_bound), (cc.limit_gait_duration, cc.num_bins_gait_duration),
+              (cc.limit_footswing_height, cc.num_bins_footswing_height), (cc.limit_body_pitch, cc.num_bins_body_pitch),
+              (cc.limit_body_roll, cc.num_bins_body_roll), (cc.limit_stance_width, cc.num_bins_stance_width),
+              (cc.limit_stance_length, cc.num_bins_stance_length), (cc.limit_aux_reward_coef, cc.num_bins_aux_reward_coef)]
+    init_region = [cc.lin_vel_x, cc.lin_vel_y, cc.ang_vel_yaw, cc.body_height_cmd, cc.gait_frequency_cmd_range, cc.gait_phase_cmd_range,
+                   cc.gait_offset_cmd_range, cc.gait_bound_cmd_range, cc.gait_duration_cmd_range, cc.footswing_height_range, cc.body_pitch_range,
+                   cc.body_roll_range, cc.stance_width_range, cc.stance_length_range, cc.aux_reward_coef_range]
+    th = c.curriculum_thresholds
+    out = {
+        "num_bodies": len(bodies), "num_commands": nc, "num_obs": int(c.env.num_observations), "num_privileged_obs": int(c.env.num_privileged_obs),
+        "obs_history_length": int(c.env.num_observation_history), "dt": float(dt), "decimation": int(c.control.decimation),
+        "max_episode_length": float(np.ceil(c.env.episode_length_s / dt)), "terminal_body_height": float(c.rewards.terminal_body_height),
+        "use_terminal_body_height": bool(c.rewards.use_terminal_body_height), "resampling_time": float(cc.resampling_time),
+        "rand_interval": float(np.ceil(c.domain_rand.rand_interval_s / dt)), "gravity_rand_interval": float(gri),
+        "gravity_rand_duration": float(np.ceil(gri * c.domain_rand.gravity_impulse_duration)),
+        "gravity_range": [float(x) for x in c.domain_rand.gravity_range], "randomize_gravity": bool(c.domain_rand.randomize_gravity),
+        "only_positive_rewards": bool(c.rewards.only_positive_rewards), "only_positive_rewards_ji22_style": bool(c.rewards.only_positive_rewards_ji22_style),
+        "sigma_rew_neg": float(c.rewards.sigma_rew_neg), "clip_observations": float(c.normalization.clip_observations),
+        "clip_actions": float(c.normalization.clip_actions), "obs_scale_dof_pos": float(osc.dof_pos), "obs_scale_dof_vel": float(osc.dof_vel),
+        "add_noise": bool(c.noise.add_noise), "observe_command": bool(c.env.observe_command), "observe_two_prev_actions": bool(c.env.observe_two_prev_actions),
+        "observe_timing_parameter": bool(c.env.observe_timing_parameter), "observe_clock_inputs": bool(c.env.observe_clock_inputs),
+        "priv_observe_friction": bool(c.env.priv_observe_friction), "priv_observe_restitution": bool(c.env.priv_observe_restitution),
+        "friction_range": [float(x) for x in c.normalization.friction_range], "restitution_range": [float(x) for x in c.normalization.restitution_range],
+        "kappa_gait_probs": float(c.rewards.kappa_gait_probs), "pacing_offset": bool(cc.pacing_offset), "gaitwise_curricula": bool(cc.gaitwise_curricula),
+        "exclusive_phase_offset": bool(cc.exclusive_phase_offset), "balance_gait_distribution": bool(cc.balance_gait_distribution),
+        "binary_phases": bool(cc.binary_phases), "randomize_motor_strength": bool(c.domain_rand.randomize_motor_strength),
+        "motor_strength_range": [float(x) for x in c.domain_rand.motor_strength_range], "randomize_motor_offset": bool(c.domain_rand.randomize_motor_offset),
+        "motor_offset_range": [float(x) for x in c.domain_rand.motor_offset_range], "x_init_range": float(c.terrain.x_init_range),
+        "y_init_range": float(c.terrain.y_init_range), "yaw_init_range": float(c.terrain.yaw_init_range), "x_init_offset": float(c.terrain.x_init_offset),
+        "y_init_offset": float(c.terrain.y_init_offset), "custom_origins": c.terrain.mesh_type in ("heightfield", "trimesh"),
+        "action_scale": float(c.control.action_scale), "hip_scale_reduction": float(c.control.hip_scale_reduction), "control_type": str(c.control.control_type),
+        "lag_timesteps": int(c.domain_rand.lag_timesteps), "randomize_lag_timesteps": bool(c.domain_rand.randomize_lag_timesteps),
+        **{"rewards/" + k: float(getattr(c.rewards, k)) for k in ("tracking_sigma", "tracking_sigma_yaw", "base_height_target", "gait_force_sigma",
+                                                                   "gait_vel_sigma", "max_contact_force")},
+        "curriculum_limits": [[float(r[0]), float(r[1]), float(n)] for r, n in limits], "curriculum_init": [[float(r[0]), float(r[1])] for r in init_region],
+        "curriculum_thresholds": [float(th.tracking_lin_vel), float(th.tracking_ang_vel), float(th.tracking_contacts_shaped_force),
+                                  float(th.tracking_contacts_shaped_vel)],
+        "reward_names": names, "reward_scales": scales, "category_names": ["pronk", "trot", "pace", "bound"] if cc.gaitwise_curricula else ["nominal"],
+        "feet_indices": feet, "penalised_contact_indices": pen, "termination_contact_indices": term,
+        "commands_scale": [f32(x) for x in commands_scale], "default_dof_pos": [default_dof_pos], "dof_pos_limits": lim,
+        "noise_scale_vec": [float(x) for x in noise_vec], "torque_limits": [f32(x) for x in model.dof_effort],
+        "base_init_state": [f32(x) for x in list(init.pos) + list(init.rot) + list(init.lin_vel) + list(init.ang_vel)],
+    }
+    return out
+
+
+class VelocityTrackingEasyEnv:
+    """go1_gym/envs/go1/velocity_tracking/__init__.py:12-60 (VelocityTrackingEasyEnv) with HistoryWrapper's obs dict folded in, around
+    VelocityStepEngine.  PhysX is replaced by a SimBackend (env.SimBackend protocol: simulate(substep) leaves the new dof_state,
+    refresh() the root / contact / rigid-body tensors); the rest of the constructor signature is the reference's.
+
+      env = VelocityTrackingEasyEnv(sim_device="cuda:0", headless=True, cfg=Cfg, sim=my_backend)
+      obs_dict = env.reset();  obs_dict, rew, done, info = env.step(actions)
+
+    cfg: the reference's Cfg tree (config_from_cfg derives the engine's table), an already derived table (dict), or None for
+    scripts/train_velocity_tracking.py's configuration.  command_source: "device" (default) or a host source (CurriculumAdapter)."""
+
+    def __init__(self, sim_device, headless, num_envs=None, prone=False, deploy=False, cfg=None, eval_cfg=None, initial_dynamics_dict=None,
+                 physics_engine="SIM_PHYSX", sim=None, command_source="device", env_origins=None, heightfield=None, seed=0):
+        from . import workload
+        if eval_cfg is not None or initial_dynamics_dict is not None or prone or deploy:
+            raise NotImplementedError("eval_cfg / initial_dynamics_dict / prone / deploy: not on the cfg 4 step path")
+        if sim is None:
+            raise ValueError("a SimBackend is required (there is no PhysX here): see legged_tracking_b200.env.SimBackend / VelReplaySim")
+        table = cfg4_config() if cfg is None else (dict(cfg) if isinstance(cfg, dict) else config_from_cfg(cfg))
+        if num_envs is None:
+            num_envs = int(cfg.env.num_envs) if (cfg is not None and not isinstance(cfg, dict)) else 4096
+        self.cfg, self.num_envs, self.num_train_envs, self.num_eval_envs = cfg, int(num_envs), int(num_envs), 0
+        self.device = torch.device(sim_device)
+        self.headless = headless
+        if env_origins is None:                                        # _get_env_origins on a plane (LRV:1700-1716): a grid, env_spacing apart
+            side = int(np.floor(np.sqrt(self.num_envs)))
+            rows = int(np.ceil(self.num_envs / side))
+            xx, yy = np.meshgrid(np.arange(rows), np.arange(side), indexing="ij")
+            spacing = float(getattr(getattr(cfg, "env", None), "env_spacing", 3.0)) if cfg is not None and not isinstance(cfg, dict) else 3.0
+            env_origins = np.zeros((self.num_envs, 3), np.float32)
+            env_origins[:, 0], env_origins[:, 1] = spacing * xx.flatten()[:self.num_envs], spacing * yy.flatten()[:self.num_envs]
+        self.engine = VelocityStepEngine(table, self.num_envs, env_origins, workload.load_actuator(), command_source, device=self.device, seed=seed,
+                                         heightfield=heightfield)
+        e = self.engine
+        self.num_obs, self.num_privileged_obs, self.num_actions = int(table["num_obs"]), int(table["num_privileged_obs"]), 12
+        self.num_obs_history = self.num_obs * int(table["obs_history_length"])
+        self.max_episode_length, self.dt = float(table["max_episode_length"]), float(table["dt"])
+        self.sim = sim
+        self.sim.attach(self)
+        # the tensors a backend writes into / reads (Isaac Gym layouts)
+        self.root_states, self.dof_state, self.contact_forces, self.rigid_body_state = e.root_states, e.dof_state, e.contact_forces, e.rigid_body_state
+        self.torques = e.tq.state["torques"]
+        self.extras = e.extras
+
+    # VecEnv attributes the runner reads (go1_gym_learn/env/vec_env.py:10-39)
+    @property
+    def obs_buf(self):
+        return self.engine.obs_buf
+
+    @property
+    def privileged_obs_buf(self):
+        return self.engine.privileged_obs_buf
+
+    @property
+    def rew_buf(self):
+        return self.engine.rew_buf
+
+    @property
+    def reset_buf(self):
+        return self.engine.reset_buf
+
+    @property
+    def episode_length_buf(self):
+        return self.engine.episode_length_buf
+
+    @property
+    def commands(self):
+        return self.engine.commands
+
+    def _obs_dict(self):
+        e = self.engine
+        return {"obs": e.obs_buf, "privileged_obs": e.privileged_obs_buf, "obs_history": e.obs_history}
+
+    def get_observations(self):
+        return self._obs_dict()
+
+    def get_privileged_observations(self):
+        return self.engine.privileged_obs_buf
+
+    def step(self, actions):
+        """LRV:60-105 through the backend: torques -> simulate -> refreshed dof_state, decimation times; then the post-physics chain."""
+        e = self.engine
+        actions = actions.to(device=self.device, dtype=torch.float32).contiguous()
+        e.begin_step(actions)
+        for sub in range(int(e.cfg["decimation"])):
+            e.apply_torques(actions, sub)
+            self.sim.simulate(sub)
+        self.sim.refresh()
+        obs, rew, done, extras = e.post_physics_step()
+        if not e.device_paths:
+            ids = done.nonzero(as_tuple=False).flatten()
+            if ids.numel():
+                self.sim.push_resets(ids)
+        else:
+            self.sim.push_resets(None)                                 # the rows are in root_states / dof_state; which ones: reset_buf
+        return obs, rew, done, extras
+
+    def reset_idx(self, env_ids):
+        e = self.engine
+        if e.device_paths:
+            e.reset_buf.zero_()
+            e.reset_buf[env_ids] = 1
+            e._device_paths(_abi.DEFINES["LT_VEL_PATH_RESET"])
+        else:
+            e.reset_idx(env_ids)
+
+    def reset(self):
+        """velocity_tracking/__init__.py:56-59: reset every env, then one step with zero actions; history cleared (history_wrapper.py:36-40)."""
+        self.reset_idx(torch.arange(self.num_envs, device=self.device))
+        self.step(torch.zeros(self.num_envs, self.num_actions, device=self.device))
+        self.engine.obs_history.zero_()
+        return self._obs_dict()
+
+
+class VelReplaySim:
+    """SimBackend of synthetic 'PhysX output' for the velocity env: a few seeded frames kept in HBM and cycled (env.ReplaySim's
+    counterpart for the single-actor tensors of cfg 4)."""
+
+    def __init__(self, seed=1000, n_frames=3):
+        self.seed, self.n_frames, self.k = seed, n_frames, 0
+
+    def attach(self, env):
+        from . import synthetic
+        self.env = env
+        e = env.engine
+        synth = synthetic.SyntheticState(e.N, e.env_origins.cpu().numpy(), num_bodies=int(e.cfg["num_bodies"]), seed=self.seed,
+                                         feet_indices=list(e.cfg["feet_indices"]))
+        dev = e.device
+        self.frames = []
+        for k in range(self.n_frames):
+            root = synth.root(k)
+            self.frames.append({"dof": [synth.dof_state(k, s).to(dev) for s in range(int(e.cfg["decimation"]))], "root": root.to(dev),
+                                "contact": synth.contact(k).to(dev), "rigid": synth.rigid(k, root).to(dev)})
+        e.episode_length_buf.copy_(synth.initial_episode_length(e.cfg["max_episode_length"]).to(dev))
+
+    def simulate(self, substep):
+        self.env.dof_state.copy_(self.frames[self.k % self.n_frames]["dof"][substep].view(self.env.dof_state.shape))
+
+    def refresh(self):
+        f = self.frames[self.k % self.n_frames]
+        self.env.root_states.copy_(f["root"])
+        self.env.contact_forces.copy_(f["contact"])
+        self.env.rigid_body_state.copy_(f["rigid"].view(self.env.rigid_body_state.shape))
+        self.k += 1
+
+    def push_resets(self, env_ids):
+        pass
