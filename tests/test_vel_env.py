@@ -541,3 +541,59 @@ def test_device_mode_graph_replay_equals_eager_steps():
         assert torch.equal(getattr(eager, name), getattr(graphed, name)), name
     assert torch.equal(eager.tq.state["lag_buffer"], graphed.tq.state["lag_buffer"]) and torch.equal(eager.tq.counters, graphed.tq.counters)
     assert int(eager.reset_buf.sum()) > 0
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# facade and configuration mapping
+def test_config_from_the_reference_cfg_tree_equals_the_recorded_table():
+    """vel_env.config_from_cfg on the reference's own Cfg class, edited by the config block of scripts/train_velocity_tracking.py
+    (executed from the reference file), gives the table recorded off the live reference env."""
+    from oracle import ref_harness
+    if not ref_harness.reference_available():
+        pytest.skip("reference tree not present on this machine")
+    from legged_tracking_b200 import vel_env
+    from oracle import gen_golden_vel
+    ref_harness.install()
+    Cfg = gen_golden_vel.build_cfg(64)
+    got, want = vel_env.config_from_cfg(Cfg), vel_env.cfg4_config()
+    assert set(got) == set(want), sorted(set(got) ^ set(want))
+    for k, w in want.items():
+        g_ = got[k]
+        if isinstance(w, (list, float)) and not (isinstance(w, list) and w and isinstance(w[0], str)):
+            np.testing.assert_allclose(np.asarray(g_, np.float64), np.asarray(w, np.float64), rtol=1e-7, atol=1e-9, err_msg=k)
+        else:
+            assert g_ == w, k
+
+
+@pytest.mark.gpu
+def test_facade_steps_like_the_engine_and_keeps_the_vecenv_surface():
+    """VelocityTrackingEasyEnv(sim_device, headless, cfg=None, sim=VelReplaySim()): reset() + steps through the SimBackend protocol
+    give what the engine gives when it is handed the same frames directly; the VecEnv attributes the runner reads exist."""
+    from legged_tracking_b200 import vel_env, workload
+    N = 1024
+    env = vel_env.VelocityTrackingEasyEnv("cuda:0", True, num_envs=N, sim=vel_env.VelReplaySim(seed=44), seed=5)
+    obs = env.reset()
+    assert obs["obs"].shape == (N, 70) and obs["obs_history"].shape == (N, 2100) and obs["privileged_obs"].shape == (N, 2)
+    assert env.num_obs == 70 and env.num_obs_history == 2100 and env.num_privileged_obs == 2 and env.num_actions == 12
+    assert float(obs["obs_history"].abs().sum()) == 0.0
+    ref = vel_env.VelocityStepEngine(vel_env.cfg4_config(), N, env.engine.env_origins.cpu().numpy(), workload.load_actuator(), "device",
+                                     device=torch.device("cuda", 0), seed=5)
+    sim = vel_env.VelReplaySim(seed=44)
+    sim.attach(type("E", (), {"engine": ref, "dof_state": ref.dof_state, "root_states": ref.root_states, "contact_forces": ref.contact_forces,
+                              "rigid_body_state": ref.rigid_body_state})())
+    ref.reset_buf.fill_(1)
+    ref._device_paths(1)
+    zero = torch.zeros(N, 12, device="cuda")
+    f0 = sim.frames[0]
+    ref.step(zero, {"dof_state": f0["dof"], "root": f0["root"], "contact": f0["contact"], "rigid": f0["rigid"]})
+    ref.obs_history.zero_()
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    for k in range(1, 5):
+        a = torch.randn(N, 12, device="cuda", generator=gen) * 0.3
+        o, r, d, info = env.step(a)
+        f = sim.frames[k % 3]
+        o2, r2, d2, _ = ref.step(a, {"dof_state": f["dof"], "root": f["root"], "contact": f["contact"], "rigid": f["rigid"]})
+        torch.cuda.synchronize()
+        assert torch.equal(o["obs"], o2["obs"]) and torch.equal(o["obs_history"], o2["obs_history"]) and torch.equal(r, r2) and torch.equal(d, d2)
+        assert "time_outs" in info and info["privileged_obs"].shape == (N, 2)
+    assert env.rew_buf.shape == (N,) and env.episode_length_buf.dtype == torch.int64 and env.commands.shape == (N, 15)
