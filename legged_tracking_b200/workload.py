@@ -21,6 +21,26 @@ CONFIGS = {
 }
 
 
+def make_cfg4(num_envs=4096, device="cuda:0", seed=1000, command_source="device", heightfield=True):
+    """BASELINE.json configs[3]: the velocity-tracking env (vel_env.VelocityTrackingEasyEnv) on a synthetic simulator backend and,
+    for the 17 x 11 height grid the config names, a synthetic int16 heightfield under the env grid.  -> the env (call reset())."""
+    from . import vel_env
+    n = int(num_envs)
+    side = int(np.floor(np.sqrt(n)))
+    rows = int(np.ceil(n / side))
+    xx, yy = np.meshgrid(np.arange(rows), np.arange(side), indexing="ij")
+    origins = np.zeros((n, 3), np.float32)
+    origins[:, 0], origins[:, 1] = 3.0 * xx.flatten()[:n], 3.0 * yy.flatten()[:n]
+    field = None
+    if heightfield:
+        rs = np.random.RandomState(5)
+        field = dict(height_samples=rs.randint(-10, 10, size=(int(3.0 * rows / 0.1) + 64, int(3.0 * side / 0.1) + 64)).astype(np.int16),
+                     border_size=2.0, horizontal_scale=0.1, vertical_scale=0.005, measured_points_x=vel_env.CFG4_MEASURED_POINTS_X,
+                     measured_points_y=vel_env.CFG4_MEASURED_POINTS_Y)
+    return vel_env.VelocityTrackingEasyEnv(device, True, num_envs=n, sim=vel_env.VelReplaySim(seed=seed), command_source=command_source,
+                                           env_origins=origins, heightfield=field, seed=seed)
+
+
 def load_actuator():
     """Weights of the reference's actuator network (resources/actuator_nets/unitree_go1.pt, LR:1307-1309) as plain arrays:
     w0 [32,6] b0 [32] w1 [32,32] b1 [32] w2 [1,32] b2 [1] (extracted by oracle/gen_golden.actuator_from_reference)."""
