@@ -597,3 +597,21 @@ def test_facade_steps_like_the_engine_and_keeps_the_vecenv_surface():
         assert torch.equal(o["obs"], o2["obs"]) and torch.equal(o["obs_history"], o2["obs_history"]) and torch.equal(r, r2) and torch.equal(d, d2)
         assert "time_outs" in info and info["privileged_obs"].shape == (N, 2)
     assert env.rew_buf.shape == (N,) and env.episode_length_buf.dtype == torch.int64 and env.commands.shape == (N, 15)
+
+
+@pytest.mark.gpu
+def test_config_4_trains_end_to_end_with_the_ppo_kernels():
+    """workload.make_cfg4 + ppo.Runner: two learning iterations (24-step rollouts of the cfg 4 env in device mode, GAE, the PPO
+    update on the 2,100-wide history) run, stay finite and move the parameters -- the reference's train_velocity_tracking.py loop
+    (Runner(HistoryWrapper(env)).learn) on the hand-written path end to end."""
+    from legged_tracking_b200 import ppo, workload
+    torch.manual_seed(0)
+    env = workload.make_cfg4(num_envs=1024)
+    runner = ppo.Runner(env, device="cuda:0")
+    before = runner.alg.actor_critic.flat.clone()
+    runner.learn(num_learning_iterations=2, init_at_random_ep_len=True)
+    torch.cuda.synchronize()
+    after = runner.alg.actor_critic.flat
+    assert torch.isfinite(after).all() and float((after - before).abs().max()) > 0
+    assert runner.alg.actor_critic.num_obs_history == 2100
+    assert torch.isfinite(env.obs_buf).all() and torch.isfinite(env.rew_buf).all()
