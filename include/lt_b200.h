@@ -501,7 +501,7 @@ int lt_vel_pre(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, void* stream);
 #define LT_VEL_PATH_CALLBACK 0
 #define LT_VEL_PATH_RESET 1
 #define LT_VEL_SLOTS 52              /* uniform slots per env and path: 0 category, 1 bin, 2..16 cell, 17 gait, 18 strength, 19..30 offsets,
-                                        31..42 dof positions, 43 yaw, 44..49 root velocity */
+                                        31..42 dof positions, 43 yaw, 44..49 root velocity, 50 / 51 x / y init offset */
 #define LT_VEL_MAX_DIMS 16
 typedef struct lt_vel_dev_cfg {
     int32_t n_bins, n_dims, n_keys;                  /* curriculum bins per category, command dims of the grid (15), task-reward keys (<= 4) */
@@ -510,6 +510,8 @@ typedef struct lt_vel_dev_cfg {
     float ep_len;                                    /* min(max_episode_length, int(resampling_time / dt)) (LRV:732-733) */
     double local_range[LT_VEL_MAX_DIMS];             /* LRV:755-757 */
     int32_t randomize_motor_strength, randomize_motor_offset, lag_slots;
+    int32_t custom_origins;                          /* heightfield / trimesh terrains: x / y init offsets drawn at reset (LRV:991-1001, slots 50, 51) */
+    float x_init_range, y_init_range, x_init_offset, y_init_offset;
     float motor_strength_lo, motor_strength_span, motor_offset_lo, motor_offset_span, yaw_init_range;   /* span = (float)(high - low), the
                                                         difference taken in double as python does before it meets the float32 tensor */
     float base_init_state[13];

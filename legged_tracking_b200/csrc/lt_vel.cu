@@ -374,6 +374,12 @@ __device__ void lt_vel_paths_env(const lt_vel_dev_params& a, int i, bool reset, 
     float* root = q.root_states_rw + (size_t)i * 13;                                 // _reset_root_states (LRV:1003-1015)
     for (int k = 0; k < 13; ++k) root[k] = d.base_init_state[k];
     for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], q.env_origins[(size_t)i * 3 + k]);
+    if (d.custom_origins) {                                                          // LRV:991-1001
+        root[0] = LT_FADD(root[0], LT_FADD(LT_FMUL(LT_FSUB(d.x_init_range, -d.x_init_range), U.get(50)), -d.x_init_range));
+        root[1] = LT_FADD(root[1], LT_FADD(LT_FMUL(LT_FSUB(d.y_init_range, -d.y_init_range), U.get(51)), -d.y_init_range));
+        root[0] = LT_FADD(root[0], d.x_init_offset);
+        root[1] = LT_FADD(root[1], d.y_init_offset);
+    }
     const float yaw = LT_FADD(LT_FMUL(LT_FSUB(d.yaw_init_range, -d.yaw_init_range), U.get(43)), -d.yaw_init_range);
     const float half = LT_FDIV(yaw, 2.0f);
     root[3] = 0.0f; root[4] = 0.0f; root[5] = sinf(half); root[6] = cosf(half);      // quat_from_angle_axis(yaw, z)

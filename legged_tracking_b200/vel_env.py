@@ -115,8 +115,8 @@ class VelocityStepEngine:
         self.lib = _abi.load()
         self.cfg, self.N = dict(cfg), int(num_envs)
         c, N, dev = self.cfg, self.N, self.device
-        if c["control_type"] != "actuator_net" or c["custom_origins"] or not c["randomize_lag_timesteps"]:
-            raise NotImplementedError("cfg 4 as scripts/train_velocity_tracking.py sets it: actuator_net, lag randomisation, flat origins")
+        if c["control_type"] != "actuator_net" or not c["randomize_lag_timesteps"]:
+            raise NotImplementedError("cfg 4 as scripts/train_velocity_tracking.py sets it: actuator_net with lag randomisation")
         self.source = command_source
         self.device_paths = isinstance(command_source, str) and command_source == "device"
         self.rng = rng or (lambda *shape: torch.rand(*shape, device=dev))
@@ -278,6 +278,9 @@ class VelocityStepEngine:
         d.motor_strength_lo, d.motor_strength_span = c["motor_strength_range"][0], c["motor_strength_range"][1] - c["motor_strength_range"][0]
         d.motor_offset_lo, d.motor_offset_span = c["motor_offset_range"][0], c["motor_offset_range"][1] - c["motor_offset_range"][0]
         d.yaw_init_range = float(c["yaw_init_range"])
+        d.custom_origins = int(bool(c["custom_origins"]))
+        d.x_init_range, d.y_init_range = float(c["x_init_range"]), float(c["y_init_range"])
+        d.x_init_offset, d.y_init_offset = float(c["x_init_offset"]), float(c["y_init_offset"])
         for i, v in enumerate(np.asarray(c["base_init_state"], np.float32).reshape(-1)):
             d.base_init_state[i] = float(v)
         d.lag_slots = int(self.tq.state["lag_buffer"].shape[0])
@@ -508,9 +511,15 @@ class VelocityStepEngine:
         # _reset_dofs (LRV:966-981)
         self.dof_state[env_ids, :, 0] = self.default_dof_pos.unsqueeze(0) * (self.rng(K, 12) * (1.5 - 0.5) + 0.5)
         self.dof_state[env_ids, :, 1] = 0.0
-        # _reset_root_states (LRV:983-1019), flat origins
+        # _reset_root_states (LRV:983-1019)
         self.root_states[env_ids] = self.base_init_state
         self.root_states[env_ids, :3] += self.env_origins[env_ids]
+        if c["custom_origins"]:                                                              # heightfield / trimesh terrains (LRV:991-1001)
+            xr, yr = float(c["x_init_range"]), float(c["y_init_range"])
+            self.root_states[env_ids, 0:1] += self.rng(K, 1) * (xr - (-xr)) + (-xr)
+            self.root_states[env_ids, 1:2] += self.rng(K, 1) * (yr - (-yr)) + (-yr)
+            self.root_states[env_ids, 0] += float(c["x_init_offset"])
+            self.root_states[env_ids, 1] += float(c["y_init_offset"])
         yaw_rng = float(c["yaw_init_range"])
         yaw = self.rng(K, 1) * (yaw_rng - (-yaw_rng)) + (-yaw_rng)
         half = yaw / 2

@@ -413,14 +413,18 @@ def test_device_sampler_draws_bins_by_weight_and_points_inside_the_bin():
 
 
 @pytest.mark.gpu
-def test_device_reset_path_equals_the_host_orchestrated_one():
+@pytest.mark.parametrize("custom_origins", [False, True])
+def test_device_reset_path_equals_the_host_orchestrated_one(custom_origins):
     """The reset path as a kernel against the torch path that free-runs the reference recording (same uniforms, injected per env):
     DR tables, dof and root rows, buffers, lag ring, episode bookkeeping; and the callback's interval DR."""
     from legged_tracking_b200 import _abi, vel_env, workload
     g = load()
     N = 1000
-    dev_eng, c = _device_engine(g, N)
-    host_eng = vel_env.VelocityStepEngine(c, N, dev_eng.env_origins.cpu().numpy(), workload.load_actuator(), ReplaySource(), device=torch.device("cuda", 0))
+    c = dict(cfg_of(g), custom_origins=custom_origins)          # True: heightfield / trimesh terrains, x / y init offsets drawn (LRV:991-1001)
+    origins = np.zeros((N, 3), np.float32)
+    origins[:, 0], origins[:, 1] = np.arange(N) % 97, np.arange(N) // 97
+    dev_eng = vel_env.VelocityStepEngine(c, N, origins, workload.load_actuator(), "device", device=torch.device("cuda", 0), seed=3)
+    host_eng = vel_env.VelocityStepEngine(c, N, origins, workload.load_actuator(), ReplaySource(), device=torch.device("cuda", 0))
     gen = torch.Generator().manual_seed(9)
     U = torch.rand(N, _abi.DEFINES["LT_VEL_SLOTS"], generator=gen)
     reset = torch.rand(N, generator=gen) < 0.3
@@ -437,7 +441,8 @@ def test_device_reset_path_equals_the_host_orchestrated_one():
         e.resample_due.zero_()
     want_means = {"rew_" + n: float(host_eng.episode_sums[i][ids.cuda()].mean()) for i, n in enumerate(host_eng.reward_names + ["total"])}
     # host path: reset_idx draws, in the reference's order -- category, motor strength, motor offsets, dof positions, yaw, root velocity
-    draws = [U[ids, 0], U[ids, 18], U[ids, 19:31], U[ids, 31:43], U[ids, 43:44], U[ids, 44:50]]
+    draws = [U[ids, 0], U[ids, 18], U[ids, 19:31], U[ids, 31:43]] + ([U[ids, 50:51], U[ids, 51:52]] if custom_origins else []) + \
+        [U[ids, 43:44], U[ids, 44:50]]
     host_eng.rng = ReplayRng([d.numpy() for d in draws], torch.device("cuda", 0))
     host_eng.source.q = [(np.zeros((int((host_eng.resampler.categories_from_uniform(U[ids, 0].cuda()) == k).sum()), 15)), np.zeros(0, np.int64))
                          for k in range(4) if int((host_eng.resampler.categories_from_uniform(U[ids, 0].cuda()) == k).sum())]
