@@ -414,7 +414,7 @@ class VelocityStepEngine:
         # ---- reset_idx (LRV:169-265)
         if self.device_paths:
             self._device_paths(_abi.DEFINES["LT_VEL_PATH_RESET"], uniform_rows[1] if uniform_rows is not None else None)
-            self.extras["time_outs"] = self.time_out_buf
+            self.extras["time_outs"] = self.time_out_buf.view(torch.bool)
         elif host_paths:
             self.reset_idx(self.reset_buf.nonzero(as_tuple=False).flatten())
         # ---- compute_observations + last_* shifts + obs clip + history (LRV:320-470, 143-148, 102-105; history_wrapper.py:23)
