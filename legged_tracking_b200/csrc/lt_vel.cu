@@ -161,9 +161,25 @@ __global__ void __launch_bounds__(256) lt_vel_observe_kernel(const __grid_consta
     const int row = H * no, old = (H - 1) * no;
     const float* in = p.obs_history_in + (size_t)i * row;
     float* out = p.obs_history_out + (size_t)i * row;
-    for (int w = threadIdx.x * VEC; w < old; w += blockDim.x * VEC) {
-        if (VEC == 2) *reinterpret_cast<float2*>(out + w) = __ldcs(reinterpret_cast<const float2*>(in + w + no));
-        else out[w] = in[w + no];
+    if (VEC == 2) {                                                                   // four independent 8-byte loads in flight per thread
+        const float2* in2 = reinterpret_cast<const float2*>(in + no);
+        float2* out2 = reinterpret_cast<float2*>(out);
+        const int n2 = old >> 1;
+        for (int base = 0; base < n2; base += 4 * (int)blockDim.x) {
+            float2 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = base + u * (int)blockDim.x + (int)threadIdx.x;
+                if (j < n2) v[u] = __ldcs(in2 + j);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = base + u * (int)blockDim.x + (int)threadIdx.x;
+                if (j < n2) __stcs(out2 + j, v[u]);
+            }
+        }
+    } else {
+        for (int w = threadIdx.x; w < old; w += blockDim.x) out[w] = in[w + no];
     }
     for (int col = threadIdx.x * VEC; col < no; col += blockDim.x * VEC) {
         float v[VEC];
