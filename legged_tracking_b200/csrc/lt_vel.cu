@@ -283,21 +283,6 @@ struct lt_vel_dev_params {
     int32_t which;
 };
 
-struct lt_vel_rng {                    // per-env uniform slots: injected row or Philox keyed (seed, step | path, env, slot / 4)
-    const float* row;
-    uint32_t seed_lo, seed_hi, step, env;
-    uint32_t blk = 0xffffffffu, o[4] = {0u, 0u, 0u, 0u};
-    __device__ float get(int slot) {
-        if (row) return row[slot];
-        const uint32_t b = (uint32_t)(slot >> 2);
-        if (b != blk) {
-            lt_philox(env, b, step, 0x52455345u, seed_lo, seed_hi, o);
-            blk = b;
-        }
-        return lt_u01(o[slot & 3]);
-    }
-};
-
 __device__ __forceinline__ bool lt_vel_mask_resample(const lt_vel_dev_params& a, int i) {
     return (a.which == LT_VEL_PATH_RESET ? a.p.reset_buf[i] : a.p.resample_due[i]) != 0;
 }
@@ -334,107 +319,145 @@ __global__ void lt_cur_apply_kernel(double* w, int32_t* hit_self, int32_t* hit_a
     hit_adj[j] = 0;
 }
 
-__device__ void lt_vel_paths_env(const lt_vel_dev_params& a, int i, bool reset, bool resample, bool dr) {
-    const lt_vel_cfg& c = a.c;
-    const lt_vel_dev_cfg& d = a.d;
-    const lt_vel_dev_ptrs& q = a.q;
-    const size_t N = (size_t)c.num_envs;
-    lt_vel_rng U;
-    U.row = a.uniform_rows ? a.uniform_rows + (size_t)i * LT_VEL_SLOTS : nullptr;
-    U.seed_lo = c.seed_lo; U.seed_hi = c.seed_hi; U.env = (uint32_t)i;
-    U.step = ((a.p.step_counter ? *a.p.step_counter : a.step) << 1) | (uint32_t)a.which;
-    if (resample) {                                                                  // LRV:759-840
-        const int n_cat = d.cmd.n_categories, nb = d.n_bins, nc = c.num_commands;
-        const float u = U.get(0);
-        const double pc = 1.0 / (double)n_cat;
-        int cat = n_cat - 1;
-        for (int k = 0; k < n_cat; ++k)
-            if ((float)(pc * k) <= u && u < (float)(pc * (k + 1))) { cat = k; break; }
-        const double* w = q.weights + (size_t)cat * nb;
-        double total = 0.0;
-        for (int g = 0; g < nb; ++g) total += w[g];
-        const double target = (double)U.get(1) * total;                              // Curriculum.sample_bins: choice(p = w / sum)
-        int bin = 0;
-        double acc = 0.0;
-        for (int g = 0; g < nb; ++g) {
-            if (w[g] <= 0.0) continue;
-            bin = g;
-            acc += w[g];
-            if (target < acc) break;
-        }
-        float* cmd = q.commands + (size_t)i * nc;
-        for (int k = 0; k < nc && k < d.n_dims; ++k) {                               // sample_uniform_from_cell: uniform(c + s / 2, c - s / 2)
-            const double ctr = q.grid[(size_t)k * nb + bin], lo = ctr + q.bin_sizes[k] / 2, hi = ctr - q.bin_sizes[k] / 2;
-            cmd[k] = (float)(lo + (hi - lo) * (double)U.get(2 + k));
-        }
-        lt_cmd_rewrite(d.cmd, cmd, cat, U.get(17));
-        q.env_bins[i] = bin;
-        q.env_categories[i] = cat;
-        const int n_rows = c.n_terms + 5;
-        for (int r = 0; r < n_rows; ++r) a.p.command_sums[(size_t)r * N + i] = 0.0f;
-    }
-    if (dr) {                                                                        // LRV:663-673
-        if (d.randomize_motor_strength) {
-            const float v = LT_FADD(LT_FMUL(U.get(18), d.motor_strength_span), d.motor_strength_lo);
-            for (int k = 0; k < 12; ++k) q.motor_strengths[(size_t)i * 12 + k] = v;
-        }
-        if (d.randomize_motor_offset)
-            for (int k = 0; k < 12; ++k)
-                q.motor_offsets[(size_t)i * 12 + k] = LT_FADD(LT_FMUL(U.get(19 + k), d.motor_offset_span), d.motor_offset_lo);
-    }
-    if (!reset) return;
-    for (int k = 0; k < 12; ++k) {                                                   // _reset_dofs (LRV:966-976)
-        q.dof_state_rw[((size_t)i * 12 + k) * 2] = LT_FMUL(a.p.default_dof_pos[k], LT_FADD(LT_FMUL(1.0f, U.get(31 + k)), 0.5f));
-        q.dof_state_rw[((size_t)i * 12 + k) * 2 + 1] = 0.0f;
-    }
-    float* root = q.root_states_rw + (size_t)i * 13;                                 // _reset_root_states (LRV:1003-1015)
-    for (int k = 0; k < 13; ++k) root[k] = d.base_init_state[k];
-    for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], q.env_origins[(size_t)i * 3 + k]);
-    if (d.custom_origins) {                                                          // LRV:991-1001
-        root[0] = LT_FADD(root[0], LT_FADD(LT_FMUL(LT_FSUB(d.x_init_range, -d.x_init_range), U.get(50)), -d.x_init_range));
-        root[1] = LT_FADD(root[1], LT_FADD(LT_FMUL(LT_FSUB(d.y_init_range, -d.y_init_range), U.get(51)), -d.y_init_range));
-        root[0] = LT_FADD(root[0], d.x_init_offset);
-        root[1] = LT_FADD(root[1], d.y_init_offset);
-    }
-    const float yaw = LT_FADD(LT_FMUL(LT_FSUB(d.yaw_init_range, -d.yaw_init_range), U.get(43)), -d.yaw_init_range);
-    const float half = LT_FDIV(yaw, 2.0f);
-    root[3] = 0.0f; root[4] = 0.0f; root[5] = sinf(half); root[6] = cosf(half);      // quat_from_angle_axis(yaw, z)
-    for (int k = 0; k < 6; ++k) root[7 + k] = LT_FADD(LT_FMUL(1.0f, U.get(44 + k)), -0.5f);
-    for (int k = 0; k < 12; ++k) {                                                   // LRV:192-198
-        a.p.last_actions[(size_t)i * 12 + k] = 0.0f;
-        a.p.last_last_actions[(size_t)i * 12 + k] = 0.0f;
-        a.p.last_dof_vel[(size_t)i * 12 + k] = 0.0f;
-    }
-    for (int k = 0; k < 4; ++k) q.feet_air_time[(size_t)i * 4 + k] = 0.0f;
-    a.p.episode_length_buf[i] = 0;
-    q.gait_indices[i] = 0.0f;                                                        // LRV:258
-    for (int s = 0; s < d.lag_slots; ++s)
-        for (int k = 0; k < 12; ++k) q.lag_buffer[((size_t)s * N + i) * 12 + k] = 0.0f;      // LRV:260-261
+// Philox uniform of (env, slot) for the indexed paths, or the injected row
+__device__ __forceinline__ float lt_vel_u(const lt_vel_dev_params& a, int i, int slot) {
+    if (a.uniform_rows) return a.uniform_rows[(size_t)i * LT_VEL_SLOTS + slot];
+    uint32_t o[4];
+    const uint32_t step = ((a.p.step_counter ? *a.p.step_counter : a.step) << 1) | (uint32_t)a.which;
+    lt_philox((uint32_t)i, (uint32_t)(slot >> 2), step, 0x52455345u, a.c.seed_lo, a.c.seed_hi, o);
+    return lt_u01(o[slot & 3]);
 }
 
-// thread per env over the masks; the finished episodes' sums (LRV:200-205) are reduced per warp before they reach the accumulators
-__global__ void __launch_bounds__(128) lt_vel_paths_kernel(const __grid_constant__ lt_vel_dev_params a) {
+// Pass 1, thread per env: which envs have indexed work this call, compacted (unordered) into work_env / work_code.
+//   code bit 0 resample, bit 1 interval / reset DR, bit 2 reset
+__global__ void __launch_bounds__(256) lt_vel_mark_kernel(const __grid_constant__ lt_vel_dev_params a) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const lt_vel_cfg& c = a.c;
-    const bool in = i < c.num_envs;
+    const bool in = i < a.c.num_envs;
     const bool reset = in && a.which == LT_VEL_PATH_RESET && a.p.reset_buf[i];
     const bool resample = in && lt_vel_mask_resample(a, i);
     const bool dr = in && (a.which == LT_VEL_PATH_RESET ? reset : (a.p.dr_due[i] != 0));
-    if (resample || dr) lt_vel_paths_env(a, i, reset, resample, dr);
-    const unsigned m = __ballot_sync(0xffffffffu, reset);
+    const int code = (resample ? 1 : 0) | (dr ? 2 : 0) | (reset ? 4 : 0);
+    const unsigned m = __ballot_sync(0xffffffffu, code != 0);
     if (m == 0u) return;
-    const size_t N = (size_t)c.num_envs;
     const int lane = threadIdx.x & 31;
-    for (int r = 0; r <= c.n_terms; ++r) {
-        float v = 0.0f;
-        if (reset) {
-            v = a.p.episode_sums[(size_t)r * N + i];
-            a.p.episode_sums[(size_t)r * N + i] = 0.0f;
-        }
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) atomicAdd(a.q.episode_acc + r, v);
+    int base = 0;
+    if (lane == 0) base = atomicAdd(a.q.work_count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (code) {
+        const int slot = base + __popc(m & ((1u << lane) - 1u));
+        a.q.work_env[slot] = i;
+        a.q.work_code[slot] = code;
     }
-    if (lane == 0) atomicAdd(a.q.episode_acc + c.n_terms + 1, (float)__popc(m));
+}
+
+// Pass 2, warp per listed env: the lanes share the env's work -- the weighted bin draw scans the category's weights 32 at a time,
+// the command columns, motor tables, dof rows, lag ring and sum rows are written one element per lane.
+__global__ void __launch_bounds__(256) lt_vel_paths_kernel(const __grid_constant__ lt_vel_dev_params a) {
+    __shared__ float s_acc[LT_CORL_MAX_TERMS + 2];
+    const lt_vel_cfg& c = a.c;
+    const lt_vel_dev_cfg& d = a.d;
+    const lt_vel_dev_ptrs& q = a.q;
+    const int count = *q.work_count;
+    const int warps = blockDim.x >> 5;
+    if ((int)blockIdx.x * warps >= count) return;                                    // block-uniform
+    const int lane = threadIdx.x & 31, wi = blockIdx.x * warps + (threadIdx.x >> 5);
+    const size_t N = (size_t)c.num_envs;
+    if (threadIdx.x < LT_CORL_MAX_TERMS + 2) s_acc[threadIdx.x] = 0.0f;
+    __syncthreads();
+    if (wi < count) {
+        const int i = q.work_env[wi], code = q.work_code[wi];
+        if (code & 1) {                                                              // _resample_commands (LRV:759-840)
+            const int n_cat = d.cmd.n_categories, nb = d.n_bins, nc = c.num_commands;
+            const float u = lt_vel_u(a, i, 0);
+            const double pc = 1.0 / (double)n_cat;
+            int cat = n_cat - 1;
+            for (int k = 0; k < n_cat; ++k)
+                if ((float)(pc * k) <= u && u < (float)(pc * (k + 1))) { cat = k; break; }
+            const double* w = q.weights + (size_t)cat * nb;
+            // Curriculum.sample_bins: choice(p = w / sum).  Lane l owns the bins [l * per, (l + 1) * per)
+            const int per = (nb + 31) / 32, g0 = lane * per, g1 = min(nb, g0 + per);
+            double local = 0.0;
+            for (int g = g0; g < g1; ++g) local += fmax(w[g], 0.0);
+            double incl = local;
+            for (int o = 1; o < 32; o <<= 1) {
+                const double t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const double total = __shfl_sync(0xffffffffu, incl, 31);
+            const double target = (double)lt_vel_u(a, i, 1) * total;
+            int bin = -1;
+            if (target < incl && local > 0.0) {                                       // the draw may fall into this lane's bins
+                double acc = incl - local;
+                for (int g = g0; g < g1; ++g) {
+                    if (w[g] <= 0.0) continue;
+                    acc += w[g];
+                    if (target < acc) { bin = g; break; }
+                }
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, bin >= 0);
+            if (hit) bin = __shfl_sync(0xffffffffu, bin, __ffs(hit) - 1);             // first lane in bin order
+            else {                                                                    // rounding at the very end: the last positive bin
+                int last = -1;
+                for (int g = g0; g < g1; ++g) if (w[g] > 0.0) last = g;
+                const unsigned has = __ballot_sync(0xffffffffu, last >= 0);
+                bin = has ? __shfl_sync(0xffffffffu, last, 31 - __clz(has)) : 0;
+            }
+            float* cmd = q.commands + (size_t)i * nc;
+            if (lane < nc && lane < d.n_dims) {                                       // sample_uniform_from_cell: uniform(c + s / 2, c - s / 2)
+                const double ctr = q.grid[(size_t)lane * nb + bin], lo = ctr + q.bin_sizes[lane] / 2, hi = ctr - q.bin_sizes[lane] / 2;
+                cmd[lane] = (float)(lo + (hi - lo) * (double)lt_vel_u(a, i, 2 + lane));
+            }
+            __syncwarp();
+            if (lane == 0) {
+                lt_cmd_rewrite(d.cmd, cmd, cat, lt_vel_u(a, i, 17));
+                q.env_bins[i] = bin;
+                q.env_categories[i] = cat;
+            }
+            for (int r = lane; r < c.n_terms + 5; r += 32) a.p.command_sums[(size_t)r * N + i] = 0.0f;
+        }
+        if (code & 2) {                                                              // _randomize_dof_props (LRV:663-673)
+            if (d.randomize_motor_strength && lane < 12)
+                q.motor_strengths[(size_t)i * 12 + lane] = LT_FADD(LT_FMUL(lt_vel_u(a, i, 18), d.motor_strength_span), d.motor_strength_lo);
+            if (d.randomize_motor_offset && lane < 12)
+                q.motor_offsets[(size_t)i * 12 + lane] = LT_FADD(LT_FMUL(lt_vel_u(a, i, 19 + lane), d.motor_offset_span), d.motor_offset_lo);
+        }
+        if (code & 4) {
+            if (lane < 12) {                                                         // _reset_dofs (LRV:966-976) and the [N,12] buffers (:192-198)
+                q.dof_state_rw[((size_t)i * 12 + lane) * 2] = LT_FMUL(a.p.default_dof_pos[lane], LT_FADD(LT_FMUL(1.0f, lt_vel_u(a, i, 31 + lane)), 0.5f));
+                q.dof_state_rw[((size_t)i * 12 + lane) * 2 + 1] = 0.0f;
+                a.p.last_actions[(size_t)i * 12 + lane] = 0.0f;
+                a.p.last_last_actions[(size_t)i * 12 + lane] = 0.0f;
+                a.p.last_dof_vel[(size_t)i * 12 + lane] = 0.0f;
+            }
+            if (lane < 4) q.feet_air_time[(size_t)i * 4 + lane] = 0.0f;
+            if (lane == 0) {                                                         // _reset_root_states (LRV:983-1015)
+                float* root = q.root_states_rw + (size_t)i * 13;
+                for (int k = 0; k < 13; ++k) root[k] = d.base_init_state[k];
+                for (int k = 0; k < 3; ++k) root[k] = LT_FADD(root[k], q.env_origins[(size_t)i * 3 + k]);
+                if (d.custom_origins) {                                              // LRV:991-1001
+                    root[0] = LT_FADD(root[0], LT_FADD(LT_FMUL(LT_FSUB(d.x_init_range, -d.x_init_range), lt_vel_u(a, i, 50)), -d.x_init_range));
+                    root[1] = LT_FADD(root[1], LT_FADD(LT_FMUL(LT_FSUB(d.y_init_range, -d.y_init_range), lt_vel_u(a, i, 51)), -d.y_init_range));
+                    root[0] = LT_FADD(root[0], d.x_init_offset);
+                    root[1] = LT_FADD(root[1], d.y_init_offset);
+                }
+                const float yaw = LT_FADD(LT_FMUL(LT_FSUB(d.yaw_init_range, -d.yaw_init_range), lt_vel_u(a, i, 43)), -d.yaw_init_range);
+                const float half = LT_FDIV(yaw, 2.0f);
+                root[3] = 0.0f; root[4] = 0.0f; root[5] = sinf(half); root[6] = cosf(half);      // quat_from_angle_axis(yaw, z)
+                for (int k = 0; k < 6; ++k) root[7 + k] = LT_FADD(LT_FMUL(1.0f, lt_vel_u(a, i, 44 + k)), -0.5f);
+                a.p.episode_length_buf[i] = 0;
+                q.gait_indices[i] = 0.0f;                                            // LRV:258
+                atomicAdd(&s_acc[c.n_terms + 1], 1.0f);
+            }
+            for (int k = lane; k < d.lag_slots * 12; k += 32)                        // LRV:260-261
+                q.lag_buffer[((size_t)(k / 12) * N + i) * 12 + (k % 12)] = 0.0f;
+            for (int r = lane; r <= c.n_terms; r += 32) {                            // LRV:200-205
+                atomicAdd(&s_acc[r], a.p.episode_sums[(size_t)r * N + i]);
+                a.p.episode_sums[(size_t)r * N + i] = 0.0f;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x <= c.n_terms + 1 && s_acc[threadIdx.x] != 0.0f) atomicAdd(q.episode_acc + threadIdx.x, s_acc[threadIdx.x]);
 }
 
 static bool lt_vel_cfg_ok(const lt_vel_cfg* c) {
@@ -493,9 +516,11 @@ int lt_vel_indexed_paths(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const l
     lt_vel_dev_params a;
     a.c = *cfg; a.p = p; a.d = d; a.q = *dptrs; a.uniform_rows = uniform_rows; a.step = step; a.which = which;
     const int n = cfg->num_envs, nw = d.cmd.n_categories * d.n_bins;
+    if (cudaMemsetAsync(dptrs->work_count, 0, sizeof(int32_t), s) != cudaSuccess) return LT_ERR_CUDA;
     lt_cur_hits_kernel<<<(n + 127) / 128, 128, 0, s>>>(a);
     lt_cur_apply_kernel<<<(nw + 127) / 128, 128, 0, s>>>(dptrs->weights, dptrs->hit_self, dptrs->hit_adj, nw);
-    lt_vel_paths_kernel<<<(n + 127) / 128, 128, 0, s>>>(a);
+    lt_vel_mark_kernel<<<(n + 255) / 256, 256, 0, s>>>(a);
+    lt_vel_paths_kernel<<<(n + 7) / 8, 256, 0, s>>>(a);              // a warp per listed env; blocks past the list's end return at once
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }
 

@@ -263,6 +263,8 @@ class VelocityStepEngine:
         self.env_bins_dev = torch.zeros(N, dtype=torch.int32, device=dev)
         self.env_categories_dev = torch.zeros(N, dtype=torch.int32, device=dev)
         self.episode_acc = torch.zeros(len(self.reward_names) + 2, device=dev)
+        self._work = torch.zeros(2, N, dtype=torch.int32, device=dev)
+        self._work_count = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_counter_dev = torch.zeros(1, dtype=torch.int32, device=dev)       # Philox step key of the device mode (uint32 bits)
         d = _abi.lt_vel_dev_cfg()
         d.n_bins, d.n_dims = nb, grid.shape[0]
@@ -291,7 +293,8 @@ class VelocityStepEngine:
                          env_bins=self.env_bins_dev, env_categories=self.env_categories_dev, commands=self.commands, dof_state_rw=self.dof_state,
                          root_states_rw=self.root_states, env_origins=self.env_origins, motor_strengths=st["motor_strengths"],
                          motor_offsets=st["motor_offsets"], lag_buffer=st["lag_buffer"], gait_indices=self.gait.gait_indices,
-                         feet_air_time=self.feet_air_time, episode_acc=self.episode_acc).items():
+                         feet_air_time=self.feet_air_time, episode_acc=self.episode_acc, work_env=self._work[0], work_code=self._work[1],
+                         work_count=self._work_count).items():
             setattr(q, k, t.data_ptr())
         self._dq = q
 

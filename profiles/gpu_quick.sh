@@ -1,4 +1,8 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_vel_env.py -m gpu -q -x 2>&1 | tail -n 3
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_cfg4_launches.csv python profiles/run_cfg4.py 65536 4 > gpurun_out/ncu_cfg4.log 2>&1
-grep "lt_vel_observe" gpurun_out/r02_cfg4_launches.csv | tail -n 2
+timeout 300 python -m pytest tests/test_vel_env.py -m gpu -q -x 2>&1 | tail -n 2
+python - <<'PY'
+import json, bench
+for n in (4096, 65536):
+    r = bench.cfg4_step_timing("cuda:0", n, steps=40)
+    print(n, round(r["ms_per_step"],3), round(r["device_mode"]["ms_per_step"],3), round(r["device_mode"]["graph_replay"]["ms_per_step"],3), round(r["device_mode"]["graph_replay"]["value"]/1e6,1))
+PY
