@@ -196,7 +196,7 @@ def test_cfg4_step_chain_free_runs_the_reference_recording():
         close(cpu(done), g[t + "out/done"], f"{k} done")
         close(cpu(eng.episode_length_buf), st["episode_length_buf"], f"{k} episode_length_buf")
         close(cpu(eng.time_out_buf).astype(bool), st["time_out_buf"], f"{k} time_out_buf")
-        close(cpu(eng.tq.state["torques"]), g[t + "out/all_torques"][-1], f"{k} torques", atol=2e-5)
+        close(cpu(eng.tq.state["torques"]), g[t + "out/all_torques"][-1], f"{k} torques", atol=1e-5)
         for name in ("base_lin_vel", "base_ang_vel", "projected_gravity", "foot_positions", "foot_velocities", "prev_foot_velocities", "commands",
                      "rew_buf_pos", "rew_buf_neg", "last_actions", "last_last_actions", "last_dof_vel", "last_root_vel", "last_joint_pos_target",
                      "last_last_joint_pos_target", "root_states", "gravity_vec"):
