@@ -493,6 +493,23 @@ def cfg4_step_timing(dev, n_envs, steps=60):
                     "three nonzero() host reads per step as in the reference"}
 
 
+def cfg4_ppo_iteration(dev, n_envs=4096, iters=2):
+    """BASELINE.json configs[3] end to end: Runner.learn on the config-4 env in device mode (24-step rollout of the env + the policy on
+    the 30 x 70 history, GAE, 5 x 4 minibatch update), wall time per iteration after one warm-up iteration."""
+    from legged_tracking_b200 import ppo
+    env = workload.make_cfg4(num_envs=n_envs, device=dev)
+    runner = ppo.Runner(env, device=dev, save_dir=None)               # no checkpoint writes inside the timed iterations
+    runner.learn(num_learning_iterations=1, init_at_random_ep_len=True)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    runner.learn(num_learning_iterations=iters)
+    torch.cuda.synchronize()
+    dt_ms = (time.perf_counter() - t0) * 1e3 / iters
+    T = runner.num_steps_per_env
+    return {"envs": n_envs, "iter_ms": dt_ms, "env_steps_per_s": n_envs * T / (dt_ms * 1e-3), "num_steps_per_env": T,
+            "obs_history_width": int(env.num_obs_history), "finite": bool(torch.isfinite(runner.alg.actor_critic.flat).all())}
+
+
 def strong_block(args, rank, world, dev, dist, peak):
     """BASELINE.json configs[4] as the north-star words it: 65,536 envs IN TOTAL, sharded over the `world` GPUs (strong scaling),
     the full step, and the PPO iteration (T = 24 rollout + GAE + 5 x 4 minibatch update) with its NCCL exchanges timed apart.
@@ -801,7 +818,8 @@ def run_b200(args, rank, world, local_rank):
             line["api_step"] = {"error": str(e)[:300]}
     if world == 1:
         try:
-            line["cfg4_step"] = {"n4096": cfg4_step_timing(dev, 4096), "n65536": cfg4_step_timing(dev, 65536, steps=30)}
+            line["cfg4_step"] = {"n4096": cfg4_step_timing(dev, 4096), "n65536": cfg4_step_timing(dev, 65536, steps=30),
+                                 "ppo_iteration_n4096": cfg4_ppo_iteration(dev, 4096)}
         except Exception as e:                    # auxiliary number
             line["cfg4_step"] = {"error": str(e)[:300]}
     try:
