@@ -453,6 +453,7 @@ def cfg4_step_timing(dev, n_envs, steps=60):
     # device mode: curriculum, resampling, DR and reset as kernels over masks -- no host read in the step
     dev_eng = vel_env.VelocityStepEngine(cfg, n_envs, origins, workload.load_actuator(), "device", device=dev, seed=9, heightfield=field)
     dev_eng.episode_length_buf.copy_(synth.initial_episode_length(cfg["max_episode_length"]).to(dev))
+    dev_eng.bind_inputs = True                 # the replayed frames are read (and, on reset, rewritten) in place, as Isaac Gym's tensors are
     dev_eng.reset_all()
     for k in range(5):
         dev_eng.step(frames[k % 3]["actions"], frames[k % 3])

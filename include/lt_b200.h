@@ -371,6 +371,8 @@ typedef struct lt_corl_cfg {
     int32_t term_ids[LT_CORL_MAX_TERMS];              /* LT_CORL_*: row t of `out` is term term_ids[t] */
     int32_t feet_indices[4], penalised[LT_CORL_MAX_TERMS];
     float dt, tracking_sigma, tracking_sigma_yaw, base_height_target, gait_force_sigma, gait_vel_sigma, max_contact_force;   /* cfg.rewards */
+    int32_t dof_stride;                               /* element stride of dof_pos / dof_vel: 0 or 1 = [N,12] rows; 2 = the columns of Isaac
+                                                         Gym's interleaved dof_state [N,12,2] (dof_pos = dof_state, dof_vel = dof_state + 1) */
 } lt_corl_cfg;
 /* env attributes the container reads (CR; shapes per env): commands [num_commands], base_lin_vel / base_ang_vel /
  * projected_gravity / gravity_vec / base_pos [3], base_quat [4], the [12] dof / action / joint-target rows, contact_forces
@@ -436,6 +438,7 @@ typedef struct lt_vel_cfg {
     int32_t use_terminal_body_height;
     float terminal_body_height, max_episode_length;
     int32_t sample_interval, rand_interval;                   /* int(resampling_time / dt), int(domain_rand.rand_interval) */
+    int32_t decimation, lag_slots;                            /* for torque_counters (below) */
     int32_t n_terms;                                          /* rows of the lt_corl_rewards block, in reward_names order */
     int32_t command_sum_adds_scale[LT_CORL_MAX_TERMS];        /* 1 for tracking_contacts_shaped_force / _vel (LRV:296-297) */
     float term_scales[LT_CORL_MAX_TERMS];                     /* reward_scales[name] * dt (LRV:1243) */
@@ -470,6 +473,9 @@ typedef struct lt_vel_ptrs {
     float *obs_buf, *privileged_obs_buf;                      /* [N,num_obs] [N,num_privileged_obs] */
     const float* obs_history_in;                              /* [N, H * num_obs] */
     float* obs_history_out;                                   /* [N, H * num_obs], a different buffer: the host ping-pongs the two */
+    int32_t* torque_counters;                                 /* lt_counters() of the handle whose lt_compute_torques ran this step, or NULL:
+                                                                 lt_vel_pre advances them as lt_post_physics_step would ([0] += 1,
+                                                                 [1] += decimation, [2] = ([2] + decimation) % lag_slots: the lag ring's head) */
     uint32_t* step_counter;                                   /* device uint32[1] or NULL.  Non-NULL: lt_vel_indexed_paths and lt_vel_observe key
                                                                  their Philox draws with *step_counter instead of their `step` argument, and
                                                                  lt_vel_observe adds 1 to it when it is done -- so that a CUDA graph of the

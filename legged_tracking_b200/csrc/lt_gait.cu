@@ -99,6 +99,7 @@ __device__ __forceinline__ void lt_apply_yaw(const float q[4], const float v[3],
 
 __global__ void __launch_bounds__(128) lt_corl_kernel(const __grid_constant__ lt_corl_params a) {
     const lt_corl_cfg& c = a.c;
+    const size_t ds = c.dof_stride > 1 ? (size_t)c.dof_stride : 1;
     const lt_corl_ptrs& p = a.p;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int N = c.num_envs;
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(128) lt_corl_kernel(const __grid_constant__ lt
             for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(p.torques[(size_t)i * D + d]));
             break;
         case LT_CORL_DOF_ACC:
-            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(LT_FDIV(LT_FSUB(p.last_dof_vel[(size_t)i * D + d], p.dof_vel[(size_t)i * D + d]), c.dt)));
+            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(LT_FDIV(LT_FSUB(p.last_dof_vel[(size_t)i * D + d], p.dof_vel[((size_t)i * D + d) * ds]), c.dt)));
             break;
         case LT_CORL_ACTION_RATE:
             for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(LT_FSUB(p.last_actions[(size_t)i * D + d], p.actions[(size_t)i * D + d])));
@@ -149,7 +150,7 @@ __global__ void __launch_bounds__(128) lt_corl_kernel(const __grid_constant__ lt
             break;
         case LT_CORL_DOF_POS_LIMITS:                                                                      // CR:54-58
             for (int d = 0; d < D; ++d) {
-                const float q = p.dof_pos[(size_t)i * D + d];
+                const float q = p.dof_pos[((size_t)i * D + d) * ds];
                 const float lo = -fminf(LT_FSUB(q, p.dof_pos_limits[2 * d]), 0.0f);
                 v = LT_FADD(v, LT_FADD(lo, fmaxf(LT_FSUB(q, p.dof_pos_limits[2 * d + 1]), 0.0f)));
             }
@@ -170,10 +171,10 @@ __global__ void __launch_bounds__(128) lt_corl_kernel(const __grid_constant__ lt
             v = LT_FDIV(v, 4.0f);
             break;
         case LT_CORL_DOF_POS:
-            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(LT_FSUB(p.dof_pos[(size_t)i * D + d], p.default_dof_pos[d])));
+            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(LT_FSUB(p.dof_pos[((size_t)i * D + d) * ds], p.default_dof_pos[d])));
             break;
         case LT_CORL_DOF_VEL:
-            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(p.dof_vel[(size_t)i * D + d]));
+            for (int d = 0; d < D; ++d) v = LT_FADD(v, lt_sq(p.dof_vel[((size_t)i * D + d) * ds]));
             break;
         case LT_CORL_ACTION_SMOOTHNESS_1:                                                                 // CR:94-98
             for (int d = 0; d < D; ++d) {

@@ -21,6 +21,11 @@ __global__ void __launch_bounds__(128) lt_vel_pre_kernel(const __grid_constant__
     const lt_vel_cfg& c = a.c;
     if (i >= c.num_envs) return;
     const lt_vel_ptrs& p = a.p;
+    if (i == 0 && p.torque_counters) {                                                // what lt_compact_kernel does in the trajectory step
+        p.torque_counters[0] += 1;
+        p.torque_counters[1] += c.decimation;
+        p.torque_counters[2] = (p.torque_counters[2] + c.decimation) % c.lag_slots;
+    }
     const int64_t ep = p.episode_length_buf[i] + 1;                                   // LRV:117
     p.episode_length_buf[i] = ep;
     const float* root = p.root_states + (size_t)i * 13;

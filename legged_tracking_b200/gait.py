@@ -93,7 +93,17 @@ class CoRLRewardKernel:
         c.num_envs, c.num_commands = N, int(cmd.shape[1])
         c.num_bodies = int(get("contact_forces").shape[1])
         keep = []
+        c.dof_stride = 1
+        dof_state = env.get("dof_state") if isinstance(env, dict) else getattr(env, "dof_state", None)
         for name in self._PTRS:
+            if name in ("dof_pos", "dof_vel") and dof_state is not None:
+                # Isaac Gym's interleaved [N,12,2] tensor read in place: no contiguous copies of its two columns
+                if dof_state.dtype != torch.float32 or dof_state.device != self.device or not dof_state.is_contiguous():
+                    raise ValueError(f"dof_state: expected a contiguous float32 tensor on {self.device}")
+                c.dof_stride = 2
+                keep.append(dof_state)
+                setattr(p, name, dof_state.data_ptr() + (4 if name == "dof_vel" else 0))
+                continue
             t = get(name)
             if name == "last_contacts":
                 if t.dtype == torch.bool:

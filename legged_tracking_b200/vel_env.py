@@ -179,6 +179,7 @@ class VelocityStepEngine:
                                           tracking_contacts_shaped_vel=0.9)     # train_velocity_tracking.py:24-27
         self.sample_interval = int(float(c["resampling_time"]) / self.dt)
         self.step_count = 0
+        self.bind_inputs = False                  # step(): use the simulator's tensors in place instead of copying them (see step)
         self.heightfield = None
         if heightfield is not None:
             hf = dict(heightfield)
@@ -212,6 +213,7 @@ class VelocityStepEngine:
         v.use_terminal_body_height, v.terminal_body_height = int(bool(c["use_terminal_body_height"])), float(c["terminal_body_height"])
         v.max_episode_length = float(c["max_episode_length"])
         v.sample_interval, v.rand_interval = self.sample_interval, int(float(c["rand_interval"]))
+        v.decimation, v.lag_slots = int(c["decimation"]), int(self.tq.state["lag_buffer"].shape[0])
         v.n_terms = len(self.reward_names)
         for i, n in enumerate(self.reward_names):
             v.term_scales[i] = self.reward_scales[n]
@@ -243,7 +245,7 @@ class VelocityStepEngine:
                  last_last_actions=self.last_last_actions, last_joint_pos_target=self.last_joint_pos_target,
                  last_last_joint_pos_target=self.last_last_joint_pos_target, last_dof_vel=self.last_dof_vel, last_root_vel=self.last_root_vel,
                  obs_buf=self.obs_buf, privileged_obs_buf=self.privileged_obs_buf, obs_history_in=self._hist[self._hist_cur],
-                 obs_history_out=self._hist[1 - self._hist_cur])
+                 obs_history_out=self._hist[1 - self._hist_cur], torque_counters=self.tq.counters)
         if self.heightfield is not None:
             d["measured_height_mean"] = self.measured_height_mean
         if self.device_paths:
@@ -352,18 +354,30 @@ class VelocityStepEngine:
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # ------------------------------------------------------------------------------------------------ the step
-    def step(self, actions, sim, noise_uniforms=None, host_paths=True, uniform_rows=None):
+    def step(self, actions, sim, noise_uniforms=None, host_paths=True, uniform_rows=None, bind=None):
         """actions [N,12]; sim: what PhysX hands back -- dof_state: one [N*12,2] (or [N,12,2]) tensor per sub-step, root [N,13],
         contact [N,B,3], rigid [N,B,13], all on the device.  -> ({'obs','privileged_obs','obs_history'}, rew, done, extras)
         host_paths=False (measurement only) leaves out the three host-orchestrated indexed paths -- command resampling, interval
         DR, reset_idx -- and with them the three nonzero() host reads: what remains is the launch chain alone.
-        uniform_rows (device mode, tests): two [N, LT_VEL_SLOTS] tensors of uniforms for the callback and the reset path."""
+        uniform_rows (device mode, tests): two [N, LT_VEL_SLOTS] tensors of uniforms for the callback and the reset path.
+        bind=True: the simulator's tensors are used in place (a reset then rewrites rows of sim["root"] / the last sim["dof_state"], as
+        the reference rewrites Isaac Gym's tensors) instead of being copied into the engine's own."""
+        bind = self.bind_inputs if bind is None else bind
         for sub, dof in enumerate(sim["dof_state"]):                                  # LRV:76-82: torques, THEN simulate + refresh
             self.apply_torques(actions, sub)
-            self.dof_state.copy_(dof.view(self.N, 12, 2))
-        self.root_states.copy_(sim["root"])
-        self.contact_forces.copy_(sim["contact"])
-        self.rigid_body_state.copy_(sim["rigid"].view(self.rigid_body_state.shape))
+            if bind:
+                self.dof_state = dof.view(self.N, 12, 2)                              # the simulator's tensor itself, as with Isaac Gym
+            else:
+                self.dof_state.copy_(dof.view(self.N, 12, 2))
+        if bind:
+            self.root_states, self.contact_forces = sim["root"], sim["contact"]
+            self.rigid_body_state = sim["rigid"].view(self.N, -1, 13)
+            if self.device_paths:
+                self._dq.dof_state_rw, self._dq.root_states_rw = self.dof_state.data_ptr(), self.root_states.data_ptr()
+        else:
+            self.root_states.copy_(sim["root"])
+            self.contact_forces.copy_(sim["contact"])
+            self.rigid_body_state.copy_(sim["rigid"].view(self.rigid_body_state.shape))
         return self.post_physics_step(noise_uniforms=noise_uniforms, host_paths=host_paths, uniform_rows=uniform_rows)
 
     def begin_step(self, actions):
@@ -376,12 +390,7 @@ class VelocityStepEngine:
 
     def post_physics_step(self, noise_uniforms=None, host_paths=True, uniform_rows=None):
         """LRV:108-154 on the simulator tensors as they stand (root_states, dof_state, contact_forces, rigid_body_state)."""
-        tq, lib, s = self.tq, self.lib, self._stream()
-        # the lag ring and sub-step counters advance with lt_compact_kernel in the trajectory step; here, by hand
-        cnt, n_sub = tq.counters, int(self.cfg["decimation"])
-        cnt[2] = (cnt[2] + n_sub) % tq.state["lag_buffer"].shape[0]
-        cnt[1] += n_sub
-        cnt[0] += 1
+        tq, lib, s = self.tq, self.lib, self._stream()        # (lt_vel_pre advances the torque handle's sub-step / lag-ring counters)
         self.common_step_counter += 1                                                 # LRV:118
         if self.heightfield is not None:                                              # LRV:708-709 (reads this step's root state only)
             hf = self.heightfield
@@ -402,10 +411,9 @@ class VelocityStepEngine:
             self._randomize_dof_props(self.dr_due.nonzero(as_tuple=False).flatten())
         self._gravity_schedule()
         # ---- compute_reward (LRV:281-318)
-        dof_pos, dof_vel = self.dof_state[..., 0].contiguous(), self.dof_state[..., 1].contiguous()
-        env = dict(commands=self.commands, base_lin_vel=self.base_lin_vel, base_ang_vel=self.base_ang_vel, projected_gravity=self.projected_gravity,
-                   gravity_vec=self.gravity_vec, base_pos=self.base_pos, base_quat=self.base_quat, torques=tq.state["torques"], dof_pos=dof_pos,
-                   dof_vel=dof_vel, last_dof_vel=self.last_dof_vel, actions=tq.state["actions"], last_actions=self.last_actions,
+        env = dict(dof_state=self.dof_state, commands=self.commands, base_lin_vel=self.base_lin_vel, base_ang_vel=self.base_ang_vel, projected_gravity=self.projected_gravity,
+                   gravity_vec=self.gravity_vec, base_pos=self.base_pos, base_quat=self.base_quat, torques=tq.state["torques"],
+                   last_dof_vel=self.last_dof_vel, actions=tq.state["actions"], last_actions=self.last_actions,
                    last_last_actions=self.last_last_actions, joint_pos_target=tq.state["joint_pos_target"],
                    last_joint_pos_target=self.last_joint_pos_target, last_last_joint_pos_target=self.last_last_joint_pos_target,
                    contact_forces=self.contact_forces, foot_positions=self.foot_positions, foot_velocities=self.foot_velocities,
@@ -428,7 +436,7 @@ class VelocityStepEngine:
         _abi.check(lib.lt_vel_observe(C.byref(self._vc), C.byref(self._ptrs()), C.c_void_p(nz.data_ptr()) if nz is not None else None,
                                       C.c_uint32(self.step_count & 0xffffffff), s), None, "lt_vel_observe")
         self._hist_cur = 1 - self._hist_cur
-        self._keep = (dof_pos, dof_vel, nz, terms)
+        self._keep = (nz, terms)
         self.extras["privileged_obs"] = self.privileged_obs_buf
         return ({"obs": self.obs_buf, "privileged_obs": self.privileged_obs_buf, "obs_history": self.obs_history}, self.rew_buf,
                 self.reset_buf.bool(), self.extras)

@@ -620,3 +620,30 @@ def test_config_4_trains_end_to_end_with_the_ppo_kernels():
     assert torch.isfinite(after).all() and float((after - before).abs().max()) > 0
     assert runner.alg.actor_critic.num_obs_history == 2100
     assert torch.isfinite(env.obs_buf).all() and torch.isfinite(env.rew_buf).all()
+
+
+@pytest.mark.gpu
+def test_bound_simulator_tensors_give_the_same_steps_as_copied_ones():
+    """bind_inputs: stepping on the simulator's own tensors (re-pointed, rewritten in place on reset) equals stepping on copies."""
+    from legged_tracking_b200 import synthetic
+    g = load()
+    N = 1024
+    engs = []
+    for bind in (False, True):
+        eng, c = _device_engine(g, N, seed=8)
+        eng.bind_inputs = bind
+        synth = synthetic.SyntheticState(N, eng.env_origins.cpu().numpy(), num_bodies=int(c["num_bodies"]), seed=3, feet_indices=list(c["feet_indices"]))
+        eng.episode_length_buf.copy_(synth.initial_episode_length(c["max_episode_length"]).cuda())
+        eng.reset_all()
+        for k in range(6):
+            root = synth.root(k)
+            sim = {"dof_state": [synth.dof_state(k, s).cuda() for s in range(int(c["decimation"]))], "root": root.cuda(), "contact": synth.contact(k).cuda(),
+                   "rigid": synth.rigid(k, root).cuda()}
+            out = eng.step(synth.actions(k).contiguous().cuda(), sim)
+        torch.cuda.synchronize()
+        engs.append((eng, out))
+    (a, oa), (b, ob) = engs
+    for name in ("obs_buf", "obs_history", "rew_buf", "commands", "episode_sums", "command_sums", "episode_length_buf", "root_states", "dof_state",
+                 "last_actions", "cur_weights", "reset_buf"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    assert torch.equal(a.tq.counters, b.tq.counters) and int(a.tq.counters[0]) == 6 and torch.equal(a.tq.state["lag_buffer"], b.tq.state["lag_buffer"])
