@@ -1,5 +1,1 @@
-mkdir -p gpurun_out
-python - <<'PY'
-import json, bench
-print(json.dumps(bench.cfg4_ppo_iteration("cuda:0", 4096)))
-PY
+LT_TORQUE_TC5=1 python profiles/variants.py run 65536 131072 2>&1 | tee gpurun_out/variants_tc5_d.txt

@@ -18,6 +18,9 @@ VARIANTS = {
     "tc5_exp2_nomma": ["TC5_EXP=2"],
     "tc5_exp3_neither": ["TC5_EXP=3"],
 }
+# round-2 experiments on this kernel (64-column TMEM layout at 4..8 CTAs per SM, paired reciprocals, early first fetch, equal tile
+# counts, staggered start): profiles/r02_tc5.md, code in profiles/r02_tc5_experiments.patch
+# earlier ablations: TC5_EXP=1 (no softsign / split arithmetic), 2 (no MMAs), 3 (neither): profiles/r01e_tc5.md
 # FP32-pipe torque kernel variants tuned in an earlier pass (build with only=None): LT_TORQUE_SPT / LT_TORQUE_MINB / LT_TORQUE_THREADS
 
 
