@@ -585,6 +585,10 @@ def run_b200(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     torch.cuda.set_device(local_rank)
     dev = f"cuda:{local_rank}"
+    host_binding = None
+    if world > 1:                              # before any pinned allocation: the staging blocks then land on the GPU's NUMA node
+        from legged_tracking_b200 import dist as lt_dist
+        host_binding = lt_dist.bind_host_to_gpu(local_rank)
     n_env = args.envs_per_gpu
     flat, terrain, act, synth = workload.make(args.config, num_envs=n_env, seed=1000 + rank)
     eng = StepEngine(flat, terrain, act, device=dev, seed=11 + rank, envs_per_warp=args.epw)
@@ -809,7 +813,8 @@ def run_b200(args, rank, world, local_rank):
                     "path": f"engine.HostStepPipeline: {n_chunks} env shards on {n_chunks} streams (H2D, kernels and D2H of different shards overlap)"
                             + ("" if args.no_graph else ", the whole pipelined step replayed as one CUDA graph")
                             if n_chunks > 1 else "single engine, one stream",
-                    "single_stream": {"value": world * n_env * ke / (ms_e2e_single * 1e-3), "ms_per_step": ms_e2e_single / ke}},
+                    "single_stream": {"value": world * n_env * ke / (ms_e2e_single * 1e-3), "ms_per_step": ms_e2e_single / ke},
+                    "host_binding_rank0": host_binding},
             "post_physics_only": {"value": world * n_env / (ms_post * 1e-3), "unit": UNIT, "ms_per_step": ms_post},
             "roofline": roofline}
     if world == 1:

@@ -44,6 +44,43 @@ def init_from_env(backend=None):
     return rank(), world_size(), local
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_host_to_gpu(device_index, sysfs="/sys"):
+    """Pins the calling process to the CPUs of the NUMA node the GPU's PCIe function hangs off, so that the pinned staging blocks a
+    rank allocates afterwards (first touch) and the thread that issues its copies sit on the GPU's side of the host: with one
+    process per GPU the ranks then stop sharing one memory controller for their H2D / D2H traffic.  Nothing is changed when the
+    host exposes no NUMA placement for the device (numa_node < 0: single-node hosts, most VMs) or when the node's CPU list does
+    not intersect the process's current affinity mask.  -> {"pci", "numa_node", "cpus", "bound"}"""
+    info = {"pci": None, "numa_node": None, "cpus": None, "bound": False}
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        pci = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        info["pci"] = pci
+        with open(os.path.join(sysfs, "bus/pci/devices", pci, "numa_node")) as f:
+            node = int(f.read().strip())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open(os.path.join(sysfs, "devices/system/node", f"node{node}", "cpulist")) as f:
+            cpus = _parse_cpulist(f.read()) & set(os.sched_getaffinity(0))
+        info["cpus"] = len(cpus)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["bound"] = True
+    except (OSError, ValueError, AttributeError) as e:
+        info["error"] = f"{type(e).__name__}: {e}"
+    return info
+
+
 def shard_bounds(total, world=None, r=None):
     """Contiguous env shard [lo, hi) of rank r: the first (total % world) ranks get one extra env."""
     world = world_size() if world is None else world
