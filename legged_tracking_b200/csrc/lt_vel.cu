@@ -26,9 +26,34 @@ __global__ void __launch_bounds__(128) lt_vel_pre_kernel(const __grid_constant__
         p.torque_counters[1] += c.decimation;
         p.torque_counters[2] = (p.torque_counters[2] + c.decimation) % c.lag_slots;
     }
+    // every load first, then the arithmetic and the stores: the output arrays are not known to be distinct from the inputs, so a load
+    // written after a store waits for it -- as first written this kernel was a chain of ~10 memory round trips per env
     const int64_t ep = p.episode_length_buf[i] + 1;                                   // LRV:117
+    float root[13], g[3], fnew[4][6], fold[12];
+    {
+        const float* rp = p.root_states + (size_t)i * 13;
+#pragma unroll
+        for (int k = 0; k < 13; ++k) root[k] = rp[k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) g[k] = p.gravity_vec[(size_t)i * 3 + k];
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+            const float* rb = p.rigid_body_state + ((size_t)i * c.num_bodies + c.feet_indices[f]) * 13;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { fnew[f][k] = rb[k]; fnew[f][3 + k] = rb[7 + k]; }
+        }
+#pragma unroll
+        for (int k = 0; k < 12; ++k) fold[k] = p.foot_velocities[(size_t)i * 12 + k];
+    }
+    bool reset = false;                                                               // check_termination (LRV:156-167)
+    for (int t = 0; t < c.n_termination; ++t) {
+        const float* f = p.contact_forces + ((size_t)i * c.num_bodies + c.termination_indices[t]) * 3;
+        reset = reset || (lt_norm3(f[0], f[1], f[2]) > 1.0f);
+    }
+    // mean(root_z - measured_heights) (LRV:163-165): lt_vel_measure_heights' height_mean, or root_z itself on a plane
+    const float clearance = (c.use_terminal_body_height && p.measured_height_mean) ? p.measured_height_mean[i] : root[2];
+
     p.episode_length_buf[i] = ep;
-    const float* root = p.root_states + (size_t)i * 13;
     float q[4], o[3];
     for (int k = 0; k < 3; ++k) p.base_pos[(size_t)i * 3 + k] = root[k];
     for (int k = 0; k < 4; ++k) { q[k] = root[3 + k]; p.base_quat[(size_t)i * 4 + k] = q[k]; }
@@ -36,29 +61,22 @@ __global__ void __launch_bounds__(128) lt_vel_pre_kernel(const __grid_constant__
     for (int k = 0; k < 3; ++k) p.base_lin_vel[(size_t)i * 3 + k] = o[k];
     lt_quat_rotate_inverse(q, root + 10, o);
     for (int k = 0; k < 3; ++k) p.base_ang_vel[(size_t)i * 3 + k] = o[k];
-    lt_quat_rotate_inverse(q, p.gravity_vec + (size_t)i * 3, o);
+    lt_quat_rotate_inverse(q, g, o);
     for (int k = 0; k < 3; ++k) p.projected_gravity[(size_t)i * 3 + k] = o[k];
+#pragma unroll
     for (int f = 0; f < 4; ++f) {                                                     // LRV:127-130; prev_foot_velocities: LRV:74
-        const float* rb = p.rigid_body_state + ((size_t)i * c.num_bodies + c.feet_indices[f]) * 13;
+#pragma unroll
         for (int k = 0; k < 3; ++k) {
             const size_t d = ((size_t)i * 4 + f) * 3 + k;
-            p.prev_foot_velocities[d] = p.foot_velocities[d];
-            p.foot_positions[d] = rb[k];
-            p.foot_velocities[d] = rb[7 + k];
+            p.prev_foot_velocities[d] = fold[3 * f + k];
+            p.foot_positions[d] = fnew[f][k];
+            p.foot_velocities[d] = fnew[f][3 + k];
         }
-    }
-    // check_termination (LRV:156-167)
-    bool reset = false;
-    for (int t = 0; t < c.n_termination; ++t) {
-        const float* f = p.contact_forces + ((size_t)i * c.num_bodies + c.termination_indices[t]) * 3;
-        reset = reset || (lt_norm3(f[0], f[1], f[2]) > 1.0f);
     }
     const bool time_out = (float)ep > c.max_episode_length;
     reset = reset || time_out;
     bool low = false;
     if (c.use_terminal_body_height) {
-        // mean(root_z - measured_heights) (LRV:163-165): lt_vel_measure_heights' height_mean, or root_z itself on a plane
-        const float clearance = p.measured_height_mean ? p.measured_height_mean[i] : root[2];
         low = clearance < c.terminal_body_height;
         reset = reset || low;
     }
@@ -95,15 +113,35 @@ __global__ void __launch_bounds__(128) lt_vel_reward_kernel(const __grid_constan
     const lt_vel_ptrs& p = a.p;
     const size_t N = (size_t)c.num_envs;
     float rew = 0.0f, pos = 0.0f, neg = 0.0f;
-    for (int t = 0; t < c.n_terms; ++t) {
-        const float r = LT_FMUL(a.aux[(size_t)t * N + i], c.term_scales[t]);
-        rew = LT_FADD(rew, r);
-        const double s = p.term_sums[t];
-        if (s >= 0.0) pos = LT_FADD(pos, r);
-        else if (s <= 0.0) neg = LT_FADD(neg, r);
-        p.episode_sums[(size_t)t * N + i] = LT_FADD(p.episode_sums[(size_t)t * N + i], r);
-        const float add = c.command_sum_adds_scale[t] ? LT_FADD(c.term_scales[t], r) : r;         // LRV:296-299
-        p.command_sums[(size_t)t * N + i] = LT_FADD(p.command_sums[(size_t)t * N + i], add);
+    // terms in blocks of CH: every load of a block is issued before its first store (the three arrays are not known to be distinct, so
+    // a rolled loop would wait out one memory round trip per term); the sums themselves stay in term order
+    constexpr int CH = 8;
+    for (int t0 = 0; t0 < c.n_terms; t0 += CH) {
+        float v[CH], es[CH], cs[CH];
+        double ts[CH];
+#pragma unroll
+        for (int k = 0; k < CH; ++k) {
+            const int t = t0 + k;
+            const bool on = t < c.n_terms;
+            const size_t at = (size_t)(on ? t : 0) * N + i;
+            v[k] = on ? a.aux[at] : 0.0f;
+            es[k] = on ? p.episode_sums[at] : 0.0f;
+            cs[k] = on ? p.command_sums[at] : 0.0f;
+            ts[k] = on ? p.term_sums[t] : 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < CH; ++k) {
+            const int t = t0 + k;
+            if (t < c.n_terms) {
+                const float r = LT_FMUL(v[k], c.term_scales[t]);
+                rew = LT_FADD(rew, r);
+                if (ts[k] >= 0.0) pos = LT_FADD(pos, r);
+                else if (ts[k] <= 0.0) neg = LT_FADD(neg, r);
+                p.episode_sums[(size_t)t * N + i] = LT_FADD(es[k], r);
+                const float add = c.command_sum_adds_scale[t] ? LT_FADD(c.term_scales[t], r) : r;     // LRV:296-299
+                p.command_sums[(size_t)t * N + i] = LT_FADD(cs[k], add);
+            }
+        }
     }
     if (c.only_positive_rewards) rew = fmaxf(rew, 0.0f);                                          // LRV:300-301
     else if (c.only_positive_rewards_ji22_style) rew = LT_FMUL(pos, expf(LT_FDIV(neg, c.sigma_rew_neg)));      // LRV:302-303
@@ -201,26 +239,35 @@ __global__ void __launch_bounds__(256) lt_vel_observe_kernel(const __grid_consta
     }
 }
 
-// thread per env: privileged observations (LRV:396-426 for the two flags cfg 4 sets) and the last_* shifts (LRV:143-148)
-__global__ void __launch_bounds__(128) lt_vel_shift_kernel(const __grid_constant__ lt_vel_params a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// privileged observations (LRV:396-426 for the two flags cfg 4 sets) and the last_* shifts (LRV:143-148).  Thread per (env, dof)
+// element: coalesced, and all of an element's loads are issued before its stores; the first 6 N threads also copy one root-velocity
+// component, the first N one env's privileged row.
+__global__ void __launch_bounds__(256) lt_vel_shift_kernel(const __grid_constant__ lt_vel_params a) {
+    const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const lt_vel_cfg& c = a.c;
-    if (i >= c.num_envs) return;
+    const size_t N = (size_t)c.num_envs;
+    if (j >= N * 12) return;
     const lt_vel_ptrs& p = a.p;
-    int k = 0;
-    float* pr = p.privileged_obs_buf + (size_t)i * c.num_privileged_obs;
-    const float clip = c.clip_observations;
-    if (c.priv_observe_friction) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(p.friction_coeffs[i], c.friction_shift), c.friction_scale), -clip), clip);
-    if (c.priv_observe_restitution) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(p.restitutions[i], c.restitution_shift), c.restitution_scale), -clip), clip);
-    for (int d = 0; d < 12; ++d) {
-        const size_t o = (size_t)i * 12 + d;
-        p.last_last_actions[o] = p.last_actions[o];
-        p.last_actions[o] = p.actions[o];
-        p.last_last_joint_pos_target[o] = p.last_joint_pos_target[o];
-        p.last_joint_pos_target[o] = p.joint_pos_target[o];
-        p.last_dof_vel[o] = p.dof_state[o * 2 + 1];
+    const float la = p.last_actions[j], ac = p.actions[j], lt = p.last_joint_pos_target[j], jt = p.joint_pos_target[j], dv = p.dof_state[j * 2 + 1];
+    float rv = 0.0f, fr = 0.0f, re = 0.0f;
+    if (j < N * 6) rv = p.root_states[(j / 6) * 13 + 7 + (j % 6)];
+    if (j < N) {
+        if (c.priv_observe_friction) fr = p.friction_coeffs[j];
+        if (c.priv_observe_restitution) re = p.restitutions[j];
     }
-    for (int d = 0; d < 6; ++d) p.last_root_vel[(size_t)i * 6 + d] = p.root_states[(size_t)i * 13 + 7 + d];
+    p.last_last_actions[j] = la;
+    p.last_actions[j] = ac;
+    p.last_last_joint_pos_target[j] = lt;
+    p.last_joint_pos_target[j] = jt;
+    p.last_dof_vel[j] = dv;
+    if (j < N * 6) p.last_root_vel[j] = rv;
+    if (j < N) {
+        int k = 0;
+        float* pr = p.privileged_obs_buf + j * c.num_privileged_obs;
+        const float clip = c.clip_observations;
+        if (c.priv_observe_friction) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(fr, c.friction_shift), c.friction_scale), -clip), clip);
+        if (c.priv_observe_restitution) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(re, c.restitution_shift), c.restitution_scale), -clip), clip);
+    }
 }
 // last launch of a step: the device-side step counter moves on (its readers of this step are all behind it on the stream)
 __global__ void lt_vel_step_counter_kernel(uint32_t* counter) { *counter += 1u; }
@@ -570,7 +617,7 @@ int lt_vel_observe(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* 
     (void)row;
     if (vec2) lt_vel_observe_kernel<2><<<cfg->num_envs, 256, 0, s>>>(a);
     else lt_vel_observe_kernel<1><<<cfg->num_envs, 256, 0, s>>>(a);
-    lt_vel_shift_kernel<<<(cfg->num_envs + 127) / 128, 128, 0, s>>>(a);               // after the observation read last_actions
+    lt_vel_shift_kernel<<<(unsigned)(((size_t)cfg->num_envs * 12 + 255) / 256), 256, 0, s>>>(a);      // after the observation read last_actions
     if (p.step_counter) lt_vel_step_counter_kernel<<<1, 1, 0, s>>>(p.step_counter);
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }

@@ -23,6 +23,7 @@ def main():
     eng = vel_env.VelocityStepEngine(cfg, n, origins, workload.load_actuator(), "device", device="cuda:0", seed=9, heightfield=field)
     synth = synthetic.SyntheticState(n, origins, num_bodies=int(cfg["num_bodies"]), seed=77, feet_indices=list(cfg["feet_indices"]))
     eng.episode_length_buf.copy_(synth.initial_episode_length(cfg["max_episode_length"]).cuda())
+    eng.bind_inputs = True
     eng.reset_all()
     for k in range(steps):
         root = synth.root(k % 3)
