@@ -404,6 +404,11 @@ __global__ void __launch_bounds__(LT_STEP_THREADS) lt_step_kernel(const __grid_c
     const int i = env0 + lane;
 
     // ---- phase 0
+    {   // the contact-force tile (read by the sweep below in three dependent batches): its lines requested now, under the tile loads
+        const char* cgb = reinterpret_cast<const char*>(p.sim.contact_forces + (size_t)env0 * B3);
+        const int bytes = nv * B3 * 4;
+        for (int o = lane * 128; o < bytes; o += 32 * 128) lt_prefetch(cgb + o);
+    }
     lt_tile_load(s_root, p.sim.root_states + (size_t)env0 * A13, nv * A13, lane, full);
     lt_tile_load(s_dof, p.sim.dof_state + (size_t)env0 * LT_ND * 2, nv * LT_ND * 2, lane, full);
     // net contact forces: never staged.  Lane <-> (env, body) pair, so that the tile is read as one coalesced stream, and
