@@ -535,7 +535,9 @@ typedef struct lt_vel_dev_ptrs {
     float *lag_buffer;                               /* [lag_slots, N, 12] */
     float *gait_indices, *feet_air_time;             /* [N], [N,4] */
     float* episode_acc;                              /* [n_terms + 2] */
-    int32_t *work_env, *work_code, *work_count;      /* [N], [N], [1] scratch: the envs with indexed work this call, compacted */
+    int32_t *work_env, *work_code, *work_count;      /* [N], [N], [3] scratch: the envs with indexed work this call, compacted;
+                                                        work_count = {collecting, published length, block ticket}, ZERO before the
+                                                        first call (the kernels leave [0] and [2] zero again) */
 } lt_vel_dev_ptrs;
 /* sizeof of the cfg 4 structs as compiled (0 lt_vel_cfg, 1 lt_vel_ptrs, 2 lt_vel_dev_cfg, 3 lt_vel_dev_ptrs, 4 lt_cmd_cfg): binding check */
 int lt_vel_struct_bytes(int32_t which);

@@ -248,6 +248,9 @@ __global__ void __launch_bounds__(256) lt_vel_shift_kernel(const __grid_constant
     const size_t N = (size_t)c.num_envs;
     if (j >= N * 12) return;
     const lt_vel_ptrs& p = a.p;
+    // last launch of a step: the device-side step counter moves on (its readers of this step are all behind this launch on the stream,
+    // and nothing in this kernel reads it)
+    if (j == 0 && p.step_counter) *p.step_counter += 1u;
     const float la = p.last_actions[j], ac = p.actions[j], lt = p.last_joint_pos_target[j], jt = p.joint_pos_target[j], dv = p.dof_state[j * 2 + 1];
     float rv = 0.0f, fr = 0.0f, re = 0.0f;
     if (j < N * 6) rv = p.root_states[(j / 6) * 13 + 7 + (j % 6)];
@@ -269,8 +272,6 @@ __global__ void __launch_bounds__(256) lt_vel_shift_kernel(const __grid_constant
         if (c.priv_observe_restitution) pr[k++] = fminf(fmaxf(LT_FMUL(LT_FSUB(re, c.restitution_shift), c.restitution_scale), -clip), clip);
     }
 }
-// last launch of a step: the device-side step counter moves on (its readers of this step are all behind it on the stream)
-__global__ void lt_vel_step_counter_kernel(uint32_t* counter) { *counter += 1u; }
 
 // ------------------------------------------------------------------------------------------------ _get_heights (LRV:1790-1824)
 struct lt_vel_height_params {
@@ -339,10 +340,11 @@ __device__ __forceinline__ bool lt_vel_mask_resample(const lt_vel_dev_params& a,
     return (a.which == LT_VEL_PATH_RESET ? a.p.reset_buf[i] : a.p.resample_due[i]) != 0;
 }
 
-// curriculum.update, phase A (curriculum.py:133-152): successes mark their own bin and count into every adjacent bin
-__global__ void __launch_bounds__(128) lt_cur_hits_kernel(const __grid_constant__ lt_vel_dev_params a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.c.num_envs || !lt_vel_mask_resample(a, i) || a.d.n_keys == 0) return;
+// curriculum.update (curriculum.py:133-152) for env i: a success marks its own bin and counts into every adjacent bin (phase A);
+// phase B -- weights[b] = clip(weights[b] + 0.2, 0, 1), once for the bin itself and once per adjacent success -- runs in the last
+// block of lt_vel_scan_kernel, when every env's marks are in.
+__device__ __forceinline__ void lt_cur_hits(const lt_vel_dev_params& a, int i) {
+    if (a.d.n_keys == 0) return;
     const size_t N = (size_t)a.c.num_envs;
     bool ok = true;
     for (int k = 0; k < a.d.n_keys; ++k)
@@ -359,17 +361,6 @@ __global__ void __launch_bounds__(128) lt_cur_hits_kernel(const __grid_constant_
         if (adj) atomicAdd(a.q.hit_adj + cat * nb + g, 1);
     }
 }
-// phase B: weights[b] = clip(weights[b] + 0.2, 0, 1), once for the bin itself and once per adjacent success
-__global__ void lt_cur_apply_kernel(double* w, int32_t* hit_self, int32_t* hit_adj, int n) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
-    const int k = hit_self[j] + hit_adj[j];
-    double v = w[j];
-    for (int r = 0; r < k; ++r) v = fmin(fmax(v + 0.2, 0.0), 1.0);
-    w[j] = v;
-    hit_self[j] = 0;
-    hit_adj[j] = 0;
-}
 
 // Philox uniform of (env, slot) for the indexed paths, or the injected row
 __device__ __forceinline__ float lt_vel_u(const lt_vel_dev_params& a, int i, int slot) {
@@ -380,25 +371,53 @@ __device__ __forceinline__ float lt_vel_u(const lt_vel_dev_params& a, int i, int
     return lt_u01(o[slot & 3]);
 }
 
-// Pass 1, thread per env: which envs have indexed work this call, compacted (unordered) into work_env / work_code.
-//   code bit 0 resample, bit 1 interval / reset DR, bit 2 reset
-__global__ void __launch_bounds__(256) lt_vel_mark_kernel(const __grid_constant__ lt_vel_dev_params a) {
+// Pass 1, thread per env, ONE launch: the curriculum's success marks of the envs about to be resampled, and which envs have indexed
+// work this call, compacted (unordered) into work_env / work_code (code bit 0 resample, bit 1 interval / reset DR, bit 2 reset).  The
+// block that finishes last (ticket in work_count[2]) then applies the marks to the weights and publishes the list length:
+// work_count[0] collects, work_count[1] is what lt_vel_paths_kernel reads; [0] and [2] are left zero for the next call, so the step
+// needs neither a memset nor separate hit / apply / mark launches.
+__global__ void __launch_bounds__(256) lt_vel_scan_kernel(const __grid_constant__ lt_vel_dev_params a) {
+    __shared__ int s_last;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool in = i < a.c.num_envs;
     const bool reset = in && a.which == LT_VEL_PATH_RESET && a.p.reset_buf[i];
     const bool resample = in && lt_vel_mask_resample(a, i);
     const bool dr = in && (a.which == LT_VEL_PATH_RESET ? reset : (a.p.dr_due[i] != 0));
+    if (resample) lt_cur_hits(a, i);
     const int code = (resample ? 1 : 0) | (dr ? 2 : 0) | (reset ? 4 : 0);
     const unsigned m = __ballot_sync(0xffffffffu, code != 0);
-    if (m == 0u) return;
-    const int lane = threadIdx.x & 31;
-    int base = 0;
-    if (lane == 0) base = atomicAdd(a.q.work_count, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (code) {
-        const int slot = base + __popc(m & ((1u << lane) - 1u));
-        a.q.work_env[slot] = i;
-        a.q.work_code[slot] = code;
+    if (m != 0u) {
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(a.q.work_count, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (code) {
+            const int slot = base + __popc(m & ((1u << lane) - 1u));
+            a.q.work_env[slot] = i;
+            a.q.work_code[slot] = code;
+        }
+    }
+    __threadfence();                                                                 // this thread's marks and list entries before its block's ticket
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(a.q.work_count + 2, 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int nw = a.d.cmd.n_categories * a.d.n_bins;
+    for (int j = threadIdx.x; j < nw; j += blockDim.x) {
+        const int k = __ldcg(a.q.hit_self + j) + __ldcg(a.q.hit_adj + j);
+        if (k) {
+            double v = a.q.weights[j];
+            for (int r = 0; r < k; ++r) v = fmin(fmax(v + 0.2, 0.0), 1.0);
+            a.q.weights[j] = v;
+            a.q.hit_self[j] = 0;
+            a.q.hit_adj[j] = 0;
+        }
+    }
+    if (threadIdx.x == 0) {
+        a.q.work_count[1] = __ldcg(a.q.work_count);
+        a.q.work_count[0] = 0;
+        a.q.work_count[2] = 0;
     }
 }
 
@@ -409,7 +428,7 @@ __global__ void __launch_bounds__(256) lt_vel_paths_kernel(const __grid_constant
     const lt_vel_cfg& c = a.c;
     const lt_vel_dev_cfg& d = a.d;
     const lt_vel_dev_ptrs& q = a.q;
-    const int count = *q.work_count;
+    const int count = q.work_count[1];
     const int warps = blockDim.x >> 5;
     if ((int)blockIdx.x * warps >= count) return;                                    // block-uniform
     const int lane = threadIdx.x & 31, wi = blockIdx.x * warps + (threadIdx.x >> 5);
@@ -568,10 +587,8 @@ int lt_vel_indexed_paths(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const l
     lt_vel_dev_params a;
     a.c = *cfg; a.p = p; a.d = d; a.q = *dptrs; a.uniform_rows = uniform_rows; a.step = step; a.which = which;
     const int n = cfg->num_envs, nw = d.cmd.n_categories * d.n_bins;
-    if (cudaMemsetAsync(dptrs->work_count, 0, sizeof(int32_t), s) != cudaSuccess) return LT_ERR_CUDA;
-    lt_cur_hits_kernel<<<(n + 127) / 128, 128, 0, s>>>(a);
-    lt_cur_apply_kernel<<<(nw + 127) / 128, 128, 0, s>>>(dptrs->weights, dptrs->hit_self, dptrs->hit_adj, nw);
-    lt_vel_mark_kernel<<<(n + 255) / 256, 256, 0, s>>>(a);
+    (void)nw;
+    lt_vel_scan_kernel<<<(n + 255) / 256, 256, 0, s>>>(a);
     lt_vel_paths_kernel<<<(n + 7) / 8, 256, 0, s>>>(a);              // a warp per listed env; blocks past the list's end return at once
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }
@@ -618,7 +635,6 @@ int lt_vel_observe(const lt_vel_cfg* cfg, const lt_vel_ptrs* ptrs, const float* 
     if (vec2) lt_vel_observe_kernel<2><<<cfg->num_envs, 256, 0, s>>>(a);
     else lt_vel_observe_kernel<1><<<cfg->num_envs, 256, 0, s>>>(a);
     lt_vel_shift_kernel<<<(unsigned)(((size_t)cfg->num_envs * 12 + 255) / 256), 256, 0, s>>>(a);      // after the observation read last_actions
-    if (p.step_counter) lt_vel_step_counter_kernel<<<1, 1, 0, s>>>(p.step_counter);
     return cudaGetLastError() == cudaSuccess ? LT_OK : LT_ERR_CUDA;
 }
 

@@ -266,7 +266,7 @@ class VelocityStepEngine:
         self.env_categories_dev = torch.zeros(N, dtype=torch.int32, device=dev)
         self.episode_acc = torch.zeros(len(self.reward_names) + 2, device=dev)
         self._work = torch.zeros(2, N, dtype=torch.int32, device=dev)
-        self._work_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._work_count = torch.zeros(3, dtype=torch.int32, device=dev)        # {collecting, published, ticket}: lt_vel_scan_kernel
         self.step_counter_dev = torch.zeros(1, dtype=torch.int32, device=dev)       # Philox step key of the device mode (uint32 bits)
         d = _abi.lt_vel_dev_cfg()
         d.n_bins, d.n_dims = nb, grid.shape[0]
