@@ -14,6 +14,6 @@ for n in 4096 65536; do
 timeout 300 python profiles/run_cfg4.py $n 4 > gpurun_out/run_cfg4_$n.log 2>&1 && \
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:lt_ -c 200 --csv --log-file gpurun_out/${TAG}_cfg4_launches_$n.csv python profiles/run_cfg4.py $n 4 > gpurun_out/ncu_cfg4_$n.log 2>&1
 done
-timeout 900 ncu --set full --clock-control none -k regex:lt_ --launch-skip 50 --launch-count 21 -o /tmp/${TAG}_cfg4_full -f python profiles/run_cfg4.py 65536 4 > gpurun_out/ncu_cfg4_full.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:lt_ --launch-skip 50 --launch-count 16 -o /tmp/${TAG}_cfg4_full -f python profiles/run_cfg4.py 65536 4 > gpurun_out/ncu_cfg4_full.log 2>&1
 ncu -i /tmp/${TAG}_cfg4_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_cfg4_full_raw.csv 2>/dev/null
 du -sh gpurun_out
