@@ -163,6 +163,16 @@ __device__ __forceinline__ float tc5_softsign(float x) {
     return x * r;
 }
 
+#ifdef TC5_TRACE
+// timing study only (profiles/tc5_trace.py, profiles/r02_tc5.md): %globaltimer stamps of each CTA's phases
+__device__ unsigned long long g_tc5_trace[2048 * 8];
+__device__ __forceinline__ unsigned long long tc5_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TC5_STAMP(k) do { if (threadIdx.x == 0 && blockIdx.x < 2048) g_tc5_trace[blockIdx.x * 8 + (k)] = tc5_now(); } while (0)
+extern "C" int lt_tc5_trace_read(unsigned long long* out) { return (int)cudaMemcpyFromSymbol(out, g_tc5_trace, sizeof(unsigned long long) * 2048 * 8); }
+#else
+#define TC5_STAMP(k) do {} while (0)
+#endif
+
 struct tc5_raw {                       // the ten words a sample reads (the prefetch unit)
     float act, pos, vel, moff, mstr, el, ell, vl, vll, lag;
 };
@@ -187,6 +197,7 @@ __global__ void __launch_bounds__(TC5_THREADS, 4) lt_torque_tc5_kernel(const __g
     const lt_config& c = p.c;
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t n = (uint32_t)c.num_envs * LT_ND;
+    TC5_STAMP(0);
 
     // one-time setup: weights to shared memory, mbarriers, TMEM allocation (warp 0)
     for (int k = tid; k < TC5_BLOB_BYTES / 16; k += TC5_THREADS)
@@ -204,6 +215,7 @@ __global__ void __launch_bounds__(TC5_THREADS, 4) lt_torque_tc5_kernel(const __g
     tc5_fence_before();
     __syncthreads();
     tc5_fence_after();
+    TC5_STAMP(1);
     const uint32_t tmem = s_tmem;
     const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);      // this warp's 32 TMEM lanes
 
@@ -235,7 +247,9 @@ __global__ void __launch_bounds__(TC5_THREADS, 4) lt_torque_tc5_kernel(const __g
         tc5_fetch(p, s0 < n ? s0 : n - 1, n, rd_fetch, cur);
     }
 
+    TC5_STAMP(2);
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        if (tile == (int)blockIdx.x + (int)gridDim.x) TC5_STAMP(4);
         const uint32_t s_raw = (uint32_t)tile * TC5_THREADS + tid;
         const bool valid = s_raw < n;
         const uint32_t s = valid ? s_raw : n - 1;
@@ -262,6 +276,7 @@ __global__ void __launch_bounds__(TC5_THREADS, 4) lt_torque_tc5_kernel(const __g
         }
         float x[LT_ACT_IN], tq = 0.0f;
         lt_torque_pre(c, dof, io, x, tq);
+        if (tile == (int)blockIdx.x) TC5_STAMP(3);
         if (head >= 0 && valid) p.st.lag_buffer[(size_t)head * n + s] = io.action_scaled;
 
         // ---- layer 1 operand row: k = 0..5 inputs, k = 6 the constant 1 (bias), rest zero; hi and lo parts
@@ -345,8 +360,10 @@ __global__ void __launch_bounds__(TC5_THREADS, 4) lt_torque_tc5_kernel(const __g
         // the next tile's tcgen05.st must not overtake this tile's tcgen05.ld of other warps' lanes: lanes are private, the MMA
         // of the next tile is issued only after the __syncthreads that follows every warp's loads -- nothing more is needed
     }
+    TC5_STAMP(5);
     tc5_fence_before();
     __syncthreads();
+    TC5_STAMP(6);
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TC5_COLS) : "memory");
 }
 

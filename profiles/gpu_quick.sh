@@ -1,8 +1,3 @@
-timeout 900 python -m pytest tests/test_vel_env.py tests/test_gait_corl.py tests/test_commands.py -m gpu -q -x 2>&1 | tail -n 4
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -n 2
-python - <<PY
-import bench
-for n in (4096, 65536):
-    r = bench.cfg4_step_timing("cuda:0", n, steps=40)
-    print(n, round(r["ms_per_step"],3), round(r["device_mode"]["ms_per_step"],3), round(r["device_mode"]["graph_replay"]["ms_per_step"],4), round(r["device_mode"]["graph_replay"]["value"]/1e6,1))
-PY
+LT_TORQUE_TC5=1 python profiles/variants.py run 65536 131072 32768 2>&1 | tee gpurun_out/variants_tc5_dyn2.txt
+LT_B200_LIB=build/variants/tc5_dyn1.so timeout 600 python -m pytest tests/test_gpu_step.py -m gpu -q -x -k tc5 2>&1 | tail -n 1
+LT_TORQUE_TC5=1 LT_B200_LIB=build/variants/tc5_dyn1_trace.so python profiles/tc5_trace.py 65536 2>&1 | tail -n 10

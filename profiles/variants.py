@@ -17,6 +17,7 @@ VARIANTS = {
     "tc5_exp1_noalu": ["TC5_EXP=1"],
     "tc5_exp2_nomma": ["TC5_EXP=2"],
     "tc5_exp3_neither": ["TC5_EXP=3"],
+    "tc5_trace": ["TC5_TRACE=1"],          # per-CTA phase stamps: LT_TORQUE_TC5=1 LT_B200_LIB=build/variants/tc5_trace.so python profiles/tc5_trace.py
 }
 # round-2 experiments on this kernel (64-column TMEM layout at 4..8 CTAs per SM, paired reciprocals, early first fetch, equal tile
 # counts, staggered start): profiles/r02_tc5.md, code in profiles/r02_tc5_experiments.patch
