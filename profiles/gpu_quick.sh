@@ -1,3 +1,7 @@
-LT_TORQUE_TC5=1 python profiles/variants.py run 65536 131072 32768 2>&1 | tee gpurun_out/variants_tc5_dyn2.txt
-LT_B200_LIB=build/variants/tc5_dyn1.so timeout 600 python -m pytest tests/test_gpu_step.py -m gpu -q -x -k tc5 2>&1 | tail -n 1
-LT_TORQUE_TC5=1 LT_B200_LIB=build/variants/tc5_dyn1_trace.so python profiles/tc5_trace.py 65536 2>&1 | tail -n 10
+# scratch: last sanity check of the shipped build
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 2
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -n 3
+timeout 600 python bench.py --steps 200 --warmup 5 2>/dev/null | python -c "
+import sys, json
+d = json.loads([l for l in sys.stdin if l.startswith('{')][-1])
+print(d['value'] / 1e6, d['ms_per_step'], d['e2e']['value'] / 1e6, d['roofline']['frac'], d['roofline']['kernels']['post_physics']['frac'])"
